@@ -1,0 +1,83 @@
+"""ctypes binding of libimgtx.so (the C ABI declared in include/imgtx.h).
+
+There is deliberately no fallback: if the shared library is missing or a call fails, we raise.  The
+product path never routes through CPU code.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libimgtx.so")
+
+_lib = None
+
+
+class ImgtxError(RuntimeError):
+    pass
+
+
+class GeomRecord(C.Structure):
+    """imgtx_geom_t (64 bytes)."""
+    _fields_ = [("kind", C.c_int32), ("dx", C.c_int32), ("dy", C.c_int32), ("pad", C.c_int32),
+                ("m", C.c_double * 6)]
+
+
+# enums (mirrors include/imgtx.h)
+PW_BRIGHTNESS, PW_SCALE_ABS, PW_POSTERIZE, PW_SOLARIZE, PW_IDENTITY = range(5)
+(GEOM_IDENTITY, GEOM_AFFINE, GEOM_SHIFT, GEOM_FLIP_LR, GEOM_CROP_REFLECT, GEOM_ROT180, GEOM_ROT90,
+ GEOM_ROT270) = range(8)
+TOU8_DENORMALIZE, TOU8_CLAMP01 = 1, 2
+CLAMP_NONE, CLAMP_SCALAR, CLAMP_PER_CHANNEL = range(3)
+FC_GAUSSIAN_NOISE, FC_BRIGHTNESS, FC_CONTRAST, FC_ADD_NOISE = range(4)
+MAX_EPS = 8
+
+_vp = C.c_void_p
+_i64 = C.c_int64
+_int = C.c_int
+_f = C.c_float
+
+# name -> argtypes (restype is always int unless listed in _RESTYPES)
+_PROTOS = {
+    "imgtx_version": [],
+    "imgtx_last_error": [],
+    "imgtx_device_info": [C.POINTER(C.c_int), C.POINTER(C.c_int)],
+    "imgtx_set_tuning": [_int, _int, _int],
+    "imgtx_pointwise_u8": [_vp, _vp, _i64, _i64, _int, _f, _vp, _vp],
+    "imgtx_geometry_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, C.POINTER(GeomRecord), _vp, _vp, _vp],
+    "imgtx_to_tensor_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp],
+    "imgtx_to_uint8_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _int, _vp],
+    "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
+    "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
+    "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
+}
+_RESTYPES = {"imgtx_last_error": C.c_char_p}
+
+
+def load():
+    """Load libimgtx.so (once). Raises ImportError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(or `make -C imagetransformations_b200/csrc`). There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, argtypes in _PROTOS.items():
+        fn = getattr(lib, name)  # AttributeError if the .so is stale: fail loudly
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPES.get(name, C.c_int)
+    _lib = lib
+    return lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().imgtx_last_error()
+        raise ImgtxError(f"libimgtx error {rc}: {msg.decode() if msg else '?'}")
+
+
+def exported_names():
+    return list(_PROTOS)

@@ -1,0 +1,312 @@
+"""Batched device API: torch CUDA tensors in, torch CUDA tensors out, every op one call into libimgtx.
+
+uint8 image batches are (n, h, w, c) contiguous; float batches are (n, c, h, w) float32 contiguous.
+PyTorch is used for device memory and streams only; all arithmetic is in the CUDA library.
+Per-image parameters may be Python scalars (uniform over the batch), sequences / numpy arrays or
+tensors of length n.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+GEOM_DTYPE = np.dtype([("kind", "<i4"), ("dx", "<i4"), ("dy", "<i4"), ("pad", "<i4"), ("m", "<f8", (6,))])
+assert GEOM_DTYPE.itemsize == C.sizeof(L.GeomRecord) == 64
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _check_u8(x: torch.Tensor) -> torch.Tensor:
+    if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.uint8 and x.dim() == 4):
+        raise TypeError("expected a CUDA uint8 tensor of shape (n, h, w, c)")
+    return x.contiguous()
+
+
+def _check_f32(x: torch.Tensor) -> torch.Tensor:
+    if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.float32):
+        raise TypeError("expected a CUDA float32 tensor")
+    return x.contiguous()
+
+
+def _per_image_f32(param, n: int, device) -> Optional[torch.Tensor]:
+    """None for a scalar, else a device f32 tensor of length n."""
+    if isinstance(param, torch.Tensor):
+        if param.numel() == 1 and param.dim() == 0:
+            return None
+        t = param.to(device=device, dtype=torch.float32).contiguous()
+    elif np.isscalar(param):
+        return None
+    else:
+        t = torch.from_numpy(np.asarray(param, dtype=np.float64).astype(np.float32)).to(device)
+    if t.numel() != n:
+        raise ValueError(f"per-image parameter has {t.numel()} entries for {n} images")
+    return t
+
+
+def _fptr(a: Optional[Sequence[float]]):
+    if a is None:
+        return None, None
+    arr = (C.c_float * len(a))(*[float(v) for v in a])
+    return arr, C.cast(arr, C.c_void_p)
+
+
+# ------------------------------------------------------------------------------------------------
+# pointwise
+# ------------------------------------------------------------------------------------------------
+def pointwise(x: torch.Tensor, op: int, param, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    x = _check_u8(x)
+    n = x.shape[0]
+    out = torch.empty_like(x) if out is None else out
+    per = _per_image_f32(param, n, x.device)
+    scalar = 0.0 if per is not None else float(param)
+    image_bytes = x[0].numel() if n else 0
+    L.check(L.load().imgtx_pointwise_u8(x.data_ptr(), out.data_ptr(), n, image_bytes, op, scalar,
+                                        per.data_ptr() if per is not None else None, _stream()))
+    return out
+
+
+def brightness(x, factor, out=None):
+    """ImageEnhance.Brightness(img).enhance(factor) on a batch."""
+    return pointwise(x, L.PW_BRIGHTNESS, factor, out)
+
+
+def convert_scale_abs(x, alpha, out=None):
+    """cv2.convertScaleAbs(img, alpha=alpha, beta=0) on a batch."""
+    return pointwise(x, L.PW_SCALE_ABS, alpha, out)
+
+
+def posterize(x, bits, out=None):
+    return pointwise(x, L.PW_POSTERIZE, bits, out)
+
+
+def solarize(x, threshold, out=None):
+    return pointwise(x, L.PW_SOLARIZE, threshold, out)
+
+
+# ------------------------------------------------------------------------------------------------
+# geometry
+# ------------------------------------------------------------------------------------------------
+def geom_records(n: int) -> np.ndarray:
+    return np.zeros(n, dtype=GEOM_DTYPE)
+
+
+def geometry(x: torch.Tensor, rec, out_hw=None, fill=None, out=None) -> torch.Tensor:
+    """rec: one GEOM_DTYPE record (uniform) or an array of n records (per image), or a device uint8
+    tensor holding n packed records."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    oh, ow = out_hw if out_hw is not None else (h, w)
+    out = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device) if out is None else out
+    uni = None
+    per_ptr = None
+    keep = None
+    if isinstance(rec, torch.Tensor):
+        if rec.numel() != n * 64:
+            raise ValueError("packed geometry tensor has the wrong size")
+        keep = rec
+        per_ptr = rec.data_ptr()
+    else:
+        rec = np.asarray(rec, dtype=GEOM_DTYPE).reshape(-1)
+        if rec.size == 1:
+            uni = L.GeomRecord.from_buffer_copy(rec.tobytes())
+        else:
+            if rec.size != n:
+                raise ValueError(f"{rec.size} geometry records for {n} images")
+            keep = torch.from_numpy(rec.view(np.uint8).copy()).to(x.device)
+            per_ptr = keep.data_ptr()
+    fill_arr = None
+    if fill is not None:
+        fv = [int(v) for v in (fill if isinstance(fill, (tuple, list)) else [fill] * c)]
+        fv = (fv + [0] * 4)[:4]
+        fill_arr = (C.c_uint8 * 4)(*fv)
+    L.check(L.load().imgtx_geometry_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, oh, ow,
+                                       C.byref(uni) if uni is not None else None, per_ptr,
+                                       C.cast(fill_arr, C.c_void_p) if fill_arr is not None else None,
+                                       _stream()))
+    return out
+
+
+def pil_rotate_matrix(angle: float, w: int, h: int):
+    """The coefficient list PIL.Image.rotate(angle, expand=False) builds in Python before calling C."""
+    angle = angle % 360.0
+    a = -math.radians(angle)
+    m = [round(math.cos(a), 15), round(math.sin(a), 15), 0.0,
+         round(-math.sin(a), 15), round(math.cos(a), 15), 0.0]
+    cx, cy = w / 2.0, h / 2.0
+    m[2] = m[0] * (-cx) + m[1] * (-cy) + m[2] + cx
+    m[5] = m[3] * (-cx) + m[4] * (-cy) + m[5] + cy
+    return m
+
+
+def rotate_records(angles, w: int, h: int) -> np.ndarray:
+    """Geometry records reproducing img.rotate(angle) (counter-clockwise degrees, NEAREST)."""
+    angles = np.atleast_1d(np.asarray(angles, dtype=np.float64))
+    rec = geom_records(len(angles))
+    for i, ang in enumerate(angles):
+        a = float(ang) % 360.0
+        if a == 0:
+            rec[i]["kind"] = L.GEOM_IDENTITY
+        elif a == 180:
+            rec[i]["kind"] = L.GEOM_ROT180
+        elif a in (90.0, 270.0) and w == h:
+            rec[i]["kind"] = L.GEOM_ROT90 if a == 90 else L.GEOM_ROT270
+        else:
+            rec[i]["kind"] = L.GEOM_AFFINE
+            rec[i]["m"] = pil_rotate_matrix(a, w, h)
+    return rec
+
+
+def rotate(x, angle, fill=0, out=None):
+    """PIL img.rotate(angle, fillcolor=fill): angle scalar or per image."""
+    n, h, w, c = x.shape
+    rec = rotate_records(angle, w, h)
+    return geometry(x, rec, fill=fill, out=out)
+
+
+def affine_nearest(x, m, out_hw=None, fill=0, out=None):
+    """PIL img.transform(size, AFFINE, m) with NEAREST resampling; m is (6,) or (n, 6)."""
+    m = np.asarray(m, dtype=np.float64)
+    rec = geom_records(1 if m.ndim == 1 else m.shape[0])
+    rec["kind"] = L.GEOM_AFFINE
+    rec["m"] = m.reshape(-1, 6)
+    return geometry(x, rec, out_hw=out_hw, fill=fill, out=out)
+
+
+def translate(x, tx, ty, out=None):
+    """reference apply_translation: integer shift with zero fill (int() truncation of tx, ty)."""
+    tx = np.atleast_1d(np.asarray(tx))
+    ty = np.atleast_1d(np.asarray(ty))
+    k = max(len(tx), len(ty))
+    rec = geom_records(k)
+    rec["kind"] = L.GEOM_SHIFT
+    rec["dx"] = np.trunc(np.broadcast_to(tx, (k,)).astype(np.float64)).astype(np.int32)
+    rec["dy"] = np.trunc(np.broadcast_to(ty, (k,)).astype(np.float64)).astype(np.int32)
+    return geometry(x, rec, out=out)
+
+
+def hflip(x, out=None):
+    rec = geom_records(1)
+    rec["kind"] = L.GEOM_FLIP_LR
+    return geometry(x, rec, out=out)
+
+
+def crop_reflect(x, i, j, pad: int, size: int, out=None):
+    """T.RandomCrop(size, padding=pad, padding_mode='reflect') with the drawn offsets (i: row, j: col)."""
+    i = np.atleast_1d(np.asarray(i))
+    j = np.atleast_1d(np.asarray(j))
+    k = max(len(i), len(j))
+    rec = geom_records(k)
+    rec["kind"] = L.GEOM_CROP_REFLECT
+    rec["dy"] = np.broadcast_to(i, (k,))
+    rec["dx"] = np.broadcast_to(j, (k,))
+    rec["pad"] = pad
+    return geometry(x, rec, out_hw=(size, size), out=out)
+
+
+# ------------------------------------------------------------------------------------------------
+# tensors
+# ------------------------------------------------------------------------------------------------
+def to_tensor(x: torch.Tensor, mean=None, std=None, out=None) -> torch.Tensor:
+    """ToTensor() [+ Normalize(mean, std)]: (n,h,w,c) u8 -> (n,c,h,w) f32."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty((n, c, h, w), dtype=torch.float32, device=x.device) if out is None else out
+    mk, mp = _fptr(mean)
+    sk, sp = _fptr(std)
+    L.check(L.load().imgtx_to_tensor_f32(x.data_ptr(), out.data_ptr(), n, h, w, c, mp, sp, _stream()))
+    return out
+
+
+def to_uint8(t: torch.Tensor, mean=None, std=None, clamp=False, out=None) -> torch.Tensor:
+    """tensor_to_pil (mean/std given, clamp=True) or TF.to_pil_image (plain): (n,c,h,w) f32 -> (n,h,w,c) u8."""
+    t = _check_f32(t)
+    n, c, h, w = t.shape
+    out = torch.empty((n, h, w, c), dtype=torch.uint8, device=t.device) if out is None else out
+    flags = (L.TOU8_DENORMALIZE if mean is not None else 0) | (L.TOU8_CLAMP01 if clamp else 0)
+    mk, mp = _fptr(mean)
+    sk, sp = _fptr(std)
+    L.check(L.load().imgtx_to_uint8_f32(t.data_ptr(), out.data_ptr(), n, h, w, c, mp, sp, flags, _stream()))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# sign-step family
+# ------------------------------------------------------------------------------------------------
+def _bounds(lo, hi, c):
+    if lo is None:
+        return L.CLAMP_NONE, None, None, None, None
+    lo_l = [float(v) for v in np.atleast_1d(np.asarray(lo, dtype=np.float64).reshape(-1))]
+    hi_l = [float(v) for v in np.atleast_1d(np.asarray(hi, dtype=np.float64).reshape(-1))]
+    if len(lo_l) == 1 and len(hi_l) == 1:
+        mode = L.CLAMP_SCALAR
+    else:
+        if len(lo_l) != c or len(hi_l) != c:
+            raise ValueError("per-channel bounds must have one entry per channel")
+        mode = L.CLAMP_PER_CHANNEL
+    lk, lp = _fptr(lo_l)
+    hk, hp = _fptr(hi_l)
+    return mode, lk, lp, hk, hp
+
+
+def sign_step(x: torch.Tensor, g: torch.Tensor, eps, direction: float = 1.0, lo=None, hi=None,
+              return_pert: bool = False):
+    """x + direction*eps*sign(g) (optionally clamped). eps scalar -> tensor like x; eps sequence of E
+    values -> (E, *x.shape) from ONE pass over x and g."""
+    x = _check_f32(x)
+    g = _check_f32(g)
+    if x.shape != g.shape:
+        raise ValueError("x and g must have the same shape")
+    shp = x.shape
+    if x.dim() == 4:
+        n, c, hw = shp[0], shp[1], shp[2] * shp[3]
+    elif x.dim() == 3:
+        n, c, hw = 1, shp[0], shp[1] * shp[2]
+    else:
+        n, c, hw = 1, 1, x.numel()
+    many = not np.isscalar(eps)
+    eps_l = [float(e) for e in (eps if many else [eps])]
+    E = len(eps_l)
+    out = torch.empty((E,) + tuple(shp), dtype=torch.float32, device=x.device)
+    pert = torch.empty_like(out) if return_pert else None
+    mode, lk, lp, hk, hp = _bounds(lo, hi, c)
+    ek, ep = _fptr(eps_l)
+    L.check(L.load().imgtx_sign_step_f32(x.data_ptr(), g.data_ptr(), out.data_ptr(),
+                                         pert.data_ptr() if pert is not None else None, n, c, hw, ep, E,
+                                         float(direction), mode, lp, hp, _stream()))
+    if not many:
+        out = out[0]
+        pert = pert[0] if pert is not None else None
+    return (out, pert) if return_pert else out
+
+
+def pgd_step(x, x0, g, alpha: float, eps: float, lo=None, hi=None):
+    x, x0, g = _check_f32(x), _check_f32(x0), _check_f32(g)
+    shp = x.shape
+    if x.dim() == 4:
+        n, c, hw = shp[0], shp[1], shp[2] * shp[3]
+    else:
+        n, c, hw = 1, 1, x.numel()
+    out = torch.empty_like(x)
+    mode, lk, lp, hk, hp = _bounds(lo, hi, c)
+    L.check(L.load().imgtx_pgd_step_f32(x.data_ptr(), x0.data_ptr(), g.data_ptr(), out.data_ptr(), n, c, hw,
+                                        float(alpha), float(eps), mode, lp, hp, _stream()))
+    return out
+
+
+def float_corrupt(x, mode: int, a: float = 0.0, b: float = 0.0, noise=None, clamp: bool = True):
+    x = _check_f32(x)
+    out = torch.empty_like(x)
+    if noise is not None:
+        noise = _check_f32(noise)
+    L.check(L.load().imgtx_float_corrupt_f32(x.data_ptr(), noise.data_ptr() if noise is not None else None,
+                                             out.data_ptr(), x.numel(), mode, float(a), float(b), int(clamp),
+                                             _stream()))
+    return out

@@ -1,0 +1,198 @@
+// Image-group pipeline: the one execution skeleton shared by every u8->u8 image operator.
+//
+// An operator ("Op") is a functor that transforms a *group* of whole images with all threads of a CTA:
+//
+//   struct Op {
+//     struct Params { ... };                       // POD, passed by value
+//     static constexpr int kThreads = 256;
+//     static size_t scratch_bytes(const Shape&, int G);   // extra shared memory per CTA
+//     template <bool STAGED>
+//     static __device__ void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0,
+//                                const Shape& s, const Params& p, uint8_t* scratch, uint8_t* gtmp);
+//   };
+//
+// Two launch modes, chosen on the host:
+//  * STAGED  (small images, e.g. CIFAR 32x32x3 = 3072 B): persistent CTAs; groups of G images are
+//    moved HBM -> shared memory with 1-D bulk TMA copies (cp.async.bulk + mbarrier, a `stages`-deep
+//    ring), transformed shared -> shared, and written back with bulk TMA stores.  HBM sees only
+//    full-line sequential traffic no matter how irregular the operator's gather pattern is.
+//  * DIRECT  (large or oddly sized images): one CTA per image, src/dst point at global memory and the
+//    gather goes through L1/L2.
+#pragma once
+#include "common.cuh"
+#include <algorithm>
+
+namespace imgtx {
+
+struct Shape {
+  int h, w, c;        // input height, width, channels (HWC interleaved u8)
+  int oh, ow;         // output height, width (same c)
+  int in_bytes;       // h*w*c
+  int out_bytes;      // oh*ow*c
+};
+
+static inline Shape make_shape(int h, int w, int c, int oh, int ow) {
+  Shape s;
+  s.h = h; s.w = w; s.c = c; s.oh = oh; s.ow = ow;
+  s.in_bytes = h * w * c;
+  s.out_bytes = oh * ow * c;
+  return s;
+}
+
+#ifdef __CUDACC__
+
+constexpr int kBarBytes = 128;  // mbarrier block at the front of dynamic smem
+constexpr int kMaxStages = 8;
+
+__host__ __device__ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+template <class Op>
+__global__ void __launch_bounds__(Op::kThreads)
+staged_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, Shape s,
+              typename Op::Params p, int G, int stages) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  const size_t in_stage = align_up((size_t)G * s.in_bytes, 128);
+  const size_t out_stage = align_up((size_t)G * s.out_bytes, 128);
+  uint8_t* in_buf = smem + kBarBytes;
+  uint8_t* out_buf = in_buf + in_stage * stages;
+  uint8_t* scratch = out_buf + out_stage * 2;
+
+  const int64_t n_groups = (n + G - 1) / G;
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    for (int i = 0; i < stages; ++i) mbar_init(&full[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  // prologue: fill the ring
+  if (tid == 0) {
+    for (int i = 0; i < stages; ++i) {
+      int64_t grp = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      if (grp < n_groups) {
+        int64_t img0 = grp * G;
+        int g = (int)min((int64_t)G, n - img0);
+        uint32_t bytes = (uint32_t)g * s.in_bytes;
+        mbar_expect_tx(&full[i], bytes);
+        bulk_g2s(in_buf + in_stage * i, in + img0 * s.in_bytes, bytes, &full[i]);
+      }
+    }
+  }
+
+  int it = 0;
+  for (int64_t grp = blockIdx.x; grp < n_groups; grp += gridDim.x, ++it) {
+    const int st = it % stages;
+    const uint32_t parity = (uint32_t)(it / stages) & 1u;
+    const int ob = it & 1;
+    const int64_t img0 = grp * G;
+    const int g = (int)min((int64_t)G, n - img0);
+
+    // the bulk store issued two iterations ago must have finished reading out_buf[ob]
+    if (tid == 0) bulk_wait_read<1>();
+    mbar_wait(&full[st], parity);
+    __syncthreads();
+
+    Op::template run<true>(in_buf + in_stage * st, out_buf + out_stage * ob, g, img0, s, p, scratch,
+                           nullptr);
+
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(out + img0 * s.out_bytes, out_buf + out_stage * ob, (uint32_t)g * s.out_bytes);
+      bulk_commit();
+      int64_t nxt = grp + (int64_t)stages * gridDim.x;
+      if (nxt < n_groups) {
+        int64_t nimg0 = nxt * G;
+        int ng = (int)min((int64_t)G, n - nimg0);
+        uint32_t bytes = (uint32_t)ng * s.in_bytes;
+        mbar_expect_tx(&full[st], bytes);
+        bulk_g2s(in_buf + in_stage * st, in + nimg0 * s.in_bytes, bytes, &full[st]);
+      }
+    }
+  }
+  if (tid == 0) bulk_wait_all<0>();
+}
+
+template <class Op>
+__global__ void __launch_bounds__(Op::kThreads)
+direct_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, Shape s,
+              typename Op::Params p, uint8_t* gtmp, size_t gtmp_per_cta) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* my_tmp = gtmp ? gtmp + (size_t)blockIdx.x * gtmp_per_cta : nullptr;
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    Op::template run<false>(in + img * s.in_bytes, out + img * s.out_bytes, 1, img, s, p, smem, my_tmp);
+    __syncthreads();
+  }
+}
+
+// Tunables (overridable from the environment for the on-GPU sweeps in bench.py).
+struct StagedTuning {
+  int target_smem;  // dynamic smem per CTA we aim for (bytes)
+  int stages;
+  int ctas_per_sm;
+};
+StagedTuning staged_tuning();
+
+template <class Op>
+int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
+                    const typename Op::Params& p, cudaStream_t stream) {
+  if (n <= 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
+  const StagedTuning tn = staged_tuning();
+  const int max_smem = max_smem_optin();
+  bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);
+  int G = 1, stages = tn.stages;
+  size_t smem_bytes = 0;
+  if (staged) {
+    auto need = [&](int g, int st) {
+      return (size_t)kBarBytes + align_up((size_t)g * s.in_bytes, 128) * st +
+             align_up((size_t)g * s.out_bytes, 128) * 2 + Op::scratch_bytes(s, g) + 128;
+    };
+    while (stages > 2 && need(1, stages) > (size_t)tn.target_smem) --stages;
+    if (need(1, stages) > (size_t)max_smem - 1024) {
+      staged = false;
+    } else {
+      G = 1;
+      while (G < 64 && need(G + 1, stages) <= (size_t)tn.target_smem) ++G;
+      smem_bytes = need(G, stages);
+    }
+  }
+  if (staged) {
+    auto kern = staged_kernel<Op>;
+    IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    int64_t n_groups = (n + G - 1) / G;
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(tn.ctas_per_sm, (size_t)max_smem / smem_bytes));
+    int64_t grid = std::min<int64_t>(n_groups, (int64_t)sm_count() * per_sm);
+    kern<<<(unsigned)grid, Op::kThreads, smem_bytes, stream>>>(in, out, n, s, p, G, stages);
+    IMGTX_LAUNCH_OK();
+    return IMGTX_OK;
+  }
+  // direct mode
+  size_t scratch = Op::scratch_bytes(s, 1);
+  uint8_t* gtmp = nullptr;
+  size_t gtmp_per_cta = 0;
+  int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 8);
+  if (scratch > (size_t)max_smem - 1024) {
+    // intermediate planes do not fit on chip: spill them to a stream-ordered global workspace
+    gtmp_per_cta = align_up(Op::gtmp_bytes(s), 256);
+    scratch = Op::scratch_bytes_spilled(s);
+    IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, gtmp_per_cta * grid, stream));
+  }
+  auto kern = direct_kernel<Op>;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch));
+  kern<<<(unsigned)grid, Op::kThreads, scratch, stream>>>(in, out, n, s, p, gtmp, gtmp_per_cta);
+  IMGTX_LAUNCH_OK();
+  if (gtmp) IMGTX_CUDA_OK(cudaFreeAsync(gtmp, stream));
+  return IMGTX_OK;
+}
+
+// Default "no spill" hooks for operators without intermediate planes.
+struct NoSpill {
+  static size_t gtmp_bytes(const Shape&) { return 0; }
+  static size_t scratch_bytes_spilled(const Shape&) { return 0; }
+};
+
+#endif  // __CUDACC__
+}  // namespace imgtx

@@ -1,0 +1,370 @@
+// Float-tensor side of the path: ToTensor/Normalize, tensor_to_pil, sign-step (FGSM family), float
+// corruptions.  All f32, un-fused, op order exactly as torch evaluates the reference expressions.
+//
+//   imgtx_to_tensor_f32      T.ToTensor() [+ T.Normalize(mean,std)]: u8 NHWC -> f32 NCHW
+//                            (fall_2025/TENT_transform.py:56-59, TTA_transforms.py:62-65,
+//                             tta_initial_claudeFixed.py:43-46, AugMix.py:17-20)
+//   imgtx_to_uint8_f32       tensor_to_pil / TF.to_pil_image: f32 NCHW -> u8 NHWC
+//                            (tta_initial_claudeFixed.py:37-41, cifar_image_transformations.py:27-30,
+//                             AugMix.py:56)
+//   imgtx_sign_step_f32      x +- eps*sign(g) [+clamp], E epsilons per pass
+//                            (attacks/fgsm.py:190-192, attacks/fgsm/cifar-10/fgsm_cifar10.py:25-28,
+//                             reverse_fgsm_cifar10.py:74-80, fall_2025/generalizedOdin2.py:47)
+//   imgtx_pgd_step_f32       step + eps-ball projection + clamp (attacks/fgsm/cifar-10/pgd_cifar10.py:37-45)
+//   imgtx_float_corrupt_f32  clamp(x*a' ...) family (pipenline/angellic.py:34-46,
+//                            fall_2025/angellic_with_corrupt.py:51-52)
+// Roofline: HBM.  to_tensor: 3 B read + 12 B written per pixel; sign-step: 8 B read + 4E B written
+// per element.
+#include "common.cuh"
+#include <string.h>
+
+namespace imgtx {
+
+struct ChanStats {
+  float mean[4];
+  float std[4];
+};
+
+// ---- u8 NHWC -> f32 NCHW ----------------------------------------------------------------------
+// One thread converts 4 consecutive pixels of one image: 12 contiguous input bytes (c == 3) and one
+// float4 per channel plane.
+__global__ void __launch_bounds__(256)
+to_tensor_c3_vec_kernel(const uint32_t* __restrict__ in, float* __restrict__ out, int64_t n_quads,
+                        int hw, ChanStats st, int do_norm) {
+  const int quads_per_img = hw >> 2;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads;
+       q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t img = q / quads_per_img;
+    const int qi = (int)(q - img * quads_per_img);
+    const uint32_t w0 = __ldg(in + q * 3), w1 = __ldg(in + q * 3 + 1), w2 = __ldg(in + q * 3 + 2);
+    // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+    float r[4] = {(float)(w0 & 255u), (float)(w0 >> 24), (float)((w1 >> 16) & 255u), (float)((w2 >> 8) & 255u)};
+    float g[4] = {(float)((w0 >> 8) & 255u), (float)(w1 & 255u), (float)(w1 >> 24), (float)((w2 >> 16) & 255u)};
+    float b[4] = {(float)((w0 >> 16) & 255u), (float)((w1 >> 8) & 255u), (float)(w2 & 255u), (float)(w2 >> 24)};
+    float* planes[3] = {r, g, b};
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      float4 o;
+      float* v = planes[ch];
+      float t0 = __fdiv_rn(v[0], 255.0f), t1 = __fdiv_rn(v[1], 255.0f), t2 = __fdiv_rn(v[2], 255.0f),
+            t3 = __fdiv_rn(v[3], 255.0f);
+      if (do_norm) {
+        t0 = __fdiv_rn(__fsub_rn(t0, st.mean[ch]), st.std[ch]);
+        t1 = __fdiv_rn(__fsub_rn(t1, st.mean[ch]), st.std[ch]);
+        t2 = __fdiv_rn(__fsub_rn(t2, st.mean[ch]), st.std[ch]);
+        t3 = __fdiv_rn(__fsub_rn(t3, st.mean[ch]), st.std[ch]);
+      }
+      o.x = t0; o.y = t1; o.z = t2; o.w = t3;
+      stg_stream_f4(reinterpret_cast<float4*>(out + ((img * 3 + ch) * (int64_t)hw) + (int64_t)qi * 4), o);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+to_tensor_generic_kernel(const uint8_t* __restrict__ in, float* __restrict__ out, int64_t total, int hw,
+                         int c, ChanStats st, int do_norm) {
+  // one thread per output element (n, ch, pix)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t plane = i / hw;
+    const int pix = (int)(i - plane * hw);
+    const int64_t img = plane / c;
+    const int ch = (int)(plane - img * c);
+    float t = __fdiv_rn((float)in[(img * hw + pix) * c + ch], 255.0f);
+    if (do_norm) t = __fdiv_rn(__fsub_rn(t, st.mean[ch]), st.std[ch]);
+    out[i] = t;
+  }
+}
+
+// ---- f32 NCHW -> u8 NHWC ----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t quant8(float v, int ch, const ChanStats& st, int flags) {
+  if (flags & IMGTX_TOU8_DENORMALIZE) v = __fadd_rn(__fmul_rn(v, st.std[ch]), st.mean[ch]);
+  if (flags & IMGTX_TOU8_CLAMP01) v = fminf(fmaxf(v, 0.0f), 1.0f);
+  // x.mul(255).byte(): truncation toward zero, modulo 256 for out-of-range values (CPU semantics)
+  return (uint32_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+}
+
+__global__ void __launch_bounds__(256)
+to_uint8_c3_vec_kernel(const float* __restrict__ in, uint32_t* __restrict__ out, int64_t n_quads, int hw,
+                       ChanStats st, int flags) {
+  const int quads_per_img = hw >> 2;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads;
+       q += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t img = q / quads_per_img;
+    const int qi = (int)(q - img * quads_per_img);
+    uint32_t v[3][4];
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      float4 f = ldg_stream_f4(reinterpret_cast<const float4*>(in + (img * 3 + ch) * (int64_t)hw + (int64_t)qi * 4));
+      v[ch][0] = quant8(f.x, ch, st, flags);
+      v[ch][1] = quant8(f.y, ch, st, flags);
+      v[ch][2] = quant8(f.z, ch, st, flags);
+      v[ch][3] = quant8(f.w, ch, st, flags);
+    }
+    out[q * 3 + 0] = v[0][0] | (v[1][0] << 8) | (v[2][0] << 16) | (v[0][1] << 24);
+    out[q * 3 + 1] = v[1][1] | (v[2][1] << 8) | (v[0][2] << 16) | (v[1][2] << 24);
+    out[q * 3 + 2] = v[2][2] | (v[0][3] << 8) | (v[1][3] << 16) | (v[2][3] << 24);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+to_uint8_generic_kernel(const float* __restrict__ in, uint8_t* __restrict__ out, int64_t total, int hw,
+                        int c, ChanStats st, int flags) {
+  // one thread per output byte (n, pix, ch)
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t px = i / c;
+    const int ch = (int)(i - px * c);
+    const int64_t img = px / hw;
+    const int pix = (int)(px - img * hw);
+    out[i] = (uint8_t)quant8(in[(img * c + ch) * (int64_t)hw + pix], ch, st, flags);
+  }
+}
+
+// ---- sign-step family -----------------------------------------------------------------------
+struct StepParams {
+  float eps[IMGTX_MAX_EPS];
+  int n_eps;
+  float dir;       // +1 / -1
+  int clamp_mode;  // imgtx_clamp_mode
+  float lo[4], hi[4];
+};
+
+// torch.sign: (g>0)-(g<0); sign(NaN)=0
+__device__ __forceinline__ float tsign(float g) { return (float)(g > 0.0f) - (float)(g < 0.0f); }
+// torch.clamp / torch.max+min: NaN in x propagates
+__device__ __forceinline__ float tclamp(float v, float lo, float hi) {
+  if (v != v) return v;
+  return fminf(fmaxf(v, lo), hi);
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+sign_step_kernel(const float* __restrict__ x, const float* __restrict__ g, float* __restrict__ out,
+                 float* __restrict__ pert, int64_t count, int64_t hw, int c, StepParams p) {
+  const int64_t n_items = count / VEC;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_items;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    float xv[VEC], gv[VEC];
+    if (VEC == 4) {
+      float4 a = ldg_stream_f4(reinterpret_cast<const float4*>(x) + i);
+      float4 b = ldg_stream_f4(reinterpret_cast<const float4*>(g) + i);
+      xv[0] = a.x; xv[VEC > 1 ? 1 : 0] = a.y; xv[VEC > 2 ? 2 : 0] = a.z; xv[VEC > 3 ? 3 : 0] = a.w;
+      gv[0] = b.x; gv[VEC > 1 ? 1 : 0] = b.y; gv[VEC > 2 ? 2 : 0] = b.z; gv[VEC > 3 ? 3 : 0] = b.w;
+    } else {
+      xv[0] = x[i]; gv[0] = g[i];
+    }
+    int ch = 0;
+    if (p.clamp_mode == IMGTX_CLAMP_PER_CHANNEL) ch = (int)(((i * VEC) / hw) % c);  // hw % VEC == 0
+    const float lo = p.lo[ch], hi = p.hi[ch];
+    float sg[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) sg[k] = tsign(gv[k]);
+    for (int e = 0; e < p.n_eps; ++e) {
+      float o[VEC], pe[VEC];
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) {
+        pe[k] = __fmul_rn(p.eps[e], sg[k]);
+        float v = p.dir > 0.0f ? __fadd_rn(xv[k], pe[k]) : __fsub_rn(xv[k], pe[k]);
+        if (p.clamp_mode != IMGTX_CLAMP_NONE) v = tclamp(v, lo, hi);
+        o[k] = v;
+      }
+      if (VEC == 4) {
+        stg_stream_f4(reinterpret_cast<float4*>(out + (int64_t)e * count) + i,
+                      make_float4(o[0], o[VEC > 1 ? 1 : 0], o[VEC > 2 ? 2 : 0], o[VEC > 3 ? 3 : 0]));
+        if (pert)
+          stg_stream_f4(reinterpret_cast<float4*>(pert + (int64_t)e * count) + i,
+                        make_float4(pe[0], pe[VEC > 1 ? 1 : 0], pe[VEC > 2 ? 2 : 0], pe[VEC > 3 ? 3 : 0]));
+      } else {
+        out[(int64_t)e * count + i] = o[0];
+        if (pert) pert[(int64_t)e * count + i] = pe[0];
+      }
+    }
+  }
+}
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+pgd_step_kernel(const float* __restrict__ x, const float* __restrict__ x0, const float* __restrict__ g,
+                float* __restrict__ out, int64_t count, int64_t hw, int c, float alpha, float eps,
+                StepParams p) {
+  const int64_t n_items = count / VEC;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_items;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int ch = 0;
+    if (p.clamp_mode == IMGTX_CLAMP_PER_CHANNEL) ch = (int)(((i * VEC) / hw) % c);
+    const float lo = p.lo[ch], hi = p.hi[ch];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      const int64_t j = i * VEC + k;
+      float xa = __fadd_rn(x[j], __fmul_rn(alpha, tsign(g[j])));
+      float eta = tclamp(__fsub_rn(xa, x0[j]), -eps, eps);
+      float v = __fadd_rn(x0[j], eta);
+      if (p.clamp_mode != IMGTX_CLAMP_NONE) v = tclamp(v, lo, hi);
+      out[j] = v;
+    }
+  }
+}
+
+// ---- float corruptions: out = clamp?( ((x - pre) * mul + post) + (r * nstd + nmean) ) ---------------
+__global__ void __launch_bounds__(256)
+float_corrupt_kernel(const float* __restrict__ x, const float* __restrict__ r, float* __restrict__ out,
+                     int64_t count, int mode, float a, float b, int do_clamp) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    float v = x[i];
+    switch (mode) {
+      case IMGTX_FC_GAUSSIAN_NOISE:  // (x + (r*std + mean))
+        v = __fadd_rn(v, __fadd_rn(__fmul_rn(r[i], a), b));
+        break;
+      case IMGTX_FC_BRIGHTNESS:  // x + f
+        v = __fadd_rn(v, a);
+        break;
+      case IMGTX_FC_CONTRAST:  // (x - 0.5) * f + 0.5
+        v = __fadd_rn(__fmul_rn(__fsub_rn(v, 0.5f), a), 0.5f);
+        break;
+      case IMGTX_FC_ADD_NOISE:  // x + r*std
+        v = __fadd_rn(v, __fmul_rn(r[i], a));
+        break;
+    }
+    if (do_clamp) v = tclamp(v, 0.0f, 1.0f);
+    out[i] = v;
+  }
+}
+
+static inline unsigned grid_for(int64_t items, int threads = 256, int per_sm = 16) {
+  int64_t want = (items + threads - 1) / threads;
+  int64_t cap = (int64_t)sm_count() * per_sm;
+  return (unsigned)(want < 1 ? 1 : (want > cap ? cap : want));
+}
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+static int fill_stats(ChanStats& st, int c, const float* mean, const float* stdv) {
+  for (int i = 0; i < 4; ++i) { st.mean[i] = 0.f; st.std[i] = 1.f; }
+  for (int i = 0; i < c && i < 4; ++i) {
+    if (mean) st.mean[i] = mean[i];
+    if (stdv) st.std[i] = stdv[i];
+  }
+  return 0;
+}
+
+extern "C" int imgtx_to_tensor_f32(const uint8_t* in, float* out, int64_t n, int h, int w, int c,
+                                   const float* mean_host, const float* std_host, imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4 && n >= 0, "bad shape");
+  IMGTX_CHECK_ARG((mean_host == nullptr) == (std_host == nullptr), "mean and std must both be given or both NULL");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null pointer");
+  ChanStats st;
+  fill_stats(st, c, mean_host, std_host);
+  const int hw = h * w;
+  const int do_norm = mean_host != nullptr;
+  if (c == 3 && hw % 4 == 0 && aligned4(in) && aligned16(out)) {
+    const int64_t nq = n * (hw / 4);
+    to_tensor_c3_vec_kernel<<<grid_for(nq), 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(in), out, nq,
+                                                             hw, st, do_norm);
+  } else {
+    const int64_t total = n * (int64_t)hw * c;
+    to_tensor_generic_kernel<<<grid_for(total), 256, 0, stream>>>(in, out, total, hw, c, st, do_norm);
+  }
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_to_uint8_f32(const float* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                  const float* mean_host, const float* std_host, int flags,
+                                  imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4 && n >= 0, "bad shape");
+  if (flags & IMGTX_TOU8_DENORMALIZE) IMGTX_CHECK_ARG(mean_host && std_host, "denormalize needs mean/std");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null pointer");
+  ChanStats st;
+  fill_stats(st, c, mean_host, std_host);
+  const int hw = h * w;
+  if (c == 3 && hw % 4 == 0 && aligned16(in) && aligned4(out)) {
+    const int64_t nq = n * (hw / 4);
+    to_uint8_c3_vec_kernel<<<grid_for(nq), 256, 0, stream>>>(in, reinterpret_cast<uint32_t*>(out), nq, hw, st,
+                                                            flags);
+  } else {
+    const int64_t total = n * (int64_t)hw * c;
+    to_uint8_generic_kernel<<<grid_for(total), 256, 0, stream>>>(in, out, total, hw, c, st, flags);
+  }
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+static int fill_step(StepParams& p, const float* eps, int n_eps, float dir, int clamp_mode, const float* lo,
+                     const float* hi, int c) {
+  memset(&p, 0, sizeof(p));
+  IMGTX_CHECK_ARG(n_eps >= 1 && n_eps <= IMGTX_MAX_EPS, "n_eps must be in [1,%d]", IMGTX_MAX_EPS);
+  IMGTX_CHECK_ARG(clamp_mode >= IMGTX_CLAMP_NONE && clamp_mode <= IMGTX_CLAMP_PER_CHANNEL, "bad clamp mode");
+  for (int i = 0; i < n_eps; ++i) p.eps[i] = eps[i];
+  p.n_eps = n_eps;
+  p.dir = dir;
+  p.clamp_mode = clamp_mode;
+  if (clamp_mode != IMGTX_CLAMP_NONE) {
+    IMGTX_CHECK_ARG(lo && hi, "clamp bounds missing");
+    const int k = clamp_mode == IMGTX_CLAMP_SCALAR ? 1 : c;
+    IMGTX_CHECK_ARG(k <= 4, "at most 4 channels");
+    for (int i = 0; i < 4; ++i) { p.lo[i] = lo[i < k ? i : 0]; p.hi[i] = hi[i < k ? i : 0]; }
+  }
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_sign_step_f32(const float* x, const float* g, float* out, float* pert, int64_t n, int c,
+                                   int64_t hw, const float* eps_host, int n_eps, float direction,
+                                   int clamp_mode, const float* lo_host, const float* hi_host,
+                                   imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(n >= 0 && c >= 1 && hw >= 1, "bad shape");
+  StepParams p;
+  int rc = fill_step(p, eps_host, n_eps, direction, clamp_mode, lo_host, hi_host, c);
+  if (rc) return rc;
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && g && out, "null pointer");
+  const int64_t count = n * c * hw;
+  const bool vec = (hw % 4 == 0) && aligned16(x) && aligned16(g) && aligned16(out) && (!pert || aligned16(pert));
+  if (vec)
+    sign_step_kernel<4><<<grid_for(count / 4), 256, 0, stream>>>(x, g, out, pert, count, hw, c, p);
+  else
+    sign_step_kernel<1><<<grid_for(count), 256, 0, stream>>>(x, g, out, pert, count, hw, c, p);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_pgd_step_f32(const float* x, const float* x0, const float* g, float* out, int64_t n,
+                                  int c, int64_t hw, float alpha, float eps, int clamp_mode,
+                                  const float* lo_host, const float* hi_host, imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(n >= 0 && c >= 1 && hw >= 1, "bad shape");
+  StepParams p;
+  float e1 = eps;
+  int rc = fill_step(p, &e1, 1, 1.0f, clamp_mode, lo_host, hi_host, c);
+  if (rc) return rc;
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && x0 && g && out, "null pointer");
+  const int64_t count = n * c * hw;
+  if (hw % 4 == 0)
+    pgd_step_kernel<4><<<grid_for(count / 4), 256, 0, stream>>>(x, x0, g, out, count, hw, c, alpha, eps, p);
+  else
+    pgd_step_kernel<1><<<grid_for(count), 256, 0, stream>>>(x, x0, g, out, count, hw, c, alpha, eps, p);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_float_corrupt_f32(const float* x, const float* noise, float* out, int64_t count, int mode,
+                                       float a, float b, int do_clamp, imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(mode >= IMGTX_FC_GAUSSIAN_NOISE && mode <= IMGTX_FC_ADD_NOISE, "bad mode");
+  if (mode == IMGTX_FC_GAUSSIAN_NOISE || mode == IMGTX_FC_ADD_NOISE)
+    IMGTX_CHECK_ARG(noise != nullptr, "this mode needs the injected standard-normal draws");
+  if (count <= 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && out, "null pointer");
+  float_corrupt_kernel<<<grid_for(count), 256, 0, stream>>>(x, noise, out, count, mode, a, b, do_clamp);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}

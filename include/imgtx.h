@@ -1,0 +1,149 @@
+/*
+ * libimgtx — C ABI of the B200-native image-transformation hot path.
+ *
+ * The reference (aaryaamoharir/ImageTransformations) has no FFI of its own: its boundary is a set of
+ * plain Python functions that call Pillow / OpenCV / torchvision / torch one image at a time.  Each entry
+ * point below replaces the arithmetic behind one (or a family) of those functions, batched over n
+ * images; the comment above each prototype cites the reference call site(s) it stands in for
+ * (paths relative to the reference repository root).  INTEGRATION.md shows the ctypes binding a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *  - Every pointer named *_dev / in / out / x / g is a DEVICE pointer owned by the caller.  The library
+ *    never allocates persistent memory, never retains a pointer past the call and never frees caller
+ *    memory.  uint8 images are HWC-interleaved and contiguous (n, h, w, c); float tensors are NCHW f32.
+ *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); no call synchronises the device.
+ *  - Return value: IMGTX_OK (0) or a negative imgtx_status; imgtx_last_error() returns a thread-local
+ *    message for the last failure.  No exception, abort or exit crosses this boundary.
+ *  - "per-image" parameter arrays are device arrays of length n (nullable: NULL selects the scalar).
+ *  - Functions ending in _host are pure host helpers (table builders); they take HOST pointers.
+ */
+#ifndef IMGTX_H_
+#define IMGTX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IMGTX_VERSION 100
+
+typedef enum {
+  IMGTX_OK = 0,
+  IMGTX_ERR_INVALID_ARGUMENT = -1,
+  IMGTX_ERR_CUDA = -2,
+  IMGTX_ERR_UNSUPPORTED = -3
+} imgtx_status;
+
+typedef void* imgtx_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------------------ */
+int imgtx_version(void);
+const char* imgtx_last_error(void);
+/* Fills the SM count and opt-in shared memory per block of the current device. */
+int imgtx_device_info(int* sm_count, int* max_smem_per_block);
+/* Tuning knobs of the staged (TMA) image pipeline; <=0 keeps the current value. */
+int imgtx_set_tuning(int target_smem_bytes, int stages, int ctas_per_sm);
+
+/* ---- pointwise uint8 maps (256-entry LUT built with the library's exact f32 formula) -------- */
+typedef enum {
+  /* PIL.ImageEnhance.Brightness(img).enhance(param) — transformation.py:261-269,
+     fall_2025/tta_initial_claudeFixed.py:64-67, pipenline/cifar_image_transformations.py:88-92 */
+  IMGTX_PW_BRIGHTNESS = 0,
+  /* cv2.convertScaleAbs(img, alpha=param, beta=0) — transformation.py:203-210 */
+  IMGTX_PW_SCALE_ABS = 1,
+  /* PIL.ImageOps.posterize(img, bits=int(param)) — fall_2025/AugMix.py:31 */
+  IMGTX_PW_POSTERIZE = 2,
+  /* PIL.ImageOps.solarize(img, threshold=int(param)) — fall_2025/AugMix.py:37 */
+  IMGTX_PW_SOLARIZE = 3,
+  /* identity copy (apply_blur(r=0), apply_rotation(0)) */
+  IMGTX_PW_IDENTITY = 4
+} imgtx_pointwise_op;
+
+int imgtx_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int64_t image_bytes, int op,
+                       float param, const float* param_per_image_dev, imgtx_stream_t stream);
+
+/* ---- integer geometry (pure index gathers, no interpolation) -------------------------------------- */
+typedef enum {
+  IMGTX_GEOM_IDENTITY = 0,
+  /* Image.transform(size, AFFINE, m) / Image.rotate(angle) with NEAREST resampling: m[6] are the doubles
+     Pillow's Python layer hands to C (for rotate: Image.py's rounded cos/sin + centre shift).
+     transformation.py:198-201, fall_2025/AugMix.py:30,32-35, fall_2025/Initial_Experiments.py:88-92 */
+  IMGTX_GEOM_AFFINE = 1,
+  /* apply_translation(img, dx, dy): integer shift, zero fill — transformation.py:284-307 */
+  IMGTX_GEOM_SHIFT = 2,
+  /* Image.transpose(FLIP_LEFT_RIGHT) — fall_2025/transformations_code:39-41,
+     fall_2025/tta_initial_claudeFixed.py:52-54, T.RandomHorizontalFlip(p=1) TTA_transforms.py:75 */
+  IMGTX_GEOM_FLIP_LR = 3,
+  /* T.RandomCrop(out, padding=pad, padding_mode='reflect') at offset (dy=i, dx=j) — TTA_transforms.py:80 */
+  IMGTX_GEOM_CROP_REFLECT = 4,
+  /* exact special cases of Image.rotate */
+  IMGTX_GEOM_ROT180 = 5,
+  IMGTX_GEOM_ROT90 = 6,
+  IMGTX_GEOM_ROT270 = 7
+} imgtx_geom_kind;
+
+typedef struct {
+  int32_t kind; /* imgtx_geom_kind */
+  int32_t dx, dy, pad;
+  double m[6];
+} imgtx_geom_t;
+
+/* One geometry record for the whole batch (uniform_host, HOST pointer) or one per image
+   (per_image_dev, DEVICE array of n records). fill_host: c bytes (NULL = zeros). */
+int imgtx_geometry_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int oh, int ow,
+                      const imgtx_geom_t* uniform_host, const imgtx_geom_t* per_image_dev,
+                      const uint8_t* fill_host, imgtx_stream_t stream);
+
+/* ---- tensors ------------------------------------------------------------------------------ */
+/* T.ToTensor() [+ T.Normalize(mean, std) when mean_host/std_host != NULL]: u8 NHWC -> f32 NCHW.
+   fall_2025/TENT_transform.py:56-59, fall_2025/TTA_transforms.py:62-65,
+   fall_2025/tta_initial_claudeFixed.py:43-46, attacks/normal_inference/cifar_corrupted.py:42-48 */
+int imgtx_to_tensor_f32(const uint8_t* in, float* out, int64_t n, int h, int w, int c, const float* mean_host,
+                        const float* std_host, imgtx_stream_t stream);
+
+#define IMGTX_TOU8_DENORMALIZE 1 /* x*std + mean first */
+#define IMGTX_TOU8_CLAMP01 2     /* torch.clamp(x, 0, 1) */
+/* tensor_to_pil (DENORMALIZE|CLAMP01) / TF.to_pil_image (flags 0: truncation with mod-256 wrap):
+   f32 NCHW -> u8 NHWC.  fall_2025/tta_initial_claudeFixed.py:37-41,
+   pipenline/cifar_image_transformations.py:27-30, fall_2025/AugMix.py:56 */
+int imgtx_to_uint8_f32(const float* in, uint8_t* out, int64_t n, int h, int w, int c, const float* mean_host,
+                       const float* std_host, int flags, imgtx_stream_t stream);
+
+/* ---- sign-step family --------------------------------------------------------------------- */
+#define IMGTX_MAX_EPS 8
+typedef enum { IMGTX_CLAMP_NONE = 0, IMGTX_CLAMP_SCALAR = 1, IMGTX_CLAMP_PER_CHANNEL = 2 } imgtx_clamp_mode;
+
+/* out[e] = clamp(x + direction * eps[e] * sign(g)) for e < n_eps, x/g (n,c,hw) f32, out (n_eps,n,c,hw);
+   pert (nullable, same shape as out) receives eps[e]*sign(g).
+   direction=+1, CLAMP_NONE: FGSM            attacks/fgsm.py:190-192, :250-251
+   direction=+1, CLAMP_SCALAR [0,1]: fgsm_attack   attacks/fgsm/cifar-10/fgsm_cifar10.py:25-28
+   direction=-1, CLAMP_PER_CHANNEL: reverse_fgsm_attack  attacks/fgsm/cifar-10/reverse_fgsm_cifar10.py:74-80
+   direction=-1, CLAMP_SCALAR: patch / entropy steps  fall_2025/angellic_patches_fgsm.py:67-69,
+                                                       pipenline/cifar100_shannon.py:72-74 */
+int imgtx_sign_step_f32(const float* x, const float* g, float* out, float* pert, int64_t n, int c, int64_t hw,
+                        const float* eps_host, int n_eps, float direction, int clamp_mode,
+                        const float* lo_host, const float* hi_host, imgtx_stream_t stream);
+
+/* PGD iteration: xa = x + alpha*sign(g); eta = clamp(xa - x0, -eps, eps); out = clamp(x0 + eta, lo, hi)
+   attacks/fgsm/cifar-10/pgd_cifar10.py:37-45, pgd_cifar10_corrupted.py:72-83 */
+int imgtx_pgd_step_f32(const float* x, const float* x0, const float* g, float* out, int64_t n, int c,
+                       int64_t hw, float alpha, float eps, int clamp_mode, const float* lo_host,
+                       const float* hi_host, imgtx_stream_t stream);
+
+typedef enum {
+  IMGTX_FC_GAUSSIAN_NOISE = 0, /* (x + (r*a + b)).clamp(0,1)        pipenline/angellic.py:34-38 */
+  IMGTX_FC_BRIGHTNESS = 1,     /* (x + a).clamp(0,1)                pipenline/angellic.py:40-42 */
+  IMGTX_FC_CONTRAST = 2,       /* ((x-0.5)*a + 0.5).clamp(0,1)      pipenline/angellic.py:44-46 */
+  IMGTX_FC_ADD_NOISE = 3       /* x + r*a   (no clamp)              fall_2025/angellic_with_corrupt.py:51-52 */
+} imgtx_float_corrupt_mode;
+/* noise: injected standard-normal draws (torch.randn_like), same shape as x; NULL for modes 1,2. */
+int imgtx_float_corrupt_f32(const float* x, const float* noise, float* out, int64_t count, int mode, float a,
+                            float b, int do_clamp, imgtx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IMGTX_H_ */
