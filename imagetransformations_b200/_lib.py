@@ -28,6 +28,9 @@ class GeomRecord(C.Structure):
 PW_BRIGHTNESS, PW_SCALE_ABS, PW_POSTERIZE, PW_SOLARIZE, PW_IDENTITY = range(5)
 (GEOM_IDENTITY, GEOM_AFFINE, GEOM_SHIFT, GEOM_FLIP_LR, GEOM_CROP_REFLECT, GEOM_ROT180, GEOM_ROT90,
  GEOM_ROT270) = range(8)
+ENH_BRIGHTNESS, ENH_CONTRAST, ENH_COLOR, ENH_SHARPNESS, ENH_EQUALIZE, ENH_HISTEQ_YUV = range(6)
+FILTER_BOX, FILTER_BILINEAR, FILTER_BICUBIC, FILTER_LANCZOS = range(4)
+NOISE_GAUSS_F32, NOISE_GAUSS_F64, NOISE_IMPULSE, NOISE_SHOT = range(4)
 TOU8_DENORMALIZE, TOU8_CLAMP01 = 1, 2
 CLAMP_NONE, CLAMP_SCALAR, CLAMP_PER_CHANNEL = range(3)
 FC_GAUSSIAN_NOISE, FC_BRIGHTNESS, FC_CONTRAST, FC_ADD_NOISE = range(4)
@@ -46,13 +49,24 @@ _PROTOS = {
     "imgtx_set_tuning": [_int, _int, _int],
     "imgtx_pointwise_u8": [_vp, _vp, _i64, _i64, _int, _f, _vp, _vp],
     "imgtx_geometry_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, C.POINTER(GeomRecord), _vp, _vp, _vp],
+    "imgtx_enhance_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _f, _vp, _vp],
+    "imgtx_resample_table_words": [_int, _int, _int],
+    "imgtx_resample_table_host": [_int, _int, _int, _vp],
+    "imgtx_resample_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _int, _int, _vp, _i64, _vp,
+                          _i64, _int, _int, _int, _int, _vp],
+    "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
+    "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _vp],
+    "imgtx_pil_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
+    "imgtx_box_filter_h_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp],
+    "imgtx_noise_injected_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, C.c_double, _vp],
+    "imgtx_noise_philox_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_uint64, _vp],
     "imgtx_to_tensor_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_to_uint8_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _int, _vp],
     "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
 }
-_RESTYPES = {"imgtx_last_error": C.c_char_p}
+_RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64}
 
 
 def load():

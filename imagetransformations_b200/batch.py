@@ -92,6 +92,43 @@ def solarize(x, threshold, out=None):
 
 
 # ------------------------------------------------------------------------------------------------
+# per-image statistics + map
+# ------------------------------------------------------------------------------------------------
+def enhance(x: torch.Tensor, kind: int, factor=1.0, out=None) -> torch.Tensor:
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    per = _per_image_f32(factor, n, x.device)
+    scalar = 0.0 if per is not None else float(factor)
+    L.check(L.load().imgtx_enhance_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, kind, scalar,
+                                      per.data_ptr() if per is not None else None, _stream()))
+    return out
+
+
+def enhance_contrast(x, factor, out=None):
+    """ImageEnhance.Contrast(img).enhance(factor)."""
+    return enhance(x, L.ENH_CONTRAST, factor, out)
+
+
+def enhance_color(x, factor, out=None):
+    return enhance(x, L.ENH_COLOR, factor, out)
+
+
+def enhance_sharpness(x, factor, out=None):
+    return enhance(x, L.ENH_SHARPNESS, factor, out)
+
+
+def equalize(x, out=None):
+    """ImageOps.equalize."""
+    return enhance(x, L.ENH_EQUALIZE, 1.0, out)
+
+
+def histogram_equalization(x, out=None):
+    """cv2 YUV equalizeHist round trip (TransformationPool.histogram_equalization)."""
+    return enhance(x, L.ENH_HISTEQ_YUV, 1.0, out)
+
+
+# ------------------------------------------------------------------------------------------------
 # geometry
 # ------------------------------------------------------------------------------------------------
 def geom_records(n: int) -> np.ndarray:
@@ -209,6 +246,168 @@ def crop_reflect(x, i, j, pad: int, size: int, out=None):
     rec["dx"] = np.broadcast_to(j, (k,))
     rec["pad"] = pad
     return geometry(x, rec, out_hw=(size, size), out=out)
+
+
+# ------------------------------------------------------------------------------------------------
+# Pillow resample
+# ------------------------------------------------------------------------------------------------
+_table_cache = {}
+
+
+def resample_table_host(in_size: int, out_size: int, filt: int) -> np.ndarray:
+    """Pillow's Q22 coefficient table for one axis, built by the library's host helper."""
+    lib = L.load()
+    words = lib.imgtx_resample_table_words(in_size, out_size, filt)
+    if words < 0:
+        raise ValueError("bad resample table request")
+    tab = np.empty(words, dtype=np.int32)
+    L.check(lib.imgtx_resample_table_host(in_size, out_size, filt, tab.ctypes.data))
+    return tab
+
+
+def _resample_table(in_size: int, out_size: int, filt: int, device) -> torch.Tensor:
+    key = (in_size, out_size, filt, str(device))
+    t = _table_cache.get(key)
+    if t is None:
+        t = torch.from_numpy(resample_table_host(in_size, out_size, filt)).to(device)
+        _table_cache[key] = t
+    return t
+
+
+def resample(x: torch.Tensor, resized_wh, filt: int, crop_box=None, crop_xy=None, out_hw=None, place_xy=(0, 0),
+             out=None) -> torch.Tensor:
+    """canvas(out_hw) <- resize(crop(x, box), resized_wh, filt) placed at place_xy (negative = crop).
+
+    crop_box = (x, y, w, h) uniform; crop_xy = (n, 2) per-image origins (x, y) overriding the box origin."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    bx, by, bw, bh = crop_box if crop_box is not None else (0, 0, w, h)
+    rw, rh = resized_wh
+    oh, ow = out_hw if out_hw is not None else (rh, rw)
+    out = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device) if out is None else out
+    ht = _resample_table(bw, rw, filt, x.device) if rw != bw else None
+    vt = _resample_table(bh, rh, filt, x.device) if rh != bh else None
+    cxy = None
+    if crop_xy is not None:
+        cxy = crop_xy if isinstance(crop_xy, torch.Tensor) else torch.from_numpy(
+            np.ascontiguousarray(np.asarray(crop_xy, dtype=np.int32).reshape(n, 2)))
+        cxy = cxy.to(device=x.device, dtype=torch.int32).contiguous()
+    L.check(L.load().imgtx_resample_u8(
+        x.data_ptr(), out.data_ptr(), n, h, w, c, int(bx), int(by), int(bw), int(bh),
+        cxy.data_ptr() if cxy is not None else None, int(rw), int(rh),
+        ht.data_ptr() if ht is not None else None, ht.numel() if ht is not None else 0,
+        vt.data_ptr() if vt is not None else None, vt.numel() if vt is not None else 0,
+        oh, ow, int(place_xy[0]), int(place_xy[1]), _stream()))
+    return out
+
+
+def apply_scale(x: torch.Tensor, s: float, out=None) -> torch.Tensor:
+    """reference apply_scale: LANCZOS resize to int(w*s) x int(h*s), centre crop (s>1) or zero-pad paste (s<1)."""
+    n, h, w, c = x.shape
+    nw, nh = int(w * s), int(h * s)
+    if s > 1.0:
+        place = (-((nw - w) // 2), -((nh - h) // 2))
+        return resample(x, (nw, nh), L.FILTER_LANCZOS, out_hw=(h, w), place_xy=place, out=out)
+    if s < 1.0:
+        place = ((w - nw) // 2, (h - nh) // 2)
+        return resample(x, (nw, nh), L.FILTER_LANCZOS, out_hw=(h, w), place_xy=place, out=out)
+    return resample(x, (nw, nh), L.FILTER_LANCZOS, out=out)
+
+
+def crop_resize(x: torch.Tensor, cx, cy, cs: int, out_size: int = 32, filt: int = None, out=None) -> torch.Tensor:
+    """rand_crop: crop (cx, cy, cx+cs, cy+cs) per image, then resize((out_size, out_size)) (BICUBIC)."""
+    n = x.shape[0]
+    filt = L.FILTER_BICUBIC if filt is None else filt
+    cxy = np.stack([np.broadcast_to(np.asarray(cx), (n,)), np.broadcast_to(np.asarray(cy), (n,))], axis=1)
+    return resample(x, (out_size, out_size), filt, crop_box=(0, 0, cs, cs), crop_xy=cxy, out=out)
+
+
+def resize_center_crop(x: torch.Tensor, size: int, crop: int, out=None) -> torch.Tensor:
+    """T.Resize(size) (BILINEAR, smaller edge) + T.CenterCrop(crop) on PIL images."""
+    n, h, w, c = x.shape
+    if w <= h:
+        ow, oh = size, int(size * h / w)
+    else:
+        oh, ow = size, int(size * w / h)
+    top = int(round((oh - crop) / 2.0))
+    left = int(round((ow - crop) / 2.0))
+    return resample(x, (ow, oh), L.FILTER_BILINEAR, out_hw=(crop, crop), place_xy=(-left, -top), out=out)
+
+
+# ------------------------------------------------------------------------------------------------
+# stencils
+# ------------------------------------------------------------------------------------------------
+def cv_gaussian_blur(x: torch.Tensor, ksize: int, sigma: float, out=None) -> torch.Tensor:
+    """cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    L.check(L.load().imgtx_cv_gaussian_blur_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, int(ksize), float(sigma),
+                                               _stream()))
+    return out
+
+
+def apply_blur(x: torch.Tensor, blur_radius: float, out=None) -> torch.Tensor:
+    """reference apply_blur: ksize = odd(int(6 r)) (min 3), sigma = r; r == 0 is the identity."""
+    if blur_radius == 0:
+        return pointwise(x, L.PW_IDENTITY, 0.0, out)
+    ksize = int(blur_radius * 6)
+    if ksize % 2 == 0:
+        ksize += 1
+    if ksize < 3:
+        ksize = 3
+    return cv_gaussian_blur(x, ksize, blur_radius, out)
+
+
+def pil_gaussian_blur(x: torch.Tensor, radius: float, out=None) -> torch.Tensor:
+    """img.filter(ImageFilter.GaussianBlur(radius))."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    L.check(L.load().imgtx_pil_gaussian_blur_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, float(radius), _stream()))
+    return out
+
+
+def box_filter_h(x: torch.Tensor, size: int, out=None) -> torch.Tensor:
+    """TransformationPool.motion_blur: cv2.filter2D with a horizontal 1/size box."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    L.check(L.load().imgtx_box_filter_h_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, int(size), _stream()))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# noise
+# ------------------------------------------------------------------------------------------------
+_NOISE_DRAW_DTYPE = {L.NOISE_GAUSS_F32: torch.float32, L.NOISE_GAUSS_F64: torch.float64,
+                     L.NOISE_IMPULSE: torch.float64, L.NOISE_SHOT: torch.int64}
+
+
+def noise_injected(x: torch.Tensor, kind: int, draws, param: float = 0.0, out=None) -> torch.Tensor:
+    """Parity mode: `draws` are the reference's RNG draws (numpy array or tensor, see include/imgtx.h)."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    dt = _NOISE_DRAW_DTYPE[kind]
+    d = draws if isinstance(draws, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(draws))
+    d = d.to(device=x.device, dtype=dt).contiguous()
+    want = n * h * w * (1 if kind == L.NOISE_IMPULSE else c)
+    if d.numel() != want:
+        raise ValueError(f"expected {want} draws, got {d.numel()}")
+    L.check(L.load().imgtx_noise_injected_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, kind, d.data_ptr(), float(param),
+                                             _stream()))
+    return out
+
+
+def noise_philox(x: torch.Tensor, kind: int, param: float, seed: int, out=None) -> torch.Tensor:
+    """Throughput mode: draws generated on chip (Philox4x32-10)."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    L.check(L.load().imgtx_noise_philox_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, kind, float(param),
+                                           int(seed) & 0xFFFFFFFFFFFFFFFF, _stream()))
+    return out
 
 
 # ------------------------------------------------------------------------------------------------

@@ -6,6 +6,8 @@
 //     struct Params { ... };                       // POD, passed by value
 //     static constexpr int kThreads = 256;
 //     static size_t scratch_bytes(const Shape&, int G);   // extra shared memory per CTA
+//     static __device__ void prepare(const Shape&, const Params&, uint8_t* scratch, bool staged);
+//                                                          // once per CTA (e.g. batch-uniform tables)
 //     template <bool STAGED>
 //     static __device__ void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0,
 //                                const Shape& s, const Params& p, uint8_t* scratch, uint8_t* gtmp);
@@ -67,6 +69,8 @@ staged_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t
   }
   __syncthreads();
 
+  Op::prepare(s, p, scratch, true);
+
   // prologue: fill the ring
   if (tid == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -121,6 +125,8 @@ direct_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t
               typename Op::Params p, uint8_t* gtmp, size_t gtmp_per_cta) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* my_tmp = gtmp ? gtmp + (size_t)blockIdx.x * gtmp_per_cta : nullptr;
+  Op::prepare(s, p, smem, false);
+  __syncthreads();
   for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
     Op::template run<false>(in + img * s.in_bytes, out + img * s.out_bytes, 1, img, s, p, smem, my_tmp);
     __syncthreads();
@@ -170,7 +176,7 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
     return IMGTX_OK;
   }
   // direct mode
-  size_t scratch = Op::scratch_bytes(s, 1);
+  size_t scratch = Op::scratch_bytes_direct(s);
   uint8_t* gtmp = nullptr;
   size_t gtmp_per_cta = 0;
   int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 8);
@@ -193,6 +199,26 @@ struct NoSpill {
   static size_t gtmp_bytes(const Shape&) { return 0; }
   static size_t scratch_bytes_spilled(const Shape&) { return 0; }
 };
+struct NoPrepare {
+  template <class S, class P>
+  __device__ static void prepare(const S&, const P&, uint8_t*, bool) {}
+};
+
+// ---- shared-memory byte helpers used by the gather-style operators -----------------------------
+// 3 bytes starting at an arbitrary byte address (reads the two enclosing aligned words; staged buffers
+// are padded so the second word is always readable).
+__device__ __forceinline__ uint32_t load_rgb(const uint8_t* p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+  return __funnelshift_r(w[0], w[1], (uint32_t)(a & 3) * 8) & 0x00FFFFFFu;
+}
+// pack four 24-bit pixels into three words (little endian byte order r0 g0 b0 r1 ...)
+__device__ __forceinline__ void pack_rgb4(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3, uint32_t& w0,
+                                          uint32_t& w1, uint32_t& w2) {
+  w0 = p0 | (p1 << 24);
+  w1 = (p1 >> 8) | (p2 << 16);
+  w2 = (p2 >> 16) | (p3 << 8);
+}
 
 #endif  // __CUDACC__
 }  // namespace imgtx

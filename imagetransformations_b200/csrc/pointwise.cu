@@ -6,57 +6,64 @@
 // Roofline: HBM, 1 B read + 1 B written per element.
 #include "common.cuh"
 #include "lut.cuh"
+#include <stdlib.h>
 
 namespace imgtx {
 
 // ---- uniform parameter: one LUT for the whole batch, replicated per shared-memory bank ----------
-// lut32 layout: word (e>>2)*32 + lane holds entries 4*(e>>2)..+3 for that lane => lane L only ever
-// touches bank L, so the 16 dependent byte lookups of a thread never conflict with its warp mates.
-constexpr int kPwThreads = 256;
+// lut layout: word e*32 + lane holds entry e for that lane => lane L only ever touches bank L, so the 16
+// dependent lookups of a thread never conflict with its warp mates; the byte index of a lookup is
+// ((value << 7) | lane*4), i.e. one shift and one 3-input logic op.
+constexpr int kPwThreads = 256;    // per-image kernel
+constexpr int kPwUniThreads = 512;
+constexpr int kPwLutBytes = 256 * 32 * 4;
 
-__device__ __forceinline__ uint32_t lut4(const uint8_t* lane_lut, uint32_t w) {
-  // lane_lut already points at this lane's bank column
-  uint32_t b0 = lane_lut[((w & 0xFCu) << 5) | (w & 3u)];
-  uint32_t w1 = w >> 8, w2 = w >> 16, w3 = w >> 24;
-  uint32_t b1 = lane_lut[((w1 & 0xFCu) << 5) | (w1 & 3u)];
-  uint32_t b2 = lane_lut[((w2 & 0xFCu) << 5) | (w2 & 3u)];
-  uint32_t b3 = lane_lut[((w3 & 0xFCu) << 5) | (w3 & 3u)];
-  return b0 | (b1 << 8) | (b2 << 16) | (b3 << 24);
+__device__ __forceinline__ uint32_t lut4(const uint8_t* lut, uint32_t lane4, uint32_t w) {
+  const uint32_t i0 = ((w << 7) & 0x7F80u) | lane4;
+  const uint32_t i1 = ((w >> 1) & 0x7F80u) | lane4;
+  const uint32_t i2 = ((w >> 9) & 0x7F80u) | lane4;
+  const uint32_t i3 = ((w >> 17) & 0x7F80u) | lane4;
+  const uint32_t v0 = *reinterpret_cast<const uint32_t*>(lut + i0);
+  const uint32_t v1 = *reinterpret_cast<const uint32_t*>(lut + i1);
+  const uint32_t v2 = *reinterpret_cast<const uint32_t*>(lut + i2);
+  const uint32_t v3 = *reinterpret_cast<const uint32_t*>(lut + i3);
+  return __byte_perm(__byte_perm(v0, v1, 0x0040), __byte_perm(v2, v3, 0x0040), 0x5410);
+}
+__device__ __forceinline__ uint4 lut16(const uint8_t* lut, uint32_t lane4, uint4 a) {
+  a.x = lut4(lut, lane4, a.x); a.y = lut4(lut, lane4, a.y);
+  a.z = lut4(lut, lane4, a.z); a.w = lut4(lut, lane4, a.w);
+  return a;
 }
 
-__global__ void __launch_bounds__(kPwThreads)
+__global__ void __launch_bounds__(kPwUniThreads)
 pointwise_uniform_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int64_t n_vec,
                          const uint8_t* __restrict__ in_tail, uint8_t* __restrict__ out_tail,
                          int n_tail, int op, float param) {
-  __shared__ __align__(16) uint8_t lut[256 * 32];
+  extern __shared__ __align__(16) uint8_t lut[];
   {
-    const int e = threadIdx.x;  // kPwThreads == 256
-    const uint8_t v = lut_entry(op, param, e);
-    const int base = ((e & 0xFC) << 5) | (e & 3);
-#pragma unroll
-    for (int l = 0; l < 32; ++l) lut[base + l * 4] = v;
+    uint32_t* l32 = reinterpret_cast<uint32_t*>(lut);
+    // thread t fills entries t/32 + 16k for its own lane column: 16 formula evaluations per thread
+    for (int i = threadIdx.x; i < 256 * 32; i += kPwUniThreads) l32[i] = lut_entry(op, param, i >> 5);
   }
   __syncthreads();
-  const uint8_t* lane_lut = lut + (threadIdx.x & 31) * 4;
+  const uint32_t lane4 = (threadIdx.x & 31) * 4;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // two independent 16-byte loads in flight per thread
-  for (; i + stride < n_vec; i += 2 * stride) {
+  // four independent 16-byte loads in flight per thread
+  for (; i + 3 * stride < n_vec; i += 4 * stride) {
     uint4 a = ldg_stream(in + i);
     uint4 b = ldg_stream(in + i + stride);
-    a.x = lut4(lane_lut, a.x); a.y = lut4(lane_lut, a.y); a.z = lut4(lane_lut, a.z); a.w = lut4(lane_lut, a.w);
-    b.x = lut4(lane_lut, b.x); b.y = lut4(lane_lut, b.y); b.z = lut4(lane_lut, b.z); b.w = lut4(lane_lut, b.w);
-    stg_stream(out + i, a);
-    stg_stream(out + i + stride, b);
+    uint4 c = ldg_stream(in + i + 2 * stride);
+    uint4 d = ldg_stream(in + i + 3 * stride);
+    stg_stream(out + i, lut16(lut, lane4, a));
+    stg_stream(out + i + stride, lut16(lut, lane4, b));
+    stg_stream(out + i + 2 * stride, lut16(lut, lane4, c));
+    stg_stream(out + i + 3 * stride, lut16(lut, lane4, d));
   }
-  if (i < n_vec) {
-    uint4 a = ldg_stream(in + i);
-    a.x = lut4(lane_lut, a.x); a.y = lut4(lane_lut, a.y); a.z = lut4(lane_lut, a.z); a.w = lut4(lane_lut, a.w);
-    stg_stream(out + i, a);
-  }
+  for (; i < n_vec; i += stride) stg_stream(out + i, lut16(lut, lane4, ldg_stream(in + i)));
   if (blockIdx.x == 0 && (int)threadIdx.x < n_tail) {
-    uint32_t e = in_tail[threadIdx.x];
-    out_tail[threadIdx.x] = lane_lut[((e & 0xFCu) << 5) | (e & 3u)];
+    const uint32_t e = in_tail[threadIdx.x];
+    out_tail[threadIdx.x] = (uint8_t) * reinterpret_cast<const uint32_t*>(lut + ((e << 7) | lane4));
   }
 }
 
@@ -121,9 +128,13 @@ extern "C" int imgtx_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, in
       IMGTX_CUDA_OK(cudaFreeAsync(tmp, stream));
       return IMGTX_OK;
     }
-    int64_t want = (n_vec + 2 * kPwThreads - 1) / (2 * kPwThreads);
-    int64_t grid = want < 1 ? 1 : (want > (int64_t)sm_count() * 8 ? (int64_t)sm_count() * 8 : want);
-    pointwise_uniform_kernel<<<(unsigned)grid, kPwThreads, 0, stream>>>(
+    static const int kCtasPerSm = getenv("IMGTX_PW_CTAS") ? atoi(getenv("IMGTX_PW_CTAS")) : 4;
+    int64_t want = (n_vec + 4 * kPwUniThreads - 1) / (4 * kPwUniThreads);
+    int64_t cap = (int64_t)sm_count() * kCtasPerSm;
+    int64_t grid = want < 1 ? 1 : (want > cap ? cap : want);
+    IMGTX_CUDA_OK(cudaFuncSetAttribute(pointwise_uniform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kPwLutBytes));
+    pointwise_uniform_kernel<<<(unsigned)grid, kPwUniThreads, kPwLutBytes, stream>>>(
         reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), n_vec, in + tail0,
         out + tail0, (int)rem, op, param);
     IMGTX_LAUNCH_OK();

@@ -1,0 +1,304 @@
+// Pillow ImagingResample (Image.resize) on uint8 HWC images, fused with the integer crop in front of it
+// and the crop / zero-pad paste behind it.  Two passes (horizontal first), Q22 integer coefficients,
+// uint8 intermediate — bit-exact with libImaging/Resample.c.
+//   reference call sites: transformation.py:173-196 (apply_scale: LANCZOS + centre crop / pad),
+//   fall_2025/tta_initial_claudeFixed.py:56-62 and fall_2025/transformations_code:43-48 (rand_crop:
+//   crop 24x24 + BICUBIC resize to 32x32), fall_2025/TTA_transforms.py:104-113 (Resize(36|40) BILINEAR +
+//   CenterCrop(32)), CIFAR-10-C pixelate (BOX down/up).
+// Coefficient tables depend only on (in_size, out_size, filter): they are built on the host in double
+// exactly as Pillow does (imgtx_resample_table_host) and uploaded once by the caller.
+// Roofline: nominally HBM (in_bytes + out_bytes per image) but the 2x(up to 7-tap) integer stencil makes
+// this pass instruction-bound; see DESIGN.md.
+#include "pipeline.cuh"
+#include <math.h>
+#include <string.h>
+#include <vector>
+
+namespace imgtx {
+
+// table layout (int32 words): [0]=out_size, [1]=ksize, then out_size records of (xmin, n, k[ksize])
+struct ResampleParams {
+  const int32_t* htab;  // device; nullptr = horizontal pass skipped (same width)
+  const int32_t* vtab;  // device; nullptr = vertical pass skipped
+  int htab_words, vtab_words;
+  int crop_x, crop_y, crop_w, crop_h;
+  const int32_t* crop_xy;  // device (n,2) per-image crop origin, nullable
+  int rw, rh;              // resized size
+  int place_x, place_y;    // where the resized image's origin lands in the output canvas
+};
+
+struct OpResample {
+  using Params = ResampleParams;
+  static constexpr int kThreads = 256;
+  // needed part of the resized image: columns [cx0, cx0+ncols) x rows [ry0, ry0+nrows)
+  __host__ __device__ static void needed(const Shape& s, const Params& p, int& cx0, int& ncols, int& ry0, int& nrows) {
+    cx0 = p.place_x < 0 ? -p.place_x : 0;
+    int cx1 = p.rw < s.ow - p.place_x ? p.rw : s.ow - p.place_x;
+    ncols = cx1 > cx0 ? cx1 - cx0 : 0;
+    ry0 = p.place_y < 0 ? -p.place_y : 0;
+    int ry1 = p.rh < s.oh - p.place_y ? p.rh : s.oh - p.place_y;
+    nrows = ry1 > ry0 ? ry1 - ry0 : 0;
+  }
+  // scratch: [tables (htab+vtab words)] [tmp: crop_h * ncols * c bytes]
+  static size_t table_bytes(const Params& p) { return align_up((size_t)(p.htab_words + p.vtab_words) * 4, 16); }
+  static size_t tmp_bytes(const Shape& s, const Params& p) {
+    int cx0, ncols, ry0, nrows;
+    needed(s, p, cx0, ncols, ry0, nrows);
+    return align_up((size_t)p.crop_h * (ncols > 0 ? ncols : 1) * s.c + 4, 16);
+  }
+  // Params are not available to scratch_bytes(); the launcher below sizes scratch itself.
+  static size_t gtmp_bytes(const Shape&) { return 0; }
+  static size_t scratch_bytes_spilled(const Shape&) { return 0; }
+
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    int32_t* t = reinterpret_cast<int32_t*>(scratch);
+    for (int i = threadIdx.x; i < p.htab_words; i += kThreads) t[i] = p.htab[i];
+    for (int i = threadIdx.x; i < p.vtab_words; i += kThreads) t[p.htab_words + i] = p.vtab[i];
+    __syncthreads();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s,
+                             const Params& p, uint8_t* scratch, uint8_t* gtmp) {
+    const int tid = threadIdx.x;
+    const int c = s.c;
+    const int32_t* ht = p.htab ? reinterpret_cast<const int32_t*>(scratch) : nullptr;
+    const int32_t* vt = p.vtab ? reinterpret_cast<const int32_t*>(scratch) + p.htab_words : nullptr;
+    uint8_t* tmp = gtmp ? gtmp : scratch + align_up((size_t)(p.htab_words + p.vtab_words) * 4, 16);
+    int cx0, ncols, ry0, nrows;
+    needed(s, p, cx0, ncols, ry0, nrows);
+    const int hk = ht ? ht[1] : 0, vk = vt ? vt[1] : 0;
+    for (int j = 0; j < g; ++j) {
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      uint8_t* om = dst + (size_t)j * s.out_bytes;
+      int ox = p.crop_x, oy = p.crop_y;
+      if (p.crop_xy) { ox = p.crop_xy[(img0 + j) * 2]; oy = p.crop_xy[(img0 + j) * 2 + 1]; }
+      // zero the canvas if the resized image does not cover it
+      const bool covers = (p.place_x <= 0 && p.place_y <= 0 && p.place_x + p.rw >= s.ow && p.place_y + p.rh >= s.oh);
+      if (!covers) {
+        for (int i = tid; i < s.out_bytes; i += kThreads) om[i] = 0;
+      }
+      __syncthreads();
+      // pass 1: horizontal, rows of the crop box, needed columns only -> tmp (crop_h x ncols)
+      for (int i = tid; i < p.crop_h * ncols; i += kThreads) {
+        const int y = i / ncols, xx = i - y * ncols;
+        const uint8_t* row = im + ((size_t)(oy + y) * s.w + ox) * c;
+        uint8_t* t = tmp + (size_t)i * c;
+        if (ht) {
+          const int32_t* rec = ht + 2 + (cx0 + xx) * (2 + hk);
+          const int xmin = rec[0], n = rec[1];
+          int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+          if (c == 3) {
+            for (int k = 0; k < n; ++k) {
+              const int kk = rec[2 + k];
+              const uint8_t* sp = row + (xmin + k) * 3;
+              a0 += sp[0] * kk; a1 += sp[1] * kk; a2 += sp[2] * kk;
+            }
+            t[0] = clip8(a0 >> 22); t[1] = clip8(a1 >> 22); t[2] = clip8(a2 >> 22);
+          } else {
+            for (int ch = 0; ch < c; ++ch) {
+              int a = 1 << 21;
+              for (int k = 0; k < n; ++k) a += row[(xmin + k) * c + ch] * rec[2 + k];
+              t[ch] = clip8(a >> 22);
+            }
+          }
+        } else {
+          for (int ch = 0; ch < c; ++ch) t[ch] = row[(cx0 + xx) * c + ch];
+        }
+      }
+      __syncthreads();
+      // pass 2: vertical, needed rows -> canvas
+      for (int i = tid; i < nrows * ncols; i += kThreads) {
+        const int yy = i / ncols, xx = i - yy * ncols;
+        uint8_t* o = om + ((size_t)(p.place_y + ry0 + yy) * s.ow + (p.place_x + cx0 + xx)) * c;
+        if (vt) {
+          const int32_t* rec = vt + 2 + (ry0 + yy) * (2 + vk);
+          const int ymin = rec[0], n = rec[1];
+          if (c == 3) {
+            int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+            for (int k = 0; k < n; ++k) {
+              const int kk = rec[2 + k];
+              const uint8_t* sp = tmp + ((size_t)(ymin + k) * ncols + xx) * 3;
+              a0 += sp[0] * kk; a1 += sp[1] * kk; a2 += sp[2] * kk;
+            }
+            o[0] = clip8(a0 >> 22); o[1] = clip8(a1 >> 22); o[2] = clip8(a2 >> 22);
+          } else {
+            for (int ch = 0; ch < c; ++ch) {
+              int a = 1 << 21;
+              for (int k = 0; k < n; ++k) a += tmp[((size_t)(ymin + k) * ncols + xx) * c + ch] * rec[2 + k];
+              o[ch] = clip8(a >> 22);
+            }
+          }
+        } else {
+          const uint8_t* sp = tmp + ((size_t)(ry0 + yy) * ncols + xx) * c;
+          for (int ch = 0; ch < c; ++ch) o[ch] = sp[ch];
+        }
+      }
+      __syncthreads();
+    }
+  }
+};
+
+// Specialised launcher: scratch depends on the parameters (table sizes, needed window).
+static int launch_resample(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, const ResampleParams& p,
+                           cudaStream_t stream) {
+  if (n <= 0) return IMGTX_OK;
+  const StagedTuning tn = staged_tuning();
+  const int max_smem = max_smem_optin();
+  const size_t op_scratch = OpResample::table_bytes(p) + OpResample::tmp_bytes(s, p);
+  bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);
+  int G = 1, stages = tn.stages;
+  size_t smem_bytes = 0;
+  auto need = [&](int g, int st) {
+    return (size_t)kBarBytes + align_up((size_t)g * s.in_bytes, 128) * st + align_up((size_t)g * s.out_bytes, 128) * 2 +
+           op_scratch + 128;
+  };
+  if (staged) {
+    while (stages > 2 && need(1, stages) > (size_t)tn.target_smem) --stages;
+    if (need(1, stages) > (size_t)max_smem - 1024) staged = false;
+    else {
+      while (G < 64 && need(G + 1, stages) <= (size_t)tn.target_smem) ++G;
+      smem_bytes = need(G, stages);
+    }
+  }
+  if (staged) {
+    auto kern = staged_kernel<OpResample>;
+    IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    int64_t n_groups = (n + G - 1) / G;
+    int per_sm = (int)std::max<size_t>(1, std::min<size_t>(tn.ctas_per_sm, (size_t)max_smem / smem_bytes));
+    int64_t grid = std::min<int64_t>(n_groups, (int64_t)sm_count() * per_sm);
+    kern<<<(unsigned)grid, OpResample::kThreads, smem_bytes, stream>>>(in, out, n, s, p, G, stages);
+    IMGTX_LAUNCH_OK();
+    return IMGTX_OK;
+  }
+  // direct mode; intermediate plane in shared memory if it fits, else in a stream-ordered workspace
+  size_t scratch = op_scratch;
+  int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 4);
+  uint8_t* gtmp = nullptr;
+  size_t per_cta = 0;
+  if (scratch > (size_t)max_smem - 1024) {
+    per_cta = align_up(OpResample::tmp_bytes(s, p), 256);
+    scratch = OpResample::table_bytes(p) + 16;
+    IMGTX_CHECK_ARG(scratch <= (size_t)max_smem - 1024, "resample tables do not fit in shared memory");
+    IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, per_cta * grid, stream));
+  }
+  auto kern = direct_kernel<OpResample>;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch));
+  kern<<<(unsigned)grid, OpResample::kThreads, scratch, stream>>>(in, out, n, s, p, gtmp, per_cta);
+  IMGTX_LAUNCH_OK();
+  if (gtmp) IMGTX_CUDA_OK(cudaFreeAsync(gtmp, stream));
+  return IMGTX_OK;
+}
+
+// ---- host: Pillow coefficient tables ----------------------------------------------------------
+static double filt_box(double x) { return (x > -0.5 && x <= 0.5) ? 1.0 : 0.0; }
+static double filt_bilinear(double x) {
+  if (x < 0.0) x = -x;
+  return x < 1.0 ? 1.0 - x : 0.0;
+}
+static double filt_bicubic(double x) {
+  const double a = -0.5;
+  if (x < 0.0) x = -x;
+  if (x < 1.0) return ((a + 2.0) * x - (a + 3.0)) * x * x + 1;
+  if (x < 2.0) return (((x - 5) * x + 8) * x - 4) * a;
+  return 0.0;
+}
+static double sinc(double x) {
+  if (x == 0.0) return 1.0;
+  x = x * M_PI;
+  return sin(x) / x;
+}
+static double filt_lanczos(double x) { return (-3.0 <= x && x < 3.0) ? sinc(x) * sinc(x / 3) : 0.0; }
+
+static bool filter_info(int filter, double (**fn)(double), double* support) {
+  switch (filter) {
+    case IMGTX_FILTER_BOX: *fn = filt_box; *support = 0.5; return true;
+    case IMGTX_FILTER_BILINEAR: *fn = filt_bilinear; *support = 1.0; return true;
+    case IMGTX_FILTER_BICUBIC: *fn = filt_bicubic; *support = 2.0; return true;
+    case IMGTX_FILTER_LANCZOS: *fn = filt_lanczos; *support = 3.0; return true;
+  }
+  return false;
+}
+
+static int table_ksize(int in_size, int out_size, double support0) {
+  double filterscale = (double)in_size / out_size;
+  if (filterscale < 1.0) filterscale = 1.0;
+  return (int)ceil(support0 * filterscale) * 2 + 1;
+}
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int64_t imgtx_resample_table_words(int in_size, int out_size, int filter) {
+  double (*fn)(double);
+  double support0;
+  if (in_size <= 0 || out_size <= 0 || !filter_info(filter, &fn, &support0)) return -1;
+  return 2 + (int64_t)out_size * (2 + table_ksize(in_size, out_size, support0));
+}
+
+extern "C" int imgtx_resample_table_host(int in_size, int out_size, int filter, int32_t* table_host) {
+  double (*fn)(double);
+  double support0;
+  IMGTX_CHECK_ARG(in_size > 0 && out_size > 0 && table_host, "bad table arguments");
+  IMGTX_CHECK_ARG(filter_info(filter, &fn, &support0), "unknown filter %d", filter);
+  // libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc
+  double scale, filterscale;
+  scale = filterscale = (double)in_size / out_size;
+  if (filterscale < 1.0) filterscale = 1.0;
+  const double support = support0 * filterscale;
+  const int ksize = (int)ceil(support) * 2 + 1;
+  table_host[0] = out_size;
+  table_host[1] = ksize;
+  std::vector<double> k(ksize);
+  const double ss = 1.0 / filterscale;
+  for (int xx = 0; xx < out_size; ++xx) {
+    const double center = 0.0 + (xx + 0.5) * scale;
+    double ww = 0.0;
+    int xmin = (int)(center - support + 0.5);
+    if (xmin < 0) xmin = 0;
+    int xmax = (int)(center + support + 0.5);
+    if (xmax > in_size) xmax = in_size;
+    xmax -= xmin;
+    for (int x = 0; x < xmax; ++x) {
+      double w = fn((x + xmin - center + 0.5) * ss);
+      k[x] = w;
+      ww += w;
+    }
+    for (int x = 0; x < xmax; ++x)
+      if (ww != 0.0) k[x] /= ww;
+    int32_t* rec = table_host + 2 + (size_t)xx * (2 + ksize);
+    rec[0] = xmin;
+    rec[1] = xmax;
+    for (int x = 0; x < ksize; ++x) {
+      double v = x < xmax ? k[x] : 0.0;
+      rec[2 + x] = v < 0 ? (int)(-0.5 + v * (1 << 22)) : (int)(0.5 + v * (1 << 22));
+    }
+  }
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int crop_x,
+                                 int crop_y, int crop_w, int crop_h, const int32_t* crop_xy_per_image_dev, int rw,
+                                 int rh, const int32_t* htable_dev, int64_t htable_words, const int32_t* vtable_dev,
+                                 int64_t vtable_words, int oh, int ow, int place_x, int place_y,
+                                 imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4 && oh > 0 && ow > 0, "bad image shape");
+  IMGTX_CHECK_ARG(crop_w > 0 && crop_h > 0 && crop_w <= w && crop_h <= h, "bad crop box");
+  if (!crop_xy_per_image_dev)
+    IMGTX_CHECK_ARG(crop_x >= 0 && crop_y >= 0 && crop_x + crop_w <= w && crop_y + crop_h <= h, "crop box outside image");
+  IMGTX_CHECK_ARG(rw > 0 && rh > 0, "bad resized size");
+  IMGTX_CHECK_ARG((htable_dev != nullptr) == (rw != crop_w), "horizontal table must be given iff the width changes");
+  IMGTX_CHECK_ARG((vtable_dev != nullptr) == (rh != crop_h), "vertical table must be given iff the height changes");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null image pointer");
+  ResampleParams p;
+  memset(&p, 0, sizeof(p));
+  p.htab = htable_dev; p.vtab = vtable_dev;
+  p.htab_words = htable_dev ? (int)htable_words : 0;
+  p.vtab_words = vtable_dev ? (int)vtable_words : 0;
+  p.crop_x = crop_x; p.crop_y = crop_y; p.crop_w = crop_w; p.crop_h = crop_h;
+  p.crop_xy = crop_xy_per_image_dev;
+  p.rw = rw; p.rh = rh; p.place_x = place_x; p.place_y = place_y;
+  return launch_resample(in, out, n, make_shape(h, w, c, oh, ow), p, (cudaStream_t)stream);
+}

@@ -97,6 +97,69 @@ int imgtx_geometry_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, 
                       const imgtx_geom_t* uniform_host, const imgtx_geom_t* per_image_dev,
                       const uint8_t* fill_host, imgtx_stream_t stream);
 
+/* ---- per-image statistics + map (ImageEnhance / ImageOps.equalize / cv2 equalizeHist) ------------- */
+typedef enum {
+  IMGTX_ENH_BRIGHTNESS = 0, /* ImageEnhance.Brightness — transformation.py:261-269 */
+  IMGTX_ENH_CONTRAST = 1,   /* ImageEnhance.Contrast — fall_2025/tta_initial_claudeFixed.py:69-72,
+                               pipenline/cifar_image_transformations.py:81-85, T.ColorJitter(contrast) */
+  IMGTX_ENH_COLOR = 2,      /* ImageEnhance.Color — pipenline/cifar_image_transformations.py:102-106 */
+  IMGTX_ENH_SHARPNESS = 3,  /* ImageEnhance.Sharpness — pipenline/cifar_image_transformations.py:95-99 */
+  IMGTX_ENH_EQUALIZE = 4,   /* ImageOps.equalize — fall_2025/AugMix.py:36 (factor ignored) */
+  IMGTX_ENH_HISTEQ_YUV = 5  /* TransformationPool.histogram_equalization —
+                               pipenline/cifar_image_transformations.py:122-129 (factor ignored) */
+} imgtx_enhance_kind;
+int imgtx_enhance_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, float factor,
+                     const float* factor_per_image_dev, imgtx_stream_t stream);
+
+/* ---- Pillow resample (Image.resize) fused with crop-before and crop/pad-after ------------------------ */
+typedef enum {
+  IMGTX_FILTER_BOX = 0,
+  IMGTX_FILTER_BILINEAR = 1,
+  IMGTX_FILTER_BICUBIC = 2,
+  IMGTX_FILTER_LANCZOS = 3
+} imgtx_filter;
+/* Host helpers: size (in int32 words) and contents of the Q22 coefficient table of one axis
+   (libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc).  The caller uploads the table. */
+int64_t imgtx_resample_table_words(int in_size, int out_size, int filter);
+int imgtx_resample_table_host(int in_size, int out_size, int filter, int32_t* table_host);
+/* out canvas (oh, ow) <- zeros; r = resize(crop(in, box), (rw, rh)); canvas[place_y.., place_x..] = r
+   (negative place = crop of r).  box origin uniform (crop_x, crop_y) or per image (crop_xy_per_image_dev,
+   (n,2) int32 x,y).  A table pointer is NULL iff that axis keeps its size (Pillow skips the pass).
+   transformation.py:173-196 (apply_scale), fall_2025/tta_initial_claudeFixed.py:56-62 (rand_crop),
+   fall_2025/TTA_transforms.py:104-113 (Resize+CenterCrop) */
+int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int crop_x, int crop_y,
+                      int crop_w, int crop_h, const int32_t* crop_xy_per_image_dev, int rw, int rh,
+                      const int32_t* htable_dev, int64_t htable_words, const int32_t* vtable_dev,
+                      int64_t vtable_words, int oh, int ow, int place_x, int place_y, imgtx_stream_t stream);
+
+/* ---- stencils ------------------------------------------------------------------------------- */
+/* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
+int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);
+/* cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8 — transformation.py:228-257 (apply_blur) */
+int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
+                              double sigma, imgtx_stream_t stream);
+/* img.filter(ImageFilter.GaussianBlur(radius)) — pipenline/cifar_image_transformations.py:72-77 */
+int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float radius,
+                               imgtx_stream_t stream);
+/* cv2.filter2D with the size x size "middle row = 1/size" kernel —
+   pipenline/cifar_image_transformations.py:109-119 (motion_blur) */
+int imgtx_box_filter_h_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int size,
+                          imgtx_stream_t stream);
+
+/* ---- noise ---------------------------------------------------------------------------------- */
+typedef enum {
+  IMGTX_NOISE_GAUSS_F32 = 0, /* transformation.py:272-281; draws: f32 (n,h,w,c) = normal(0, std*255) cast */
+  IMGTX_NOISE_GAUSS_F64 = 1, /* cifar_image_transformations.py:39-48; draws: f64 (n,h,w,c) */
+  IMGTX_NOISE_IMPULSE = 2,   /* :50-59; draws: f64 (n,h,w) uniform mask; param = noise_prob */
+  IMGTX_NOISE_SHOT = 3       /* :61-70; draws: int64 (n,h,w,c) Poisson counts; param = lambda */
+} imgtx_noise_kind;
+/* parity mode: the reference's RNG draws are inputs */
+int imgtx_noise_injected_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
+                            const void* draws_dev, double param, imgtx_stream_t stream);
+/* throughput mode: on-chip Philox4x32-10 keyed by (seed, element); param = std*255 | prob | lambda */
+int imgtx_noise_philox_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double param,
+                          uint64_t seed, imgtx_stream_t stream);
+
 /* ---- tensors ------------------------------------------------------------------------------ */
 /* T.ToTensor() [+ T.Normalize(mean, std) when mean_host/std_host != NULL]: u8 NHWC -> f32 NCHW.
    fall_2025/TENT_transform.py:56-59, fall_2025/TTA_transforms.py:62-65,

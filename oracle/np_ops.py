@@ -381,3 +381,427 @@ def pgd_step(x, x0, g, alpha, eps, lo, hi):
         lo = lo.reshape(1, -1, 1, 1)
         hi = hi.reshape(1, -1, 1, 1)
     return _clamp_nan(out, lo, hi)
+
+
+# =================================================================================================
+# A.3  Pillow ImagingResample (Image.resize): two passes, Q22 coefficients, uint8 intermediate
+# =================================================================================================
+BOX, BILINEAR, BICUBIC, LANCZOS = 0, 1, 2, 3
+_SUPPORT = {BOX: 0.5, BILINEAR: 1.0, BICUBIC: 2.0, LANCZOS: 3.0}
+
+
+def _filter_value(filt: int, x: float) -> float:
+    if filt == BOX:
+        return 1.0 if -0.5 < x <= 0.5 else 0.0
+    if filt == BILINEAR:
+        x = abs(x)
+        return 1.0 - x if x < 1.0 else 0.0
+    if filt == BICUBIC:
+        a = -0.5
+        x = abs(x)
+        if x < 1.0:
+            return ((a + 2.0) * x - (a + 3.0)) * x * x + 1
+        if x < 2.0:
+            return (((x - 5) * x + 8) * x - 4) * a
+        return 0.0
+    if filt == LANCZOS:
+        def sinc(v):
+            if v == 0.0:
+                return 1.0
+            v = v * math.pi
+            return math.sin(v) / v
+        if -3.0 <= x < 3.0:
+            return sinc(x) * sinc(x / 3)
+        return 0.0
+    raise ValueError(filt)
+
+
+def resample_coeffs(in_size: int, out_size: int, filt: int, box=None):
+    """libImaging/Resample.c precompute_coeffs + normalize_coeffs_8bpc.
+    Returns (xmin[out], n[out], kk[out, ksize] int32 Q22)."""
+    in0, in1 = (0.0, float(in_size)) if box is None else box
+    scale = filterscale = (in1 - in0) / out_size
+    if filterscale < 1.0:
+        filterscale = 1.0
+    support = _SUPPORT[filt] * filterscale
+    ksize = int(math.ceil(support)) * 2 + 1
+    xmins = np.zeros(out_size, np.int32)
+    ns = np.zeros(out_size, np.int32)
+    kk = np.zeros((out_size, ksize), np.int32)
+    ss = 1.0 / filterscale
+    for xx in range(out_size):
+        center = in0 + (xx + 0.5) * scale
+        xmin = int(center - support + 0.5)
+        if xmin < 0:
+            xmin = 0
+        xmax = int(center + support + 0.5)
+        if xmax > in_size:
+            xmax = in_size
+        xmax -= xmin
+        w = [_filter_value(filt, (x + xmin - center + 0.5) * ss) for x in range(xmax)]
+        ww = 0.0
+        for v in w:
+            ww += v
+        for x in range(xmax):
+            if ww != 0.0:
+                w[x] /= ww
+        xmins[xx] = xmin
+        ns[xx] = xmax
+        for x in range(xmax):
+            v = w[x]
+            kk[xx, x] = int(-0.5 + v * (1 << 22)) if v < 0 else int(0.5 + v * (1 << 22))
+    return xmins, ns, kk
+
+
+def _resample_axis(img: np.ndarray, out_size: int, filt: int, axis: int) -> np.ndarray:
+    """One pass along `axis` (1 = vertical/H, 2 = horizontal/W) of an (n,h,w,c) uint8 batch."""
+    in_size = img.shape[axis]
+    xmins, ns, kk = resample_coeffs(in_size, out_size, filt)
+    shp = list(img.shape)
+    shp[axis] = out_size
+    out = np.empty(shp, np.uint8)
+    src = img.astype(np.int64)
+    for xx in range(out_size):
+        x0, n = int(xmins[xx]), int(ns[xx])
+        k = kk[xx, :n].astype(np.int64)
+        if axis == 2:
+            acc = (src[:, :, x0:x0 + n, :] * k[None, None, :, None]).sum(axis=2)
+            out[:, :, xx, :] = np.clip((acc + (1 << 21)) >> 22, 0, 255)
+        else:
+            acc = (src[:, x0:x0 + n, :, :] * k[None, :, None, None]).sum(axis=1)
+            out[:, xx, :, :] = np.clip((acc + (1 << 21)) >> 22, 0, 255)
+    return out
+
+
+def pil_resize(img: np.ndarray, size, filt: int = BICUBIC) -> np.ndarray:
+    """Image.resize((ow, oh), filt): horizontal pass first, each pass skipped if the size is unchanged."""
+    ow, oh = size
+    out = img
+    if ow != img.shape[2]:
+        out = _resample_axis(out, ow, filt, 2)
+    if oh != img.shape[1]:
+        out = _resample_axis(out, oh, filt, 1)
+    return out.copy()
+
+
+def apply_scale(img: np.ndarray, s: float) -> np.ndarray:
+    """transformation.py:173-196: LANCZOS resize to int(w*s) then centre crop / zero-pad paste."""
+    n, h, w, c = img.shape
+    nw, nh = int(w * s), int(h * s)
+    sc = pil_resize(img, (nw, nh), LANCZOS)
+    if s > 1.0:
+        l, t = (nw - w) // 2, (nh - h) // 2
+        return sc[:, t:t + h, l:l + w].copy()
+    if s < 1.0:
+        out = np.zeros_like(img)
+        px, py = (w - nw) // 2, (h - nh) // 2
+        out[:, py:py + nh, px:px + nw] = sc
+        return out
+    return sc
+
+
+def crop_resize(img: np.ndarray, x, y, cs: int, out_size: int = 32, filt: int = BICUBIC) -> np.ndarray:
+    """rand_crop — tta_initial_claudeFixed.py:56-62: crop (x,y,x+cs,y+cs) then resize((32,32)) (BICUBIC default)."""
+    n = img.shape[0]
+    x = np.broadcast_to(np.asarray(x), (n,))
+    y = np.broadcast_to(np.asarray(y), (n,))
+    crops = np.stack([img[i, y[i]:y[i] + cs, x[i]:x[i] + cs] for i in range(n)])
+    return pil_resize(crops, (out_size, out_size), filt)
+
+
+def resize_center_crop(img: np.ndarray, size: int, crop: int) -> np.ndarray:
+    """T.Resize(size) + T.CenterCrop(crop) on PIL (BILINEAR) — TTA_transforms.py:104-113."""
+    n, h, w, c = img.shape
+    if w <= h:
+        ow, oh = size, int(size * h / w)
+    else:
+        oh, ow = size, int(size * w / h)
+    r = pil_resize(img, (ow, oh), BILINEAR)
+    top = int(round((oh - crop) / 2.0))
+    left = int(round((ow - crop) / 2.0))
+    return r[:, top:top + crop, left:left + crop].copy()
+
+
+# =================================================================================================
+# A.2  Pillow generic transform with BILINEAR / BICUBIC filters (f64)
+# =================================================================================================
+
+
+def _bicubic_w(v1, v2, v3, v4, d):
+    p1 = v2
+    p2 = -v1 + v3
+    p3 = 2 * (v1 - v2) + v3 - v4
+    p4 = -v1 + v2 - v3 + v4
+    return p1 + d * (p2 + d * (p3 + d * p4))
+
+
+def pil_transform(img: np.ndarray, coeffs, out_size, mode="affine", resample="bicubic", fill=0) -> np.ndarray:
+    """Image.transform(size, AFFINE|PERSPECTIVE, coeffs, resample=BILINEAR|BICUBIC, fillcolor=fill).
+    libImaging/Geometry.c ImagingGenericTransform + bilinear_filter8 / bicubic_filter8.
+    reference: transformation.py:212-226 (apply_shear), fall_2025/Initial_Experiments.py:88-92."""
+    n, h, w, c = img.shape
+    ow, oh = out_size
+    a = [float(v) for v in coeffs]
+    out = np.empty((n, oh, ow, c), np.uint8)
+    out[:] = np.broadcast_to(np.asarray(fill, np.uint8), (c,))
+    ys, xs = np.mgrid[0:oh, 0:ow]
+    xin = xs + 0.5
+    yin = ys + 0.5
+    if mode == "affine":
+        sx = a[0] * xin + a[1] * yin + a[2]
+        sy = a[3] * xin + a[4] * yin + a[5]
+    else:
+        den = a[6] * xin + a[7] * yin + 1
+        sx = (a[0] * xin + a[1] * yin + a[2]) / den
+        sy = (a[3] * xin + a[4] * yin + a[5]) / den
+    valid = ~((sx < 0.0) | (sx >= w) | (sy < 0.0) | (sy >= h))
+    sx = sx - 0.5
+    sy = sy - 0.5
+    x0 = np.floor(sx).astype(np.int64)
+    y0 = np.floor(sy).astype(np.int64)
+    dx = sx - x0
+    dy = sy - y0
+    src = img.astype(np.float64)
+
+    def px(yy, xx):
+        return src[:, yy, np.clip(xx, 0, w - 1), :]  # (n, oh, ow, c)
+
+    if resample == "bilinear":
+        def row(yy):
+            yyc = np.clip(yy, 0, h - 1)
+            l = src[:, yyc, np.clip(x0, 0, w - 1), :]
+            r = src[:, yyc, np.clip(x0 + 1, 0, w - 1), :]
+            return l + (r - l) * dx[None, :, :, None]
+        v1 = row(y0)
+        ok2 = ((y0 + 1) >= 0) & ((y0 + 1) < h)
+        v2 = np.where(ok2[None, :, :, None], row(y0 + 1), v1)
+        v = v1 + (v2 - v1) * dy[None, :, :, None]
+        res = v.astype(np.int64).astype(np.uint8)  # (UINT8) v
+    else:
+        def row(yy):
+            yyc = np.clip(yy, 0, h - 1)
+            t = [src[:, yyc, np.clip(x0 + k, 0, w - 1), :] for k in (-1, 0, 1, 2)]
+            return _bicubic_w(t[0], t[1], t[2], t[3], dx[None, :, :, None])
+        # rows y0-1 .. y0+2; a row outside the image reuses the previous row's value (v1 always computed
+        # from clamp of y0-1? no: libImaging uses in = im->image8[YCLIP(im, y)] for first row only)
+        v1 = row(y0 - 1)
+        def ok(k):
+            yy = y0 + k
+            return ((yy >= 0) & (yy < h))[None, :, :, None]
+        v2 = np.where(ok(0), row(y0), v1)
+        v3 = np.where(ok(1), row(y0 + 1), v2)
+        v4 = np.where(ok(2), row(y0 + 2), v3)
+        v = _bicubic_w(v1, v2, v3, v4, dy[None, :, :, None])
+        res = np.where(v <= 0.0, 0, np.where(v >= 255.0, 255, np.trunc(np.clip(v, 0, 255)))).astype(np.uint8)
+    m = valid[None, :, :, None]
+    return np.where(m, res, out)
+
+
+def apply_shear(img: np.ndarray, sf: float) -> np.ndarray:
+    """transformation.py:212-226."""
+    n, h, w, c = img.shape
+    shift = int(math.ceil(sf * h))
+    return pil_transform(img, (1, sf, -shift if sf > 0 else 0, 0, 1, 0), (w + shift, h), "affine", "bicubic", 255)
+
+
+# =================================================================================================
+# A.6  cv2.GaussianBlur on uint8 (Q8 separable, REFLECT_101)
+# =================================================================================================
+
+
+def cv_gaussian_kernel_q8(ksize: int, sigma: float) -> np.ndarray:
+    """OpenCV getGaussianKernelBitExact for CV_8U: 64-bit kernel quantised to Q8 with error diffusion."""
+    n = ksize
+    x = np.arange(n, dtype=np.float64) - (n - 1) * 0.5
+    scale2x = -0.5 / (sigma * sigma)
+    g = np.exp(scale2x * x * x)
+    g = g / g.sum()
+    k = np.zeros(n, np.int64)
+    err = 0.0
+    for i in range(n // 2):
+        adj = g[i] * 256 + err
+        v = float(np.rint(adj))
+        err = adj - v
+        k[i] = k[n - 1 - i] = int(v)
+    k[n // 2] = 256 - (k.sum())
+    return k
+
+
+def _reflect101_idx(idx, n):
+    idx = np.asarray(idx)
+    if n == 1:
+        return np.zeros_like(idx)
+    period = 2 * n - 2
+    m = np.mod(idx, period)
+    return np.where(m >= n, period - m, m)
+
+
+def cv_gaussian_blur(img: np.ndarray, ksize: int, sigma: float) -> np.ndarray:
+    """cv2.GaussianBlur(img, (ksize,ksize), sigma) for uint8: fixed-point path (ufixedpoint16)."""
+    n, h, w, c = img.shape
+    k = cv_gaussian_kernel_q8(ksize, sigma)
+    r = ksize // 2
+    xi = _reflect101_idx(np.arange(-r, w + r), w)
+    yi = _reflect101_idx(np.arange(-r, h + r), h)
+    src = img.astype(np.int64)
+    hp = np.zeros((n, h, w, c), np.int64)
+    for i in range(ksize):
+        hp += k[i] * src[:, :, xi[i:i + w], :]
+    hp = np.minimum(hp, 65535)
+    vp = np.zeros((n, h, w, c), np.int64)
+    for i in range(ksize):
+        vp += k[i] * hp[:, yi[i:i + h], :, :]
+    return np.clip((vp + (1 << 15)) >> 16, 0, 255).astype(np.uint8)
+
+
+def apply_blur(img: np.ndarray, r: float) -> np.ndarray:
+    """transformation.py:228-257."""
+    if r == 0:
+        return img.copy()
+    ks = int(r * 6)
+    if ks % 2 == 0:
+        ks += 1
+    if ks < 3:
+        ks = 3
+    return cv_gaussian_blur(img, ks, r)
+
+
+# =================================================================================================
+# A.6b  Pillow ImageFilter.GaussianBlur (3 extended box passes per axis)
+# =================================================================================================
+
+
+def pil_gaussian_box_radius(radius: float) -> float:
+    """libImaging/BoxBlur.c _gaussian_blur_radius with n=3 passes, in C float/double mix."""
+    sigma2 = f32(radius * radius / 3)  # float sigma2 = radius*radius/passes
+    L = f32(math.sqrt(12.0 * float(sigma2) + 1.0))
+    l = f32(math.floor((float(L) - 1.0) / 2.0))
+    a = f32((2 * l + 1) * (l * (l + 1) - 3 * sigma2))
+    a = f32(a / f32(6 * (sigma2 - (l + 1) * (l + 1))))
+    return float(f32(l + a))
+
+
+def _box_pass_x(img: np.ndarray, R: float) -> np.ndarray:
+    """One ImagingLineBoxBlur8 pass along axis 2 (x) with edge replication."""
+    n, h, w, c = img.shape
+    ri = int(R)
+    ww = int(np.uint32(f32(1 << 24) / f32(f32(R) * 2 + 1)))
+    fw = ((1 << 24) - (ri * 2 + 1) * ww) // 2
+    src = img.astype(np.int64)
+    idx = np.arange(w)
+    acc = np.zeros((n, h, w, c), np.int64)
+    for i in range(-ri, ri + 1):
+        acc += src[:, :, np.clip(idx + i, 0, w - 1), :]
+    far = src[:, :, np.clip(idx - ri - 1, 0, w - 1), :] + src[:, :, np.clip(idx + ri + 1, 0, w - 1), :]
+    v = (acc * ww + far * fw) & 0xFFFFFFFF
+    v = ((v + (1 << 23)) & 0xFFFFFFFF) >> 24
+    return v.astype(np.uint8)
+
+
+def pil_gaussian_blur(img: np.ndarray, radius: float) -> np.ndarray:
+    """img.filter(ImageFilter.GaussianBlur(radius)) — pipenline/cifar_image_transformations.py:72-77."""
+    R = pil_gaussian_box_radius(radius)
+    out = img
+    for _ in range(3):
+        out = _box_pass_x(out, R)
+    out = out.transpose(0, 2, 1, 3)
+    for _ in range(3):
+        out = _box_pass_x(out, R)
+    return out.transpose(0, 2, 1, 3).copy()
+
+
+# =================================================================================================
+# A.6c  motion_blur (cv2.filter2D horizontal box) and A.14 histogram_equalization
+# =================================================================================================
+
+
+def motion_blur_box(img: np.ndarray, size: int) -> np.ndarray:
+    """cv2.filter2D(img, -1, K) with K = size x size, middle row 1/size
+    (pipenline/cifar_image_transformations.py:109-119): horizontal box, REFLECT_101, f32 accumulate,
+    round-half-even."""
+    n, h, w, c = img.shape
+    r = (size - 1) // 2
+    xi = _reflect101_idx(np.arange(-r, w + r), w)
+    kv = f32(np.float64(1.0) / size)
+    src = img.astype(f32)
+    acc = np.zeros((n, h, w, c), f32)
+    for i in range(size):
+        acc = (acc + (src[:, :, xi[i:i + w], :] * kv).astype(f32)).astype(f32)
+    return np.clip(np.rint(acc), 0, 255).astype(np.uint8)
+
+
+def _D14(x):
+    return (x + 8192) >> 14
+
+
+def histogram_equalization(img: np.ndarray) -> np.ndarray:
+    """RGB->YUV (OpenCV Q14), equalizeHist(Y), YUV->RGB — cifar_image_transformations.py:122-129."""
+    r = img[..., 0].astype(np.int64)
+    g = img[..., 1].astype(np.int64)
+    b = img[..., 2].astype(np.int64)
+    Y = _D14(4899 * r + 9617 * g + 1868 * b)
+    U = np.clip(_D14((b - Y) * 8061 + (128 << 14)), 0, 255)
+    V = np.clip(_D14((r - Y) * 14369 + (128 << 14)), 0, 255)
+    Y = np.clip(Y, 0, 255)
+    out = np.empty_like(img)
+    for i in range(img.shape[0]):
+        y = Y[i]
+        hist = np.bincount(y.ravel(), minlength=256)
+        total = y.size
+        nz = np.nonzero(hist)[0]
+        first = int(nz[0])
+        if hist[first] == total:
+            yeq = np.full_like(y, first)
+        else:
+            scale = f32(255.0) / f32(total - hist[first])
+            lut = np.zeros(256, np.int64)
+            s = 0
+            for j in range(first + 1, 256):
+                s += int(hist[j])
+                lut[j] = min(max(int(np.rint(f32(s) * scale)), 0), 255)
+            yeq = lut[y]
+        u = U[i] - 128
+        v = V[i] - 128
+        R = yeq + _D14(v * 18678)
+        G = yeq + _D14(v * (-9519) + u * (-6472))
+        Bc = yeq + _D14(u * 33292)
+        out[i, ..., 0] = np.clip(R, 0, 255)
+        out[i, ..., 1] = np.clip(G, 0, 255)
+        out[i, ..., 2] = np.clip(Bc, 0, 255)
+    return out
+
+
+# =================================================================================================
+# A.8  noise (draws injected)
+# =================================================================================================
+
+
+def gaussian_noise_f32(img: np.ndarray, noise_f32: np.ndarray) -> np.ndarray:
+    """transformation.apply_gaussian_noise (:272-281): noise already scaled (std*255) and cast to f32."""
+    v = (img.astype(f32) + noise_f32.astype(f32)).astype(f32)
+    return np.clip(v, 0, 255).astype(np.uint8)
+
+
+def gaussian_noise_f64(img: np.ndarray, noise_f64: np.ndarray) -> np.ndarray:
+    """TransformationPool.gaussian_noise (:39-48): f32 image + f64 noise (already scaled) summed in f64."""
+    v = img.astype(f32).astype(np.float64) + noise_f64
+    return np.clip(v, 0, 255).astype(np.uint8)
+
+
+def impulse_noise(img: np.ndarray, mask: np.ndarray, prob: float) -> np.ndarray:
+    """TransformationPool.impulse_noise (:50-59): mask (n,h,w) uniform f64 shared by channels."""
+    out = img.copy()
+    out[mask < prob / 2] = 0
+    out[mask > 1 - prob / 2] = 255
+    return out
+
+
+def shot_noise_scaled(img: np.ndarray, lam: float) -> np.ndarray:
+    """The Poisson rate array the reference hands to np.random.poisson (f32)."""
+    return (img.astype(f32) / f32(255.0) * f32(lam)).astype(f32)
+
+
+def shot_noise(img: np.ndarray, counts: np.ndarray, lam: float) -> np.ndarray:
+    """TransformationPool.shot_noise (:61-70) with the Poisson draws injected: k/lam*255.0 in f64."""
+    v = counts.astype(np.float64) / lam * 255.0
+    return np.clip(v, 0, 255).astype(np.uint8)

@@ -1,0 +1,140 @@
+"""GPU parity: enhance / resample / stencil / noise kernels vs the numpy oracle (bit-exact)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import np_ops as O
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [(32, 32), (224, 224), (37, 53), (64, 48)]
+
+
+def _imgs(seed, n, h, w, c=3, skew=False):
+    x = np.random.default_rng(seed).integers(0, 256, (n, h, w, c), dtype=np.uint8)
+    if skew:
+        x = (x // 3 + 40).astype(np.uint8)
+    return x
+
+
+def _B():
+    from imagetransformations_b200 import batch as B
+    return B
+
+
+def _cu(x):
+    return torch.from_numpy(x).cuda()
+
+
+@pytest.mark.parametrize("hw", SIZES)
+def test_enhance(cuda, hw):
+    B = _B()
+    for skew in (False, True):
+        x = _imgs(21, 7, *hw, skew=skew)
+        xd = _cu(x)
+        for f in [0.8, 0.83, 1.0, 1.17, 1.2, 0.5, 2.0, 0.0]:
+            assert np.array_equal(B.enhance_contrast(xd, f).cpu().numpy(), O.enhance_contrast(x, f)), ("contrast", f)
+            assert np.array_equal(B.enhance_color(xd, f).cpu().numpy(), O.enhance_color(x, f)), ("color", f)
+            assert np.array_equal(B.enhance_sharpness(xd, f).cpu().numpy(), O.enhance_sharpness(x, f)), ("sharp", f)
+        assert np.array_equal(B.equalize(xd).cpu().numpy(), O.equalize(x))
+        assert np.array_equal(B.histogram_equalization(xd).cpu().numpy(), O.histogram_equalization(x))
+
+
+def test_enhance_per_image_and_degenerate(cuda):
+    B = _B()
+    x = _imgs(22, 41, 32, 32)
+    x[0] = 77            # constant image: equalize identity, histeq constant
+    x[1, :, :, 1] = 3    # one constant channel
+    x[2] = 0
+    xd = _cu(x)
+    f = np.random.default_rng(23).uniform(0.8, 1.2, 41)
+    assert np.array_equal(B.enhance_contrast(xd, f).cpu().numpy(), O.enhance_contrast(x, f))
+    f = np.random.default_rng(24).uniform(0.5, 1.5, 41)
+    assert np.array_equal(B.enhance(xd, 0, f).cpu().numpy(), O.enhance_brightness(x, f))
+    assert np.array_equal(B.equalize(xd).cpu().numpy(), O.equalize(x))
+    assert np.array_equal(B.histogram_equalization(xd).cpu().numpy(), O.histogram_equalization(x))
+
+
+@pytest.mark.parametrize("hw", SIZES)
+def test_apply_scale(cuda, hw):
+    B = _B()
+    x = _imgs(25, 5, *hw)
+    xd = _cu(x)
+    for s in [0.9, 1.0, 1.1, 1.2000000000000002, 1.3, 1.05]:
+        assert np.array_equal(B.apply_scale(xd, s).cpu().numpy(), O.apply_scale(x, s)), s
+
+
+def test_crop_resize_and_multiscale(cuda):
+    B = _B()
+    x = _imgs(26, 50, 32, 32)
+    rng = np.random.default_rng(27)
+    cx, cy = rng.integers(0, 9, 50), rng.integers(0, 9, 50)
+    assert np.array_equal(B.crop_resize(_cu(x), cx, cy, 24).cpu().numpy(), O.crop_resize(x, cx, cy, 24))
+    for sz in (36, 40):
+        assert np.array_equal(B.resize_center_crop(_cu(x), sz, 32).cpu().numpy(), O.resize_center_crop(x, sz, 32))
+    # pixelate-style BOX down/up
+    from imagetransformations_b200 import _lib as L
+    d = B.resample(_cu(x), (30, 30), L.FILTER_BOX)
+    u = B.resample(d, (32, 32), L.FILTER_BOX)
+    ref = O.pil_resize(O.pil_resize(x, (30, 30), O.BOX), (32, 32), O.BOX)
+    assert np.array_equal(u.cpu().numpy(), ref)
+
+
+@pytest.mark.parametrize("hw", SIZES)
+def test_blurs(cuda, hw):
+    B = _B()
+    x = _imgs(28, 4, *hw)
+    xd = _cu(x)
+    for r in [0.0, 0.5, 1.0, 1.5, 2.0, 2.5, 3.0, 3.5, 4.0, 4.5, 5.0]:
+        assert np.array_equal(B.apply_blur(xd, r).cpu().numpy(), O.apply_blur(x, r)), r
+    for rad in [3, 4, 6, 8, 10, 0.5, 1.7]:
+        assert np.array_equal(B.pil_gaussian_blur(xd, rad).cpu().numpy(), O.pil_gaussian_blur(x, rad)), rad
+    for size in [5, 7, 9, 11]:
+        assert np.array_equal(B.box_filter_h(xd, size).cpu().numpy(), O.motion_blur_box(x, size)), size
+
+
+def test_noise_injected(cuda):
+    B = _B()
+    from imagetransformations_b200 import _lib as L
+    x = _imgs(29, 16, 32, 32)
+    xd = _cu(x)
+    rs = np.random.RandomState(30)
+    nz32 = rs.normal(0, 0.05 * 255, x.shape).astype(np.float32)
+    assert np.array_equal(B.noise_injected(xd, L.NOISE_GAUSS_F32, nz32).cpu().numpy(), O.gaussian_noise_f32(x, nz32))
+    nz64 = rs.normal(0, 0.18 * 255, x.shape)
+    assert np.array_equal(B.noise_injected(xd, L.NOISE_GAUSS_F64, nz64).cpu().numpy(), O.gaussian_noise_f64(x, nz64))
+    mask = rs.random_sample(x.shape[:3])
+    assert np.array_equal(B.noise_injected(xd, L.NOISE_IMPULSE, mask, 0.09).cpu().numpy(), O.impulse_noise(x, mask, 0.09))
+    for lam in (60, 12, 3):
+        k = rs.poisson(O.shot_noise_scaled(x, lam))
+        assert np.array_equal(B.noise_injected(xd, L.NOISE_SHOT, k, lam).cpu().numpy(), O.shot_noise(x, k, lam))
+
+
+def test_noise_philox_statistics(cuda):
+    """Throughput-mode RNG: mean/variance of the induced noise match the injected-draw distribution."""
+    B = _B()
+    from imagetransformations_b200 import _lib as L
+    n = 2000
+    x = np.full((n, 32, 32, 3), 128, np.uint8)
+    xd = _cu(x)
+    out = B.noise_philox(xd, L.NOISE_GAUSS_F32, 0.05 * 255, seed=1).cpu().numpy().astype(np.float64)
+    d = out - 128 + 0.5   # truncation bias
+    assert abs(d.mean()) < 0.05 and abs(d.std() - 0.05 * 255) < 0.1
+    out2 = B.noise_philox(xd, L.NOISE_GAUSS_F32, 0.05 * 255, seed=2).cpu().numpy()
+    assert (out2 != out).mean() > 0.5           # different seed, different draws
+    out3 = B.noise_philox(xd, L.NOISE_GAUSS_F32, 0.05 * 255, seed=1).cpu().numpy()
+    assert np.array_equal(out3, out)            # same seed reproducible
+    imp = B.noise_philox(xd, L.NOISE_IMPULSE, 0.09, seed=3).cpu().numpy()
+    frac0 = (imp[..., 0] == 0).mean()
+    frac255 = (imp[..., 0] == 255).mean()
+    assert abs(frac0 - 0.045) < 0.003 and abs(frac255 - 0.045) < 0.003
+    assert np.array_equal(imp[..., 0] == 0, imp[..., 1] == 0)   # mask shared by channels
+    for lam, val in ((60, 128), (12, 200), (3, 90), (500, 255)):
+        xs = _cu(np.full((500, 32, 32, 3), val, np.uint8))
+        o = B.noise_philox(xs, L.NOISE_SHOT, lam, seed=4).cpu().numpy().astype(np.float64)
+        rate = np.float32(val) / np.float32(255) * np.float32(lam)
+        # k/lam*255 truncated and clipped: compare against numpy draws pushed through the same map
+        k = np.random.RandomState(5).poisson(float(rate), o.size)
+        ref = np.clip(k / lam * 255.0, 0, 255).astype(np.uint8).astype(np.float64)
+        assert abs(o.mean() - ref.mean()) < 0.02 * ref.std() + 0.05, (lam, o.mean(), ref.mean())
+        assert abs(o.std() - ref.std()) < 0.02 * ref.std() + 0.05, (lam, o.std(), ref.std())
