@@ -35,6 +35,9 @@ TOU8_DENORMALIZE, TOU8_CLAMP01 = 1, 2
 CLAMP_NONE, CLAMP_SCALAR, CLAMP_PER_CHANNEL = range(3)
 FC_GAUSSIAN_NOISE, FC_BRIGHTNESS, FC_CONTRAST, FC_ADD_NOISE = range(4)
 MAX_EPS = 8
+(VIEW_IDENTITY, VIEW_FLIP, VIEW_CROP_RESIZE, VIEW_BRIGHTNESS, VIEW_CONTRAST, VIEW_CROP_REFLECT,
+ VIEW_FLIP_CROP_REFLECT, VIEW_RESIZE_CENTER_CROP) = range(8)
+AUG_NONE, AUG_GEOM, AUG_POSTERIZE, AUG_SOLARIZE, AUG_EQUALIZE = range(5)
 
 _vp = C.c_void_p
 _i64 = C.c_int64
@@ -58,10 +61,15 @@ _PROTOS = {
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _vp],
     "imgtx_pil_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_box_filter_h_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp],
+    "imgtx_pil_transform_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _vp, _vp, _vp],
+    "imgtx_perspective_tensor_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _f, _vp],
+    "imgtx_gaussian_blur_f32": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_noise_injected_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, C.c_double, _vp],
     "imgtx_noise_philox_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_uint64, _vp],
     "imgtx_to_tensor_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_to_uint8_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _int, _vp],
+    "imgtx_augmix_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],
+    "imgtx_views_f32": [_vp, _int, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp, _vp],
     "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],

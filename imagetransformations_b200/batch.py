@@ -509,3 +509,75 @@ def float_corrupt(x, mode: int, a: float = 0.0, b: float = 0.0, noise=None, clam
                                              out.data_ptr(), x.numel(), mode, float(a), float(b), int(clamp),
                                              _stream()))
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# interpolating warps
+# ------------------------------------------------------------------------------------------------
+def pil_transform(x: torch.Tensor, coeffs, out_hw=None, perspective: bool = False, bicubic: bool = False, fill=0,
+                  out=None) -> torch.Tensor:
+    """PIL img.transform(size, AFFINE|PERSPECTIVE, coeffs, resample=BILINEAR|BICUBIC, fillcolor=fill).
+    coeffs: (6|8,) uniform or (n, 6|8) per image (doubles)."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    oh, ow = out_hw if out_hw is not None else (h, w)
+    out = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device) if out is None else out
+    k = 8 if perspective else 6
+    co = np.asarray(coeffs, dtype=np.float64)
+    host = dev = None
+    if co.ndim == 1:
+        host = np.zeros(8, np.float64)
+        host[:k] = co[:k]
+    else:
+        full = np.zeros((n, 8), np.float64)
+        full[:, :k] = co.reshape(n, -1)[:, :k]
+        dev = torch.from_numpy(full).to(x.device)
+    fv = [int(v) for v in (fill if isinstance(fill, (tuple, list)) else [fill] * c)]
+    fill_arr = (C.c_uint8 * 4)(*((fv + [0] * 4)[:4]))
+    L.check(L.load().imgtx_pil_transform_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, oh, ow, int(perspective),
+                                            int(bicubic), host.ctypes.data if host is not None else None,
+                                            dev.data_ptr() if dev is not None else None,
+                                            C.cast(fill_arr, C.c_void_p), _stream()))
+    return out
+
+
+def apply_shear(x: torch.Tensor, sf: float, out=None) -> torch.Tensor:
+    """reference apply_shear: AFFINE (1, sf, -shift, 0, 1, 0), BICUBIC, white fill, width + ceil(sf*h)."""
+    n, h, w, c = x.shape
+    shift = int(math.ceil(sf * h))
+    return pil_transform(x, (1, sf, -shift if sf > 0 else 0, 0, 1, 0), out_hw=(h, w + shift), bicubic=True,
+                         fill=255, out=out)
+
+
+def perspective_coeffs(startpoints, endpoints) -> np.ndarray:
+    """torchvision _get_perspective_coeffs (least squares in f64): output pixel -> input pixel."""
+    a = np.zeros((8, 8), np.float64)
+    for i, (p1, p2) in enumerate(zip(endpoints, startpoints)):
+        a[2 * i] = [p1[0], p1[1], 1, 0, 0, 0, -p2[0] * p1[0], -p2[0] * p1[1]]
+        a[2 * i + 1] = [0, 0, 0, p1[0], p1[1], 1, -p2[1] * p1[0], -p2[1] * p1[1]]
+    b = np.asarray(startpoints, np.float64).reshape(8)
+    return np.linalg.lstsq(a, b, rcond=None)[0]
+
+
+def perspective_tensor(x: torch.Tensor, coeffs, fill: float = 0.0, out=None) -> torch.Tensor:
+    """ToTensor -> TF.perspective(tensor, BILINEAR, fill) -> ToPILImage on a u8 batch; coeffs (n,8) or (8,)."""
+    x = _check_u8(x)
+    n, h, w, c = x.shape
+    out = torch.empty_like(x) if out is None else out
+    co = np.broadcast_to(np.asarray(coeffs, np.float64).astype(np.float32).reshape(-1, 8), (n, 8))
+    cd = torch.from_numpy(np.ascontiguousarray(co)).to(x.device)
+    L.check(L.load().imgtx_perspective_tensor_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, cd.data_ptr(), float(fill),
+                                                 _stream()))
+    return out
+
+
+def gaussian_blur_f32(t: torch.Tensor, kernel_size: int = 3, sigma: float = None) -> torch.Tensor:
+    """TF.gaussian_blur(t, kernel_size[, sigma]) on f32 (..., h, w)."""
+    t = _check_f32(t)
+    if sigma is None:
+        sigma = 0.3 * ((kernel_size - 1) * 0.5 - 1) + 0.8
+    h, w = t.shape[-2:]
+    out = torch.empty_like(t)
+    L.check(L.load().imgtx_gaussian_blur_f32(t.data_ptr(), out.data_ptr(), t.numel() // (h * w), h, w, int(kernel_size),
+                                             float(sigma), _stream()))
+    return out

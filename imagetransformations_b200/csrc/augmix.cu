@@ -1,0 +1,246 @@
+// Fused AugMix (fall_2025/AugMix.py:45-62): one pass per image.
+//
+//   q   = TF.to_pil_image(x)            (trunc(x*255) mod 256, kept in shared memory as HWC uint8)
+//   u_i = op_{i,d-1}( ... op_{i,0}(q))  for each of `width` chains, WITHOUT materialising intermediates:
+//         NEAREST geometric ops (rotate / shear / translate: Pillow 16.16 fixed-point affine gathers) compose as
+//         index maps applied stage by stage (each stage rounds separately, exactly like Pillow), point ops
+//         (posterize / solarize / equalize) compose as per-channel 256-entry LUTs; a pixel that leaves the image at
+//         geometric stage k takes the fill value 0 pushed through the point ops after k.
+//         `equalize` needs the histogram of its input image: one extra sweep over the shared-memory image evaluating
+//         the chain prefix.
+//   mix = sum_i f32(w_i) * (u_i / 255)   sequential f32
+//   out = f32(1-m) * x + f32(m) * mix
+//
+// HBM traffic per image: x read once (12*h*w B; the second read in the output phase hits L2) + out written once.
+// Roofline: HBM, 24 B per pixel.
+#include "common.cuh"
+#include "lut.cuh"
+#include <algorithm>
+
+namespace imgtx {
+
+struct AugOp {  // == imgtx_augmix_op_t
+  int32_t kind;
+  int32_t a[6];
+  int32_t param;
+};
+
+__device__ __forceinline__ uint8_t augmix_point(const AugOp& op, int v) {
+  if (op.kind == IMGTX_AUG_POSTERIZE) return (uint8_t)(v & op.param);
+  return (uint8_t)(v < op.param ? v : 255 - v);  // SOLARIZE
+}
+
+// Walk the geometric stages [0, upto) backwards from output pixel (x, y).  Returns the source byte offset, or -1
+// with fillk = the stage whose source fell outside the image.
+__device__ __forceinline__ int trace_back(const AugOp* ops, int upto, int x, int y, int w, int h, int& fillk) {
+  for (int k = upto - 1; k >= 0; --k) {
+    if (ops[k].kind != IMGTX_AUG_GEOM) continue;
+    const int nx = (ops[k].a[2] + y * ops[k].a[1] + x * ops[k].a[0]) >> 16;
+    const int ny = (ops[k].a[5] + y * ops[k].a[4] + x * ops[k].a[3]) >> 16;
+    if (nx < 0 || nx >= w || ny < 0 || ny >= h) {
+      fillk = k;
+      return -1;
+    }
+    x = nx;
+    y = ny;
+  }
+  return (y * w + x) * 3;
+}
+
+// comp[c][v] = point ops of stages [0, upto) applied in order to v; fills[k][c] = 0 pushed through the point ops of
+// stages (k, upto).  stage_lut holds one [3][256] table per point-op stage.
+__device__ void build_composed(const AugOp* ops, const uint8_t* stage_lut, int upto, uint8_t* comp, uint8_t* fills) {
+  for (int t = threadIdx.x; t < 768; t += blockDim.x) {
+    const int c = t >> 8;
+    int v = t & 255;
+    for (int k = 0; k < upto; ++k)
+      if (ops[k].kind >= IMGTX_AUG_POSTERIZE) v = stage_lut[k * 768 + c * 256 + v];
+    comp[t] = (uint8_t)v;
+  }
+  for (int t = threadIdx.x; t < upto * 3; t += blockDim.x) {
+    const int k = t / 3, c = t - k * 3;
+    int v = 0;
+    for (int kk = k + 1; kk < upto; ++kk)
+      if (ops[kk].kind >= IMGTX_AUG_POSTERIZE) v = stage_lut[kk * 768 + c * 256 + v];
+    fills[k * 4 + c] = (uint8_t)v;
+  }
+}
+
+__global__ void augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, int h, int w, int width,
+                              int depth, const AugOp* __restrict__ ops_g, const float* __restrict__ wts_g) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int hw = h * w;
+  const int nstage = width * depth;
+  uint8_t* q = smem;                                                   // hw*3 (+pad)
+  uint8_t* stage_lut = q + ((hw * 3 + 4 + 15) & ~15);                  // nstage * 768
+  uint8_t* comp = stage_lut + (size_t)nstage * 768;                    // width * 768
+  uint8_t* fills = comp + (size_t)width * 768;                         // nstage * 4
+  uint32_t* hist = reinterpret_cast<uint32_t*>(fills + ((nstage * 4 + 15) & ~15));  // 768
+  float* T = reinterpret_cast<float*>(hist + 768);                     // 256: u/255
+  AugOp* ops = reinterpret_cast<AugOp*>(T + 256);                      // nstage
+  float* wts = reinterpret_cast<float*>(ops + nstage);                 // width + 2
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+
+  for (int i = tid; i < 256; i += nt) T[i] = __fdiv_rn((float)i, 255.0f);
+
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    const float* xi = x + img * 3 * (int64_t)hw;
+    float* oi = out + img * 3 * (int64_t)hw;
+    __syncthreads();  // previous image fully written before its tables are overwritten
+    {
+      const int32_t* src = reinterpret_cast<const int32_t*>(ops_g + img * nstage);
+      int32_t* dst = reinterpret_cast<int32_t*>(ops);
+      for (int i = tid; i < nstage * 8; i += nt) dst[i] = src[i];
+      for (int i = tid; i < width + 2; i += nt) wts[i] = wts_g[img * (width + 2) + i];
+    }
+    // ---- phase A: quantise to HWC uint8 in shared memory ----
+    if ((hw & 3) == 0) {
+      uint32_t* q32 = reinterpret_cast<uint32_t*>(q);
+      for (int p4 = tid; p4 < (hw >> 2); p4 += nt) {
+        uint32_t v[3][4];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const float4 f = *reinterpret_cast<const float4*>(xi + (int64_t)c * hw + p4 * 4);
+          v[c][0] = (uint32_t)(__float2int_rz(__fmul_rn(f.x, 255.0f)) & 255);
+          v[c][1] = (uint32_t)(__float2int_rz(__fmul_rn(f.y, 255.0f)) & 255);
+          v[c][2] = (uint32_t)(__float2int_rz(__fmul_rn(f.z, 255.0f)) & 255);
+          v[c][3] = (uint32_t)(__float2int_rz(__fmul_rn(f.w, 255.0f)) & 255);
+        }
+        q32[p4 * 3 + 0] = v[0][0] | (v[1][0] << 8) | (v[2][0] << 16) | (v[0][1] << 24);
+        q32[p4 * 3 + 1] = v[1][1] | (v[2][1] << 8) | (v[0][2] << 16) | (v[1][2] << 24);
+        q32[p4 * 3 + 2] = v[2][2] | (v[0][3] << 8) | (v[1][3] << 16) | (v[2][3] << 24);
+      }
+    } else {
+      for (int i = tid; i < hw * 3; i += nt) {
+        const int c = i / hw, p = i - c * hw;
+        q[p * 3 + c] = (uint8_t)(__float2int_rz(__fmul_rn(xi[i], 255.0f)) & 255);
+      }
+    }
+    __syncthreads();
+
+    // ---- phase B: per-chain tables ----
+    for (int ci = 0; ci < width; ++ci) {
+      const AugOp* cops = ops + ci * depth;
+      uint8_t* clut = stage_lut + (size_t)ci * depth * 768;
+      uint8_t* ccomp = comp + ci * 768;
+      uint8_t* cfill = fills + ci * depth * 4;
+      for (int j = 0; j < depth; ++j) {
+        const int kind = cops[j].kind;
+        if (kind == IMGTX_AUG_POSTERIZE || kind == IMGTX_AUG_SOLARIZE) {
+          for (int t = tid; t < 768; t += nt) clut[j * 768 + t] = augmix_point(cops[j], t & 255);
+          __syncthreads();
+        } else if (kind == IMGTX_AUG_EQUALIZE) {
+          build_composed(cops, clut, j, ccomp, cfill);
+          for (int t = tid; t < 768; t += nt) hist[t] = 0u;
+          __syncthreads();
+          bool has_geom = false;
+          for (int k = 0; k < j; ++k) has_geom |= (cops[k].kind == IMGTX_AUG_GEOM);
+          if (!has_geom) {
+            for (int i = tid; i < hw * 3; i += nt) {
+              const int c = i % 3;
+              atomicAdd(&hist[c * 256 + ccomp[c * 256 + q[i]]], 1u);
+            }
+          } else {
+            for (int p = tid; p < hw; p += nt) {
+              const int y = p / w, xx = p - y * w;
+              int fk = 0;
+              const int o = trace_back(cops, j, xx, y, w, h, fk);
+#pragma unroll
+              for (int c = 0; c < 3; ++c) {
+                const int v = o >= 0 ? ccomp[c * 256 + q[o + c]] : cfill[fk * 4 + c];
+                atomicAdd(&hist[c * 256 + v], 1u);
+              }
+            }
+          }
+          __syncthreads();
+          if (warp < 3) equalize_lut_warp(hist + warp * 256, clut + j * 768 + warp * 256, lane);
+          __syncthreads();
+        }
+      }
+      build_composed(cops, clut, depth, ccomp, cfill);
+    }
+    __syncthreads();
+
+    // ---- phase C: mix and write ----
+    const float m = wts[width], one_m = wts[width + 1];
+    if ((hw & 3) == 0 && (w & 3) == 0) {
+      for (int p4 = tid; p4 < (hw >> 2); p4 += nt) {
+        const int p0 = p4 * 4;
+        const int y = p0 / w, x0 = p0 - y * w;
+        float mix[3][4];
+#pragma unroll
+        for (int c = 0; c < 3; ++c)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mix[c][k] = 0.0f;
+        for (int ci = 0; ci < width; ++ci) {
+          const AugOp* cops = ops + ci * depth;
+          const uint8_t* ccomp = comp + ci * 768;
+          const uint8_t* cfill = fills + ci * depth * 4;
+          const float wi = wts[ci];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            int fk = 0;
+            const int o = trace_back(cops, depth, x0 + k, y, w, h, fk);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const int u = o >= 0 ? ccomp[c * 256 + q[o + c]] : cfill[fk * 4 + c];
+              mix[c][k] = __fadd_rn(mix[c][k], __fmul_rn(wi, T[u]));
+            }
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const float4 f = *reinterpret_cast<const float4*>(xi + (int64_t)c * hw + p0);
+          float4 r;
+          r.x = __fadd_rn(__fmul_rn(one_m, f.x), __fmul_rn(m, mix[c][0]));
+          r.y = __fadd_rn(__fmul_rn(one_m, f.y), __fmul_rn(m, mix[c][1]));
+          r.z = __fadd_rn(__fmul_rn(one_m, f.z), __fmul_rn(m, mix[c][2]));
+          r.w = __fadd_rn(__fmul_rn(one_m, f.w), __fmul_rn(m, mix[c][3]));
+          stg_stream_f4(reinterpret_cast<float4*>(oi + (int64_t)c * hw + p0), r);
+        }
+      }
+    } else {
+      for (int p = tid; p < hw; p += nt) {
+        const int y = p / w, xx = p - y * w;
+        float mix[3] = {0.0f, 0.0f, 0.0f};
+        for (int ci = 0; ci < width; ++ci) {
+          const AugOp* cops = ops + ci * depth;
+          int fk = 0;
+          const int o = trace_back(cops, depth, xx, y, w, h, fk);
+          for (int c = 0; c < 3; ++c) {
+            const int u = o >= 0 ? comp[ci * 768 + c * 256 + q[o + c]] : fills[(ci * depth + fk) * 4 + c];
+            mix[c] = __fadd_rn(mix[c], __fmul_rn(wts[ci], T[u]));
+          }
+        }
+        for (int c = 0; c < 3; ++c)
+          oi[(int64_t)c * hw + p] = __fadd_rn(__fmul_rn(one_m, xi[(int64_t)c * hw + p]), __fmul_rn(m, mix[c]));
+      }
+    }
+  }
+}
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_augmix_f32(const float* x, float* out, int64_t n, int h, int w, int width, int depth,
+                                const imgtx_augmix_op_t* ops_dev, const float* weights_dev, imgtx_stream_t stream) {
+  static_assert(sizeof(imgtx_augmix_op_t) == sizeof(AugOp) && sizeof(AugOp) == 32, "op record layout");
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && n >= 0, "bad image shape");
+  IMGTX_CHECK_ARG(width >= 1 && width <= 16 && depth >= 1 && depth <= 16, "width/depth must be in [1,16]");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && out && ops_dev && weights_dev, "null pointer");
+  const int hw = h * w, nstage = width * depth;
+  IMGTX_CHECK_ARG(((int64_t)hw % 4 != 0) || (aligned16(x) && aligned16(out)), "f32 tensors must be 16-byte aligned");
+  size_t smem = ((size_t)hw * 3 + 4 + 15) / 16 * 16 + (size_t)nstage * 768 + (size_t)width * 768 +
+                ((size_t)nstage * 4 + 15) / 16 * 16 + 768 * 4 + 256 * 4 + (size_t)nstage * 32 + (size_t)(width + 2) * 4 + 16;
+  IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused AugMix", h, w);
+  const int threads = hw >= 128 * 128 ? 1024 : 256;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(augmix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2048 / threads, (size_t)max_smem_optin() / (smem + 1024)));
+  int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * per_sm);
+  augmix_kernel<<<(unsigned)grid, threads, smem, (cudaStream_t)stream>>>(x, out, n, h, w, width, depth,
+                                                                        reinterpret_cast<const AugOp*>(ops_dev), weights_dev);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}

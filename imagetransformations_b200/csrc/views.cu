@@ -1,0 +1,212 @@
+// Fused test-time-augmentation view expansion: one image in, V normalised f32 views out, one pass.
+//
+//   reference: fall_2025/tta_initial_claudeFixed.py:37-78,218-230 (16 views: tensor_to_pil, then 1 flip, 5 crop(24)+
+//              BICUBIC resize, 5 ImageEnhance.Brightness, 5 ImageEnhance.Contrast, each followed by pil_to_tensor),
+//              fall_2025/TTA_transforms.py:69-138 (three strategies of 4 views: identity, RandomHorizontalFlip(p=1),
+//              RandomCrop(32, 4, 'reflect'), flip+crop, Resize(36|40)+CenterCrop(32), ColorJitter brightness /
+//              contrast; all end in ToTensor+Normalize).
+//
+// The image is read from HBM once (uint8 HWC, or the normalised f32 CHW tensor that is first quantised exactly like
+// tensor_to_pil), lives in shared memory, and every view is produced from it: index maps for flips / reflect crops,
+// Pillow's two-pass Q22 resample for the crop-resize views (uint8 intermediate in shared memory), Pillow's f32 blend
+// for the enhancers, and a 768-entry table for ToTensor+Normalize ((u/255 - mean)/std with IEEE division, evaluated
+// once per CTA).  Roofline: HBM writes — V * 12 * h * w bytes out per image versus 3 (or 12) * h * w in.
+#include "common.cuh"
+#include "lut.cuh"
+#include <algorithm>
+#include <string.h>
+
+namespace imgtx {
+
+constexpr int kMaxViews = 32;
+constexpr int kViewThreads = 256;
+
+struct ViewSet {
+  imgtx_view_t v[kMaxViews];
+  int n_views;
+  int table_off[kMaxViews + 1];  // word offsets of the resample tables inside the table blob
+  float in_mean[4], in_std[4], out_mean[4], out_std[4];
+  int in_is_f32, any_contrast, tmp_rows;
+};
+
+__device__ __forceinline__ int pil_luma_v(int r, int g, int b) { return (19595 * r + 38470 * g + 7471 * b + 0x8000) >> 16; }
+
+__global__ void __launch_bounds__(kViewThreads)
+views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, int h, int w, ViewSet vs,
+             const float* __restrict__ params, const int32_t* __restrict__ tables_g, int table_words) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int hw = h * w;
+  const int tid = threadIdx.x;
+  const int V = vs.n_views;
+  float* NT = reinterpret_cast<float*>(smem);                        // [3][256] normalise table
+  int32_t* tables = reinterpret_cast<int32_t*>(NT + 768);            // table_words
+  uint8_t* u = reinterpret_cast<uint8_t*>(tables + ((table_words + 3) & ~3));  // hw*3 (+4)
+  uint8_t* tmp = u + ((hw * 3 + 4 + 15) & ~15);                      // tmp_rows * w * 3 (+4)
+  __shared__ unsigned long long s_luma;
+  __shared__ float s_par[kMaxViews * 2];
+
+  for (int i = tid; i < 768; i += kViewThreads) {
+    const int c = i >> 8;
+    NT[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)(i & 255), 255.0f), vs.out_mean[c]), vs.out_std[c]);
+  }
+  for (int i = tid; i < table_words; i += kViewThreads) tables[i] = tables_g[i];
+
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    __syncthreads();
+    if (tid == 0) s_luma = 0ull;
+    for (int i = tid; i < V * 2; i += kViewThreads) s_par[i] = params[img * V * 2 + i];
+    // ---- load / quantise ----
+    if (vs.in_is_f32) {
+      const float* xi = reinterpret_cast<const float*>(in) + img * 3 * (int64_t)hw;
+      for (int i = tid; i < hw * 3; i += kViewThreads) {
+        const int c = i / hw, p = i - c * hw;
+        float v = __fadd_rn(__fmul_rn(xi[i], vs.in_std[c]), vs.in_mean[c]);
+        v = fminf(fmaxf(v, 0.0f), 1.0f);
+        u[p * 3 + c] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+      }
+    } else {
+      const uint8_t* xi = reinterpret_cast<const uint8_t*>(in) + img * 3 * (int64_t)hw;
+      if (((hw * 3) & 15) == 0) {
+        const uint4* s4 = reinterpret_cast<const uint4*>(xi);
+        uint4* d4 = reinterpret_cast<uint4*>(u);
+        for (int i = tid; i < (hw * 3) >> 4; i += kViewThreads) d4[i] = ldg_stream(s4 + i);
+      } else {
+        for (int i = tid; i < hw * 3; i += kViewThreads) u[i] = xi[i];
+      }
+    }
+    __syncthreads();
+    int degenerate = 0;
+    if (vs.any_contrast) {
+      unsigned acc = 0;
+      for (int p = tid; p < hw; p += kViewThreads) acc += pil_luma_v(u[p * 3], u[p * 3 + 1], u[p * 3 + 2]);
+      for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if ((tid & 31) == 0) atomicAdd(&s_luma, (unsigned long long)acc);
+      __syncthreads();
+      degenerate = (int)((double)s_luma / (double)hw + 0.5);
+    }
+
+    for (int vi = 0; vi < V; ++vi) {
+      const imgtx_view_t vw = vs.v[vi];
+      float* ov = out + ((img * V + vi) * 3) * (int64_t)hw;
+      const float p0 = s_par[vi * 2], p1 = s_par[vi * 2 + 1];
+      switch (vw.kind) {
+        case IMGTX_VIEW_IDENTITY:
+        case IMGTX_VIEW_FLIP:
+        case IMGTX_VIEW_CROP_REFLECT:
+        case IMGTX_VIEW_FLIP_CROP_REFLECT:
+        case IMGTX_VIEW_BRIGHTNESS:
+        case IMGTX_VIEW_CONTRAST: {
+          const bool flip = vw.kind == IMGTX_VIEW_FLIP || vw.kind == IMGTX_VIEW_FLIP_CROP_REFLECT;
+          const bool crop = vw.kind == IMGTX_VIEW_CROP_REFLECT || vw.kind == IMGTX_VIEW_FLIP_CROP_REFLECT;
+          const bool blend = vw.kind == IMGTX_VIEW_BRIGHTNESS || vw.kind == IMGTX_VIEW_CONTRAST;
+          const int d = vw.kind == IMGTX_VIEW_CONTRAST ? degenerate : 0;
+          const int ci = (int)p0 - vw.i0, cj = (int)p1 - vw.i0;  // crop offsets minus padding (row, col)
+          for (int i = tid; i < hw * 3; i += kViewThreads) {
+            const int c = i / hw, p = i - c * hw;
+            int y = p / w, x = p - y * w;
+            if (crop) {
+              y = reflect101(y + ci, h);
+              x = reflect101(x + cj, w);
+            }
+            if (flip) x = w - 1 - x;
+            int val = u[(y * w + x) * 3 + c];
+            if (blend) val = pil_blend(d, val, p0);
+            ov[i] = NT[c * 256 + val];
+          }
+          break;
+        }
+        case IMGTX_VIEW_CROP_RESIZE:
+        case IMGTX_VIEW_RESIZE_CENTER_CROP: {
+          // source box (ox, oy, bw, bh) -> resized (rw, rh) -> window (left, top, w, h) of the resized image
+          const bool cr = vw.kind == IMGTX_VIEW_CROP_RESIZE;
+          const int ox = cr ? (int)p0 : 0, oy = cr ? (int)p1 : 0;
+          const int bh = cr ? vw.i0 : h;
+          const int left = cr ? 0 : vw.i0, top = cr ? 0 : vw.i1;
+          const int32_t* ht = tables + vs.table_off[vw.table_h];
+          const int32_t* vt = tables + vs.table_off[vw.table_v];
+          const int hk = ht[1], vk = vt[1];
+          __syncthreads();  // tmp may still be read by the previous resample view
+          for (int i = tid; i < bh * w; i += kViewThreads) {
+            const int y = i / w, xx = i - y * w;
+            const int32_t* rec = ht + 2 + (left + xx) * (2 + hk);
+            const int xmin = rec[0], nk = rec[1];
+            const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
+            int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+            for (int k = 0; k < nk; ++k) {
+              const int kk = rec[2 + k];
+              a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
+            }
+            tmp[i * 3] = clip8(a0 >> 22); tmp[i * 3 + 1] = clip8(a1 >> 22); tmp[i * 3 + 2] = clip8(a2 >> 22);
+          }
+          __syncthreads();
+          for (int i = tid; i < hw * 3; i += kViewThreads) {
+            const int c = i / hw, p = i - c * hw;
+            const int y = p / w, x = p - y * w;
+            const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
+            const int ymin = rec[0], nk = rec[1];
+            int a = 1 << 21;
+            for (int k = 0; k < nk; ++k) a += tmp[((ymin + k) * w + x) * 3 + c] * rec[2 + k];
+            ov[i] = NT[c * 256 + clip8(a >> 22)];
+          }
+          break;
+        }
+      }
+    }
+  }
+}
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_views_f32(const void* in, int in_is_f32, float* out, int64_t n, int h, int w, int n_views,
+                               const imgtx_view_t* views_host, const float* params_dev, const int32_t* tables_dev,
+                               const int32_t* table_offsets_host, int n_tables, const float* in_mean_host,
+                               const float* in_std_host, const float* out_mean_host, const float* out_std_host,
+                               imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && n >= 0, "bad image shape");
+  IMGTX_CHECK_ARG(n_views >= 1 && n_views <= kMaxViews && views_host, "1..%d views", kMaxViews);
+  IMGTX_CHECK_ARG(n_tables >= 0 && n_tables <= kMaxViews, "too many resample tables");
+  IMGTX_CHECK_ARG(out_mean_host && out_std_host, "output mean/std missing");
+  if (in_is_f32) IMGTX_CHECK_ARG(in_mean_host && in_std_host, "input mean/std missing (tensor_to_pil prologue)");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out && params_dev, "null pointer");
+  ViewSet vs;
+  memset(&vs, 0, sizeof(vs));
+  vs.n_views = n_views;
+  vs.in_is_f32 = in_is_f32;
+  int tmp_rows = 1;
+  for (int i = 0; i < n_views; ++i) {
+    vs.v[i] = views_host[i];
+    const int k = views_host[i].kind;
+    IMGTX_CHECK_ARG(k >= IMGTX_VIEW_IDENTITY && k <= IMGTX_VIEW_RESIZE_CENTER_CROP, "unknown view kind %d", k);
+    if (k == IMGTX_VIEW_CONTRAST) vs.any_contrast = 1;
+    if (k == IMGTX_VIEW_CROP_RESIZE || k == IMGTX_VIEW_RESIZE_CENTER_CROP) {
+      IMGTX_CHECK_ARG(tables_dev && table_offsets_host && views_host[i].table_h >= 0 && views_host[i].table_h < n_tables &&
+                          views_host[i].table_v >= 0 && views_host[i].table_v < n_tables, "bad resample table index");
+      tmp_rows = std::max(tmp_rows, k == IMGTX_VIEW_CROP_RESIZE ? views_host[i].i0 : h);
+      if (k == IMGTX_VIEW_CROP_RESIZE) IMGTX_CHECK_ARG(views_host[i].i0 > 0 && views_host[i].i0 <= std::min(h, w), "bad crop size");
+    }
+  }
+  int table_words = 0;
+  for (int i = 0; i <= n_tables; ++i) vs.table_off[i] = table_offsets_host ? table_offsets_host[i] : 0;
+  if (n_tables > 0) table_words = table_offsets_host[n_tables];
+  for (int i = 0; i < 3; ++i) {
+    vs.in_mean[i] = in_mean_host ? in_mean_host[i] : 0.f;
+    vs.in_std[i] = in_std_host ? in_std_host[i] : 1.f;
+    vs.out_mean[i] = out_mean_host[i];
+    vs.out_std[i] = out_std_host[i];
+  }
+  vs.tmp_rows = tmp_rows;
+  const int hw = h * w;
+  size_t smem = 768 * 4 + (size_t)((table_words + 3) & ~3) * 4 + ((size_t)hw * 3 + 4 + 15) / 16 * 16 +
+                ((size_t)tmp_rows * w * 3 + 4 + 15) / 16 * 16 + 16;
+  IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused views", h, w);
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)max_smem_optin() / (smem + 1024)));
+  int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * per_sm);
+  views_kernel<<<(unsigned)grid, kViewThreads, smem, (cudaStream_t)stream>>>(in, out, n, h, w, vs, params_dev, tables_dev,
+                                                                            table_words);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}

@@ -146,6 +146,23 @@ int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h
 int imgtx_box_filter_h_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int size,
                           imgtx_stream_t stream);
 
+/* ---- interpolating warps --------------------------------------------------------------------- */
+/* Pillow Image.transform(size=(ow,oh), AFFINE (6 coeffs) | PERSPECTIVE (8 coeffs), resample=BILINEAR|BICUBIC,
+   fillcolor): f64 evaluation identical to libImaging/Geometry.c.  coeffs_host (HOST, uniform) or
+   coeffs_per_image_dev (DEVICE, (n,8) doubles).  transformation.py:212-226 (apply_shear),
+   fall_2025/Initial_Experiments.py:88-92 (RandomPerspective / BILINEAR on PIL images) */
+int imgtx_pil_transform_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int oh, int ow,
+                           int perspective, int bicubic, const double* coeffs_host,
+                           const double* coeffs_per_image_dev, const uint8_t* fill_host, imgtx_stream_t stream);
+/* ToTensor -> torchvision RandomPerspective(p=1) on the tensor (bilinear grid_sample, fill) -> ToPILImage.
+   coeffs: DEVICE (n,8) f32 from _get_perspective_coeffs.  fall_2025/transformations_code:50-66 */
+int imgtx_perspective_tensor_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                const float* coeffs_per_image_dev, float fill, imgtx_stream_t stream);
+/* TF.gaussian_blur(img, kernel_size, sigma) on f32 planes (reflect padding) —
+   fall_2025/angellic_with_corrupt.py:54-56 */
+int imgtx_gaussian_blur_f32(const float* in, float* out, int64_t planes, int h, int w, int kernel_size, float sigma,
+                            imgtx_stream_t stream);
+
 /* ---- noise ---------------------------------------------------------------------------------- */
 typedef enum {
   IMGTX_NOISE_GAUSS_F32 = 0, /* transformation.py:272-281; draws: f32 (n,h,w,c) = normal(0, std*255) cast */
@@ -174,6 +191,55 @@ int imgtx_to_tensor_f32(const uint8_t* in, float* out, int64_t n, int h, int w, 
    pipenline/cifar_image_transformations.py:27-30, fall_2025/AugMix.py:56 */
 int imgtx_to_uint8_f32(const float* in, uint8_t* out, int64_t n, int h, int w, int c, const float* mean_host,
                        const float* std_host, int flags, imgtx_stream_t stream);
+
+/* ---- fused AugMix ---------------------------------------------------------------------------- */
+typedef enum {
+  IMGTX_AUG_NONE = 0,      /* chain shorter than `depth`, or a rotate by 0 degrees */
+  IMGTX_AUG_GEOM = 1,      /* Pillow NEAREST affine: a[0..5] = 16.16 fixed-point (a0,a1,a2,a3,a4,a5);
+                              rotate / shear_x / shear_y / translate_x / translate_y — fall_2025/AugMix.py:30,32-35 */
+  IMGTX_AUG_POSTERIZE = 2, /* param = byte mask — AugMix.py:31 */
+  IMGTX_AUG_SOLARIZE = 3,  /* param = threshold — AugMix.py:37 */
+  IMGTX_AUG_EQUALIZE = 4   /* ImageOps.equalize — AugMix.py:36 */
+} imgtx_augmix_kind;
+typedef struct {
+  int32_t kind;
+  int32_t a[6];
+  int32_t param;
+} imgtx_augmix_op_t;
+/* augmix(image_tensor, severity, width, depth) — fall_2025/AugMix.py:45-62 — for n images in one launch.
+   x/out: (n,3,h,w) f32.  ops_dev: (n, width, depth) records (op order within a chain = application order).
+   weights_dev: (n, width+2) f32 = [f32(ws_0..ws_{width-1}), f32(m), f32(1-m)] (1-m evaluated in double first). */
+int imgtx_augmix_f32(const float* x, float* out, int64_t n, int h, int w, int width, int depth,
+                     const imgtx_augmix_op_t* ops_dev, const float* weights_dev, imgtx_stream_t stream);
+
+/* ---- fused TTA view expansion --------------------------------------------------------------------- */
+typedef enum {
+  IMGTX_VIEW_IDENTITY = 0,           /* ToTensor+Normalize only */
+  IMGTX_VIEW_FLIP = 1,               /* FLIP_LEFT_RIGHT / RandomHorizontalFlip(p=1) */
+  IMGTX_VIEW_CROP_RESIZE = 2,        /* crop (p0,p1,p0+i0,p1+i0) then Image.resize((w,h)) — rand_crop; tables: i0->w, i0->h */
+  IMGTX_VIEW_BRIGHTNESS = 3,         /* ImageEnhance.Brightness(p0) */
+  IMGTX_VIEW_CONTRAST = 4,           /* ImageEnhance.Contrast(p0) */
+  IMGTX_VIEW_CROP_REFLECT = 5,       /* RandomCrop(size, padding=i0, 'reflect') at row p0, col p1 */
+  IMGTX_VIEW_FLIP_CROP_REFLECT = 6,  /* flip, then the reflect crop */
+  IMGTX_VIEW_RESIZE_CENTER_CROP = 7  /* Resize(s) + CenterCrop: tables w->s, h->s; window origin (i0 left, i1 top) */
+} imgtx_view_kind;
+typedef struct {
+  int32_t kind;
+  int32_t table_h, table_v; /* indices into the table blob (resample views only) */
+  int32_t i0, i1;
+  int32_t reserved[3];
+} imgtx_view_t;
+/* One image -> n_views normalised f32 CHW views, (n, n_views, 3, h, w), in one pass.
+   in: uint8 (n,h,w,3), or (in_is_f32) the normalised f32 (n,3,h,w) tensor, quantised first exactly like
+   tensor_to_pil(x*in_std + in_mean, clamp, *255 trunc).  views_host: HOST array, uniform over the batch;
+   params_dev: DEVICE (n, n_views, 2) f32 per-image parameters (p0, p1); tables_dev: DEVICE blob of Q22 tables from
+   imgtx_resample_table_host, table_offsets_host[n_tables+1] word offsets.
+   fall_2025/tta_initial_claudeFixed.py:37-78,218-230; fall_2025/TTA_transforms.py:69-138 */
+int imgtx_views_f32(const void* in, int in_is_f32, float* out, int64_t n, int h, int w, int n_views,
+                    const imgtx_view_t* views_host, const float* params_dev, const int32_t* tables_dev,
+                    const int32_t* table_offsets_host, int n_tables, const float* in_mean_host,
+                    const float* in_std_host, const float* out_mean_host, const float* out_std_host,
+                    imgtx_stream_t stream);
 
 /* ---- sign-step family --------------------------------------------------------------------- */
 #define IMGTX_MAX_EPS 8
