@@ -565,7 +565,7 @@ def perspective_tensor(x: torch.Tensor, coeffs, fill: float = 0.0, out=None) -> 
     n, h, w, c = x.shape
     out = torch.empty_like(x) if out is None else out
     co = np.broadcast_to(np.asarray(coeffs, np.float64).astype(np.float32).reshape(-1, 8), (n, 8))
-    cd = torch.from_numpy(np.ascontiguousarray(co)).to(x.device)
+    cd = torch.from_numpy(np.array(co, dtype=np.float32, order="C")).to(x.device)
     L.check(L.load().imgtx_perspective_tensor_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, cd.data_ptr(), float(fill),
                                                  _stream()))
     return out
