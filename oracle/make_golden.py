@@ -549,11 +549,26 @@ def gen_fgsm(X):
     b.save()
 
 
+def gen_fixtures(X):
+    """The reference's own CIFAR-10-C samples (CIFAR-10-C/store/*.png, lossless, all severity 1 — SURVEY §2.1) as one
+    array per corruption type, ordered by source index (0, 1001, 2002, 3003, 4004)."""
+    from PIL import Image
+    import re
+    out = {}
+    for p in sorted(glob.glob(os.path.join(R.REF_ROOT, "CIFAR-10-C", "store", "*.png"))):
+        m = re.match(r"(.+)_severity(\d)_idx(\d+)\.png", os.path.basename(p))
+        out.setdefault(m.group(1), []).append((int(m.group(3)), np.array(Image.open(p).convert("RGB"))))
+    arrays = {k: np.stack([a for _, a in sorted(v, key=lambda t: t[0])]) for k, v in out.items()}
+    path = os.path.join(GOLDEN_DIR, "cifar_c_fixtures.npz")
+    np.savez_compressed(path, **arrays)
+    print(f"{path}: {len(arrays)} types, {os.path.getsize(path) / 1e6:.2f} MB")
+
+
 def main():
     if not R.available():
         raise SystemExit("the reference is not mounted at " + R.REF_ROOT)
     X = make_inputs()
-    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm"]
+    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "fixtures"]
     for w in which:
         globals()["gen_" + w](X)
 
