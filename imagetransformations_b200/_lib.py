@@ -35,6 +35,7 @@ TOU8_DENORMALIZE, TOU8_CLAMP01 = 1, 2
 CLAMP_NONE, CLAMP_SCALAR, CLAMP_PER_CHANNEL = range(3)
 FC_GAUSSIAN_NOISE, FC_BRIGHTNESS, FC_CONTRAST, FC_ADD_NOISE = range(4)
 MAX_EPS = 8
+CC_GAUSSIAN, CC_SHOT, CC_IMPULSE, CC_SPECKLE, CC_BRIGHTNESS, CC_CONTRAST, CC_FOG, CC_FROST = range(8)
 (VIEW_IDENTITY, VIEW_FLIP, VIEW_CROP_RESIZE, VIEW_BRIGHTNESS, VIEW_CONTRAST, VIEW_CROP_REFLECT,
  VIEW_FLIP_CROP_REFLECT, VIEW_RESIZE_CENTER_CROP) = range(8)
 AUG_NONE, AUG_GEOM, AUG_POSTERIZE, AUG_SOLARIZE, AUG_EQUALIZE = range(5)
@@ -66,6 +67,17 @@ _PROTOS = {
     "imgtx_gaussian_blur_f32": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_noise_injected_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, C.c_double, _vp],
     "imgtx_noise_philox_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_uint64, _vp],
+    "imgtx_cc_pointwise_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_double, _vp, _vp, C.c_uint64, _int,
+                              _int, _int, _vp],
+    "imgtx_cc_defocus_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],
+    "imgtx_cc_csr_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _vp],
+    "imgtx_cc_glass_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _int, _vp, C.c_uint64, _vp],
+    "imgtx_cc_motion_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, C.c_double, C.c_double, C.c_uint64, _vp],
+    "imgtx_cc_snow_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _f, _f, _vp, _vp, _int, _vp, _vp, _vp, C.c_double,
+                         C.c_double, C.c_double, C.c_double, C.c_uint64, _vp],
+    "imgtx_cc_elastic_u8": [_vp, _vp, _i64, _int, _int, _int, C.c_double, _vp, _int, _vp, _vp, _vp, C.c_double,
+                            C.c_uint64, _vp],
+    "imgtx_cc_jpeg_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp],
     "imgtx_to_tensor_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_to_uint8_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _int, _vp],
     "imgtx_augmix_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],

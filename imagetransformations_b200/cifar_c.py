@@ -1,0 +1,391 @@
+"""CIFAR-10-C-style corruption generation: 15 types x 5 severities, batched on the GPU.
+
+The reference names the types (attacks/fgsm/cifar-10/reverse_fgsm_cifar10_corrupted.py:18-23) and consumes
+(50000,32,32,3) uint8 severity-major .npy files (fall_2025/TTA_transforms.py:16-26, transformation.py:35-41); its own
+generators exist for four types with ImageNet-C constants (pipenline/cifar_image_transformations.py:39-77 — those are the
+`table="reference"` variants here and the TransformationPool drop-ins).  `table="cifar"` (default) is the canonical
+CIFAR-10-C recipe.  Severity tables are data; small host-side tables (Gaussian taps, the disk kernel, the
+merged zoom operator, JPEG quantisers) are built here with numpy and handed to libimgtx.
+
+Random inputs: pass `draws` (a dict of arrays, see `DRAW_KEYS`) to inject them (parity mode), or leave it None to have
+them drawn on chip from Philox keyed by (seed, image index) (throughput mode).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib as L
+from . import batch as B
+
+CORRUPTIONS = ["gaussian_noise", "shot_noise", "impulse_noise", "defocus_blur", "glass_blur", "motion_blur",
+               "zoom_blur", "snow", "frost", "fog", "brightness", "contrast", "elastic_transform", "pixelate",
+               "jpeg_compression"]
+EXTRA = ["speckle_noise"]
+
+CIFAR_TABLE = {
+    "gaussian_noise": [0.04, 0.06, 0.08, 0.09, 0.10],
+    "shot_noise": [500, 250, 100, 75, 50],
+    "impulse_noise": [0.01, 0.02, 0.03, 0.05, 0.07],
+    "speckle_noise": [0.06, 0.1, 0.12, 0.16, 0.2],
+    "defocus_blur": [(0.3, 0.4), (0.4, 0.5), (0.5, 0.6), (1, 0.2), (1.5, 0.1)],
+    "glass_blur": [(0.05, 1, 1), (0.25, 1, 1), (0.4, 1, 1), (0.25, 1, 2), (0.4, 1, 2)],
+    "motion_blur": [(10, 1), (10, 1.5), (10, 2), (10, 2.5), (12, 3)],
+    "zoom_blur": [(1, 1.06), (1, 1.11), (1, 1.16), (1, 1.21), (1, 1.26)],
+    "snow": [(0.1, 0.2, 1, 0.6, 8, 3, 0.95), (0.1, 0.2, 1, 0.5, 10, 4, 0.9), (0.15, 0.3, 1.75, 0.55, 10, 4, 0.9),
+             (0.25, 0.3, 2.25, 0.6, 12, 6, 0.85), (0.3, 0.3, 1.25, 0.65, 14, 12, 0.8)],
+    "frost": [(1, 0.2), (1, 0.3), (0.9, 0.4), (0.85, 0.4), (0.75, 0.45)],
+    "fog": [(0.2, 3), (0.5, 3), (0.75, 2.5), (1, 2), (1.5, 1.75)],
+    "brightness": [0.05, 0.1, 0.15, 0.2, 0.3],
+    "contrast": [0.75, 0.5, 0.4, 0.3, 0.15],
+    "elastic_transform": [(0, 0, 0.08), (0.05, 0.2, 0.07), (0.08, 0.06, 0.06), (0.1, 0.04, 0.05), (0.1, 0.03, 0.03)],
+    "pixelate": [0.95, 0.9, 0.85, 0.75, 0.65],
+    "jpeg_compression": [80, 65, 58, 50, 40],
+}
+# the reference's own generators (ImageNet-C constants) — pipenline/cifar_image_transformations.py:39-77
+REFERENCE_TABLE = {
+    "gaussian_noise": [0.08, 0.12, 0.18, 0.26, 0.38],
+    "impulse_noise": [0.03, 0.06, 0.09, 0.17, 0.27],
+    "shot_noise": [60, 25, 12, 5, 3],
+    "defocus_blur": [3, 4, 6, 8, 10],
+}
+DRAW_KEYS = {
+    "gaussian_noise": ("noise",), "speckle_noise": ("noise",), "shot_noise": ("counts",),
+    "impulse_noise": ("u_flip", "u_salt"), "glass_blur": ("deltas",), "motion_blur": ("angles",),
+    "snow": ("layer", "angles"), "frost": ("frost",), "fog": ("plasma",), "elastic_transform": ("jitter", "ux", "uy"),
+}
+
+
+# ------------------------------------------------------------------------------------------------
+# host-side tables (numpy, float64 unless stated)
+# ------------------------------------------------------------------------------------------------
+def _reflect101(i, n):
+    if n == 1:
+        return np.zeros_like(i)
+    period = 2 * n - 2
+    m = np.mod(i, period)
+    return np.where(m >= n, period - m, m)
+
+
+def disk_taps(radius: float, alias_blur: float):
+    """make_cifar_c.disk(radius, alias_blur) as sparse taps: the 17x17 indicator disk, normalised in f32, blurred with
+    OpenCV's 3x3 f32 Gaussian (symmetric separable form, REFLECT_101).  Returns ((ntaps,2) int32 dy/dx, (ntaps,) f64)."""
+    f32 = np.float32
+    Lr = np.arange(-8, 8 + 1)
+    X, Y = np.meshgrid(Lr, Lr)
+    d = np.array((X ** 2 + Y ** 2) <= radius ** 2, dtype=f32)
+    d /= np.sum(d)
+    cf = np.exp(-0.5 / (alias_blur * alias_blur) * np.array([1.0, 0.0, 1.0]))
+    k = (cf / cf.sum()).astype(f32)
+
+    def sym3(a, axis):
+        n = a.shape[axis]
+        idx = _reflect101(np.arange(-1, n + 1), n)
+        lo = np.take(a, idx[0:n], axis)
+        hi = np.take(a, idx[2:n + 2], axis)
+        return (a * k[1] + (lo + hi).astype(f32) * k[0]).astype(f32)
+
+    kern = sym3(sym3(d, 1), 0)
+    ys, xs = np.nonzero(kern)
+    dydx = np.stack([ys - 8, xs - 8], axis=1).astype(np.int32)
+    return np.ascontiguousarray(dydx), kern[ys, xs].astype(np.float64)
+
+
+def gaussian_taps(sigma: float, truncate: float) -> np.ndarray:
+    """scipy.ndimage._gaussian_kernel1d: centre tap first, radius int(truncate*sigma + 0.5)."""
+    lw = int(truncate * float(sigma) + 0.5)
+    full = np.exp(-0.5 / (sigma * sigma) * np.arange(-lw, lw + 1, dtype=np.float64) ** 2)
+    full = full / full.sum()
+    return np.ascontiguousarray(full[lw:])
+
+
+def motion_kernel(radius: float, sigma: float) -> np.ndarray:
+    """ImageMagick's one-sided Gaussian line kernel (f32), width 2*ceil(radius)+1."""
+    width = int(2.0 * math.ceil(radius) + 1.0)
+    i = np.arange(width, dtype=np.float64)
+    k = np.exp(-(i * i) / (2.0 * sigma * sigma)) / (math.sqrt(2.0 * math.pi) * sigma)
+    return (k / k.sum()).astype(np.float32)
+
+
+def motion_offsets(width: int, angles_deg) -> np.ndarray:
+    """(n, width, 2) int32 (dx, dy) pixel offsets of the line taps for each angle."""
+    a = np.radians(np.asarray(angles_deg, np.float64)).reshape(-1, 1)
+    px, py = width * np.sin(a), width * np.cos(a)
+    hyp = np.hypot(px, py)
+    i = np.arange(width, dtype=np.float64)[None, :]
+    off = np.stack([np.ceil(i * py / hyp - 0.5), np.ceil(i * px / hyp - 0.5)], axis=2)
+    return np.ascontiguousarray(off.astype(np.int32))
+
+
+def zoom_axis_table(size: int, z: float):
+    """clipped_zoom along one axis: source indices (i0, i1) and fraction t (f32) per output sample
+    (scipy.ndimage.zoom order=1 coordinate o*(in-1)/(out-1), centre crop before, centre trim after)."""
+    ch = int(np.ceil(size / z))
+    top = (size - ch) // 2
+    osz = int(round(ch * z))
+    trim = (osz - size) // 2
+    o = np.arange(size) + trim
+    cc = o.astype(np.float64) * (np.float64(ch - 1) / np.float64(osz - 1)) if osz > 1 else np.zeros(size)
+    i0 = np.floor(cc).astype(np.int64)
+    t = (cc - i0).astype(np.float32)
+    i0 = np.clip(i0, 0, ch - 1)
+    i1 = np.minimum(i0 + 1, ch - 1)
+    return i0 + top, i1 + top, t
+
+
+_zoom_cache = {}
+
+
+def zoom_operator(h: int, w: int, severity: int, device):
+    """zoom_blur as one sparse linear operator W = (I + sum_z Zoom_z)/(n+1) in CSR form on `device` (taps of a row merged
+    in f64, sorted by source index, weights f32)."""
+    key = (h, w, severity, str(device))
+    if key in _zoom_cache:
+        return _zoom_cache[key]
+    lo, hi = CIFAR_TABLE["zoom_blur"][severity - 1]
+    zs = np.arange(lo, hi, 0.01)
+    P = h * w
+    W = np.zeros((P, P), np.float64)
+    rows = np.arange(P)
+    W[rows, rows] += 1.0
+    for z in zs:
+        y0, y1, ty = zoom_axis_table(h, float(z))
+        x0, x1, tx = zoom_axis_table(w, float(z))
+        ty, tx = ty.astype(np.float64), tx.astype(np.float64)
+        for ya, wy in ((y0, 1 - ty), (y1, ty)):
+            for xa, wx in ((x0, 1 - tx), (x1, tx)):
+                q = (ya[:, None] * w + xa[None, :]).reshape(-1)
+                np.add.at(W, (rows, q), (wy[:, None] * wx[None, :]).reshape(-1))
+    W /= (len(zs) + 1)
+    nzr, nzc = np.nonzero(W)
+    indptr = np.zeros(P + 1, np.int32)
+    np.add.at(indptr, nzr + 1, 1)
+    indptr = np.cumsum(indptr).astype(np.int32)
+    op = (torch.from_numpy(indptr).to(device), torch.from_numpy(nzc.astype(np.int32)).to(device),
+          torch.from_numpy(W[nzr, nzc].astype(np.float32)).to(device))
+    _zoom_cache[key] = op
+    return op
+
+
+_JPEG_LUMA = np.array([16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57, 69, 56,
+                       14, 17, 22, 29, 51, 87, 80, 62, 18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64, 81, 104, 113,
+                       92, 49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99], np.int64)
+_JPEG_CHROMA = np.array([17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99, 24, 26, 56, 99, 99, 99, 99,
+                         99, 47, 66, 99, 99, 99, 99, 99, 99] + [99] * 32, np.int64)
+
+
+def jpeg_qtables(quality: int) -> np.ndarray:
+    """libjpeg jpeg_set_quality(quality, force_baseline): (2, 64) int32, natural order."""
+    q = max(1, min(100, int(quality)))
+    scale = 5000 // q if q < 50 else 200 - q * 2
+    return np.stack([np.clip((b * scale + 50) // 100, 1, 255) for b in (_JPEG_LUMA, _JPEG_CHROMA)]).astype(np.int32)
+
+
+def affine_from_jitter(jitter: np.ndarray, size: int) -> np.ndarray:
+    """cv2.getAffineTransform(pts1, pts1 + jitter) for each image: (n, 6) f64 row-major 2x3 matrices."""
+    cs = np.float32((size, size)) // 2
+    sq = min((size, size)) // 3
+    pts1 = np.float32([cs + sq, [cs[0] + sq, cs[1] - sq], cs - sq])
+    out = np.empty((len(jitter), 6), np.float64)
+    A = np.zeros((6, 6))
+    for i in range(3):
+        A[i, 0:3] = [pts1[i][0], pts1[i][1], 1]
+        A[i + 3, 3:6] = [pts1[i][0], pts1[i][1], 1]
+    for k in range(len(jitter)):
+        pts2 = pts1 + np.asarray(jitter[k], np.float32)
+        out[k] = np.linalg.solve(A, np.concatenate([pts2[:, 0], pts2[:, 1]]).astype(np.float64))
+    return out
+
+
+_frost_cache = {}
+
+
+def procedural_frost_bank(device, n_tex: int = 5, size: int = 96, seed: int = 1234) -> torch.Tensor:
+    """(n_tex, size, size, 3) uint8 stand-in for the canonical frost photographs (which are not available): smoothed
+    multi-octave noise with a cold tint.  Documented substitute; any bank of textures can be passed instead."""
+    key = (str(device), n_tex, size, seed)
+    if key not in _frost_cache:
+        rng = np.random.default_rng(seed)
+        bank = np.empty((n_tex, size, size, 3), np.uint8)
+        for t in range(n_tex):
+            acc = np.zeros((size, size))
+            for octave in (4, 8, 16, 32):
+                g = rng.random((size // octave + 2, size // octave + 2))
+                acc += np.kron(g, np.ones((octave, octave)))[:size, :size] * octave
+            acc = (acc - acc.min()) / (acc.max() - acc.min())
+            crystals = (rng.random((size, size)) > 0.93) * rng.random((size, size))
+            v = np.clip(0.55 * acc + 0.6 * crystals, 0, 1)
+            bank[t] = np.stack([v * 215, v * 235, v * 255], axis=-1).astype(np.uint8)
+        _frost_cache[key] = torch.from_numpy(bank).to(device)
+    return _frost_cache[key]
+
+
+# ------------------------------------------------------------------------------------------------
+# one corruption
+# ------------------------------------------------------------------------------------------------
+def _dev(a, dtype, device):
+    if a is None:
+        return None
+    t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(a))
+    return t.to(device=device, dtype=dtype).contiguous()
+
+
+def _ptr(t):
+    return t.data_ptr() if t is not None else None
+
+
+def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = None, seed: int = 0, table: str = "cifar",
+            out: Optional[torch.Tensor] = None, frost_bank: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x: (n,h,w,3) uint8 CUDA -> same shape.  `draws` injects the random inputs (DRAW_KEYS[name]); None = on-chip RNG."""
+    x = B._check_u8(x)
+    n, h, w, c = x.shape
+    if not 1 <= severity <= 5:
+        raise ValueError("severity must be 1..5")
+    d = draws or {}
+    dev = x.device
+    lib = L.load()
+    st = B._stream()
+    seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    if table == "reference":
+        return _corrupt_reference(x, name, severity, d, seed, out)
+    if table != "cifar":
+        raise ValueError("table must be 'cifar' or 'reference'")
+    p = CIFAR_TABLE[name][severity - 1]
+    out = torch.empty_like(x) if out is None else out
+    xp, op = x.data_ptr(), out.data_ptr()
+
+    def point(kind, p0, p1=0.0, a=None, b=None, tex=(0, 0, 0)):
+        L.check(lib.imgtx_cc_pointwise_u8(xp, op, n, h, w, c, kind, float(p0), float(p1), _ptr(a), _ptr(b), seed, tex[0],
+                                          tex[1], tex[2], st))
+
+    # NB every device staging tensor is bound to a local name until the call returns: a temporary would hand its block
+    # back to the caching allocator before the next one is staged
+    if name in ("gaussian_noise", "speckle_noise"):
+        point(L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SPECKLE, p, a=_dev(d.get("noise"), torch.float64, dev))
+    elif name == "shot_noise":
+        point(L.CC_SHOT, p, a=_dev(d.get("counts"), torch.int64, dev))
+    elif name == "impulse_noise":
+        point(L.CC_IMPULSE, p, a=_dev(d.get("u_flip"), torch.float64, dev), b=_dev(d.get("u_salt"), torch.float64, dev))
+    elif name == "brightness":
+        point(L.CC_BRIGHTNESS, p)
+    elif name == "contrast":
+        point(L.CC_CONTRAST, p)
+    elif name == "fog":
+        point(L.CC_FOG, p[0], p[1], a=_dev(d.get("plasma"), torch.float64, dev))
+    elif name == "frost":
+        if "frost" in d:
+            point(L.CC_FROST, p[0], p[1], a=_dev(d["frost"], torch.uint8, dev))
+        else:
+            bank = procedural_frost_bank(dev) if frost_bank is None else frost_bank
+            point(L.CC_FROST, p[0], p[1], a=bank, tex=(bank.shape[0], bank.shape[1], bank.shape[2]))
+    elif name == "defocus_blur":
+        dydx, wts = disk_taps(p[0], p[1])
+        L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, st))
+    elif name == "zoom_blur":
+        ip, idx, wt = zoom_operator(h, w, severity, dev)
+        L.check(lib.imgtx_cc_csr_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(), st))
+    elif name == "glass_blur":
+        wts = gaussian_taps(p[0], 4.0)
+        deltas = _dev(d.get("deltas"), torch.int8, dev)
+        if deltas is not None and deltas.numel() != n * p[2] * (h - 2) * (w - 2) * 2:
+            raise ValueError("deltas must have shape (n, iters, h-2, w-2, 2)")
+        L.check(lib.imgtx_cc_glass_u8(xp, op, n, h, w, c, wts.ctypes.data, len(wts) - 1, p[2], _ptr(deltas), seed, st))
+    elif name == "motion_blur":
+        k = motion_kernel(p[0], p[1])
+        off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
+        L.check(lib.imgtx_cc_motion_u8(xp, op, n, h, w, c, len(k), k.ctypes.data, _ptr(off), -45.0, 45.0, seed, st))
+    elif name == "snow":
+        k = motion_kernel(p[4], p[5])
+        off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
+        y0, y1, ty = zoom_axis_table(h, float(p[2]))
+        x0, x1, tx = zoom_axis_table(w, float(p[2]))
+        zi = np.ascontiguousarray(np.concatenate([y0, y1, x0, x1]).astype(np.int32))
+        zt = np.ascontiguousarray(np.concatenate([ty, tx]).astype(np.float32))
+        layer = _dev(d.get("layer"), torch.float64, dev)
+        L.check(lib.imgtx_cc_snow_u8(xp, op, n, h, w, c, float(np.float32(p[3])), float(np.float32(p[6])),
+                                     float(np.float32(1 - p[6])), zi.ctypes.data, zt.ctypes.data, len(k), k.ctypes.data,
+                                     _ptr(off), _ptr(layer), float(p[0]), float(p[1]), -135.0, -45.0, seed, st))
+    elif name == "elastic_transform":
+        alpha, sigma, c2 = p[0] * h, p[1] * h, p[2] * h
+        if sigma > 1e-15:
+            wts = gaussian_taps(sigma, 3.0)
+            lw = len(wts) - 1
+        else:
+            wts, lw = np.zeros(1), -1
+        M = _dev(affine_from_jitter(d["jitter"], h), torch.float64, dev) if "jitter" in d else None
+        ux, uy = _dev(d.get("ux"), torch.float64, dev), _dev(d.get("uy"), torch.float64, dev)
+        L.check(lib.imgtx_cc_elastic_u8(xp, op, n, h, w, c, float(alpha), wts.ctypes.data, lw, _ptr(M), _ptr(ux), _ptr(uy),
+                                        float(c2), seed, st))
+    elif name == "pixelate":
+        small = B.resample(x, (int(w * p), int(h * p)), L.FILTER_BOX)
+        B.resample(small, (w, h), L.FILTER_BOX, out=out)
+    elif name == "jpeg_compression":
+        qt = jpeg_qtables(p)
+        L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, st))
+    else:
+        raise KeyError(name)
+    return out
+
+
+def _corrupt_reference(x, name, severity, d, seed, out):
+    """The reference's own four generators (TransformationPool, ImageNet-C constants)."""
+    p = REFERENCE_TABLE[name][severity - 1]
+    if name == "gaussian_noise":
+        if "noise" in d:
+            return B.noise_injected(x, L.NOISE_GAUSS_F64, d["noise"], out=out)
+        return B.noise_philox(x, L.NOISE_GAUSS_F64, p * 255.0, seed, out=out)
+    if name == "impulse_noise":
+        if "mask" in d:
+            return B.noise_injected(x, L.NOISE_IMPULSE, d["mask"], p, out=out)
+        return B.noise_philox(x, L.NOISE_IMPULSE, p, seed, out=out)
+    if name == "shot_noise":
+        if "counts" in d:
+            return B.noise_injected(x, L.NOISE_SHOT, d["counts"], p, out=out)
+        return B.noise_philox(x, L.NOISE_SHOT, p, seed, out=out)
+    if name == "defocus_blur":
+        return B.pil_gaussian_blur(x, p, out=out)
+    raise KeyError(f"the reference has no generator for {name}")
+
+
+# ------------------------------------------------------------------------------------------------
+# the suite
+# ------------------------------------------------------------------------------------------------
+def suite_passes(corruptions=None, severities=(1, 2, 3, 4, 5)):
+    return [(c, s) for c in (corruptions or CORRUPTIONS) for s in severities]
+
+
+def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5), seed: int = 0, out=None, sink=None):
+    """Run every (corruption, severity) pass over the device-resident batch x.  Each pass is one kernel launch (two for
+    pixelate).  `out`: optional (len(passes), n, h, w, 3) uint8 CUDA tensor receiving every pass; otherwise `sink(name,
+    severity, tensor)` is called per pass with a reused buffer (e.g. to checksum or stage to the host)."""
+    passes = suite_passes(corruptions, severities)
+    buf = None if out is not None else torch.empty_like(x)
+    for k, (name, sev) in enumerate(passes):
+        dst = out[k] if out is not None else buf
+        corrupt(x, name, sev, seed=seed * 1000 + k, out=dst)
+        if sink is not None:
+            sink(name, sev, dst)
+    return out if out is not None else buf
+
+
+def write_cifar_c(root: str, x_u8: np.ndarray, labels: np.ndarray, corruptions=None, seed: int = 0, batch: int = 10000):
+    """Write Hendrycks-layout files: <root>/<corruption>.npy of shape (5*N, h, w, 3), severity-major, plus labels.npy
+    (the layout CIFARC_Dataset slices: fall_2025/TTA_transforms.py:16-26)."""
+    os.makedirs(root, exist_ok=True)
+    n = len(x_u8)
+    np.save(os.path.join(root, "labels.npy"), np.tile(np.asarray(labels), 5))
+    pinned = torch.from_numpy(np.ascontiguousarray(x_u8)).pin_memory()
+    for ci, name in enumerate(corruptions or CORRUPTIONS):
+        dst = np.lib.format.open_memmap(os.path.join(root, f"{name}.npy"), mode="w+", dtype=np.uint8,
+                                        shape=(5 * n,) + tuple(x_u8.shape[1:]))
+        for sev in range(1, 6):
+            for i in range(0, n, batch):
+                xb = pinned[i:i + batch].cuda(non_blocking=True)
+                yb = corrupt(xb, name, sev, seed=(seed * 1000 + ci * 5 + sev) * 65536 + i // batch)
+                dst[(sev - 1) * n + i:(sev - 1) * n + i + len(xb)] = yb.cpu().numpy()
+        dst.flush()

@@ -1,0 +1,319 @@
+// CIFAR-10-C-style corruptions, part 1: pointwise types (float64 arithmetic, exactly the canonical numpy expressions;
+// specification: oracle/cifar_c.py).  The reference names the 15 types
+// (attacks/fgsm/cifar-10/reverse_fgsm_cifar10_corrupted.py:18-23) and consumes (50000,32,32,3) uint8 files of them
+// (fall_2025/TTA_transforms.py:16-26); SURVEY.md App. B gives the provisional spec.
+//
+//   IMGTX_CC_GAUSSIAN    clip(x/255 + n, 0, 1)*255                 n: injected f64 draws or on-chip N(0, p0)
+//   IMGTX_CC_SHOT        clip(k/p0, 0, 1)*255                      k: injected Poisson counts or on-chip Poisson(x/255*p0)
+//   IMGTX_CC_IMPULSE     salt & pepper per element                 u1 <= p0 flips; u2 <= 0.5 salts
+//   IMGTX_CC_SPECKLE     clip(v + v*n, 0, 1)*255, v = x/255
+//   IMGTX_CC_BRIGHTNESS  rgb -> hsv, V = clip(V + p0), hsv -> rgb (skimage formulas)
+//   IMGTX_CC_CONTRAST    clip((v - mean_c)*p0 + mean_c)            per-image per-channel mean (warp-shuffle reduction)
+//   IMGTX_CC_FOG         (v + p0*plasma) * max/(max + p0)          per-image max; plasma injected or generated on chip
+//                                                                  (diamond-square, p1 = wibbledecay)
+//   IMGTX_CC_FROST       clip(p0*x + p1*frost, 0, 255)             frost: injected crops, or random crops of a texture bank
+// Every byte is read once and written once (staged TMA pipeline); injected draws are streamed from HBM.
+// Roofline: HBM, 2 B/element (+ 8 B/element of draws in parity mode); on-chip RNG modes are ALU-bound.
+#include "pipeline.cuh"
+#include "rng.cuh"
+#include <string.h>
+
+namespace imgtx {
+
+struct CcPointParams {
+  int kind;
+  double p0, p1;
+  const void* a;   // draws (see header), device
+  const void* b;
+  uint64_t seed;
+  int tex_n, tex_h, tex_w;
+};
+
+__device__ __forceinline__ uint8_t q255(double v) {  // np.uint8(np.clip(v, 0, 1) * 255)
+  v = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
+  return (uint8_t)(int)(v * 255.0);
+}
+
+// On-chip plasma fractal (make_cifar_c.plasma_fractal) for one image: map is msz x msz doubles in shared memory.
+__device__ void plasma_device(double* map, int msz, double decay, const Philox& rng, uint32_t img_lo, uint32_t img_hi,
+                              double* red /* 2 doubles */) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  if (tid == 0) map[0] = 0.0;
+  __syncthreads();
+  double wibble = 100.0;
+  uint32_t draw = 0;
+  for (int s = msz; s >= 2; s >>= 1) {
+    const int half = s >> 1, m = msz / s;
+    // square centres
+    for (int i = tid; i < m * m; i += nt) {
+      const int a = i / m, b = i - a * m, a1 = (a + 1) % m, b1 = (b + 1) % m;
+      const double acc = map[(a * s) * msz + b * s] + map[(a1 * s) * msz + b * s] + map[(a * s) * msz + b1 * s] +
+                         map[(a1 * s) * msz + b1 * s];
+      const uint4 r = rng(img_lo, img_hi, 0x70u + draw, (uint32_t)i);
+      const double u = -wibble + 2.0 * wibble * (double)u01(r.x);
+      map[(half + a * s) * msz + half + b * s] = acc / 4 + wibble * u;
+    }
+    __syncthreads();
+    // edge midpoints (both families read only corners and centres: no hazard between them)
+    for (int i = tid; i < 2 * m * m; i += nt) {
+      const int fam = i / (m * m), k = i - fam * m * m;
+      const int a = k / m, b = k - a * m;
+      const uint4 r = rng(img_lo, img_hi, 0x71u + draw + fam, (uint32_t)k);
+      const double u = -wibble + 2.0 * wibble * (double)u01(r.x);
+      auto dr = [&](int ii, int jj) { return map[(half + ((ii + m) % m) * s) * msz + half + ((jj + m) % m) * s]; };
+      auto ul = [&](int ii, int jj) { return map[(((ii + m) % m) * s) * msz + ((jj + m) % m) * s]; };
+      if (fam == 0) {
+        const double acc = dr(a, b) + dr(a - 1, b) + ul(a, b) + ul(a, b + 1);
+        map[(a * s) * msz + half + b * s] = acc / 4 + wibble * u;
+      } else {
+        const double acc = dr(a, b) + dr(a, b - 1) + ul(a, b) + ul(a + 1, b);
+        map[(half + a * s) * msz + b * s] = acc / 4 + wibble * u;
+      }
+    }
+    __syncthreads();
+    draw += 3;
+    wibble /= decay;
+  }
+  // normalise to [0,1]
+  double mn = 1e300, mx = -1e300;
+  for (int i = tid; i < msz * msz; i += nt) { mn = fmin(mn, map[i]); mx = fmax(mx, map[i]); }
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  if (tid == 0) { red[0] = 1e300; red[1] = -1e300; }
+  __syncthreads();
+  if ((tid & 31) == 0) {
+    // doubles have no native atomic min/max: serialise the few warps through a CAS loop on the bit pattern
+    unsigned long long* p0 = reinterpret_cast<unsigned long long*>(&red[0]);
+    unsigned long long* p1 = reinterpret_cast<unsigned long long*>(&red[1]);
+    unsigned long long old = *p0, assumed;
+    do { assumed = old; if (__longlong_as_double(assumed) <= mn) break; old = atomicCAS(p0, assumed, __double_as_longlong(mn)); } while (assumed != old);
+    old = *p1;
+    do { assumed = old; if (__longlong_as_double(assumed) >= mx) break; old = atomicCAS(p1, assumed, __double_as_longlong(mx)); } while (assumed != old);
+  }
+  __syncthreads();
+  const double lo = red[0], span = red[1] - red[0];
+  for (int i = tid; i < msz * msz; i += nt) map[i] = (map[i] - lo) / span;
+  __syncthreads();
+}
+
+struct OpCcPoint : NoSpill {
+  using Params = CcPointParams;
+  static constexpr int kThreads = 256;
+  // T64 LUT (2 KB) + reduction cells (64 B) + plasma map (fog on-chip mode; sized for 32x32, see entry point)
+  static size_t scratch_bytes(const Shape&, int) { return 2048 + 64 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
+    __syncthreads();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    unsigned long long* cells = reinterpret_cast<unsigned long long*>(scratch + 2048);  // 8 cells
+    double* plasma_map = reinterpret_cast<double*>(scratch + 2048 + 64 + 16);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int hw = s.h * s.w, ne = hw * s.c;
+    const Philox rng(p.seed);
+    for (int j = 0; j < g; ++j) {
+      const int64_t img = img0 + j;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      uint8_t* om = dst + (size_t)j * s.out_bytes;
+      const int64_t ebase = img * ne;
+      switch (p.kind) {
+        case IMGTX_CC_GAUSSIAN:
+        case IMGTX_CC_SPECKLE: {
+          const double* nz = reinterpret_cast<const double*>(p.a);
+          for (int i = tid; i < ne; i += kThreads) {
+            double z;
+            if (nz) {
+              z = nz[ebase + i];
+            } else {
+              const uint64_t e = (uint64_t)(ebase + i);
+              const uint4 r = rng((uint32_t)(e >> 1), (uint32_t)(e >> 33), 0x10u, 0u);
+              float z0, z1;
+              box_muller(r.x, r.y, z0, z1);
+              z = (double)((e & 1) ? z1 : z0) * p.p0;
+            }
+            const double v = T[im[i]];
+            om[i] = q255(p.kind == IMGTX_CC_GAUSSIAN ? v + z : v + v * z);
+          }
+          break;
+        }
+        case IMGTX_CC_SHOT: {
+          const long long* cnt = reinterpret_cast<const long long*>(p.a);
+          for (int i = tid; i < ne; i += kThreads) {
+            double k;
+            if (cnt) {
+              k = (double)cnt[ebase + i];
+            } else {
+              const uint64_t e = (uint64_t)(ebase + i);
+              uint32_t ctr = 0;
+              k = (double)poisson_sample(rng, (uint32_t)e, (uint32_t)(e >> 32), 0x20u, ctr, (float)(T[im[i]] * p.p0));
+            }
+            om[i] = q255(k / p.p0);
+          }
+          break;
+        }
+        case IMGTX_CC_IMPULSE: {
+          const double* u1 = reinterpret_cast<const double*>(p.a);
+          const double* u2 = reinterpret_cast<const double*>(p.b);
+          for (int i = tid; i < ne; i += kThreads) {
+            double a, b;
+            if (u1) {
+              a = u1[ebase + i];
+              b = u2[ebase + i];
+            } else {
+              const uint64_t e = (uint64_t)(ebase + i);
+              const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x30u, 0u);
+              a = (double)u01(r.x);
+              b = (double)u01(r.y);
+            }
+            uint8_t o = im[i];
+            if (a <= p.p0) o = (b <= 0.5) ? 255 : 0;
+            om[i] = o;
+          }
+          break;
+        }
+        case IMGTX_CC_BRIGHTNESS: {
+          for (int px = tid; px < hw; px += kThreads) {
+            const double r = T[im[px * 3]], gg = T[im[px * 3 + 1]], b = T[im[px * 3 + 2]];
+            const double v = fmax(r, fmax(gg, b)), mn = fmin(r, fmin(gg, b));
+            const double delta = v - mn;
+            double sat = 0.0, h = 0.0;
+            if (delta != 0.0) {
+              sat = delta / v;
+              if (r == v) h = (gg - b) / delta;
+              if (gg == v) h = 2.0 + (b - r) / delta;
+              if (b == v) h = 4.0 + (r - gg) / delta;
+              h = h / 6.0;
+              h = h - trunc(h);          // fmod(h, 1.0), exact
+              if (h < 0.0) h = h + 1.0;   // numpy's % takes the divisor's sign
+            }
+            double v2 = v + p.p0;
+            v2 = v2 < 0.0 ? 0.0 : (v2 > 1.0 ? 1.0 : v2);
+            const double h6 = h * 6;
+            const double hif = floor(h6);
+            const double f = h6 - hif;
+            const double pp = v2 * (1 - sat), q = v2 * (1 - f * sat), t = v2 * (1 - (1 - f) * sat);
+            const int hi = ((int)hif & 255) % 6;
+            double o0, o1, o2;
+            switch (hi) {
+              case 0: o0 = v2; o1 = t; o2 = pp; break;
+              case 1: o0 = q; o1 = v2; o2 = pp; break;
+              case 2: o0 = pp; o1 = v2; o2 = t; break;
+              case 3: o0 = pp; o1 = q; o2 = v2; break;
+              case 4: o0 = t; o1 = pp; o2 = v2; break;
+              default: o0 = v2; o1 = pp; o2 = q; break;
+            }
+            om[px * 3] = q255(o0); om[px * 3 + 1] = q255(o1); om[px * 3 + 2] = q255(o2);
+          }
+          break;
+        }
+        case IMGTX_CC_CONTRAST: {
+          __syncthreads();
+          if (tid < 4) cells[tid] = 0ull;
+          __syncthreads();
+          unsigned a0 = 0, a1 = 0, a2 = 0;
+          for (int px = tid; px < hw; px += kThreads) { a0 += im[px * 3]; a1 += im[px * 3 + 1]; a2 += im[px * 3 + 2]; }
+          for (int o = 16; o > 0; o >>= 1) {
+            a0 += __shfl_xor_sync(0xffffffffu, a0, o);
+            a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+            a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+          }
+          if (lane == 0) { atomicAdd(&cells[0], a0); atomicAdd(&cells[1], a1); atomicAdd(&cells[2], a2); }
+          __syncthreads();
+          double mean[3];
+          for (int ch = 0; ch < 3; ++ch) mean[ch] = (double)cells[ch] / (double)hw / 255.0;
+          for (int i = tid; i < ne; i += kThreads) {
+            const int ch = i % 3;
+            om[i] = q255((T[im[i]] - mean[ch]) * p.p0 + mean[ch]);
+          }
+          break;
+        }
+        case IMGTX_CC_FOG: {
+          __syncthreads();
+          if (tid == 0) cells[4] = 0ull;
+          __syncthreads();
+          unsigned mx = 0;
+          for (int i = tid; i < ne; i += kThreads) mx = max(mx, (unsigned)im[i]);
+          for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+          if (lane == 0) atomicMax(&cells[4], (unsigned long long)mx);
+          __syncthreads();
+          const double mval = T[(int)cells[4]];
+          const double* pl = reinterpret_cast<const double*>(p.a);
+          if (pl) {
+            pl += img * hw;
+          } else {
+            plasma_device(plasma_map, s.h, p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32),
+                          reinterpret_cast<double*>(&cells[5]));
+            pl = plasma_map;
+          }
+          const double den = mval + p.p0;
+          for (int i = tid; i < ne; i += kThreads) {
+            const double v = T[im[i]] + p.p0 * pl[i / 3];
+            om[i] = q255(v * mval / den);
+          }
+          break;
+        }
+        default: {  // IMGTX_CC_FROST
+          const uint8_t* fr = reinterpret_cast<const uint8_t*>(p.a);
+          if (p.tex_n == 0) {
+            fr += ebase;
+            for (int i = tid; i < ne; i += kThreads) {
+              double v = p.p0 * (double)im[i] + p.p1 * (double)fr[i];
+              v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);
+              om[i] = (uint8_t)(int)v;
+            }
+          } else {
+            // random crop of a random texture: idx = randint(n_tex), (y0, x0) = randint(th - h), randint(tw - w)
+            const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x50u, 0u);
+            const int ti = (int)(r.x % (uint32_t)p.tex_n);
+            const int y0 = (int)(r.y % (uint32_t)(p.tex_h - s.h)), x0 = (int)(r.z % (uint32_t)(p.tex_w - s.w));
+            const uint8_t* tex = fr + ((size_t)ti * p.tex_h + y0) * p.tex_w * 3 + (size_t)x0 * 3;
+            const int rowb = s.w * 3;
+            for (int i = tid; i < ne; i += kThreads) {
+              const int y = i / rowb, xb = i - y * rowb;
+              double v = p.p0 * (double)im[i] + p.p1 * (double)__ldg(tex + (size_t)y * p.tex_w * 3 + xb);
+              v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);
+              om[i] = (uint8_t)(int)v;
+            }
+          }
+          break;
+        }
+      }
+    }
+  }
+};
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0,
+                                     double p1, const void* draws_a_dev, const void* draws_b_dev, uint64_t seed,
+                                     int tex_n, int tex_h, int tex_w, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  IMGTX_CHECK_ARG(kind >= IMGTX_CC_GAUSSIAN && kind <= IMGTX_CC_FROST, "unknown corruption kind %d", kind);
+  if (kind == IMGTX_CC_IMPULSE) IMGTX_CHECK_ARG((draws_a_dev == nullptr) == (draws_b_dev == nullptr), "impulse needs both draw arrays or none");
+  if (kind == IMGTX_CC_SHOT || kind == IMGTX_CC_GAUSSIAN) IMGTX_CHECK_ARG(p0 > 0 || draws_a_dev, "scale must be positive");
+  size_t extra = 0;
+  if (kind == IMGTX_CC_FOG && !draws_a_dev) {
+    IMGTX_CHECK_ARG(h == w && (h & (h - 1)) == 0 && h <= 64, "on-chip plasma needs a square power-of-two image (<= 64)");
+    extra = (size_t)h * w * sizeof(double);
+  }
+  if (kind == IMGTX_CC_FROST) {
+    IMGTX_CHECK_ARG(draws_a_dev, "frost needs crops or a texture bank");
+    if (tex_n > 0) IMGTX_CHECK_ARG(tex_h > h && tex_w > w, "texture smaller than the image");
+  }
+  CcPointParams p;
+  memset(&p, 0, sizeof(p));
+  p.kind = kind; p.p0 = p0; p.p1 = p1; p.a = draws_a_dev; p.b = draws_b_dev; p.seed = seed;
+  p.tex_n = kind == IMGTX_CC_FROST ? tex_n : 0; p.tex_h = tex_h; p.tex_w = tex_w;
+  return launch_image_op<OpCcPoint>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, extra);
+}

@@ -1,0 +1,480 @@
+// CIFAR-10-C-style corruptions, part 2: stencil types (specification: oracle/cifar_c.py).
+//
+//   imgtx_cc_defocus_u8  cv2.filter2D(x/255, disk kernel) per channel, REFLECT_101: sparse taps, float64 accumulation in
+//                        row-major tap order (bit-identical to OpenCV for these kernels).
+//   imgtx_cc_csr_u8      any fixed linear map out[p] = sum_k W[k] * (x/255)[idx[k]] given in CSR form, f32 accumulation in
+//                        stored order — zoom_blur (the per-severity merged operator (I + sum_z Zoom_z)/(n+1)).
+//   imgtx_cc_glass_u8    Gaussian (scipy symmetric-pair f64 order, edge replicate) -> uint8 -> sequential local pixel
+//                        swaps -> Gaussian.  The swap sweep is a 2-D recurrence; it runs as a skew-2 wavefront, one warp
+//                        per image (lane = row), 88 steps instead of 900.
+//   imgtx_cc_motion_u8   one-sided Gaussian line kernel along a per-image angle (ImageMagick MotionBlurImage restated),
+//                        edge virtual pixels, f32, rounded to nearest.
+//   imgtx_cc_snow_u8     noise layer -> centre zoom -> threshold -> 8-bit -> motion blur -> blend with the whitened image
+//                        plus the layer and its 180-degree rotation.
+// All images of a group stay in shared memory (staged TMA pipeline): HBM sees 1 read + 1 write per byte (+ draws).
+// Roofline: nominally HBM (2 B/element); the wide float stencils are ALU-bound (DESIGN.md has the per-pass numbers).
+#include "pipeline.cuh"
+#include "rng.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace imgtx {
+
+__device__ __forceinline__ uint8_t q255d(double v) {
+  v = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
+  return (uint8_t)(int)(v * 255.0);
+}
+__device__ __forceinline__ uint8_t q255f(float v) {
+  v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+  return (uint8_t)__float2int_rz(__fmul_rn(v, 255.0f));
+}
+
+// ------------------------------------------------------------------------------------------------
+// defocus_blur
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxTaps = 32;
+struct DefocusParams {
+  int ntaps;
+  int8_t dy[kMaxTaps], dx[kMaxTaps];
+  double w[kMaxTaps];
+};
+
+struct OpCcDefocus : NoSpill {
+  using Params = DefocusParams;
+  static constexpr int kThreads = 256;
+  static size_t scratch_bytes(const Shape&, int) { return 2048 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    const int hw = s.h * s.w, r = 2;  // |dy|,|dx| <= 2 for every severity; interior pixels skip the reflection
+    for (int i = threadIdx.x; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0;
+      const bool interior = (y >= r && y < s.h - r && x >= r && x < s.w - r);
+      for (int k = 0; k < p.ntaps; ++k) {
+        int yy = y + p.dy[k], xx = x + p.dx[k];
+        if (!interior) { yy = reflect101(yy, s.h); xx = reflect101(xx, s.w); }
+        const uint8_t* q = im + (yy * s.w + xx) * 3;
+        const double wt = p.w[k];
+        a0 = a0 + T[q[0]] * wt; a1 = a1 + T[q[1]] * wt; a2 = a2 + T[q[2]] * wt;
+      }
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+      o[0] = q255d(a0); o[1] = q255d(a1); o[2] = q255d(a2);
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// fixed sparse linear operator (zoom_blur)
+// ------------------------------------------------------------------------------------------------
+struct CsrParams {
+  const int32_t* indptr;   // device, P+1
+  const int32_t* indices;  // device, nnz
+  const float* weights;    // device, nnz
+  int nnz;
+};
+
+struct OpCcCsr : NoSpill {
+  using Params = CsrParams;
+  static constexpr int kThreads = 256;
+  // scratch: T32 (1 KB) | indptr (P+1) i32 | packed taps nnz x {u16 idx... kept as int32 idx, f32 w} (extra_scratch)
+  static size_t scratch_bytes(const Shape&, int) { return 1024 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  static size_t table_bytes(int P, int nnz) { return align_up((size_t)(P + 1) * 4, 16) + (size_t)nnz * 8 + 16; }
+  __device__ static void prepare(const Shape& s, const Params& p, uint8_t* scratch, bool) {
+    float* T = reinterpret_cast<float*>(scratch);
+    const int P = s.h * s.w;
+    int32_t* ip = reinterpret_cast<int32_t*>(scratch + 1024 + 16);
+    int2* taps = reinterpret_cast<int2*>(scratch + 1024 + 16 + align_up((size_t)(P + 1) * 4, 16));
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    for (int i = threadIdx.x; i <= P; i += kThreads) ip[i] = p.indptr[i];
+    for (int i = threadIdx.x; i < p.nnz; i += kThreads) taps[i] = make_int2(p.indices[i] * 3, __float_as_int(p.weights[i]));
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const float* T = reinterpret_cast<const float*>(scratch);
+    const int P = s.h * s.w;
+    const int32_t* ip = reinterpret_cast<const int32_t*>(scratch + 1024 + 16);
+    const int2* taps = reinterpret_cast<const int2*>(scratch + 1024 + 16 + align_up((size_t)(P + 1) * 4, 16));
+    for (int i = threadIdx.x; i < g * P; i += kThreads) {
+      const int j = i / P, px = i - j * P;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+      const int k1 = ip[px + 1];
+      for (int k = ip[px]; k < k1; ++k) {
+        const int2 t = taps[k];
+        const float wt = __int_as_float(t.y);
+        const uint32_t rgb = load_rgb(im + t.x);
+        a0 = __fadd_rn(a0, __fmul_rn(T[rgb & 255u], wt));
+        a1 = __fadd_rn(a1, __fmul_rn(T[(rgb >> 8) & 255u], wt));
+        a2 = __fadd_rn(a2, __fmul_rn(T[(rgb >> 16) & 255u], wt));
+      }
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+      o[0] = q255f(a0); o[1] = q255f(a1); o[2] = q255f(a2);
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// glass_blur
+// ------------------------------------------------------------------------------------------------
+struct GlassParams {
+  double w[4];  // centre, +-1, +-2 (lw <= 2 for every severity)
+  int lw, iters;
+  const int8_t* deltas;  // device (n, iters, h-2, w-2, 2) or nullptr (on-chip draws)
+  uint64_t seed;
+};
+
+struct OpCcGlass : NoSpill {
+  using Params = GlassParams;
+  static constexpr int kThreads = 256;
+  // T64 (2 KB) + one f64 plane (h*w*3*8)
+  static size_t scratch_bytes(const Shape& s, int) { return 2048 + (size_t)s.in_bytes * 8 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
+    __syncthreads();
+  }
+
+  // scipy gaussian_filter (axis y first, then x), mode 'nearest'; in/out are u8 images, tmp is the f64 plane
+  template <bool FINAL>
+  __device__ static void gaussian(const uint8_t* in, uint8_t* out, double* tmp, const double* T, const Shape& s,
+                                  const Params& p) {
+    const int ne = s.in_bytes, rowb = s.w * 3;
+    for (int i = threadIdx.x; i < ne; i += kThreads) {
+      const int y = i / rowb, xb = i - y * rowb;
+      double acc = T[in[i]] * p.w[0];
+      for (int k = p.lw; k >= 1; --k)
+        acc = acc + (T[in[clampi(y - k, 0, s.h - 1) * rowb + xb]] + T[in[clampi(y + k, 0, s.h - 1) * rowb + xb]]) * p.w[k];
+      tmp[i] = acc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < ne; i += kThreads) {
+      const int y = i / rowb, xb = i - y * rowb;
+      const int x = xb / 3, ch = xb - x * 3;
+      const double* row = tmp + y * rowb + ch;
+      double acc = row[x * 3] * p.w[0];
+      for (int k = p.lw; k >= 1; --k)
+        acc = acc + (row[clampi(x - k, 0, s.w - 1) * 3] + row[clampi(x + k, 0, s.w - 1) * 3]) * p.w[k];
+      out[i] = FINAL ? q255d(acc) : (uint8_t)(int)(acc * 255.0);
+    }
+    __syncthreads();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    double* tmp = reinterpret_cast<double*>(scratch + 2048);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int j = 0; j < g; ++j)
+      gaussian<false>(src + (size_t)j * s.in_bytes, dst + (size_t)j * s.out_bytes, tmp, T, s, p);
+    // ---- swaps: one warp per image, rows on lanes, skew-2 wavefront (requires h - 2 <= 32) ----
+    const int R = s.h - 2, Ccols = s.w - 2;
+    const Philox rng(p.seed);
+    for (int j = warp; j < g; j += kThreads >> 5) {
+      uint8_t* im = dst + (size_t)j * s.out_bytes;
+      const int64_t img = img0 + j;
+      for (int it = 0; it < p.iters; ++it) {
+        const int h = s.h - 1 - lane;
+        for (int t = 0; t < 2 * (R - 1) + Ccols; ++t) {
+          const int ci = t - 2 * lane;
+          if (lane < R && ci >= 0 && ci < Ccols) {
+            const int w = s.w - 1 - ci;
+            int dx, dy;
+            if (p.deltas) {
+              const int8_t* d = p.deltas + ((((img * p.iters + it) * R + lane) * Ccols + ci) << 1);
+              dx = d[0]; dy = d[1];
+            } else {
+              const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)(lane * Ccols + ci));
+              dx = -(int)(r.x & 1u); dy = -(int)(r.y & 1u);
+            }
+            uint8_t* a = im + (h * s.w + w) * 3;
+            uint8_t* b = im + ((h + dy) * s.w + (w + dx)) * 3;
+            const uint8_t t0 = a[0], t1 = a[1], t2 = a[2];
+            a[0] = b[0]; a[1] = b[1]; a[2] = b[2];
+            b[0] = t0; b[1] = t1; b[2] = t2;
+          }
+          __syncwarp();
+        }
+      }
+    }
+    __syncthreads();
+    for (int j = 0; j < g; ++j) {
+      uint8_t* im = dst + (size_t)j * s.out_bytes;
+      gaussian<true>(im, im, tmp, T, s, p);
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// motion_blur (also the snow layer's blur)
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxLine = 32;
+struct MotionParams {
+  int width;
+  float k[kMaxLine];
+  const int32_t* offsets;  // device (n, width, 2) (dx, dy) or nullptr: angle drawn on chip in [lo, hi] degrees
+  double lo, hi;
+  uint64_t seed;
+};
+
+// ImageMagick MotionBlurImage offsets for one angle (float64, like the host code path)
+__device__ inline void motion_offsets(double angle_deg, int width, int* off /* width*2 */) {
+  const double a = angle_deg * 0.017453292519943295;
+  const double px = (double)width * sin(a), py = (double)width * cos(a);
+  const double hyp = hypot(px, py);
+  for (int i = threadIdx.x & 31; i < width; i += 32) {
+    off[i * 2] = (int)ceil((double)i * py / hyp - 0.5);
+    off[i * 2 + 1] = (int)ceil((double)i * px / hyp - 0.5);
+  }
+}
+
+struct OpCcMotion : NoSpill {
+  using Params = MotionParams;
+  static constexpr int kThreads = 256;
+  static size_t scratch_bytes(const Shape&, int G) { return (size_t)G * kMaxLine * 2 * 4 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t*, bool) {}
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    int* off = reinterpret_cast<int*>(scratch);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const Philox rng(p.seed);
+    __syncthreads();
+    if (p.offsets) {
+      for (int i = tid; i < g * p.width * 2; i += kThreads) {
+        const int j = i / (p.width * 2), k = i - j * p.width * 2;
+        off[j * kMaxLine * 2 + k] = p.offsets[(img0 + j) * p.width * 2 + k];
+      }
+    } else {
+      for (int j = warp; j < g; j += kThreads >> 5) {
+        const int64_t img = img0 + j;
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x60u, 0u);
+        motion_offsets(p.lo + (p.hi - p.lo) * (double)u01(r.x), p.width, off + j * kMaxLine * 2);
+      }
+    }
+    __syncthreads();
+    const int hw = s.h * s.w;
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      const int* oj = off + j * kMaxLine * 2;
+      float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+      for (int k = 0; k < p.width; ++k) {
+        const int xx = clampi(x + oj[k * 2], 0, s.w - 1), yy = clampi(y + oj[k * 2 + 1], 0, s.h - 1);
+        const uint32_t rgb = load_rgb(im + (yy * s.w + xx) * 3);
+        const float wt = p.k[k];
+        a0 = __fadd_rn(a0, __fmul_rn((float)(rgb & 255u), wt));
+        a1 = __fadd_rn(a1, __fmul_rn((float)((rgb >> 8) & 255u), wt));
+        a2 = __fadd_rn(a2, __fmul_rn((float)((rgb >> 16) & 255u), wt));
+      }
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+      o[0] = clip8((int)floorf(__fadd_rn(a0, 0.5f)));
+      o[1] = clip8((int)floorf(__fadd_rn(a1, 0.5f)));
+      o[2] = clip8((int)floorf(__fadd_rn(a2, 0.5f)));
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// snow
+// ------------------------------------------------------------------------------------------------
+constexpr int kSnowMax = 64;  // max image side
+struct SnowParams {
+  float thresh, c6, one_minus_c6;
+  double loc, scale;  // on-chip layer draws
+  int8_t y0[kSnowMax], y1[kSnowMax], x0[kSnowMax], x1[kSnowMax];  // centre-zoom tables of the layer
+  float ty[kSnowMax], tx[kSnowMax];
+  MotionParams m;          // layer blur
+  const double* layer;     // device (n,h,w) f64 or nullptr
+};
+
+struct OpCcSnow : NoSpill {
+  using Params = SnowParams;
+  static constexpr int kThreads = 256;
+  // per image: L0 f32[hw] + L1 u8[hw] + L2 u8[hw] + offsets
+  static size_t per_image(const Shape& s) { return (size_t)s.h * s.w * 6 + kMaxLine * 2 * 4; }
+  static size_t scratch_bytes(const Shape& s, int G) { return align_up((size_t)G * per_image(s), 16) + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t*, bool) {}
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int hw = s.h * s.w;
+    float* L0 = reinterpret_cast<float*>(scratch);                          // [g][hw]
+    int* off = reinterpret_cast<int*>(L0 + (size_t)g * hw);                  // [g][kMaxLine*2]
+    uint8_t* L1 = reinterpret_cast<uint8_t*>(off + (size_t)g * kMaxLine * 2);  // [g][hw]
+    uint8_t* L2 = L1 + (size_t)g * hw;
+    const Philox rng(p.m.seed);
+    __syncthreads();
+    // noise layer (f64 draws cast to f32) and blur offsets
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int64_t img = img0 + j;
+      if (p.layer) {
+        L0[i] = (float)p.layer[img * hw + px];
+      } else {
+        const uint64_t e = (uint64_t)(img * hw + px);
+        const uint4 r = rng((uint32_t)(e >> 1), (uint32_t)(e >> 33), 0x61u, 0u);
+        float z0, z1;
+        box_muller(r.x, r.y, z0, z1);
+        L0[i] = (float)(p.loc + p.scale * (double)((e & 1) ? z1 : z0));
+      }
+    }
+    if (p.m.offsets) {
+      for (int i = tid; i < g * p.m.width * 2; i += kThreads) {
+        const int j = i / (p.m.width * 2), k = i - j * p.m.width * 2;
+        off[j * kMaxLine * 2 + k] = p.m.offsets[(img0 + j) * p.m.width * 2 + k];
+      }
+    } else {
+      for (int j = warp; j < g; j += kThreads >> 5) {
+        const int64_t img = img0 + j;
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x62u, 0u);
+        motion_offsets(p.m.lo + (p.m.hi - p.m.lo) * (double)u01(r.x), p.m.width, off + j * kMaxLine * 2);
+      }
+    }
+    __syncthreads();
+    // centre zoom (order-1), threshold, 8-bit
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      const float* L = L0 + (size_t)j * hw;
+      const float ty = p.ty[y], tx = p.tx[x], uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
+      float acc = __fmul_rn(__fmul_rn(L[p.y0[y] * s.w + p.x0[x]], uy), ux);
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y0[y] * s.w + p.x1[x]], uy), tx));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y1[y] * s.w + p.x0[x]], ty), ux));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y1[y] * s.w + p.x1[x]], ty), tx));
+      if (acc < p.thresh) acc = 0.0f;
+      L1[i] = q255f(acc);
+    }
+    __syncthreads();
+    // motion blur of the 8-bit layer, rounded back to 8 bits
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      const uint8_t* L = L1 + (size_t)j * hw;
+      const int* oj = off + j * kMaxLine * 2;
+      float acc = 0.0f;
+      for (int k = 0; k < p.m.width; ++k) {
+        const int xx = clampi(x + oj[k * 2], 0, s.w - 1), yy = clampi(y + oj[k * 2 + 1], 0, s.h - 1);
+        acc = __fadd_rn(acc, __fmul_rn((float)L[yy * s.w + xx], p.m.k[k]));
+      }
+      L2[i] = clip8((int)floorf(__fadd_rn(acc, 0.5f)));
+    }
+    __syncthreads();
+    // blend
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const uint8_t* im = src + (size_t)j * s.in_bytes + px * 3;
+      const uint8_t* L = L2 + (size_t)j * hw;
+      const float sl = __fdiv_rn((float)L[px], 255.0f), sr = __fdiv_rn((float)L[hw - 1 - px], 255.0f);
+      const float r = __fdiv_rn((float)im[0], 255.0f), gg = __fdiv_rn((float)im[1], 255.0f), b = __fdiv_rn((float)im[2], 255.0f);
+      float gray = __fadd_rn(__fmul_rn(r, 0.299f), __fmul_rn(gg, 0.587f));
+      gray = __fadd_rn(gray, __fmul_rn(b, 0.114f));
+      const float whit = __fadd_rn(__fmul_rn(gray, 1.5f), 0.5f);
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+      const float ch[3] = {r, gg, b};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float mix = __fadd_rn(__fmul_rn(p.c6, ch[c]), __fmul_rn(p.one_minus_c6, fmaxf(ch[c], whit)));
+        o[c] = q255f(__fadd_rn(__fadd_rn(mix, sl), sr));
+      }
+    }
+  }
+};
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
+                                   const int32_t* dydx_host, const double* weights_host, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 4 && w > 4 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  IMGTX_CHECK_ARG(ntaps >= 1 && ntaps <= kMaxTaps && dydx_host && weights_host, "1..%d taps", kMaxTaps);
+  DefocusParams p;
+  memset(&p, 0, sizeof(p));
+  p.ntaps = ntaps;
+  for (int i = 0; i < ntaps; ++i) {
+    IMGTX_CHECK_ARG(abs(dydx_host[2 * i]) <= 2 && abs(dydx_host[2 * i + 1]) <= 2, "tap offset outside +-2");
+    p.dy[i] = (int8_t)dydx_host[2 * i];
+    p.dx[i] = (int8_t)dydx_host[2 * i + 1];
+    p.w[i] = weights_host[i];
+  }
+  return launch_image_op<OpCcDefocus>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+}
+
+extern "C" int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+                               const int32_t* indices_dev, const float* weights_dev, int nnz, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0, "missing operator");
+  CsrParams p;
+  p.indptr = indptr_dev; p.indices = indices_dev; p.weights = weights_dev; p.nnz = nnz;
+  const size_t extra = OpCcCsr::table_bytes(h * w, nnz);
+  IMGTX_CHECK_ARG(extra + 64 * 1024 <= (size_t)max_smem_optin(), "operator too large for shared memory (%d taps)", nnz);
+  return launch_image_op<OpCcCsr>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, extra,
+                                  (int)extra + 64 * 1024);
+}
+
+extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
+                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 2 && w > 2 && h <= 34 && c == 3 && n >= 0, "glass_blur takes (n,h<=34,w,3) images");
+  IMGTX_CHECK_ARG(lw >= 0 && lw <= 3 && weights_host && iters >= 0, "bad Gaussian");
+  GlassParams p;
+  memset(&p, 0, sizeof(p));
+  for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
+  p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
+  return launch_image_op<OpCcGlass>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+}
+
+static int fill_motion(MotionParams& m, int width, const float* k_host, const int32_t* offsets_dev, double lo, double hi,
+                       uint64_t seed) {
+  IMGTX_CHECK_ARG(width >= 1 && width <= kMaxLine && k_host, "line kernel width must be in [1,%d]", kMaxLine);
+  memset(&m, 0, sizeof(m));
+  m.width = width;
+  for (int i = 0; i < width; ++i) m.k[i] = k_host[i];
+  m.offsets = offsets_dev; m.lo = lo; m.hi = hi; m.seed = seed;
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
+                                  const float* k_host, const int32_t* offsets_dev, double angle_lo, double angle_hi,
+                                  uint64_t seed, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  MotionParams p;
+  int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
+  if (rc) return rc;
+  return launch_image_op<OpCcMotion>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+}
+
+extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
+                                float one_minus_c6, const int32_t* zoom_idx_host /* y0,y1 (h each), x0,x1 (w each) */,
+                                const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
+                                const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
+                                double angle_lo, double angle_hi, uint64_t seed, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && h <= kSnowMax && w <= kSnowMax && c == 3 && n >= 0, "snow takes (n,h<=64,w<=64,3) images");
+  IMGTX_CHECK_ARG(zoom_idx_host && zoom_t_host, "missing zoom tables");
+  SnowParams p;
+  memset(&p, 0, sizeof(p));
+  int rc = fill_motion(p.m, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
+  if (rc) return rc;
+  p.thresh = thresh; p.c6 = c6; p.one_minus_c6 = one_minus_c6; p.loc = loc; p.scale = scale; p.layer = layer_dev;
+  for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }
+  for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
+  return launch_image_op<OpCcSnow>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+}

@@ -1,0 +1,431 @@
+// CIFAR-10-C-style corruptions, part 3: elastic_transform and jpeg_compression (specification: oracle/cifar_c.py,
+// both pinned bit-for-bit against the libraries they restate: cv2.warpAffine + scipy.ndimage gaussian_filter /
+// map_coordinates, and Pillow's libjpeg-turbo round trip).
+//
+//   imgtx_cc_elastic_u8  random affine (cv2.warpAffine: inverse map in f64, 1/1024 fixed-point coordinates snapped to 1/32
+//                        sub-pixels, f32 table weights, REFLECT_101) -> Gaussian-smoothed random displacement field
+//                        (scipy symmetric-pair f64 order, half-sample 'reflect') -> bilinear map_coordinates (f64 weights,
+//                        'reflect').
+//   imgtx_cc_jpeg_u8     baseline JPEG round trip without the (lossless) entropy coder: RGB->YCbCr, 4:2:0 h2v2 downsample,
+//                        islow forward DCT, quantise / dequantise, islow inverse DCT, h2v2 fancy upsample, YCbCr->RGB —
+//                        all in libjpeg's integer arithmetic.  8 threads per 8x8 block (one per row / column).
+// Roofline: nominally HBM (2 B/element); both are integer/f64-ALU bound.
+#include "pipeline.cuh"
+#include "rng.cuh"
+#include <math.h>
+#include <string.h>
+
+namespace imgtx {
+
+// ------------------------------------------------------------------------------------------------
+// elastic_transform
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxLw = 20;
+struct ElasticParams {
+  double alpha;
+  double w[kMaxLw + 1];
+  int lw;                 // -1: sigma == 0 (no smoothing)
+  const double* M;        // device (n,6) forward affine matrices, or nullptr (jitter drawn on chip, amplitude c2)
+  const double* ux;       // device (n,h,w) uniform(-1,1) fields or nullptr
+  const double* uy;
+  double c2;
+  uint64_t seed;
+};
+
+__device__ __forceinline__ int reflect_half(int i, int n) {  // scipy 'reflect': d c b a | a b c d | d c b a
+  const int period = 2 * n;
+  int m = i % period;
+  if (m < 0) m += period;
+  return m >= n ? period - 1 - m : m;
+}
+
+struct OpCcElastic : NoSpill {
+  using Params = ElasticParams;
+  static constexpr int kThreads = 256;
+  // T32 (1 KB) + warped image f32 (hw*3*4) + two f64 field planes (hw*8 each) + dx, dy f32 (hw*4 each) + M (64 B)
+  static size_t scratch_bytes(const Shape& s, int) { return 1024 + (size_t)s.h * s.w * (12 + 16 + 8) + 64 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    float* T = reinterpret_cast<float*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    __syncthreads();
+  }
+
+  // gaussian_filter(field, sigma, mode='reflect') * alpha -> f32; F0 holds the field, F1 is scratch
+  __device__ static void smooth(double* F0, double* F1, float* out, const Shape& s, const Params& p) {
+    const int hw = s.h * s.w, tid = threadIdx.x;
+    if (p.lw < 0) {
+      for (int i = tid; i < hw; i += kThreads) out[i] = (float)(F0[i] * p.alpha);
+      __syncthreads();
+      return;
+    }
+    for (int i = tid; i < hw; i += kThreads) {  // axis y
+      const int y = i / s.w, x = i - y * s.w;
+      double acc = F0[i] * p.w[0];
+      for (int k = p.lw; k >= 1; --k)
+        acc = acc + (F0[reflect_half(y - k, s.h) * s.w + x] + F0[reflect_half(y + k, s.h) * s.w + x]) * p.w[k];
+      F1[i] = acc;
+    }
+    __syncthreads();
+    for (int i = tid; i < hw; i += kThreads) {  // axis x
+      const int y = i / s.w, x = i - y * s.w;
+      const double* row = F1 + y * s.w;
+      double acc = row[x] * p.w[0];
+      for (int k = p.lw; k >= 1; --k) acc = acc + (row[reflect_half(x - k, s.w)] + row[reflect_half(x + k, s.w)]) * p.w[k];
+      out[i] = (float)(acc * p.alpha);
+    }
+    __syncthreads();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int tid = threadIdx.x;
+    const int hw = s.h * s.w;
+    const float* T = reinterpret_cast<const float*>(scratch);
+    float* W = reinterpret_cast<float*>(scratch + 1024);        // warped image, HWC f32
+    double* F0 = reinterpret_cast<double*>(W + hw * 3);
+    double* F1 = F0 + hw;
+    float* DX = reinterpret_cast<float*>(F1 + hw);
+    float* DY = DX + hw;
+    double* Ms = reinterpret_cast<double*>(DY + hw);            // inverse matrix (6)
+    const Philox rng(p.seed);
+    for (int j = 0; j < g; ++j) {
+      const int64_t img = img0 + j;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      uint8_t* om = dst + (size_t)j * s.out_bytes;
+      __syncthreads();
+      if (tid == 0) {
+        double M[6];
+        if (p.M) {
+          for (int k = 0; k < 6; ++k) M[k] = p.M[img * 6 + k];
+        } else {
+          // pts1 = [(c+q, c+q), (c+q, c-q), (c-q, c-q)], pts2 = pts1 + U(-c2, c2): closed-form affine through 3 points
+          const float cs = (float)(s.h / 2), q = (float)(s.h / 3);
+          const float p1[3][2] = {{cs + q, cs + q}, {cs + q, cs - q}, {cs - q, cs - q}};
+          double p2[3][2];
+          const uint4 r0 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 0u);
+          const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 1u);
+          const uint32_t rr[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y};
+          for (int k = 0; k < 6; ++k)
+            p2[k / 2][k % 2] = (double)(p1[k / 2][k % 2] + (float)(-p.c2 + 2.0 * p.c2 * (double)u01(rr[k])));
+          const double x0 = p1[0][0], y0 = p1[0][1], x1 = p1[1][0], y1 = p1[1][1], x2 = p1[2][0], y2 = p1[2][1];
+          const double det = x0 * (y1 - y2) - y0 * (x1 - x2) + (x1 * y2 - x2 * y1);
+          for (int rrow = 0; rrow < 2; ++rrow) {
+            const double u0 = p2[0][rrow], u1 = p2[1][rrow], u2 = p2[2][rrow];
+            M[rrow * 3 + 0] = (u0 * (y1 - y2) - y0 * (u1 - u2) + (u1 * y2 - u2 * y1)) / det;
+            M[rrow * 3 + 1] = (x0 * (u1 - u2) - u0 * (x1 - x2) + (x1 * u2 - x2 * u1)) / det;
+            M[rrow * 3 + 2] = (x0 * (y1 * u2 - y2 * u1) - y0 * (x1 * u2 - x2 * u1) + u0 * (x1 * y2 - x2 * y1)) / det;
+          }
+        }
+        // cv2.warpAffine: invert (no WARP_INVERSE_MAP)
+        double D = M[0] * M[4] - M[1] * M[3];
+        D = D != 0.0 ? 1.0 / D : 0.0;
+        const double A11 = M[4] * D, A22 = M[0] * D;
+        M[0] = A11; M[1] *= -D; M[3] *= -D; M[4] = A22;
+        const double b1 = -M[0] * M[2] - M[1] * M[5];
+        const double b2 = -M[3] * M[2] - M[4] * M[5];
+        M[2] = b1; M[5] = b2;
+        for (int k = 0; k < 6; ++k) Ms[k] = M[k];
+      }
+      // displacement-field draws
+      for (int i = tid; i < hw; i += kThreads) {
+        if (p.ux) {
+          F0[i] = p.ux[img * hw + i];
+        } else {
+          const uint64_t e = (uint64_t)(img * hw + i);
+          const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x81u, 0u);
+          F0[i] = -1.0 + 2.0 * (double)u01(r.x);
+        }
+      }
+      __syncthreads();
+      smooth(F0, F1, DX, s, p);
+      for (int i = tid; i < hw; i += kThreads) {
+        if (p.uy) {
+          F0[i] = p.uy[img * hw + i];
+        } else {
+          const uint64_t e = (uint64_t)(img * hw + i);
+          const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x82u, 0u);
+          F0[i] = -1.0 + 2.0 * (double)u01(r.x);
+        }
+      }
+      __syncthreads();
+      smooth(F0, F1, DY, s, p);
+      // affine warp into W
+      for (int px = tid; px < hw; px += kThreads) {
+        const int y = px / s.w, x = px - y * s.w;
+        const int adelta = (int)rint(Ms[0] * (double)x * 1024), bdelta = (int)rint(Ms[3] * (double)x * 1024);
+        const int X0 = (int)rint((Ms[1] * (double)y + Ms[2]) * 1024) + 16;
+        const int Y0 = (int)rint((Ms[4] * (double)y + Ms[5]) * 1024) + 16;
+        const int X = (X0 + adelta) >> 5, Y = (Y0 + bdelta) >> 5;
+        const int sx = X >> 5, sy = Y >> 5;
+        const float fx = __fmul_rn((float)(X & 31), 0.03125f), fy = __fmul_rn((float)(Y & 31), 0.03125f);
+        const float wx0 = __fsub_rn(1.0f, fx), wy0 = __fsub_rn(1.0f, fy);
+        const float w00 = __fmul_rn(wy0, wx0), w01 = __fmul_rn(wy0, fx), w10 = __fmul_rn(fy, wx0), w11 = __fmul_rn(fy, fx);
+        const int ya = reflect101(sy, s.h), yb = reflect101(sy + 1, s.h), xa = reflect101(sx, s.w), xb = reflect101(sx + 1, s.w);
+        const uint8_t* q00 = im + (ya * s.w + xa) * 3;
+        const uint8_t* q01 = im + (ya * s.w + xb) * 3;
+        const uint8_t* q10 = im + (yb * s.w + xa) * 3;
+        const uint8_t* q11 = im + (yb * s.w + xb) * 3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          float acc = __fmul_rn(T[q00[c]], w00);
+          acc = __fadd_rn(acc, __fmul_rn(T[q01[c]], w01));
+          acc = __fadd_rn(acc, __fmul_rn(T[q10[c]], w10));
+          acc = __fadd_rn(acc, __fmul_rn(T[q11[c]], w11));
+          W[px * 3 + c] = acc;
+        }
+      }
+      __syncthreads();
+      // bilinear resampling at (y + dy, x + dx)
+      for (int px = tid; px < hw; px += kThreads) {
+        const int y = px / s.w, x = px - y * s.w;
+        const double yy = (double)__fadd_rn((float)y, DY[px]), xx = (double)__fadd_rn((float)x, DX[px]);
+        const double fy0 = floor(yy), fx0 = floor(xx);
+        const double ty = yy - fy0, tx = xx - fx0;
+        const int y0 = (int)fy0, x0 = (int)fx0;
+        const int ya = reflect_half(y0, s.h), yb = reflect_half(y0 + 1, s.h), xa = reflect_half(x0, s.w), xb = reflect_half(x0 + 1, s.w);
+        const float* q00 = W + (ya * s.w + xa) * 3;
+        const float* q01 = W + (ya * s.w + xb) * 3;
+        const float* q10 = W + (yb * s.w + xa) * 3;
+        const float* q11 = W + (yb * s.w + xb) * 3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          double acc = ((double)q00[c] * (1 - ty)) * (1 - tx);
+          acc = acc + ((double)q01[c] * (1 - ty)) * tx;
+          acc = acc + ((double)q10[c] * ty) * (1 - tx);
+          acc = acc + ((double)q11[c] * ty) * tx;
+          float v = (float)acc;
+          v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+          om[px * 3 + c] = (uint8_t)__float2int_rz(__fmul_rn(v, 255.0f));
+        }
+      }
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// jpeg_compression
+// ------------------------------------------------------------------------------------------------
+struct JpegParams {
+  int16_t q[2][64];  // luma, chroma quantisation tables (natural order)
+};
+
+#define JFIX(x) ((int)((x) * 8192 + 0.5))
+constexpr int F_0_298631336 = JFIX(0.298631336), F_0_390180644 = JFIX(0.390180644), F_0_541196100 = JFIX(0.541196100),
+              F_0_765366865 = JFIX(0.765366865), F_0_899976223 = JFIX(0.899976223), F_1_175875602 = JFIX(1.175875602),
+              F_1_501321110 = JFIX(1.501321110), F_1_847759065 = JFIX(1.847759065), F_1_961570560 = JFIX(1.961570560),
+              F_2_053119869 = JFIX(2.053119869), F_2_562915447 = JFIX(2.562915447), F_3_072711026 = JFIX(3.072711026);
+
+__device__ __forceinline__ int descale(int x, int n) { return (x + (1 << (n - 1))) >> n; }
+
+// jfdctint.c, one 1-D pass.  PASS 1: even outputs << 2, odd DESCALE(.., 11); PASS 2: even DESCALE(.., 2), odd DESCALE(.., 15)
+template <int PASS>
+__device__ __forceinline__ void fdct8(int* d) {
+  const int tmp0 = d[0] + d[7], tmp7 = d[0] - d[7], tmp1 = d[1] + d[6], tmp6 = d[1] - d[6];
+  const int tmp2 = d[2] + d[5], tmp5 = d[2] - d[5], tmp3 = d[3] + d[4], tmp4 = d[3] - d[4];
+  const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  constexpr int SH = PASS == 1 ? 11 : 15;
+  d[0] = PASS == 1 ? (tmp10 + tmp11) << 2 : descale(tmp10 + tmp11, 2);
+  d[4] = PASS == 1 ? (tmp10 - tmp11) << 2 : descale(tmp10 - tmp11, 2);
+  int z1 = (tmp12 + tmp13) * F_0_541196100;
+  d[2] = descale(z1 + tmp13 * F_0_765366865, SH);
+  d[6] = descale(z1 + tmp12 * (-F_1_847759065), SH);
+  z1 = tmp4 + tmp7;
+  int z2 = tmp5 + tmp6, z3 = tmp4 + tmp6, z4 = tmp5 + tmp7;
+  const int z5 = (z3 + z4) * F_1_175875602;
+  const int t4 = tmp4 * F_0_298631336, t5 = tmp5 * F_2_053119869, t6 = tmp6 * F_3_072711026, t7 = tmp7 * F_1_501321110;
+  z1 *= -F_0_899976223; z2 *= -F_2_562915447;
+  z3 = z3 * (-F_1_961570560) + z5; z4 = z4 * (-F_0_390180644) + z5;
+  d[7] = descale(t4 + z1 + z3, SH); d[5] = descale(t5 + z2 + z4, SH);
+  d[3] = descale(t6 + z2 + z3, SH); d[1] = descale(t7 + z1 + z4, SH);
+}
+
+// jidctint.c, one 1-D pass.  PASS 1 (columns): DESCALE(.., 11); PASS 2 (rows): DESCALE(.., 18)
+template <int PASS>
+__device__ __forceinline__ void idct8(int* d) {
+  constexpr int SH = PASS == 1 ? 11 : 18;
+  int z2 = d[2], z3 = d[6];
+  int z1 = (z2 + z3) * F_0_541196100;
+  const int tmp2 = z1 + z3 * (-F_1_847759065), tmp3 = z1 + z2 * F_0_765366865;
+  z2 = d[0]; z3 = d[4];
+  const int tmp0 = (z2 + z3) << 13, tmp1 = (z2 - z3) << 13;
+  const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+  int t0 = d[7], t1 = d[5], t2 = d[3], t3 = d[1];
+  z1 = t0 + t3; z2 = t1 + t2; z3 = t0 + t2;
+  int z4 = t1 + t3;
+  const int z5 = (z3 + z4) * F_1_175875602;
+  t0 *= F_0_298631336; t1 *= F_2_053119869; t2 *= F_3_072711026; t3 *= F_1_501321110;
+  z1 *= -F_0_899976223; z2 *= -F_2_562915447;
+  z3 = z3 * (-F_1_961570560) + z5; z4 = z4 * (-F_0_390180644) + z5;
+  t0 += z1 + z3; t1 += z2 + z4; t2 += z2 + z3; t3 += z1 + z4;
+  d[0] = descale(tmp10 + t3, SH); d[7] = descale(tmp10 - t3, SH);
+  d[1] = descale(tmp11 + t2, SH); d[6] = descale(tmp11 - t2, SH);
+  d[2] = descale(tmp12 + t1, SH); d[5] = descale(tmp12 - t1, SH);
+  d[3] = descale(tmp13 + t0, SH); d[4] = descale(tmp13 - t0, SH);
+}
+
+struct OpCcJpeg : NoSpill {
+  using Params = JpegParams;
+  static constexpr int kThreads = 256;
+  // per image: three planes as int32 (Y: hw, Cb/Cr: hw/4 each)
+  static size_t per_image(const Shape& s) { return (size_t)s.h * s.w * 6; }
+  static size_t scratch_bytes(const Shape& s, int G) { return (size_t)G * per_image(s) + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t*, bool) {}
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int tid = threadIdx.x;
+    const int h = s.h, w = s.w, hw = h * w, ch = h >> 1, cw = w >> 1;
+    const int plane_words = hw + 2 * ch * cw;
+    int* planes = reinterpret_cast<int*>(scratch);
+    __syncthreads();
+    // ---- colour conversion + 4:2:0 downsample (one thread per 2x2 quad) ----
+    for (int i = tid; i < g * ch * cw; i += kThreads) {
+      const int j = i / (ch * cw), qd = i - j * ch * cw;
+      const int yc = qd / cw, xc = qd - yc * cw;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      int* Yp = planes + (size_t)j * plane_words;
+      int* Cb = Yp + hw;
+      int* Cr = Cb + ch * cw;
+      int sb = 0, sr = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int y = yc * 2 + (k >> 1), x = xc * 2 + (k & 1);
+        const uint8_t* q = im + (y * w + x) * 3;
+        const int r = q[0], gg = q[1], b = q[2];
+        Yp[y * w + x] = (19595 * r + 38470 * gg + 7471 * b + 32768) >> 16;
+        sb += (-11059 * r - 21709 * gg + 32768 * b + (128 << 16) + 32767) >> 16;
+        sr += (32768 * r - 27439 * gg - 5329 * b + (128 << 16) + 32767) >> 16;
+      }
+      const int bias = 1 + (xc & 1);
+      Cb[qd] = (sb + bias) >> 2;
+      Cr[qd] = (sr + bias) >> 2;
+    }
+    __syncthreads();
+    // ---- DCT round trip: 8 threads per block ----
+    const int ybx = w >> 3, yblocks = (h >> 3) * ybx, cbx = cw >> 3, cblocks = (ch >> 3) * cbx;
+    const int blocks_per_img = yblocks + 2 * cblocks;
+    const int lines = g * blocks_per_img * 8;
+    // pass A: forward rows
+    for (int i = tid; i < lines; i += kThreads) {
+      const int l = i & 7, bi = i >> 3;
+      const int j = bi / blocks_per_img;
+      int b = bi - j * blocks_per_img;
+      int* base; int stride;
+      int* Yp = planes + (size_t)j * plane_words;
+      if (b < yblocks) { base = Yp + ((b / ybx) * 8) * w + (b % ybx) * 8; stride = w; }
+      else { b -= yblocks; const int pl = b / cblocks; b -= pl * cblocks; base = Yp + hw + pl * ch * cw + ((b / cbx) * 8) * cw + (b % cbx) * 8; stride = cw; }
+      int d[8];
+      int* row = base + l * stride;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d[k] = row[k] - 128;
+      fdct8<1>(d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) row[k] = d[k];
+    }
+    __syncthreads();
+    // pass B: forward columns, quantise, dequantise, inverse columns
+    for (int i = tid; i < lines; i += kThreads) {
+      const int l = i & 7, bi = i >> 3;
+      const int j = bi / blocks_per_img;
+      int b = bi - j * blocks_per_img;
+      int* base; int stride; int tq = 0;
+      int* Yp = planes + (size_t)j * plane_words;
+      if (b < yblocks) { base = Yp + ((b / ybx) * 8) * w + (b % ybx) * 8; stride = w; }
+      else { tq = 1; b -= yblocks; const int pl = b / cblocks; b -= pl * cblocks; base = Yp + hw + pl * ch * cw + ((b / cbx) * 8) * cw + (b % cbx) * 8; stride = cw; }
+      int d[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d[k] = base[k * stride + l];
+      fdct8<2>(d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int qt = p.q[tq][k * 8 + l], qv = qt << 3;
+        int t = d[k];
+        if (t < 0) { t = -t; t += qv >> 1; t = t >= qv ? t / qv : 0; t = -t; }
+        else { t += qv >> 1; t = t >= qv ? t / qv : 0; }
+        d[k] = t * qt;
+      }
+      idct8<1>(d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) base[k * stride + l] = d[k];
+    }
+    __syncthreads();
+    // pass C: inverse rows, range limit
+    for (int i = tid; i < lines; i += kThreads) {
+      const int l = i & 7, bi = i >> 3;
+      const int j = bi / blocks_per_img;
+      int b = bi - j * blocks_per_img;
+      int* base; int stride;
+      int* Yp = planes + (size_t)j * plane_words;
+      if (b < yblocks) { base = Yp + ((b / ybx) * 8) * w + (b % ybx) * 8; stride = w; }
+      else { b -= yblocks; const int pl = b / cblocks; b -= pl * cblocks; base = Yp + hw + pl * ch * cw + ((b / cbx) * 8) * cw + (b % cbx) * 8; stride = cw; }
+      int d[8];
+      int* row = base + l * stride;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) d[k] = row[k];
+      idct8<2>(d);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { int v = d[k] + 128; row[k] = v < 0 ? 0 : (v > 255 ? 255 : v); }
+    }
+    __syncthreads();
+    // ---- fancy upsample + YCbCr -> RGB ----
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / w, x = px - y * w;
+      const int* Yp = planes + (size_t)j * plane_words;
+      const int* Cb = Yp + hw;
+      const int* Cr = Cb + ch * cw;
+      const int yc = y >> 1, xc = x >> 1;
+      const int yn = clampi((y & 1) ? yc + 1 : yc - 1, 0, ch - 1);
+      const int xn = clampi((x & 1) ? xc + 1 : xc - 1, 0, cw - 1);
+      const int bias = (x & 1) ? 7 : 8;
+      int cbv, crv;
+      {
+        const int a = Cb[yc * cw + xc] * 3 + Cb[yn * cw + xc], bq = Cb[yc * cw + xn] * 3 + Cb[yn * cw + xn];
+        cbv = ((a * 3 + bq + bias) >> 4) - 128;
+        const int a2 = Cr[yc * cw + xc] * 3 + Cr[yn * cw + xc], b2 = Cr[yc * cw + xn] * 3 + Cr[yn * cw + xn];
+        crv = ((a2 * 3 + b2 + bias) >> 4) - 128;
+      }
+      const int Y = Yp[px];
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+      o[0] = clip8(Y + ((91881 * crv + 32768) >> 16));
+      o[1] = clip8(Y + ((-22554 * cbv - 46802 * crv + 32768) >> 16));
+      o[2] = clip8(Y + ((116130 * cbv + 32768) >> 16));
+    }
+  }
+};
+
+}  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
+                                   const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
+                                   const double* uy_dev, double c2, uint64_t seed, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 1 && w > 1 && h <= 64 && w <= 64 && c == 3 && n >= 0, "elastic_transform takes (n,h<=64,w<=64,3) images");
+  IMGTX_CHECK_ARG(lw >= -1 && lw <= kMaxLw && (lw < 0 || weights_host), "Gaussian radius must be <= %d", kMaxLw);
+  IMGTX_CHECK_ARG((ux_dev == nullptr) == (uy_dev == nullptr), "give both displacement fields or none");
+  ElasticParams p;
+  memset(&p, 0, sizeof(p));
+  p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed;
+  for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
+  return launch_image_op<OpCcElastic>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 72 * 1024);
+}
+
+extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                const int32_t* qtables_host /* 2 x 64, natural order */, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && (h % 16) == 0 && (w % 16) == 0 && c == 3 && n >= 0,
+                  "jpeg_compression takes (n,h,w,3) images with h, w multiples of 16");
+  IMGTX_CHECK_ARG(qtables_host, "missing quantisation tables");
+  JpegParams p;
+  for (int t = 0; t < 2; ++t)
+    for (int i = 0; i < 64; ++i) {
+      const int v = qtables_host[t * 64 + i];
+      IMGTX_CHECK_ARG(v >= 1 && v <= 255, "quantiser out of baseline range");
+      p.q[t][i] = (int16_t)v;
+    }
+  return launch_image_op<OpCcJpeg>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 80 * 1024);
+}

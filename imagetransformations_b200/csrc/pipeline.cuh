@@ -141,12 +141,16 @@ struct StagedTuning {
 };
 StagedTuning staged_tuning();
 
+// extra_scratch: parameter-dependent shared memory on top of Op::scratch_bytes (tables sized at run time);
+// target_override > 0 replaces the tuned per-CTA shared-memory target (operators with large fixed tables).
 template <class Op>
 int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
-                    const typename Op::Params& p, cudaStream_t stream) {
+                    const typename Op::Params& p, cudaStream_t stream, size_t extra_scratch = 0,
+                    int target_override = 0) {
   if (n <= 0) return IMGTX_OK;
   IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
-  const StagedTuning tn = staged_tuning();
+  StagedTuning tn = staged_tuning();
+  if (target_override > 0) tn.target_smem = target_override;
   const int max_smem = max_smem_optin();
   bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);
   int G = 1, stages = tn.stages;
@@ -154,7 +158,7 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
   if (staged) {
     auto need = [&](int g, int st) {
       return (size_t)kBarBytes + align_up((size_t)g * s.in_bytes, 128) * st +
-             align_up((size_t)g * s.out_bytes, 128) * 2 + Op::scratch_bytes(s, g) + 128;
+             align_up((size_t)g * s.out_bytes, 128) * 2 + Op::scratch_bytes(s, g) + extra_scratch + 128;
     };
     while (stages > 2 && need(1, stages) > (size_t)tn.target_smem) --stages;
     if (need(1, stages) > (size_t)max_smem - 1024) {
@@ -176,14 +180,14 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
     return IMGTX_OK;
   }
   // direct mode
-  size_t scratch = Op::scratch_bytes_direct(s);
+  size_t scratch = Op::scratch_bytes_direct(s) + extra_scratch;
   uint8_t* gtmp = nullptr;
   size_t gtmp_per_cta = 0;
   int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 8);
   if (scratch > (size_t)max_smem - 1024) {
     // intermediate planes do not fit on chip: spill them to a stream-ordered global workspace
     gtmp_per_cta = align_up(Op::gtmp_bytes(s), 256);
-    scratch = Op::scratch_bytes_spilled(s);
+    scratch = Op::scratch_bytes_spilled(s) + extra_scratch;
     IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, gtmp_per_cta * grid, stream));
   }
   auto kern = direct_kernel<Op>;

@@ -177,6 +177,59 @@ int imgtx_noise_injected_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, i
 int imgtx_noise_philox_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double param,
                           uint64_t seed, imgtx_stream_t stream);
 
+/* ---- CIFAR-10-C-style corruption suite ------------------------------------------------------------ */
+/* The reference names the 15 corruption types (attacks/fgsm/cifar-10/reverse_fgsm_cifar10_corrupted.py:18-23) and
+   consumes them as (50000,32,32,3) uint8 severity-major files (fall_2025/TTA_transforms.py:16-26,
+   transformation.py:35-41); it has generator code for four of them only
+   (pipenline/cifar_image_transformations.py:39-77 -> imgtx_noise_injected_u8 / imgtx_pil_gaussian_blur_u8).  The entry
+   points below generate all 15 canonical types (specification: oracle/cifar_c.py).  Every random
+   input is either INJECTED (device array of the draws; parity mode) or, when its pointer is NULL, drawn on chip from
+   Philox4x32-10 keyed by (seed, image index, element) (throughput mode). */
+typedef enum {
+  IMGTX_CC_GAUSSIAN = 0,   /* p0 = sigma (on-chip mode); a = f64 (n,h,w,3) noise, already scaled */
+  IMGTX_CC_SHOT = 1,       /* p0 = c; a = int64 (n,h,w,3) Poisson counts */
+  IMGTX_CC_IMPULSE = 2,    /* p0 = amount; a, b = f64 (n,h,w,3) uniforms (flip, salt) */
+  IMGTX_CC_SPECKLE = 3,    /* p0 = sigma; a = f64 noise */
+  IMGTX_CC_BRIGHTNESS = 4, /* p0 = c (HSV value shift) */
+  IMGTX_CC_CONTRAST = 5,   /* p0 = c */
+  IMGTX_CC_FOG = 6,        /* p0 = c0, p1 = wibbledecay; a = f64 (n,h,w) plasma maps */
+  IMGTX_CC_FROST = 7       /* p0 = c0, p1 = c1; a = uint8 (n,h,w,3) frost crops (tex_n == 0) or a texture bank
+                              (tex_n, tex_h, tex_w, 3) cropped at random per image */
+} imgtx_cc_kind;
+int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0, double p1,
+                          const void* draws_a_dev, const void* draws_b_dev, uint64_t seed, int tex_n, int tex_h,
+                          int tex_w, imgtx_stream_t stream);
+/* defocus_blur: correlation with the sparse taps (dy, dx, weight) of the anti-aliased disk kernel, REFLECT_101, f64.
+   dydx_host: (ntaps, 2) int32; |offset| <= 2. */
+int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
+                        const int32_t* dydx_host, const double* weights_host, imgtx_stream_t stream);
+/* zoom_blur (any fixed linear map on x/255 in CSR form, applied in f32 in stored order). */
+int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+                    const int32_t* indices_dev, const float* weights_dev, int nnz, imgtx_stream_t stream);
+/* glass_blur: weights_host[0..lw] = scipy Gaussian taps (centre first); deltas_dev (n, iters, h-2, w-2, 2) int8 (dx, dy). */
+int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host, int lw,
+                      int iters, const int8_t* deltas_dev, uint64_t seed, imgtx_stream_t stream);
+/* motion_blur: k_host[width] one-sided Gaussian line weights; offsets_dev (n, width, 2) int32 (dx, dy), or NULL with the
+   angle drawn uniformly in [angle_lo, angle_hi] degrees. */
+int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width, const float* k_host,
+                       const int32_t* offsets_dev, double angle_lo, double angle_hi, uint64_t seed,
+                       imgtx_stream_t stream);
+/* snow: zoom_idx_host = [y0 (h), y1 (h), x0 (w), x1 (w)], zoom_t_host = [ty (h), tx (w)] (centre-zoom tables of the noise
+   layer); layer_dev (n,h,w) f64 normal(loc, scale) draws or NULL. */
+int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
+                     float one_minus_c6, const int32_t* zoom_idx_host, const float* zoom_t_host, int width,
+                     const float* k_host, const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
+                     double angle_lo, double angle_hi, uint64_t seed, imgtx_stream_t stream);
+/* elastic_transform: M_dev (n,6) f64 forward affine matrices (cv2.getAffineTransform) or NULL (corner jitter of amplitude
+   c2 drawn on chip); ux_dev / uy_dev (n,h,w) f64 uniform(-1,1) fields or NULL; weights_host[0..lw] Gaussian taps (lw = -1:
+   no smoothing). */
+int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
+                        const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
+                        const double* uy_dev, double c2, uint64_t seed, imgtx_stream_t stream);
+/* jpeg_compression: baseline round trip (4:2:0, islow DCT) with the two quantisation tables (natural order). */
+int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* qtables_host,
+                     imgtx_stream_t stream);
+
 /* ---- tensors ------------------------------------------------------------------------------ */
 /* T.ToTensor() [+ T.Normalize(mean, std) when mean_host/std_host != NULL]: u8 NHWC -> f32 NCHW.
    fall_2025/TENT_transform.py:56-59, fall_2025/TTA_transforms.py:62-65,
