@@ -69,6 +69,9 @@ _PROTOS = {
     "imgtx_noise_philox_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_uint64, _vp],
     "imgtx_cc_pointwise_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_double, _vp, _vp, C.c_uint64, _int,
                               _int, _int, _vp],
+    "imgtx_cc_noise_table_words": [_int, C.c_double],
+    "imgtx_cc_noise_table_host": [_int, C.c_double, _vp, _i64],
+    "imgtx_cc_noise_onchip_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _i64, C.c_uint64, _vp],
     "imgtx_cc_defocus_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_cc_csr_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _vp],
     "imgtx_cc_glass_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _int, _vp, C.c_uint64, _vp],
@@ -86,7 +89,8 @@ _PROTOS = {
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
 }
-_RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64}
+_RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64,
+             "imgtx_cc_noise_table_words": C.c_int64}
 
 
 def load():

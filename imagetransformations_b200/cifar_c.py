@@ -202,6 +202,29 @@ def affine_from_jitter(jitter: np.ndarray, size: int) -> np.ndarray:
     return out
 
 
+_alias_cache = {}
+
+
+def noise_alias_table_host(kind: int, p0: float):
+    """Walker alias table (int32 words, layout in csrc/cifar_c_fast.cuh) of the output-domain law of on-chip gaussian_noise
+    (p0 = sigma) or shot_noise (p0 = c); None when the parameter is outside the tabulated range."""
+    lib = L.load()
+    words = lib.imgtx_cc_noise_table_words(kind, float(p0))
+    if words <= 0:
+        return None
+    tab = np.empty(words, np.int32)
+    L.check(lib.imgtx_cc_noise_table_host(kind, float(p0), tab.ctypes.data, words))
+    return tab
+
+
+def noise_alias_table(kind: int, p0: float, device):
+    key = (kind, float(p0), str(device))
+    if key not in _alias_cache:
+        tab = noise_alias_table_host(kind, p0)
+        _alias_cache[key] = None if tab is None else torch.from_numpy(tab).to(device)
+    return _alias_cache[key]
+
+
 _frost_cache = {}
 
 
@@ -265,6 +288,12 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
 
     # NB every device staging tensor is bound to a local name until the call returns: a temporary would hand its block
     # back to the caching allocator before the next one is staged
+    if name in ("gaussian_noise", "shot_noise") and not d and (h * w * c) % 16 == 0:
+        kind = L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SHOT
+        tab = noise_alias_table(kind, float(p), dev)
+        if tab is not None:
+            L.check(lib.imgtx_cc_noise_onchip_u8(xp, op, n, h, w, c, kind, tab.data_ptr(), tab.numel(), seed, st))
+            return out
     if name in ("gaussian_noise", "speckle_noise"):
         point(L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SPECKLE, p, a=_dev(d.get("noise"), torch.float64, dev))
     elif name == "shot_noise":

@@ -1,0 +1,305 @@
+// CIFAR-10-C-style pointwise corruptions: the throughput forms (word-vectorised shared-memory passes).
+//
+// Everything here produces the same bytes as the reference formulas in cifar_c_point.cu (the f64 per-element forms,
+// which stay as the path for injected draws); what changes is how the work is organised:
+//   * a thread handles one 32-bit word (4 bytes) of the staged group per step, never a single byte;
+//   * a map u8 -> u8 that depends only on (value, per-image constants) is evaluated ONCE per (image, channel, value)
+//     into a byte LUT with the exact f64 formula and then applied with byte lookups (contrast);
+//   * on-chip noise is sampled in the OUTPUT domain.  The input has 256 values and the output has 256 values, so
+//     gaussian_noise is "add floor(255*sigma*Z)" (one discrete distribution) and shot_noise is a 256-row stochastic
+//     matrix; both are sampled with Walker/Vose alias tables built on the host in f64 (imgtx_cc_noise_table_host) and
+//     held in shared memory: one 32-bit Philox word, one multiply and one table lookup per element instead of
+//     Box-Muller / rejection sampling;
+//   * floor(v) of a double is taken with one round-down add of 2^52 instead of a conversion instruction.
+#pragma once
+#include "pipeline.cuh"
+#include "rng.cuh"
+
+namespace imgtx {
+
+// ---- alias-table layout (int32 words) -------------------------------------------------------------------------
+//   [0] magic 'ALT1'   [1] kind   [2] n_rows (1 = gaussian, 256 = shot)   [3] n_entries   [4] n_out (KO bytes)   [5..7] 0
+//   rows:    n_rows x 2 words: { entry base, (W << 16) | lo16 }          (W = number of outcomes, 1..512; lo16 = first
+//            delta as int16 (gaussian: outcome i is the delta lo16 + i) or the row's offset into `out` (shot))
+//   entries: n_entries words:  (threshold23 << 9) | alias9               (slot i is kept if frac23 < threshold)
+//   out:     n_out bytes (padded to a word): shot only, outcome index -> output byte
+constexpr int kAliasHeaderWords = 8;
+constexpr uint32_t kAliasMagic = 0x31544C41u;
+
+struct AliasView {
+  const uint2* rows;
+  const uint32_t* entries;
+  const uint8_t* out;
+};
+__device__ __forceinline__ AliasView alias_view(const uint8_t* scratch) {
+  const uint32_t* t = reinterpret_cast<const uint32_t*>(scratch);
+  AliasView v;
+  v.rows = reinterpret_cast<const uint2*>(t + kAliasHeaderWords);
+  v.entries = t + kAliasHeaderWords + 2 * t[2];
+  v.out = reinterpret_cast<const uint8_t*>(v.entries + t[3]);
+  return v;
+}
+// one outcome index from one 32-bit random word
+__device__ __forceinline__ uint32_t alias_draw(const uint32_t* entries, uint2 row, uint32_t r) {
+  const uint32_t W = row.y >> 16;
+  const uint64_t prod = (uint64_t)r * W;
+  const uint32_t slot = (uint32_t)(prod >> 32);
+  const uint32_t frac = (uint32_t)prod >> 9;
+  const uint32_t e = entries[row.x + slot];
+  return (frac < (e >> 9)) ? slot : (e & 511u);
+}
+
+struct CcFastParams {
+  int kind;
+  double p0, p1;
+  const void* a;
+  const void* b;
+  uint64_t seed;
+  int tex_n, tex_h, tex_w;
+  int table_words;  // alias table size (noise kinds)
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// gaussian_noise / shot_noise, on-chip draws
+// ---------------------------------------------------------------------------------------------------------------
+struct OpCcNoiseAlias : NoSpill {
+  using Params = CcFastParams;
+  static constexpr int kThreads = 512;
+  static size_t scratch_bytes(const Shape&, int) { return 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(p.b);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(scratch);
+    for (int i = threadIdx.x; i < p.table_words; i += kThreads) dst[i] = __ldg(src + i);
+    __syncthreads();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const AliasView av = alias_view(scratch);
+    const Philox rng(p.seed);
+    const int wpi = s.in_bytes >> 2;  // words per image (in_bytes % 16 == 0 in staged mode; checked at launch)
+    const int total = g * wpi;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+    const uint64_t word0 = (uint64_t)img0 * (uint64_t)wpi;
+    if (p.kind == IMGTX_CC_GAUSSIAN) {
+      const uint2 row = av.rows[0];
+      const int dlo = (int)(int16_t)(row.y & 0xFFFFu);  // outcomes are the contiguous deltas dlo, dlo+1, ...
+      for (int i = threadIdx.x; i < total; i += kThreads) {
+        const uint32_t w = s32[i];
+        const uint64_t gw = word0 + (uint64_t)i;
+        const uint4 r = rng((uint32_t)gw, (uint32_t)(gw >> 32), 0x11u, 0u);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+        uint32_t o = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int x = (int)((w >> (8 * b)) & 255u);
+          const int d = dlo + (int)alias_draw(av.entries, row, rr[b]);
+          const int v = min(max(x + d, 0), 255);
+          o |= (uint32_t)v << (8 * b);
+        }
+        d32[i] = o;
+      }
+    } else {  // IMGTX_CC_SHOT
+      for (int i = threadIdx.x; i < total; i += kThreads) {
+        const uint32_t w = s32[i];
+        const uint64_t gw = word0 + (uint64_t)i;
+        const uint4 r = rng((uint32_t)gw, (uint32_t)(gw >> 32), 0x21u, 0u);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+        uint32_t o = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const uint2 row = av.rows[(w >> (8 * b)) & 255u];
+          const uint32_t v = av.out[(row.y & 0xFFFFu) + alias_draw(av.entries, row, rr[b])];
+          o |= v << (8 * b);
+        }
+        d32[i] = o;
+      }
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// impulse_noise, on-chip draws: element flips iff r < amount * 2^32; the low bit of r (independent of that event to
+// 2^-31) chooses salt or pepper
+// ---------------------------------------------------------------------------------------------------------------
+struct OpCcImpulseFast : NoSpill, NoPrepare {
+  using Params = CcFastParams;
+  static constexpr int kThreads = 256;
+  static size_t scratch_bytes(const Shape&, int) { return 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t*, uint8_t*) {
+    const Philox rng(p.seed);
+    const int wpi = s.in_bytes >> 2;
+    const int total = g * wpi;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+    const uint64_t word0 = (uint64_t)img0 * (uint64_t)wpi;
+    const double t = p.p0 * 4294967296.0;
+    const uint32_t thr = t >= 4294967295.0 ? 0xFFFFFFFFu : (t <= 0.0 ? 0u : (uint32_t)t);
+    for (int i = threadIdx.x; i < total; i += kThreads) {
+      uint32_t w = s32[i];
+      const uint64_t gw = word0 + (uint64_t)i;
+      const uint4 r = rng((uint32_t)gw, (uint32_t)(gw >> 32), 0x31u, 0u);
+      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        if (rr[b] < thr) {
+          const uint32_t m = 255u << (8 * b);
+          w = (rr[b] & 1u) ? (w | m) : (w & ~m);
+        }
+      }
+      d32[i] = w;
+    }
+  }
+};
+
+// floor(v) for |v| < 2^31 as an int: one round-down add of 2^52 (the integer lands in the low mantissa word)
+__device__ __forceinline__ int floor_magic(double v) {
+  return __double2loint(__dadd_rd(v, 4503599627370496.0 + 2147483648.0)) ^ 0x80000000;
+}
+// np.uint8(np.clip(v, 0, 1) * 255): RN multiply is monotone, so clipping may follow it
+__device__ __forceinline__ uint32_t q255_fast(double v) {
+  // guard the magic add against values outside int range (injected draws may be anything finite or not)
+  v = fmin(fmax(v, -2.0), 2.0);
+  return (uint32_t)min(max(floor_magic(v * 255.0), 0), 255);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// contrast: per-image per-channel sums (one warp per image), a 3 x 256 byte LUT built with the f64 formula, lookups
+// ---------------------------------------------------------------------------------------------------------------
+struct OpCcContrastFast : NoSpill, NoPrepare {
+  using Params = CcFastParams;
+  static constexpr int kThreads = 256;
+  static constexpr int kWarps = kThreads / 32;
+  static size_t scratch_bytes(const Shape&, int) { return (size_t)kWarps * 768 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t* lut = scratch + warp * 768;
+    const int triples = s.in_bytes / 12;  // 4 pixels = 3 words (h*w % 4 == 0 checked at launch)
+    const int hw = s.h * s.w;
+    for (int j = warp; j < g; j += kWarps) {
+      const uint32_t* im = reinterpret_cast<const uint32_t*>(src + (size_t)j * s.in_bytes);
+      uint32_t* om = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes);
+      // byte sums per position of the 12-byte period, packed 2 x 16 bit (<= 255 * 2 per step: flushed every 64 steps)
+      uint32_t c0 = 0, c1 = 0, c2 = 0;
+      uint32_t e0 = 0, o0 = 0, e1 = 0, o1 = 0, e2 = 0, o2 = 0;
+      int since = 0;
+      for (int t = lane; t < triples; t += 32) {
+        const uint32_t w0 = im[3 * t], w1 = im[3 * t + 1], w2 = im[3 * t + 2];
+        e0 += w0 & 0x00FF00FFu; o0 += (w0 >> 8) & 0x00FF00FFu;
+        e1 += w1 & 0x00FF00FFu; o1 += (w1 >> 8) & 0x00FF00FFu;
+        e2 += w2 & 0x00FF00FFu; o2 += (w2 >> 8) & 0x00FF00FFu;
+        if (++since == 128 || t + 32 >= triples) {
+          // bytes of the period: w0 = r g b r | w1 = g b r g | w2 = b r g b
+          c0 += (e0 & 0xFFFFu) + (o0 >> 16) + (e1 >> 16) + (o2 & 0xFFFFu);
+          c1 += (o0 & 0xFFFFu) + (e1 & 0xFFFFu) + (o1 >> 16) + (e2 >> 16);
+          c2 += (e0 >> 16) + (o1 & 0xFFFFu) + (e2 & 0xFFFFu) + (o2 >> 16);
+          e0 = o0 = e1 = o1 = e2 = o2 = 0;
+          since = 0;
+        }
+      }
+      for (int o = 16; o > 0; o >>= 1) {
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        c2 += __shfl_xor_sync(0xffffffffu, c2, o);
+      }
+      const double m0 = (double)c0 / (double)hw / 255.0, m1 = (double)c1 / (double)hw / 255.0,
+                   m2 = (double)c2 / (double)hw / 255.0;
+      __syncwarp();
+      for (int e = lane; e < 256; e += 32) {
+        const double v = (double)e / 255.0;
+        lut[e] = (uint8_t)q255_fast((v - m0) * p.p0 + m0);
+        lut[256 + e] = (uint8_t)q255_fast((v - m1) * p.p0 + m1);
+        lut[512 + e] = (uint8_t)q255_fast((v - m2) * p.p0 + m2);
+      }
+      __syncwarp();
+      const uint8_t *l0 = lut, *l1 = lut + 256, *l2 = lut + 512;
+      for (int t = lane; t < triples; t += 32) {
+        const uint32_t w0 = im[3 * t], w1 = im[3 * t + 1], w2 = im[3 * t + 2];
+        om[3 * t] = l0[w0 & 255u] | (l1[(w0 >> 8) & 255u] << 8) | (l2[(w0 >> 16) & 255u] << 16) | (l0[w0 >> 24] << 24);
+        om[3 * t + 1] = l1[w1 & 255u] | (l2[(w1 >> 8) & 255u] << 8) | (l0[(w1 >> 16) & 255u] << 16) | (l1[w1 >> 24] << 24);
+        om[3 * t + 2] = l2[w2 & 255u] | (l0[(w2 >> 8) & 255u] << 8) | (l1[(w2 >> 16) & 255u] << 16) | (l2[w2 >> 24] << 24);
+      }
+      __syncwarp();
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// frost: clip(p0*x + p1*f, 0, 255) in f64 with the two products tabulated (256 doubles each)
+// ---------------------------------------------------------------------------------------------------------------
+struct OpCcFrostFast : NoSpill {
+  using Params = CcFastParams;
+  static constexpr int kThreads = 256;
+  static size_t scratch_bytes(const Shape&, int) { return 4096 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    double* A = reinterpret_cast<double*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) {
+      A[i] = p.p0 * (double)i;
+      A[256 + i] = p.p1 * (double)i;
+    }
+    __syncthreads();
+  }
+
+  __device__ static __forceinline__ uint32_t mix4(const double* A, uint32_t w, uint32_t f) {
+    uint32_t o = 0;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      // 0 <= v < 2^31 (the entry point only takes this path for 0 <= p0, p1 <= 1000)
+      const double v = A[(w >> (8 * b)) & 255u] + A[256 + ((f >> (8 * b)) & 255u)];
+      o |= (uint32_t)min(floor_magic(v), 255) << (8 * b);
+    }
+    return o;
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* A = reinterpret_cast<const double*>(scratch);
+    const int wpi = s.in_bytes >> 2;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+    if (p.tex_n == 0) {
+      // injected crops: same layout as the images, streamed from global memory
+      const uint32_t* fr = reinterpret_cast<const uint32_t*>(p.a) + (size_t)img0 * wpi;
+      const int total = g * wpi;
+      for (int i = threadIdx.x; i < total; i += kThreads) d32[i] = mix4(A, s32[i], __ldg(fr + i));
+      return;
+    }
+    const Philox rng(p.seed);
+    const int row_words = (s.w * 3) >> 2;  // words per image row (w % 4 == 0 checked at launch)
+    const uint8_t* bank = reinterpret_cast<const uint8_t*>(p.a);
+    for (int j = 0; j < g; ++j) {
+      const int64_t img = img0 + j;
+      const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x50u, 0u);
+      const int ti = (int)(r.x % (uint32_t)p.tex_n);
+      const int y0 = (int)(r.y % (uint32_t)(p.tex_h - s.h)), x0 = (int)(r.z % (uint32_t)(p.tex_w - s.w));
+      const uint8_t* tex = bank + ((size_t)ti * p.tex_h + y0) * p.tex_w * 3 + (size_t)x0 * 3;
+      const size_t tex_pitch = (size_t)p.tex_w * 3;
+      for (int i = threadIdx.x; i < wpi; i += kThreads) {
+        const int y = i / row_words, xw = i - y * row_words;
+        const uint8_t* q = tex + (size_t)y * tex_pitch + (size_t)xw * 4;
+        // unaligned 4-byte read of the texture row: two aligned words + funnel shift (the bank is padded by 4 bytes)
+        const uintptr_t a = reinterpret_cast<uintptr_t>(q);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t f = __funnelshift_r(__ldg(wp), __ldg(wp + 1), (uint32_t)(a & 3) * 8);
+        d32[j * wpi + i] = mix4(A, s32[j * wpi + i], f);
+      }
+    }
+  }
+};
+
+}  // namespace imgtx

@@ -16,7 +16,10 @@
 // Roofline: HBM, 2 B/element (+ 8 B/element of draws in parity mode); on-chip RNG modes are ALU-bound.
 #include "pipeline.cuh"
 #include "rng.cuh"
+#include "cifar_c_fast.cuh"
+#include <math.h>
 #include <string.h>
+#include <vector>
 
 namespace imgtx {
 
@@ -311,9 +314,171 @@ extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n,
     IMGTX_CHECK_ARG(draws_a_dev, "frost needs crops or a texture bank");
     if (tex_n > 0) IMGTX_CHECK_ARG(tex_h > h && tex_w > w, "texture smaller than the image");
   }
+  const Shape shp = make_shape(h, w, c, h, w);
+  const bool wordable = shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out);
+  if (wordable) {
+    CcFastParams f;
+    memset(&f, 0, sizeof(f));
+    f.kind = kind; f.p0 = p0; f.p1 = p1; f.a = draws_a_dev; f.b = draws_b_dev; f.seed = seed;
+    f.tex_n = kind == IMGTX_CC_FROST ? tex_n : 0; f.tex_h = tex_h; f.tex_w = tex_w;
+    if (kind == IMGTX_CC_IMPULSE && !draws_a_dev) return launch_image_op<OpCcImpulseFast>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && (int64_t)h * w * 255 < (1ll << 31))
+      return launch_image_op<OpCcContrastFast>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (kind == IMGTX_CC_FROST && w % 4 == 0 && p0 >= 0 && p1 >= 0 && p0 <= 1000 && p1 <= 1000 &&
+        (tex_n == 0 || ((reinterpret_cast<uintptr_t>(draws_a_dev) & 3u) == 0)))
+      return launch_image_op<OpCcFrostFast>(in, out, n, shp, f, (cudaStream_t)stream);
+  }
   CcPointParams p;
   memset(&p, 0, sizeof(p));
   p.kind = kind; p.p0 = p0; p.p1 = p1; p.a = draws_a_dev; p.b = draws_b_dev; p.seed = seed;
   p.tex_n = kind == IMGTX_CC_FROST ? tex_n : 0; p.tex_h = tex_h; p.tex_w = tex_w;
   return launch_image_op<OpCcPoint>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, extra);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// alias tables for the on-chip noise (host, f64)
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+
+// Walker/Vose alias table of a discrete distribution; entry = (threshold23 << 9) | alias9
+void vose(const std::vector<double>& pr, std::vector<uint32_t>& entries) {
+  const int W = (int)pr.size();
+  std::vector<double> q(W);
+  std::vector<int> alias(W), small, large;
+  double tot = 0;
+  for (double v : pr) tot += v;
+  for (int i = 0; i < W; ++i) {
+    q[i] = pr[i] / tot * W;
+    alias[i] = i;
+    (q[i] < 1.0 ? small : large).push_back(i);
+  }
+  while (!small.empty() && !large.empty()) {
+    const int s = small.back(); small.pop_back();
+    const int l = large.back();
+    alias[s] = l;
+    q[l] = (q[l] + q[s]) - 1.0;
+    if (q[l] < 1.0) { large.pop_back(); small.push_back(l); }
+  }
+  for (int i : large) { q[i] = 1.0; alias[i] = i; }
+  for (int i : small) { q[i] = 1.0; alias[i] = i; }   // round-off leftovers
+  for (int i = 0; i < W; ++i) {
+    double t = floor(q[i] * 8388608.0 + 0.5);
+    uint32_t thr = t >= 8388607.0 ? 8388607u : (t <= 0 ? 0u : (uint32_t)t);
+    int a = alias[i];
+    if (q[i] >= 1.0) a = i;  // "always keep": both branches give i
+    entries.push_back((thr << 9) | (uint32_t)a);
+  }
+}
+
+struct AliasTable {
+  std::vector<uint32_t> rows, entries;
+  std::vector<uint8_t> out;
+};
+
+// gaussian_noise: the increment of the output byte is floor(255*sigma*Z): P(d) = Phi((d+1)/s) - Phi(d/s), |d| <= 6.5 s
+bool build_gaussian(double sigma, AliasTable& t) {
+  const double s = sigma * 255.0;
+  if (!(s > 0)) return false;
+  const int K = (int)ceil(6.5 * s) + 1;
+  if (2 * K > 512) return false;
+  std::vector<double> pr(2 * K);
+  const double inv = 1.0 / (s * sqrt(2.0));
+  for (int d = 0; d < K; ++d) {
+    const double pd = 0.5 * (erfc(d * inv) - erfc((d + 1) * inv));
+    pr[K + d] = pd;        // delta d
+    pr[K - 1 - d] = pd;    // delta -d-1
+  }
+  t.rows = {0u, ((uint32_t)(2 * K) << 16) | (uint32_t)(uint16_t)(int16_t)(-K)};
+  vose(pr, t.entries);
+  return true;
+}
+
+// shot_noise: row x is the law of uint8(clip(Poisson(x/255*c)/c, 0, 1)*255); Poisson mass below 1e-10 is dropped
+bool build_shot(double c, AliasTable& t) {
+  if (!(c > 0)) return false;
+  for (int x = 0; x < 256; ++x) {
+    const double lam = (double)x / 255.0 * c;
+    std::vector<double> pr;
+    std::vector<uint8_t> ov;
+    auto outv = [&](long long k) {
+      double v = (double)k / c;
+      v = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
+      return (uint8_t)(int)(v * 255.0);
+    };
+    if (lam <= 0) {
+      pr.push_back(1.0); ov.push_back(outv(0));
+    } else {
+      const double ll = log(lam);
+      auto pmf = [&](long long k) { return exp((double)k * ll - lam - lgamma((double)k + 1.0)); };
+      long long mode = (long long)floor(lam), klo = mode, khi = mode;
+      while (klo > 0 && pmf(klo - 1) > 1e-10) --klo;
+      while (pmf(khi + 1) > 1e-10) ++khi;
+      for (long long k = klo; k <= khi; ++k) {
+        const uint8_t o = outv(k);
+        if (!ov.empty() && ov.back() == o) pr.back() += pmf(k);
+        else { ov.push_back(o); pr.push_back(pmf(k)); }
+      }
+    }
+    if (pr.size() > 512 || t.out.size() + ov.size() > 65535) return false;
+    t.rows.push_back((uint32_t)t.entries.size());
+    t.rows.push_back(((uint32_t)pr.size() << 16) | (uint32_t)t.out.size());
+    vose(pr, t.entries);
+    t.out.insert(t.out.end(), ov.begin(), ov.end());
+  }
+  return true;
+}
+
+bool build_table(int kind, double p0, std::vector<uint32_t>& words) {
+  AliasTable t;
+  const bool ok = kind == IMGTX_CC_GAUSSIAN ? build_gaussian(p0, t) : (kind == IMGTX_CC_SHOT ? build_shot(p0, t) : false);
+  if (!ok) return false;
+  while (t.out.size() % 4) t.out.push_back(0);
+  words.assign(kAliasHeaderWords, 0u);
+  words[0] = kAliasMagic; words[1] = (uint32_t)kind; words[2] = (uint32_t)(t.rows.size() / 2);
+  words[3] = (uint32_t)t.entries.size(); words[4] = (uint32_t)t.out.size();
+  words.insert(words.end(), t.rows.begin(), t.rows.end());
+  words.insert(words.end(), t.entries.begin(), t.entries.end());
+  const size_t base = words.size();
+  words.resize(base + t.out.size() / 4);
+  if (!t.out.empty()) memcpy(&words[base], t.out.data(), t.out.size());
+  return true;
+}
+
+}  // namespace
+
+extern "C" int64_t imgtx_cc_noise_table_words(int kind, double p0) {
+  std::vector<uint32_t> w;
+  return build_table(kind, p0, w) ? (int64_t)w.size() : 0;
+}
+
+extern "C" int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_host, int64_t capacity_words) {
+  std::vector<uint32_t> w;
+  IMGTX_CHECK_ARG(table_host != nullptr, "null table");
+  if (!build_table(kind, p0, w)) {
+    set_error("no alias table for kind %d with parameter %g (gaussian: 255*sigma <= 39; shot: <= 512 outcomes per value)", kind, p0);
+    return IMGTX_ERR_UNSUPPORTED;
+  }
+  IMGTX_CHECK_ARG((int64_t)w.size() <= capacity_words, "table needs %lld words", (long long)w.size());
+  memcpy(table_host, w.data(), w.size() * 4);
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
+                                        const int32_t* table_dev, int64_t table_words, uint64_t seed,
+                                        imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  IMGTX_CHECK_ARG(kind == IMGTX_CC_GAUSSIAN || kind == IMGTX_CC_SHOT, "alias-table noise is gaussian or shot");
+  IMGTX_CHECK_ARG(table_dev != nullptr && table_words > kAliasHeaderWords && aligned16(table_dev), "bad alias table");
+  const Shape shp = make_shape(h, w, c, h, w);
+  IMGTX_CHECK_ARG(shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out),
+                  "image bytes must be a multiple of 16 and the buffers 16-byte aligned");
+  const size_t tbytes = (size_t)table_words * 4;
+  IMGTX_CHECK_ARG(tbytes + 32 * 1024 <= (size_t)max_smem_optin(), "alias table does not fit in shared memory");
+  CcFastParams f;
+  memset(&f, 0, sizeof(f));
+  f.kind = kind; f.b = table_dev; f.seed = seed; f.table_words = (int)table_words;
+  // small table: default occupancy; large table (shot): one CTA per SM, the rest of shared memory stages images
+  int target = 0;
+  if (tbytes > 16 * 1024) target = (int)std::min<size_t>((size_t)max_smem_optin() - 2048, tbytes + 72 * 1024);
+  return launch_image_op<OpCcNoiseAlias>(in, out, n, shp, f, (cudaStream_t)stream, tbytes, target);
 }

@@ -199,6 +199,17 @@ typedef enum {
 int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0, double p1,
                           const void* draws_a_dev, const void* draws_b_dev, uint64_t seed, int tex_n, int tex_h,
                           int tex_w, imgtx_stream_t stream);
+/* On-chip gaussian_noise / shot_noise sampled in the OUTPUT domain.  Input and output are bytes, so gaussian_noise adds the
+   integer floor(255*sigma*Z) (one discrete law) and shot_noise is a 256-row stochastic matrix (row x = law of
+   uint8(clip(Poisson(x/255*c)/c)*255)); both are sampled with Walker alias tables: one 32-bit Philox word, one multiply and
+   one shared-memory lookup per element.  The table is built on the HOST in f64 (tail mass < 1e-10 dropped, thresholds
+   rounded to 2^-23) by imgtx_cc_noise_table_host, uploaded by the caller and passed as table_dev (16-byte aligned).
+   imgtx_cc_noise_table_words returns 0 when no table exists for the parameter (gaussian: 255*sigma > 39; shot: more than
+   512 outcomes per input value); imgtx_cc_pointwise_u8 with NULL draws is the general (slower) on-chip path. */
+int64_t imgtx_cc_noise_table_words(int kind, double p0);
+int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_host, int64_t capacity_words);
+int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
+                             const int32_t* table_dev, int64_t table_words, uint64_t seed, imgtx_stream_t stream);
 /* defocus_blur: correlation with the sparse taps (dy, dx, weight) of the anti-aliased disk kernel, REFLECT_101, f64.
    dydx_host: (ntaps, 2) int32; |offset| <= 2. */
 int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,

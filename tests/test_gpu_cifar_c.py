@@ -132,3 +132,52 @@ def test_write_and_read_back_cifar_c_layout(cuda, tmp_path):
         assert len(ds) == 10000
         img, lab = ds[7]
         assert int(lab) == 7 and np.array_equal(np.array(img), CC.contrast(x[7:8], CC.PARAMS["contrast"][sev - 1])[0])
+
+
+def test_onchip_noise_follows_the_oracle_law(cuda):
+    """On-chip gaussian / shot / impulse noise: the empirical law of the output byte given the input byte must match the law
+    the oracle formula defines (normal / Poisson draws pushed through oracle/cifar_c.py), bin by bin."""
+    from scipy import stats
+    C = _C()
+    n = 1500
+    N = n * 3072
+    for sev in (1, 3, 5):
+        sigma = CC.PARAMS["gaussian_noise"][sev - 1]
+        for xv in (0, 128, 250):
+            xd = torch.full((n, 32, 32, 3), xv, dtype=torch.uint8, device="cuda")
+            o = C.corrupt(xd, "gaussian_noise", sev, seed=sev * 10 + xv).cpu().numpy().ravel()
+            emp = np.bincount(o, minlength=256) / N
+            edges = (np.arange(257) - xv) / (255.0 * sigma)           # out = b  <=>  255*sigma*z in [b - x, b + 1 - x)
+            want = np.diff(stats.norm.cdf(edges))
+            want[0] += stats.norm.cdf(edges[0])
+            want[255] += 1 - stats.norm.cdf(edges[256])
+            tol = 5 * np.sqrt(want * (1 - want) / N) + 2e-6
+            assert (np.abs(emp - want) <= tol).all(), ("gaussian", sev, xv, np.abs(emp - want).max())
+        c = CC.PARAMS["shot_noise"][sev - 1]
+        for xv in (0, 3, 128, 255):
+            xd = torch.full((n, 32, 32, 3), xv, dtype=torch.uint8, device="cuda")
+            o = C.corrupt(xd, "shot_noise", sev, seed=sev * 10 + xv).cpu().numpy().ravel()
+            emp = np.bincount(o, minlength=256) / N
+            lam = xv / 255.0 * c
+            k = np.arange(0, int(lam + 12 * np.sqrt(lam + 1) + 30))
+            pk = stats.poisson.pmf(k, lam) if lam > 0 else (k == 0).astype(float)
+            ob = CC.shot_noise(np.zeros((1, 1, 1, len(k)), np.uint8), k.reshape(1, 1, 1, -1), c).ravel().astype(int)
+            want = np.zeros(256)
+            np.add.at(want, ob, pk)
+            tol = 5 * np.sqrt(want * (1 - want) / N) + 2e-6
+            assert (np.abs(emp - want) <= tol).all(), ("shot", sev, xv, np.abs(emp - want).max())
+        p = CC.PARAMS["impulse_noise"][sev - 1]
+        xd = torch.full((n, 32, 32, 3), 77, dtype=torch.uint8, device="cuda")
+        o = C.corrupt(xd, "impulse_noise", sev, seed=sev).cpu().numpy().ravel()
+        f0, f255 = (o == 0).mean(), (o == 255).mean()
+        assert abs(f0 - p / 2) < 5 * np.sqrt(p / 2 / N) and abs(f255 - p / 2) < 5 * np.sqrt(p / 2 / N)
+        assert ((o == 0) | (o == 255) | (o == 77)).all()
+    # neighbouring elements are independent (no stream reuse inside a word / across words / across images)
+    xd = torch.full((64, 32, 32, 3), 128, dtype=torch.uint8, device="cuda")
+    g = C.corrupt(xd, "gaussian_noise", 5, seed=99).cpu().numpy().astype(np.float64).reshape(64, -1)
+    g = g - g.mean()
+    for lag in (1, 2, 3, 4, 768, 1536):
+        r = (g[:, :-lag] * g[:, lag:]).mean() / g.var()
+        assert abs(r) < 0.01, (lag, r)
+    r = (g[:-1] * g[1:]).mean() / g.var()
+    assert abs(r) < 0.01
