@@ -15,8 +15,10 @@
 // Roofline: nominally HBM (2 B/element); the wide float stencils are ALU-bound (DESIGN.md has the per-pass numbers).
 #include "pipeline.cuh"
 #include "rng.cuh"
+#include "sweep_stencil.cuh"
 #include <math.h>
 #include <string.h>
+#include <algorithm>
 
 namespace imgtx {
 
@@ -69,6 +71,65 @@ struct OpCcDefocus : NoSpill {
       }
       uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
       o[0] = q255d(a0); o[1] = q255d(a1); o[2] = q255d(a2);
+    }
+  }
+};
+
+// Fast form for mirror-symmetric kernels (every canonical severity): fixed-point column sweep, exact f64 taps only for the
+// elements whose fixed-point value lies within 2^-11 LSB of an integer (sweep_stencil.cuh).
+struct DefocusFastParams {
+  DefocusParams exact;
+  uint32_t Wt[18];  // (R+1)^2 hi words then (R+1)^2 lo words, [|dy|][|dx|] at stride R+1
+  int R;
+};
+
+template <int R>
+struct OpCcDefocusFast : NoSpill {
+  using Params = DefocusFastParams;
+  static constexpr int kThreads = 192;
+  static constexpr int kMinBlocks = R == 2 ? 2 : 3;
+  static constexpr int kSeg = 2;  // row segments per column item
+  // scratch: T64 (2 KB) | tap weights f64 [32] | tap offsets (dy, dx) int8 [32][2]
+  static size_t scratch_bytes(const Shape&, int) { return 2048 + 256 + 64 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    double* tw = T + 256;
+    int8_t* td = reinterpret_cast<int8_t*>(tw + kMaxTaps);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
+    for (int i = threadIdx.x; i < p.exact.ntaps; i += kThreads) {
+      tw[i] = p.exact.w[i];
+      td[2 * i] = p.exact.dy[i];
+      td[2 * i + 1] = p.exact.dx[i];
+    }
+    __syncthreads();
+  }
+  __device__ static __noinline__ uint32_t exact_px(const uint8_t* im, const double* T, int ntaps, int h, int w, int y, int x,
+                                                   int ch) {
+    const double* tw = T + 256;
+    const int8_t* td = reinterpret_cast<const int8_t*>(tw + kMaxTaps);
+    double a = 0.0;
+    for (int k = 0; k < ntaps; ++k) {
+      const int yy = reflect101(y + td[2 * k], h), xx = reflect101(x + td[2 * k + 1], w);
+      a = a + T[im[(yy * w + xx) * 3 + ch]] * tw[k];
+    }
+    return q255d(a);
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    const int pgs = s.w >> 2, per_img = 3 * pgs * kSeg;
+    const int seg_rows = (s.h + kSeg - 1) / kSeg;
+    for (int item = threadIdx.x; item < g * per_img; item += kThreads) {
+      const int j = item / per_img, r = item - j * per_img;
+      const int seg = r / (3 * pgs), q = r - seg * 3 * pgs;
+      const int pg = q / 3, ch = q - pg * 3;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      uint8_t* om = dst + (size_t)j * s.out_bytes;
+      const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
+      auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.exact.ntaps, s.h, s.w, y, x, c); };
+      sweep_sym_stencil<R, BORDER_REFLECT101>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
     }
   }
 };
@@ -215,6 +276,152 @@ struct OpCcGlass : NoSpill {
     for (int j = 0; j < g; ++j) {
       uint8_t* im = dst + (size_t)j * s.out_bytes;
       gaussian<true>(im, im, tmp, T, s, p);
+    }
+  }
+};
+
+// Fast form (lw <= 2, w % 4 == 0): both Gaussians run as fixed-point column sweeps with the exact f64 two-pass evaluation
+// only inside the tie band (sweep_stencil.cuh); lw == 0 degenerates to a byte LUT.  The swap sweep permutes pixels without
+// looking at them, so it runs on a u16 index map (one warp per image, skew-2 wavefront, one Philox call per row and
+// iteration) and is applied afterwards as one gather.
+struct GlassFastParams {
+  GlassParams g;
+  uint32_t Wt[18];
+};
+
+template <int R>
+struct OpCcGlassFast : NoSpill {
+  using Params = GlassFastParams;
+  static constexpr int kThreads = 192;
+  static constexpr int kMinBlocks = R == 2 ? 2 : 3;
+  static constexpr int kSeg = 2;
+  // scratch: T64 (2 KB) | flat-window LUTs 2 x 256 B | per image: u16 index map
+  static size_t scratch_bytes(const Shape& s, int G) { return 2048 + 512 + (size_t)G * s.h * s.w * 2 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  // literal scipy two-pass evaluation at one element (axis y first, then x; mode 'nearest')
+  __device__ static __noinline__ uint32_t exact_px(const uint8_t* im, const double* T, const double* wt, int lw, int h,
+                                                   int w, int y, int x, int ch, bool FINAL) {
+    const int rowb = w * 3;
+    // flat window: the answer depends on the centre byte only
+    const uint8_t* flat = reinterpret_cast<const uint8_t*>(T + 256) + (FINAL ? 256 : 0);
+    const int c0 = im[y * rowb + x * 3 + ch];
+    bool is_flat = true;
+    for (int dy = -lw; dy <= lw && is_flat; ++dy)
+      for (int dx = -lw; dx <= lw; ++dx)
+        if (im[clampi(y + dy, 0, h - 1) * rowb + clampi(x + dx, 0, w - 1) * 3 + ch] != c0) { is_flat = false; break; }
+    if (is_flat) return flat[c0];
+    double col[5];
+    for (int dx = -lw; dx <= lw; ++dx) {
+      const int xb = clampi(x + dx, 0, w - 1) * 3 + ch;
+      double acc = T[im[y * rowb + xb]] * wt[0];
+      for (int k = lw; k >= 1; --k)
+        acc = acc + (T[im[clampi(y - k, 0, h - 1) * rowb + xb]] + T[im[clampi(y + k, 0, h - 1) * rowb + xb]]) * wt[k];
+      col[dx + lw] = acc;
+    }
+    double acc = col[lw] * wt[0];
+    for (int k = lw; k >= 1; --k) acc = acc + (col[lw - k] + col[lw + k]) * wt[k];
+    return FINAL ? q255d(acc) : (uint32_t)(int)(acc * 255.0);
+  }
+  __device__ static double flat_value(double t, const double* wt, int lw) {
+    double acc = t * wt[0];
+    for (int k = lw; k >= 1; --k) acc = acc + (t + t) * wt[k];
+    double a2 = acc * wt[0];
+    for (int k = lw; k >= 1; --k) a2 = a2 + (acc + acc) * wt[k];
+    return a2;
+  }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    uint8_t* flat = reinterpret_cast<uint8_t*>(T + 256);
+    for (int i = threadIdx.x; i < 256; i += kThreads) {
+      const double t = (double)i / 255.0;
+      T[i] = t;
+      const double a = flat_value(t, p.g.w, p.g.lw);
+      flat[i] = (uint8_t)(int)(a * 255.0);
+      flat[256 + i] = q255d(a);
+    }
+    __syncthreads();
+  }
+
+  __device__ static __forceinline__ void blur(const uint8_t* src, uint8_t* dst, int g, const Shape& s, const Params& p,
+                                             const double* T, bool FINAL) {
+    const uint8_t* flat = reinterpret_cast<const uint8_t*>(T + 256) + (FINAL ? 256 : 0);
+    if (R == 0) {
+      const int total = g * s.in_bytes;
+      for (int i = threadIdx.x; i < total; i += kThreads) dst[i] = flat[src[i]];
+      return;
+    }
+    const int pgs = s.w >> 2, per_img = 3 * pgs * kSeg;
+    const int seg_rows = (s.h + kSeg - 1) / kSeg;
+    for (int item = threadIdx.x; item < g * per_img; item += kThreads) {
+      const int j = item / per_img, r = item - j * per_img;
+      const int seg = r / (3 * pgs), q = r - seg * 3 * pgs;
+      const int pg = q / 3, ch = q - pg * 3;
+      const uint8_t* im = src + (size_t)j * s.in_bytes;
+      uint8_t* om = dst + (size_t)j * s.out_bytes;
+      const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
+      auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.g.w, p.g.lw, s.h, s.w, y, x, c, FINAL); };
+      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
+    }
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    uint16_t* maps = reinterpret_cast<uint16_t*>(scratch + 2048 + 512);
+    uint8_t* work = const_cast<uint8_t*>(src);  // the staged input buffer is ours until the next group is loaded
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int hw = s.h * s.w;
+    const int Rr = s.h - 2, Cc = s.w - 2;
+    const Philox rng(p.g.seed);
+    __syncthreads();
+    for (int pass = 0; pass < 2; ++pass) {
+      // Gaussian: pass 0 src -> dst (uint8(g*255)); pass 1 work -> dst (clip, *255).  One call site: one copy of the sweep.
+      blur(pass == 0 ? src : work, dst, g, s, p, T, pass == 1);
+      if (pass == 1) break;
+      // index map of the swap sweep (independent of the pixels)
+      for (int i = tid; i < g * hw; i += kThreads) maps[i] = (uint16_t)(i % hw);
+      __syncthreads();
+      for (int j = warp; j < g; j += kThreads >> 5) {
+        uint16_t* m = maps + (size_t)j * hw;
+        const int64_t img = img0 + j;
+        for (int it = 0; it < p.g.iters; ++it) {
+          const int h = s.h - 1 - lane;
+          uint32_t bx = 0, by = 0, bx2 = 0, by2 = 0;  // on-chip draws: one bit per swap, 64 swaps per row at most
+          if (!p.g.deltas && lane < Rr) {
+            const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
+            bx = r.x; by = r.y; bx2 = r.z; by2 = r.w;
+          }
+          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+            const int ci = t - 2 * lane;
+            if (lane < Rr && ci >= 0 && ci < Cc) {
+              const int w = s.w - 1 - ci;
+              int dx, dy;
+              if (p.g.deltas) {
+                const int8_t* d = p.g.deltas + ((((img * p.g.iters + it) * Rr + lane) * Cc + ci) << 1);
+                dx = d[0]; dy = d[1];
+              } else {
+                dx = -(int)(((ci < 32 ? bx : bx2) >> (ci & 31)) & 1u);
+                dy = -(int)(((ci < 32 ? by : by2) >> (ci & 31)) & 1u);
+              }
+              const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
+              const uint16_t ta = m[a], tb = m[b];
+              m[a] = tb; m[b] = ta;
+            }
+            __syncwarp();
+          }
+        }
+      }
+      __syncthreads();
+      // apply the map: work[p] = dst[map[p]]
+      for (int i = tid; i < g * hw; i += kThreads) {
+        const int j = i / hw, px = i - j * hw;
+        const uint8_t* a = dst + (size_t)j * s.out_bytes + (int)maps[i] * 3;
+        uint8_t* o = work + (size_t)j * s.in_bytes + px * 3;
+        o[0] = a[0]; o[1] = a[1]; o[2] = a[2];
+      }
+      __syncthreads();
     }
   }
 };
@@ -416,6 +623,41 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
     p.dx[i] = (int8_t)dydx_host[2 * i + 1];
     p.w[i] = weights_host[i];
   }
+  // mirror-symmetric kernel (K[dy][dx] == K[|dy|][|dx|], all weights >= 0) on a width that is a multiple of 4: fast form
+  {
+    double K[5][5];
+    memset(K, 0, sizeof(K));
+    int R = 0;
+    for (int i = 0; i < ntaps; ++i) {
+      K[p.dy[i] + 2][p.dx[i] + 2] += p.w[i];
+      R = std::max(R, std::max(abs((int)p.dy[i]), abs((int)p.dx[i])));
+    }
+    bool sym = (w % 4 == 0) && R >= 1;
+    for (int a = 0; a < 5 && sym; ++a)
+      for (int b = 0; b < 5; ++b)
+        if (K[a][b] != K[4 - a][b] || K[a][b] != K[a][4 - b]) sym = false;
+    if (sym) {
+      DefocusFastParams f;
+      memset(&f, 0, sizeof(f));
+      f.exact = p;
+      f.R = R;
+      double cw[9];
+      int mult[9];
+      memset(cw, 0, sizeof(cw));
+      for (int i = 0; i <= R; ++i)
+        for (int k = 0; k <= R; ++k) {
+          cw[i * (R + 1) + k] = K[2 + i][2 + k];
+          mult[i * (R + 1) + k] = (i ? 2 : 1) * (k ? 2 : 1);
+        }
+      if (fix_weights(cw, (R + 1) * (R + 1), mult, f.Wt)) {
+        // 4 images per group (192 items = 192 threads), three CTAs per SM
+        const Shape shp = make_shape(h, w, c, h, w);
+        const int target = 128 + 5 * 4 * shp.in_bytes + 4096;
+        if (R == 1) return launch_image_op<OpCcDefocusFast<1>>(in, out, n, shp, f, (cudaStream_t)stream, 0, target);
+        return launch_image_op<OpCcDefocusFast<2>>(in, out, n, shp, f, (cudaStream_t)stream, 0, target);
+      }
+    }
+  }
   return launch_image_op<OpCcDefocus>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
 }
 
@@ -439,7 +681,31 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   memset(&p, 0, sizeof(p));
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
-  return launch_image_op<OpCcGlass>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+  const Shape shp = make_shape(h, w, c, h, w);
+  if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out)) {
+    GlassFastParams f;
+    memset(&f, 0, sizeof(f));
+    f.g = p;
+    bool ok = true;
+    if (lw >= 1) {
+      double cw[9];
+      int mult[9];
+      for (int i = 0; i <= lw; ++i)
+        for (int k = 0; k <= lw; ++k) {
+          cw[i * (lw + 1) + k] = p.w[i] * p.w[k];
+          mult[i * (lw + 1) + k] = (i ? 2 : 1) * (k ? 2 : 1);
+        }
+      ok = fix_weights(cw, (lw + 1) * (lw + 1), mult, f.Wt);
+    }
+    if (ok) {
+      const int target = 128 + 5 * 4 * shp.in_bytes + 4 * h * w * 2 + 4096;  // 4 images per group
+      cudaStream_t st = (cudaStream_t)stream;
+      if (lw == 0) return launch_image_op<OpCcGlassFast<0>>(in, out, n, shp, f, st, 0, target);
+      if (lw == 1) return launch_image_op<OpCcGlassFast<1>>(in, out, n, shp, f, st, 0, target);
+      return launch_image_op<OpCcGlassFast<2>>(in, out, n, shp, f, st, 0, target);
+    }
+  }
+  return launch_image_op<OpCcGlass>(in, out, n, shp, p, (cudaStream_t)stream);
 }
 
 static int fill_motion(MotionParams& m, int width, const float* k_host, const int32_t* offsets_dev, double lo, double hi,

@@ -48,8 +48,14 @@ constexpr int kMaxStages = 8;
 
 __host__ __device__ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Ops may declare `static constexpr int kMinBlocks` (occupancy target handed to ptxas via __launch_bounds__).
+template <class Op, class = void>
+struct MinBlocks { static constexpr int value = 1; };
 template <class Op>
-__global__ void __launch_bounds__(Op::kThreads)
+struct MinBlocks<Op, decltype((void)Op::kMinBlocks)> { static constexpr int value = Op::kMinBlocks; };
+
+template <class Op>
+__global__ void __launch_bounds__(Op::kThreads, MinBlocks<Op>::value)
 staged_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, Shape s,
               typename Op::Params p, int G, int stages) {
   extern __shared__ __align__(128) uint8_t smem[];
