@@ -181,3 +181,22 @@ def test_onchip_noise_follows_the_oracle_law(cuda):
         assert abs(r) < 0.01, (lag, r)
     r = (g[:-1] * g[1:]).mean() / g.var()
     assert abs(r) < 0.01
+
+
+def test_sharded_equals_single_gpu(cuda):
+    """shards are independent, so cutting the batch (and its injected draws) at rank boundaries and
+    concatenating the results is bit-identical to one launch.  Ranks are emulated on one GPU (ragged world sizes too)."""
+    from imagetransformations_b200 import shard as S
+    C = _C()
+    x = imgs(9, 23)
+    for name, sev in (("gaussian_noise", 3), ("glass_blur", 4), ("elastic_transform", 2), ("snow", 5), ("fog", 2),
+                      ("motion_blur", 5), ("contrast", 2)):
+        d = CC.draw(name, sev, x, np.random.RandomState(7))
+        full = C.corrupt(torch.from_numpy(x).cuda(), name, sev, draws=d)
+        for ws in (2, 3, 8):
+            parts = []
+            for r in range(ws):
+                xs = S.shard(x, r, ws)
+                parts.append(C.corrupt(torch.from_numpy(xs).cuda(), name, sev, draws=S.shard_draws(d, len(x), r, ws)))
+            assert torch.equal(torch.cat(parts), full), (name, ws)
+            assert torch.equal(S.image_checksums(torch.cat(parts)), S.image_checksums(full))
