@@ -64,6 +64,7 @@ struct CcFastParams {
 // ---------------------------------------------------------------------------------------------------------------
 struct OpCcNoiseAlias : NoSpill {
   using Params = CcFastParams;
+  static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 512;
   static size_t scratch_bytes(const Shape&, int) { return 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
@@ -241,6 +242,7 @@ struct OpCcContrastFast : NoSpill, NoPrepare {
 // ---------------------------------------------------------------------------------------------------------------
 struct OpCcFrostFast : NoSpill {
   using Params = CcFastParams;
+  static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
   static size_t scratch_bytes(const Shape&, int) { return 4096 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
@@ -298,6 +300,136 @@ struct OpCcFrostFast : NoSpill {
         const uint32_t f = __funnelshift_r(__ldg(wp), __ldg(wp + 1), (uint32_t)(a & 3) * 8);
         d32[j * wpi + i] = mix4(A, s32[j * wpi + i], f);
       }
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// fog with the plasma fractal drawn on chip.  One warp owns an image from start to finish (no block-wide barrier): byte
+// maximum, diamond-square recursion on a float map in shared memory (four uniforms per Philox call), then
+// (x/255 + c0*plasma) * max / (max + c0) in float64 with the division replaced by a multiplication with 1/den and
+// replayed exactly only if the scaled value lies within 1e-9 of an integer.
+// ---------------------------------------------------------------------------------------------------------------
+struct OpCcFogFast : NoSpill {
+  using Params = CcFastParams;
+  static constexpr int kThreads = 128;
+  static constexpr int kStages = 2, kOutBufs = 1;   // latency-bound (serial recursion): spend shared memory on occupancy
+  static constexpr int kWarps = kThreads / 32;
+  static size_t scratch_bytes(const Shape& s, int) { return 2048 + (size_t)kWarps * s.h * s.w * 4 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
+    __syncthreads();
+  }
+
+  // make_cifar_c.plasma_fractal on an msz x msz float map (msz = 2^lg), one warp
+  __device__ static void plasma_warp(float* map, int lg, float decay, const Philox& rng, uint32_t img_lo, uint32_t img_hi) {
+    const int lane = threadIdx.x & 31, msz = 1 << lg, mask = msz - 1;
+    if (lane == 0) map[0] = 0.0f;
+    __syncwarp();
+    float wibble = 100.0f;
+    uint32_t stream = 0x70u;
+    for (int ls = lg; ls >= 1; --ls) {          // stepsize s = 2^ls, m = msz / s points per axis
+      const int sft = ls, half = 1 << (ls - 1), lm = lg - ls, m = 1 << lm;
+      // square centres
+      for (int q = lane; q < (m * m + 3) >> 2; q += 32) {
+        const uint4 r = rng(img_lo, img_hi, stream, (uint32_t)q);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = 4 * q + e;
+          if (i < m * m) {
+            const int a = i >> lm, b = i & (m - 1);
+            const int y0 = a << sft, y1 = ((a + 1) << sft) & mask, x0 = b << sft, x1 = ((b + 1) << sft) & mask;
+            const float acc = map[(y0 << lg) + x0] + map[(y1 << lg) + x0] + map[(y0 << lg) + x1] + map[(y1 << lg) + x1];
+            const float u = -wibble + 2.0f * wibble * u01(rr[e]);
+            map[((y0 + half) << lg) + x0 + half] = acc * 0.25f + wibble * u;
+          }
+        }
+      }
+      __syncwarp();
+      // edge midpoints: family 0 = (row a*s, col half + b*s), family 1 = (row half + a*s, col b*s); both read only corners
+      // and centres, so they do not depend on each other
+      for (int q = lane; q < (2 * m * m + 3) >> 2; q += 32) {
+        const uint4 r = rng(img_lo, img_hi, stream + 1u, (uint32_t)q);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = 4 * q + e;
+          if (i < 2 * m * m) {
+            const int fam = i >> (2 * lm), k = i & (m * m - 1);
+            const int a = k >> lm, b = k & (m - 1);
+            const float u = -wibble + 2.0f * wibble * u01(rr[e]);
+            auto dr = [&](int ii, int jj) { return map[((half + ((ii & (m - 1)) << sft)) << lg) + half + ((jj & (m - 1)) << sft)]; };
+            auto ul = [&](int ii, int jj) { return map[(((ii & (m - 1)) << sft) << lg) + ((jj & (m - 1)) << sft)]; };
+            if (fam == 0) {
+              const float acc = dr(a, b) + dr(a - 1, b) + ul(a, b) + ul(a, b + 1);
+              map[((a << sft) << lg) + half + (b << sft)] = acc * 0.25f + wibble * u;
+            } else {
+              const float acc = dr(a, b) + dr(a, b - 1) + ul(a, b) + ul(a + 1, b);
+              map[((half + (a << sft)) << lg) + (b << sft)] = acc * 0.25f + wibble * u;
+            }
+          }
+        }
+      }
+      __syncwarp();
+      stream += 2u;
+      wibble = __fdiv_rn(wibble, decay);
+    }
+    float mn = 3.0e38f, mx = -3.0e38f;
+    for (int i = lane; i < msz * msz; i += 32) { mn = fminf(mn, map[i]); mx = fmaxf(mx, map[i]); }
+    for (int o = 16; o > 0; o >>= 1) {
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    const float span = mx - mn;
+    for (int i = lane; i < msz * msz; i += 32) map[i] = __fdiv_rn(map[i] - mn, span);
+    __syncwarp();
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int hw = s.h * s.w;
+    float* map = reinterpret_cast<float*>(scratch + 2048) + (size_t)warp * hw;
+    const Philox rng(p.seed);
+    const int lg = 31 - __clz(s.h);
+    const int triples = s.in_bytes / 12;
+    for (int j = warp; j < g; j += kWarps) {
+      const int64_t img = img0 + j;
+      const uint32_t* im = reinterpret_cast<const uint32_t*>(src + (size_t)j * s.in_bytes);
+      uint32_t* om = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes);
+      uint32_t mx4 = 0;
+      for (int i = lane; i < (s.in_bytes >> 2); i += 32) mx4 = __vmaxu4(mx4, im[i]);
+      uint32_t mxb = max(max(mx4 & 255u, (mx4 >> 8) & 255u), max((mx4 >> 16) & 255u, mx4 >> 24));
+      for (int o = 16; o > 0; o >>= 1) mxb = max(mxb, __shfl_xor_sync(0xffffffffu, mxb, o));
+      const double mval = T[mxb], den = mval + p.p0, rden = 1.0 / den;
+      plasma_warp(map, lg, (float)p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32));
+      for (int t = lane; t < triples; t += 32) {   // 4 pixels = 3 words
+        const uint32_t w[3] = {im[3 * t], im[3 * t + 1], im[3 * t + 2]};
+        uint32_t o[3] = {0u, 0u, 0u};
+        double cpl[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) cpl[k] = p.p0 * (double)map[4 * t + k];
+#pragma unroll
+        for (int b = 0; b < 12; ++b) {
+          const uint32_t x = (w[b >> 2] >> (8 * (b & 3))) & 255u;
+          const double num = (T[x] + cpl[b / 3]) * mval;
+          const double q = (num * rden) * 255.0;
+          int r = floor_magic(q);
+          if (floor_magic(q - 1e-9) != floor_magic(q + 1e-9)) {   // exact replay: np.clip(num / den, 0, 1) * 255
+            double e = num / den;
+            e = e < 0.0 ? 0.0 : (e > 1.0 ? 1.0 : e);
+            r = (int)(e * 255.0);
+          }
+          o[b >> 2] |= (uint32_t)min(max(r, 0), 255) << (8 * (b & 3));
+        }
+        om[3 * t] = o[0]; om[3 * t + 1] = o[1]; om[3 * t + 2] = o[2];
+      }
+      __syncwarp();
     }
   }
 };

@@ -86,6 +86,7 @@ struct DefocusFastParams {
 template <int R>
 struct OpCcDefocusFast : NoSpill {
   using Params = DefocusFastParams;
+  static constexpr int kStages = 2, kOutBufs = 1;
   static constexpr int kThreads = 192;
   static constexpr int kMinBlocks = R == 2 ? 2 : 3;
   static constexpr int kSeg = 2;  // row segments per column item
@@ -146,7 +147,8 @@ struct CsrParams {
 
 struct OpCcCsr : NoSpill {
   using Params = CsrParams;
-  static constexpr int kThreads = 256;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 1024;  // the operator table (<= 100 KB) allows one CTA per SM: fill it with warps
   // scratch: T32 (1 KB) | indptr (P+1) i32 | packed taps nnz x {u16 idx... kept as int32 idx, f32 w} (extra_scratch)
   static size_t scratch_bytes(const Shape&, int) { return 1024 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
@@ -176,7 +178,7 @@ struct OpCcCsr : NoSpill {
       for (int k = ip[px]; k < k1; ++k) {
         const int2 t = taps[k];
         const float wt = __int_as_float(t.y);
-        const uint32_t rgb = load_rgb(im + t.x);
+        const uint32_t rgb = load_rgb(im, t.x);
         a0 = __fadd_rn(a0, __fmul_rn(T[rgb & 255u], wt));
         a1 = __fadd_rn(a1, __fmul_rn(T[(rgb >> 8) & 255u], wt));
         a2 = __fadd_rn(a2, __fmul_rn(T[(rgb >> 16) & 255u], wt));
@@ -292,6 +294,8 @@ struct GlassFastParams {
 template <int R>
 struct OpCcGlassFast : NoSpill {
   using Params = GlassFastParams;
+  static constexpr int kStages = R == 1 ? 3 : 2, kOutBufs = R == 1 ? 2 : 1;   // measured per radius
+  static constexpr bool kCifarCopy = R == 0;
   static constexpr int kThreads = 192;
   static constexpr int kMinBlocks = R == 2 ? 2 : 3;
   static constexpr int kSeg = 2;
@@ -484,7 +488,7 @@ struct OpCcMotion : NoSpill {
       float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
       for (int k = 0; k < p.width; ++k) {
         const int xx = clampi(x + oj[k * 2], 0, s.w - 1), yy = clampi(y + oj[k * 2 + 1], 0, s.h - 1);
-        const uint32_t rgb = load_rgb(im + (yy * s.w + xx) * 3);
+        const uint32_t rgb = load_rgb(im, (yy * s.w + xx) * 3);
         const float wt = p.k[k];
         a0 = __fadd_rn(a0, __fmul_rn((float)(rgb & 255u), wt));
         a1 = __fadd_rn(a1, __fmul_rn((float)((rgb >> 8) & 255u), wt));
@@ -606,6 +610,258 @@ struct OpCcSnow : NoSpill {
   }
 };
 
+// ------------------------------------------------------------------------------------------------
+// motion_blur / snow, throughput forms
+// ------------------------------------------------------------------------------------------------
+// The ordered float32 sum is kept literally (it IS the specification), but organised around words: the image is copied once
+// into an edge-replicated canvas that covers every tap offset of that image's line, so a tap is one unaligned 4-byte fetch
+// (two LDS + one funnel shift) serving four outputs, with no clamping and no index arithmetic in the inner loop; bytes
+// become floats with a byte-permute into the 2^23 mantissa instead of a conversion instruction.
+struct LineGeom {   // per image, in shared memory
+  int dxmin, dymin, pw, ph;   // canvas = image extended by the bounding box of the tap offsets
+  int off[kMaxLine];          // byte offset of tap i relative to the output position inside the canvas
+};
+
+// offsets (dx, dy) of one image -> LineGeom; one warp, CH = bytes per pixel
+template <int CH>
+__device__ __forceinline__ void make_line_geom(LineGeom* gm, const int* offs /* (width,2) dx,dy */, int width, int w, int h) {
+  const int lane = threadIdx.x & 31;
+  int x0 = 0, x1 = 0, y0 = 0, y1 = 0;
+  for (int i = lane; i < width; i += 32) {
+    x0 = min(x0, offs[2 * i]); x1 = max(x1, offs[2 * i]);
+    y0 = min(y0, offs[2 * i + 1]); y1 = max(y1, offs[2 * i + 1]);
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, o)); x1 = max(x1, __shfl_xor_sync(0xffffffffu, x1, o));
+    y0 = min(y0, __shfl_xor_sync(0xffffffffu, y0, o)); y1 = max(y1, __shfl_xor_sync(0xffffffffu, y1, o));
+  }
+  const int pw = w + (x1 - x0), ph = h + (y1 - y0);
+  if (lane == 0) { gm->dxmin = x0; gm->dymin = y0; gm->pw = pw; gm->ph = ph; }
+  for (int i = lane; i < width; i += 32) gm->off[i] = ((offs[2 * i + 1] - y0) * pw + (offs[2 * i] - x0)) * CH;
+}
+
+// edge-replicated canvas of one image (all threads of the CTA: `tid` of `nt`)
+template <int CH>
+__device__ __forceinline__ void fill_canvas(uint8_t* canvas, const uint8_t* im, const LineGeom& gm, int w, int h, int tid, int nt) {
+  const int npx = gm.pw * gm.ph;
+  for (int i = tid; i < npx; i += nt) {
+    const int py = i / gm.pw, px = i - py * gm.pw;
+    const int sy = min(max(py + gm.dymin, 0), h - 1), sx = min(max(px + gm.dxmin, 0), w - 1);
+    const uint8_t* q = im + (sy * w + sx) * CH;
+    uint8_t* o = canvas + i * CH;
+#pragma unroll
+    for (int c = 0; c < CH; ++c) o[c] = q[c];
+  }
+}
+
+// four consecutive output bytes starting at byte `ob` of an image with `rowb` bytes per row (rowb % 4 == 0)
+template <int CH>
+__device__ __forceinline__ uint32_t line_blur_word(const uint8_t* canvas, const LineGeom& gm, const float* k, int width,
+                                                   int rowb, int ob) {
+  const int y = ob / rowb, xb = ob - y * rowb;
+  const uint32_t* c32 = reinterpret_cast<const uint32_t*>(canvas);   // canvas is 16-byte aligned
+  const int base = y * gm.pw * CH + xb;
+  float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+  for (int i = 0; i < width; ++i) {
+    const int bo = base + gm.off[i];
+    const uint32_t* wp = c32 + (bo >> 2);
+    const uint32_t v = __funnelshift_r(wp[0], wp[1], (uint32_t)bo << 3);
+    const float wt = k[i];
+    a0 = __fadd_rn(a0, __fmul_rn(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440u)), 8388608.0f), wt));
+    a1 = __fadd_rn(a1, __fmul_rn(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7441u)), 8388608.0f), wt));
+    a2 = __fadd_rn(a2, __fmul_rn(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7442u)), 8388608.0f), wt));
+    a3 = __fadd_rn(a3, __fmul_rn(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7443u)), 8388608.0f), wt));
+  }
+  const int r0 = min(max(__float2int_rd(__fadd_rn(a0, 0.5f)), 0), 255), r1 = min(max(__float2int_rd(__fadd_rn(a1, 0.5f)), 0), 255);
+  const int r2 = min(max(__float2int_rd(__fadd_rn(a2, 0.5f)), 0), 255), r3 = min(max(__float2int_rd(__fadd_rn(a3, 0.5f)), 0), 255);
+  return (uint32_t)r0 | ((uint32_t)r1 << 8) | ((uint32_t)r2 << 16) | ((uint32_t)r3 << 24);
+}
+
+struct OpCcMotionFast : NoSpill {
+  using Params = MotionParams;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 256;
+  static constexpr int kMinBlocks = 2;
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) * 3 + 8, 16); }  // aux = line width
+  // weights f32[32] | per image: LineGeom + raw offsets (2 x 32 int) + canvas
+  __host__ __device__ static size_t per_image(const Shape& s) { return sizeof(LineGeom) + kMaxLine * 2 * 4 + canvas_bytes(s); }
+  static size_t scratch_bytes(const Shape& s, int G) { return 128 + (size_t)G * per_image(s) + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    float* k = reinterpret_cast<float*>(scratch);
+    for (int i = threadIdx.x; i < kMaxLine; i += kThreads) k[i] = i < p.width ? p.k[i] : 0.0f;
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const float* k = reinterpret_cast<const float*>(scratch);
+    const size_t pi = per_image(s);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const Philox rng(p.seed);
+    __syncthreads();
+    for (int j = warp; j < g; j += kThreads >> 5) {
+      uint8_t* base = scratch + 128 + (size_t)j * pi;
+      LineGeom* gm = reinterpret_cast<LineGeom*>(base);
+      int* raw = reinterpret_cast<int*>(base + sizeof(LineGeom));
+      const int64_t img = img0 + j;
+      if (p.offsets) {
+        for (int i = tid & 31; i < p.width * 2; i += 32) raw[i] = p.offsets[img * p.width * 2 + i];
+      } else {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x60u, 0u);
+        motion_offsets(p.lo + (p.hi - p.lo) * (double)u01(r.x), p.width, raw);
+      }
+      __syncwarp();
+      make_line_geom<3>(gm, raw, p.width, s.w, s.h);
+    }
+    __syncthreads();
+    for (int j = 0; j < g; ++j) {
+      uint8_t* base = scratch + 128 + (size_t)j * pi;
+      fill_canvas<3>(base + sizeof(LineGeom) + kMaxLine * 2 * 4, src + (size_t)j * s.in_bytes,
+                     *reinterpret_cast<const LineGeom*>(base), s.w, s.h, tid, kThreads);
+    }
+    __syncthreads();
+    const int wpi = s.in_bytes >> 2, rowb = s.w * 3;
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+    for (int i = tid; i < g * wpi; i += kThreads) {
+      const int j = i / wpi, wi = i - j * wpi;
+      const uint8_t* base = scratch + 128 + (size_t)j * pi;
+      const LineGeom& gm = *reinterpret_cast<const LineGeom*>(base);
+      const uint8_t* canvas = base + sizeof(LineGeom) + kMaxLine * 2 * 4;
+      // canvas origin: output (0,0) sits at canvas (-dymin, -dxmin); tap offsets are relative to (dymin, dxmin)
+      d32[(size_t)j * (s.out_bytes >> 2) + wi] = line_blur_word<3>(canvas, gm, k, p.width, rowb, wi * 4);
+    }
+  }
+};
+
+struct OpCcSnowFast : NoSpill {
+  using Params = SnowParams;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 256;
+  static constexpr int kMinBlocks = 2;
+  // header: T32[256] | k[32] | ty[64] tx[64] | y0 y1 x0 x1 [64 each, int]        = 1024 + 128 + 512 + 1024
+  static constexpr int kHeader = 1024 + 128 + 512 + 1024;
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) + 8, 16); }  // aux = line width
+  // per image: LineGeom + raw offsets + L0 f32[hw] + L1 u8[hw] + L2 u8[hw] + canvas
+  __host__ __device__ static size_t per_image(const Shape& s) {
+    return sizeof(LineGeom) + kMaxLine * 2 * 4 + align_up((size_t)s.h * s.w * 6, 16) + canvas_bytes(s);
+  }
+  static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * per_image(s) + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape& s, const Params& p, uint8_t* scratch, bool) {
+    float* T = reinterpret_cast<float*>(scratch);
+    float* k = T + 256;
+    float* ty = k + 32;
+    float* tx = ty + 64;
+    int* idx = reinterpret_cast<int*>(tx + 64);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    for (int i = threadIdx.x; i < kMaxLine; i += kThreads) k[i] = i < p.m.width ? p.m.k[i] : 0.0f;
+    for (int i = threadIdx.x; i < kSnowMax; i += kThreads) {
+      ty[i] = p.ty[i]; tx[i] = p.tx[i];
+      idx[i] = p.y0[i]; idx[64 + i] = p.y1[i]; idx[128 + i] = p.x0[i]; idx[192 + i] = p.x1[i];
+    }
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const float* T = reinterpret_cast<const float*>(scratch);
+    const float* k = T + 256;
+    const float* tyv = k + 32;
+    const float* txv = tyv + 64;
+    const int* idx = reinterpret_cast<const int*>(txv + 64);
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int hw = s.h * s.w;
+    const size_t pi = per_image(s);
+    const size_t o_l0 = sizeof(LineGeom) + kMaxLine * 2 * 4, o_l1 = o_l0 + (size_t)hw * 4, o_l2 = o_l1 + hw,
+                 o_cv = o_l0 + align_up((size_t)hw * 6, 16);
+    const Philox rng(p.m.seed);
+    __syncthreads();
+    // A. line geometry, one warp per image
+    for (int j = warp; j < g; j += kThreads >> 5) {
+      uint8_t* base = scratch + kHeader + (size_t)j * pi;
+      int* raw = reinterpret_cast<int*>(base + sizeof(LineGeom));
+      const int64_t img = img0 + j;
+      if (p.m.offsets) {
+        for (int i = tid & 31; i < p.m.width * 2; i += 32) raw[i] = p.m.offsets[img * p.m.width * 2 + i];
+      } else {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x62u, 0u);
+        motion_offsets(p.m.lo + (p.m.hi - p.m.lo) * (double)u01(r.x), p.m.width, raw);
+      }
+      __syncwarp();
+      make_line_geom<1>(reinterpret_cast<LineGeom*>(base), raw, p.m.width, s.w, s.h);
+    }
+    // B. noise layer (f64 draws cast to f32)
+    if (p.layer) {
+      for (int i = tid; i < g * hw; i += kThreads) {
+        const int j = i / hw, px = i - j * hw;
+        reinterpret_cast<float*>(scratch + kHeader + (size_t)j * pi + o_l0)[px] = (float)p.layer[(img0 + j) * hw + px];
+      }
+    } else {
+      for (int i = tid; i < (g * hw) >> 2; i += kThreads) {   // hw % 4 == 0 (checked at launch)
+        const int j = (4 * i) / hw, px = 4 * i - j * hw;
+        const uint64_t e = (uint64_t)((img0 + j) * hw + px) >> 2;
+        const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x61u, 1u);
+        float z0, z1, z2, z3;
+        box_muller(r.x, r.y, z0, z1);
+        box_muller(r.z, r.w, z2, z3);
+        float* L0 = reinterpret_cast<float*>(scratch + kHeader + (size_t)j * pi + o_l0) + px;
+        L0[0] = (float)(p.loc + p.scale * (double)z0); L0[1] = (float)(p.loc + p.scale * (double)z1);
+        L0[2] = (float)(p.loc + p.scale * (double)z2); L0[3] = (float)(p.loc + p.scale * (double)z3);
+      }
+    }
+    __syncthreads();
+    // C. centre zoom (order 1), threshold, 8 bits
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      const uint8_t* base = scratch + kHeader + (size_t)j * pi;
+      const float* L = reinterpret_cast<const float*>(base + o_l0);
+      const float ty = tyv[y], tx = txv[x], uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
+      const int ya = idx[y] * s.w, yb = idx[64 + y] * s.w, xa = idx[128 + x], xb = idx[192 + x];
+      float acc = __fmul_rn(__fmul_rn(L[ya + xa], uy), ux);
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[ya + xb], uy), tx));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[yb + xa], ty), ux));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[yb + xb], ty), tx));
+      if (acc < p.thresh) acc = 0.0f;
+      const_cast<uint8_t*>(base)[o_l1 + px] = q255f(acc);
+    }
+    __syncthreads();
+    // D. edge-replicated canvas of the 8-bit layer
+    for (int j = 0; j < g; ++j) {
+      uint8_t* base = scratch + kHeader + (size_t)j * pi;
+      fill_canvas<1>(base + o_cv, base + o_l1, *reinterpret_cast<const LineGeom*>(base), s.w, s.h, tid, kThreads);
+    }
+    __syncthreads();
+    // E. line blur, rounded back to 8 bits
+    const int wpl = hw >> 2;
+    for (int i = tid; i < g * wpl; i += kThreads) {
+      const int j = i / wpl, wi = i - j * wpl;
+      uint8_t* base = scratch + kHeader + (size_t)j * pi;
+      reinterpret_cast<uint32_t*>(base + o_l2)[wi] =
+          line_blur_word<1>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.width, s.w, wi * 4);
+    }
+    __syncthreads();
+    // F. blend with the whitened image, the layer and its 180-degree rotation
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const uint8_t* L = scratch + kHeader + (size_t)j * pi + o_l2;
+      const uint32_t rgb = load_rgb(src + (size_t)j * s.in_bytes, px * 3);
+      const float sl = T[L[px]], sr = T[L[hw - 1 - px]];
+      const float ch[3] = {T[rgb & 255u], T[(rgb >> 8) & 255u], T[(rgb >> 16) & 255u]};
+      float gray = __fadd_rn(__fmul_rn(ch[0], 0.299f), __fmul_rn(ch[1], 0.587f));
+      gray = __fadd_rn(gray, __fmul_rn(ch[2], 0.114f));
+      const float whit = __fadd_rn(__fmul_rn(gray, 1.5f), 0.5f);
+      uint8_t* o = dst + (size_t)j * s.out_bytes + px * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float mix = __fadd_rn(__fmul_rn(p.c6, ch[c]), __fmul_rn(p.one_minus_c6, fmaxf(ch[c], whit)));
+        o[c] = q255f(__fadd_rn(__fadd_rn(mix, sl), sr));
+      }
+    }
+  }
+};
+
 }  // namespace imgtx
 
 using namespace imgtx;
@@ -652,7 +908,7 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       if (fix_weights(cw, (R + 1) * (R + 1), mult, f.Wt)) {
         // 4 images per group (192 items = 192 threads), three CTAs per SM
         const Shape shp = make_shape(h, w, c, h, w);
-        const int target = 128 + 5 * 4 * shp.in_bytes + 4096;
+        const int target = 128 + 3 * 4 * shp.in_bytes + 4096;
         if (R == 1) return launch_image_op<OpCcDefocusFast<1>>(in, out, n, shp, f, (cudaStream_t)stream, 0, target);
         return launch_image_op<OpCcDefocusFast<2>>(in, out, n, shp, f, (cudaStream_t)stream, 0, target);
       }
@@ -698,7 +954,7 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
       ok = fix_weights(cw, (lw + 1) * (lw + 1), mult, f.Wt);
     }
     if (ok) {
-      const int target = 128 + 5 * 4 * shp.in_bytes + 4 * h * w * 2 + 4096;  // 4 images per group
+      const int target = 128 + (lw == 1 ? 5 : 3) * 4 * shp.in_bytes + 4 * h * w * 2 + 4096;  // 4 images per group
       cudaStream_t st = (cudaStream_t)stream;
       if (lw == 0) return launch_image_op<OpCcGlassFast<0>>(in, out, n, shp, f, st, 0, target);
       if (lw == 1) return launch_image_op<OpCcGlassFast<1>>(in, out, n, shp, f, st, 0, target);
@@ -725,7 +981,14 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
   MotionParams p;
   int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
   if (rc) return rc;
-  return launch_image_op<OpCcMotion>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+  Shape shp = make_shape(h, w, c, h, w);
+  shp.aux = width;
+  if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
+      OpCcMotionFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
+    const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcMotionFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
+    return launch_image_op<OpCcMotionFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
+  }
+  return launch_image_op<OpCcMotion>(in, out, n, shp, p, (cudaStream_t)stream);
 }
 
 extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
@@ -742,5 +1005,12 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
   p.thresh = thresh; p.c6 = c6; p.one_minus_c6 = one_minus_c6; p.loc = loc; p.scale = scale; p.layer = layer_dev;
   for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }
   for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
-  return launch_image_op<OpCcSnow>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+  Shape shp = make_shape(h, w, c, h, w);
+  shp.aux = width;
+  if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
+      OpCcSnowFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
+    const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcSnowFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
+    return launch_image_op<OpCcSnowFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
+  }
+  return launch_image_op<OpCcSnow>(in, out, n, shp, p, (cudaStream_t)stream);
 }

@@ -213,6 +213,7 @@ struct OpCcElastic : NoSpill {
 // image is kept as float64 so the bilinear stage converts nothing.
 struct OpCcElasticFast : NoSpill {
   using Params = ElasticParams;
+  static constexpr int kStages = 2, kOutBufs = 1;
   static constexpr int kThreads = 256;
   static constexpr int kMaxG = 8;
   static constexpr int kStrip = 8;
@@ -376,8 +377,8 @@ struct OpCcElasticFast : NoSpill {
         const float wx0 = __fsub_rn(1.0f, fx), wy0 = __fsub_rn(1.0f, fy);
         const float w00 = __fmul_rn(wy0, wx0), w01 = __fmul_rn(wy0, fx), w10 = __fmul_rn(fy, wx0), w11 = __fmul_rn(fy, fx);
         const int ya = refl101_any(sy, s.h), yb = refl101_any(sy + 1, s.h), xa = refl101_any(sx, s.w), xb = refl101_any(sx + 1, s.w);
-        const uint32_t c00 = load_rgb(im + (ya * s.w + xa) * 3), c01 = load_rgb(im + (ya * s.w + xb) * 3);
-        const uint32_t c10 = load_rgb(im + (yb * s.w + xa) * 3), c11 = load_rgb(im + (yb * s.w + xb) * 3);
+        const uint32_t c00 = load_rgb(im, (ya * s.w + xa) * 3), c01 = load_rgb(im, (ya * s.w + xb) * 3);
+        const uint32_t c10 = load_rgb(im, (yb * s.w + xa) * 3), c11 = load_rgb(im, (yb * s.w + xb) * 3);
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           float acc = __fmul_rn(T[(c00 >> (8 * c)) & 255u], w00);
@@ -481,6 +482,7 @@ __device__ __forceinline__ void idct8(int* d) {
 
 struct OpCcJpeg : NoSpill {
   using Params = JpegParams;
+  static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
   // per image: three planes as int32 (Y: hw, Cb/Cr: hw/4 each)
   static size_t per_image(const Shape& s) { return (size_t)s.h * s.w * 6; }
@@ -628,8 +630,8 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
   if (lw <= std::min(h, w) && (h * w) % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out)) {
-    // two images per group: 3 CTAs per SM
-    const int target = 128 + 5 * 2 * shp.in_bytes + (int)OpCcElasticFast::scratch_bytes(shp, 2) + 512;
+    // four CTAs per SM
+    const int target = 128 + 3 * 1 * shp.in_bytes + (int)OpCcElasticFast::scratch_bytes(shp, 1) + 512;  // one image per group
     return launch_image_op<OpCcElasticFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, target);
   }
   return launch_image_op<OpCcElastic>(in, out, n, shp, p, (cudaStream_t)stream, 0, 72 * 1024);

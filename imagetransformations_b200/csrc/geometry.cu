@@ -165,10 +165,10 @@ struct OpGeometry : NoSpill {
           uint32_t* ow32 = reinterpret_cast<uint32_t*>(om);
           for (int q4 = tid; q4 < (npix >> 2); q4 += kThreads) {
             const int4 o = offs4[q4];
-            const uint32_t p0 = o.x >= 0 ? load_rgb(im + o.x) : fill;
-            const uint32_t p1 = o.y >= 0 ? load_rgb(im + o.y) : fill;
-            const uint32_t p2 = o.z >= 0 ? load_rgb(im + o.z) : fill;
-            const uint32_t p3 = o.w >= 0 ? load_rgb(im + o.w) : fill;
+            const uint32_t p0 = o.x >= 0 ? load_rgb(im, o.x) : fill;
+            const uint32_t p1 = o.y >= 0 ? load_rgb(im, o.y) : fill;
+            const uint32_t p2 = o.z >= 0 ? load_rgb(im, o.z) : fill;
+            const uint32_t p3 = o.w >= 0 ? load_rgb(im, o.w) : fill;
             uint32_t w0, w1, w2;
             pack_rgb4(p0, p1, p2, p3, w0, w1, w2);
             ow32[q4 * 3] = w0; ow32[q4 * 3 + 1] = w1; ow32[q4 * 3 + 2] = w2;
