@@ -214,10 +214,15 @@ struct OpCcElastic : NoSpill {
 struct OpCcElasticFast : NoSpill {
   using Params = ElasticParams;
   static constexpr int kStages = 2, kOutBufs = 1;
+  static constexpr int kMinBlocks = 3;   // 256 threads x 3 CTAs: <= 80 registers
+  static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
   static constexpr int kMaxG = 8;
   static constexpr int kStrip = 8;
-  static size_t scratch_bytes(const Shape& s, int) { return 1024 + 256 + kMaxG * 48 + (size_t)s.h * s.w * (32 + 8) + 16; }
+  static constexpr int kQueue = 63;
+  static size_t scratch_bytes(const Shape& s, int) {
+    return 1024 + 256 + kMaxG * 48 + (size_t)s.h * s.w * (32 + 8) + (kQueue + 1) * 4 + 8 + (kThreads / 32) * (2 * kMaxLw + 1) * 8 + 16;
+  }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
     float* T = reinterpret_cast<float*>(scratch);
@@ -229,26 +234,34 @@ struct OpCcElasticFast : NoSpill {
   __device__ static __forceinline__ int refl_half(int i, int n) {  // one fold is enough when lw <= n
     return i < 0 ? -1 - i : (i >= n ? 2 * n - 1 - i : i);
   }
+  // in range / one fold: branch-free; further out (possible only with injected matrices or fields): the general routine
   __device__ static __forceinline__ int refl_half_any(int i, int n) {
-    return (unsigned)i < (unsigned)n ? i : reflect_half(i, n);
+    if (i < -n || i >= 2 * n) return reflect_half(i, n);
+    return i < 0 ? -1 - i : (i >= n ? 2 * n - 1 - i : i);
   }
   __device__ static __forceinline__ int refl101_any(int i, int n) {
-    return (unsigned)i < (unsigned)n ? i : reflect101(i, n);
+    if (i <= -n || i >= 2 * n - 1) return reflect101(i, n);
+    return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
   }
 
-  // 8 consecutive outputs of one line: out[o] = sum_k w[|k|] * in[refl(s0 + o + k)]
+  // 8 consecutive outputs of one line: out[o] = sum_k w[|k|] * in[refl(s0 + o + k)].  The 8-entry input window rotates
+  // through registers: at step u (unrolled by 8) logical entry o lives in physical slot (o + u) % 8, so no moves are needed.
   __device__ static __forceinline__ void strip(const double* line, int stride, int n, int s0, const double* Wg, int lw,
                                                double* acc) {
     double win[kStrip];
 #pragma unroll
     for (int o = 0; o < kStrip; ++o) { acc[o] = 0.0; win[o] = line[refl_half(s0 + o - lw, n) * stride]; }
-    for (int k = -lw; k <= lw; ++k) {
-      const double wk = Wg[k < 0 ? -k : k];
+    for (int k0 = -lw; k0 <= lw; k0 += kStrip) {
 #pragma unroll
-      for (int o = 0; o < kStrip; ++o) acc[o] = __fma_rn(wk, win[o], acc[o]);
+      for (int u = 0; u < kStrip; ++u) {
+        const int k = k0 + u;
+        if (k <= lw) {
+          const double wk = Wg[k < 0 ? -k : k];
 #pragma unroll
-      for (int o = 0; o < kStrip - 1; ++o) win[o] = win[o + 1];
-      win[kStrip - 1] = line[refl_half(s0 + kStrip + k, n) * stride];
+          for (int o = 0; o < kStrip; ++o) acc[o] = __fma_rn(wk, win[(o + u) % kStrip], acc[o]);
+          win[u % kStrip] = line[refl_half(s0 + kStrip + k, n) * stride];
+        }
+      }
     }
   }
 
@@ -278,6 +291,9 @@ struct OpCcElasticFast : NoSpill {
     double* F1 = F0 + 2 * hw;                                            // [2][hw] after the y pass
     float* DXY = reinterpret_cast<float*>(F1 + 2 * hw);                  // [2][hw] f32 displacements
     double* Wd = F0;                                                     // warped image, HWC f64 (aliases F0/F1: 24 <= 32 B/px)
+    int* qn = reinterpret_cast<int*>(DXY + 2 * hw);                      // replay queue: counter, entries, column scratch
+    int* queue = qn + 1;
+    double* qcols = reinterpret_cast<double*>(queue + kQueue);     // 1 + 63 ints = 256 bytes: stays 8-byte aligned
     const Philox rng(p.seed);
     const double tol = 4e-14 * fmax(1.0, fabs(p.alpha));
     __syncthreads();
@@ -318,6 +334,7 @@ struct OpCcElasticFast : NoSpill {
       const uint8_t* im = src + (size_t)j * s.in_bytes;
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       __syncthreads();  // previous image's bilinear stage has finished reading Wd / DXY
+      if (tid == 0) *qn = 0;
       // ---- raw fields: F0[0] = ux, F0[1] = uy ----
       if (p.ux) {
         for (int i = tid; i < 2 * hw; i += kThreads) F0[i] = i < hw ? p.ux[img * hw + i] : p.uy[img * hw + (i - hw)];
@@ -355,12 +372,37 @@ struct OpCcElasticFast : NoSpill {
           for (int o = 0; o < kStrip; ++o) {
             const int x = st * kStrip + o;
             if (x < s.w) {
-              double t = acc[o] * p.alpha;
-              float v = (float)t;
-              if ((float)(t - tol) != (float)(t + tol)) v = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
-              DXY[f * hw + y * s.w + x] = v;
+              const double t = acc[o] * p.alpha;
+              DXY[f * hw + y * s.w + x] = (float)t;
+              if ((float)(t - tol) != (float)(t + tol)) {     // too close to a float32 rounding boundary: replay literally
+                const int slot = atomicAdd(qn, 1);
+                if (slot < kQueue) queue[slot] = (f << 24) | (y << 12) | x;
+                else DXY[f * hw + y * s.w + x] = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
+              }
             }
           }
+        }
+        __syncthreads();
+        // replay queue: one warp per point, lanes over the 2*lw+1 columns (each in the literal order), lane 0 finishes
+        const int nq = min(*qn, kQueue);
+        for (int e = tid >> 5; e < nq; e += kThreads >> 5) {
+          const int f = queue[e] >> 24, y = (queue[e] >> 12) & 4095, x = queue[e] & 4095;
+          const double* F = F0 + f * hw;
+          double* col = qcols + (tid >> 5) * (2 * kMaxLw + 1);
+          for (int d = (tid & 31) - p.lw; d <= p.lw; d += 32) {
+            const int xx = refl_half(x + d, s.w);
+            double a = F[y * s.w + xx] * Wg[0];
+            for (int k = p.lw; k >= 1; --k)
+              a = a + (F[refl_half(y - k, s.h) * s.w + xx] + F[refl_half(y + k, s.h) * s.w + xx]) * Wg[k];
+            col[d + p.lw] = a;
+          }
+          __syncwarp();
+          if ((tid & 31) == 0) {
+            double a = col[p.lw] * Wg[0];
+            for (int k = p.lw; k >= 1; --k) a = a + (col[p.lw - k] + col[p.lw + k]) * Wg[k];
+            DXY[f * hw + y * s.w + x] = (float)(a * p.alpha);
+          }
+          __syncwarp();
         }
       }
       __syncthreads();
