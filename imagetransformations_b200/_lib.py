@@ -58,6 +58,7 @@ _PROTOS = {
     "imgtx_resample_table_host": [_int, _int, _int, _vp],
     "imgtx_resample_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _int, _int, _vp, _i64, _vp,
                           _i64, _int, _int, _int, _int, _vp],
+    "imgtx_resize_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
     "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _vp],
     "imgtx_pil_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
@@ -74,6 +75,7 @@ _PROTOS = {
     "imgtx_cc_noise_onchip_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _i64, C.c_uint64, _vp],
     "imgtx_cc_defocus_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_cc_csr_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _vp],
+    "imgtx_cc_csr_ell_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _int, _vp],
     "imgtx_cc_glass_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _int, _vp, C.c_uint64, _vp],
     "imgtx_cc_motion_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, C.c_double, C.c_double, C.c_uint64, _vp],
     "imgtx_cc_snow_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _f, _f, _vp, _vp, _int, _vp, _vp, _vp, C.c_double,

@@ -167,7 +167,7 @@ def zoom_operator(h: int, w: int, severity: int, device):
     np.add.at(indptr, nzr + 1, 1)
     indptr = np.cumsum(indptr).astype(np.int32)
     op = (torch.from_numpy(indptr).to(device), torch.from_numpy(nzc.astype(np.int32)).to(device),
-          torch.from_numpy(W[nzr, nzc].astype(np.float32)).to(device))
+          torch.from_numpy(W[nzr, nzc].astype(np.float32)).to(device), int(np.diff(indptr).max()))
     _zoom_cache[key] = op
     return op
 
@@ -316,8 +316,9 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
         dydx, wts = disk_taps(p[0], p[1])
         L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, st))
     elif name == "zoom_blur":
-        ip, idx, wt = zoom_operator(h, w, severity, dev)
-        L.check(lib.imgtx_cc_csr_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(), st))
+        ip, idx, wt, max_row = zoom_operator(h, w, severity, dev)
+        L.check(lib.imgtx_cc_csr_ell_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(),
+                                        max_row, st))
     elif name == "glass_blur":
         wts = gaussian_taps(p[0], 4.0)
         deltas = _dev(d.get("deltas"), torch.int8, dev)
@@ -351,8 +352,14 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
         L.check(lib.imgtx_cc_elastic_u8(xp, op, n, h, w, c, float(alpha), wts.ctypes.data, lw, _ptr(M), _ptr(ux), _ptr(uy),
                                         float(c2), seed, st))
     elif name == "pixelate":
-        small = B.resample(x, (int(w * p), int(h * p)), L.FILTER_BOX)
-        B.resample(small, (w, h), L.FILTER_BOX, out=out)
+        sw, sh = int(w * p), int(h * p)
+        if sw == w or sh == h:     # Pillow skips a pass whose size does not change: use the general path
+            small = B.resample(x, (sw, sh), L.FILTER_BOX)
+            B.resample(small, (w, h), L.FILTER_BOX, out=out)
+        else:
+            t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
+            L.check(lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
+                                              t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(), t[3].numel(), st))
     elif name == "jpeg_compression":
         qt = jpeg_qtables(p)
         L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, st))

@@ -189,6 +189,86 @@ struct OpCcCsr : NoSpill {
   }
 };
 
+// Throughput form.  The gather is shared-memory-bandwidth bound, so everything is laid out for conflict-free access: the
+// operator is re-packed per CTA into ELL form [tap][pixel] (u16 source index, f32 weight; short rows padded with zero
+// weights, which leave the ordered float32 sum bit-identical), the group is converted once into PLANAR float images (one
+// LUT lookup per byte instead of one per tap), and a warp owns one output row with lanes over x, so tap loads are
+// consecutive words and source reads are near-consecutive.
+struct CsrEllParams {
+  CsrParams csr;
+  int max_row;   // taps in the longest row (ELL height)
+};
+
+struct OpCcCsrEll : NoSpill {
+  using Params = CsrEllParams;
+  static constexpr int kThreads = 1024;
+  static constexpr int kStages = 2, kOutBufs = 1;
+  static constexpr bool kCifarCopy = true;
+  // scratch: T32 (1 KB) | ELL idx u16 [max_row][P] | ELL w f32 [max_row][P] | per image 3 float planes   (aux = table bytes)
+  __host__ __device__ static size_t table_bytes(int P, int max_row) {
+    return 1024 + align_up((size_t)max_row * P * 2, 16) + align_up((size_t)max_row * P * 4, 16);
+  }
+  static size_t scratch_bytes(const Shape& s, int G) { return (size_t)s.aux + (size_t)G * s.in_bytes * 4 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape& s, const Params& p, uint8_t* scratch, bool) {
+    const int P = s.h * s.w, tid = threadIdx.x;
+    float* T = reinterpret_cast<float*>(scratch);
+    uint16_t* eidx = reinterpret_cast<uint16_t*>(scratch + 1024);
+    float* ew = reinterpret_cast<float*>(scratch + 1024 + align_up((size_t)p.max_row * P * 2, 16));
+    for (int i = tid; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    for (int px = tid; px < P; px += kThreads) {
+      const int k0 = p.csr.indptr[px], n = min(p.csr.indptr[px + 1] - k0, p.max_row);
+      for (int k = 0; k < p.max_row; ++k) {
+        eidx[k * P + px] = k < n ? (uint16_t)p.csr.indices[k0 + k] : (uint16_t)px;
+        ew[k * P + px] = k < n ? p.csr.weights[k0 + k] : 0.0f;
+      }
+    }
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int P = s.h * s.w, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const float* T = reinterpret_cast<const float*>(scratch);
+    const uint16_t* eidx = reinterpret_cast<const uint16_t*>(scratch + 1024);
+    const float* ew = reinterpret_cast<const float*>(scratch + 1024 + align_up((size_t)p.max_row * P * 2, 16));
+    float* F = reinterpret_cast<float*>(scratch + s.aux);   // [g][3][P]
+    __syncthreads();
+    // HWC bytes -> planar floats, 4 pixels (3 words) per step
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    const int quads = P >> 2;   // P % 4 == 0 (checked at launch)
+    for (int i = tid; i < g * quads; i += kThreads) {
+      const int j = i / quads, q = i - j * quads;
+      const uint32_t* w = s32 + (size_t)j * (s.in_bytes >> 2) + 3 * q;
+      const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+      float* f = F + (size_t)j * 3 * P + 4 * q;
+      *reinterpret_cast<float4*>(f) = make_float4(T[w0 & 255u], T[w0 >> 24], T[(w1 >> 16) & 255u], T[(w2 >> 8) & 255u]);
+      *reinterpret_cast<float4*>(f + P) = make_float4(T[(w0 >> 8) & 255u], T[w1 & 255u], T[w1 >> 24], T[(w2 >> 16) & 255u]);
+      *reinterpret_cast<float4*>(f + 2 * P) = make_float4(T[(w0 >> 16) & 255u], T[(w1 >> 8) & 255u], T[w2 & 255u], T[w2 >> 24]);
+    }
+    __syncthreads();
+    // one warp per output row
+    for (int r = warp; r < g * s.h; r += kThreads >> 5) {
+      const int j = r / s.h, y = r - j * s.h;
+      const float* f0 = F + (size_t)j * 3 * P;
+      uint8_t* orow = dst + (size_t)j * s.out_bytes + (size_t)y * s.w * 3;
+      for (int x = lane; x < s.w; x += 32) {
+        const int px = y * s.w + x;
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+        for (int k = 0; k < p.max_row; ++k) {
+          const int si = eidx[k * P + px];
+          const float wt = ew[k * P + px];
+          a0 = __fadd_rn(a0, __fmul_rn(f0[si], wt));
+          a1 = __fadd_rn(a1, __fmul_rn(f0[P + si], wt));
+          a2 = __fadd_rn(a2, __fmul_rn(f0[2 * P + si], wt));
+        }
+        uint8_t* o = orow + x * 3;
+        o[0] = q255f(a0); o[1] = q255f(a1); o[2] = q255f(a2);
+      }
+    }
+  }
+};
+
 // ------------------------------------------------------------------------------------------------
 // glass_blur
 // ------------------------------------------------------------------------------------------------
@@ -643,14 +723,17 @@ __device__ __forceinline__ void make_line_geom(LineGeom* gm, const int* offs /* 
 // edge-replicated canvas of one image (all threads of the CTA: `tid` of `nt`)
 template <int CH>
 __device__ __forceinline__ void fill_canvas(uint8_t* canvas, const uint8_t* im, const LineGeom& gm, int w, int h, int tid, int nt) {
-  const int npx = gm.pw * gm.ph;
-  for (int i = tid; i < npx; i += nt) {
-    const int py = i / gm.pw, px = i - py * gm.pw;
-    const int sy = min(max(py + gm.dymin, 0), h - 1), sx = min(max(px + gm.dxmin, 0), w - 1);
-    const uint8_t* q = im + (sy * w + sx) * CH;
-    uint8_t* o = canvas + i * CH;
+  // one warp per canvas row, lanes over x (no division by the per-image canvas width)
+  const int lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+  for (int py = warp; py < gm.ph; py += nw) {
+    const int sy = min(max(py + gm.dymin, 0), h - 1);
+    for (int px = lane; px < gm.pw; px += 32) {
+      const int sx = min(max(px + gm.dxmin, 0), w - 1);
+      const uint8_t* q = im + (sy * w + sx) * CH;
+      uint8_t* o = canvas + (py * gm.pw + px) * CH;
 #pragma unroll
-    for (int c = 0; c < CH; ++c) o[c] = q[c];
+      for (int c = 0; c < CH; ++c) o[c] = q[c];
+    }
   }
 }
 
@@ -927,6 +1010,26 @@ extern "C" int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h
   IMGTX_CHECK_ARG(extra + 64 * 1024 <= (size_t)max_smem_optin(), "operator too large for shared memory (%d taps)", nnz);
   return launch_image_op<OpCcCsr>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, extra,
                                   (int)extra + 64 * 1024);
+}
+
+extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+                                   const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
+                                   imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0 && max_row_taps > 0, "missing operator");
+  Shape shp = make_shape(h, w, c, h, w);
+  const size_t tb = OpCcCsrEll::table_bytes(h * w, max_row_taps);
+  shp.aux = (int)tb;
+  int G = 4;   // float planes of G images + shallow ring next to the ELL table: one CTA of 32 warps per SM
+  auto need = [&](int g) { return 128 + 3 * (size_t)g * shp.in_bytes + OpCcCsrEll::scratch_bytes(shp, g) + 512; };
+  while (G > 1 && need(G) > (size_t)max_smem_optin() - 1024) --G;
+  if ((h * w) % 4 != 0 || h * w > 65535 || shp.in_bytes % 16 != 0 || !aligned16(in) || !aligned16(out) ||
+      need(G) > (size_t)max_smem_optin() - 1024)
+    return imgtx_cc_csr_u8(in, out, n, h, w, c, indptr_dev, indices_dev, weights_dev, nnz, stream);
+  CsrEllParams p;
+  p.csr.indptr = indptr_dev; p.csr.indices = indices_dev; p.csr.weights = weights_dev; p.csr.nnz = nnz;
+  p.max_row = max_row_taps;
+  return launch_image_op<OpCcCsrEll>(in, out, n, shp, p, (cudaStream_t)stream, 0, (int)need(G));
 }
 
 extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,

@@ -13,6 +13,7 @@
 #include <math.h>
 #include <string.h>
 #include <vector>
+#include <algorithm>
 
 namespace imgtx {
 
@@ -136,6 +137,78 @@ struct OpResample {
       }
       __syncthreads();
     }
+  }
+};
+
+// ---- two chained resizes in one launch (CIFAR-10-C pixelate: BOX down to (sw, sh), BOX back up) -----------------------
+// Four Q22 passes (h, v, h, v) with uint8 intermediates exactly like two Image.resize calls, but the intermediates never
+// leave shared memory and every pass is flattened over all images of the group (4 barriers per group, not 6 per image).
+struct ChainParams {
+  const int32_t* tab[4];   // device tables: h1 (w -> sw), v1 (h -> sh), h2 (sw -> w), v2 (sh -> h)
+  int words[4];
+  int sw, sh;
+};
+
+struct OpResizeChain : NoSpill {
+  using Params = ChainParams;
+  static constexpr int kThreads = 256;
+  static constexpr int kStages = 2, kOutBufs = 1;
+  // scratch: tables | per image two ping-pong planes of max(h,sh) x max(w,sw) x 3 bytes
+  __host__ __device__ static size_t plane_bytes(const Shape& s) { return align_up((size_t)s.h * s.w * 3 + 4, 16); }
+  static size_t scratch_bytes(const Shape& s, int G) { return (size_t)s.aux + (size_t)G * 2 * plane_bytes(s) + 16; }  // aux = table bytes
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    int32_t* t = reinterpret_cast<int32_t*>(scratch);
+    int off = 0;
+    for (int q = 0; q < 4; ++q) {
+      for (int i = threadIdx.x; i < p.words[q]; i += kThreads) t[off + i] = p.tab[q][i];
+      off += p.words[q];
+    }
+    __syncthreads();
+  }
+  // one pass over all g images: out[j][y][x] = clip8((2^21 + sum_k in[j][..] * k) >> 22), along x (HORIZ) or y
+  template <bool HORIZ>
+  __device__ static __forceinline__ void pass(const uint8_t* in, size_t in_pitch_img, int in_w, uint8_t* out,
+                                              size_t out_pitch_img, int out_w, int out_h, const int32_t* tab, int g) {
+    // one warp per output row, lanes over x: no integer division anywhere (it costs ~35 instructions per pixel otherwise)
+    const int ks = tab[1], lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int j = 0; j < g; ++j) {
+      const uint8_t* ip = in + (size_t)j * in_pitch_img;
+      uint8_t* op = out + (size_t)j * out_pitch_img;
+      for (int y = warp; y < out_h; y += kThreads >> 5) {
+        for (int x = lane; x < out_w; x += 32) {
+          const int32_t* rec = tab + 2 + (HORIZ ? x : y) * (2 + ks);
+          const int lo = rec[0], n = rec[1];
+          int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+          for (int k = 0; k < n; ++k) {
+            const int kk = rec[2 + k];
+            const uint32_t px = load_rgb(ip, HORIZ ? (y * in_w + lo + k) * 3 : ((lo + k) * in_w + x) * 3);
+            a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)((px >> 16) & 255u) * kk;
+          }
+          uint8_t* o = op + (y * out_w + x) * 3;
+          o[0] = clip8(a0 >> 22); o[1] = clip8(a1 >> 22); o[2] = clip8(a2 >> 22);
+        }
+      }
+    }
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int32_t* t0 = reinterpret_cast<const int32_t*>(scratch);
+    const int32_t* t1 = t0 + p.words[0];
+    const int32_t* t2 = t1 + p.words[1];
+    const int32_t* t3 = t2 + p.words[2];
+    const size_t pb = plane_bytes(s);
+    uint8_t* A = scratch + s.aux;
+    uint8_t* B = A + (size_t)g * pb;
+    __syncthreads();
+    pass<true>(src, s.in_bytes, s.w, A, pb, p.sw, s.h, t0, g);        // (h, w)  -> (h, sw)
+    __syncthreads();
+    pass<false>(A, pb, p.sw, B, pb, p.sw, p.sh, t1, g);               // (h, sw) -> (sh, sw)
+    __syncthreads();
+    pass<true>(B, pb, p.sw, A, pb, s.w, p.sh, t2, g);                 // (sh, sw) -> (sh, w)
+    __syncthreads();
+    pass<false>(A, pb, s.w, dst, s.out_bytes, s.w, s.h, t3, g);       // (sh, w) -> (h, w)
   }
 };
 
@@ -301,4 +374,25 @@ extern "C" int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   p.crop_xy = crop_xy_per_image_dev;
   p.rw = rw; p.rh = rh; p.place_x = place_x; p.place_y = place_y;
   return launch_resample(in, out, n, make_shape(h, w, c, oh, ow), p, (cudaStream_t)stream);
+}
+
+/* Image.resize((sw, sh), filter) followed by Image.resize((w, h), filter) in one launch; tables from
+   imgtx_resample_table_host for (w -> sw), (h -> sh), (sw -> w), (sh -> h).  CIFAR-10-C pixelate (BOX both ways). */
+extern "C" int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                                     const int32_t* h1_dev, int64_t h1_words, const int32_t* v1_dev, int64_t v1_words,
+                                     const int32_t* h2_dev, int64_t h2_words, const int32_t* v2_dev, int64_t v2_words,
+                                     imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "resize chain takes (n,h,w,3) images");
+  IMGTX_CHECK_ARG(sw > 0 && sh > 0 && sw <= w && sh <= h, "the intermediate size must not exceed the image");
+  IMGTX_CHECK_ARG(h1_dev && v1_dev && h2_dev && v2_dev && h1_words > 2 && v1_words > 2 && h2_words > 2 && v2_words > 2,
+                  "four coefficient tables are required");
+  if (n == 0) return IMGTX_OK;
+  ChainParams p;
+  p.tab[0] = h1_dev; p.tab[1] = v1_dev; p.tab[2] = h2_dev; p.tab[3] = v2_dev;
+  p.words[0] = (int)h1_words; p.words[1] = (int)v1_words; p.words[2] = (int)h2_words; p.words[3] = (int)v2_words;
+  p.sw = sw; p.sh = sh;
+  Shape shp = make_shape(h, w, c, h, w);
+  shp.aux = (int)align_up((size_t)(h1_words + v1_words + h2_words + v2_words) * 4, 16);
+  const int target = 128 + 3 * 4 * shp.in_bytes + (int)OpResizeChain::scratch_bytes(shp, 4) + 512;   // 4 images per group
+  return launch_image_op<OpResizeChain>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
 }

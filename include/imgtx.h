@@ -132,6 +132,14 @@ int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, 
                       const int32_t* htable_dev, int64_t htable_words, const int32_t* vtable_dev,
                       int64_t vtable_words, int oh, int ow, int place_x, int place_y, imgtx_stream_t stream);
 
+/* Image.resize((sw, sh), f) followed by Image.resize((w, h), f) in one launch (uint8 intermediates stay in shared memory);
+   tables from imgtx_resample_table_host for (w -> sw), (h -> sh), (sw -> w), (sh -> h).  CIFAR-10-C pixelate: BOX both
+   ways (names only in the reference: attacks/fgsm/cifar-10/reverse_fgsm_cifar10_corrupted.py:18-23). */
+int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                          const int32_t* h1_dev, int64_t h1_words, const int32_t* v1_dev, int64_t v1_words,
+                          const int32_t* h2_dev, int64_t h2_words, const int32_t* v2_dev, int64_t v2_words,
+                          imgtx_stream_t stream);
+
 /* ---- stencils ------------------------------------------------------------------------------- */
 /* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
 int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);
@@ -217,6 +225,12 @@ int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w
 /* zoom_blur (any fixed linear map on x/255 in CSR form, applied in f32 in stored order). */
 int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                     const int32_t* indices_dev, const float* weights_dev, int nnz, imgtx_stream_t stream);
+/* The same operator with the caller stating the length of its longest row (max_row_taps >= max(diff(indptr)); rows are
+   truncated to it): the kernel re-packs the operator into ELL form in shared memory for conflict-free access.  Falls back
+   to imgtx_cc_csr_u8 when the table does not fit. */
+int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+                        const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
+                        imgtx_stream_t stream);
 /* glass_blur: weights_host[0..lw] = scipy Gaussian taps (centre first); deltas_dev (n, iters, h-2, w-2, 2) int8 (dx, dy). */
 int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host, int lw,
                       int iters, const int8_t* deltas_dev, uint64_t seed, imgtx_stream_t stream);
