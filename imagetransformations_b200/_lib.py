@@ -58,6 +58,7 @@ _PROTOS = {
     "imgtx_resample_table_host": [_int, _int, _int, _vp],
     "imgtx_resample_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _int, _int, _vp, _i64, _vp,
                           _i64, _int, _int, _int, _int, _vp],
+    "imgtx_box_pixelate_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp],
     "imgtx_resize_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
     "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _vp],

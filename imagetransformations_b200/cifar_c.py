@@ -357,9 +357,12 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
             small = B.resample(x, (sw, sh), L.FILTER_BOX)
             B.resample(small, (w, h), L.FILTER_BOX, out=out)
         else:
-            t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
-            L.check(lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
-                                              t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(), t[3].numel(), st))
+            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, st)   # small images: gather form; 1 = not applicable
+            if rc == 1:
+                t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
+                rc = lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
+                                               t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(), t[3].numel(), st)
+            L.check(rc)
     elif name == "jpeg_compression":
         qt = jpeg_qtables(p)
         L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, st))

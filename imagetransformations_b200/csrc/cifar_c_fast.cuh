@@ -238,6 +238,128 @@ struct OpCcContrastFast : NoSpill, NoPrepare {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
+// brightness: HSV round trip.  Real-valued result of channel x of a pixel with maximum M: 255 * V2(M) * x / M with
+// V2(M) = clip(M/255 + c, 0, 1); the float64 chain of skimage (rgb2hsv, hsv2rgb) only adds rounding noise of ~1e-13.
+//   * every channel equal to M receives v2 itself in hsv2rgb (all six sectors and all ties): a 256-byte
+//     table built with the exact f64 expression;
+//   * every other channel is x * K[M] in 8.24 fixed point (K rounded to nearest: error <= 254 * 0.5 * 2^-24 = 7.6e-6 LSB);
+//     when the product lies within 2^-16 of an integer the pixel is queued and replayed with the literal f64 formulas,
+//     so the bytes never depend on the fixed-point path.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cc_brightness_exact(const double* T, uint32_t rgb, double c) {
+  const double r = T[rgb & 255u], gg = T[(rgb >> 8) & 255u], b = T[(rgb >> 16) & 255u];
+  const double v = fmax(r, fmax(gg, b)), mn = fmin(r, fmin(gg, b));
+  const double delta = v - mn;
+  double sat = 0.0, h = 0.0;
+  if (delta != 0.0) {
+    sat = delta / v;
+    if (r == v) h = (gg - b) / delta;
+    if (gg == v) h = 2.0 + (b - r) / delta;
+    if (b == v) h = 4.0 + (r - gg) / delta;
+    h = h / 6.0;
+    h = h - trunc(h);          // fmod(h, 1.0), exact
+    if (h < 0.0) h = h + 1.0;   // numpy's % takes the divisor's sign
+  }
+  double v2 = v + c;
+  v2 = v2 < 0.0 ? 0.0 : (v2 > 1.0 ? 1.0 : v2);
+  const double h6 = h * 6;
+  const double hif = floor(h6);
+  const double f = h6 - hif;
+  const double pp = v2 * (1 - sat), q = v2 * (1 - f * sat), t = v2 * (1 - (1 - f) * sat);
+  const int hi = ((int)hif & 255) % 6;
+  double o0, o1, o2;
+  switch (hi) {
+    case 0: o0 = v2; o1 = t; o2 = pp; break;
+    case 1: o0 = q; o1 = v2; o2 = pp; break;
+    case 2: o0 = pp; o1 = v2; o2 = t; break;
+    case 3: o0 = pp; o1 = q; o2 = v2; break;
+    case 4: o0 = t; o1 = pp; o2 = v2; break;
+    default: o0 = v2; o1 = pp; o2 = q; break;
+  }
+  return q255_fast(o0) | (q255_fast(o1) << 8) | (q255_fast(o2) << 16);
+}
+
+struct OpCcBrightnessFast : NoSpill {
+  using Params = CcFastParams;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 256;
+  static constexpr int kQueue = 1023;
+  // T f64[256] | K u32[256] | L u8[256] | queue counter + entries
+  static size_t scratch_bytes(const Shape&, int) { return 2048 + 1024 + 256 + (kQueue + 1) * 4 + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    double* T = reinterpret_cast<double*>(scratch);
+    uint32_t* K = reinterpret_cast<uint32_t*>(scratch + 2048);
+    uint8_t* L = scratch + 3072;
+    for (int i = threadIdx.x; i < 256; i += kThreads) {
+      const double t = (double)i / 255.0;
+      T[i] = t;
+      double v2 = t + p.p0;
+      v2 = v2 < 0.0 ? 0.0 : (v2 > 1.0 ? 1.0 : v2);
+      L[i] = (uint8_t)q255_fast(v2);
+      K[i] = i == 0 ? 0u : (uint32_t)__double2ull_rn(255.0 * v2 / (double)i * 16777216.0);
+    }
+    __syncthreads();
+  }
+  // one pixel (24-bit rgb) -> 24-bit result; `amb` is set when a non-maximum channel is too close to an integer
+  __device__ static __forceinline__ uint32_t pixel(uint32_t px, const uint32_t* K, const uint8_t* L, bool& amb) {
+    const uint32_t r = px & 255u, g = (px >> 8) & 255u, b = px >> 16;
+    const uint32_t M = max(r, max(g, b));
+    const uint32_t k = K[M], l = L[M];
+    const uint32_t pr = r * k, pg = g * k, pb = b * k;
+    // distance of the 24-bit fraction from 0 (mod 2^24), as a value that is 0 inside the band
+    const uint32_t tr = r == M ? 1u : ((pr + 256u) & 0x00FFFE00u), tg = g == M ? 1u : ((pg + 256u) & 0x00FFFE00u),
+                   tb = b == M ? 1u : ((pb + 256u) & 0x00FFFE00u);
+    amb = min(tr, min(tg, tb)) == 0u;
+    const uint32_t orr = r == M ? l : (pr >> 24), og = g == M ? l : (pg >> 24), ob = b == M ? l : (pb >> 24);
+    return orr | (og << 8) | (ob << 16);
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const double* T = reinterpret_cast<const double*>(scratch);
+    const uint32_t* K = reinterpret_cast<const uint32_t*>(scratch + 2048);
+    const uint8_t* L = scratch + 3072;
+    int* qn = reinterpret_cast<int*>(scratch + 3072 + 256);
+    uint32_t* queue = reinterpret_cast<uint32_t*>(qn + 1);
+    const int tid = threadIdx.x;
+    const int quads = (g * s.in_bytes) / 12;   // 4 pixels = 3 words; h*w % 4 == 0 (checked at launch)
+    const uint32_t* im = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* om = reinterpret_cast<uint32_t*>(dst);
+    // staged groups are contiguous (in_bytes == out_bytes), so the whole group is one run of quads
+    if (tid == 0) *qn = 0;
+    __syncthreads();
+    for (int t = tid; t < quads; t += kThreads) {
+      const uint32_t w0 = im[3 * t], w1 = im[3 * t + 1], w2 = im[3 * t + 2];
+      uint32_t px[4] = {w0 & 0x00FFFFFFu, (w0 >> 24) | ((w1 & 0xFFFFu) << 8), (w1 >> 16) | ((w2 & 0xFFu) << 16), w2 >> 8};
+      uint32_t o[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        bool amb;
+        o[q] = pixel(px[q], K, L, amb);
+        if (amb) {
+          const int slot = atomicAdd(qn, 1);
+          if (slot < kQueue) queue[slot] = (uint32_t)(4 * t + q);
+          else o[q] = cc_brightness_exact(T, px[q], p.p0);
+        }
+      }
+      uint32_t a, b, c;
+      pack_rgb4(o[0], o[1], o[2], o[3], a, b, c);
+      om[3 * t] = a; om[3 * t + 1] = b; om[3 * t + 2] = c;
+    }
+    __syncthreads();
+    const int nq = min(*qn, kQueue);
+    for (int e = tid; e < nq; e += kThreads) {
+      const int pi = (int)queue[e];
+      const uint8_t* q = src + pi * 3;
+      const uint32_t v = cc_brightness_exact(T, (uint32_t)q[0] | ((uint32_t)q[1] << 8) | ((uint32_t)q[2] << 16), p.p0);
+      uint8_t* o = dst + pi * 3;
+      o[0] = (uint8_t)v; o[1] = (uint8_t)(v >> 8); o[2] = (uint8_t)(v >> 16);
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
 // frost: clip(p0*x + p1*f, 0, 255) in f64 with the two products tabulated (256 doubles each)
 // ---------------------------------------------------------------------------------------------------------------
 struct OpCcFrostFast : NoSpill {

@@ -212,6 +212,82 @@ struct OpResizeChain : NoSpill {
   }
 };
 
+// ---- BOX pixelate, throughput form ------------------------------------------------------------------------------------
+// For the BOX filter the two up-sampling passes have exactly one tap of weight 2^22 per output (a pure gather), and the two
+// down-sampling passes have at most two taps.  So only the small (sh x sw) image is ever computed — 32-bit pixels, two
+// branch-free taps — and the output is one gather written as words.  The host verifies the table structure; anything else
+// goes through OpResizeChain.  Same Q22 arithmetic and uint8 rounding between passes as Resample.c.
+constexpr int kPixMax = 64;
+struct BoxPixParams {
+  int sw, sh;
+  uint8_t hlo[kPixMax], hlo1[kPixMax], vlo[kPixMax], vlo1[kPixMax], xmap[kPixMax], ymap[kPixMax];
+  int32_t hk0[kPixMax], hk1[kPixMax], vk0[kPixMax], vk1[kPixMax];
+};
+
+struct OpBoxPixelate : NoSpill {
+  using Params = BoxPixParams;
+  static constexpr int kThreads = 256;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kHeader = 6 * kPixMax * 4 + 4 * kPixMax * 4;   // index tables widened to int + weights
+  // per image: A (h x sw) and B (sh x sw) as 32-bit pixels
+  static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * 2 * s.h * s.aux * 4 + 16; }   // aux = sw
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    int* t = reinterpret_cast<int*>(scratch);
+    for (int i = threadIdx.x; i < kPixMax; i += kThreads) {
+      t[i] = p.hlo[i]; t[kPixMax + i] = p.hlo1[i]; t[2 * kPixMax + i] = p.vlo[i]; t[3 * kPixMax + i] = p.vlo1[i];
+      t[4 * kPixMax + i] = p.xmap[i]; t[5 * kPixMax + i] = p.ymap[i];
+      t[6 * kPixMax + i] = p.hk0[i]; t[7 * kPixMax + i] = p.hk1[i]; t[8 * kPixMax + i] = p.vk0[i]; t[9 * kPixMax + i] = p.vk1[i];
+    }
+    __syncthreads();
+  }
+  __device__ static __forceinline__ uint32_t blend2(uint32_t a, uint32_t b, int k0, int k1) {
+    const int r0 = ((1 << 21) + (int)(a & 255u) * k0 + (int)(b & 255u) * k1) >> 22;
+    const int r1 = ((1 << 21) + (int)((a >> 8) & 255u) * k0 + (int)((b >> 8) & 255u) * k1) >> 22;
+    const int r2 = ((1 << 21) + (int)((a >> 16) & 255u) * k0 + (int)((b >> 16) & 255u) * k1) >> 22;
+    return (uint32_t)min(r0, 255) | ((uint32_t)min(r1, 255) << 8) | ((uint32_t)min(r2, 255) << 16);
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int* t = reinterpret_cast<const int*>(scratch);
+    const int *hlo = t, *hlo1 = t + kPixMax, *vlo = t + 2 * kPixMax, *vlo1 = t + 3 * kPixMax, *xmap = t + 4 * kPixMax,
+              *ymap = t + 5 * kPixMax, *hk0 = t + 6 * kPixMax, *hk1 = t + 7 * kPixMax, *vk0 = t + 8 * kPixMax, *vk1 = t + 9 * kPixMax;
+    const int sw = p.sw, sh = p.sh, lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = kThreads >> 5;
+    uint32_t* A = reinterpret_cast<uint32_t*>(scratch + kHeader);   // [g][h][sw]
+    uint32_t* B = A + (size_t)g * s.h * sw;                          // [g][sh][sw]
+    __syncthreads();
+    // 1. horizontal down-sampling: one warp per (image, row), lanes over the small width
+    for (int r = warp; r < g * s.h; r += nw) {
+      const int j = r / s.h, y = r - j * s.h;
+      const uint8_t* row = src + (size_t)j * s.in_bytes + y * s.w * 3;
+      for (int x = lane; x < sw; x += 32)
+        A[(size_t)r * sw + x] = blend2(load_rgb(row, hlo[x] * 3), load_rgb(row, hlo1[x] * 3), hk0[x], hk1[x]);
+    }
+    __syncthreads();
+    // 2. vertical down-sampling
+    for (int r = warp; r < g * sh; r += nw) {
+      const int j = r / sh, y = r - j * sh;
+      const uint32_t* a0 = A + ((size_t)j * s.h + vlo[y]) * sw;
+      const uint32_t* a1 = A + ((size_t)j * s.h + vlo1[y]) * sw;
+      const int k0 = vk0[y], k1 = vk1[y];
+      for (int x = lane; x < sw; x += 32) B[(size_t)r * sw + x] = blend2(a0[x], a1[x], k0, k1);
+    }
+    __syncthreads();
+    // 3. both up-sampling passes: out[y][x] = B[ymap[y]][xmap[x]], four pixels (three words) per thread
+    const int qpr = s.w >> 2;   // w % 4 == 0 (checked on the host)
+    for (int i = threadIdx.x; i < g * s.h * qpr; i += kThreads) {
+      const int r = i / qpr, q = i - r * qpr;
+      const int j = r / s.h, y = r - j * s.h;
+      const uint32_t* b = B + ((size_t)j * sh + ymap[y]) * sw;
+      uint32_t* o = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes + y * s.w * 3);
+      uint32_t w0, w1, w2;
+      pack_rgb4(b[xmap[4 * q]], b[xmap[4 * q + 1]], b[xmap[4 * q + 2]], b[xmap[4 * q + 3]], w0, w1, w2);
+      o[3 * q] = w0; o[3 * q + 1] = w1; o[3 * q + 2] = w2;
+    }
+  }
+};
+
 // Specialised launcher: scratch depends on the parameters (table sizes, needed window).
 static int launch_resample(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, const ResampleParams& p,
                            cudaStream_t stream) {
@@ -395,4 +471,51 @@ extern "C" int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n,
   shp.aux = (int)align_up((size_t)(h1_words + v1_words + h2_words + v2_words) * 4, 16);
   const int target = 128 + 3 * 4 * shp.in_bytes + (int)OpResizeChain::scratch_bytes(shp, 4) + 512;   // 4 images per group
   return launch_image_op<OpResizeChain>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
+}
+
+/* CIFAR-10-C pixelate, throughput form: Image.resize((sw, sh), BOX) then Image.resize((w, h), BOX) for images up to 64x64.
+   Returns IMGTX_OK when launched, 1 when the BOX tables do not have the (<= 2 taps down, single unit tap up) structure or
+   the shape is outside the fast path — the caller then uses imgtx_resize_chain_u8 (same results). */
+extern "C" int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                                     imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "pixelate takes (n,h,w,3) images");
+  IMGTX_CHECK_ARG(sw > 0 && sh > 0 && sw <= w && sh <= h, "the intermediate size must not exceed the image");
+  if (h > kPixMax || w > kPixMax || (w & 3) || sw == w || sh == h) return 1;
+  if (n == 0) return IMGTX_OK;
+  BoxPixParams p;
+  memset(&p, 0, sizeof(p));
+  p.sw = sw; p.sh = sh;
+  const int kBox = IMGTX_FILTER_BOX;
+  auto down = [&](int in_size, int out_size, uint8_t* lo, uint8_t* lo1, int32_t* k0, int32_t* k1) -> bool {
+    std::vector<int32_t> t((size_t)imgtx_resample_table_words(in_size, out_size, kBox));
+    if (imgtx_resample_table_host(in_size, out_size, kBox, t.data()) != IMGTX_OK) return false;
+    const int ks = t[1];
+    for (int i = 0; i < out_size; ++i) {
+      const int32_t* rec = t.data() + 2 + (size_t)i * (2 + ks);
+      if (rec[1] < 1 || rec[1] > 2) return false;
+      lo[i] = (uint8_t)rec[0];
+      lo1[i] = (uint8_t)(rec[1] == 2 ? rec[0] + 1 : rec[0]);
+      k0[i] = rec[2];
+      k1[i] = rec[1] == 2 ? rec[3] : 0;
+      if (k0[i] < 0 || k1[i] < 0) return false;
+    }
+    return true;
+  };
+  auto up = [&](int in_size, int out_size, uint8_t* map) -> bool {
+    std::vector<int32_t> t((size_t)imgtx_resample_table_words(in_size, out_size, kBox));
+    if (imgtx_resample_table_host(in_size, out_size, kBox, t.data()) != IMGTX_OK) return false;
+    const int ks = t[1];
+    for (int i = 0; i < out_size; ++i) {
+      const int32_t* rec = t.data() + 2 + (size_t)i * (2 + ks);
+      if (rec[1] != 1 || rec[2] != (1 << 22)) return false;
+      map[i] = (uint8_t)rec[0];
+    }
+    return true;
+  };
+  if (!down(w, sw, p.hlo, p.hlo1, p.hk0, p.hk1) || !down(h, sh, p.vlo, p.vlo1, p.vk0, p.vk1) || !up(sw, w, p.xmap) ||
+      !up(sh, h, p.ymap))
+    return 1;
+  Shape shp = make_shape(h, w, c, h, w);
+  shp.aux = sw;
+  return launch_image_op<OpBoxPixelate>(in, out, n, shp, p, (cudaStream_t)stream);
 }

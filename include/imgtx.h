@@ -140,6 +140,12 @@ int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
                           const int32_t* h2_dev, int64_t h2_words, const int32_t* v2_dev, int64_t v2_words,
                           imgtx_stream_t stream);
 
+/* The same BOX down / BOX up chain for images up to 64x64 (CIFAR-10-C pixelate), throughput form: BOX up-sampling is a pure
+   gather and BOX down-sampling has at most two taps, so only the small image is computed.  Returns IMGTX_OK when launched,
+   1 when the shape or table structure is outside the fast path (use imgtx_resize_chain_u8: identical results). */
+int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                          imgtx_stream_t stream);
+
 /* ---- stencils ------------------------------------------------------------------------------- */
 /* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
 int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);

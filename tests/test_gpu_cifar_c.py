@@ -200,3 +200,30 @@ def test_sharded_equals_single_gpu(cuda):
                 parts.append(C.corrupt(torch.from_numpy(xs).cuda(), name, sev, draws=S.shard_draws(d, len(x), r, ws)))
             assert torch.equal(torch.cat(parts), full), (name, ws)
             assert torch.equal(S.image_checksums(torch.cat(parts)), S.image_checksums(full))
+
+
+@pytest.mark.parametrize("sev", [1, 2, 3, 4, 5])
+def test_brightness_all_colours(cuda, sev):
+    """The fixed-point fast path + literal replay of brightness, over a 1/2 sample of all 2^24 colours (every value of
+    every channel, all orderings and ties), bit-exact against the f64 oracle."""
+    C = _C()
+    idx = np.arange(0, 1 << 24, 2, dtype=np.int64) + (np.arange(1 << 23) >> 11 & 1)   # alternate parity so both halves occur
+    x = np.stack([idx & 255, (idx >> 8) & 255, (idx >> 16) & 255], -1).astype(np.uint8).reshape(-1, 32, 32, 3)
+    got = C.corrupt(torch.from_numpy(x).cuda(), "brightness", sev).cpu().numpy()
+    want = np.concatenate([CC.brightness(x[i:i + 1024], CC.PARAMS["brightness"][sev - 1]) for i in range(0, len(x), 1024)])
+    assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
+
+
+@pytest.mark.parametrize("hw,c", [((32, 32), 0.95), ((32, 32), 0.65), ((64, 48), 0.75), ((16, 40), 0.5), ((48, 64), 0.9)])
+def test_pixelate_gather_form_shapes(cuda, hw, c):
+    """BOX pixelate fast path (<= 64x64) on non-CIFAR shapes against the Pillow-exact oracle."""
+    from imagetransformations_b200 import _lib as L
+    h, w = hw
+    x = np.random.default_rng(h * w).integers(0, 256, (37, h, w, 3), dtype=np.uint8)
+    xd = torch.from_numpy(x).cuda()
+    out = torch.empty_like(xd)
+    sw, sh = int(w * c), int(h * c)
+    rc = L.load().imgtx_box_pixelate_u8(xd.data_ptr(), out.data_ptr(), len(x), h, w, 3, sw, sh, None)
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), CC.pixelate(x, c))

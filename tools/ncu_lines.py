@@ -1,5 +1,5 @@
 """Per-source-line totals (warp instructions executed, stall samples) from a .ncu-rep captured with --import-source on.
-usage: python tools/ncu_lines.py file.ncu-rep [top_n]"""
+usage: python tools/ncu_lines.py file.ncu-rep [top_n] [launch_index]"""
 import csv
 import io
 import subprocess
@@ -7,14 +7,16 @@ import sys
 
 
 def main():
-    out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv", "--print-source", "cuda,sass"],
-                         capture_output=True, text=True).stdout
+    cmd = ["ncu", "-i", sys.argv[1], "--page", "source", "--csv", "--print-source", "cuda,sass"]
+    if len(sys.argv) > 3:
+        cmd += ["--launch-skip", sys.argv[3], "--launch-count", "1"]
+    out = subprocess.run(cmd, capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     fname = ""
     lines = []
     hdr = None
     for r in rows:
-        if len(r) >= 2 and r[0] == "File Path":
+        if len(r) >= 2 and r[0] in ("File Path", "File Name"):
             fname = r[1].split("/")[-1]
             continue
         if len(r) > 5 and r[0] == "Line No":
