@@ -516,6 +516,7 @@ struct OpCcGlassFast : NoSpill {
 constexpr int kMaxLine = 32;
 struct MotionParams {
   int width;
+  int n_eff;               // taps 0..n_eff-1 carry all but 2^-20 LSB of the weight (throughput forms; set by fill_motion)
   float k[kMaxLine];
   const int32_t* offsets;  // device (n, width, 2) (dx, dy) or nullptr: angle drawn on chip in [lo, hi] degrees
   double lo, hi;
@@ -760,15 +761,77 @@ __device__ __forceinline__ uint32_t line_blur_word(const uint8_t* canvas, const 
   return (uint32_t)r0 | ((uint32_t)r1 << 8) | ((uint32_t)r2 << 16) | ((uint32_t)r3 << 24);
 }
 
+// Throughput evaluation of the same sum.  The specification is the float32 sum in tap order; here the taps that carry
+// weight (the one-sided Gaussian underflows quickly: 7 of 21 taps at sigma = 1) are accumulated with fused multiply-adds in
+// float32, which differs from the ordered sum by less than 4e-4 (every partial sum is below 256, so each of the <= 25 + 19 roundings
+// is at most 2^-17, plus the products, the dropped tail and the rounding of acc + 0.5), and an output is only trusted when
+// acc + 0.5 is at least 5e-4 away from an integer; the other words (about 0.4 %) are queued and replayed literally.
+template <int CH>
+__device__ __forceinline__ uint32_t line_blur_word_fast(const uint8_t* canvas, const LineGeom& gm, const float* k, int n_eff,
+                                                        int rowb, int ob, bool& amb) {
+  const int y = ob / rowb, xb = ob - y * rowb;
+  const uint32_t* c32 = reinterpret_cast<const uint32_t*>(canvas);   // canvas is 16-byte aligned
+  const int base = y * gm.pw * CH + xb;
+  float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+  for (int i = 0; i < n_eff; ++i) {
+    const int bo = base + gm.off[i];
+    const uint32_t* wp = c32 + (bo >> 2);
+    const uint32_t v = __funnelshift_r(wp[0], wp[1], (uint32_t)bo << 3);
+    const float wt = k[i];
+    a0 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440u)), 8388608.0f), wt, a0);
+    a1 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7441u)), 8388608.0f), wt, a1);
+    a2 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7442u)), 8388608.0f), wt, a2);
+    a3 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7443u)), 8388608.0f), wt, a3);
+  }
+  const float r0 = a0 + 0.5f, r1 = a1 + 0.5f, r2 = a2 + 0.5f, r3 = a3 + 0.5f;
+  const float f0 = floorf(r0), f1 = floorf(r1), f2 = floorf(r2), f3 = floorf(r3);
+  const float d0 = fabsf(r0 - f0 - 0.5f), d1 = fabsf(r1 - f1 - 0.5f), d2 = fabsf(r2 - f2 - 0.5f), d3 = fabsf(r3 - f3 - 0.5f);
+  amb = !(fmaxf(fmaxf(d0, d1), fmaxf(d2, d3)) <= 0.4995f);   // distance of the fraction from 1/2 (also true for NaN)
+  const int q0 = min(max((int)f0, 0), 255), q1 = min(max((int)f1, 0), 255), q2 = min(max((int)f2, 0), 255), q3 = min(max((int)f3, 0), 255);
+  return (uint32_t)q0 | ((uint32_t)q1 << 8) | ((uint32_t)q2 << 16) | ((uint32_t)q3 << 24);
+}
+
+// literal evaluation of output byte `b` from the (unpadded) image with clamped coordinates.  The float32 additions are a
+// dependent chain by definition; the loads and products of eight taps at a time are independent and issued together.
+template <int CH>
+__device__ __forceinline__ uint32_t line_blur_elem_exact(const uint8_t* im, const int* offs /* (width,2) dx,dy */, const float* k,
+                                                         int width, int w, int h, int b) {
+  const int px = b / CH, ch = b - px * CH, y = px / w, x = px - y * w;
+  float a = 0.0f;
+  for (int i0 = 0; i0 < width; i0 += 8) {
+    float pr[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = min(i0 + u, width - 1);
+      const int xx = min(max(x + offs[2 * i], 0), w - 1), yy = min(max(y + offs[2 * i + 1], 0), h - 1);
+      pr[u] = __fmul_rn((float)im[(yy * w + xx) * CH + ch], k[i]);
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (i0 + u < width) a = __fadd_rn(a, pr[u]);
+  }
+  return (uint32_t)min(max(__float2int_rd(__fadd_rn(a, 0.5f)), 0), 255);
+}
+template <int CH>
+__device__ __noinline__ uint32_t line_blur_word_exact(const uint8_t* im, const int* offs, const float* k, int width, int w, int h,
+                                                      int ob) {
+  uint32_t out = 0;
+  for (int e = 0; e < 4; ++e) out |= line_blur_elem_exact<CH>(im, offs, k, width, w, h, ob + e) << (8 * e);
+  return out;
+}
+
 struct OpCcMotionFast : NoSpill {
   using Params = MotionParams;
   static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
   static constexpr int kMinBlocks = 2;
-  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) * 3 + 8, 16); }  // aux = line width
-  // weights f32[32] | per image: LineGeom + raw offsets (2 x 32 int) + canvas
+  static constexpr int kQueue = 255;
+  static constexpr int kHeader = 128 + (kQueue + 1) * 4;   // weights f32[32] | replay queue
+  // aux = n_eff: the canvas only has to cover the taps the fast path reads
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) * 3 + 8, 16); }
+  // per image: LineGeom + raw offsets (2 x 32 int) + canvas
   __host__ __device__ static size_t per_image(const Shape& s) { return sizeof(LineGeom) + kMaxLine * 2 * 4 + canvas_bytes(s); }
-  static size_t scratch_bytes(const Shape& s, int G) { return 128 + (size_t)G * per_image(s) + 16; }
+  static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * per_image(s) + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
     float* k = reinterpret_cast<float*>(scratch);
@@ -779,12 +842,15 @@ struct OpCcMotionFast : NoSpill {
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
                              uint8_t* scratch, uint8_t*) {
     const float* k = reinterpret_cast<const float*>(scratch);
+    int* qn = reinterpret_cast<int*>(scratch + 128);
+    int* queue = qn + 1;
     const size_t pi = per_image(s);
     const int tid = threadIdx.x, warp = tid >> 5;
     const Philox rng(p.seed);
     __syncthreads();
+    if (tid == 0) *qn = 0;
     for (int j = warp; j < g; j += kThreads >> 5) {
-      uint8_t* base = scratch + 128 + (size_t)j * pi;
+      uint8_t* base = scratch + kHeader + (size_t)j * pi;
       LineGeom* gm = reinterpret_cast<LineGeom*>(base);
       int* raw = reinterpret_cast<int*>(base + sizeof(LineGeom));
       const int64_t img = img0 + j;
@@ -795,11 +861,11 @@ struct OpCcMotionFast : NoSpill {
         motion_offsets(p.lo + (p.hi - p.lo) * (double)u01(r.x), p.width, raw);
       }
       __syncwarp();
-      make_line_geom<3>(gm, raw, p.width, s.w, s.h);
+      make_line_geom<3>(gm, raw, p.n_eff, s.w, s.h);
     }
     __syncthreads();
     for (int j = 0; j < g; ++j) {
-      uint8_t* base = scratch + 128 + (size_t)j * pi;
+      uint8_t* base = scratch + kHeader + (size_t)j * pi;
       fill_canvas<3>(base + sizeof(LineGeom) + kMaxLine * 2 * 4, src + (size_t)j * s.in_bytes,
                      *reinterpret_cast<const LineGeom*>(base), s.w, s.h, tid, kThreads);
     }
@@ -808,11 +874,27 @@ struct OpCcMotionFast : NoSpill {
     uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
     for (int i = tid; i < g * wpi; i += kThreads) {
       const int j = i / wpi, wi = i - j * wpi;
-      const uint8_t* base = scratch + 128 + (size_t)j * pi;
+      const uint8_t* base = scratch + kHeader + (size_t)j * pi;
       const LineGeom& gm = *reinterpret_cast<const LineGeom*>(base);
       const uint8_t* canvas = base + sizeof(LineGeom) + kMaxLine * 2 * 4;
       // canvas origin: output (0,0) sits at canvas (-dymin, -dxmin); tap offsets are relative to (dymin, dxmin)
-      d32[(size_t)j * (s.out_bytes >> 2) + wi] = line_blur_word<3>(canvas, gm, k, p.width, rowb, wi * 4);
+      bool amb;
+      uint32_t v = line_blur_word_fast<3>(canvas, gm, k, p.n_eff, rowb, wi * 4, amb);
+      if (amb) {
+        const int slot = atomicAdd(qn, 1);
+        if (slot < kQueue) queue[slot] = i;
+        else v = line_blur_word_exact<3>(src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)),
+                                         k, p.width, s.w, s.h, wi * 4);
+      }
+      d32[(size_t)j * (s.out_bytes >> 2) + wi] = v;
+    }
+    __syncthreads();
+    const int nq = min(*qn, kQueue);
+    for (int e = tid; e < 4 * nq; e += kThreads) {   // one thread per byte of the queued words
+      const int i = queue[e >> 2], j = i / wpi, wi = i - j * wpi;
+      const uint8_t* base = scratch + kHeader + (size_t)j * pi;
+      dst[(size_t)j * s.out_bytes + wi * 4 + (e & 3)] = (uint8_t)line_blur_elem_exact<3>(
+          src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.width, s.w, s.h, wi * 4 + (e & 3));
     }
   }
 };
@@ -823,8 +905,9 @@ struct OpCcSnowFast : NoSpill {
   static constexpr int kThreads = 256;
   static constexpr int kMinBlocks = 2;
   // header: T32[256] | k[32] | ty[64] tx[64] | y0 y1 x0 x1 [64 each, int]        = 1024 + 128 + 512 + 1024
-  static constexpr int kHeader = 1024 + 128 + 512 + 1024;
-  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) + 8, 16); }  // aux = line width
+  static constexpr int kQueue = 255;
+  static constexpr int kHeader = 1024 + 128 + 512 + 1024 + (kQueue + 1) * 4;   // ... | replay queue
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) + 8, 16); }  // aux = n_eff
   // per image: LineGeom + raw offsets + L0 f32[hw] + L1 u8[hw] + L2 u8[hw] + canvas
   __host__ __device__ static size_t per_image(const Shape& s) {
     return sizeof(LineGeom) + kMaxLine * 2 * 4 + align_up((size_t)s.h * s.w * 6, 16) + canvas_bytes(s);
@@ -853,6 +936,8 @@ struct OpCcSnowFast : NoSpill {
     const float* tyv = k + 32;
     const float* txv = tyv + 64;
     const int* idx = reinterpret_cast<const int*>(txv + 64);
+    int* qn = const_cast<int*>(idx) + 256;
+    int* queue = qn + 1;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int hw = s.h * s.w;
     const size_t pi = per_image(s);
@@ -860,6 +945,7 @@ struct OpCcSnowFast : NoSpill {
                  o_cv = o_l0 + align_up((size_t)hw * 6, 16);
     const Philox rng(p.m.seed);
     __syncthreads();
+    if (threadIdx.x == 0) *qn = 0;
     // A. line geometry, one warp per image
     for (int j = warp; j < g; j += kThreads >> 5) {
       uint8_t* base = scratch + kHeader + (size_t)j * pi;
@@ -872,7 +958,7 @@ struct OpCcSnowFast : NoSpill {
         motion_offsets(p.m.lo + (p.m.hi - p.m.lo) * (double)u01(r.x), p.m.width, raw);
       }
       __syncwarp();
-      make_line_geom<1>(reinterpret_cast<LineGeom*>(base), raw, p.m.width, s.w, s.h);
+      make_line_geom<1>(reinterpret_cast<LineGeom*>(base), raw, p.m.n_eff, s.w, s.h);
     }
     // B. noise layer (f64 draws cast to f32)
     if (p.layer) {
@@ -916,13 +1002,29 @@ struct OpCcSnowFast : NoSpill {
       fill_canvas<1>(base + o_cv, base + o_l1, *reinterpret_cast<const LineGeom*>(base), s.w, s.h, tid, kThreads);
     }
     __syncthreads();
-    // E. line blur, rounded back to 8 bits
+    // E. line blur, rounded back to 8 bits (float32 fused evaluation; words near a rounding boundary are replayed literally)
     const int wpl = hw >> 2;
     for (int i = tid; i < g * wpl; i += kThreads) {
       const int j = i / wpl, wi = i - j * wpl;
       uint8_t* base = scratch + kHeader + (size_t)j * pi;
-      reinterpret_cast<uint32_t*>(base + o_l2)[wi] =
-          line_blur_word<1>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.width, s.w, wi * 4);
+      bool amb;
+      uint32_t v = line_blur_word_fast<1>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.n_eff, s.w, wi * 4, amb);
+      if (amb) {
+        const int slot = atomicAdd(qn, 1);
+        if (slot < kQueue) queue[slot] = i;
+        else v = line_blur_word_exact<1>(base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h, wi * 4);
+      }
+      reinterpret_cast<uint32_t*>(base + o_l2)[wi] = v;
+    }
+    __syncthreads();
+    {
+      const int nq = min(*qn, kQueue);
+      for (int e = tid; e < 4 * nq; e += kThreads) {   // one thread per byte of the queued words
+        const int i = queue[e >> 2], j = i / wpl, wi = i - j * wpl;
+        uint8_t* base = scratch + kHeader + (size_t)j * pi;
+        base[o_l2 + wi * 4 + (e & 3)] = (uint8_t)line_blur_elem_exact<1>(
+            base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h, wi * 4 + (e & 3));
+      }
     }
     __syncthreads();
     // F. blend with the whitened image, the layer and its 180-degree rotation
@@ -1073,6 +1175,10 @@ static int fill_motion(MotionParams& m, int width, const float* k_host, const in
   memset(&m, 0, sizeof(m));
   m.width = width;
   for (int i = 0; i < width; ++i) m.k[i] = k_host[i];
+  // taps the throughput forms evaluate: drop the tail whose total weight is below 2^-20 LSB (|k| * 255 summed)
+  m.n_eff = width;
+  double tail = 0.0;
+  while (m.n_eff > 1 && tail + fabs((double)k_host[m.n_eff - 1]) * 255.0 <= 9.5e-7) tail += fabs((double)k_host[--m.n_eff]) * 255.0;
   m.offsets = offsets_dev; m.lo = lo; m.hi = hi; m.seed = seed;
   return IMGTX_OK;
 }
@@ -1085,7 +1191,7 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
   int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
   if (rc) return rc;
   Shape shp = make_shape(h, w, c, h, w);
-  shp.aux = width;
+  shp.aux = p.n_eff;
   if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcMotionFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
     const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcMotionFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
@@ -1109,7 +1215,7 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
   for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }
   for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
   Shape shp = make_shape(h, w, c, h, w);
-  shp.aux = width;
+  shp.aux = p.m.n_eff;
   if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcSnowFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
     const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcSnowFast::scratch_bytes(shp, 4) + 512;  // 4 images per group

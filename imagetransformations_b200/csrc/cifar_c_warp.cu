@@ -208,29 +208,12 @@ struct OpCcElastic : NoSpill {
 // Throughput form.  The displacement field only reaches the image through its float32 cast, so the smoothing may be
 // evaluated in any float64 order: each thread produces a strip of 8 outputs of one line from a sliding register window
 // (one shared-memory load per tap instead of eight) with fused multiply-adds, and the literal scipy order is replayed only
-// if the result lies within 4e-14*max(1,|alpha|) of a float32 rounding boundary (probability ~1e-5 per value).  The three
-// affine matrices of a group are inverted by three threads at once, both fields are smoothed concurrently, and the warped
-// image is kept as float64 so the bilinear stage converts nothing.
-struct OpCcElasticFast : NoSpill {
-  using Params = ElasticParams;
-  static constexpr int kStages = 2, kOutBufs = 1;
-  static constexpr int kMinBlocks = 3;   // 256 threads x 3 CTAs: <= 80 registers
-  static constexpr bool kCifarCopy = true;
-  static constexpr int kThreads = 256;
-  static constexpr int kMaxG = 8;
-  static constexpr int kStrip = 8;
-  static constexpr int kQueue = 63;
-  static size_t scratch_bytes(const Shape& s, int) {
-    return 1024 + 256 + kMaxG * 48 + (size_t)s.h * s.w * (32 + 8) + (kQueue + 1) * 4 + 8 + (kThreads / 32) * (2 * kMaxLw + 1) * 8 + 16;
-  }
-  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
-  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
-    float* T = reinterpret_cast<float*>(scratch);
-    double* Wg = reinterpret_cast<double*>(scratch + 1024);
-    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
-    for (int i = threadIdx.x; i <= p.lw; i += kThreads) Wg[i] = p.w[i];
-    __syncthreads();
-  }
+// if the result lies within 4e-14*max(1,|alpha|) of a float32 rounding boundary (probability ~1e-5 per value).  The
+// intermediate plane is stored transposed with an odd row pitch so that both passes walk shared memory conflict-free.
+// cv2.warpAffine's per-row / per-column fixed-point terms are tabulated once per image (as OpenCV does), the warped image
+// stays float32, and the bilinear stage runs in float32 with a literal-f64 replay for the pixels whose value lies within
+// 1e-3 of an integer after scaling by 255 (the float32 evaluation is accurate to 1e-4 there; about 0.2 % of the values).
+struct ElasticCommon {
   __device__ static __forceinline__ int refl_half(int i, int n) {  // one fold is enough when lw <= n
     return i < 0 ? -1 - i : (i >= n ? 2 * n - 1 - i : i);
   }
@@ -242,6 +225,144 @@ struct OpCcElasticFast : NoSpill {
   __device__ static __forceinline__ int refl101_any(int i, int n) {
     if (i <= -n || i >= 2 * n - 1) return reflect101(i, n);
     return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
+  }
+  // inverse affine matrix of image `img` (cv2.getAffineTransform of the jittered triangle, then cv2.warpAffine's inversion)
+  __device__ static void inverse_matrix(const ElasticParams& p, const Philox& rng, int64_t img, int h, double* Mo) {
+    double M[6];
+    if (p.M) {
+      for (int k = 0; k < 6; ++k) M[k] = p.M[img * 6 + k];
+    } else {
+      // pts1 = [(c+q, c+q), (c+q, c-q), (c-q, c-q)], pts2 = pts1 + U(-c2, c2): closed-form affine through 3 points
+      const float cs = (float)(h / 2), q = (float)(h / 3);
+      const float p1[3][2] = {{cs + q, cs + q}, {cs + q, cs - q}, {cs - q, cs - q}};
+      double p2[3][2];
+      const uint4 r0 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 0u);
+      const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 1u);
+      const uint32_t rr[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y};
+      for (int k = 0; k < 6; ++k)
+        p2[k / 2][k % 2] = (double)(p1[k / 2][k % 2] + (float)(-p.c2 + 2.0 * p.c2 * (double)u01(rr[k])));
+      const double x0 = p1[0][0], y0 = p1[0][1], x1 = p1[1][0], y1 = p1[1][1], x2 = p1[2][0], y2 = p1[2][1];
+      const double det = x0 * (y1 - y2) - y0 * (x1 - x2) + (x1 * y2 - x2 * y1);
+      for (int rrow = 0; rrow < 2; ++rrow) {
+        const double u0 = p2[0][rrow], u1 = p2[1][rrow], u2 = p2[2][rrow];
+        M[rrow * 3 + 0] = (u0 * (y1 - y2) - y0 * (u1 - u2) + (u1 * y2 - u2 * y1)) / det;
+        M[rrow * 3 + 1] = (x0 * (u1 - u2) - u0 * (x1 - x2) + (x1 * u2 - x2 * u1)) / det;
+        M[rrow * 3 + 2] = (x0 * (y1 * u2 - y2 * u1) - y0 * (x1 * u2 - x2 * u1) + u0 * (x1 * y2 - x2 * y1)) / det;
+      }
+    }
+    double D = M[0] * M[4] - M[1] * M[3];
+    D = D != 0.0 ? 1.0 / D : 0.0;
+    const double A11 = M[4] * D, A22 = M[0] * D;
+    M[0] = A11; M[1] *= -D; M[3] *= -D; M[4] = A22;
+    const double b1 = -M[0] * M[2] - M[1] * M[5];
+    const double b2 = -M[3] * M[2] - M[4] * M[5];
+    M[2] = b1; M[5] = b2;
+    for (int k = 0; k < 6; ++k) Mo[k] = M[k];
+  }
+  // cv2.warpAffine's tables for one image: tab[2x], tab[2x+1] = adelta, bdelta; tab[2(w+y)], tab[2(w+y)+1] = X0, Y0
+  __device__ static __forceinline__ void affine_tables(const double* Mi, int h, int w, int* tab, int i) {
+    if (i < w) {
+      tab[2 * i] = (int)rint(Mi[0] * (double)i * 1024);
+      tab[2 * i + 1] = (int)rint(Mi[3] * (double)i * 1024);
+    } else if (i < w + h) {
+      const int y = i - w;
+      tab[2 * i] = (int)rint((Mi[1] * (double)y + Mi[2]) * 1024) + 16;
+      tab[2 * i + 1] = (int)rint((Mi[4] * (double)y + Mi[5]) * 1024) + 16;
+    }
+  }
+  // one pixel of cv2.warpAffine(INTER_LINEAR, BORDER_REFLECT_101) of the image / 255: three float32 channel values
+  __device__ static __forceinline__ void warp_pixel(const uint8_t* im, const float* T, const int* tab, int h, int w, int y, int x,
+                                                    float& o0, float& o1, float& o2) {
+    const int X = (tab[2 * (w + y)] + tab[2 * x]) >> 5, Y = (tab[2 * (w + y) + 1] + tab[2 * x + 1]) >> 5;
+    const int sx = X >> 5, sy = Y >> 5;
+    const float fx = __fmul_rn((float)(X & 31), 0.03125f), fy = __fmul_rn((float)(Y & 31), 0.03125f);
+    const float wx0 = __fsub_rn(1.0f, fx), wy0 = __fsub_rn(1.0f, fy);
+    const float w00 = __fmul_rn(wy0, wx0), w01 = __fmul_rn(wy0, fx), w10 = __fmul_rn(fy, wx0), w11 = __fmul_rn(fy, fx);
+    const int ya = refl101_any(sy, h), yb = refl101_any(sy + 1, h), xa = refl101_any(sx, w), xb = refl101_any(sx + 1, w);
+    const uint32_t c00 = load_rgb(im, (ya * w + xa) * 3), c01 = load_rgb(im, (ya * w + xb) * 3);
+    const uint32_t c10 = load_rgb(im, (yb * w + xa) * 3), c11 = load_rgb(im, (yb * w + xb) * 3);
+    float o[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float acc = __fmul_rn(T[(c00 >> (8 * c)) & 255u], w00);
+      acc = __fadd_rn(acc, __fmul_rn(T[(c01 >> (8 * c)) & 255u], w01));
+      acc = __fadd_rn(acc, __fmul_rn(T[(c10 >> (8 * c)) & 255u], w10));
+      acc = __fadd_rn(acc, __fmul_rn(T[(c11 >> (8 * c)) & 255u], w11));
+      o[c] = acc;
+    }
+    o0 = o[0]; o1 = o[1]; o2 = o[2];
+  }
+  __device__ static __forceinline__ uint32_t q255_f32(float v) {   // np.uint8(np.clip(v, 0, 1) * f32(255))
+    v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
+    return (uint32_t)__float2int_rz(__fmul_rn(v, 255.0f));
+  }
+};
+
+// alpha == 0 (severity 1 of the CIFAR table): the displacement is (float)(field * 0) = +-0 everywhere, so the bilinear stage
+// samples at integer coordinates with ty = tx = 0 and returns the warped image itself — (q00*1)*1 + (q01*1)*0 + (q10*0)*1 +
+// (q11*0)*0 == q00 for finite fields.  Only the affine warp is left; whole groups of images are processed per barrier.
+struct OpCcAffineWarp : NoSpill, ElasticCommon {
+  using Params = ElasticParams;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 256;
+  // T32 | per image: inverse matrix (6 f64) + tables (w + h) x 2 int
+  static size_t scratch_bytes(const Shape& s, int G) { return 1024 + (size_t)G * (48 + (s.h + s.w) * 8) + 16; }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
+    float* T = reinterpret_cast<float*>(scratch);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    __syncthreads();
+  }
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int tid = threadIdx.x, hw = s.h * s.w, per = 48 + (s.h + s.w) * 8;
+    const float* T = reinterpret_cast<const float*>(scratch);
+    uint8_t* base = scratch + 1024;
+    const Philox rng(p.seed);
+    __syncthreads();
+    for (int j = tid; j < g; j += kThreads) inverse_matrix(p, rng, img0 + j, s.h, reinterpret_cast<double*>(base + (size_t)j * per));
+    __syncthreads();
+    for (int i = tid; i < g * (s.w + s.h); i += kThreads) {
+      const int j = i / (s.w + s.h), k = i - j * (s.w + s.h);
+      affine_tables(reinterpret_cast<const double*>(base + (size_t)j * per), s.h, s.w,
+                    reinterpret_cast<int*>(base + (size_t)j * per + 48), k);
+    }
+    __syncthreads();
+    for (int i = tid; i < g * hw; i += kThreads) {
+      const int j = i / hw, px = i - j * hw;
+      const int y = px / s.w, x = px - y * s.w;
+      float a, b, c;
+      warp_pixel(src + (size_t)j * s.in_bytes, T, reinterpret_cast<const int*>(base + (size_t)j * per + 48), s.h, s.w, y, x, a, b, c);
+      const uint32_t o = q255_f32(a) | (q255_f32(b) << 8) | (q255_f32(c) << 16);
+      uint8_t* op = dst + (size_t)j * s.out_bytes + px * 3;
+      op[0] = (uint8_t)o; op[1] = (uint8_t)(o >> 8); op[2] = (uint8_t)(o >> 16);
+    }
+  }
+};
+
+struct OpCcElasticFast : NoSpill, ElasticCommon {
+  using Params = ElasticParams;
+  static constexpr int kStages = 2, kOutBufs = 1;
+  static constexpr int kMinBlocks = 3;   // 256 threads x 3 CTAs: <= 80 registers
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kThreads = 256;
+  static constexpr int kStrip = 8;
+  static constexpr int kQueue = 63;      // smoothing replays (per image)
+  static constexpr int kQueue2 = 255;    // bilinear replays (per image)
+  __host__ __device__ static constexpr int pitch(int n) { return n | 1; }   // odd pitch of the transposed planes
+  // T32 | Wg | Mi | affine tables | F0 [2][hw] f64 | F1T [2][w][pitch(h)] f64 | DXYT [2][w][pitch(h)] f32 | queues | columns
+  static size_t scratch_bytes(const Shape& s, int) {
+    return 1024 + 256 + 48 + (size_t)(s.h + s.w) * 8 + (size_t)s.h * s.w * 16 + (size_t)2 * s.w * pitch(s.h) * 12 +
+           (kQueue + 1) * 4 + (kQueue2 + 1) * 4 + (kThreads / 32) * (2 * kMaxLw + 1) * 8 + 32;
+  }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    float* T = reinterpret_cast<float*>(scratch);
+    double* Wg = reinterpret_cast<double*>(scratch + 1024);
+    for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
+    for (int i = threadIdx.x; i <= p.lw; i += kThreads) Wg[i] = p.w[i];
+    __syncthreads();
   }
 
   // 8 consecutive outputs of one line: out[o] = sum_k w[|k|] * in[refl(s0 + o + k)].  The 8-entry input window rotates
@@ -265,6 +386,29 @@ struct OpCcElasticFast : NoSpill {
     }
   }
 
+  // literal scipy map_coordinates(order=1, mode='reflect') of one pixel of the float32 warped image W at float32 (yy, xx)
+  __device__ static __noinline__ uint32_t bilinear_exact(const float* W, int h, int w, float yyf, float xxf) {
+    const double yy = (double)yyf, xx = (double)xxf;
+    const double fy0 = floor(yy), fx0 = floor(xx);
+    const double ty = yy - fy0, tx = xx - fx0, uy = 1 - ty, ux = 1 - tx;
+    const int y0 = (int)fy0, x0 = (int)fx0;
+    const int ya = refl_half_any(y0, h), yb = refl_half_any(y0 + 1, h), xa = refl_half_any(x0, w), xb = refl_half_any(x0 + 1, w);
+    const float* q00 = W + (ya * w + xa) * 3;
+    const float* q01 = W + (ya * w + xb) * 3;
+    const float* q10 = W + (yb * w + xa) * 3;
+    const float* q11 = W + (yb * w + xb) * 3;
+    uint32_t o = 0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      double acc = ((double)q00[c] * uy) * ux;
+      acc = acc + ((double)q01[c] * uy) * tx;
+      acc = acc + ((double)q10[c] * ty) * ux;
+      acc = acc + ((double)q11[c] * ty) * tx;
+      o |= q255_f32((float)acc) << (8 * c);
+    }
+    return o;
+  }
+
   // literal scipy order at one point of the field F (h x w doubles)
   __device__ static __noinline__ double literal(const double* F, const double* Wg, int lw, int h, int w, int y, int x) {
     double col[2 * kMaxLw + 1];
@@ -283,94 +427,28 @@ struct OpCcElasticFast : NoSpill {
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
                              uint8_t* scratch, uint8_t*) {
     const int tid = threadIdx.x;
-    const int hw = s.h * s.w;
+    const int hw = s.h * s.w, ph = pitch(s.h), plane = s.w * ph;
     const float* T = reinterpret_cast<const float*>(scratch);
     const double* Wg = reinterpret_cast<const double*>(scratch + 1024);
-    double* Ms = reinterpret_cast<double*>(scratch + 1024 + 256);       // [kMaxG][6] inverse matrices
-    double* F0 = Ms + kMaxG * 6;                                         // [2][hw] raw fields (x, y)
-    double* F1 = F0 + 2 * hw;                                            // [2][hw] after the y pass
-    float* DXY = reinterpret_cast<float*>(F1 + 2 * hw);                  // [2][hw] f32 displacements
-    double* Wd = F0;                                                     // warped image, HWC f64 (aliases F0/F1: 24 <= 32 B/px)
-    int* qn = reinterpret_cast<int*>(DXY + 2 * hw);                      // replay queue: counter, entries, column scratch
+    double* Mi = reinterpret_cast<double*>(scratch + 1024 + 256);
+    int* tab = reinterpret_cast<int*>(Mi + 6);
+    double* F0 = reinterpret_cast<double*>(tab + 2 * (s.h + s.w));     // [2][hw] raw fields (x, y); (h + w) * 8 keeps alignment
+    double* F1T = F0 + 2 * hw;                                          // [2][w][ph] after the y pass, transposed
+    float* DXYT = reinterpret_cast<float*>(F1T + 2 * plane);            // [2][w][ph] f32 displacements, transposed
+    float* Wf = reinterpret_cast<float*>(F0);                           // warped image, HWC f32 (aliases F0: 12 <= 16 B/px)
+    int* qn = reinterpret_cast<int*>(DXYT + 2 * plane);                 // smoothing replay queue
     int* queue = qn + 1;
-    double* qcols = reinterpret_cast<double*>(queue + kQueue);     // 1 + 63 ints = 256 bytes: stays 8-byte aligned
+    int* q2n = queue + kQueue;                                          // bilinear replay queue
+    int* queue2 = q2n + 1;
+    double* qcols = reinterpret_cast<double*>(queue2 + kQueue2);        // (64 + 256) ints: stays 8-byte aligned
     const Philox rng(p.seed);
     const double tol = 4e-14 * fmax(1.0, fabs(p.alpha));
-    __syncthreads();
-    if (tid < g) {
-      const int64_t img = img0 + tid;
-      double M[6];
-      if (p.M) {
-        for (int k = 0; k < 6; ++k) M[k] = p.M[img * 6 + k];
-      } else {
-        const float cs = (float)(s.h / 2), q = (float)(s.h / 3);
-        const float p1[3][2] = {{cs + q, cs + q}, {cs + q, cs - q}, {cs - q, cs - q}};
-        double p2[3][2];
-        const uint4 r0 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 0u);
-        const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 1u);
-        const uint32_t rr[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y};
-        for (int k = 0; k < 6; ++k)
-          p2[k / 2][k % 2] = (double)(p1[k / 2][k % 2] + (float)(-p.c2 + 2.0 * p.c2 * (double)u01(rr[k])));
-        const double x0 = p1[0][0], y0 = p1[0][1], x1 = p1[1][0], y1 = p1[1][1], x2 = p1[2][0], y2 = p1[2][1];
-        const double det = x0 * (y1 - y2) - y0 * (x1 - x2) + (x1 * y2 - x2 * y1);
-        for (int rrow = 0; rrow < 2; ++rrow) {
-          const double u0 = p2[0][rrow], u1 = p2[1][rrow], u2 = p2[2][rrow];
-          M[rrow * 3 + 0] = (u0 * (y1 - y2) - y0 * (u1 - u2) + (u1 * y2 - u2 * y1)) / det;
-          M[rrow * 3 + 1] = (x0 * (u1 - u2) - u0 * (x1 - x2) + (x1 * u2 - x2 * u1)) / det;
-          M[rrow * 3 + 2] = (x0 * (y1 * u2 - y2 * u1) - y0 * (x1 * u2 - x2 * u1) + u0 * (x1 * y2 - x2 * y1)) / det;
-        }
-      }
-      double D = M[0] * M[4] - M[1] * M[3];
-      D = D != 0.0 ? 1.0 / D : 0.0;
-      const double A11 = M[4] * D, A22 = M[0] * D;
-      M[0] = A11; M[1] *= -D; M[3] *= -D; M[4] = A22;
-      const double b1 = -M[0] * M[2] - M[1] * M[5];
-      const double b2 = -M[3] * M[2] - M[4] * M[5];
-      M[2] = b1; M[5] = b2;
-      for (int k = 0; k < 6; ++k) Ms[tid * 6 + k] = M[k];
-    }
-    if (p.alpha == 0.0) {
-      // alpha == 0 (severity 1 of the CIFAR table): the displacement is (float)(field * 0) = +-0 everywhere, so the bilinear
-      // stage samples at integer coordinates with ty = tx = 0 and returns the warped image itself:
-      // (q00*1)*1 + (q01*1)*0 + (q10*0)*1 + (q11*0)*0 == q00 for finite fields.  Only the affine warp is left.
-      __syncthreads();
-      for (int i = tid; i < g * hw; i += kThreads) {
-        const int j = i / hw, px = i - j * hw;
-        const int y = px / s.w, x = px - y * s.w;
-        const uint8_t* im = src + (size_t)j * s.in_bytes;
-        const double* Mi = Ms + j * 6;
-        const int adelta = (int)rint(Mi[0] * (double)x * 1024), bdelta = (int)rint(Mi[3] * (double)x * 1024);
-        const int X0 = (int)rint((Mi[1] * (double)y + Mi[2]) * 1024) + 16;
-        const int Y0 = (int)rint((Mi[4] * (double)y + Mi[5]) * 1024) + 16;
-        const int X = (X0 + adelta) >> 5, Y = (Y0 + bdelta) >> 5;
-        const int sx = X >> 5, sy = Y >> 5;
-        const float fx = __fmul_rn((float)(X & 31), 0.03125f), fy = __fmul_rn((float)(Y & 31), 0.03125f);
-        const float wx0 = __fsub_rn(1.0f, fx), wy0 = __fsub_rn(1.0f, fy);
-        const float w00 = __fmul_rn(wy0, wx0), w01 = __fmul_rn(wy0, fx), w10 = __fmul_rn(fy, wx0), w11 = __fmul_rn(fy, fx);
-        const int ya = refl101_any(sy, s.h), yb = refl101_any(sy + 1, s.h), xa = refl101_any(sx, s.w), xb = refl101_any(sx + 1, s.w);
-        const uint32_t c00 = load_rgb(im, (ya * s.w + xa) * 3), c01 = load_rgb(im, (ya * s.w + xb) * 3);
-        const uint32_t c10 = load_rgb(im, (yb * s.w + xa) * 3), c11 = load_rgb(im, (yb * s.w + xb) * 3);
-        uint32_t o = 0;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          float acc = __fmul_rn(T[(c00 >> (8 * c)) & 255u], w00);
-          acc = __fadd_rn(acc, __fmul_rn(T[(c01 >> (8 * c)) & 255u], w01));
-          acc = __fadd_rn(acc, __fmul_rn(T[(c10 >> (8 * c)) & 255u], w10));
-          acc = __fadd_rn(acc, __fmul_rn(T[(c11 >> (8 * c)) & 255u], w11));
-          const float v = acc < 0.0f ? 0.0f : (acc > 1.0f ? 1.0f : acc);
-          o |= (uint32_t)__float2int_rz(__fmul_rn(v, 255.0f)) << (8 * c);
-        }
-        uint8_t* op = dst + (size_t)j * s.out_bytes + px * 3;
-        op[0] = (uint8_t)o; op[1] = (uint8_t)(o >> 8); op[2] = (uint8_t)(o >> 16);
-      }
-      return;
-    }
     for (int j = 0; j < g; ++j) {
       const int64_t img = img0 + j;
       const uint8_t* im = src + (size_t)j * s.in_bytes;
       uint8_t* om = dst + (size_t)j * s.out_bytes;
-      __syncthreads();  // previous image's bilinear stage has finished reading Wd / DXY
-      if (tid == 0) *qn = 0;
+      __syncthreads();  // previous image's bilinear stage has finished reading Wf / DXYT / queues
+      if (tid == 0) { *qn = 0; *q2n = 0; inverse_matrix(p, rng, img, s.h, Mi); }
       // ---- raw fields: F0[0] = ux, F0[1] = uy ----
       if (p.ux) {
         for (int i = tid; i < 2 * hw; i += kThreads) F0[i] = i < hw ? p.ux[img * hw + i] : p.uy[img * hw + (i - hw)];
@@ -385,35 +463,40 @@ struct OpCcElasticFast : NoSpill {
         }
       }
       __syncthreads();
+      if (tid < s.w + s.h) affine_tables(Mi, s.h, s.w, tab, tid);   // h + w <= 128 < kThreads
       if (p.lw < 0) {
-        for (int i = tid; i < 2 * hw; i += kThreads) DXY[i] = (float)(F0[i] * p.alpha);
+        for (int i = tid; i < 2 * hw; i += kThreads) {
+          const int f = i >= hw, px = i - f * hw, y = px / s.w, x = px - y * s.w;
+          DXYT[f * plane + x * ph + y] = (float)(F0[i] * p.alpha);
+        }
       } else {
-        // y pass: item = (field, column x, strip of 8 rows)
+        // y pass: item = (field, strip of 8 rows, column x), x fastest -> F1T[f][x][y]
         const int sy = (s.h + kStrip - 1) / kStrip, sx = (s.w + kStrip - 1) / kStrip;
         for (int item = tid; item < 2 * s.w * sy; item += kThreads) {
           const int f = item / (s.w * sy), r = item - f * s.w * sy, st = r / s.w, x = r - st * s.w;
           double acc[kStrip];
           strip(F0 + f * hw + x, s.w, s.h, st * kStrip, Wg, p.lw, acc);
+          double* o = F1T + f * plane + x * ph + st * kStrip;
 #pragma unroll
-          for (int o = 0; o < kStrip; ++o)
-            if (st * kStrip + o < s.h) F1[f * hw + (st * kStrip + o) * s.w + x] = acc[o];
+          for (int k = 0; k < kStrip; ++k)
+            if (st * kStrip + k < s.h) o[k] = acc[k];
         }
         __syncthreads();
-        // x pass: item = (field, row y, strip of 8 columns) -> f32 displacement
+        // x pass: item = (field, strip of 8 columns, row y), y fastest -> f32 displacement DXYT[f][x][y]
         for (int item = tid; item < 2 * s.h * sx; item += kThreads) {
-          const int f = item / (s.h * sx), r = item - f * s.h * sx, y = r / sx, st = r - y * sx;
+          const int f = item / (s.h * sx), r = item - f * s.h * sx, st = r / s.h, y = r - st * s.h;
           double acc[kStrip];
-          strip(F1 + f * hw + y * s.w, 1, s.w, st * kStrip, Wg, p.lw, acc);
+          strip(F1T + f * plane + y, ph, s.w, st * kStrip, Wg, p.lw, acc);
 #pragma unroll
-          for (int o = 0; o < kStrip; ++o) {
-            const int x = st * kStrip + o;
+          for (int k = 0; k < kStrip; ++k) {
+            const int x = st * kStrip + k;
             if (x < s.w) {
-              const double t = acc[o] * p.alpha;
-              DXY[f * hw + y * s.w + x] = (float)t;
+              const double t = acc[k] * p.alpha;
+              DXYT[f * plane + x * ph + y] = (float)t;
               if ((float)(t - tol) != (float)(t + tol)) {     // too close to a float32 rounding boundary: replay literally
                 const int slot = atomicAdd(qn, 1);
                 if (slot < kQueue) queue[slot] = (f << 24) | (y << 12) | x;
-                else DXY[f * hw + y * s.w + x] = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
+                else DXYT[f * plane + x * ph + y] = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
               }
             }
           }
@@ -436,60 +519,56 @@ struct OpCcElasticFast : NoSpill {
           if ((tid & 31) == 0) {
             double a = col[p.lw] * Wg[0];
             for (int k = p.lw; k >= 1; --k) a = a + (col[p.lw - k] + col[p.lw + k]) * Wg[k];
-            DXY[f * hw + y * s.w + x] = (float)(a * p.alpha);
+            DXYT[f * plane + x * ph + y] = (float)(a * p.alpha);
           }
           __syncwarp();
         }
       }
       __syncthreads();
-      // ---- affine warp (cv2.warpAffine arithmetic) into Wd ----
-      const double* Mi = Ms + j * 6;
+      // ---- affine warp (cv2.warpAffine arithmetic) into Wf (F0 is dead from here on) ----
       for (int px = tid; px < hw; px += kThreads) {
         const int y = px / s.w, x = px - y * s.w;
-        const int adelta = (int)rint(Mi[0] * (double)x * 1024), bdelta = (int)rint(Mi[3] * (double)x * 1024);
-        const int X0 = (int)rint((Mi[1] * (double)y + Mi[2]) * 1024) + 16;
-        const int Y0 = (int)rint((Mi[4] * (double)y + Mi[5]) * 1024) + 16;
-        const int X = (X0 + adelta) >> 5, Y = (Y0 + bdelta) >> 5;
-        const int sx = X >> 5, sy = Y >> 5;
-        const float fx = __fmul_rn((float)(X & 31), 0.03125f), fy = __fmul_rn((float)(Y & 31), 0.03125f);
-        const float wx0 = __fsub_rn(1.0f, fx), wy0 = __fsub_rn(1.0f, fy);
-        const float w00 = __fmul_rn(wy0, wx0), w01 = __fmul_rn(wy0, fx), w10 = __fmul_rn(fy, wx0), w11 = __fmul_rn(fy, fx);
-        const int ya = refl101_any(sy, s.h), yb = refl101_any(sy + 1, s.h), xa = refl101_any(sx, s.w), xb = refl101_any(sx + 1, s.w);
-        const uint32_t c00 = load_rgb(im, (ya * s.w + xa) * 3), c01 = load_rgb(im, (ya * s.w + xb) * 3);
-        const uint32_t c10 = load_rgb(im, (yb * s.w + xa) * 3), c11 = load_rgb(im, (yb * s.w + xb) * 3);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          float acc = __fmul_rn(T[(c00 >> (8 * c)) & 255u], w00);
-          acc = __fadd_rn(acc, __fmul_rn(T[(c01 >> (8 * c)) & 255u], w01));
-          acc = __fadd_rn(acc, __fmul_rn(T[(c10 >> (8 * c)) & 255u], w10));
-          acc = __fadd_rn(acc, __fmul_rn(T[(c11 >> (8 * c)) & 255u], w11));
-          Wd[px * 3 + c] = (double)acc;
-        }
+        float a, b, c;
+        warp_pixel(im, T, tab, s.h, s.w, y, x, a, b, c);
+        Wf[px * 3] = a; Wf[px * 3 + 1] = b; Wf[px * 3 + 2] = c;
       }
       __syncthreads();
-      // ---- bilinear resampling at (y + dy, x + dx): scipy map_coordinates order-1 arithmetic ----
+      // ---- bilinear resampling at (y + dy, x + dx): float32 evaluation, literal replay near integers ----
       for (int px = tid; px < hw; px += kThreads) {
         const int y = px / s.w, x = px - y * s.w;
-        const double yy = (double)__fadd_rn((float)y, DXY[hw + px]), xx = (double)__fadd_rn((float)x, DXY[px]);
-        const double fy0 = floor(yy), fx0 = floor(xx);
-        const double ty = yy - fy0, tx = xx - fx0, uy = 1 - ty, ux = 1 - tx;
+        const float yy = __fadd_rn((float)y, DXYT[plane + x * ph + y]), xx = __fadd_rn((float)x, DXYT[x * ph + y]);
+        const float fy0 = floorf(yy), fx0 = floorf(xx);
+        const float ty = __fsub_rn(yy, fy0), tx = __fsub_rn(xx, fx0), uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
         const int y0 = (int)fy0, x0 = (int)fx0;
         const int ya = refl_half_any(y0, s.h), yb = refl_half_any(y0 + 1, s.h), xa = refl_half_any(x0, s.w), xb = refl_half_any(x0 + 1, s.w);
-        const double* q00 = Wd + (ya * s.w + xa) * 3;
-        const double* q01 = Wd + (ya * s.w + xb) * 3;
-        const double* q10 = Wd + (yb * s.w + xa) * 3;
-        const double* q11 = Wd + (yb * s.w + xb) * 3;
+        const float* q00 = Wf + (ya * s.w + xa) * 3;
+        const float* q01 = Wf + (ya * s.w + xb) * 3;
+        const float* q10 = Wf + (yb * s.w + xa) * 3;
+        const float* q11 = Wf + (yb * s.w + xb) * 3;
+        const float w00 = uy * ux, w01 = uy * tx, w10 = ty * ux, w11 = ty * tx;
         uint32_t o = 0;
+        float dist = 1.0f;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          double acc = (q00[c] * uy) * ux;
-          acc = acc + (q01[c] * uy) * tx;
-          acc = acc + (q10[c] * ty) * ux;
-          acc = acc + (q11[c] * ty) * tx;
-          float v = (float)acc;
-          v = v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v);
-          o |= (uint32_t)__float2int_rz(__fmul_rn(v, 255.0f)) << (8 * c);
+          const float acc = fmaf(q11[c], w11, fmaf(q10[c], w10, fmaf(q01[c], w01, q00[c] * w00)));
+          const float r = acc * 255.0f;
+          dist = fminf(dist, fabsf(r - rintf(r)));
+          o |= (uint32_t)min(max(__float2int_rz(r), 0), 255) << (8 * c);
         }
+        if (!(dist >= 1e-3f)) {    // also catches NaN (injected fields)
+          const int slot = atomicAdd(q2n, 1);
+          if (slot < kQueue2) queue2[slot] = px;
+          else o = bilinear_exact(Wf, s.h, s.w, yy, xx);
+        }
+        uint8_t* op = om + px * 3;
+        op[0] = (uint8_t)o; op[1] = (uint8_t)(o >> 8); op[2] = (uint8_t)(o >> 16);
+      }
+      __syncthreads();
+      const int n2 = min(*q2n, kQueue2);
+      for (int e = tid; e < n2; e += kThreads) {
+        const int px = queue2[e], y = px / s.w, x = px - y * s.w;
+        const float yy = __fadd_rn((float)y, DXYT[plane + x * ph + y]), xx = __fadd_rn((float)x, DXYT[x * ph + y]);
+        const uint32_t o = bilinear_exact(Wf, s.h, s.w, yy, xx);
         uint8_t* op = om + px * 3;
         op[0] = (uint8_t)o; op[1] = (uint8_t)(o >> 8); op[2] = (uint8_t)(o >> 16);
       }
@@ -707,6 +786,8 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed;
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
+  if (alpha == 0.0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out))
+    return launch_image_op<OpCcAffineWarp>(in, out, n, shp, p, (cudaStream_t)stream);   // zero displacement: the warp alone
   if (lw <= std::min(h, w) && (h * w) % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out)) {
     // four CTAs per SM
     const int target = 128 + 3 * 1 * shp.in_bytes + (int)OpCcElasticFast::scratch_bytes(shp, 1) + 512;  // one image per group
