@@ -716,24 +716,46 @@ __device__ __forceinline__ void make_line_geom(LineGeom* gm, const int* offs /* 
     x0 = min(x0, __shfl_xor_sync(0xffffffffu, x0, o)); x1 = max(x1, __shfl_xor_sync(0xffffffffu, x1, o));
     y0 = min(y0, __shfl_xor_sync(0xffffffffu, y0, o)); y1 = max(y1, __shfl_xor_sync(0xffffffffu, y1, o));
   }
-  const int pw = w + (x1 - x0), ph = h + (y1 - y0);
+  x0 = -((-x0 + 3) & ~3);                                        // left border: a multiple of 4 pixels, so image words stay words
+  const int pw = (w + (x1 - x0) + 3) & ~3, ph = h + (y1 - y0);   // row pitch in bytes is a multiple of 4 for any CH
   if (lane == 0) { gm->dxmin = x0; gm->dymin = y0; gm->pw = pw; gm->ph = ph; }
   for (int i = lane; i < width; i += 32) gm->off[i] = ((offs[2 * i + 1] - y0) * pw + (offs[2 * i] - x0)) * CH;
 }
 
-// edge-replicated canvas of one image (all threads of the CTA: `tid` of `nt`)
+// edge-replicated canvas of one image (all threads of the CTA: `tid` of `nt`): one warp per canvas row, one lane per canvas
+// word.  The left border is a multiple of 4 pixels and w % 4 == 0, so the image part of a row is a plain word copy and the
+// borders are the 3-word (CH = 3) or 1-word (CH = 1) pattern of the replicated edge pixel.  `im` must be 4-byte aligned.
 template <int CH>
 __device__ __forceinline__ void fill_canvas(uint8_t* canvas, const uint8_t* im, const LineGeom& gm, int w, int h, int tid, int nt) {
-  // one warp per canvas row, lanes over x (no division by the per-image canvas width)
+  static_assert(CH == 1 || CH == 3, "pattern words are written for 1 or 3 channels");
   const int lane = tid & 31, warp = tid >> 5, nw = nt >> 5;
+  const int wpr = (gm.pw * CH) >> 2, lw = (-gm.dxmin * CH) >> 2, iw = (w * CH) >> 2;
+  const uint32_t* im32 = reinterpret_cast<const uint32_t*>(im);
+  uint32_t* c32 = reinterpret_cast<uint32_t*>(canvas);
   for (int py = warp; py < gm.ph; py += nw) {
     const int sy = min(max(py + gm.dymin, 0), h - 1);
-    for (int px = lane; px < gm.pw; px += 32) {
-      const int sx = min(max(px + gm.dxmin, 0), w - 1);
-      const uint8_t* q = im + (sy * w + sx) * CH;
-      uint8_t* o = canvas + (py * gm.pw + px) * CH;
-#pragma unroll
-      for (int c = 0; c < CH; ++c) o[c] = q[c];
+    const uint32_t* row = im32 + sy * iw;
+    uint32_t L[3], R[3];
+    if (CH == 3) {
+      const uint32_t a = row[0] & 0x00FFFFFFu, b = row[iw - 1] >> 8;
+      pack_rgb4(a, a, a, a, L[0], L[1], L[2]);
+      pack_rgb4(b, b, b, b, R[0], R[1], R[2]);
+    } else {
+      L[0] = L[1] = L[2] = (row[0] & 255u) * 0x01010101u;
+      R[0] = R[1] = R[2] = (row[iw - 1] >> 24) * 0x01010101u;
+    }
+    for (int q = lane; q < wpr; q += 32) {
+      uint32_t v;
+      if (q < lw) {
+        const int m = CH == 3 ? q % 3 : 0;
+        v = m == 0 ? L[0] : (m == 1 ? L[1] : L[2]);
+      } else if (q < lw + iw) {
+        v = row[q - lw];
+      } else {
+        const int m = CH == 3 ? (q - lw - iw) % 3 : 0;
+        v = m == 0 ? R[0] : (m == 1 ? R[1] : R[2]);
+      }
+      c32[py * wpr + q] = v;
     }
   }
 }
@@ -766,29 +788,47 @@ __device__ __forceinline__ uint32_t line_blur_word(const uint8_t* canvas, const 
 // float32, which differs from the ordered sum by less than 4e-4 (every partial sum is below 256, so each of the <= 25 + 19 roundings
 // is at most 2^-17, plus the products, the dropped tail and the rounding of acc + 0.5), and an output is only trusted when
 // acc + 0.5 is at least 5e-4 away from an integer; the other words (about 0.4 %) are queued and replayed literally.
-template <int CH>
-__device__ __forceinline__ uint32_t line_blur_word_fast(const uint8_t* canvas, const LineGeom& gm, const float* k, int n_eff,
-                                                        int rowb, int ob, bool& amb) {
+template <int CH, int NW>
+__device__ __forceinline__ void line_blur_words_fast(const uint8_t* canvas, const LineGeom& gm, const float* k, int n_eff,
+                                                     int rowb, int ob, uint32_t* out /* NW words */, bool& amb) {
   const int y = ob / rowb, xb = ob - y * rowb;
   const uint32_t* c32 = reinterpret_cast<const uint32_t*>(canvas);   // canvas is 16-byte aligned
   const int base = y * gm.pw * CH + xb;
-  float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+  float a[4 * NW];
+#pragma unroll
+  for (int e = 0; e < 4 * NW; ++e) a[e] = 0.0f;
   for (int i = 0; i < n_eff; ++i) {
     const int bo = base + gm.off[i];
     const uint32_t* wp = c32 + (bo >> 2);
-    const uint32_t v = __funnelshift_r(wp[0], wp[1], (uint32_t)bo << 3);
     const float wt = k[i];
-    a0 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440u)), 8388608.0f), wt, a0);
-    a1 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7441u)), 8388608.0f), wt, a1);
-    a2 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7442u)), 8388608.0f), wt, a2);
-    a3 = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7443u)), 8388608.0f), wt, a3);
+    uint32_t w[NW + 1];
+#pragma unroll
+    for (int q = 0; q <= NW; ++q) w[q] = wp[q];
+#pragma unroll
+    for (int q = 0; q < NW; ++q) {
+      const uint32_t v = __funnelshift_r(w[q], w[q + 1], (uint32_t)bo << 3);
+      a[4 * q + 0] = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7440u)), 8388608.0f), wt, a[4 * q + 0]);
+      a[4 * q + 1] = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7441u)), 8388608.0f), wt, a[4 * q + 1]);
+      a[4 * q + 2] = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7442u)), 8388608.0f), wt, a[4 * q + 2]);
+      a[4 * q + 3] = fmaf(__fsub_rn(__uint_as_float(__byte_perm(v, 0x4B000000u, 0x7443u)), 8388608.0f), wt, a[4 * q + 3]);
+    }
   }
-  const float r0 = a0 + 0.5f, r1 = a1 + 0.5f, r2 = a2 + 0.5f, r3 = a3 + 0.5f;
-  const float f0 = floorf(r0), f1 = floorf(r1), f2 = floorf(r2), f3 = floorf(r3);
-  const float d0 = fabsf(r0 - f0 - 0.5f), d1 = fabsf(r1 - f1 - 0.5f), d2 = fabsf(r2 - f2 - 0.5f), d3 = fabsf(r3 - f3 - 0.5f);
-  amb = !(fmaxf(fmaxf(d0, d1), fmaxf(d2, d3)) <= 0.4995f);   // distance of the fraction from 1/2 (also true for NaN)
-  const int q0 = min(max((int)f0, 0), 255), q1 = min(max((int)f1, 0), 255), q2 = min(max((int)f2, 0), 255), q3 = min(max((int)f3, 0), 255);
-  return (uint32_t)q0 | ((uint32_t)q1 << 8) | ((uint32_t)q2 << 16) | ((uint32_t)q3 << 24);
+  // round to nearest with the 1.5 * 2^23 magic add: n = rint(acc), frac = acc - n in [-1/2, 1/2]; floor(acc + 1/2) = n unless
+  // acc sits on a tie, which is inside the replay band anyway.  0 <= acc < 255.5, so no clamping is needed.
+  float dmax = 0.0f;
+#pragma unroll
+  for (int q = 0; q < NW; ++q) {
+    uint32_t word = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float t = __fadd_rn(a[4 * q + e], 12582912.0f);
+      const float n = __fsub_rn(t, 12582912.0f);
+      dmax = fmaxf(dmax, fabsf(__fsub_rn(a[4 * q + e], n)));
+      word |= (__float_as_uint(t) & 255u) << (8 * e);
+    }
+    out[q] = word;
+  }
+  amb = !(dmax <= 0.4995f);   // within 5e-4 of a rounding boundary of floor(acc + 1/2) (also true for NaN)
 }
 
 // literal evaluation of output byte `b` from the (unpadded) image with clamped coordinates.  The float32 additions are a
@@ -824,11 +864,12 @@ struct OpCcMotionFast : NoSpill {
   using Params = MotionParams;
   static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
-  static constexpr int kMinBlocks = 2;
+  static constexpr int kMinBlocks = 3;
+  static constexpr int kStages = 2, kOutBufs = 1;   // compute-bound: a shallow ring frees shared memory for a third CTA
   static constexpr int kQueue = 255;
   static constexpr int kHeader = 128 + (kQueue + 1) * 4;   // weights f32[32] | replay queue
   // aux = n_eff: the canvas only has to cover the taps the fast path reads
-  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) * 3 + 8, 16); }
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux + 6) * 3 + 8, 16); }
   // per image: LineGeom + raw offsets (2 x 32 int) + canvas
   __host__ __device__ static size_t per_image(const Shape& s) { return sizeof(LineGeom) + kMaxLine * 2 * 4 + canvas_bytes(s); }
   static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * per_image(s) + 16; }
@@ -870,31 +911,37 @@ struct OpCcMotionFast : NoSpill {
                      *reinterpret_cast<const LineGeom*>(base), s.w, s.h, tid, kThreads);
     }
     __syncthreads();
-    const int wpi = s.in_bytes >> 2, rowb = s.w * 3;
+    constexpr int NW = 3;                                  // 12 bytes = 4 pixels per thread (w % 4 == 0)
+    const int ipi = s.in_bytes / (4 * NW), rowb = s.w * 3;
     uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
-    for (int i = tid; i < g * wpi; i += kThreads) {
-      const int j = i / wpi, wi = i - j * wpi;
+    for (int i = tid; i < g * ipi; i += kThreads) {
+      const int j = i / ipi, ti = i - j * ipi;
       const uint8_t* base = scratch + kHeader + (size_t)j * pi;
       const LineGeom& gm = *reinterpret_cast<const LineGeom*>(base);
       const uint8_t* canvas = base + sizeof(LineGeom) + kMaxLine * 2 * 4;
       // canvas origin: output (0,0) sits at canvas (-dymin, -dxmin); tap offsets are relative to (dymin, dxmin)
       bool amb;
-      uint32_t v = line_blur_word_fast<3>(canvas, gm, k, p.n_eff, rowb, wi * 4, amb);
+      uint32_t v[NW];
+      line_blur_words_fast<3, NW>(canvas, gm, k, p.n_eff, rowb, ti * 4 * NW, v, amb);
       if (amb) {
         const int slot = atomicAdd(qn, 1);
         if (slot < kQueue) queue[slot] = i;
-        else v = line_blur_word_exact<3>(src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)),
-                                         k, p.width, s.w, s.h, wi * 4);
+        else
+          for (int q = 0; q < NW; ++q)
+            v[q] = line_blur_word_exact<3>(src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)),
+                                           k, p.width, s.w, s.h, (ti * NW + q) * 4);
       }
-      d32[(size_t)j * (s.out_bytes >> 2) + wi] = v;
+      uint32_t* o = d32 + (size_t)j * (s.out_bytes >> 2) + ti * NW;
+#pragma unroll
+      for (int q = 0; q < NW; ++q) o[q] = v[q];
     }
     __syncthreads();
     const int nq = min(*qn, kQueue);
-    for (int e = tid; e < 4 * nq; e += kThreads) {   // one thread per byte of the queued words
-      const int i = queue[e >> 2], j = i / wpi, wi = i - j * wpi;
+    for (int e = tid; e < 4 * NW * nq; e += kThreads) {   // one thread per byte of the queued items
+      const int i = queue[e / (4 * NW)], b = e % (4 * NW), j = i / ipi, ti = i - j * ipi;
       const uint8_t* base = scratch + kHeader + (size_t)j * pi;
-      dst[(size_t)j * s.out_bytes + wi * 4 + (e & 3)] = (uint8_t)line_blur_elem_exact<3>(
-          src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.width, s.w, s.h, wi * 4 + (e & 3));
+      dst[(size_t)j * s.out_bytes + ti * 4 * NW + b] = (uint8_t)line_blur_elem_exact<3>(
+          src + (size_t)j * s.in_bytes, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.width, s.w, s.h, ti * 4 * NW + b);
     }
   }
 };
@@ -903,11 +950,12 @@ struct OpCcSnowFast : NoSpill {
   using Params = SnowParams;
   static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
-  static constexpr int kMinBlocks = 2;
+  static constexpr int kMinBlocks = 3;
+  static constexpr int kStages = 2, kOutBufs = 1;   // compute-bound: a shallow ring frees shared memory for a third CTA
   // header: T32[256] | k[32] | ty[64] tx[64] | y0 y1 x0 x1 [64 each, int]        = 1024 + 128 + 512 + 1024
   static constexpr int kQueue = 255;
   static constexpr int kHeader = 1024 + 128 + 512 + 1024 + (kQueue + 1) * 4;   // ... | replay queue
-  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux) + 8, 16); }  // aux = n_eff
+  __host__ __device__ static size_t canvas_bytes(const Shape& s) { return align_up((size_t)(s.h + s.aux) * (s.w + s.aux + 6) + 8, 16); }  // aux = n_eff
   // per image: LineGeom + raw offsets + L0 f32[hw] + L1 u8[hw] + L2 u8[hw] + canvas
   __host__ __device__ static size_t per_image(const Shape& s) {
     return sizeof(LineGeom) + kMaxLine * 2 * 4 + align_up((size_t)s.h * s.w * 6, 16) + canvas_bytes(s);
@@ -1003,27 +1051,33 @@ struct OpCcSnowFast : NoSpill {
     }
     __syncthreads();
     // E. line blur, rounded back to 8 bits (float32 fused evaluation; words near a rounding boundary are replayed literally)
-    const int wpl = hw >> 2;
-    for (int i = tid; i < g * wpl; i += kThreads) {
-      const int j = i / wpl, wi = i - j * wpl;
+    constexpr int NW = 2;                                  // 8 layer bytes per thread (w % 8 == 0, else one word)
+    const int ipl = hw / (4 * NW);
+    for (int i = tid; i < g * ipl; i += kThreads) {
+      const int j = i / ipl, ti = i - j * ipl;
       uint8_t* base = scratch + kHeader + (size_t)j * pi;
       bool amb;
-      uint32_t v = line_blur_word_fast<1>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.n_eff, s.w, wi * 4, amb);
+      uint32_t v[NW];
+      line_blur_words_fast<1, NW>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.n_eff, s.w, ti * 4 * NW, v, amb);
       if (amb) {
         const int slot = atomicAdd(qn, 1);
         if (slot < kQueue) queue[slot] = i;
-        else v = line_blur_word_exact<1>(base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h, wi * 4);
+        else
+          for (int q = 0; q < NW; ++q)
+            v[q] = line_blur_word_exact<1>(base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h,
+                                           (ti * NW + q) * 4);
       }
-      reinterpret_cast<uint32_t*>(base + o_l2)[wi] = v;
+#pragma unroll
+      for (int q = 0; q < NW; ++q) reinterpret_cast<uint32_t*>(base + o_l2)[ti * NW + q] = v[q];
     }
     __syncthreads();
     {
       const int nq = min(*qn, kQueue);
-      for (int e = tid; e < 4 * nq; e += kThreads) {   // one thread per byte of the queued words
-        const int i = queue[e >> 2], j = i / wpl, wi = i - j * wpl;
+      for (int e = tid; e < 4 * NW * nq; e += kThreads) {   // one thread per byte of the queued items
+        const int i = queue[e / (4 * NW)], b = e % (4 * NW), j = i / ipl, ti = i - j * ipl;
         uint8_t* base = scratch + kHeader + (size_t)j * pi;
-        base[o_l2 + wi * 4 + (e & 3)] = (uint8_t)line_blur_elem_exact<1>(
-            base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h, wi * 4 + (e & 3));
+        base[o_l2 + ti * 4 * NW + b] = (uint8_t)line_blur_elem_exact<1>(
+            base + o_l1, reinterpret_cast<const int*>(base + sizeof(LineGeom)), k, p.m.width, s.w, s.h, ti * 4 * NW + b);
       }
     }
     __syncthreads();
@@ -1194,7 +1248,7 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
   shp.aux = p.n_eff;
   if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcMotionFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
-    const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcMotionFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
+    const int target = 128 + 3 * 4 * shp.in_bytes + (int)OpCcMotionFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
     return launch_image_op<OpCcMotionFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
   }
   return launch_image_op<OpCcMotion>(in, out, n, shp, p, (cudaStream_t)stream);
@@ -1216,9 +1270,9 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
   for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
   Shape shp = make_shape(h, w, c, h, w);
   shp.aux = p.m.n_eff;
-  if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
+  if (w % 8 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcSnowFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
-    const int target = 128 + 5 * 4 * shp.in_bytes + (int)OpCcSnowFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
+    const int target = 128 + 3 * 4 * shp.in_bytes + (int)OpCcSnowFast::scratch_bytes(shp, 4) + 512;  // 4 images per group
     return launch_image_op<OpCcSnowFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
   }
   return launch_image_op<OpCcSnow>(in, out, n, shp, p, (cudaStream_t)stream);
