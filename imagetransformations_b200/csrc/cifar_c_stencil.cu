@@ -130,7 +130,7 @@ struct OpCcDefocusFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.exact.ntaps, s.h, s.w, y, x, c); };
-      sweep_sym_stencil<R, BORDER_REFLECT101>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
+      sweep_sym_stencil<R, BORDER_REFLECT101, true>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
     }
   }
 };
@@ -445,7 +445,7 @@ struct OpCcGlassFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.g.w, p.g.lw, s.h, s.w, y, x, c, FINAL); };
-      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
+      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE, false>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
     }
   }
 
@@ -477,23 +477,34 @@ struct OpCcGlassFast : NoSpill {
             const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
             bx = r.x; by = r.y; bx2 = r.z; by2 = r.w;
           }
-          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
-            const int ci = t - 2 * lane;
-            if (lane < Rr && ci >= 0 && ci < Cc) {
-              const int w = s.w - 1 - ci;
-              int dx, dy;
-              if (p.g.deltas) {
+          if (p.g.deltas) {
+            for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+              const int ci = t - 2 * lane;
+              if (lane < Rr && ci >= 0 && ci < Cc) {
+                const int w = s.w - 1 - ci;
                 const int8_t* d = p.g.deltas + ((((img * p.g.iters + it) * Rr + lane) * Cc + ci) << 1);
-                dx = d[0]; dy = d[1];
-              } else {
-                dx = -(int)(((ci < 32 ? bx : bx2) >> (ci & 31)) & 1u);
-                dy = -(int)(((ci < 32 ? by : by2) >> (ci & 31)) & 1u);
+                const int dx = d[0], dy = d[1];
+                const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
+                const uint16_t ta = m[a], tb = m[b];
+                m[a] = tb; m[b] = ta;
               }
-              const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
-              const uint16_t ta = m[a], tb = m[b];
-              m[a] = tb; m[b] = ta;
+              __syncwarp();
             }
-            __syncwarp();
+          } else {
+            // on-chip draws: the bits are consumed from two 64-bit shift registers, the position walks down by one
+            uint64_t BX = (uint64_t)bx | ((uint64_t)bx2 << 32), BY = (uint64_t)by | ((uint64_t)by2 << 32);
+            uint16_t* ma = m + h * s.w + (s.w - 1);
+            const uint32_t first = 2u * (uint32_t)lane, cnt = lane < Rr ? (uint32_t)Cc : 0u;
+            for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+              if ((uint32_t)t - first < cnt) {
+                uint16_t* mb = ma - ((int)((uint32_t)BY & 1u) * s.w + (int)((uint32_t)BX & 1u));
+                BX >>= 1; BY >>= 1;
+                const uint16_t ta = *ma, tb = *mb;
+                *ma = tb; *mb = ta;
+                --ma;
+              }
+              __syncwarp();
+            }
           }
         }
       }
@@ -1144,7 +1155,7 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
           cw[i * (R + 1) + k] = K[2 + i][2 + k];
           mult[i * (R + 1) + k] = (i ? 2 : 1) * (k ? 2 : 1);
         }
-      if (fix_weights(cw, (R + 1) * (R + 1), mult, f.Wt)) {
+      if (fix_weights40(cw, (R + 1) * (R + 1), mult, f.Wt)) {
         // 4 images per group (192 items = 192 threads), three CTAs per SM
         const Shape shp = make_shape(h, w, c, h, w);
         const int target = 128 + 3 * 4 * shp.in_bytes + 4096;
