@@ -51,6 +51,7 @@ _PROTOS = {
     "imgtx_last_error": [],
     "imgtx_device_info": [C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "imgtx_set_tuning": [_int, _int, _int],
+    "imgtx_set_force_exact": [_int],
     "imgtx_pointwise_u8": [_vp, _vp, _i64, _i64, _int, _f, _vp, _vp],
     "imgtx_geometry_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, C.POINTER(GeomRecord), _vp, _vp, _vp],
     "imgtx_enhance_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _f, _vp, _vp],

@@ -57,6 +57,7 @@ struct CcFastParams {
   uint64_t seed;
   int tex_n, tex_h, tex_w;
   int table_words;  // alias table size (noise kinds)
+  int force_exact;  // test knob (imgtx_set_force_exact)
 };
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -337,7 +338,7 @@ struct OpCcBrightnessFast : NoSpill {
       for (int q = 0; q < 4; ++q) {
         bool amb;
         o[q] = pixel(px[q], K, L, amb);
-        if (amb) {
+        if (amb || p.force_exact) {
           const int slot = atomicAdd(qn, 1);
           if (slot < kQueue) queue[slot] = (uint32_t)(4 * t + q);
           else o[q] = cc_brightness_exact(T, px[q], p.p0);
@@ -429,8 +430,8 @@ struct OpCcFrostFast : NoSpill {
 // ---------------------------------------------------------------------------------------------------------------
 // fog with the plasma fractal drawn on chip.  One warp owns an image from start to finish (no block-wide barrier): byte
 // maximum, diamond-square recursion on a float map in shared memory (four uniforms per Philox call), then
-// (x/255 + c0*plasma) * max / (max + c0) in float64 with the division replaced by a multiplication with 1/den and
-// replayed exactly only if the scaled value lies within 1e-9 of an integer.
+// (x/255 + c0*plasma) * max / (max + c0) * 255 as one float32 multiply-add per element, replayed with the float64
+// reference expression only if the value lies within 1e-3 of an integer.
 // ---------------------------------------------------------------------------------------------------------------
 struct OpCcFogFast : NoSpill {
   using Params = CcFastParams;
@@ -528,22 +529,26 @@ struct OpCcFogFast : NoSpill {
       for (int i = lane; i < (s.in_bytes >> 2); i += 32) mx4 = __vmaxu4(mx4, im[i]);
       uint32_t mxb = max(max(mx4 & 255u, (mx4 >> 8) & 255u), max((mx4 >> 16) & 255u, mx4 >> 24));
       for (int o = 16; o > 0; o >>= 1) mxb = max(mxb, __shfl_xor_sync(0xffffffffu, mxb, o));
-      const double mval = T[mxb], den = mval + p.p0, rden = 1.0 / den;
+      const double mval = T[mxb], den = mval + p.p0;
+      // q = (x/255 + c0*pl) * mval/den * 255 = x*S + pl*C: one float32 multiply-add per element (|error| < 2e-4); the
+      // float64 reference expression is evaluated only within 1e-3 of an integer.
+      const float S = (float)(mval / den), C = (float)(255.0 * p.p0 * mval / den);
       plasma_warp(map, lg, (float)p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32));
       for (int t = lane; t < triples; t += 32) {   // 4 pixels = 3 words
         const uint32_t w[3] = {im[3 * t], im[3 * t + 1], im[3 * t + 2]};
         uint32_t o[3] = {0u, 0u, 0u};
-        double cpl[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) cpl[k] = p.p0 * (double)map[4 * t + k];
+        const float4 pl = *reinterpret_cast<const float4*>(map + 4 * t);
+        const float cpl[4] = {pl.x * C, pl.y * C, pl.z * C, pl.w * C};
 #pragma unroll
         for (int b = 0; b < 12; ++b) {
-          const uint32_t x = (w[b >> 2] >> (8 * (b & 3))) & 255u;
-          const double num = (T[x] + cpl[b / 3]) * mval;
-          const double q = (num * rden) * 255.0;
-          int r = floor_magic(q);
-          if (floor_magic(q - 1e-9) != floor_magic(q + 1e-9)) {   // exact replay: np.clip(num / den, 0, 1) * 255
-            double e = num / den;
+          const float fx = __fsub_rn(__uint_as_float(__byte_perm(w[b >> 2], 0x4B000000u, 0x7440u + (b & 3))), 8388608.0f);
+          const float q = fmaf(fx, S, cpl[b / 3]);
+          const float tt = __fadd_rn(q, 12582912.0f);                 // 1.5 * 2^23: the low mantissa bits hold rint(q)
+          const float df = __fsub_rn(q, __fsub_rn(tt, 12582912.0f));   // q - rint(q)
+          int r = (int)(__float_as_uint(tt) & 511u) - (df < 0.0f ? 1 : 0);
+          if (!(fabsf(df) >= 1e-3f) || p.force_exact) {   // exact replay: np.clip(num / den, 0, 1) * 255 in float64
+            const uint32_t x = (w[b >> 2] >> (8 * (b & 3))) & 255u;
+            double e = ((T[x] + p.p0 * (double)map[4 * t + b / 3]) * mval) / den;
             e = e < 0.0 ? 0.0 : (e > 1.0 ? 1.0 : e);
             r = (int)(e * 255.0);
           }

@@ -322,6 +322,7 @@ extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n,
     memset(&f, 0, sizeof(f));
     f.kind = kind; f.p0 = p0; f.p1 = p1; f.a = draws_a_dev; f.b = draws_b_dev; f.seed = seed;
     f.tex_n = kind == IMGTX_CC_FROST ? tex_n : 0; f.tex_h = tex_h; f.tex_w = tex_w;
+    f.force_exact = force_exact();
     if (kind == IMGTX_CC_IMPULSE && !draws_a_dev) return launch_image_op<OpCcImpulseFast>(in, out, n, shp, f, (cudaStream_t)stream);
     if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && (int64_t)h * w * 255 < (1ll << 31))
       return launch_image_op<OpCcContrastFast>(in, out, n, shp, f, (cudaStream_t)stream);

@@ -81,6 +81,7 @@ struct DefocusFastParams {
   DefocusParams exact;
   uint32_t Wt[18];  // (R+1)^2 hi words then (R+1)^2 lo words, [|dy|][|dx|] at stride R+1
   int R;
+  int force_exact;  // test knob (imgtx_set_force_exact)
 };
 
 template <int R>
@@ -130,7 +131,7 @@ struct OpCcDefocusFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.exact.ntaps, s.h, s.w, y, x, c); };
-      sweep_sym_stencil<R, BORDER_REFLECT101, true>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
+      sweep_sym_stencil<R, BORDER_REFLECT101, true>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex, p.force_exact != 0);
     }
   }
 };
@@ -369,6 +370,7 @@ struct OpCcGlass : NoSpill {
 struct GlassFastParams {
   GlassParams g;
   uint32_t Wt[18];
+  int force_exact;  // test knob (imgtx_set_force_exact)
 };
 
 template <int R>
@@ -445,7 +447,7 @@ struct OpCcGlassFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.g.w, p.g.lw, s.h, s.w, y, x, c, FINAL); };
-      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE, false>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
+      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE, false>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex, p.force_exact != 0);
     }
   }
 
@@ -527,6 +529,7 @@ struct OpCcGlassFast : NoSpill {
 constexpr int kMaxLine = 32;
 struct MotionParams {
   int width;
+  int force_exact;         // test knob (imgtx_set_force_exact)
   int n_eff;               // taps 0..n_eff-1 carry all but 2^-20 LSB of the weight (throughput forms; set by fill_motion)
   float k[kMaxLine];
   const int32_t* offsets;  // device (n, width, 2) (dx, dy) or nullptr: angle drawn on chip in [lo, hi] degrees
@@ -934,7 +937,7 @@ struct OpCcMotionFast : NoSpill {
       bool amb;
       uint32_t v[NW];
       line_blur_words_fast<3, NW>(canvas, gm, k, p.n_eff, rowb, ti * 4 * NW, v, amb);
-      if (amb) {
+      if (amb || p.force_exact) {
         const int slot = atomicAdd(qn, 1);
         if (slot < kQueue) queue[slot] = i;
         else
@@ -1070,7 +1073,7 @@ struct OpCcSnowFast : NoSpill {
       bool amb;
       uint32_t v[NW];
       line_blur_words_fast<1, NW>(base + o_cv, *reinterpret_cast<const LineGeom*>(base), k, p.m.n_eff, s.w, ti * 4 * NW, v, amb);
-      if (amb) {
+      if (amb || p.m.force_exact) {
         const int slot = atomicAdd(qn, 1);
         if (slot < kQueue) queue[slot] = i;
         else
@@ -1147,6 +1150,7 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       memset(&f, 0, sizeof(f));
       f.exact = p;
       f.R = R;
+      f.force_exact = force_exact();
       double cw[9];
       int mult[9];
       memset(cw, 0, sizeof(cw));
@@ -1212,6 +1216,7 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
     GlassFastParams f;
     memset(&f, 0, sizeof(f));
     f.g = p;
+    f.force_exact = force_exact();
     bool ok = true;
     if (lw >= 1) {
       double cw[9];
@@ -1245,6 +1250,7 @@ static int fill_motion(MotionParams& m, int width, const float* k_host, const in
   double tail = 0.0;
   while (m.n_eff > 1 && tail + fabs((double)k_host[m.n_eff - 1]) * 255.0 <= 9.5e-7) tail += fabs((double)k_host[--m.n_eff]) * 255.0;
   m.offsets = offsets_dev; m.lo = lo; m.hi = hi; m.seed = seed;
+  m.force_exact = force_exact();
   return IMGTX_OK;
 }
 

@@ -31,6 +31,7 @@ struct ElasticParams {
   const double* uy;
   double c2;
   uint64_t seed;
+  int force_exact;        // test knob (imgtx_set_force_exact)
 };
 
 __device__ __forceinline__ int reflect_half(int i, int n) {  // scipy 'reflect': d c b a | a b c d | d c b a
@@ -493,7 +494,7 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
             if (x < s.w) {
               const double t = acc[k] * p.alpha;
               DXYT[f * plane + x * ph + y] = (float)t;
-              if ((float)(t - tol) != (float)(t + tol)) {     // too close to a float32 rounding boundary: replay literally
+              if ((float)(t - tol) != (float)(t + tol) || p.force_exact) {     // too close to a float32 rounding boundary: replay literally
                 const int slot = atomicAdd(qn, 1);
                 if (slot < kQueue) queue[slot] = (f << 24) | (y << 12) | x;
                 else DXYT[f * plane + x * ph + y] = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
@@ -555,7 +556,7 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
           dist = fminf(dist, fabsf(r - rintf(r)));
           o |= (uint32_t)min(max(__float2int_rz(r), 0), 255) << (8 * c);
         }
-        if (!(dist >= 1e-3f)) {    // also catches NaN (injected fields)
+        if (!(dist >= 1e-3f) || p.force_exact) {    // also catches NaN (injected fields)
           const int slot = atomicAdd(q2n, 1);
           if (slot < kQueue2) queue2[slot] = px;
           else o = bilinear_exact(Wf, s.h, s.w, yy, xx);
@@ -580,7 +581,8 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
 // jpeg_compression
 // ------------------------------------------------------------------------------------------------
 struct JpegParams {
-  int16_t q[2][64];  // luma, chroma quantisation tables (natural order)
+  int16_t q[2][64];   // luma, chroma quantisation tables (natural order)
+  uint32_t rq[2][64]; // floor(2^32 / (8 q)) + 1: (n * rq) >> 32 == n / (8 q) exactly for n < 2^17 (excess < n * 2^-32 < 1 / (8 q))
 };
 
 #define JFIX(x) ((int)((x) * 8192 + 0.5))
@@ -643,9 +645,14 @@ struct OpCcJpeg : NoSpill {
   static constexpr int kThreads = 256;
   // per image: three planes as int32 (Y: hw, Cb/Cr: hw/4 each)
   static size_t per_image(const Shape& s) { return (size_t)s.h * s.w * 6; }
-  static size_t scratch_bytes(const Shape& s, int G) { return (size_t)G * per_image(s) + 16; }
+  static constexpr int kHeader = 2 * 64 * 8;   // quantiser and reciprocal per (table, coefficient), interleaved
+  static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * per_image(s) + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
-  __device__ static void prepare(const Shape&, const Params&, uint8_t*, bool) {}
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+    uint2* qt = reinterpret_cast<uint2*>(scratch);
+    for (int i = threadIdx.x; i < 128; i += kThreads) qt[i] = make_uint2((uint32_t)p.q[i >> 6][i & 63], p.rq[i >> 6][i & 63]);
+    __syncthreads();
+  }
 
   template <bool STAGED>
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
@@ -653,7 +660,8 @@ struct OpCcJpeg : NoSpill {
     const int tid = threadIdx.x;
     const int h = s.h, w = s.w, hw = h * w, ch = h >> 1, cw = w >> 1;
     const int plane_words = hw + 2 * ch * cw;
-    int* planes = reinterpret_cast<int*>(scratch);
+    const uint2* qtab = reinterpret_cast<const uint2*>(scratch);
+    int* planes = reinterpret_cast<int*>(scratch + kHeader);
     __syncthreads();
     // ---- colour conversion + 4:2:0 downsample (one thread per 2x2 quad) ----
     for (int i = tid; i < g * ch * cw; i += kThreads) {
@@ -715,11 +723,10 @@ struct OpCcJpeg : NoSpill {
       fdct8<2>(d);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
-        const int qt = p.q[tq][k * 8 + l], qv = qt << 3;
-        int t = d[k];
-        if (t < 0) { t = -t; t += qv >> 1; t = t >= qv ? t / qv : 0; t = -t; }
-        else { t += qv >> 1; t = t >= qv ? t / qv : 0; }
-        d[k] = t * qt;
+        const uint2 qr = qtab[tq * 64 + k * 8 + l];     // lanes l = 0..7 read consecutive entries
+        const int qt = (int)qr.x, t = d[k];
+        const int qn = (int)__umulhi((uint32_t)(abs(t) + (qt << 2)), qr.y);   // (|t| + 8q/2) / (8q), exact (see JpegParams)
+        d[k] = (t < 0 ? -qn : qn) * qt;
       }
       idct8<1>(d);
 #pragma unroll
@@ -783,7 +790,7 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   IMGTX_CHECK_ARG((ux_dev == nullptr) == (uy_dev == nullptr), "give both displacement fields or none");
   ElasticParams p;
   memset(&p, 0, sizeof(p));
-  p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed;
+  p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed; p.force_exact = force_exact();
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
   if (alpha == 0.0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out))
@@ -807,6 +814,7 @@ extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
       const int v = qtables_host[t * 64 + i];
       IMGTX_CHECK_ARG(v >= 1 && v <= 255, "quantiser out of baseline range");
       p.q[t][i] = (int16_t)v;
+      p.rq[t][i] = (uint32_t)((1ull << 32) / (uint64_t)(8 * v)) + 1u;
     }
   return launch_image_op<OpCcJpeg>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 80 * 1024);
 }

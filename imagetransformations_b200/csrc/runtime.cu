@@ -38,6 +38,8 @@ int max_smem_optin() {
   return g_dev.smem > 0 ? g_dev.smem : 232448;
 }
 
+static std::atomic<int> g_force_exact{0};
+int force_exact() { return g_force_exact; }
 static std::atomic<int> g_target_smem{56 * 1024};
 static std::atomic<int> g_stages{3};
 static std::atomic<int> g_ctas_per_sm{4};
@@ -65,6 +67,10 @@ extern "C" int imgtx_device_info(int* sms, int* smem) {
   IMGTX_CUDA_OK(cudaGetDevice(&dev));
   if (sms) *sms = imgtx::sm_count();
   if (smem) *smem = imgtx::max_smem_optin();
+  return IMGTX_OK;
+}
+extern "C" int imgtx_set_force_exact(int on) {
+  imgtx::g_force_exact = on ? 1 : 0;
   return IMGTX_OK;
 }
 extern "C" int imgtx_set_tuning(int target_smem, int stages, int ctas_per_sm) {

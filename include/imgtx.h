@@ -46,6 +46,11 @@ const char* imgtx_last_error(void);
 int imgtx_device_info(int* sm_count, int* max_smem_per_block);
 /* Tuning knobs of the staged (TMA) image pipeline; <=0 keeps the current value. */
 int imgtx_set_tuning(int target_smem_bytes, int stages, int ctas_per_sm);
+/* Test knob (process-wide, default 0).  The CIFAR-10-C-style kernels decide most bytes with a fixed-point or float32 evaluation
+   and replay the reference's literal arithmetic only near a rounding boundary; with on = 1 every element takes the literal
+   replay, so tests can check that both routes give the same bytes (also for on-chip random draws, where no CPU oracle has
+   the same draws). */
+int imgtx_set_force_exact(int on);
 
 /* ---- pointwise uint8 maps (256-entry LUT built with the library's exact f32 formula) -------- */
 typedef enum {

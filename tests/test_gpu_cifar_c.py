@@ -227,3 +227,21 @@ def test_pixelate_gather_form_shapes(cuda, hw, c):
     assert rc == 0
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), CC.pixelate(x, c))
+
+
+@pytest.mark.parametrize("name", ["brightness", "fog", "defocus_blur", "glass_blur", "motion_blur", "snow", "elastic_transform"])
+def test_fast_path_equals_literal_replay(cuda, name):
+    """Every kernel that decides bytes with a fixed-point / float32 evaluation must agree with its own literal replay on the
+    same on-chip draws: run the suite pass twice, the second time with every element forced through the replay."""
+    from imagetransformations_b200 import _lib as L
+    C = _C()
+    lib = L.load()
+    x = torch.from_numpy(np.concatenate([imgs(3, 40), np.zeros((1, 32, 32, 3), np.uint8), np.full((1, 32, 32, 3), 255, np.uint8)])).cuda()
+    for sev in (1, 3, 5):
+        fast = C.corrupt(x, name, sev, seed=11).cpu().numpy()
+        L.check(lib.imgtx_set_force_exact(1))
+        try:
+            lit = C.corrupt(x, name, sev, seed=11).cpu().numpy()
+        finally:
+            L.check(lib.imgtx_set_force_exact(0))
+        assert np.array_equal(fast, lit), f"{name}/{sev}: {int((fast != lit).sum())} bytes differ"
