@@ -352,17 +352,46 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
   static constexpr int kQueue = 63;      // smoothing replays (per image)
   static constexpr int kQueue2 = 255;    // bilinear replays (per image)
   __host__ __device__ static constexpr int pitch(int n) { return n | 1; }   // odd pitch of the transposed planes
-  // T32 | Wg | Mi | affine tables | F0 [2][hw] f64 | F1T [2][w][pitch(h)] f64 | DXYT [2][w][pitch(h)] f32 | queues | columns
-  static size_t scratch_bytes(const Shape& s, int) {
-    return 1024 + 256 + 48 + (size_t)(s.h + s.w) * 8 + (size_t)s.h * s.w * 16 + (size_t)2 * s.w * pitch(s.h) * 12 +
-           (kQueue + 1) * 4 + (kQueue2 + 1) * 4 + (kThreads / 32) * (2 * kMaxLw + 1) * 8 + 32;
+  // 32x32 images: the two smoothing passes are dense 32x32x32 float64 products with the folded Gaussian operator
+  // (A[o][i] = sum of the taps that the reflecting border maps onto input i), run on the tensor cores (mma.m8n8k4.f64).
+  // Row pitches are chosen so that every fragment load is conflict-free: 36 doubles for row-fragment operands, 40 for the
+  // column-fragment operand (the raw field).
+  static constexpr int kN = 32, kPA = 36, kPF = 40;
+  __host__ __device__ static bool use_mma(const Shape& s) { return s.h == kN && s.w == kN; }
+  __host__ __device__ static int field_pitch(const Shape& s) { return use_mma(s) ? kPF : s.w; }
+  __host__ __device__ static size_t mid_bytes(const Shape& s) {   // plane pair between the two passes
+    return use_mma(s) ? (size_t)2 * kN * kPA * 8 : (size_t)2 * s.w * pitch(s.h) * 8;
+  }
+  // T32 | Wg | Mi | affine tables | F0 [2][h][field_pitch] f64 | mid planes f64 | DXYT [2][w][pitch(h)] f32 | queues | columns |
+  // folded operator A [32][36] f64 (mma path)
+  __host__ __device__ static size_t scratch_bytes(const Shape& s, int) {
+    return 1024 + 256 + 48 + (size_t)(s.h + s.w) * 8 + (size_t)2 * s.h * field_pitch(s) * 8 + mid_bytes(s) +
+           (size_t)2 * s.w * pitch(s.h) * 4 + (kQueue + 1) * 4 + (kQueue2 + 1) * 4 + (kThreads / 32) * (2 * kMaxLw + 1) * 8 +
+           (use_mma(s) ? (size_t)kN * kPA * 8 : 0) + 32;
+  }
+  __device__ static __forceinline__ double* operator_matrix(const Shape& s, uint8_t* scratch) {
+    return reinterpret_cast<double*>(scratch + scratch_bytes(s, 1) - 32 - (size_t)kN * kPA * 8);
+  }
+  __device__ static __forceinline__ void dmma(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
   }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
-  __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
+  __device__ static void prepare(const Shape& s, const Params& p, uint8_t* scratch, bool) {
     float* T = reinterpret_cast<float*>(scratch);
     double* Wg = reinterpret_cast<double*>(scratch + 1024);
     for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = __fdiv_rn((float)i, 255.0f);
     for (int i = threadIdx.x; i <= p.lw; i += kThreads) Wg[i] = p.w[i];
+    if (use_mma(s) && p.lw >= 0) {
+      double* A = operator_matrix(s, scratch);
+      for (int e = threadIdx.x; e < kN * kN; e += kThreads) {
+        const int o = e / kN, i = e - o * kN;
+        double a = 0.0;
+        for (int k = -p.lw; k <= p.lw; ++k)
+          if (refl_half(o + k, kN) == i) a += p.w[k < 0 ? -k : k];
+        A[o * kPA + i] = a;
+      }
+    }
     __syncthreads();
   }
 
@@ -411,12 +440,12 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
   }
 
   // literal scipy order at one point of the field F (h x w doubles)
-  __device__ static __noinline__ double literal(const double* F, const double* Wg, int lw, int h, int w, int y, int x) {
+  __device__ static __noinline__ double literal(const double* F, int fp, const double* Wg, int lw, int h, int w, int y, int x) {
     double col[2 * kMaxLw + 1];
     for (int d = -lw; d <= lw; ++d) {
       const int xx = refl_half(x + d, w);
-      double a = F[y * w + xx] * Wg[0];
-      for (int k = lw; k >= 1; --k) a = a + (F[refl_half(y - k, h) * w + xx] + F[refl_half(y + k, h) * w + xx]) * Wg[k];
+      double a = F[y * fp + xx] * Wg[0];
+      for (int k = lw; k >= 1; --k) a = a + (F[refl_half(y - k, h) * fp + xx] + F[refl_half(y + k, h) * fp + xx]) * Wg[k];
       col[d + lw] = a;
     }
     double a = col[lw] * Wg[0];
@@ -433,9 +462,11 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
     const double* Wg = reinterpret_cast<const double*>(scratch + 1024);
     double* Mi = reinterpret_cast<double*>(scratch + 1024 + 256);
     int* tab = reinterpret_cast<int*>(Mi + 6);
-    double* F0 = reinterpret_cast<double*>(tab + 2 * (s.h + s.w));     // [2][hw] raw fields (x, y); (h + w) * 8 keeps alignment
-    double* F1T = F0 + 2 * hw;                                          // [2][w][ph] after the y pass, transposed
-    float* DXYT = reinterpret_cast<float*>(F1T + 2 * plane);            // [2][w][ph] f32 displacements, transposed
+    const bool mma = use_mma(s);
+    const int fp = field_pitch(s), fplane = s.h * fp;
+    double* F0 = reinterpret_cast<double*>(tab + 2 * (s.h + s.w));     // [2][h][fp] raw fields (x, y); (h + w) * 8 keeps alignment
+    double* F1T = F0 + 2 * fplane;                                      // strips: [2][w][ph] after the y pass, transposed; mma: G [2][32][36]
+    float* DXYT = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(F1T) + mid_bytes(s));   // [2][w][ph] f32 displacements, transposed
     float* Wf = reinterpret_cast<float*>(F0);                           // warped image, HWC f32 (aliases F0: 12 <= 16 B/px)
     int* qn = reinterpret_cast<int*>(DXYT + 2 * plane);                 // smoothing replay queue
     int* queue = qn + 1;
@@ -452,13 +483,17 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
       if (tid == 0) { *qn = 0; *q2n = 0; inverse_matrix(p, rng, img, s.h, Mi); }
       // ---- raw fields: F0[0] = ux, F0[1] = uy ----
       if (p.ux) {
-        for (int i = tid; i < 2 * hw; i += kThreads) F0[i] = i < hw ? p.ux[img * hw + i] : p.uy[img * hw + (i - hw)];
+        for (int i = tid; i < 2 * hw; i += kThreads) {
+          const int f = i >= hw, px = i - f * hw, y = px / s.w, x = px - y * s.w;
+          F0[f * fplane + y * fp + x] = f ? p.uy[img * hw + px] : p.ux[img * hw + px];
+        }
       } else {
         for (int i = tid; i < (2 * hw) >> 2; i += kThreads) {   // hw % 4 == 0 (checked at launch)
           const int f = (4 * i) >= hw, e4 = 4 * i - f * hw;
           const uint64_t e = (uint64_t)(img * hw + e4);
           const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x81u + f, 1u);
-          double* d = F0 + 4 * i;
+          const int y4 = e4 / s.w, x4 = e4 - y4 * s.w;          // w % 4 == 0: the four values share a row
+          double* d = F0 + f * fplane + y4 * fp + x4;
           d[0] = -1.0 + 2.0 * (double)u01(r.x); d[1] = -1.0 + 2.0 * (double)u01(r.y);
           d[2] = -1.0 + 2.0 * (double)u01(r.z); d[3] = -1.0 + 2.0 * (double)u01(r.w);
         }
@@ -468,7 +503,50 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
       if (p.lw < 0) {
         for (int i = tid; i < 2 * hw; i += kThreads) {
           const int f = i >= hw, px = i - f * hw, y = px / s.w, x = px - y * s.w;
-          DXYT[f * plane + x * ph + y] = (float)(F0[i] * p.alpha);
+          DXYT[f * plane + x * ph + y] = (float)(F0[f * fplane + y * fp + x] * p.alpha);
+        }
+      } else if (mma) {
+        // tensor-core passes: warp = (field, 8 output rows).  Fragment owner: r = lane / 4, c = lane % 4.
+        const double* A = operator_matrix(s, scratch);
+        const int lane = tid & 31, wq = tid >> 5, f = wq >> 2, m0 = (wq & 3) * 8, r = lane >> 2, c = lane & 3;
+        {   // G = A * F   (axis y):  G[o][x] = sum_i A[o][i] F[i][x]
+          const double* Ff = F0 + f * fplane;
+          double acc[4][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+          for (int k0 = 0; k0 < kN; k0 += 4) {
+            const double a = A[(m0 + r) * kPA + k0 + c];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) dmma(acc[nt][0], acc[nt][1], a, Ff[(k0 + c) * kPF + nt * 8 + r]);
+          }
+          double* G = F1T + f * kN * kPA + (m0 + r) * kPA + 2 * c;
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) *reinterpret_cast<double2*>(G + nt * 8) = make_double2(acc[nt][0], acc[nt][1]);
+        }
+        __syncthreads();
+        {   // S = G * A^T (axis x):  S[y][o] = sum_i G[y][i] A[o][i]
+          const double* Gf = F1T + f * kN * kPA;
+          double acc[4][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+#pragma unroll
+          for (int k0 = 0; k0 < kN; k0 += 4) {
+            const double a = Gf[(m0 + r) * kPA + k0 + c];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) dmma(acc[nt][0], acc[nt][1], a, A[(nt * 8 + r) * kPA + k0 + c]);
+          }
+          const int y = m0 + r;
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) {
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+              const int x = nt * 8 + 2 * c + u;
+              const double t = acc[nt][u] * p.alpha;
+              DXYT[f * plane + x * ph + y] = (float)t;
+              if ((float)(t - tol) != (float)(t + tol) || p.force_exact) {     // too close to a float32 rounding boundary
+                const int slot = atomicAdd(qn, 1);
+                if (slot < kQueue) queue[slot] = (f << 24) | (y << 12) | x;
+                else DXYT[f * plane + x * ph + y] = (float)(literal(F0 + f * fplane, fp, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
+              }
+            }
+          }
         }
       } else {
         // y pass: item = (field, strip of 8 rows, column x), x fastest -> F1T[f][x][y]
@@ -476,7 +554,7 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
         for (int item = tid; item < 2 * s.w * sy; item += kThreads) {
           const int f = item / (s.w * sy), r = item - f * s.w * sy, st = r / s.w, x = r - st * s.w;
           double acc[kStrip];
-          strip(F0 + f * hw + x, s.w, s.h, st * kStrip, Wg, p.lw, acc);
+          strip(F0 + f * fplane + x, fp, s.h, st * kStrip, Wg, p.lw, acc);
           double* o = F1T + f * plane + x * ph + st * kStrip;
 #pragma unroll
           for (int k = 0; k < kStrip; ++k)
@@ -497,23 +575,25 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
               if ((float)(t - tol) != (float)(t + tol) || p.force_exact) {     // too close to a float32 rounding boundary: replay literally
                 const int slot = atomicAdd(qn, 1);
                 if (slot < kQueue) queue[slot] = (f << 24) | (y << 12) | x;
-                else DXYT[f * plane + x * ph + y] = (float)(literal(F0 + f * hw, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
+                else DXYT[f * plane + x * ph + y] = (float)(literal(F0 + f * fplane, fp, Wg, p.lw, s.h, s.w, y, x) * p.alpha);
               }
             }
           }
         }
+      }
+      if (p.lw >= 0) {
         __syncthreads();
         // replay queue: one warp per point, lanes over the 2*lw+1 columns (each in the literal order), lane 0 finishes
         const int nq = min(*qn, kQueue);
         for (int e = tid >> 5; e < nq; e += kThreads >> 5) {
           const int f = queue[e] >> 24, y = (queue[e] >> 12) & 4095, x = queue[e] & 4095;
-          const double* F = F0 + f * hw;
+          const double* F = F0 + f * fplane;
           double* col = qcols + (tid >> 5) * (2 * kMaxLw + 1);
           for (int d = (tid & 31) - p.lw; d <= p.lw; d += 32) {
             const int xx = refl_half(x + d, s.w);
-            double a = F[y * s.w + xx] * Wg[0];
+            double a = F[y * fp + xx] * Wg[0];
             for (int k = p.lw; k >= 1; --k)
-              a = a + (F[refl_half(y - k, s.h) * s.w + xx] + F[refl_half(y + k, s.h) * s.w + xx]) * Wg[k];
+              a = a + (F[refl_half(y - k, s.h) * fp + xx] + F[refl_half(y + k, s.h) * fp + xx]) * Wg[k];
             col[d + p.lw] = a;
           }
           __syncwarp();
