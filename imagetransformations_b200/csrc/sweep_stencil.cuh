@@ -61,6 +61,7 @@ __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om
 #pragma unroll
   for (int i = 0; i < NW; ++i) { Wf[i] = Wt[i]; if (FIX40) Wl[i] = Wt[NW + i]; }
 
+  const uint32_t fmask = force_exact ? 15u : 0u;   // test knob: every output through the literal functor
   int ring[N][R + 1][4];
   for (int yb = y_begin - R; yb < y_end + R; yb += N) {
 #pragma unroll
@@ -78,7 +79,7 @@ __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om
         const int y = row - R;
         if (y >= y_begin) {
           // slots: row y+d lives in slot (s - R + d) mod N, all static
-          uint32_t pack = 0, need = 0;
+          uint32_t pack = 0, need = fmask;
 #pragma unroll
           for (int o = 0; o < 4; ++o) {
             uint32_t ip;
@@ -115,7 +116,6 @@ __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om
             }
             pack |= min(ip, 255u) << (8 * o);
           }
-          if (force_exact) need = 15u;
           if (need) {  // rare: the literal f64 evaluation decides
             for (int o = 0; o < 4; ++o)
               if ((need >> o) & 1u) pack = (pack & ~(255u << (8 * o))) | ((uint32_t)exact(y, 4 * pg + o, ch) << (8 * o));
