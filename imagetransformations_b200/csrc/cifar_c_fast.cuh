@@ -63,10 +63,12 @@ struct CcFastParams {
 // ---------------------------------------------------------------------------------------------------------------
 // gaussian_noise / shot_noise, on-chip draws
 // ---------------------------------------------------------------------------------------------------------------
-struct OpCcNoiseAlias : NoSpill {
+// (a 1024-thread variant for the 147 KB shot table, one CTA per SM, was measured: no gain)
+template <int THREADS>
+struct OpCcNoiseAliasT : NoSpill {
   using Params = CcFastParams;
   static constexpr bool kCifarCopy = true;
-  static constexpr int kThreads = 512;
+  static constexpr int kThreads = THREADS;
   static size_t scratch_bytes(const Shape&, int) { return 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
 
@@ -123,6 +125,8 @@ struct OpCcNoiseAlias : NoSpill {
     }
   }
 };
+
+using OpCcNoiseAlias = OpCcNoiseAliasT<512>;
 
 // ---------------------------------------------------------------------------------------------------------------
 // impulse_noise, on-chip draws: element flips iff r < amount * 2^32; the low bit of r (independent of that event to

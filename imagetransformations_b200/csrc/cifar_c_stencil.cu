@@ -81,7 +81,6 @@ struct DefocusFastParams {
   DefocusParams exact;
   uint32_t Wt[18];  // (R+1)^2 hi words then (R+1)^2 lo words, [|dy|][|dx|] at stride R+1
   int R;
-  int force_exact;  // test knob (imgtx_set_force_exact)
 };
 
 template <int R>
@@ -131,7 +130,7 @@ struct OpCcDefocusFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.exact.ntaps, s.h, s.w, y, x, c); };
-      sweep_sym_stencil<R, BORDER_REFLECT101, true>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex, p.force_exact != 0);
+      sweep_sym_stencil<R, BORDER_REFLECT101, true>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
     }
   }
 };
@@ -333,6 +332,9 @@ struct OpCcGlass : NoSpill {
       const int64_t img = img0 + j;
       for (int it = 0; it < p.iters; ++it) {
         const int h = s.h - 1 - lane;
+        // on-chip draws: one bit per swap from one Philox call per (image, iteration, row) — the convention of OpCcGlassFast
+        uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+        if (!p.deltas && lane < R) rb = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
         for (int t = 0; t < 2 * (R - 1) + Ccols; ++t) {
           const int ci = t - 2 * lane;
           if (lane < R && ci >= 0 && ci < Ccols) {
@@ -342,8 +344,8 @@ struct OpCcGlass : NoSpill {
               const int8_t* d = p.deltas + ((((img * p.iters + it) * R + lane) * Ccols + ci) << 1);
               dx = d[0]; dy = d[1];
             } else {
-              const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)(lane * Ccols + ci));
-              dx = -(int)(r.x & 1u); dy = -(int)(r.y & 1u);
+              dx = -(int)(((ci < 32 ? rb.x : rb.z) >> (ci & 31)) & 1u);
+              dy = -(int)(((ci < 32 ? rb.y : rb.w) >> (ci & 31)) & 1u);
             }
             uint8_t* a = im + (h * s.w + w) * 3;
             uint8_t* b = im + ((h + dy) * s.w + (w + dx)) * 3;
@@ -370,7 +372,6 @@ struct OpCcGlass : NoSpill {
 struct GlassFastParams {
   GlassParams g;
   uint32_t Wt[18];
-  int force_exact;  // test knob (imgtx_set_force_exact)
 };
 
 template <int R>
@@ -381,8 +382,8 @@ struct OpCcGlassFast : NoSpill {
   static constexpr int kThreads = 192;
   static constexpr int kMinBlocks = R == 2 ? 2 : 3;
   static constexpr int kSeg = 2;
-  // scratch: T64 (2 KB) | flat-window LUTs 2 x 256 B | per image: u16 index map
-  static size_t scratch_bytes(const Shape& s, int G) { return 2048 + 512 + (size_t)G * s.h * s.w * 2 + 16; }
+  // scratch: T64 (2 KB) | flat-window LUTs 2 x 256 B + their composition 256 B | per image: u16 index map
+  static size_t scratch_bytes(const Shape& s, int G) { return 2048 + 768 + (size_t)G * s.h * s.w * 2 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
 
   // literal scipy two-pass evaluation at one element (axis y first, then x; mode 'nearest')
@@ -427,6 +428,8 @@ struct OpCcGlassFast : NoSpill {
       flat[256 + i] = q255d(a);
     }
     __syncthreads();
+    for (int i = threadIdx.x; i < 256; i += kThreads) flat[512 + i] = flat[256 + flat[i]];   // second Gaussian of the first
+    __syncthreads();
   }
 
   __device__ static __forceinline__ void blur(const uint8_t* src, uint8_t* dst, int g, const Shape& s, const Params& p,
@@ -447,7 +450,7 @@ struct OpCcGlassFast : NoSpill {
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       const int y0 = seg * seg_rows, y1 = min(s.h, y0 + seg_rows);
       auto ex = [&](int y, int x, int c) { return exact_px(im, T, p.g.w, p.g.lw, s.h, s.w, y, x, c, FINAL); };
-      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE, false>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex, p.force_exact != 0);
+      sweep_sym_stencil<(R > 0 ? R : 1), BORDER_REPLICATE, false>(im, om, s.h, s.w, p.Wt, ch, pg, y0, y1, ex);
     }
   }
 
@@ -455,70 +458,98 @@ struct OpCcGlassFast : NoSpill {
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
                              uint8_t* scratch, uint8_t*) {
     const double* T = reinterpret_cast<const double*>(scratch);
-    uint16_t* maps = reinterpret_cast<uint16_t*>(scratch + 2048 + 512);
+    uint16_t* maps = reinterpret_cast<uint16_t*>(scratch + 2048 + 768);
     uint8_t* work = const_cast<uint8_t*>(src);  // the staged input buffer is ours until the next group is loaded
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int hw = s.h * s.w;
     const int Rr = s.h - 2, Cc = s.w - 2;
     const Philox rng(p.g.seed);
     __syncthreads();
-    for (int pass = 0; pass < 2; ++pass) {
-      // Gaussian: pass 0 src -> dst (uint8(g*255)); pass 1 work -> dst (clip, *255).  One call site: one copy of the sweep.
-      blur(pass == 0 ? src : work, dst, g, s, p, T, pass == 1);
-      if (pass == 1) break;
-      // index map of the swap sweep (independent of the pixels)
-      for (int i = tid; i < g * hw; i += kThreads) maps[i] = (uint16_t)(i % hw);
-      __syncthreads();
-      for (int j = warp; j < g; j += kThreads >> 5) {
-        uint16_t* m = maps + (size_t)j * hw;
-        const int64_t img = img0 + j;
-        for (int it = 0; it < p.g.iters; ++it) {
-          const int h = s.h - 1 - lane;
-          uint32_t bx = 0, by = 0, bx2 = 0, by2 = 0;  // on-chip draws: one bit per swap, 64 swaps per row at most
-          if (!p.g.deltas && lane < Rr) {
-            const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
-            bx = r.x; by = r.y; bx2 = r.z; by2 = r.w;
+    for (int pass = 0; pass < 2; ++pass) {   // one call site of the sweep: one copy of its code
+    // Gaussian: pass 0 src -> dst as uint8(g * 255) (R == 0: a byte map, folded into the gather below); pass 1 work -> dst, clipped
+    if (R > 0) blur(pass == 0 ? src : work, dst, g, s, p, T, pass == 1);
+    if (pass == 1) break;
+    // index map of the swap sweep (independent of the pixels)
+    for (int j = 0; j < g; ++j)
+      for (int px = tid; px < hw; px += kThreads) maps[j * hw + px] = (uint16_t)px;
+    __syncthreads();
+    for (int j = warp; j < g; j += kThreads >> 5) {
+      uint16_t* m = maps + (size_t)j * hw;
+      const int64_t img = img0 + j;
+      for (int it = 0; it < p.g.iters; ++it) {
+        const int h = s.h - 1 - lane;
+        uint32_t bx = 0, by = 0, bx2 = 0, by2 = 0;  // on-chip draws: one bit per swap, 64 swaps per row at most
+        if (!p.g.deltas && lane < Rr) {
+          const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
+          bx = r.x; by = r.y; bx2 = r.z; by2 = r.w;
+        }
+        if (p.g.deltas) {
+          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+            const int ci = t - 2 * lane;
+            if (lane < Rr && ci >= 0 && ci < Cc) {
+              const int w = s.w - 1 - ci;
+              const int8_t* d = p.g.deltas + ((((img * p.g.iters + it) * Rr + lane) * Cc + ci) << 1);
+              const int dx = d[0], dy = d[1];
+              const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
+              const uint16_t ta = m[a], tb = m[b];
+              m[a] = tb; m[b] = ta;
+            }
+            __syncwarp();
           }
-          if (p.g.deltas) {
-            for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
-              const int ci = t - 2 * lane;
-              if (lane < Rr && ci >= 0 && ci < Cc) {
-                const int w = s.w - 1 - ci;
-                const int8_t* d = p.g.deltas + ((((img * p.g.iters + it) * Rr + lane) * Cc + ci) << 1);
-                const int dx = d[0], dy = d[1];
-                const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
-                const uint16_t ta = m[a], tb = m[b];
-                m[a] = tb; m[b] = ta;
-              }
-              __syncwarp();
+        } else {
+          // on-chip draws: the bits are consumed from two 64-bit shift registers, the position walks down by one
+          uint64_t BX = (uint64_t)bx | ((uint64_t)bx2 << 32), BY = (uint64_t)by | ((uint64_t)by2 << 32);
+          uint16_t* ma = m + h * s.w + (s.w - 1);
+          const uint32_t first = 2u * (uint32_t)lane, cnt = lane < Rr ? (uint32_t)Cc : 0u;
+          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+            if ((uint32_t)t - first < cnt) {
+              uint16_t* mb = ma - ((int)((uint32_t)BY & 1u) * s.w + (int)((uint32_t)BX & 1u));
+              BX >>= 1; BY >>= 1;
+              const uint16_t ta = *ma, tb = *mb;
+              *ma = tb; *mb = ta;
+              --ma;
             }
-          } else {
-            // on-chip draws: the bits are consumed from two 64-bit shift registers, the position walks down by one
-            uint64_t BX = (uint64_t)bx | ((uint64_t)bx2 << 32), BY = (uint64_t)by | ((uint64_t)by2 << 32);
-            uint16_t* ma = m + h * s.w + (s.w - 1);
-            const uint32_t first = 2u * (uint32_t)lane, cnt = lane < Rr ? (uint32_t)Cc : 0u;
-            for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
-              if ((uint32_t)t - first < cnt) {
-                uint16_t* mb = ma - ((int)((uint32_t)BY & 1u) * s.w + (int)((uint32_t)BX & 1u));
-                BX >>= 1; BY >>= 1;
-                const uint16_t ta = *ma, tb = *mb;
-                *ma = tb; *mb = ta;
-                --ma;
-              }
-              __syncwarp();
-            }
+            __syncwarp();
           }
         }
       }
-      __syncthreads();
-      // apply the map: work[p] = dst[map[p]]
-      for (int i = tid; i < g * hw; i += kThreads) {
-        const int j = i / hw, px = i - j * hw;
-        const uint8_t* a = dst + (size_t)j * s.out_bytes + (int)maps[i] * 3;
-        uint8_t* o = work + (size_t)j * s.in_bytes + px * 3;
-        o[0] = a[0]; o[1] = a[1]; o[2] = a[2];
+    }
+    __syncthreads();
+    const int quads = hw >> 2;   // w % 4 == 0 (checked at launch)
+    if (R == 0) {
+      // sigma < 0.125: both Gaussians are byte maps, so the whole corruption is one gather: dst[p] = flat2[flat1[src[map[p]]]]
+      const uint8_t* lut = reinterpret_cast<const uint8_t*>(T + 256) + 512;
+      for (int j = 0; j < g; ++j) {
+        const uint8_t* im = src + (size_t)j * s.in_bytes;
+        const uint16_t* m = maps + (size_t)j * hw;
+        uint32_t* o = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes);
+        for (int q = tid; q < quads; q += kThreads) {
+          uint32_t px[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t v = load_rgb(im, (int)m[4 * q + e] * 3);
+            px[e] = (uint32_t)lut[v & 255u] | ((uint32_t)lut[(v >> 8) & 255u] << 8) | ((uint32_t)lut[v >> 16] << 16);
+          }
+          uint32_t a, b, c;
+          pack_rgb4(px[0], px[1], px[2], px[3], a, b, c);
+          o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
+        }
       }
-      __syncthreads();
+      return;
+    }
+    // apply the map: work[p] = dst[map[p]], four pixels per thread
+    for (int j = 0; j < g; ++j) {
+      const uint8_t* im = dst + (size_t)j * s.out_bytes;
+      const uint16_t* m = maps + (size_t)j * hw;
+      uint32_t* o = reinterpret_cast<uint32_t*>(work + (size_t)j * s.in_bytes);
+      for (int q = tid; q < quads; q += kThreads) {
+        uint32_t a, b, c;
+        pack_rgb4(load_rgb(im, (int)m[4 * q] * 3), load_rgb(im, (int)m[4 * q + 1] * 3), load_rgb(im, (int)m[4 * q + 2] * 3),
+                  load_rgb(im, (int)m[4 * q + 3] * 3), a, b, c);
+        o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
+      }
+    }
+    __syncthreads();
     }
   }
 };
@@ -1141,7 +1172,7 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       K[p.dy[i] + 2][p.dx[i] + 2] += p.w[i];
       R = std::max(R, std::max(abs((int)p.dy[i]), abs((int)p.dx[i])));
     }
-    bool sym = (w % 4 == 0) && R >= 1;
+    bool sym = (w % 4 == 0) && R >= 1 && !force_exact();   // test knob: the literal kernel instead of the fixed-point sweep
     for (int a = 0; a < 5 && sym; ++a)
       for (int b = 0; b < 5; ++b)
         if (K[a][b] != K[4 - a][b] || K[a][b] != K[a][4 - b]) sym = false;
@@ -1150,7 +1181,6 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       memset(&f, 0, sizeof(f));
       f.exact = p;
       f.R = R;
-      f.force_exact = force_exact();
       double cw[9];
       int mult[9];
       memset(cw, 0, sizeof(cw));
@@ -1212,11 +1242,11 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
   const Shape shp = make_shape(h, w, c, h, w);
-  if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out)) {
+  if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
+      !force_exact()) {   // test knob: the literal kernel instead of the fixed-point sweeps
     GlassFastParams f;
     memset(&f, 0, sizeof(f));
     f.g = p;
-    f.force_exact = force_exact();
     bool ok = true;
     if (lw >= 1) {
       double cw[9];

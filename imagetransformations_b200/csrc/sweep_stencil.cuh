@@ -49,7 +49,7 @@ __device__ __forceinline__ int hfold(const int* v, int o, int k) {
 template <int R, int BORDER, bool FIX40, class Exact>
 __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om, int h, int w,
                                                   const uint32_t* Wt, int ch, int pg, int y_begin, int y_end,
-                                                  Exact exact, bool force_exact = false) {
+                                                  Exact exact) {
   constexpr int N = 2 * R + 1;   // ring depth
   constexpr int L = 2 * R + 4;   // loaded bytes per row
   const int rowb = w * 3;
@@ -61,7 +61,6 @@ __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om
 #pragma unroll
   for (int i = 0; i < NW; ++i) { Wf[i] = Wt[i]; if (FIX40) Wl[i] = Wt[NW + i]; }
 
-  const uint32_t fmask = force_exact ? 15u : 0u;   // test knob: every output through the literal functor
   int ring[N][R + 1][4];
   for (int yb = y_begin - R; yb < y_end + R; yb += N) {
 #pragma unroll
@@ -79,7 +78,7 @@ __device__ __forceinline__ void sweep_sym_stencil(const uint8_t* im, uint8_t* om
         const int y = row - R;
         if (y >= y_begin) {
           // slots: row y+d lives in slot (s - R + d) mod N, all static
-          uint32_t pack = 0, need = fmask;
+          uint32_t pack = 0, need = 0;
 #pragma unroll
           for (int o = 0; o < 4; ++o) {
             uint32_t ip;
