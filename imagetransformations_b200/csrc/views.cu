@@ -39,9 +39,15 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
   const int tid = threadIdx.x;
   const int V = vs.n_views;
   float* NT = reinterpret_cast<float*>(smem);                        // [3][256] normalise table
-  int32_t* tables = reinterpret_cast<int32_t*>(NT + 768);            // table_words
+  float* VL = NT + 768;                                              // [3][256] the current view's byte -> float map
+  int32_t* tables = reinterpret_cast<int32_t*>(VL + 768);            // table_words
   uint8_t* u = reinterpret_cast<uint8_t*>(tables + ((table_words + 3) & ~3));  // hw*3 (+4)
-  uint8_t* tmp = u + ((hw * 3 + 4 + 15) & ~15);                      // tmp_rows * w * 3 (+4)
+  uint8_t* tmp = u + ((hw * 3 + 4 + 15) & ~15);                      // tmp_rows * w 32-bit pixels
+  // fast paths: threads are laid out as (row, quad of 4 pixels) / (row, pixel) once, so no loop divides by a run-time size
+  const bool quads_ok = (w & 3) == 0 && (w >> 2) <= kViewThreads;
+  const int qpr = quads_ok ? (w >> 2) : 1, q_rows = kViewThreads / qpr, q_ty = tid / qpr, q_tx = tid - q_ty * qpr;
+  const bool cols_ok = w <= kViewThreads;
+  const int c_rows = cols_ok ? kViewThreads / w : 1, c_ty = cols_ok ? tid / w : 0, c_tx = cols_ok ? tid - c_ty * w : 0;
   __shared__ unsigned long long s_luma;
   __shared__ float s_par[kMaxViews * 2];
 
@@ -58,11 +64,13 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
     // ---- load / quantise ----
     if (vs.in_is_f32) {
       const float* xi = reinterpret_cast<const float*>(in) + img * 3 * (int64_t)hw;
-      for (int i = tid; i < hw * 3; i += kViewThreads) {
-        const int c = i / hw, p = i - c * hw;
-        float v = __fadd_rn(__fmul_rn(xi[i], vs.in_std[c]), vs.in_mean[c]);
-        v = fminf(fmaxf(v, 0.0f), 1.0f);
-        u[p * 3 + c] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+      for (int c = 0; c < 3; ++c) {
+        const float sd = vs.in_std[c], mn = vs.in_mean[c];
+        for (int p = tid; p < hw; p += kViewThreads) {
+          float v = __fadd_rn(__fmul_rn(__ldcs(xi + c * hw + p), sd), mn);
+          v = fminf(fmaxf(v, 0.0f), 1.0f);
+          u[p * 3 + c] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+        }
       }
     } else {
       const uint8_t* xi = reinterpret_cast<const uint8_t*>(in) + img * 3 * (int64_t)hw;
@@ -101,17 +109,47 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
           const bool blend = vw.kind == IMGTX_VIEW_BRIGHTNESS || vw.kind == IMGTX_VIEW_CONTRAST;
           const int d = vw.kind == IMGTX_VIEW_CONTRAST ? degenerate : 0;
           const int ci = (int)p0 - vw.i0, cj = (int)p1 - vw.i0;  // crop offsets minus padding (row, col)
-          for (int i = tid; i < hw * 3; i += kViewThreads) {
-            const int c = i / hw, p = i - c * hw;
-            int y = p / w, x = p - y * w;
-            if (crop) {
-              y = reflect101(y + ci, h);
-              x = reflect101(x + cj, w);
+          const float* lut = NT;
+          if (blend) {
+            // the enhancer is a byte map per image: compose it with ToTensor+Normalize once (256 blends instead of 3*h*w)
+            __syncthreads();   // the previous view may still read VL
+            for (int e = tid; e < 256; e += kViewThreads) {
+              const int bv = pil_blend(d, e, p0);
+              VL[e] = NT[bv]; VL[256 + e] = NT[256 + bv]; VL[512 + e] = NT[512 + bv];
             }
-            if (flip) x = w - 1 - x;
-            int val = u[(y * w + x) * 3 + c];
-            if (blend) val = pil_blend(d, val, p0);
-            ov[i] = NT[c * 256 + val];
+            __syncthreads();
+            lut = VL;
+          }
+          if (quads_ok) {
+            if (q_ty < q_rows) {
+              for (int c = 0; c < 3; ++c) {
+                const float* lc = lut + c * 256;
+                for (int y = q_ty; y < h; y += q_rows) {
+                  const int yy = crop ? reflect101(y + ci, h) : y;
+                  const uint8_t* row = u + yy * w * 3 + c;
+                  float o[4];
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    int x = q_tx * 4 + e;
+                    if (crop) x = reflect101(x + cj, w);
+                    if (flip) x = w - 1 - x;
+                    o[e] = lc[row[x * 3]];
+                  }
+                  __stcs(reinterpret_cast<float4*>(ov + c * hw + y * w) + q_tx, make_float4(o[0], o[1], o[2], o[3]));
+                }
+              }
+            }
+          } else {
+            for (int i = tid; i < hw * 3; i += kViewThreads) {
+              const int c = i / hw, p = i - c * hw;
+              int y = p / w, x = p - y * w;
+              if (crop) {
+                y = reflect101(y + ci, h);
+                x = reflect101(x + cj, w);
+              }
+              if (flip) x = w - 1 - x;
+              ov[i] = lut[c * 256 + u[(y * w + x) * 3 + c]];
+            }
           }
           break;
         }
@@ -126,27 +164,63 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
           const int32_t* vt = tables + vs.table_off[vw.table_v];
           const int hk = ht[1], vk = vt[1];
           __syncthreads();  // tmp may still be read by the previous resample view
-          for (int i = tid; i < bh * w; i += kViewThreads) {
-            const int y = i / w, xx = i - y * w;
-            const int32_t* rec = ht + 2 + (left + xx) * (2 + hk);
-            const int xmin = rec[0], nk = rec[1];
-            const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
-            int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-            for (int k = 0; k < nk; ++k) {
-              const int kk = rec[2 + k];
-              a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
+          uint32_t* tmp32 = reinterpret_cast<uint32_t*>(tmp);   // 32-bit pixels (r | g << 8 | b << 16)
+          if (cols_ok) {
+            // horizontal pass: thread = column xx of rows c_ty, c_ty + c_rows, ... (its coefficient record is loaded once)
+            if (c_ty < c_rows) {
+              const int32_t* rec = ht + 2 + (left + c_tx) * (2 + hk);
+              const int xmin = rec[0], nk = rec[1];
+              for (int y = c_ty; y < bh; y += c_rows) {
+                const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
+                int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+                for (int k = 0; k < nk; ++k) {
+                  const int kk = rec[2 + k];
+                  a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
+                }
+                tmp32[y * w + c_tx] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) | ((uint32_t)clip8(a2 >> 22) << 16);
+              }
             }
-            tmp[i * 3] = clip8(a0 >> 22); tmp[i * 3 + 1] = clip8(a1 >> 22); tmp[i * 3 + 2] = clip8(a2 >> 22);
-          }
-          __syncthreads();
-          for (int i = tid; i < hw * 3; i += kViewThreads) {
-            const int c = i / hw, p = i - c * hw;
-            const int y = p / w, x = p - y * w;
-            const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
-            const int ymin = rec[0], nk = rec[1];
-            int a = 1 << 21;
-            for (int k = 0; k < nk; ++k) a += tmp[((ymin + k) * w + x) * 3 + c] * rec[2 + k];
-            ov[i] = NT[c * 256 + clip8(a >> 22)];
+            __syncthreads();
+            // vertical pass: thread = pixel (y, x), all three channels from one 32-bit load per tap
+            if (c_ty < c_rows) {
+              for (int y = c_ty; y < h; y += c_rows) {
+                const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
+                const int ymin = rec[0], nk = rec[1];
+                int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+                for (int k = 0; k < nk; ++k) {
+                  const uint32_t px = tmp32[(ymin + k) * w + c_tx];
+                  const int kk = rec[2 + k];
+                  a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
+                }
+                float* o = ov + y * w + c_tx;
+                __stcs(o, NT[clip8(a0 >> 22)]);
+                __stcs(o + hw, NT[256 + clip8(a1 >> 22)]);
+                __stcs(o + 2 * hw, NT[512 + clip8(a2 >> 22)]);
+              }
+            }
+          } else {
+            for (int i = tid; i < bh * w; i += kViewThreads) {
+              const int y = i / w, xx = i - y * w;
+              const int32_t* rec = ht + 2 + (left + xx) * (2 + hk);
+              const int xmin = rec[0], nk = rec[1];
+              const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
+              int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+              for (int k = 0; k < nk; ++k) {
+                const int kk = rec[2 + k];
+                a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
+              }
+              tmp32[i] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) | ((uint32_t)clip8(a2 >> 22) << 16);
+            }
+            __syncthreads();
+            for (int i = tid; i < hw * 3; i += kViewThreads) {
+              const int c = i / hw, p = i - c * hw;
+              const int y = p / w, x = p - y * w;
+              const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
+              const int ymin = rec[0], nk = rec[1];
+              int a = 1 << 21;
+              for (int k = 0; k < nk; ++k) a += (int)((tmp32[(ymin + k) * w + x] >> (8 * c)) & 255u) * rec[2 + k];
+              ov[i] = NT[c * 256 + clip8(a >> 22)];
+            }
           }
           break;
         }
@@ -199,8 +273,8 @@ extern "C" int imgtx_views_f32(const void* in, int in_is_f32, float* out, int64_
   }
   vs.tmp_rows = tmp_rows;
   const int hw = h * w;
-  size_t smem = 768 * 4 + (size_t)((table_words + 3) & ~3) * 4 + ((size_t)hw * 3 + 4 + 15) / 16 * 16 +
-                ((size_t)tmp_rows * w * 3 + 4 + 15) / 16 * 16 + 16;
+  size_t smem = 2 * 768 * 4 + (size_t)((table_words + 3) & ~3) * 4 + ((size_t)hw * 3 + 4 + 15) / 16 * 16 +
+                ((size_t)tmp_rows * w * 4 + 15) / 16 * 16 + 16;
   IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused views", h, w);
   IMGTX_CUDA_OK(cudaFuncSetAttribute(views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)max_smem_optin() / (smem + 1024)));
