@@ -183,6 +183,7 @@ __device__ __forceinline__ uint32_t q255_fast(double v) {
 struct OpCcContrastFast : NoSpill, NoPrepare {
   using Params = CcFastParams;
   static constexpr int kThreads = 256;
+  static constexpr int kStages = 2, kOutBufs = 1;   // a warp owns an image: groups of 8 images keep all 8 warps busy
   static constexpr int kWarps = kThreads / 32;
   static size_t scratch_bytes(const Shape&, int) { return (size_t)kWarps * 768 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }

@@ -325,7 +325,8 @@ extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n,
     f.force_exact = force_exact();
     if (kind == IMGTX_CC_IMPULSE && !draws_a_dev) return launch_image_op<OpCcImpulseFast>(in, out, n, shp, f, (cudaStream_t)stream);
     if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && (int64_t)h * w * 255 < (1ll << 31))
-      return launch_image_op<OpCcContrastFast>(in, out, n, shp, f, (cudaStream_t)stream);
+      return launch_image_op<OpCcContrastFast>(in, out, n, shp, f, (cudaStream_t)stream, 0,
+                                               128 + 3 * 8 * shp.in_bytes + (int)OpCcContrastFast::scratch_bytes(shp, 8) + 512);   // 8 images per group
     if (kind == IMGTX_CC_BRIGHTNESS && (h * w) % 4 == 0 && p0 > -10 && p0 < 10)
       return launch_image_op<OpCcBrightnessFast>(in, out, n, shp, f, (cudaStream_t)stream);
     if (kind == IMGTX_CC_FOG && !draws_a_dev && h == w && (h & (h - 1)) == 0 && h >= 4 && h <= 64 && p0 > 0 && p0 < 100 && p1 > 0) {

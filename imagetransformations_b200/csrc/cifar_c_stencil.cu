@@ -380,7 +380,7 @@ struct OpCcGlassFast : NoSpill {
   static constexpr int kStages = R == 1 ? 3 : 2, kOutBufs = R == 1 ? 2 : 1;   // measured per radius
   static constexpr bool kCifarCopy = R == 0;
   static constexpr int kThreads = 192;
-  static constexpr int kMinBlocks = R == 2 ? 2 : 3;
+  static constexpr int kMinBlocks = R == 2 ? 2 : 3;   // (3 CTAs at R == 2 spill: measured 25 % slower)
   static constexpr int kSeg = 2;
   // scratch: T64 (2 KB) | flat-window LUTs 2 x 256 B + their composition 256 B | per image: u16 index map
   static size_t scratch_bytes(const Shape& s, int G) { return 2048 + 768 + (size_t)G * s.h * s.w * 2 + 16; }
@@ -465,9 +465,77 @@ struct OpCcGlassFast : NoSpill {
     const int Rr = s.h - 2, Cc = s.w - 2;
     const Philox rng(p.g.seed);
     __syncthreads();
+    if (R == 0) {
+    // index map of the swap sweep (independent of the pixels)
+    for (int j = 0; j < g; ++j)
+      for (int px = tid; px < hw; px += kThreads) maps[j * hw + px] = (uint16_t)px;
+    __syncthreads();
+    for (int j = warp; j < g; j += kThreads >> 5) {
+      uint16_t* m = maps + (size_t)j * hw;
+      const int64_t img = img0 + j;
+      for (int it = 0; it < p.g.iters; ++it) {
+        const int h = s.h - 1 - lane;
+        uint32_t bx = 0, by = 0, bx2 = 0, by2 = 0;  // on-chip draws: one bit per swap, 64 swaps per row at most
+        if (!p.g.deltas && lane < Rr) {
+          const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
+          bx = r.x; by = r.y; bx2 = r.z; by2 = r.w;
+        }
+        if (p.g.deltas) {
+          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+            const int ci = t - 2 * lane;
+            if (lane < Rr && ci >= 0 && ci < Cc) {
+              const int w = s.w - 1 - ci;
+              const int8_t* d = p.g.deltas + ((((img * p.g.iters + it) * Rr + lane) * Cc + ci) << 1);
+              const int dx = d[0], dy = d[1];
+              const int a = h * s.w + w, b = (h + dy) * s.w + (w + dx);
+              const uint16_t ta = m[a], tb = m[b];
+              m[a] = tb; m[b] = ta;
+            }
+            __syncwarp();
+          }
+        } else {
+          // on-chip draws: the bits are consumed from two 64-bit shift registers, the position walks down by one
+          uint64_t BX = (uint64_t)bx | ((uint64_t)bx2 << 32), BY = (uint64_t)by | ((uint64_t)by2 << 32);
+          uint16_t* ma = m + h * s.w + (s.w - 1);
+          const uint32_t first = 2u * (uint32_t)lane, cnt = lane < Rr ? (uint32_t)Cc : 0u;
+          for (int t = 0; t < 2 * (Rr - 1) + Cc; ++t) {
+            if ((uint32_t)t - first < cnt) {
+              uint16_t* mb = ma - ((int)((uint32_t)BY & 1u) * s.w + (int)((uint32_t)BX & 1u));
+              BX >>= 1; BY >>= 1;
+              const uint16_t ta = *ma, tb = *mb;
+              *ma = tb; *mb = ta;
+              --ma;
+            }
+            __syncwarp();
+          }
+        }
+      }
+    }
+    __syncthreads();
+    const int quads = hw >> 2;   // w % 4 == 0 (checked at launch)
+      // sigma < 0.125: both Gaussians are byte maps, so the whole corruption is one gather: dst[p] = flat2[flat1[src[map[p]]]]
+      const uint8_t* lut = reinterpret_cast<const uint8_t*>(T + 256) + 512;
+      for (int j = 0; j < g; ++j) {
+        const uint8_t* im = src + (size_t)j * s.in_bytes;
+        const uint16_t* m = maps + (size_t)j * hw;
+        uint32_t* o = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes);
+        for (int q = tid; q < quads; q += kThreads) {
+          uint32_t px[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t v = load_rgb(im, (int)m[4 * q + e] * 3);
+            px[e] = (uint32_t)lut[v & 255u] | ((uint32_t)lut[(v >> 8) & 255u] << 8) | ((uint32_t)lut[v >> 16] << 16);
+          }
+          uint32_t a, b, c;
+          pack_rgb4(px[0], px[1], px[2], px[3], a, b, c);
+          o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
+        }
+      }
+      return;
+    }
     for (int pass = 0; pass < 2; ++pass) {   // one call site of the sweep: one copy of its code
-    // Gaussian: pass 0 src -> dst as uint8(g * 255) (R == 0: a byte map, folded into the gather below); pass 1 work -> dst, clipped
-    if (R > 0) blur(pass == 0 ? src : work, dst, g, s, p, T, pass == 1);
+    // Gaussian: pass 0 src -> dst as uint8(g * 255); pass 1 work -> dst, clipped
+    blur(pass == 0 ? src : work, dst, g, s, p, T, pass == 1);
     if (pass == 1) break;
     // index map of the swap sweep (independent of the pixels)
     for (int j = 0; j < g; ++j)
@@ -516,27 +584,6 @@ struct OpCcGlassFast : NoSpill {
     }
     __syncthreads();
     const int quads = hw >> 2;   // w % 4 == 0 (checked at launch)
-    if (R == 0) {
-      // sigma < 0.125: both Gaussians are byte maps, so the whole corruption is one gather: dst[p] = flat2[flat1[src[map[p]]]]
-      const uint8_t* lut = reinterpret_cast<const uint8_t*>(T + 256) + 512;
-      for (int j = 0; j < g; ++j) {
-        const uint8_t* im = src + (size_t)j * s.in_bytes;
-        const uint16_t* m = maps + (size_t)j * hw;
-        uint32_t* o = reinterpret_cast<uint32_t*>(dst + (size_t)j * s.out_bytes);
-        for (int q = tid; q < quads; q += kThreads) {
-          uint32_t px[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const uint32_t v = load_rgb(im, (int)m[4 * q + e] * 3);
-            px[e] = (uint32_t)lut[v & 255u] | ((uint32_t)lut[(v >> 8) & 255u] << 8) | ((uint32_t)lut[v >> 16] << 16);
-          }
-          uint32_t a, b, c;
-          pack_rgb4(px[0], px[1], px[2], px[3], a, b, c);
-          o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
-        }
-      }
-      return;
-    }
     // apply the map: work[p] = dst[map[p]], four pixels per thread
     for (int j = 0; j < g; ++j) {
       const uint8_t* im = dst + (size_t)j * s.out_bytes;
