@@ -824,7 +824,11 @@ __device__ __forceinline__ void fill_canvas(uint8_t* canvas, const uint8_t* im, 
   const int wpr = (gm.pw * CH) >> 2, lw = (-gm.dxmin * CH) >> 2, iw = (w * CH) >> 2;
   const uint32_t* im32 = reinterpret_cast<const uint32_t*>(im);
   uint32_t* c32 = reinterpret_cast<uint32_t*>(canvas);
-  for (int py = warp; py < gm.ph; py += nw) {
+  // narrow canvases (one channel): several rows per warp, lpr lanes per row
+  const int lpr = wpr <= 8 ? 8 : (wpr <= 16 ? 16 : 32), rpi = 32 / lpr, lr = lane / lpr, lq = lane - lr * lpr;
+  for (int py0 = warp * rpi; py0 < gm.ph; py0 += nw * rpi) {
+    const int py = py0 + lr;
+    if (py >= gm.ph) continue;
     const int sy = min(max(py + gm.dymin, 0), h - 1);
     const uint32_t* row = im32 + sy * iw;
     uint32_t L[3], R[3];
@@ -836,7 +840,7 @@ __device__ __forceinline__ void fill_canvas(uint8_t* canvas, const uint8_t* im, 
       L[0] = L[1] = L[2] = (row[0] & 255u) * 0x01010101u;
       R[0] = R[1] = R[2] = (row[iw - 1] >> 24) * 0x01010101u;
     }
-    for (int q = lane; q < wpr; q += 32) {
+    for (int q = lq; q < wpr; q += lpr) {
       uint32_t v;
       if (q < lw) {
         const int m = CH == 3 ? q % 3 : 0;
