@@ -77,7 +77,11 @@ __global__ void augmix_kernel(const float* __restrict__ x, float* __restrict__ o
   uint8_t* fills = comp + (size_t)width * 768;                         // nstage * 4
   uint32_t* hist = reinterpret_cast<uint32_t*>(fills + ((nstage * 4 + 15) & ~15));  // 768
   float* T = reinterpret_cast<float*>(hist + 768);                     // 256: u/255
-  AugOp* ops = reinterpret_cast<AugOp*>(T + 256);                      // nstage
+  float* FT = T + 256;                                                 // width * 768: w_i * T[comp_i[c][v]]
+  float* FF = FT + (size_t)width * 768;                                // nstage * 4:  w_i * T[fill]
+  int32_t* G = reinterpret_cast<int32_t*>(FF + (size_t)nstage * 4);    // per chain: [ng,-,-,-] + depth * [a0..a5,k,-]
+  const int gstride = 4 + depth * 8;
+  AugOp* ops = reinterpret_cast<AugOp*>(G + (size_t)width * gstride);  // nstage
   float* wts = reinterpret_cast<float*>(ops + nstage);                 // width + 2
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
 
@@ -161,6 +165,25 @@ __global__ void augmix_kernel(const float* __restrict__ x, float* __restrict__ o
     }
     __syncthreads();
 
+    // ---- phase B': per-chain float tables (weight folded in: fmul(w_i, T[u]) is evaluated once per table entry
+    //      instead of once per pixel) and the chain's geometric stages compacted in trace-back order ----
+    for (int t = tid; t < width * 768; t += nt) FT[t] = __fmul_rn(wts[t / 768], T[comp[t]]);
+    for (int t = tid; t < nstage * 4; t += nt) FF[t] = __fmul_rn(wts[(t >> 2) / depth], T[fills[t]]);
+    if (tid < width) {
+      int32_t* g = G + tid * gstride;
+      int ng = 0;
+      for (int k = depth - 1; k >= 0; --k) {
+        const AugOp& op = ops[tid * depth + k];
+        if (op.kind != IMGTX_AUG_GEOM) continue;
+        int32_t* r = g + 4 + ng * 8;
+        for (int e = 0; e < 6; ++e) r[e] = op.a[e];
+        r[6] = k;
+        ++ng;
+      }
+      g[0] = ng;
+    }
+    __syncthreads();
+
     // ---- phase C: mix and write ----
     const float m = wts[width], one_m = wts[width + 1];
     if ((hw & 3) == 0 && (w & 3) == 0) {
@@ -173,18 +196,37 @@ __global__ void augmix_kernel(const float* __restrict__ x, float* __restrict__ o
 #pragma unroll
           for (int k = 0; k < 4; ++k) mix[c][k] = 0.0f;
         for (int ci = 0; ci < width; ++ci) {
-          const AugOp* cops = ops + ci * depth;
-          const uint8_t* ccomp = comp + ci * 768;
-          const uint8_t* cfill = fills + ci * depth * 4;
-          const float wi = wts[ci];
+          const int32_t* g = G + ci * gstride;
+          const int ng = g[0];
+          const float* ft = FT + ci * 768;
+          // four adjacent pixels walk the chain's geometric stages together: one coefficient fetch per stage
+          int xs[4], ys[4], fk[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) { xs[k] = x0 + k; ys[k] = y; fk[k] = -1; }
+          for (int s2 = 0; s2 < ng; ++s2) {
+            const int4 A = *reinterpret_cast<const int4*>(g + 4 + s2 * 8);
+            const int4 Bv = *reinterpret_cast<const int4*>(g + 8 + s2 * 8);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              const int nx = (A.z + ys[k] * A.y + xs[k] * A.x) >> 16;
+              const int ny = (Bv.y + ys[k] * Bv.x + xs[k] * A.w) >> 16;
+              const bool outside = (unsigned)nx >= (unsigned)w || (unsigned)ny >= (unsigned)h;
+              if (fk[k] < 0) {
+                if (outside) fk[k] = Bv.z;
+                else { xs[k] = nx; ys[k] = ny; }
+              }
+            }
+          }
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            int fk = 0;
-            const int o = trace_back(cops, depth, x0 + k, y, w, h, fk);
+            if (fk[k] < 0) {
+              const uint8_t* sp = q + (ys[k] * w + xs[k]) * 3;
 #pragma unroll
-            for (int c = 0; c < 3; ++c) {
-              const int u = o >= 0 ? ccomp[c * 256 + q[o + c]] : cfill[fk * 4 + c];
-              mix[c][k] = __fadd_rn(mix[c][k], __fmul_rn(wi, T[u]));
+              for (int c = 0; c < 3; ++c) mix[c][k] = __fadd_rn(mix[c][k], ft[c * 256 + sp[c]]);
+            } else {
+              const float* ff = FF + (ci * depth + fk[k]) * 4;
+#pragma unroll
+              for (int c = 0; c < 3; ++c) mix[c][k] = __fadd_rn(mix[c][k], ff[c]);
             }
           }
         }
@@ -233,7 +275,8 @@ extern "C" int imgtx_augmix_f32(const float* x, float* out, int64_t n, int h, in
   const int hw = h * w, nstage = width * depth;
   IMGTX_CHECK_ARG(((int64_t)hw % 4 != 0) || (aligned16(x) && aligned16(out)), "f32 tensors must be 16-byte aligned");
   size_t smem = ((size_t)hw * 3 + 4 + 15) / 16 * 16 + (size_t)nstage * 768 + (size_t)width * 768 +
-                ((size_t)nstage * 4 + 15) / 16 * 16 + 768 * 4 + 256 * 4 + (size_t)nstage * 32 + (size_t)(width + 2) * 4 + 16;
+                ((size_t)nstage * 4 + 15) / 16 * 16 + 768 * 4 + 256 * 4 + (size_t)width * 768 * 4 + (size_t)nstage * 16 +
+                (size_t)width * (4 + depth * 8) * 4 + (size_t)nstage * 32 + (size_t)(width + 2) * 4 + 16;
   IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused AugMix", h, w);
   const int threads = hw >= 128 * 128 ? 1024 : 256;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(augmix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

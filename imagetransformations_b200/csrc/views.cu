@@ -31,7 +31,90 @@ struct ViewSet {
 
 __device__ __forceinline__ int pil_luma_v(int r, int g, int b) { return (19595 * r + 38470 * g + 7471 * b + 0x8000) >> 16; }
 
-__global__ void __launch_bounds__(kViewThreads)
+// byte c of a packed pixel as a byte offset into a float[256] table
+__device__ __forceinline__ float lut_at(const float* t, uint32_t px, int c) {
+  const uint32_t off = c == 0 ? (px << 2) & 0x3FCu : (px >> (8 * c - 2)) & 0x3FCu;
+  return *reinterpret_cast<const float*>(reinterpret_cast<const char*>(t + c * 256) + off);
+}
+__device__ __forceinline__ uint32_t pack_q22(int a0, int a1, int a2) {
+  return (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) | ((uint32_t)clip8(a2 >> 22) << 16);
+}
+
+// Pillow's two-pass resample of one view on packed 32-bit pixels.  KS > 0: the table's tap count, fully unrolled
+// (records are zero-padded to KS taps, and both pixel arrays are padded so the extra taps read harmless words);
+// KS == 0: run-time tap count.
+template <int KS>
+__device__ __forceinline__ void resize_view(const uint32_t* u32, uint32_t* tmp32, float* ov, const float* NT,
+                                            const int32_t* ht, const int32_t* vt, int h, int w, int ox, int oy, int bh,
+                                            int left, int top, int c_rows, int c_ty, int c_tx) {
+  const int hw = h * w;
+  const int hk = KS ? KS : ht[1], vk = KS ? KS : vt[1];
+  if (c_ty < c_rows) {
+    // horizontal pass: thread = column of rows c_ty, c_ty + c_rows, ...; its coefficient record stays in registers
+    const int32_t* rec = ht + 2 + (left + c_tx) * (2 + hk);
+    const int xmin = rec[0];
+    if (KS) {
+      int kk[KS ? KS : 1];
+#pragma unroll
+      for (int k = 0; k < KS; ++k) kk[k] = rec[2 + k];
+      for (int y = c_ty; y < bh; y += c_rows) {
+        const uint32_t* row = u32 + (oy + y) * w + ox + xmin;
+        int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+#pragma unroll
+        for (int k = 0; k < KS; ++k) {
+          const uint32_t px = row[k];
+          a0 += (int)(px & 255u) * kk[k]; a1 += (int)((px >> 8) & 255u) * kk[k]; a2 += (int)(px >> 16) * kk[k];
+        }
+        tmp32[y * w + c_tx] = pack_q22(a0, a1, a2);
+      }
+    } else {
+      const int nk = rec[1];
+      for (int y = c_ty; y < bh; y += c_rows) {
+        const uint32_t* row = u32 + (oy + y) * w + ox + xmin;
+        int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+        for (int k = 0; k < nk; ++k) {
+          const uint32_t px = row[k];
+          const int kk = rec[2 + k];
+          a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
+        }
+        tmp32[y * w + c_tx] = pack_q22(a0, a1, a2);
+      }
+    }
+  }
+  __syncthreads();
+  if (c_ty < c_rows) {
+    // vertical pass: thread = pixel (y, x); a warp shares the row's record (broadcast loads)
+    for (int y = c_ty; y < h; y += c_rows) {
+      const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
+      const uint32_t* col = tmp32 + rec[0] * w + c_tx;
+      int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
+      if (KS) {
+#pragma unroll
+        for (int k = 0; k < KS; ++k) {
+          const uint32_t px = col[k * w];
+          const int kk = rec[2 + k];
+          a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
+        }
+      } else {
+        const int nk = rec[1];
+        for (int k = 0; k < nk; ++k) {
+          const uint32_t px = col[k * w];
+          const int kk = rec[2 + k];
+          a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
+        }
+      }
+      float* o = ov + y * w + c_tx;
+      __stcs(o, NT[clip8(a0 >> 22)]);
+      __stcs(o + hw, NT[256 + clip8(a1 >> 22)]);
+      __stcs(o + 2 * hw, NT[512 + clip8(a2 >> 22)]);
+    }
+  }
+}
+
+constexpr int kPixelPad = 8;   // words after the image, read (times a zero coefficient) by the unrolled taps
+constexpr int kTmpPadRows = 6;
+
+__global__ void __launch_bounds__(kViewThreads, 5)
 views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, int h, int w, ViewSet vs,
              const float* __restrict__ params, const int32_t* __restrict__ tables_g, int table_words) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -41,9 +124,9 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
   float* NT = reinterpret_cast<float*>(smem);                        // [3][256] normalise table
   float* VL = NT + 768;                                              // [3][256] the current view's byte -> float map
   int32_t* tables = reinterpret_cast<int32_t*>(VL + 768);            // table_words
-  uint8_t* u = reinterpret_cast<uint8_t*>(tables + ((table_words + 3) & ~3));  // hw*3 (+4)
-  uint8_t* tmp = u + ((hw * 3 + 4 + 15) & ~15);                      // tmp_rows * w 32-bit pixels
-  // fast paths: threads are laid out as (row, quad of 4 pixels) / (row, pixel) once, so no loop divides by a run-time size
+  uint32_t* u32 = reinterpret_cast<uint32_t*>(tables + ((table_words + 3) & ~3));  // hw packed pixels r | g<<8 | b<<16
+  uint32_t* tmp32 = u32 + ((hw + kPixelPad + 3) & ~3);               // (tmp_rows + pad) * w packed pixels
+  // threads are laid out as (row, quad of 4 pixels) / (row, pixel) once, so no loop divides by a run-time size
   const bool quads_ok = (w & 3) == 0 && (w >> 2) <= kViewThreads;
   const int qpr = quads_ok ? (w >> 2) : 1, q_rows = kViewThreads / qpr, q_ty = tid / qpr, q_tx = tid - q_ty * qpr;
   const bool cols_ok = w <= kViewThreads;
@@ -56,37 +139,39 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
     NT[i] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)(i & 255), 255.0f), vs.out_mean[c]), vs.out_std[c]);
   }
   for (int i = tid; i < table_words; i += kViewThreads) tables[i] = tables_g[i];
+  for (int i = tid; i < kPixelPad; i += kViewThreads) u32[hw + i] = 0u;
+  for (int i = tid; i < (vs.tmp_rows + kTmpPadRows) * w; i += kViewThreads) tmp32[i] = 0u;
 
   for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
     __syncthreads();
     if (tid == 0) s_luma = 0ull;
     for (int i = tid; i < V * 2; i += kViewThreads) s_par[i] = params[img * V * 2 + i];
-    // ---- load / quantise ----
+    // ---- load / quantise into packed pixels ----
     if (vs.in_is_f32) {
       const float* xi = reinterpret_cast<const float*>(in) + img * 3 * (int64_t)hw;
-      for (int c = 0; c < 3; ++c) {
-        const float sd = vs.in_std[c], mn = vs.in_mean[c];
-        for (int p = tid; p < hw; p += kViewThreads) {
-          float v = __fadd_rn(__fmul_rn(__ldcs(xi + c * hw + p), sd), mn);
+      for (int p = tid; p < hw; p += kViewThreads) {
+        uint32_t px = 0;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          float v = __fadd_rn(__fmul_rn(__ldcs(xi + c * hw + p), vs.in_std[c]), vs.in_mean[c]);
           v = fminf(fmaxf(v, 0.0f), 1.0f);
-          u[p * 3 + c] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+          px |= (uint32_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255) << (8 * c);
         }
+        u32[p] = px;
       }
     } else {
       const uint8_t* xi = reinterpret_cast<const uint8_t*>(in) + img * 3 * (int64_t)hw;
-      if (((hw * 3) & 15) == 0) {
-        const uint4* s4 = reinterpret_cast<const uint4*>(xi);
-        uint4* d4 = reinterpret_cast<uint4*>(u);
-        for (int i = tid; i < (hw * 3) >> 4; i += kViewThreads) d4[i] = ldg_stream(s4 + i);
-      } else {
-        for (int i = tid; i < hw * 3; i += kViewThreads) u[i] = xi[i];
-      }
+      for (int p = tid; p < hw; p += kViewThreads)
+        u32[p] = (uint32_t)xi[p * 3] | ((uint32_t)xi[p * 3 + 1] << 8) | ((uint32_t)xi[p * 3 + 2] << 16);
     }
     __syncthreads();
     int degenerate = 0;
     if (vs.any_contrast) {
       unsigned acc = 0;
-      for (int p = tid; p < hw; p += kViewThreads) acc += pil_luma_v(u[p * 3], u[p * 3 + 1], u[p * 3 + 2]);
+      for (int p = tid; p < hw; p += kViewThreads) {
+        const uint32_t px = u32[p];
+        acc += pil_luma_v(px & 255u, (px >> 8) & 255u, px >> 16);
+      }
       for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
       if ((tid & 31) == 0) atomicAdd(&s_luma, (unsigned long long)acc);
       __syncthreads();
@@ -121,22 +206,27 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
             lut = VL;
           }
           if (quads_ok) {
+            // thread = four adjacent pixels of a row: the pixels are fetched once for the three planes
             if (q_ty < q_rows) {
-              for (int c = 0; c < 3; ++c) {
-                const float* lc = lut + c * 256;
-                for (int y = q_ty; y < h; y += q_rows) {
-                  const int yy = crop ? reflect101(y + ci, h) : y;
-                  const uint8_t* row = u + yy * w * 3 + c;
-                  float o[4];
+              for (int y = q_ty; y < h; y += q_rows) {
+                uint32_t px[4];
+                if (!crop) {
+                  const uint4 v = *reinterpret_cast<const uint4*>(u32 + y * w + (flip ? w - 4 - q_tx * 4 : q_tx * 4));
+                  px[0] = flip ? v.w : v.x; px[1] = flip ? v.z : v.y; px[2] = flip ? v.y : v.z; px[3] = flip ? v.x : v.w;
+                } else {
+                  const uint32_t* row = u32 + reflect101(y + ci, h) * w;
 #pragma unroll
                   for (int e = 0; e < 4; ++e) {
-                    int x = q_tx * 4 + e;
-                    if (crop) x = reflect101(x + cj, w);
+                    int x = reflect101(q_tx * 4 + e + cj, w);
                     if (flip) x = w - 1 - x;
-                    o[e] = lc[row[x * 3]];
+                    px[e] = row[x];
                   }
-                  __stcs(reinterpret_cast<float4*>(ov + c * hw + y * w) + q_tx, make_float4(o[0], o[1], o[2], o[3]));
                 }
+                float4* o4 = reinterpret_cast<float4*>(ov + y * w) + q_tx;
+#pragma unroll
+                for (int c = 0; c < 3; ++c)
+                  __stcs(o4 + c * (hw >> 2),
+                         make_float4(lut_at(lut, px[0], c), lut_at(lut, px[1], c), lut_at(lut, px[2], c), lut_at(lut, px[3], c)));
               }
             }
           } else {
@@ -148,7 +238,7 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
                 x = reflect101(x + cj, w);
               }
               if (flip) x = w - 1 - x;
-              ov[i] = lut[c * 256 + u[(y * w + x) * 3 + c]];
+              ov[i] = lut[c * 256 + ((u32[y * w + x] >> (8 * c)) & 255u)];
             }
           }
           break;
@@ -164,52 +254,26 @@ views_kernel(const void* __restrict__ in, float* __restrict__ out, int64_t n, in
           const int32_t* vt = tables + vs.table_off[vw.table_v];
           const int hk = ht[1], vk = vt[1];
           __syncthreads();  // tmp may still be read by the previous resample view
-          uint32_t* tmp32 = reinterpret_cast<uint32_t*>(tmp);   // 32-bit pixels (r | g << 8 | b << 16)
           if (cols_ok) {
-            // horizontal pass: thread = column xx of rows c_ty, c_ty + c_rows, ... (its coefficient record is loaded once)
-            if (c_ty < c_rows) {
-              const int32_t* rec = ht + 2 + (left + c_tx) * (2 + hk);
-              const int xmin = rec[0], nk = rec[1];
-              for (int y = c_ty; y < bh; y += c_rows) {
-                const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
-                int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-                for (int k = 0; k < nk; ++k) {
-                  const int kk = rec[2 + k];
-                  a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
-                }
-                tmp32[y * w + c_tx] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) | ((uint32_t)clip8(a2 >> 22) << 16);
-              }
-            }
-            __syncthreads();
-            // vertical pass: thread = pixel (y, x), all three channels from one 32-bit load per tap
-            if (c_ty < c_rows) {
-              for (int y = c_ty; y < h; y += c_rows) {
-                const int32_t* rec = vt + 2 + (top + y) * (2 + vk);
-                const int ymin = rec[0], nk = rec[1];
-                int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
-                for (int k = 0; k < nk; ++k) {
-                  const uint32_t px = tmp32[(ymin + k) * w + c_tx];
-                  const int kk = rec[2 + k];
-                  a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
-                }
-                float* o = ov + y * w + c_tx;
-                __stcs(o, NT[clip8(a0 >> 22)]);
-                __stcs(o + hw, NT[256 + clip8(a1 >> 22)]);
-                __stcs(o + 2 * hw, NT[512 + clip8(a2 >> 22)]);
-              }
-            }
+            if (hk == 5 && vk == 5)
+              resize_view<5>(u32, tmp32, ov, NT, ht, vt, h, w, ox, oy, bh, left, top, c_rows, c_ty, c_tx);
+            else if (hk == 3 && vk == 3)
+              resize_view<3>(u32, tmp32, ov, NT, ht, vt, h, w, ox, oy, bh, left, top, c_rows, c_ty, c_tx);
+            else
+              resize_view<0>(u32, tmp32, ov, NT, ht, vt, h, w, ox, oy, bh, left, top, c_rows, c_ty, c_tx);
           } else {
             for (int i = tid; i < bh * w; i += kViewThreads) {
               const int y = i / w, xx = i - y * w;
               const int32_t* rec = ht + 2 + (left + xx) * (2 + hk);
               const int xmin = rec[0], nk = rec[1];
-              const uint8_t* row = u + ((oy + y) * w + ox + xmin) * 3;
+              const uint32_t* row = u32 + (oy + y) * w + ox + xmin;
               int a0 = 1 << 21, a1 = 1 << 21, a2 = 1 << 21;
               for (int k = 0; k < nk; ++k) {
+                const uint32_t px = row[k];
                 const int kk = rec[2 + k];
-                a0 += row[k * 3] * kk; a1 += row[k * 3 + 1] * kk; a2 += row[k * 3 + 2] * kk;
+                a0 += (int)(px & 255u) * kk; a1 += (int)((px >> 8) & 255u) * kk; a2 += (int)(px >> 16) * kk;
               }
-              tmp32[i] = (uint32_t)clip8(a0 >> 22) | ((uint32_t)clip8(a1 >> 22) << 8) | ((uint32_t)clip8(a2 >> 22) << 16);
+              tmp32[i] = pack_q22(a0, a1, a2);
             }
             __syncthreads();
             for (int i = tid; i < hw * 3; i += kViewThreads) {
@@ -273,8 +337,8 @@ extern "C" int imgtx_views_f32(const void* in, int in_is_f32, float* out, int64_
   }
   vs.tmp_rows = tmp_rows;
   const int hw = h * w;
-  size_t smem = 2 * 768 * 4 + (size_t)((table_words + 3) & ~3) * 4 + ((size_t)hw * 3 + 4 + 15) / 16 * 16 +
-                ((size_t)tmp_rows * w * 4 + 15) / 16 * 16 + 16;
+  size_t smem = 2 * 768 * 4 + (size_t)((table_words + 3) & ~3) * 4 + (size_t)((hw + kPixelPad + 3) & ~3) * 4 +
+                ((size_t)(tmp_rows + kTmpPadRows) * w * 4 + 15) / 16 * 16 + 16;
   IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused views", h, w);
   IMGTX_CUDA_OK(cudaFuncSetAttribute(views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)max_smem_optin() / (smem + 1024)));

@@ -60,9 +60,19 @@ def expand(x: torch.Tensor, views: np.ndarray, params: np.ndarray, table_specs, 
     return out
 
 
-def tta16(tn: torch.Tensor, crop_xy, brightness, contrast, mean, std, out=None) -> torch.Tensor:
+def tta16_draws(n: int, crop_xy, brightness, contrast, device) -> torch.Tensor:
+    """The (n,16,2) f32 per-view parameter block of tta16 on the device: upload the draws once, reuse across calls."""
+    params = np.zeros((n, 16, 2), np.float32)
+    params[:, 1:6, :] = np.asarray(crop_xy, np.float64).reshape(n, 5, 2)
+    params[:, 6:11, 0] = np.asarray(brightness, np.float64).reshape(n, 5)
+    params[:, 11:16, 0] = np.asarray(contrast, np.float64).reshape(n, 5)
+    return torch.from_numpy(params).to(device)
+
+
+def tta16(tn: torch.Tensor, crop_xy, brightness, contrast, mean, std, out=None, draws=None) -> torch.Tensor:
     """The 16-view expansion of tta_initial_claudeFixed.py (AUG_COUNTS [1,5,5,5]) for normalised f32 input (or a
-    uint8 batch, which skips the tensor_to_pil prologue)."""
+    uint8 batch, which skips the tensor_to_pil prologue).  draws: the device block of tta16_draws (then crop_xy,
+    brightness and contrast are ignored and nothing is copied from the host)."""
     n = tn.shape[0]
     h, w = (tn.shape[2], tn.shape[3]) if tn.dtype == torch.float32 else (tn.shape[1], tn.shape[2])
     cs = int(w * 0.78)
@@ -74,10 +84,16 @@ def tta16(tn: torch.Tensor, crop_xy, brightness, contrast, mean, std, out=None) 
     views["table_v"][1:6] = 1
     views["kind"][6:11] = L.VIEW_BRIGHTNESS
     views["kind"][11:16] = L.VIEW_CONTRAST
-    params = np.zeros((n, 16, 2), np.float64)
-    params[:, 1:6, :] = np.asarray(crop_xy).reshape(n, 5, 2)
-    params[:, 6:11, 0] = np.asarray(brightness).reshape(n, 5)
-    params[:, 11:16, 0] = np.asarray(contrast).reshape(n, 5)
+    if draws is not None:
+        if not (isinstance(draws, torch.Tensor) and draws.is_cuda and draws.dtype == torch.float32
+                and tuple(draws.shape) == (n, 16, 2)):
+            raise TypeError("draws must be the CUDA float32 (n,16,2) block of tta16_draws")
+        params = draws
+    else:
+        params = np.zeros((n, 16, 2), np.float64)
+        params[:, 1:6, :] = np.asarray(crop_xy).reshape(n, 5, 2)
+        params[:, 6:11, 0] = np.asarray(brightness).reshape(n, 5)
+        params[:, 11:16, 0] = np.asarray(contrast).reshape(n, 5)
     specs = [(cs, w, L.FILTER_BICUBIC), (cs, h, L.FILTER_BICUBIC)]
     f32_in = tn.dtype == torch.float32
     return expand(tn, views, params, specs, mean, std, mean if f32_in else None, std if f32_in else None, out=out)

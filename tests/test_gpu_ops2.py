@@ -138,3 +138,29 @@ def test_noise_philox_statistics(cuda):
         ref = np.clip(k / lam * 255.0, 0, 255).astype(np.uint8).astype(np.float64)
         assert abs(o.mean() - ref.mean()) < 0.02 * ref.std() + 0.05, (lam, o.mean(), ref.mean())
         assert abs(o.std() - ref.std()) < 0.02 * ref.std() + 0.05, (lam, o.std(), ref.std())
+
+
+def test_tta16_batch_and_device_draws(cuda):
+    """A whole batch of 16-view expansions against the oracle, and the device-resident draws block (tta16_draws) against
+    the host-draws call: same bytes."""
+    from imagetransformations_b200 import tta_initial as TI, views as V
+    from oracle import np_chains as CH
+    B = _B()
+    n = 48
+    x = _imgs(77, n, 32, 32)
+    x[0] = 0
+    x[1] = 255
+    x[2, :, :, 1] = 7          # flat channels: contrast degenerate edge
+    tn = B.to_tensor(_cu(x), TI.CIFAR100_MEAN, TI.CIFAR100_STD)
+    np.random.seed(11)
+    crop, br, ct = TI.sample_view_draws(n)
+    crop[3] = 0
+    crop[4] = 8                # both ends of the crop range
+    got = TI.views16_batch(tn, crop, br, ct).cpu().numpy()
+    tnh = tn.cpu().numpy()
+    for i in range(n):
+        ref = CH.tta_views16(tnh[i], crop[i], br[i], ct[i])
+        assert np.array_equal(got[i], ref), i
+    draws = V.tta16_draws(n, crop, br, ct, "cuda")
+    got2 = V.tta16(tn, None, None, None, TI.CIFAR100_MEAN, TI.CIFAR100_STD, draws=draws).cpu().numpy()
+    assert np.array_equal(got, got2)

@@ -15,6 +15,10 @@ PEAK = 6542.7
 
 
 def timeit(fn, iters=20, warm=5):
+    if os.environ.get("ONCE"):      # one call (for ncu captures)
+        fn()
+        torch.cuda.synchronize()
+        return 1.0
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
@@ -29,6 +33,8 @@ def timeit(fn, iters=20, warm=5):
 
 def main():
     res = {}
+
+    only = os.environ.get("ONLY", "")
 
     def rec(name, secs, nbytes, units, unit_name):
         res[name] = {"us": round(secs * 1e6, 1), "GBs": round(nbytes / secs / 1e9, 1), "frac_of_hbm_peak": round(nbytes / secs / 1e9 / PEAK, 3),
@@ -58,7 +64,8 @@ def main():
     np.random.seed(3)
     crop, br, ct = tta_initial.sample_view_draws(n1)
     vout = [torch.empty((n1, 16, 3, 32, 32), dtype=torch.float32, device="cuda") for _ in range(2)]
-    rec("C3 TTA 16 views / image (fused)", timeit(lambda: V.tta16(tn, crop, br, ct, tta_initial.CIFAR100_MEAN, tta_initial.CIFAR100_STD, out=vout[k[0] & 1]), iters=10),
+    draws = V.tta16_draws(n1, crop, br, ct, "cuda")
+    rec("C3 TTA 16 views / image (fused)", timeit(lambda: V.tta16(tn, None, None, None, tta_initial.CIFAR100_MEAN, tta_initial.CIFAR100_STD, out=vout[k[0] & 1], draws=draws), iters=10),
         n1 * (12288 + 16 * 12288), n1 * 16, "view")
     # ---- C5: FGSM eps sweep, 10000 x 3x32x32 f32 (24 576 B read + E * 12 288 B written per image) ----
     xf = B.to_tensor(x)
