@@ -100,6 +100,7 @@ __global__ void augmix_kernel(const float* __restrict__ x, float* __restrict__ o
     // ---- phase A: quantise to HWC uint8 in shared memory ----
     if ((hw & 3) == 0) {
       uint32_t* q32 = reinterpret_cast<uint32_t*>(q);
+#pragma unroll 4
       for (int p4 = tid; p4 < (hw >> 2); p4 += nt) {
         uint32_t v[3][4];
 #pragma unroll
