@@ -92,6 +92,7 @@ _PROTOS = {
     "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
+    "imgtx_shannon_entropy_f32": [_vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _vp],
 }
 _RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64,
              "imgtx_cc_noise_table_words": C.c_int64}

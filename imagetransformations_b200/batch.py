@@ -455,6 +455,26 @@ def _bounds(lo, hi, c):
     return mode, lk, lp, hk, hp
 
 
+def shannon_entropy(x: torch.Tensor, mean=None, std=None, return_counts: bool = False):
+    """Per-image Shannon entropy (bits) of the 256-bin histogram of all c*h*w values: (n,c,h,w) f32 -> f64[n] on the
+    device (and the exact u32 counts (n,256) when return_counts).  mean/std given: x is normalised and is mapped
+    x*std+mean, clamp[0,1] first (fall_2025/TENT_Pipelines.py:99-121); else values outside [0,1] are not counted
+    (fall_2025/Initial_Experiments.py:95-113)."""
+    x = _check_f32(x)
+    if x.dim() == 3:
+        x = x.unsqueeze(0)
+    if x.dim() != 4:
+        raise ValueError("expected a (n,c,h,w) or (c,h,w) tensor")
+    n, c, h, w = x.shape
+    ent = torch.empty(n, dtype=torch.float64, device=x.device)
+    counts = torch.empty((n, 256), dtype=torch.int32, device=x.device) if return_counts else None
+    mk, mp = _fptr(mean)
+    sk, sp = _fptr(std)
+    L.check(L.load().imgtx_shannon_entropy_f32(x.data_ptr(), n, c, h, w, mp, sp, ent.data_ptr(),
+                                               counts.data_ptr() if counts is not None else None, _stream()))
+    return (ent, counts) if return_counts else ent
+
+
 def sign_step(x: torch.Tensor, g: torch.Tensor, eps, direction: float = 1.0, lo=None, hi=None,
               return_pert: bool = False):
     """x + direction*eps*sign(g) (optionally clamped). eps scalar -> tensor like x; eps sequence of E

@@ -361,6 +361,17 @@ typedef enum {
 int imgtx_float_corrupt_f32(const float* x, const float* noise, float* out, int64_t count, int mode, float a,
                             float b, int do_clamp, imgtx_stream_t stream);
 
+/* ---- per-image metric: Shannon-entropy gate -------------------------------- */
+/* compute_shannon_entropy for a batch: x f32 (n,c,h,w) -> entropy_dev[n] (f64, bits) of the 256-bin histogram over all
+   c*h*w values; counts_dev (optional, n*256 u32) receives the integer histogram np.histogram(bins=256, range=(0,1))
+   would give.  mean_host/std_host != NULL: the tensor is normalised and is first mapped x*std+mean (f32) and clamped
+   to [0,1] (fall_2025/TENT_Pipelines.py:99-121, caller :257-274); NULL: values are used as they are and those
+   outside [0,1] are not counted (fall_2025/Initial_Experiments.py:95-113, caller :147-157).  The counts are exact;
+   the entropy is summed in f64 in a fixed order (within 1e-12 of SciPy's value).  An image with no countable value
+   gives NaN, as the reference does. */
+int imgtx_shannon_entropy_f32(const float* x, int64_t n, int c, int h, int w, const float* mean_host,
+                              const float* std_host, double* entropy_dev, uint32_t* counts_dev, imgtx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

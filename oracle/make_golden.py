@@ -549,6 +549,48 @@ def gen_fgsm(X):
     b.save()
 
 
+def gen_entropy(X):
+    """Per-image Shannon entropy gate: the two compute_shannon_entropy variants run on normalised and on
+    [0,1] tensors, plus the plain 256-bin counts np.histogram gives for the same values."""
+    import torch
+    b = Book("entropy")
+    E = R.entropy_gate()
+    mean, std = E.CIFAR_MEAN, E.CIFAR_STD
+    x = torch.from_numpy(X["x32"]).permute(0, 3, 1, 2).contiguous().float().div(255)
+    xn = ((x - torch.tensor(mean).view(1, 3, 1, 1)) / torch.tensor(std).view(1, 3, 1, 1)).clone()
+    rng = np.random.default_rng(41)
+    extra = torch.from_numpy(rng.normal(0.0, 1.5, (6, 3, 32, 32)).astype(np.float32))   # many values clamp to 0 / 1
+    extra[0] = 0.25                        # one bin per channel
+    extra[1, :, :, :16] = -9.0             # half the image clamps to 0
+    extra[2].view(-1)[:512] = torch.arange(512, dtype=torch.float32) / 256.0 - 0.5
+    xn = torch.cat([xn, extra])
+    unit = torch.cat([x, torch.from_numpy(rng.random((4, 3, 32, 32)).astype(np.float32))])
+    unit[-1].view(-1)[:257] = torch.arange(257, dtype=torch.float32) / 256.0     # exact bin edges, 1.0 included
+    unit[-2].view(-1)[:6] = torch.tensor([-0.5, 1.5, float("nan"), 1.0, 0.0, -0.0])  # outside [0,1]: not counted
+    big = torch.from_numpy(rng.random((1, 3, 224, 224)).astype(np.float32) ** 2)
+    b.put("xn", xn.numpy())
+    b.put("unit", unit.numpy())
+    b.put("big", big.numpy())
+
+    def counts_tent(t):
+        img = t.clone()
+        for c in range(3):
+            img[c] = img[c] * std[c] + mean[c]
+        return np.histogram(torch.clamp(img, 0, 1).numpy().flatten(), bins=256, range=(0, 1))[0]
+
+    def counts_unit(t):
+        return np.histogram(t.numpy().flatten(), bins=256, range=(0, 1))[0]
+
+    b.case("TENT_Pipelines.compute_shannon_entropy", "xn",
+           np.array([float(E.tent_entropy(t)) for t in xn], np.float64),
+           draws={"counts": np.stack([counts_tent(t) for t in xn]).astype(np.int64)})
+    for key, arr in (("unit", unit), ("big", big)):
+        b.case("Initial_Experiments.compute_shannon_entropy", key,
+               np.array([float(E.unit_entropy(t)) for t in arr], np.float64),
+               draws={"counts": np.stack([counts_unit(t) for t in arr]).astype(np.int64)})
+    b.save()
+
+
 def gen_fixtures(X):
     """The reference's own CIFAR-10-C samples (CIFAR-10-C/store/*.png, lossless, all severity 1 — SURVEY §2.1) as one
     array per corruption type, ordered by source index (0, 1001, 2002, 3003, 4004)."""
@@ -568,7 +610,7 @@ def main():
     if not R.available():
         raise SystemExit("the reference is not mounted at " + R.REF_ROOT)
     X = make_inputs()
-    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "fixtures"]
+    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "entropy", "fixtures"]
     for w in which:
         globals()["gen_" + w](X)
 

@@ -338,6 +338,43 @@ def tensor_to_pil(t: np.ndarray, mean, std) -> np.ndarray:
 
 
 # =================================================================================================
+# SURVEY 8f-3  per-image Shannon-entropy gate
+# =================================================================================================
+
+
+def shannon_entropy(t: np.ndarray, mean=None, std=None):
+    """compute_shannon_entropy for a batch (n,c,h,w) f32 -> (entropy f64[n], counts i64[n,256]).
+
+    fall_2025/TENT_Pipelines.py:99-121 (mean/std given: x*std+mean per channel in f32 with the Python scalars cast to
+    f32, then clamp to [0,1]) and fall_2025/Initial_Experiments.py:95-113 (mean is None: values used as they are).
+    np.histogram(bins=256, range=(0,1)) on f32 data: values outside [0,1] (and NaN) are not counted, the bin is
+    min(floor(256*v), 255) (256*v is exact in f32; the edges k/256 are exact, so numpy's edge fix-ups never fire);
+    density=True only rescales.  scipy.stats.entropy(hist[hist>0], base=2) = -sum(p ln p)/ln 2 with p = count/N in f64.
+    An image with no countable value gives NaN (0/0), as the reference does."""
+    v = np.asarray(t, f32)
+    n = v.shape[0]
+    if mean is not None:
+        m = np.asarray(mean, f32).reshape(1, -1, 1, 1)
+        s = np.asarray(std, f32).reshape(1, -1, 1, 1)
+        v = (v * s).astype(f32)
+        v = (v + m).astype(f32)
+        v = np.where(np.isnan(v), v, np.minimum(np.maximum(v, f32(0)), f32(1)))
+    v = v.reshape(n, int(np.prod(v.shape[1:])))
+    ent = np.empty(n, np.float64)
+    counts = np.zeros((n, 256), np.int64)
+    for i in range(n):
+        r = v[i]
+        r = r[(r >= 0) & (r <= 1)]
+        idx = np.minimum(np.floor(r * f32(256)).astype(np.int64), 255)
+        counts[i] = np.bincount(idx, minlength=256)
+        tot = counts[i].sum()
+        with np.errstate(invalid="ignore", divide="ignore"):
+            p = counts[i][counts[i] > 0] / np.float64(tot)
+            ent[i] = -(p * np.log(p)).sum() / np.log(2.0) if tot > 0 else np.nan
+    return ent, counts
+
+
+# =================================================================================================
 # A.12  sign-step family
 # =================================================================================================
 

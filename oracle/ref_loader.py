@@ -140,6 +140,20 @@ def fgsm():
     return _cache["fgsm"]
 
 
+def entropy_gate():
+    """compute_shannon_entropy of fall_2025/TENT_Pipelines.py:99-121 (normalised input) and of
+    fall_2025/Initial_Experiments.py:95-113 ([0,1] input)."""
+    if "entropy_gate" not in _cache:
+        import scipy.stats
+        ns = types.SimpleNamespace()
+        t = slice_module("fall_2025/TENT_Pipelines.py", {"compute_shannon_entropy", "CIFAR_MEAN", "CIFAR_STD"})
+        ns.tent_entropy, ns.CIFAR_MEAN, ns.CIFAR_STD = t.compute_shannon_entropy, t.CIFAR_MEAN, t.CIFAR_STD
+        ns.unit_entropy = slice_module("fall_2025/Initial_Experiments.py", {"compute_shannon_entropy"},
+                                       extra_globals={"entropy": scipy.stats.entropy}).compute_shannon_entropy
+        _cache["entropy_gate"] = ns
+    return _cache["entropy_gate"]
+
+
 def angellic():
     if "angellic" not in _cache:
         _cache["angellic"] = slice_module("pipenline/angellic.py",

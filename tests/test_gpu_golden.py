@@ -210,3 +210,28 @@ def test_cuda_matches_reference_golden(cuda, fi):
     c = g.cases[i]
     got = gpu_eval(g, c)
     G.compare(c["fn"], got, g.arr(c["out"]))
+
+
+ENTROPY_TOL = 1e-12   # f64 entropy: device log() and a fixed-order tree sum versus scipy's entr + pairwise sum
+
+
+def test_cuda_entropy_golden(cuda):
+    """SURVEY 8f-3 through the C ABI: histogram counts bit-exact against np.histogram of the live reference's values,
+    entropies within 1e-12 of the reference's floats; and the reference-signature wrappers."""
+    from imagetransformations_b200 import Initial_Experiments as IE, TENT_Pipelines as TP, batch as B
+    g = G.golden("entropy")
+    for c in g.cases:
+        x = torch.from_numpy(g.arr(c["in"])).cuda()
+        tent = c["fn"].startswith("TENT_Pipelines")
+        e, h = B.shannon_entropy(x, TP.CIFAR_MEAN, TP.CIFAR_STD, return_counts=True) if tent else \
+            B.shannon_entropy(x, return_counts=True)
+        want = g.arr(c["out"])
+        assert np.array_equal(h.cpu().numpy().astype(np.int64), g.draws(c)["counts"]), c["fn"]
+        assert np.max(np.abs(e.cpu().numpy() - want)) <= ENTROPY_TOL, c["fn"]
+        one = (TP if tent else IE).compute_shannon_entropy(x[0])
+        assert isinstance(one, float) and abs(one - want[0]) <= ENTROPY_TOL
+        if tent:
+            mask, num, adapt = TP.high_entropy_gate(x, 7.16)
+            assert np.array_equal(mask.cpu().numpy(), want > 7.16) and num == int((want > 7.16).sum())
+            assert adapt == (num > len(want) / 2)
+            assert np.array_equal(IE.adaptive_mask(x).cpu().numpy(), want > IE.ENTROPY_THRESHOLD)

@@ -164,3 +164,27 @@ def test_tta16_batch_and_device_draws(cuda):
     draws = V.tta16_draws(n, crop, br, ct, "cuda")
     got2 = V.tta16(tn, None, None, None, TI.CIFAR100_MEAN, TI.CIFAR100_STD, draws=draws).cpu().numpy()
     assert np.array_equal(got, got2)
+
+
+@pytest.mark.parametrize("shape", [(64, 3, 32, 32), (5, 3, 37, 53), (3, 1, 32, 32), (2, 3, 224, 224), (0, 3, 32, 32)])
+def test_shannon_entropy(cuda, shape):
+    """Entropy gate vs the oracle: exact counts, entropy to 1e-12; skewed / clamped / NaN inputs, odd sizes."""
+    B = _B()
+    rng = np.random.default_rng(5)
+    x = rng.normal(0.3, 0.9, shape).astype(np.float32)
+    if shape[0] > 2:
+        x[0] = 0.5
+        x[1].reshape(-1)[:7] = [np.nan, np.inf, -np.inf, 1.0, 0.0, -0.0, 1.0000001]
+        x[2] = np.nan                                       # nothing countable -> NaN
+    xd = _cu(x)
+    mean, std = (0.4914, 0.4822, 0.4465)[:shape[1]], (0.2023, 0.1994, 0.2010)[:shape[1]]
+    for kw in ({}, {"mean": mean, "std": std}):
+        e, h = B.shannon_entropy(xd, return_counts=True, **kw)
+        we, wh = O.shannon_entropy(x, **kw)
+        assert np.array_equal(h.cpu().numpy().astype(np.int64), wh)
+        got = e.cpu().numpy()
+        assert np.array_equal(np.isnan(got), np.isnan(we))
+        ok = ~np.isnan(we)
+        assert np.all(np.abs(got[ok] - we[ok]) <= 1e-12)
+    if shape[0] > 2:
+        assert np.isnan(B.shannon_entropy(xd)[2].item()) and B.shannon_entropy(xd)[0].item() == 0.0

@@ -67,6 +67,9 @@ def main():
     draws = V.tta16_draws(n1, crop, br, ct, "cuda")
     rec("C3 TTA 16 views / image (fused)", timeit(lambda: V.tta16(tn, None, None, None, tta_initial.CIFAR100_MEAN, tta_initial.CIFAR100_STD, out=vout[k[0] & 1], draws=draws), iters=10),
         n1 * (12288 + 16 * 12288), n1 * 16, "view")
+    # ---- 8f-3: Shannon-entropy gate over the same normalised batch (12 288 B read per image) ----
+    rec("8f-3 Shannon-entropy gate (256-bin, f64)", timeit(lambda: B.shannon_entropy(tn, tta_initial.CIFAR100_MEAN, tta_initial.CIFAR100_STD)),
+        n1 * 12288, n1, "img")
     # ---- C5: FGSM eps sweep, 10000 x 3x32x32 f32 (24 576 B read + E * 12 288 B written per image) ----
     xf = B.to_tensor(x)
     g = torch.randn_like(xf)
