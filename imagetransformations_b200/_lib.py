@@ -93,6 +93,8 @@ _PROTOS = {
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
     "imgtx_shannon_entropy_f32": [_vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _vp],
+    "imgtx_tensor_tta_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp],
+    "imgtx_mean_views_f32": [_vp, _vp, _i64, _int, _vp],
 }
 _RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64,
              "imgtx_cc_noise_table_words": C.c_int64}

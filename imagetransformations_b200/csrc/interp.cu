@@ -113,12 +113,12 @@ perspective_tensor_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ 
     const float X = (float)x + 0.5f, Y = (float)y + 0.5f;
     const float t0 = __fdiv_rn(co[0], hw), t1 = __fdiv_rn(co[1], hw), t2 = __fdiv_rn(co[2], hw);
     const float t3 = __fdiv_rn(co[3], hh), t4 = __fdiv_rn(co[4], hh), t5 = __fdiv_rn(co[5], hh);
-    const float g1x = __fadd_rn(__fadd_rn(__fmul_rn(X, t0), __fmul_rn(Y, t1)), t2);
-    const float g1y = __fadd_rn(__fadd_rn(__fmul_rn(X, t3), __fmul_rn(Y, t4)), t5);
-    const float g2 = __fadd_rn(__fadd_rn(__fmul_rn(X, co[6]), __fmul_rn(Y, co[7])), 1.0f);
+    const float g1x = __fadd_rn(__fmaf_rn(Y, t1, __fmul_rn(X, t0)), t2);   // torch.bmm's order on the CPU reference
+    const float g1y = __fadd_rn(__fmaf_rn(Y, t4, __fmul_rn(X, t3)), t5);
+    const float g2 = __fadd_rn(__fmaf_rn(Y, co[7], __fmul_rn(X, co[6])), 1.0f);
     const float gx = __fsub_rn(__fdiv_rn(g1x, g2), 1.0f), gy = __fsub_rn(__fdiv_rn(g1y, g2), 1.0f);
-    const float ix = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(gx, 1.0f), (float)w), 1.0f), 2.0f);
-    const float iy = __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(gy, 1.0f), (float)h), 1.0f), 2.0f);
+    const float ix = __fmaf_rn(__fadd_rn(gx, 1.0f), __fmul_rn(0.5f, (float)w), -0.5f);   // ATen: fma(g + 1, size/2, -0.5)
+    const float iy = __fmaf_rn(__fadd_rn(gy, 1.0f), __fmul_rn(0.5f, (float)h), -0.5f);
     const float fx0 = floorf(ix), fy0 = floorf(iy);
     const float wx1 = __fsub_rn(ix, fx0), wy1 = __fsub_rn(iy, fy0);
     const float wx0 = __fsub_rn(1.0f, wx1), wy0 = __fsub_rn(1.0f, wy1);
@@ -130,7 +130,7 @@ perspective_tensor_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ 
     const bool oky0 = y0 >= 0 && y0 < h, oky1 = y0 + 1 >= 0 && y0 + 1 < h;
     const float m00 = (okx0 && oky0) ? 1.f : 0.f, m01 = (okx1 && oky0) ? 1.f : 0.f;
     const float m10 = (okx0 && oky1) ? 1.f : 0.f, m11 = (okx1 && oky1) ? 1.f : 0.f;
-    const float mask = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(m00, w00), __fmul_rn(m01, w01)), __fmul_rn(m10, w10)), __fmul_rn(m11, w11));
+    const float mask = __fmaf_rn(m11, w11, __fmaf_rn(m10, w10, __fmaf_rn(m01, w01, __fmul_rn(m00, w00))));
     const uint8_t* im = in + img * (int64_t)h * w * c;
     const int cx0 = clampi(x0, 0, w - 1), cx1 = clampi(x0 + 1, 0, w - 1), cy0 = clampi(y0, 0, h - 1), cy1 = clampi(y0 + 1, 0, h - 1);
     for (int ch = 0; ch < c; ++ch) {
@@ -138,7 +138,7 @@ perspective_tensor_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ 
       const float v01 = m01 * __fdiv_rn((float)im[((int64_t)cy0 * w + cx1) * c + ch], 255.0f);
       const float v10 = m10 * __fdiv_rn((float)im[((int64_t)cy1 * w + cx0) * c + ch], 255.0f);
       const float v11 = m11 * __fdiv_rn((float)im[((int64_t)cy1 * w + cx1) * c + ch], 255.0f);
-      float v = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(v00, w00), __fmul_rn(v01, w01)), __fmul_rn(v10, w10)), __fmul_rn(v11, w11));
+      float v = __fmaf_rn(v11, w11, __fmaf_rn(v10, w10, __fmaf_rn(v01, w01, __fmul_rn(v00, w00))));
       v = __fadd_rn(__fmul_rn(v, mask), __fmul_rn(__fsub_rn(1.0f, mask), fill));
       out[i * c + ch] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
     }

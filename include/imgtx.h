@@ -372,6 +372,28 @@ int imgtx_float_corrupt_f32(const float* x, const float* noise, float* out, int6
 int imgtx_shannon_entropy_f32(const float* x, int64_t n, int c, int h, int w, const float* mean_host,
                               const float* std_host, double* entropy_dev, uint32_t* counts_dev, imgtx_stream_t stream);
 
+/* ---- tensor-backend TTA chain ------------------------------------------------ */
+/* One record per OUTPUT image of TestTimeAugmentation (fall_2025/post_hoc_aaryaa.py:24-51): the draws of
+   Compose([RandomHorizontalFlip, RandomRotation(10), RandomAffine(0, scale), ColorJitter(brightness),
+   RandomPerspective]) already turned into torchvision's parameters on the host. */
+typedef struct {
+  int32_t flip;        /* RandomHorizontalFlip fired */
+  int32_t perspective; /* RandomPerspective fired */
+  float brightness;    /* ColorJitter brightness factor (f32 cast of the Python float) */
+  float reserved;
+  float rot[6];        /* _get_inverse_affine_matrix([0,0], -angle, [0,0], 1, [0,0]) cast to f32 */
+  float aff[6];        /* _get_inverse_affine_matrix([0,0], 0, [0,0], scale, [0,0]) cast to f32 */
+  float persp[8];      /* _get_perspective_coeffs(startpoints, endpoints) cast to f32 */
+} imgtx_tta_chain_t;
+/* x f32 (n,c,h,w) -> out f32 (n*views,c,h,w): output image j is the chain chains_dev[j] applied to input image
+   j / views.  NEAREST rotate/affine through torchvision's f32 grid (bit-identical picks), brightness blend + clamp,
+   BILINEAR perspective with the ones-mask fill (within 1e-5*max(1,|v|) of torch's grid_sample: summation order). */
+int imgtx_tensor_tta_f32(const float* x, float* out, int64_t n, int views, int c, int h, int w,
+                         const imgtx_tta_chain_t* chains_dev, imgtx_stream_t stream);
+/* Mean over views: in f32 (views, count) -> out[i] = (((0 + in[0][i]) + in[1][i]) + ...) / views
+   (fall_2025/post_hoc_aaryaa.py:334-342 mean logits; fall_2025/TTA_transforms.py:208-209 mean probabilities). */
+int imgtx_mean_views_f32(const float* in, float* out, int64_t count, int views, imgtx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

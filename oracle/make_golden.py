@@ -591,6 +591,57 @@ def gen_entropy(X):
     b.save()
 
 
+def gen_posthoc(X):
+    """Tensor-backend TTA chain: the reference's TestTimeAugmentation()(x) on f32 CHW tensors under
+    recorded torch seeds, with the draws it consumed (replayed through torchvision's own get_params), and the mean over
+    T+1 'logit' vectors accumulated as post_hoc_aaryaa.py:334-342 does."""
+    import torch
+    import torchvision.transforms as T
+    b = Book("posthoc")
+    tta = R.post_hoc().TestTimeAugmentation()
+    x = torch.from_numpy(X["x32"]).permute(0, 3, 1, 2).contiguous().float().div(255)
+    rng = np.random.default_rng(43)
+    xodd = torch.from_numpy(rng.random((2, 3, 37, 53)).astype(np.float32))
+    b.put("x", x.numpy())
+    b.put("xodd", xodd.numpy())
+    for key, arr in (("x", x), ("xodd", xodd)):
+        n, _, h, w = arr.shape
+        views = 6
+        outs, draws = [], {k: [] for k in ("flip", "angle", "scale", "brightness", "persp", "start", "end")}
+        for i in range(n):
+            for v in range(views):
+                seed = 7000 + 100 * i + v
+                torch.manual_seed(seed)
+                outs.append(tta(arr[i]).numpy())
+                torch.manual_seed(seed)                  # replay: the same RNG consumption, draw by draw
+                flip = bool(torch.rand(1) < 0.5)
+                angle = T.RandomRotation.get_params([-10.0, 10.0])
+                _, _, scale, _ = T.RandomAffine.get_params((0.0, 0.0), None, (1.0, 1.1), None, [w, h])
+                _, br, _, _, _ = T.ColorJitter.get_params((0.9, 1.1), None, None, None)
+                fired = bool(torch.rand(1) < 0.5)
+                sp, ep = T.RandomPerspective.get_params(w, h, 0.2) if fired else ([[0, 0]] * 4, [[0, 0]] * 4)
+                for k, val in zip(draws, (flip, angle, scale, br, fired, sp, ep)):
+                    draws[k].append(val)
+        b.case("post_hoc_aaryaa.TestTimeAugmentation", key, np.stack(outs), args={"views": views, "seed0": 7000},
+               draws={"flip": np.array(draws["flip"], np.int32), "angle": np.array(draws["angle"], np.float64),
+                      "scale": np.array(draws["scale"], np.float64),
+                      "brightness": np.array(draws["brightness"], np.float64),
+                      "persp": np.array(draws["persp"], np.int32), "start": np.array(draws["start"], np.int64),
+                      "end": np.array(draws["end"], np.int64)})
+    # mean over T+1 logit vectors (:334-342) and torch.stack(...).mean(0) (TTA_transforms.py:208-209)
+    L = [torch.from_numpy(rng.normal(0, 3, (1, 100)).astype(np.float32)) for _ in range(11)]
+    l_hat = 0
+    for logits in L:
+        l_hat = l_hat + logits
+    l_hat = l_hat / (10 + 1)
+    b.put("logits", torch.stack(L).numpy())
+    b.case("post_hoc_aaryaa.mean_logits", "logits", l_hat.numpy())
+    probs = [torch.softmax(t, dim=1) for t in L[:4]]
+    b.put("probs", torch.stack(probs).numpy())
+    b.case("TTA_transforms.mean_probs", "probs", torch.stack(probs).mean(dim=0).numpy())
+    b.save()
+
+
 def gen_fixtures(X):
     """The reference's own CIFAR-10-C samples (CIFAR-10-C/store/*.png, lossless, all severity 1 — SURVEY §2.1) as one
     array per corruption type, ordered by source index (0, 1001, 2002, 3003, 4004)."""
@@ -610,7 +661,7 @@ def main():
     if not R.available():
         raise SystemExit("the reference is not mounted at " + R.REF_ROOT)
     X = make_inputs()
-    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "entropy", "fixtures"]
+    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "entropy", "posthoc", "fixtures"]
     for w in which:
         globals()["gen_" + w](X)
 

@@ -154,6 +154,13 @@ def entropy_gate():
     return _cache["entropy_gate"]
 
 
+def post_hoc():
+    """TestTimeAugmentation of fall_2025/post_hoc_aaryaa.py:22-51 (the class only; the file trains models at import)."""
+    if "post_hoc" not in _cache:
+        _cache["post_hoc"] = slice_module("fall_2025/post_hoc_aaryaa.py", {"TestTimeAugmentation"})
+    return _cache["post_hoc"]
+
+
 def angellic():
     if "angellic" not in _cache:
         _cache["angellic"] = slice_module("pipenline/angellic.py",

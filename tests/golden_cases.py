@@ -201,3 +201,33 @@ def cifarc_synthetic(seed):
         labels = rng.integers(0, 10, 50000).astype(np.int64)
         _cifarc[seed] = (data, labels)
     return _cifarc[seed]
+
+
+# ---- tensor-backend TTA chain: shared by the CPU and GPU golden tests --------------------------------
+TTA_CHAIN_TOL = 1e-5   # |a-b| <= 1e-5*max(1,|b|) on perspective views (grid_sample summation order);
+                       # views where RandomPerspective did not fire are NEAREST gathers + one multiply: bit-exact
+
+
+def posthoc_chain_cases():
+    """(input (n,c,h,w), expected (n*views,c,h,w), views, list of per-output draw dicts) per golden chain case."""
+    g = golden("posthoc")
+    out = []
+    for c in g.cases:
+        if c["fn"] != "post_hoc_aaryaa.TestTimeAugmentation":
+            continue
+        d = g.draws(c)
+        draws = []
+        for j in range(len(d["flip"])):
+            fired = bool(d["persp"][j])
+            draws.append({"flip": bool(d["flip"][j]), "angle": float(d["angle"][j]), "scale": float(d["scale"][j]),
+                          "brightness": float(d["brightness"][j]),
+                          "perspective": (d["start"][j].tolist(), d["end"][j].tolist()) if fired else None})
+        out.append((g.arr(c["in"]), g.arr(c["out"]), c["args"]["views"], draws))
+    return out
+
+
+def check_chain_view(got, want, fired):
+    if not fired:
+        assert np.array_equal(got, want)
+    else:
+        assert np.all(np.abs(got - want) <= TTA_CHAIN_TOL * np.maximum(1.0, np.abs(want)))

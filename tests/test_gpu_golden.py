@@ -235,3 +235,26 @@ def test_cuda_entropy_golden(cuda):
             assert np.array_equal(mask.cpu().numpy(), want > 7.16) and num == int((want > 7.16).sum())
             assert adapt == (num > len(want) / 2)
             assert np.array_equal(IE.adaptive_mask(x).cpu().numpy(), want > IE.ENTROPY_THRESHOLD)
+
+
+def test_cuda_tensor_tta_chain_golden(cuda):
+    """SURVEY 8f-4 through the C ABI: every golden view in one launch per case; the drop-in class replays the reference's
+    torch RNG consumption under the recorded seeds; mean over views bit-exact."""
+    from imagetransformations_b200 import post_hoc_aaryaa as PH
+    for x, want, views, draws in G.posthoc_chain_cases():
+        recs = np.stack([PH.chain_record(d) for d in draws])
+        got = PH.tta_chain_batch(torch.from_numpy(x).cuda(), recs, views=views).cpu().numpy()
+        for j, d in enumerate(draws):
+            G.check_chain_view(got[j], want[j], d["perspective"] is not None)
+        tta = PH.TestTimeAugmentation()
+        xd = torch.from_numpy(x).cuda()
+        for i in range(x.shape[0]):
+            for v in (0, views - 1):
+                torch.manual_seed(7000 + 100 * i + v)
+                one = tta(xd[i]).cpu().numpy()
+                assert np.array_equal(one, got[i * views + v])
+    g = G.golden("posthoc")
+    for c in g.cases:
+        if c["fn"] in ("post_hoc_aaryaa.mean_logits", "TTA_transforms.mean_probs"):
+            out = PH.mean_views(torch.from_numpy(g.arr(c["in"])).cuda()).cpu().numpy()
+            assert np.array_equal(out, g.arr(c["out"])), c["fn"]

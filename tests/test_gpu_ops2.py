@@ -188,3 +188,34 @@ def test_shannon_entropy(cuda, shape):
         assert np.all(np.abs(got[ok] - we[ok]) <= 1e-12)
     if shape[0] > 2:
         assert np.isnan(B.shannon_entropy(xd)[2].item()) and B.shannon_entropy(xd)[0].item() == 0.0
+
+
+@pytest.mark.parametrize("shape", [(40, 3, 32, 32), (6, 3, 37, 53), (4, 1, 64, 48), (0, 3, 32, 32)])
+def test_tensor_tta_chain_batch(cuda, shape):
+    """Fused tensor-backend TTA chain vs the oracle on seeded draws: views without perspective bit-exact, perspective
+    views within 1e-5*max(1,|v|); extreme draws (angle +-10, scale ends, identity) included."""
+    from imagetransformations_b200 import post_hoc_aaryaa as PH
+    from oracle import np_chains as CH
+    n, c, h, w = shape
+    views = 3
+    rng = np.random.default_rng(9)
+    x = rng.random(shape).astype(np.float32)
+    torch.manual_seed(123)
+    draws = [PH.draw_chain(w, h) for _ in range(n * views)]
+    if n:
+        draws[0].update(flip=False, angle=0.0, scale=1.0, brightness=1.0, perspective=None)   # identity chain
+        draws[1].update(angle=10.0, scale=1.1)
+        draws[2].update(angle=-10.0, scale=1.0, brightness=1.1)
+    recs = np.stack([PH.chain_record(d) for d in draws]) if n else np.zeros(0, PH.CHAIN_DTYPE)
+    got = PH.tta_chain_batch(_cu(x), recs, views=views).cpu().numpy()
+    assert got.shape == (n * views, c, h, w)
+    if n:
+        assert np.array_equal(got[0], x[0])
+    for j, d in enumerate(draws):
+        r = recs[j]
+        want = CH.tensor_tta_chain(x[j // views], d["flip"], r["rot"], r["aff"], d["brightness"],
+                                   r["persp"] if d["perspective"] is not None else None)
+        if d["perspective"] is None:
+            assert np.array_equal(got[j], want), j
+        else:
+            assert np.all(np.abs(got[j] - want) <= 1e-5 * np.maximum(1.0, np.abs(want))), j

@@ -70,6 +70,17 @@ def main():
     # ---- 8f-3: Shannon-entropy gate over the same normalised batch (12 288 B read per image) ----
     rec("8f-3 Shannon-entropy gate (256-bin, f64)", timeit(lambda: B.shannon_entropy(tn, tta_initial.CIFAR100_MEAN, tta_initial.CIFAR100_STD)),
         n1 * 12288, n1, "img")
+    # ---- 8f-4: tensor-backend TTA chain, 10 views per image (12 288 B read + 10 * 12 288 B written per image) ----
+    from imagetransformations_b200 import post_hoc_aaryaa as PH
+    torch.manual_seed(5)
+    base = [PH.chain_record(PH.draw_chain(32, 32)) for _ in range(512)]
+    recs = np.stack([base[i % 512] for i in range(n1 * 10)])
+    rdev = torch.from_numpy(recs.view(np.uint8).reshape(-1).copy()).cuda()
+    tout = torch.empty((n1 * 10, 3, 32, 32), dtype=torch.float32, device="cuda")
+    lib0 = L.load()
+    rec("8f-4 tensor TTA chain, 10 views / image (fused)",
+        timeit(lambda: L.check(lib0.imgtx_tensor_tta_f32(tn.data_ptr(), tout.data_ptr(), n1, 10, 3, 32, 32, rdev.data_ptr(), B._stream())), iters=10),
+        n1 * 11 * 12288, n1 * 10, "view")
     # ---- C5: FGSM eps sweep, 10000 x 3x32x32 f32 (24 576 B read + E * 12 288 B written per image) ----
     xf = B.to_tensor(x)
     g = torch.randn_like(xf)
