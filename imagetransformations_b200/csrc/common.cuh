@@ -142,6 +142,17 @@ __device__ __forceinline__ void fence_async_smem() {
 }
 
 // --- small arithmetic helpers that pin down library semantics --------------------------------
+// n / d and n % d for a run-time divisor without the integer-division sequence: exact while n * d < 2^32.
+struct FastDiv {
+  uint32_t m, d;
+  __device__ __forceinline__ explicit FastDiv(int dd) : m(dd > 1 ? 0xFFFFFFFFu / (uint32_t)dd + 1u : 0u), d((uint32_t)dd) {}
+  __device__ __forceinline__ int div(int n) const { return d > 1 ? (int)__umulhi((uint32_t)n, m) : n; }
+  __device__ __forceinline__ void divmod(int n, int& q, int& r) const {
+    q = div(n);
+    r = n - q * (int)d;
+  }
+};
+
 __device__ __forceinline__ uint8_t clip8(int v) { return (uint8_t)(v < 0 ? 0 : (v > 255 ? 255 : v)); }
 // C cast (uint8)float for values known to be in [0,256): truncation toward zero.
 __device__ __forceinline__ uint8_t trunc8(float v) { return (uint8_t)__float2int_rz(v); }

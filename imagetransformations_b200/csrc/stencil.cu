@@ -97,6 +97,157 @@ struct OpCvGauss : NoSpill {
 };
 
 // ---------------------------------------------------------------------------------------------
+// The same blur with four multiply-adds per instruction (small images, every Q8 weight <= 255, radius < min(h, w)):
+//   * the image is de-interleaved into per-channel byte rows with the REFLECT_101 border materialised (a canvas whose
+//     left pad is a multiple of four), so a run of taps is a run of bytes;
+//   * a thread produces four adjacent outputs; output i needs the canvas bytes from 4q + (pad - r) + i on, i.e. the
+//     SAME aligned words for every thread with the kernel pre-shifted by (pad - r + i) bytes: four packed weight rows,
+//     one __dp4a per word and output;
+//   * the u16 intermediate (<= 65280) is stored transposed as a high-byte and a low-byte plane, border rows reflected,
+//     so the vertical pass is the same routine on each plane: v = (sum_hi << 8) + sum_lo, out = (v + 2^15) >> 16.
+// Integer arithmetic throughout: identical to the literal kernel above (tests compare both with the oracle).
+struct OpCvGaussDp : NoSpill {
+  using Params = CvGaussParams;
+  static constexpr int kThreads = 256;
+  static constexpr bool kCifarCopy = true;
+  static constexpr int kHeader = 4 * 12 * 4;   // Wt[4][12]
+  __host__ __device__ static int pad_of(int r) { return (r + 3) & ~3; }
+  __host__ __device__ static int row_bytes(int len, int r) {
+    int b = len + 2 * pad_of(r);
+    return (b & 31) == 0 ? b + 4 : b;          // keep the word stride off a multiple of 8 banks
+  }
+  __host__ __device__ static size_t per_image(const Shape& s) {
+    const int r = s.aux;
+    return (size_t)s.c * s.h * row_bytes(s.w, r) + 2 * (size_t)s.c * s.w * row_bytes(s.h, r);
+  }
+  // +64: the zero-weight tail words of the last column may lie past the last plane
+  static size_t scratch_bytes(const Shape& s, int G) { return align_up(kHeader + (size_t)G * per_image(s) + 64, 16); }
+  static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+
+  __device__ static void prepare(const Shape& s, const Params& p, uint8_t* scratch, bool) {
+    uint32_t* Wt = reinterpret_cast<uint32_t*>(scratch);
+    const int r = s.aux, n = p.ksize, t0 = pad_of(r) - r;
+    for (int e = threadIdx.x; e < 48; e += kThreads) {
+      const int i = e / 12, m = e - i * 12;
+      uint32_t wv = 0;
+      for (int lane = 0; lane < 4; ++lane) {
+        const int j = 4 * m + lane - (t0 + i);
+        if (j >= 0 && j < n) wv |= (uint32_t)p.k[j] << (8 * lane);
+      }
+      Wt[e] = wv;
+    }
+  }
+
+  template <bool STAGED>
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+                             uint8_t* scratch, uint8_t*) {
+    const int tid = threadIdx.x;
+    const int c = s.c, w = s.w, h = s.h, n = p.ksize, r = s.aux;
+    const int PL = pad_of(r), W2 = row_bytes(w, r), H2 = row_bytes(h, r);
+    const int MW = ((PL - r + 3 + n - 1) >> 2) + 1;
+    const uint32_t* Wt = reinterpret_cast<const uint32_t*>(scratch);
+    const size_t per = per_image(s);
+    const int wq = w >> 2, hq = h >> 2, W2w = W2 >> 2;
+    const FastDiv dW2w(W2w), dh(h), dc(c), dwq(wq), dhq(hq), dw(w), dr(r), dcol(2 * c * w);
+    // ---- canvas: planar rows with reflected borders ----
+    if (c == 3) {
+      // interior: four RGB pixels = three aligned words -> one word per channel plane (byte permutes)
+      for (int it = tid; it < g * h * wq; it += kThreads) {
+        int t, q, y, j;
+        dwq.divmod(it, t, q);
+        dh.divmod(t, j, y);
+        const uint32_t* sp = reinterpret_cast<const uint32_t*>(src + (size_t)j * s.in_bytes + (size_t)y * w * 3) + q * 3;
+        const uint32_t w0 = sp[0], w1 = sp[1], w2 = sp[2];
+        uint32_t* cv = reinterpret_cast<uint32_t*>(scratch + kHeader + j * per) + y * W2w + (PL >> 2) + q;
+        cv[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);            // bytes 0, 3, 6, 9
+        cv[h * W2w] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);      // bytes 1, 4, 7, 10
+        cv[2 * h * W2w] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);  // bytes 2, 5, 8, 11
+      }
+    }
+    {
+      // border words (all words when c != 3): byte gathers through the reflection
+      const int PLw = PL >> 2, edge = c == 3 ? 2 * PLw : W2w;
+      const FastDiv de(edge);
+      for (int it = tid; it < g * c * h * edge; it += kThreads) {
+        int t, e, y, ch, j;
+        de.divmod(it, t, e);
+        dh.divmod(t, t, y);
+        dc.divmod(t, j, ch);
+        const int xw = c == 3 ? (e < PLw ? e : e - PLw + PLw + wq) : e;
+        const uint8_t* sj = src + (size_t)j * s.in_bytes + (size_t)y * w * c + ch;
+        uint32_t word = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int cx = 4 * xw + k - PL;
+          const int rx = cx < 0 ? -cx : (cx >= w ? 2 * w - 2 - cx : cx);     // r < w: one reflection
+          if (cx >= -r && cx < w + r) word |= (uint32_t)sj[rx * c] << (8 * k);
+        }
+        if (xw < W2w) reinterpret_cast<uint32_t*>(scratch + kHeader + j * per)[(ch * h + y) * W2w + xw] = word;
+      }
+    }
+    __syncthreads();
+    // ---- horizontal: four outputs per item, transposed hi / lo planes out ----
+    const size_t plane = (size_t)c * w * H2;
+    for (int it = tid; it < g * c * h * wq; it += kThreads) {
+      int t, q, y, ch, j;
+      dwq.divmod(it, t, q);
+      dh.divmod(t, t, y);
+      dc.divmod(t, j, ch);
+      uint8_t* base = scratch + kHeader + j * per;
+      const uint32_t* row = reinterpret_cast<const uint32_t*>(base) + (ch * h + y) * W2w + q;
+      uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+      for (int m = 0; m < MW; ++m) {
+        const uint32_t v = row[m];
+        a0 = __dp4a(v, Wt[m], a0); a1 = __dp4a(v, Wt[12 + m], a1);
+        a2 = __dp4a(v, Wt[24 + m], a2); a3 = __dp4a(v, Wt[36 + m], a3);
+      }
+      uint8_t* th = base + (size_t)c * h * W2 + (size_t)(ch * w + 4 * q) * H2 + PL + y;
+      uint8_t* tl = th + plane;
+      th[0] = (uint8_t)(a0 >> 8); th[H2] = (uint8_t)(a1 >> 8); th[2 * H2] = (uint8_t)(a2 >> 8); th[3 * H2] = (uint8_t)(a3 >> 8);
+      tl[0] = (uint8_t)a0; tl[H2] = (uint8_t)a1; tl[2 * H2] = (uint8_t)a2; tl[3 * H2] = (uint8_t)a3;
+    }
+    __syncthreads();
+    // ---- reflect the border rows of both planes ----
+    for (int it = tid; it < g * 2 * c * w * r; it += kThreads) {
+      int t, d, col, j;
+      dr.divmod(it, t, d);
+      dcol.divmod(t, j, col);
+      uint8_t* colp = scratch + kHeader + j * per + (size_t)c * h * W2 + (size_t)col * H2 + PL;
+      colp[-1 - d] = colp[1 + d];
+      colp[h + d] = colp[h - 2 - d];
+    }
+    __syncthreads();
+    // ---- vertical: the same routine down each column of both planes ----
+    for (int it = tid; it < g * c * w * hq; it += kThreads) {
+      int t, q, x, ch, j;
+      dhq.divmod(it, t, q);
+      dw.divmod(t, t, x);
+      dc.divmod(t, j, ch);
+      const uint8_t* base = scratch + kHeader + j * per + (size_t)c * h * W2;
+      const uint32_t* ch_ = reinterpret_cast<const uint32_t*>(base + (size_t)(ch * w + x) * H2) + q;
+      const uint32_t* cl_ = reinterpret_cast<const uint32_t*>(base + plane + (size_t)(ch * w + x) * H2) + q;
+      uint32_t hi[4] = {0, 0, 0, 0}, lo[4] = {0, 0, 0, 0};
+      for (int m = 0; m < MW; ++m) {
+        const uint32_t vh = ch_[m], vl = cl_[m];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint32_t wv = Wt[12 * i + m];
+          hi[i] = __dp4a(vh, wv, hi[i]);
+          lo[i] = __dp4a(vl, wv, lo[i]);
+        }
+      }
+      uint8_t* o = dst + (size_t)j * s.out_bytes + ((size_t)(4 * q) * w + x) * c + ch;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const uint32_t v = (hi[i] << 8) + lo[i] + (1u << 15);
+        o[(size_t)i * w * c] = (uint8_t)min(v >> 16, 255u);
+      }
+    }
+    __syncthreads();
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
 struct PilGaussParams {
   int ri;
   uint32_t ww, fw;
@@ -224,7 +375,16 @@ extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_
   p.ksize = ksize;
   int rc = imgtx_cv_gaussian_kernel_host(ksize, sigma, p.k);
   if (rc) return rc;
-  return launch_image_op<OpCvGauss>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+  Shape s = make_shape(h, w, c, h, w);
+  const int r = ksize >> 1;
+  bool small_weights = true;
+  for (int i = 0; i < ksize; ++i) small_weights = small_weights && p.k[i] >= 0 && p.k[i] <= 255;
+  s.aux = r;
+  if (!force_exact() && small_weights && r >= 1 && r < std::min(h, w) && (w & 3) == 0 && (h & 3) == 0 &&
+      OpCvGaussDp::per_image(s) <= 40 * 1024 && (OpCvGaussDp::row_bytes(h, r) & 3) == 0 && (OpCvGaussDp::row_bytes(w, r) & 3) == 0)
+    return launch_image_op<OpCvGaussDp>(in, out, n, s, p, (cudaStream_t)stream);
+  s.aux = 0;
+  return launch_image_op<OpCvGauss>(in, out, n, s, p, (cudaStream_t)stream);
 }
 
 extern "C" int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
