@@ -45,9 +45,12 @@ __device__ __forceinline__ void affine_pick(const float* r, int x, int y, int w,
   ry = rintf(iy);
 }
 
+// CT: compile-time channel count (3 = RGB: the channel loops unroll), 0 = run-time c_rt
+template <int CT>
 __global__ void __launch_bounds__(256)
-tensor_tta_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n_out, int views, int c, int h, int w,
+tensor_tta_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n_out, int views, int c_rt, int h, int w,
                   const TtaChain* __restrict__ chains) {
+  const int c = CT ? CT : c_rt;
   extern __shared__ __align__(16) float sm[];
   const int hw = h * w, chw = c * hw;
   float* A = sm;
@@ -82,20 +85,23 @@ tensor_tta_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t 
       affine_pick(r1, xx, yy, w, h, rx, ry);
       const bool ok = rx >= 0.0f && rx < (float)w && ry >= 0.0f && ry < (float)h;
       const int s = ok ? (int)ry * w + (int)rx : 0;
+#pragma unroll
       for (int k = 0; k < c; ++k) B[k * hw + p] = ok ? A[k * hw + s] : 0.0f;
     }
     __syncthreads();
     // stage 2: RandomAffine(scale) -> F.affine(NEAREST), then ColorJitter brightness: (b*v + 0).clamp(0,1): B -> A / out
     const bool persp = ch.perspective != 0;
+    const float bright = ch.brightness;
     for (int p = tid, yy = ty0, xx = tx0; p < hw; p += 256, yy += dy, xx += dx) {
       if (xx >= w) { xx -= w; ++yy; }
       float rx, ry;
       affine_pick(r2, xx, yy, w, h, rx, ry);
       const bool ok = rx >= 0.0f && rx < (float)w && ry >= 0.0f && ry < (float)h;
       const int s = ok ? (int)ry * w + (int)rx : 0;
+#pragma unroll
       for (int k = 0; k < c; ++k) {
         float v = ok ? B[k * hw + s] : 0.0f;
-        v = __fadd_rn(__fmul_rn(ch.brightness, v), 0.0f);
+        v = __fadd_rn(__fmul_rn(bright, v), 0.0f);
         v = v != v ? v : fminf(fmaxf(v, 0.0f), 1.0f);
         if (persp) A[k * hw + p] = v;
         else oi[k * hw + p] = v;
@@ -129,6 +135,7 @@ tensor_tta_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t 
       const float m10 = (okx0 && oky1) ? 1.f : 0.f, m11 = (okx1 && oky1) ? 1.f : 0.f;
       const float mask = __fmaf_rn(m11, w11, __fmaf_rn(m10, w10, __fmaf_rn(m01, w01, __fmul_rn(m00, w00))));
       const int cx0 = clampi(x0, 0, w - 1), cx1 = clampi(x0 + 1, 0, w - 1), cy0 = clampi(y0, 0, h - 1), cy1 = clampi(y0 + 1, 0, h - 1);
+#pragma unroll
       for (int k = 0; k < c; ++k) {
         const float* a = A + k * hw;
         const float v00 = (okx0 && oky0) ? a[cy0 * w + cx0] : 0.f, v01 = (okx1 && oky0) ? a[cy0 * w + cx1] : 0.f;
@@ -162,12 +169,13 @@ extern "C" int imgtx_tensor_tta_f32(const float* x, float* out, int64_t n, int v
   IMGTX_CHECK_ARG(x && out && chains_dev, "null pointer");
   const size_t smem = (size_t)2 * c * h * w * sizeof(float);
   IMGTX_CHECK_ARG(smem + 1024 <= (size_t)max_smem_optin(), "image (%dx%dx%d) does not fit in shared memory for the fused TTA chain", c, h, w);
-  IMGTX_CUDA_OK(cudaFuncSetAttribute(tensor_tta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kern = c == 3 ? tensor_tta_kernel<3> : tensor_tta_kernel<0>;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)max_smem_optin() / (smem + 1024)));
   const int64_t n_out = n * views;
   const int64_t grid = std::min<int64_t>(n_out, (int64_t)sm_count() * per_sm);
-  tensor_tta_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(x, out, n_out, views, c, h, w,
-                                                                       reinterpret_cast<const TtaChain*>(chains_dev));
+  kern<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(x, out, n_out, views, c, h, w,
+                                                          reinterpret_cast<const TtaChain*>(chains_dev));
   IMGTX_LAUNCH_OK();
   return IMGTX_OK;
 }
