@@ -29,7 +29,7 @@ def test_shard_ranges_tile_the_batch():
 def _stub_corrupt(x, name, severity, draws=None, seed=0):
     """Per-image, order-sensitive stand-in: out = (x * (severity + 1) + per-image draw) mod 256."""
     d = draws["k"] if draws else torch.zeros(len(x), dtype=torch.int64)
-    d = torch.as_tensor(np.asarray(d)).reshape(-1, 1, 1, 1)
+    d = torch.as_tensor(np.asarray(d)).reshape(-1, 1, 1, 1).to(x.device)   # the shard may live on a GPU when one is present
     return ((x.to(torch.int64) * (severity + 1) + d) % 256).to(torch.uint8)
 
 
@@ -44,9 +44,10 @@ def _worker(rank, ws, port, n, q):
         assert len(sd["k"]) == hi - lo and sd["shared"] == 5
         out, sums, gathered = S.corrupt_sharded(x, "stub", 2, draws=draws, gather_outputs=True, corrupt_fn=_stub_corrupt)
         full = _stub_corrupt(torch.from_numpy(x), "stub", 2, draws=draws)
-        assert torch.equal(out, full[lo:hi])
-        assert torch.equal(gathered, full)
-        assert torch.equal(sums, S.image_checksums(full))
+        # on a GPU box the shard lives on cuda:<rank>: compare on the host
+        assert torch.equal(out.cpu(), full[lo:hi])
+        assert torch.equal(gathered.cpu(), full)
+        assert torch.equal(sums.cpu(), S.image_checksums(full).cpu())
         q.put((rank, True))
     finally:
         dist.destroy_process_group()
