@@ -22,6 +22,7 @@
 //    gather goes through L1/L2.
 #pragma once
 #include "common.cuh"
+#include <stdlib.h>
 #include <algorithm>
 
 namespace imgtx {
@@ -70,6 +71,12 @@ template <class Op, class = void>
 struct RingDepth { static constexpr int stages = 0, out_bufs = 2; };
 template <class Op>
 struct RingDepth<Op, decltype((void)Op::kStages)> { static constexpr int stages = Op::kStages, out_bufs = Op::kOutBufs; };
+
+// Ops may declare `static constexpr int kCtasPerSm = N` to replace the tuned CTAs-per-SM cap (grid size) for their launches.
+template <class Op, class = void>
+struct CtasPerSm { static constexpr int value = 0; };
+template <class Op>
+struct CtasPerSm<Op, decltype((void)Op::kCtasPerSm)> { static constexpr int value = Op::kCtasPerSm; };
 
 template <class Op>
 __global__ void __launch_bounds__(Op::kThreads, MinBlocks<Op>::value)
@@ -182,6 +189,7 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
   IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
   StagedTuning tn = staged_tuning();
   if (target_override > 0) tn.target_smem = target_override;
+  if (CtasPerSm<Op>::value > 0 && !getenv("IMGTX_CTAS_PER_SM")) tn.ctas_per_sm = CtasPerSm<Op>::value;
   const int max_smem = max_smem_optin();
   bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);
   int G = 1, stages = RingDepth<Op>::stages > 0 ? RingDepth<Op>::stages : tn.stages;
