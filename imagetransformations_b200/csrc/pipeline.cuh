@@ -188,9 +188,14 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
   if (n <= 0) return IMGTX_OK;
   IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
   StagedTuning tn = staged_tuning();
-  if (target_override > 0) tn.target_smem = target_override;
+  if (target_override > 0) {
+    tn.target_smem = target_override;
+    // sweep knob: scale an operator's own target (percent), e.g. IMGTX_TARGET_SCALE=150
+    if (const char* e = getenv("IMGTX_TARGET_SCALE")) tn.target_smem = (int)((int64_t)target_override * atoi(e) / 100);
+  }
   if (CtasPerSm<Op>::value > 0 && !getenv("IMGTX_CTAS_PER_SM")) tn.ctas_per_sm = CtasPerSm<Op>::value;
   const int max_smem = max_smem_optin();
+  if (tn.target_smem > max_smem - 1024) tn.target_smem = max_smem - 1024;   // a target can ask for more than the SM has
   bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);
   int G = 1, stages = RingDepth<Op>::stages > 0 ? RingDepth<Op>::stages : tn.stages;
   constexpr int kOut = RingDepth<Op>::out_bufs;
