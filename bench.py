@@ -152,6 +152,11 @@ def run_ours(args, rank, world, local_rank):
         raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_cores = 0
+    if world > 1 and not os.environ.get("IMGTX_NO_BIND"):
+        # one process per GPU: keep it (and the pinned buffers it allocates below) on the GPU's own NUMA node
+        from imagetransformations_b200 import shard as S
+        numa_cores = S.bind_to_gpu_cpus(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     passes = C.suite_passes()
@@ -264,7 +269,8 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "cifar10c_suite_15x5", "images_per_gpu": N_IMAGES, "image": "32x32x3 uint8",
                        "passes": len(passes), "severity_table": "cifar", "rng": "on-chip Philox4x32-10",
-                       "l2": "working set 461 MB (input + 2 rotating outputs) > 126 MB L2"},
+                       "l2": "working set 461 MB (input + 2 rotating outputs) > 126 MB L2",
+                       "host_cores_bound_per_rank": numa_cores},
             "suite_algorithmic_gbs": suite_gbs, "suite_frac_of_hbm_peak": suite_gbs / peak,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
