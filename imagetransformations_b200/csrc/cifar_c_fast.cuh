@@ -511,8 +511,9 @@ struct OpCcFogFast : NoSpill {
       mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     }
-    const float span = mx - mn;
-    for (int i = lane; i < msz * msz; i += 32) map[i] = __fdiv_rn(map[i] - mn, span);
+    // on-chip plasma is defined with one reciprocal per image (the f64 oracle law is reached through the injected-map mode)
+    const float inv_span = __fdiv_rn(1.0f, mx - mn);
+    for (int i = lane; i < msz * msz; i += 32) map[i] = __fmul_rn(map[i] - mn, inv_span);
     __syncwarp();
   }
 
