@@ -512,8 +512,12 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
         {   // G = A * F   (axis y):  G[o][x] = sum_i A[o][i] F[i][x]
           const double* Ff = F0 + f * fplane;
           double acc[4][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
+          // the operator is banded (|o - i| <= lw after the reflection is folded in): k-steps outside the band of this
+          // warp's 8 output rows multiply exact zeros and are skipped (warp-uniform branch)
+          const int klo = m0 - p.lw - 3, khi = m0 + 7 + p.lw;
 #pragma unroll
           for (int k0 = 0; k0 < kN; k0 += 4) {
+            if (k0 < klo || k0 > khi) continue;
             const double a = A[(m0 + r) * kPA + k0 + c];
 #pragma unroll
             for (int nt = 0; nt < 4; ++nt) dmma(acc[nt][0], acc[nt][1], a, Ff[(k0 + c) * kPF + nt * 8 + r]);
@@ -530,7 +534,10 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
           for (int k0 = 0; k0 < kN; k0 += 4) {
             const double a = Gf[(m0 + r) * kPA + k0 + c];
 #pragma unroll
-            for (int nt = 0; nt < 4; ++nt) dmma(acc[nt][0], acc[nt][1], a, A[(nt * 8 + r) * kPA + k0 + c]);
+            for (int nt = 0; nt < 4; ++nt) {
+              if (k0 < nt * 8 - p.lw - 3 || k0 > nt * 8 + 7 + p.lw) continue;   // outside the band of outputs nt*8 .. nt*8+7
+              dmma(acc[nt][0], acc[nt][1], a, A[(nt * 8 + r) * kPA + k0 + c]);
+            }
           }
           const int y = m0 + r;
 #pragma unroll
