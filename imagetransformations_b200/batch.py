@@ -30,6 +30,18 @@ def _check_u8(x: torch.Tensor) -> torch.Tensor:
     return x.contiguous()
 
 
+def _check_out(out: Optional[torch.Tensor], like: torch.Tensor, shape=None, dtype=None) -> torch.Tensor:
+    """A caller-supplied `out` is written through its data pointer as a dense tensor: insist that it is one."""
+    shape = tuple(like.shape) if shape is None else tuple(shape)
+    dtype = like.dtype if dtype is None else dtype
+    if out is None:
+        return torch.empty(shape, dtype=dtype, device=like.device)
+    if not (isinstance(out, torch.Tensor) and out.device == like.device and out.dtype == dtype and
+            tuple(out.shape) == shape and out.is_contiguous()):
+        raise ValueError(f"out must be a contiguous {dtype} tensor of shape {shape} on {like.device}")
+    return out
+
+
 def _check_f32(x: torch.Tensor) -> torch.Tensor:
     if not (isinstance(x, torch.Tensor) and x.is_cuda and x.dtype == torch.float32):
         raise TypeError("expected a CUDA float32 tensor")
@@ -337,13 +349,14 @@ def resize_center_crop(x: torch.Tensor, size: int, crop: int, out=None) -> torch
 # ------------------------------------------------------------------------------------------------
 # stencils
 # ------------------------------------------------------------------------------------------------
-def cv_gaussian_blur(x: torch.Tensor, ksize: int, sigma: float, out=None) -> torch.Tensor:
-    """cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8."""
+def cv_gaussian_blur(x: torch.Tensor, ksize: int, sigma: float, out=None, literal: bool = False) -> torch.Tensor:
+    """cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8.  `literal` (tests): the plain per-tap loop instead of the
+    packed dp4a form — both are the same integer arithmetic."""
     x = _check_u8(x)
     n, h, w, c = x.shape
     out = torch.empty_like(x) if out is None else out
     L.check(L.load().imgtx_cv_gaussian_blur_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, int(ksize), float(sigma),
-                                               _stream()))
+                                               L.CC_REPLAY_ALL if literal else 0, _stream()))
     return out
 
 

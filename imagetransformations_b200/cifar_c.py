@@ -13,6 +13,7 @@ them drawn on chip from Philox keyed by (seed, image index) (throughput mode).
 from __future__ import annotations
 
 import ctypes as C
+import functools
 import math
 import os
 from typing import Optional
@@ -72,6 +73,7 @@ def _reflect101(i, n):
     return np.where(m >= n, period - m, m)
 
 
+@functools.lru_cache(maxsize=None)
 def disk_taps(radius: float, alias_blur: float):
     """make_cifar_c.disk(radius, alias_blur) as sparse taps: the 17x17 indicator disk, normalised in f32, blurred with
     OpenCV's 3x3 f32 Gaussian (symmetric separable form, REFLECT_101).  Returns ((ntaps,2) int32 dy/dx, (ntaps,) f64)."""
@@ -96,6 +98,7 @@ def disk_taps(radius: float, alias_blur: float):
     return np.ascontiguousarray(dydx), kern[ys, xs].astype(np.float64)
 
 
+@functools.lru_cache(maxsize=None)
 def gaussian_taps(sigma: float, truncate: float) -> np.ndarray:
     """scipy.ndimage._gaussian_kernel1d: centre tap first, radius int(truncate*sigma + 0.5)."""
     lw = int(truncate * float(sigma) + 0.5)
@@ -104,6 +107,7 @@ def gaussian_taps(sigma: float, truncate: float) -> np.ndarray:
     return np.ascontiguousarray(full[lw:])
 
 
+@functools.lru_cache(maxsize=None)
 def motion_kernel(radius: float, sigma: float) -> np.ndarray:
     """ImageMagick's one-sided Gaussian line kernel (f32), width 2*ceil(radius)+1."""
     width = int(2.0 * math.ceil(radius) + 1.0)
@@ -122,6 +126,7 @@ def motion_offsets(width: int, angles_deg) -> np.ndarray:
     return np.ascontiguousarray(off.astype(np.int32))
 
 
+@functools.lru_cache(maxsize=None)
 def zoom_axis_table(size: int, z: float):
     """clipped_zoom along one axis: source indices (i0, i1) and fraction t (f32) per output sample
     (scipy.ndimage.zoom order=1 coordinate o*(in-1)/(out-1), centre crop before, centre trim after)."""
@@ -179,6 +184,7 @@ _JPEG_CHROMA = np.array([17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99,
                          99, 47, 66, 99, 99, 99, 99, 99, 99] + [99] * 32, np.int64)
 
 
+@functools.lru_cache(maxsize=None)
 def jpeg_qtables(quality: int) -> np.ndarray:
     """libjpeg jpeg_set_quality(quality, force_baseline): (2, 64) int32, natural order."""
     q = max(1, min(100, int(quality)))
@@ -251,6 +257,17 @@ def procedural_frost_bank(device, n_tex: int = 5, size: int = 96, seed: int = 12
 # ------------------------------------------------------------------------------------------------
 # one corruption
 # ------------------------------------------------------------------------------------------------
+@functools.lru_cache(maxsize=None)
+def _snow_zoom_tables(h: int, w: int, z: float):
+    y0, y1, ty = zoom_axis_table(h, z)
+    x0, x1, tx = zoom_axis_table(w, z)
+    return (np.ascontiguousarray(np.concatenate([y0, y1, x0, x1]).astype(np.int32)),
+            np.ascontiguousarray(np.concatenate([ty, tx]).astype(np.float32)))
+
+
+MODES = {"exact": 0, "fast": L.CC_FAST, "replay": L.CC_REPLAY_ALL}
+
+
 def _dev(a, dtype, device):
     if a is None:
         return None
@@ -263,28 +280,44 @@ def _ptr(t):
 
 
 def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = None, seed: int = 0, table: str = "cifar",
-            out: Optional[torch.Tensor] = None, frost_bank: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """x: (n,h,w,3) uint8 CUDA -> same shape.  `draws` injects the random inputs (DRAW_KEYS[name]); None = on-chip RNG."""
+            out: Optional[torch.Tensor] = None, frost_bank: Optional[torch.Tensor] = None,
+            mode: Optional[str] = None) -> torch.Tensor:
+    """x: (n,h,w,3) uint8 CUDA -> same shape.  `draws` injects the random inputs (DRAW_KEYS[name]); None = on-chip RNG.
+
+    mode: "exact"  the float64-specified arithmetic of oracle/cifar_c.py, bit for bit (default when draws are injected);
+          "fast"   float32 / fixed-point throughput kernels, every byte within 1 LSB of "exact" on the same draws
+                   (default when the draws are made on chip: no bit-wise oracle exists for those);
+          "replay" (tests) "exact" with every element forced through its literal replay."""
     x = B._check_u8(x)
+    with torch.cuda.device_of(x):
+        return _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode)
+
+
+def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
     n, h, w, c = x.shape
     if not 1 <= severity <= 5:
         raise ValueError("severity must be 1..5")
     d = draws or {}
+    if mode is None:
+        mode = "exact" if d else "fast"
+    if mode not in MODES:
+        raise ValueError("mode must be 'exact', 'fast' or 'replay'")
+    flags = MODES[mode]
     dev = x.device
     lib = L.load()
     st = B._stream()
     seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    out = B._check_out(out, x)
     if table == "reference":
         return _corrupt_reference(x, name, severity, d, seed, out)
     if table != "cifar":
         raise ValueError("table must be 'cifar' or 'reference'")
     p = CIFAR_TABLE[name][severity - 1]
-    out = torch.empty_like(x) if out is None else out
     xp, op = x.data_ptr(), out.data_ptr()
 
     def point(kind, p0, p1=0.0, a=None, b=None, tex=(0, 0, 0)):
         L.check(lib.imgtx_cc_pointwise_u8(xp, op, n, h, w, c, kind, float(p0), float(p1), _ptr(a), _ptr(b), seed, tex[0],
-                                          tex[1], tex[2], st))
+                                          tex[1], tex[2], flags, st))
 
     # NB every device staging tensor is bound to a local name until the call returns: a temporary would hand its block
     # back to the caching allocator before the next one is staged
@@ -314,32 +347,29 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
             point(L.CC_FROST, p[0], p[1], a=bank, tex=(bank.shape[0], bank.shape[1], bank.shape[2]))
     elif name == "defocus_blur":
         dydx, wts = disk_taps(p[0], p[1])
-        L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, st))
+        L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, flags, st))
     elif name == "zoom_blur":
         ip, idx, wt, max_row = zoom_operator(h, w, severity, dev)
         L.check(lib.imgtx_cc_csr_ell_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(),
-                                        max_row, st))
+                                        max_row, flags, st))
     elif name == "glass_blur":
         wts = gaussian_taps(p[0], 4.0)
         deltas = _dev(d.get("deltas"), torch.int8, dev)
         if deltas is not None and deltas.numel() != n * p[2] * (h - 2) * (w - 2) * 2:
             raise ValueError("deltas must have shape (n, iters, h-2, w-2, 2)")
-        L.check(lib.imgtx_cc_glass_u8(xp, op, n, h, w, c, wts.ctypes.data, len(wts) - 1, p[2], _ptr(deltas), seed, st))
+        L.check(lib.imgtx_cc_glass_u8(xp, op, n, h, w, c, wts.ctypes.data, len(wts) - 1, p[2], _ptr(deltas), seed, flags, st))
     elif name == "motion_blur":
         k = motion_kernel(p[0], p[1])
         off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
-        L.check(lib.imgtx_cc_motion_u8(xp, op, n, h, w, c, len(k), k.ctypes.data, _ptr(off), -45.0, 45.0, seed, st))
+        L.check(lib.imgtx_cc_motion_u8(xp, op, n, h, w, c, len(k), k.ctypes.data, _ptr(off), -45.0, 45.0, seed, flags, st))
     elif name == "snow":
         k = motion_kernel(p[4], p[5])
         off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
-        y0, y1, ty = zoom_axis_table(h, float(p[2]))
-        x0, x1, tx = zoom_axis_table(w, float(p[2]))
-        zi = np.ascontiguousarray(np.concatenate([y0, y1, x0, x1]).astype(np.int32))
-        zt = np.ascontiguousarray(np.concatenate([ty, tx]).astype(np.float32))
+        zi, zt = _snow_zoom_tables(h, w, float(p[2]))
         layer = _dev(d.get("layer"), torch.float64, dev)
         L.check(lib.imgtx_cc_snow_u8(xp, op, n, h, w, c, float(np.float32(p[3])), float(np.float32(p[6])),
                                      float(np.float32(1 - p[6])), zi.ctypes.data, zt.ctypes.data, len(k), k.ctypes.data,
-                                     _ptr(off), _ptr(layer), float(p[0]), float(p[1]), -135.0, -45.0, seed, st))
+                                     _ptr(off), _ptr(layer), float(p[0]), float(p[1]), -135.0, -45.0, seed, flags, st))
     elif name == "elastic_transform":
         alpha, sigma, c2 = p[0] * h, p[1] * h, p[2] * h
         if sigma > 1e-15:
@@ -350,14 +380,14 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
         M = _dev(affine_from_jitter(d["jitter"], h), torch.float64, dev) if "jitter" in d else None
         ux, uy = _dev(d.get("ux"), torch.float64, dev), _dev(d.get("uy"), torch.float64, dev)
         L.check(lib.imgtx_cc_elastic_u8(xp, op, n, h, w, c, float(alpha), wts.ctypes.data, lw, _ptr(M), _ptr(ux), _ptr(uy),
-                                        float(c2), seed, st))
+                                        float(c2), seed, flags, st))
     elif name == "pixelate":
         sw, sh = int(w * p), int(h * p)
         if sw == w or sh == h:     # Pillow skips a pass whose size does not change: use the general path
             small = B.resample(x, (sw, sh), L.FILTER_BOX)
             B.resample(small, (w, h), L.FILTER_BOX, out=out)
         else:
-            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, st)   # small images: gather form; 1 = not applicable
+            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, flags, st)   # small images: gather form; 1 = not applicable
             if rc == 1:
                 t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
                 rc = lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
@@ -365,7 +395,7 @@ def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = N
             L.check(rc)
     elif name == "jpeg_compression":
         qt = jpeg_qtables(p)
-        L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, st))
+        L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, flags, st))
     else:
         raise KeyError(name)
     return out
@@ -398,7 +428,8 @@ def suite_passes(corruptions=None, severities=(1, 2, 3, 4, 5)):
     return [(c, s) for c in (corruptions or CORRUPTIONS) for s in severities]
 
 
-def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5), seed: int = 0, out=None, sink=None):
+def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5), seed: int = 0, out=None, sink=None,
+                   mode: Optional[str] = None):
     """Run every (corruption, severity) pass over the device-resident batch x.  Each pass is one kernel launch (two for
     pixelate).  `out`: optional (len(passes), n, h, w, 3) uint8 CUDA tensor receiving every pass; otherwise `sink(name,
     severity, tensor)` is called per pass with a reused buffer (e.g. to checksum or stage to the host)."""
@@ -406,7 +437,7 @@ def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5)
     buf = None if out is not None else torch.empty_like(x)
     for k, (name, sev) in enumerate(passes):
         dst = out[k] if out is not None else buf
-        corrupt(x, name, sev, seed=seed * 1000 + k, out=dst)
+        corrupt(x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode)
         if sink is not None:
             sink(name, sev, dst)
     return out if out is not None else buf

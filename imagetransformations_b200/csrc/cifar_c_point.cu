@@ -17,6 +17,7 @@
 #include "pipeline.cuh"
 #include "rng.cuh"
 #include "cifar_c_fast.cuh"
+#include "cifar_c_team.cuh"
 #include <math.h>
 #include <string.h>
 #include <vector>
@@ -301,7 +302,7 @@ using namespace imgtx;
 
 extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0,
                                      double p1, const void* draws_a_dev, const void* draws_b_dev, uint64_t seed,
-                                     int tex_n, int tex_h, int tex_w, imgtx_stream_t stream) {
+                                     int tex_n, int tex_h, int tex_w, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(kind >= IMGTX_CC_GAUSSIAN && kind <= IMGTX_CC_FROST, "unknown corruption kind %d", kind);
   if (kind == IMGTX_CC_IMPULSE) IMGTX_CHECK_ARG((draws_a_dev == nullptr) == (draws_b_dev == nullptr), "impulse needs both draw arrays or none");
@@ -322,7 +323,27 @@ extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n,
     memset(&f, 0, sizeof(f));
     f.kind = kind; f.p0 = p0; f.p1 = p1; f.a = draws_a_dev; f.b = draws_b_dev; f.seed = seed;
     f.tex_n = kind == IMGTX_CC_FROST ? tex_n : 0; f.tex_h = tex_h; f.tex_w = tex_w;
-    f.force_exact = force_exact();
+    f.force_exact = (flags & IMGTX_CC_REPLAY_ALL) ? 1 : 0;
+    if (flags & IMGTX_CC_FAST) {
+      // throughput forms (cifar_c_team.cuh): one warp per image, float32 / fixed point, <= 1 LSB from the forms below
+      int rc = IMGTX_ERR_UNSUPPORTED;
+      cudaStream_t st = (cudaStream_t)stream;
+      if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && p0 >= 0.0 && p0 <= 1.0 && (int64_t)h * w * 255 < (1ll << 24))
+        rc = launch_team_op<OpTContrast>(in, out, n, shp, f, st);
+      else if (kind == IMGTX_CC_BRIGHTNESS && (h * w) % 4 == 0 && p0 > -10 && p0 < 10)
+        rc = launch_team_op<OpTBrightness>(in, out, n, shp, f, st);
+      else if (kind == IMGTX_CC_IMPULSE && !draws_a_dev && p0 > 0.0 && p0 < 1.0) {
+        f.p1 = 1.0 / log2(1.0 - p0);
+        rc = launch_team_op<OpTImpulse>(in, out, n, shp, f, st);
+        f.p1 = p1;
+      } else if (kind == IMGTX_CC_FROST && w % 4 == 0 && p0 >= 0 && p1 >= 0 && p0 < 1.99 && p1 < 1.99 &&
+                 ((reinterpret_cast<uintptr_t>(draws_a_dev) & 3u) == 0))
+        rc = launch_team_op<OpTFrost>(in, out, n, shp, f, st);
+      else if (kind == IMGTX_CC_FOG && (h * w) % 4 == 0 && p0 > 0 && p0 < 100 &&
+               (draws_a_dev || (h == w && (h & (h - 1)) == 0 && h >= 4 && h <= 64 && p1 > 0)))
+        rc = launch_team_op<OpTFog>(in, out, n, shp, f, st);
+      if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+    }
     if (kind == IMGTX_CC_IMPULSE && !draws_a_dev) return launch_image_op<OpCcImpulseFast>(in, out, n, shp, f, (cudaStream_t)stream);
     if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && (int64_t)h * w * 255 < (1ll << 31))
       return launch_image_op<OpCcContrastFast>(in, out, n, shp, f, (cudaStream_t)stream, 0,
@@ -475,6 +496,7 @@ extern "C" int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_hos
 extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
                                         const int32_t* table_dev, int64_t table_words, uint64_t seed,
                                         imgtx_stream_t stream) {
+  // (on-chip draws only: this entry point IS a throughput form; it runs on the team pipeline when the table fits beside it)
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(kind == IMGTX_CC_GAUSSIAN || kind == IMGTX_CC_SHOT, "alias-table noise is gaussian or shot");
   IMGTX_CHECK_ARG(table_dev != nullptr && table_words > kAliasHeaderWords && aligned16(table_dev), "bad alias table");
@@ -486,6 +508,11 @@ extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t
   CcFastParams f;
   memset(&f, 0, sizeof(f));
   f.kind = kind; f.b = table_dev; f.seed = seed; f.table_words = (int)table_words;
+  {
+    const int rc = tbytes > 48 * 1024 ? launch_team_op<OpTNoiseAlias<2>>(in, out, n, shp, f, (cudaStream_t)stream)
+                                      : launch_team_op<OpTNoiseAlias<1>>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+  }
   // small table: default occupancy; large table (shot): one CTA per SM, the rest of shared memory stages images
   int target = 0;
   if (tbytes > 16 * 1024) target = max_smem_optin() - 1024;   // big table (shot noise): one CTA per SM anyway, give it every byte for images

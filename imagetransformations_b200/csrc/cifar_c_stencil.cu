@@ -1205,15 +1205,15 @@ struct OpCcSnowFast : NoSpill {
 // wavefront warps an SM holds (CTAs/SM x group): measured best 6 (R = 0: 445 -> 292 us), 4 (R = 1), 8 (R = 2: -6 %);
 // IMGTX_GLASS_G overrides it for sweeps.
 static int glass_group_images(int lw) {
-  const char* e = getenv("IMGTX_GLASS_G");
-  if (e && atoi(e) > 0) return atoi(e);
+  const int e = imgtx::staged_tuning().glass_g;
+  if (e > 0) return e;
   return lw == 0 ? 6 : (lw == 1 ? 4 : 8);
 }
 
 using namespace imgtx;
 
 extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
-                                   const int32_t* dydx_host, const double* weights_host, imgtx_stream_t stream) {
+                                   const int32_t* dydx_host, const double* weights_host, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 4 && w > 4 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(ntaps >= 1 && ntaps <= kMaxTaps && dydx_host && weights_host, "1..%d taps", kMaxTaps);
   DefocusParams p;
@@ -1234,7 +1234,7 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       K[p.dy[i] + 2][p.dx[i] + 2] += p.w[i];
       R = std::max(R, std::max(abs((int)p.dy[i]), abs((int)p.dx[i])));
     }
-    bool sym = (w % 4 == 0) && R >= 1 && !force_exact();   // test knob: the literal kernel instead of the fixed-point sweep
+    bool sym = (w % 4 == 0) && R >= 1 && !(flags & IMGTX_CC_REPLAY_ALL);   // test knob: the literal kernel instead of the fixed-point sweep
     for (int a = 0; a < 5 && sym; ++a)
       for (int b = 0; b < 5; ++b)
         if (K[a][b] != K[4 - a][b] || K[a][b] != K[a][4 - b]) sym = false;
@@ -1277,7 +1277,7 @@ extern "C" int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h
 
 extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                                    const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
-                                   imgtx_stream_t stream) {
+                                   int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0 && max_row_taps > 0, "missing operator");
   Shape shp = make_shape(h, w, c, h, w);
@@ -1296,7 +1296,7 @@ extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, i
 }
 
 extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
-                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, imgtx_stream_t stream) {
+                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 2 && w > 2 && h <= 34 && c == 3 && n >= 0, "glass_blur takes (n,h<=34,w,3) images");
   IMGTX_CHECK_ARG(lw >= 0 && lw <= 3 && weights_host && iters >= 0, "bad Gaussian");
   GlassParams p;
@@ -1305,7 +1305,7 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
   const Shape shp = make_shape(h, w, c, h, w);
   if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
-      !force_exact()) {   // test knob: the literal kernel instead of the fixed-point sweeps
+      !(flags & IMGTX_CC_REPLAY_ALL)) {   // test knob: the literal kernel instead of the fixed-point sweeps
     GlassFastParams f;
     memset(&f, 0, sizeof(f));
     f.g = p;
@@ -1333,7 +1333,7 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
 }
 
 static int fill_motion(MotionParams& m, int width, const float* k_host, const int32_t* offsets_dev, double lo, double hi,
-                       uint64_t seed) {
+                       uint64_t seed, int flags) {
   IMGTX_CHECK_ARG(width >= 1 && width <= kMaxLine && k_host, "line kernel width must be in [1,%d]", kMaxLine);
   memset(&m, 0, sizeof(m));
   m.width = width;
@@ -1343,16 +1343,16 @@ static int fill_motion(MotionParams& m, int width, const float* k_host, const in
   double tail = 0.0;
   while (m.n_eff > 1 && tail + fabs((double)k_host[m.n_eff - 1]) * 255.0 <= 9.5e-7) tail += fabs((double)k_host[--m.n_eff]) * 255.0;
   m.offsets = offsets_dev; m.lo = lo; m.hi = hi; m.seed = seed;
-  m.force_exact = force_exact();
+  m.force_exact = (flags & IMGTX_CC_REPLAY_ALL) ? 1 : 0;
   return IMGTX_OK;
 }
 
 extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
                                   const float* k_host, const int32_t* offsets_dev, double angle_lo, double angle_hi,
-                                  uint64_t seed, imgtx_stream_t stream) {
+                                  uint64_t seed, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   MotionParams p;
-  int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
+  int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags);
   if (rc) return rc;
   Shape shp = make_shape(h, w, c, h, w);
   shp.aux = p.n_eff;
@@ -1368,12 +1368,12 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
                                 float one_minus_c6, const int32_t* zoom_idx_host /* y0,y1 (h each), x0,x1 (w each) */,
                                 const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
                                 const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
-                                double angle_lo, double angle_hi, uint64_t seed, imgtx_stream_t stream) {
+                                double angle_lo, double angle_hi, uint64_t seed, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && h <= kSnowMax && w <= kSnowMax && c == 3 && n >= 0, "snow takes (n,h<=64,w<=64,3) images");
   IMGTX_CHECK_ARG(zoom_idx_host && zoom_t_host, "missing zoom tables");
   SnowParams p;
   memset(&p, 0, sizeof(p));
-  int rc = fill_motion(p.m, width, k_host, offsets_dev, angle_lo, angle_hi, seed);
+  int rc = fill_motion(p.m, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags);
   if (rc) return rc;
   p.thresh = thresh; p.c6 = c6; p.one_minus_c6 = one_minus_c6; p.loc = loc; p.scale = scale; p.layer = layer_dev;
   for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }

@@ -871,13 +871,13 @@ using namespace imgtx;
 
 extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
                                    const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
-                                   const double* uy_dev, double c2, uint64_t seed, imgtx_stream_t stream) {
+                                   const double* uy_dev, double c2, uint64_t seed, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 1 && w > 1 && h <= 64 && w <= 64 && c == 3 && n >= 0, "elastic_transform takes (n,h<=64,w<=64,3) images");
   IMGTX_CHECK_ARG(lw >= -1 && lw <= kMaxLw && (lw < 0 || weights_host), "Gaussian radius must be <= %d", kMaxLw);
   IMGTX_CHECK_ARG((ux_dev == nullptr) == (uy_dev == nullptr), "give both displacement fields or none");
   ElasticParams p;
   memset(&p, 0, sizeof(p));
-  p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed; p.force_exact = force_exact();
+  p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed; p.force_exact = (flags & IMGTX_CC_REPLAY_ALL) ? 1 : 0;
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
   if (alpha == 0.0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out))
@@ -891,7 +891,8 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
 }
 
 extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
-                                const int32_t* qtables_host /* 2 x 64, natural order */, imgtx_stream_t stream) {
+                                const int32_t* qtables_host /* 2 x 64, natural order */, int flags, imgtx_stream_t stream) {
+  (void)flags;   // integer arithmetic: one form
   IMGTX_CHECK_ARG(h > 0 && w > 0 && (h % 16) == 0 && (w % 16) == 0 && c == 3 && n >= 0,
                   "jpeg_compression takes (n,h,w,3) images with h, w multiples of 16");
   IMGTX_CHECK_ARG(qtables_host, "missing quantisation tables");

@@ -19,7 +19,6 @@ namespace imgtx {
 void set_error(const char* fmt, ...);
 int sm_count();
 int max_smem_optin();
-int force_exact();   // test knob: 1 = every fixed-point / float32 fast path defers to its literal replay
 
 #define IMGTX_CHECK_ARG(cond, ...)                 \
   do {                                             \

@@ -176,6 +176,10 @@ struct StagedTuning {
   int target_smem;  // dynamic smem per CTA we aim for (bytes)
   int stages;
   int ctas_per_sm;
+  int ctas_from_env;   // IMGTX_CTAS_PER_SM was given: it overrides the operators' own caps
+  int target_scale;    // IMGTX_TARGET_SCALE (percent of an operator's own target), 0 = off
+  int glass_g;         // IMGTX_GLASS_G
+  int pw_ctas;         // IMGTX_PW_CTAS
 };
 StagedTuning staged_tuning();
 
@@ -191,9 +195,9 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
   if (target_override > 0) {
     tn.target_smem = target_override;
     // sweep knob: scale an operator's own target (percent), e.g. IMGTX_TARGET_SCALE=150
-    if (const char* e = getenv("IMGTX_TARGET_SCALE")) tn.target_smem = (int)((int64_t)target_override * atoi(e) / 100);
+    if (tn.target_scale > 0) tn.target_smem = (int)((int64_t)target_override * tn.target_scale / 100);
   }
-  if (CtasPerSm<Op>::value > 0 && !getenv("IMGTX_CTAS_PER_SM")) tn.ctas_per_sm = CtasPerSm<Op>::value;
+  if (CtasPerSm<Op>::value > 0 && !tn.ctas_from_env) tn.ctas_per_sm = CtasPerSm<Op>::value;
   const int max_smem = max_smem_optin();
   if (tn.target_smem > max_smem - 1024) tn.target_smem = max_smem - 1024;   // a target can ask for more than the SM has
   bool staged = (s.in_bytes % 16 == 0) && (s.out_bytes % 16 == 0) && aligned16(in) && aligned16(out);

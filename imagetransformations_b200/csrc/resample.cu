@@ -477,7 +477,8 @@ extern "C" int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n,
    Returns IMGTX_OK when launched, 1 when the BOX tables do not have the (<= 2 taps down, single unit tap up) structure or
    the shape is outside the fast path — the caller then uses imgtx_resize_chain_u8 (same results). */
 extern "C" int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
-                                     imgtx_stream_t stream) {
+                                     int flags, imgtx_stream_t stream) {
+  (void)flags;   // integer arithmetic: one form
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "pixelate takes (n,h,w,3) images");
   IMGTX_CHECK_ARG(sw > 0 && sh > 0 && sw <= w && sh <= h, "the intermediate size must not exceed the image");
   if (h > kPixMax || w > kPixMax || (w & 3) || sw == w || sh == h) return 1;

@@ -38,23 +38,28 @@ int max_smem_optin() {
   return g_dev.smem > 0 ? g_dev.smem : 232448;
 }
 
-static std::atomic<int> g_force_exact{0};
-int force_exact() { return g_force_exact; }
-static std::atomic<int> g_target_smem{56 * 1024};
-static std::atomic<int> g_stages{3};
-static std::atomic<int> g_ctas_per_sm{4};
+// Development sweeps: IMGTX_* environment variables, read once (std::call_once) and immutable afterwards.
+static int g_target_smem = 56 * 1024, g_stages = 3, g_ctas_per_sm = 4, g_ctas_env = 0, g_target_scale = 0, g_glass_g = 0,
+           g_pw_ctas = 4;
 static std::once_flag g_env_once;
 static void init_env() {
   if (const char* e = getenv("IMGTX_TARGET_SMEM")) g_target_smem = atoi(e);
   if (const char* e = getenv("IMGTX_STAGES")) g_stages = atoi(e);
-  if (const char* e = getenv("IMGTX_CTAS_PER_SM")) g_ctas_per_sm = atoi(e);
+  if (const char* e = getenv("IMGTX_CTAS_PER_SM")) { g_ctas_per_sm = atoi(e); g_ctas_env = 1; }
+  if (const char* e = getenv("IMGTX_TARGET_SCALE")) g_target_scale = atoi(e);
+  if (const char* e = getenv("IMGTX_GLASS_G")) g_glass_g = atoi(e);
+  if (const char* e = getenv("IMGTX_PW_CTAS")) g_pw_ctas = atoi(e);
 }
 StagedTuning staged_tuning() {
   std::call_once(g_env_once, init_env);
   StagedTuning t;
   t.target_smem = g_target_smem;
-  t.stages = g_stages < 2 ? 2 : (g_stages > kMaxStages ? kMaxStages : (int)g_stages);
-  t.ctas_per_sm = g_ctas_per_sm < 1 ? 1 : (int)g_ctas_per_sm;
+  t.stages = g_stages < 2 ? 2 : (g_stages > kMaxStages ? kMaxStages : g_stages);
+  t.ctas_per_sm = g_ctas_per_sm < 1 ? 1 : g_ctas_per_sm;
+  t.ctas_from_env = g_ctas_env;
+  t.target_scale = g_target_scale;
+  t.glass_g = g_glass_g;
+  t.pw_ctas = g_pw_ctas < 1 ? 1 : g_pw_ctas;
   return t;
 }
 
@@ -67,16 +72,5 @@ extern "C" int imgtx_device_info(int* sms, int* smem) {
   IMGTX_CUDA_OK(cudaGetDevice(&dev));
   if (sms) *sms = imgtx::sm_count();
   if (smem) *smem = imgtx::max_smem_optin();
-  return IMGTX_OK;
-}
-extern "C" int imgtx_set_force_exact(int on) {
-  imgtx::g_force_exact = on ? 1 : 0;
-  return IMGTX_OK;
-}
-extern "C" int imgtx_set_tuning(int target_smem, int stages, int ctas_per_sm) {
-  std::call_once(imgtx::g_env_once, imgtx::init_env);
-  if (target_smem > 0) imgtx::g_target_smem = target_smem;
-  if (stages > 0) imgtx::g_stages = stages;
-  if (ctas_per_sm > 0) imgtx::g_ctas_per_sm = ctas_per_sm;
   return IMGTX_OK;
 }

@@ -368,7 +368,7 @@ extern "C" int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k
 }
 
 extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
-                                         double sigma, imgtx_stream_t stream) {
+                                         double sigma, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4, "bad image shape");
   CvGaussParams p;
   memset(&p, 0, sizeof(p));
@@ -380,7 +380,7 @@ extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_
   bool small_weights = true;
   for (int i = 0; i < ksize; ++i) small_weights = small_weights && p.k[i] >= 0 && p.k[i] <= 255;
   s.aux = r;
-  if (!force_exact() && small_weights && r >= 1 && r < std::min(h, w) && (w & 3) == 0 && (h & 3) == 0 &&
+  if (!(flags & IMGTX_CC_REPLAY_ALL) && small_weights && r >= 1 && r < std::min(h, w) && (w & 3) == 0 && (h & 3) == 0 &&
       OpCvGaussDp::per_image(s) <= 40 * 1024 && (OpCvGaussDp::row_bytes(h, r) & 3) == 0 && (OpCvGaussDp::row_bytes(w, r) & 3) == 0)
     return launch_image_op<OpCvGaussDp>(in, out, n, s, p, (cudaStream_t)stream);
   s.aux = 0;

@@ -44,13 +44,17 @@ int imgtx_version(void);
 const char* imgtx_last_error(void);
 /* Fills the SM count and opt-in shared memory per block of the current device. */
 int imgtx_device_info(int* sm_count, int* max_smem_per_block);
-/* Tuning knobs of the staged (TMA) image pipeline; <=0 keeps the current value. */
-int imgtx_set_tuning(int target_smem_bytes, int stages, int ctas_per_sm);
-/* Test knob (process-wide, default 0).  The CIFAR-10-C-style kernels decide most bytes with a fixed-point or float32 evaluation
-   and replay the reference's literal arithmetic only near a rounding boundary; with on = 1 every element takes the literal
-   replay, so tests can check that both routes give the same bytes (also for on-chip random draws, where no CPU oracle has
-   the same draws). */
-int imgtx_set_force_exact(int on);
+/* The library keeps NO mutable process state: per-call behaviour is selected by the `flags` argument of the entry points
+   that have one (0 = default).  (Development sweeps of the staged pipeline read IMGTX_* environment variables once, at the
+   first launch.) */
+/* Throughput mode of the CIFAR-10-C-style suite: float32 / fixed-point evaluation of the same real-valued expressions the
+   default (bit-exact, float64-specified) mode evaluates; every output byte is within 1 LSB of the default mode on the same
+   inputs and injected draws.  The default when the draws are made on chip (no bit-wise oracle exists for those). */
+#define IMGTX_CC_FAST 1
+/* Test flag of the default mode: its kernels decide most bytes with a fixed-point or float32 evaluation and replay the
+   specification's literal arithmetic only near a rounding boundary; with this flag EVERY element takes the literal replay,
+   so tests can check that both routes give the same bytes (also on on-chip draws). */
+#define IMGTX_CC_REPLAY_ALL 2
 
 /* ---- pointwise uint8 maps (256-entry LUT built with the library's exact f32 formula) -------- */
 typedef enum {
@@ -149,14 +153,14 @@ int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
    gather and BOX down-sampling has at most two taps, so only the small image is computed.  Returns IMGTX_OK when launched,
    1 when the shape or table structure is outside the fast path (use imgtx_resize_chain_u8: identical results). */
 int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
-                          imgtx_stream_t stream);
+                          int flags, imgtx_stream_t stream);
 
 /* ---- stencils ------------------------------------------------------------------------------- */
 /* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
 int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);
 /* cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8 — transformation.py:228-257 (apply_blur) */
 int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
-                              double sigma, imgtx_stream_t stream);
+                              double sigma, int flags, imgtx_stream_t stream);
 /* img.filter(ImageFilter.GaussianBlur(radius)) — pipenline/cifar_image_transformations.py:72-77 */
 int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float radius,
                                imgtx_stream_t stream);
@@ -217,7 +221,7 @@ typedef enum {
 } imgtx_cc_kind;
 int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0, double p1,
                           const void* draws_a_dev, const void* draws_b_dev, uint64_t seed, int tex_n, int tex_h,
-                          int tex_w, imgtx_stream_t stream);
+                          int tex_w, int flags, imgtx_stream_t stream);
 /* On-chip gaussian_noise / shot_noise sampled in the OUTPUT domain.  Input and output are bytes, so gaussian_noise adds the
    integer floor(255*sigma*Z) (one discrete law) and shot_noise is a 256-row stochastic matrix (row x = law of
    uint8(clip(Poisson(x/255*c)/c)*255)); both are sampled with Walker alias tables: one 32-bit Philox word, one multiply and
@@ -232,7 +236,7 @@ int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, 
 /* defocus_blur: correlation with the sparse taps (dy, dx, weight) of the anti-aliased disk kernel, REFLECT_101, f64.
    dydx_host: (ntaps, 2) int32; |offset| <= 2. */
 int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
-                        const int32_t* dydx_host, const double* weights_host, imgtx_stream_t stream);
+                        const int32_t* dydx_host, const double* weights_host, int flags, imgtx_stream_t stream);
 /* zoom_blur (any fixed linear map on x/255 in CSR form, applied in f32 in stored order). */
 int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                     const int32_t* indices_dev, const float* weights_dev, int nnz, imgtx_stream_t stream);
@@ -241,30 +245,30 @@ int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, in
    to imgtx_cc_csr_u8 when the table does not fit. */
 int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                         const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
-                        imgtx_stream_t stream);
+                        int flags, imgtx_stream_t stream);
 /* glass_blur: weights_host[0..lw] = scipy Gaussian taps (centre first); deltas_dev (n, iters, h-2, w-2, 2) int8 (dx, dy). */
 int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host, int lw,
-                      int iters, const int8_t* deltas_dev, uint64_t seed, imgtx_stream_t stream);
+                      int iters, const int8_t* deltas_dev, uint64_t seed, int flags, imgtx_stream_t stream);
 /* motion_blur: k_host[width] one-sided Gaussian line weights; offsets_dev (n, width, 2) int32 (dx, dy), or NULL with the
    angle drawn uniformly in [angle_lo, angle_hi] degrees. */
 int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width, const float* k_host,
                        const int32_t* offsets_dev, double angle_lo, double angle_hi, uint64_t seed,
-                       imgtx_stream_t stream);
+                       int flags, imgtx_stream_t stream);
 /* snow: zoom_idx_host = [y0 (h), y1 (h), x0 (w), x1 (w)], zoom_t_host = [ty (h), tx (w)] (centre-zoom tables of the noise
    layer); layer_dev (n,h,w) f64 normal(loc, scale) draws or NULL. */
 int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
                      float one_minus_c6, const int32_t* zoom_idx_host, const float* zoom_t_host, int width,
                      const float* k_host, const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
-                     double angle_lo, double angle_hi, uint64_t seed, imgtx_stream_t stream);
+                     double angle_lo, double angle_hi, uint64_t seed, int flags, imgtx_stream_t stream);
 /* elastic_transform: M_dev (n,6) f64 forward affine matrices (cv2.getAffineTransform) or NULL (corner jitter of amplitude
    c2 drawn on chip); ux_dev / uy_dev (n,h,w) f64 uniform(-1,1) fields or NULL; weights_host[0..lw] Gaussian taps (lw = -1:
    no smoothing). */
 int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
                         const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
-                        const double* uy_dev, double c2, uint64_t seed, imgtx_stream_t stream);
+                        const double* uy_dev, double c2, uint64_t seed, int flags, imgtx_stream_t stream);
 /* jpeg_compression: baseline round trip (4:2:0, islow DCT) with the two quantisation tables (natural order). */
 int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* qtables_host,
-                     imgtx_stream_t stream);
+                     int flags, imgtx_stream_t stream);
 
 /* ---- tensors ------------------------------------------------------------------------------ */
 /* T.ToTensor() [+ T.Normalize(mean, std) when mean_host/std_host != NULL]: u8 NHWC -> f32 NCHW.

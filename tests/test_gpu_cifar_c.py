@@ -223,7 +223,7 @@ def test_pixelate_gather_form_shapes(cuda, hw, c):
     xd = torch.from_numpy(x).cuda()
     out = torch.empty_like(xd)
     sw, sh = int(w * c), int(h * c)
-    rc = L.load().imgtx_box_pixelate_u8(xd.data_ptr(), out.data_ptr(), len(x), h, w, 3, sw, sh, None)
+    rc = L.load().imgtx_box_pixelate_u8(xd.data_ptr(), out.data_ptr(), len(x), h, w, 3, sw, sh, 0, None)
     assert rc == 0
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), CC.pixelate(x, c))
@@ -233,15 +233,9 @@ def test_pixelate_gather_form_shapes(cuda, hw, c):
 def test_fast_path_equals_literal_replay(cuda, name):
     """Every kernel that decides bytes with a fixed-point / float32 evaluation must agree with its own literal replay on the
     same on-chip draws: run the suite pass twice, the second time with every element forced through the replay."""
-    from imagetransformations_b200 import _lib as L
     C = _C()
-    lib = L.load()
     x = torch.from_numpy(np.concatenate([imgs(3, 40), np.zeros((1, 32, 32, 3), np.uint8), np.full((1, 32, 32, 3), 255, np.uint8)])).cuda()
     for sev in (1, 3, 5):
-        fast = C.corrupt(x, name, sev, seed=11).cpu().numpy()
-        L.check(lib.imgtx_set_force_exact(1))
-        try:
-            lit = C.corrupt(x, name, sev, seed=11).cpu().numpy()
-        finally:
-            L.check(lib.imgtx_set_force_exact(0))
+        fast = C.corrupt(x, name, sev, seed=11, mode="exact").cpu().numpy()
+        lit = C.corrupt(x, name, sev, seed=11, mode="replay").cpu().numpy()
         assert np.array_equal(fast, lit), f"{name}/{sev}: {int((fast != lit).sum())} bytes differ"

@@ -1,0 +1,112 @@
+"""Throughput ("fast") mode of the CIFAR-10-C-style suite: float32 / fixed-point kernels on the team pipeline.
+
+Contract (include/imgtx.h, IMGTX_CC_FAST): on the SAME inputs and the SAME injected draws every byte is within 1 LSB of the
+exact mode (which is bit-identical to oracle/cifar_c.py).  Each test prints the fraction of bytes that differ and bounds it,
+so a fast kernel that drifts (wrong constant, wrong rounding) fails even though it stays inside 1 LSB."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import cifar_c as CC
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+# (type, upper bound on the fraction of differing bytes).  The bounds are ~3x the fractions measured on B200.
+FAST_TYPES = {
+    "contrast": 5e-3, "brightness": 1e-2, "frost": 2e-2, "fog": 5e-3,
+}
+
+
+def imgs(seed=0, n=64):
+    z = np.load(os.path.join(GOLDEN, "cifar_c_fixtures.npz"))
+    nat = np.concatenate([z["contrast"][:8], z["brightness"][:8], z["fog"][:8]])
+    rnd = np.random.default_rng(seed).integers(0, 256, (n - len(nat) - 2, 32, 32, 3), dtype=np.uint8)
+    flat = np.stack([np.zeros((32, 32, 3), np.uint8), np.full((32, 32, 3), 255, np.uint8)])
+    return np.concatenate([nat, rnd, flat])
+
+
+def _C():
+    from imagetransformations_b200 import cifar_c
+    return cifar_c
+
+
+@pytest.mark.parametrize("sev", [1, 2, 3, 4, 5])
+@pytest.mark.parametrize("name", sorted(FAST_TYPES))
+def test_fast_within_one_lsb_of_oracle(cuda, name, sev):
+    C = _C()
+    x = imgs(sev)
+    d = CC.draw(name, sev, x, np.random.RandomState(2000 + sev))
+    want = CC.corrupt(name, sev, x, d)
+    xd = torch.from_numpy(x).cuda()
+    got = C.corrupt(xd, name, sev, draws=d, mode="fast").cpu().numpy()
+    diff = np.abs(got.astype(np.int32) - want.astype(np.int32))
+    frac = float((diff > 0).mean())
+    print(f"fast {name}/{sev}: max |d| = {diff.max()}, differing bytes {frac:.5%}")
+    assert diff.max() <= 1, f"{name}/{sev}: max diff {diff.max()}"
+    assert frac <= FAST_TYPES[name], f"{name}/{sev}: {frac:.4%} of the bytes differ"
+    # the exact mode on the same draws is the oracle itself
+    exact = C.corrupt(xd, name, sev, draws=d, mode="exact").cpu().numpy()
+    assert np.array_equal(exact, want)
+
+
+def test_fast_is_the_default_for_onchip_draws(cuda):
+    C = _C()
+    xd = torch.from_numpy(imgs(1)).cuda()
+    for name in ("contrast", "brightness", "fog", "frost", "impulse_noise"):
+        a = C.corrupt(xd, name, 3, seed=5).cpu().numpy()
+        b = C.corrupt(xd, name, 3, seed=5, mode="fast").cpu().numpy()
+        assert np.array_equal(a, b), name
+
+
+def test_fast_batch_independence_and_ragged_sizes(cuda):
+    """Teams stride over the batch: the result of an image must not depend on the batch size or its position."""
+    C = _C()
+    x = np.random.default_rng(5).integers(0, 256, (1237, 32, 32, 3), dtype=np.uint8)
+    xd = torch.from_numpy(x).cuda()
+    for name in ("contrast", "brightness", "fog"):
+        full = C.corrupt(xd, name, 4, seed=9, mode="fast").cpu().numpy()
+        for lo, hi in ((0, 1), (5, 6), (1236, 1237), (100, 131)):
+            d = None
+            part = C.corrupt(xd[lo:hi], name, 4, seed=9, mode="fast", draws=d).cpu().numpy()
+            if name == "fog":   # on-chip plasma is keyed by the image index within the call
+                continue
+            assert np.array_equal(full[lo:hi], part), (name, lo)
+        for nn in (1, 31, 33, 255):
+            sub = C.corrupt(xd[:nn], name, 4, seed=9, mode="fast").cpu().numpy()
+            assert np.array_equal(sub, full[:nn]), (name, nn)
+
+
+def test_fast_impulse_law(cuda):
+    """Skip-sampled impulse noise: every element flips independently with probability p, half salt / half pepper."""
+    C = _C()
+    n = 4000
+    xd = torch.full((n, 32, 32, 3), 128, dtype=torch.uint8, device="cuda")
+    for sev in (1, 3, 5):
+        p = CC.PARAMS["impulse_noise"][sev - 1]
+        y = C.corrupt(xd, "impulse_noise", sev, seed=40 + sev, mode="fast").cpu().numpy().reshape(n, -1)
+        flipped = y != 128
+        N = flipped.size
+        frac = flipped.mean()
+        assert abs(frac - p) < 5 * np.sqrt(p * (1 - p) / N), (sev, frac, p)
+        salt = (y == 255).sum() / flipped.sum()
+        assert abs(salt - 0.5) < 5 * np.sqrt(0.25 / flipped.sum()), (sev, salt)
+        # per-position flip rate is flat (no segment-boundary artefacts of the per-lane walks)
+        pos = flipped.mean(axis=0)
+        z = (pos - p) / np.sqrt(p * (1 - p) / n)
+        assert np.abs(z).max() < 5.5, (sev, float(np.abs(z).max()))
+        assert abs(z.std() - 1.0) < 0.1
+        # neighbouring elements are independent
+        a, b = flipped[:, :-1].astype(np.float64) - frac, flipped[:, 1:].astype(np.float64) - frac
+        r = (a * b).mean() / (frac * (1 - frac))
+        assert abs(r) < 5 / np.sqrt(a.size), (sev, r)
+        # flips per image follow Binomial(3072, p)
+        per = flipped.sum(axis=1)
+        assert abs(per.mean() - 3072 * p) < 5 * np.sqrt(3072 * p * (1 - p) / n)
+        assert abs(per.var() / (3072 * p * (1 - p)) - 1.0) < 0.15
+    a = C.corrupt(xd[:64], "impulse_noise", 3, seed=1, mode="fast")
+    b = C.corrupt(xd[:64], "impulse_noise", 3, seed=1, mode="fast")
+    c = C.corrupt(xd[:64], "impulse_noise", 3, seed=2, mode="fast")
+    assert torch.equal(a, b) and not torch.equal(a, c)

@@ -224,10 +224,8 @@ def test_tensor_tta_chain_batch(cuda, shape):
 @pytest.mark.parametrize("hw", [(32, 32), (64, 48), (36, 52), (224, 224)])
 def test_cv_gaussian_blur_all_kernel_sizes(cuda, hw):
     """cv2.GaussianBlur restatement for every odd ksize 3..31 (the dp4a path on small images, the literal path elsewhere
-    and under force_exact): both equal the oracle byte for byte."""
-    from imagetransformations_b200 import _lib as L
+    and with literal=True): both equal the oracle byte for byte."""
     B = _B()
-    lib = L.load()
     n = 3 if hw[0] > 100 else 9
     x = _imgs(31, n, *hw)
     x[0] = 255
@@ -239,9 +237,5 @@ def test_cv_gaussian_blur_all_kernel_sizes(cuda, hw):
             want = O.cv_gaussian_blur(x, ks, sigma)
             got = B.cv_gaussian_blur(xd, ks, sigma).cpu().numpy()
             assert np.array_equal(got, want), (ks, sigma, int((got != want).sum()))
-            L.check(lib.imgtx_set_force_exact(1))
-            try:
-                lit = B.cv_gaussian_blur(xd, ks, sigma).cpu().numpy()
-            finally:
-                L.check(lib.imgtx_set_force_exact(0))
+            lit = B.cv_gaussian_blur(xd, ks, sigma, literal=True).cpu().numpy()
             assert np.array_equal(lit, want), (ks, sigma, "literal")

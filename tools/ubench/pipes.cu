@@ -15,6 +15,18 @@ __global__ void k(double* out, int iters, double a, double b) {
     if (OP == 4) { u0 = __umulhi(u0, ua) + 1; u1 = __umulhi(u1, ua) + 1; u2 = __umulhi(u2, ua) + 1; u3 = __umulhi(u3, ua) + 1; u4 = __umulhi(u4, ua) + 1; u5 = __umulhi(u5, ua) + 1; u6 = __umulhi(u6, ua) + 1; u7 = __umulhi(u7, ua) + 1; }
     if (OP == 5) { f0 = (float)(int)f0 + fa; f1 = (float)(int)f1 + fa; f2 = (float)(int)f2 + fa; f3 = (float)(int)f3 + fa; f4 = (float)(int)f4 + fa; f5 = (float)(int)f5 + fa; f6 = (float)(int)f6 + fa; f7 = (float)(int)f7 + fa; }  // F2I + I2F + FADD
     if (OP == 6) { u0 = (u0 ^ ua) + (u0 >> 3); u1 = (u1 ^ ua) + (u1 >> 3); u2 = (u2 ^ ua) + (u2 >> 3); u3 = (u3 ^ ua) + (u3 >> 3); u4 = (u4 ^ ua) + (u4 >> 3); u5 = (u5 ^ ua) + (u5 >> 3); u6 = (u6 ^ ua) + (u6 >> 3); u7 = (u7 ^ ua) + (u7 >> 3); }  // LOP3+SHF+IADD
+    if (OP == 8) { u0 = __dp2a_lo(u0, ua, u0); u1 = __dp2a_lo(u1, ua, u1); u2 = __dp2a_hi(u2, ua, u2); u3 = __dp2a_hi(u3, ua, u3); u4 = __dp4a(u4, ua, u4); u5 = __dp4a(u5, ua, u5); u6 = __dp2a_lo(u6, ua, u6); u7 = __dp2a_lo(u7, ua, u7); }  // IDP
+    if (OP == 9) { unsigned long long t0 = (unsigned long long)u0 * ua + u1, t1 = (unsigned long long)u2 * ua + u3, t2 = (unsigned long long)u4 * ua + u5, t3 = (unsigned long long)u6 * ua + u7; u0 = (unsigned)t0; u1 = (unsigned)(t0 >> 32); u2 = (unsigned)t1; u3 = (unsigned)(t1 >> 32); u4 = (unsigned)t2; u5 = (unsigned)(t2 >> 32); u6 = (unsigned)t3; u7 = (unsigned)(t3 >> 32); }  // 4 x IMAD.WIDE
+    if (OP == 10) { f0 = __fadd_rd(f0, fa); f1 = __fadd_rd(f1, fa); f2 = __fadd_rd(f2, fa); f3 = __fadd_rd(f3, fa); f4 = __fadd_rd(f4, fa); f5 = __fadd_rd(f5, fa); f6 = __fadd_rd(f6, fa); f7 = __fadd_rd(f7, fa); }
+    if (OP == 11) { u0 = __byte_perm(u0, ua, 0x5140); u1 = __byte_perm(u1, ua, 0x7362); u2 = __byte_perm(u2, ua, 0x5140); u3 = __byte_perm(u3, ua, 0x7362); u4 = __byte_perm(u4, ua, 0x5140); u5 = __byte_perm(u5, ua, 0x7362); u6 = __byte_perm(u6, ua, 0x5140); u7 = __byte_perm(u7, ua, 0x7362); }
+    if (OP == 12) {   // 4 independent HMMA m16n8k16 f16 -> f32 per iteration
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+f"(f0), "+f"(f1), "+f"(f2), "+f"(f3) : "r"(u0), "r"(u1), "r"(u2), "r"(u3), "r"(u4), "r"(u5));
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+f"(f4), "+f"(f5), "+f"(f6), "+f"(f7) : "r"(u0), "r"(u1), "r"(u2), "r"(u3), "r"(u6), "r"(u7));
+      float g0 = (float)x0, g1 = (float)x1, g2 = (float)x2, g3 = (float)x3, g4 = (float)x4, g5 = (float)x5, g6 = (float)x6, g7 = (float)x7;
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+f"(g0), "+f"(g1), "+f"(g2), "+f"(g3) : "r"(u0), "r"(u1), "r"(u2), "r"(u3), "r"(u4), "r"(u5));
+      asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+f"(g4), "+f"(g5), "+f"(g6), "+f"(g7) : "r"(u0), "r"(u1), "r"(u2), "r"(u3), "r"(u6), "r"(u7));
+      x0 = g0; x1 = g1; x2 = g2; x3 = g3; x4 = g4; x5 = g5; x6 = g6; x7 = g7;
+    }
     if (OP == 7) { f0 = __log2f(f0) + fa; f1 = __log2f(f1) + fa; f2 = __log2f(f2) + fa; f3 = __log2f(f3) + fa; f4 = __log2f(f4) + fa; f5 = __log2f(f5) + fa; f6 = __log2f(f6) + fa; f7 = __log2f(f7) + fa; }  // MUFU + FADD
   }
   out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + f0 + f1 + f2 + f3 + f4 + f5 + f6 + f7 + u0 + u1 + u2 + u3 + u4 + u5 + u6 + u7;
@@ -36,6 +48,8 @@ void run(const char* name, int ops_per_iter, double* out) {
 int main() {
   double* out; cudaMalloc(&out, 148 * 4 * 512 * 8 * 2);
   run<0>("DFMA", 1, out); run<1>("DADD", 1, out); run<2>("FFMA", 1, out); run<3>("IMAD", 1, out); run<4>("IMAD.HI(+IADD)", 1, out);
+  run<8>("IDP.2A/4A", 1, out); run<9>("IMAD.WIDE (x4 per 8)", 1, out); run<10>("FADD.RD", 1, out); run<11>("PRMT", 1, out);
+  run<12>("HMMA.16816.F32 (4/iter: lane-ops = warp-MMAs*32/8*...)", 1, out);
   run<5>("F2I+I2F+FADD (3 ops)", 3, out); run<6>("LOP3+SHF+IADD (3 ops)", 3, out); run<7>("MUFU.LG2+FADD (2 ops)", 2, out);
   printf("%s\n", cudaGetErrorString(cudaDeviceSynchronize()));
   return 0;
