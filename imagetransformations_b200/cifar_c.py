@@ -299,7 +299,7 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
         raise ValueError("severity must be 1..5")
     d = draws or {}
     if mode is None:
-        mode = "exact" if d else "fast"
+        mode = "exact" if draws is not None else "fast"   # an (even empty) draws dict asks for the parity path
     if mode not in MODES:
         raise ValueError("mode must be 'exact', 'fast' or 'replay'")
     flags = MODES[mode]
@@ -443,7 +443,8 @@ def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5)
     return out if out is not None else buf
 
 
-def write_cifar_c(root: str, x_u8: np.ndarray, labels: np.ndarray, corruptions=None, seed: int = 0, batch: int = 10000):
+def write_cifar_c(root: str, x_u8: np.ndarray, labels: np.ndarray, corruptions=None, seed: int = 0, batch: int = 10000,
+                  mode: Optional[str] = None):
     """Write Hendrycks-layout files: <root>/<corruption>.npy of shape (5*N, h, w, 3), severity-major, plus labels.npy
     (the layout CIFARC_Dataset slices: fall_2025/TTA_transforms.py:16-26)."""
     os.makedirs(root, exist_ok=True)
@@ -456,6 +457,6 @@ def write_cifar_c(root: str, x_u8: np.ndarray, labels: np.ndarray, corruptions=N
         for sev in range(1, 6):
             for i in range(0, n, batch):
                 xb = pinned[i:i + batch].cuda(non_blocking=True)
-                yb = corrupt(xb, name, sev, seed=(seed * 1000 + ci * 5 + sev) * 65536 + i // batch)
+                yb = corrupt(xb, name, sev, seed=(seed * 1000 + ci * 5 + sev) * 65536 + i // batch, mode=mode)
                 dst[(sev - 1) * n + i:(sev - 1) * n + i + len(xb)] = yb.cpu().numpy()
         dst.flush()

@@ -16,6 +16,7 @@
 #include "pipeline.cuh"
 #include "rng.cuh"
 #include "sweep_stencil.cuh"
+#include "cifar_c_team2.cuh"
 #include <math.h>
 #include <string.h>
 #include <stdlib.h>
@@ -1212,6 +1213,11 @@ static int glass_group_images(int lw) {
 
 using namespace imgtx;
 
+namespace imgtx {
+int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const int32_t* indptr, const int32_t* indices,
+              const float* weights, int max_row_taps, cudaStream_t stream);   // cifar_c_zoom.cu
+}
+
 extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
                                    const int32_t* dydx_host, const double* weights_host, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 4 && w > 4 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
@@ -1280,6 +1286,10 @@ extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, i
                                    int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0 && max_row_taps > 0, "missing operator");
+  if (flags & IMGTX_CC_FAST) {
+    const int rc = zoom_fast(in, out, n, h, w, indptr_dev, indices_dev, weights_dev, max_row_taps, (cudaStream_t)stream);
+    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+  }
   Shape shp = make_shape(h, w, c, h, w);
   const size_t tb = OpCcCsrEll::table_bytes(h * w, max_row_taps);
   shp.aux = (int)tb;
@@ -1347,6 +1357,21 @@ static int fill_motion(MotionParams& m, int width, const float* k_host, const in
   return IMGTX_OK;
 }
 
+// Throughput form: taps whose total weight is below 1e-3 LSB are dropped; the canvas is padded by the largest row offset the
+// declared angle range can produce.
+static void fill_motion_fast(MotionFastParams& f, const MotionParams& m, double lo, double hi) {
+  f.width = m.width;
+  f.n_eff = m.width;
+  double tail = 0.0;
+  while (f.n_eff > 1 && tail + fabs((double)m.k[f.n_eff - 1]) * 255.0 <= 1e-3) tail += fabs((double)m.k[--f.n_eff]) * 255.0;
+  for (int i = 0; i < f.n_eff; ++i) f.k[i] = m.k[i];
+  double smax = std::max(fabs(sin(lo * 0.017453292519943295)), fabs(sin(hi * 0.017453292519943295)));
+  if (lo <= -90.0 && hi >= -90.0) smax = 1.0;
+  if (lo <= 90.0 && hi >= 90.0) smax = 1.0;
+  f.padv = std::min(f.n_eff - 1, (int)ceil((f.n_eff - 1) * smax + 0.5));
+  f.offsets = m.offsets; f.lo = (float)lo; f.hi = (float)hi; f.seed = m.seed;
+}
+
 extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
                                   const float* k_host, const int32_t* offsets_dev, double angle_lo, double angle_hi,
                                   uint64_t seed, int flags, imgtx_stream_t stream) {
@@ -1355,6 +1380,13 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
   int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags);
   if (rc) return rc;
   Shape shp = make_shape(h, w, c, h, w);
+  if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32) {
+    MotionFastParams f;
+    memset(&f, 0, sizeof(f));
+    fill_motion_fast(f, p, angle_lo, angle_hi);
+    const int rc2 = launch_team_op<OpTMotion>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (rc2 != IMGTX_ERR_UNSUPPORTED) return rc2;
+  }
   shp.aux = p.n_eff;
   if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcMotionFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {
@@ -1379,6 +1411,24 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
   for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }
   for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
   Shape shp = make_shape(h, w, c, h, w);
+  if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32) {
+    SnowFastParams f;
+    memset(&f, 0, sizeof(f));
+    fill_motion_fast(f.m, p.m, angle_lo, angle_hi);
+    // rows the line can reach: dy_i = ceil(i*sin(a) - 1/2) over the declared angle range
+    double smin = std::min(sin(angle_lo * 0.017453292519943295), sin(angle_hi * 0.017453292519943295)),
+           smax = std::max(sin(angle_lo * 0.017453292519943295), sin(angle_hi * 0.017453292519943295));
+    if (angle_lo <= -90.0 && angle_hi >= -90.0) smin = -1.0;
+    if (angle_lo <= 90.0 && angle_hi >= 90.0) smax = 1.0;
+    f.pad_top = std::min(f.m.n_eff - 1, std::max(0, (int)ceil(-(f.m.n_eff - 1) * smin + 0.5)));
+    f.pad_bot = std::min(f.m.n_eff - 1, std::max(0, (int)ceil((f.m.n_eff - 1) * smax + 0.5)));
+    f.thresh = thresh; f.c6 = c6; f.one_minus_c6 = one_minus_c6; f.loc = (float)loc; f.scale = (float)scale; f.layer = layer_dev;
+    for (int i = 0; i < 32; ++i) {
+      f.y0[i] = p.y0[i]; f.y1[i] = p.y1[i]; f.x0[i] = p.x0[i]; f.x1[i] = p.x1[i]; f.ty[i] = p.ty[i]; f.tx[i] = p.tx[i];
+    }
+    const int rc2 = launch_team_op<OpTSnow>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (rc2 != IMGTX_ERR_UNSUPPORTED) return rc2;
+  }
   shp.aux = p.m.n_eff;
   if (w % 8 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       OpCcSnowFast::scratch_bytes(shp, 1) + 6 * (size_t)shp.in_bytes < (size_t)max_smem_optin()) {

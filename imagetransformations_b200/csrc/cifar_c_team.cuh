@@ -142,7 +142,7 @@ struct OpTImpulse : NoTeamPrepare {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
-// frost: floor(clip(c0*x + c1*f, 0, 255)) with c0, c1 in Q15 (|error| < 0.008 LSB): one IDP.2A per byte.
+// frost: floor(clip(c0*x + c1*f, 0, 255)) with c0, c1 in Q15 (0 <= error < 0.016 LSB): one IDP.2A per byte.
 struct OpTFrost : NoTeamPrepare {
   using Params = CcFastParams;
   static constexpr int kTeamWarps = 1, kInBufs = 4, kOutBufs = 0, kMaxTeams = 16, kCtasPerSm = 2, kMinBlocks = 2;
@@ -158,7 +158,9 @@ struct OpTFrost : NoTeamPrepare {
     const uint32_t* im = reinterpret_cast<const uint32_t*>(src);
     uint32_t* om = reinterpret_cast<uint32_t*>(dst);
     const int wpi = s.in_bytes >> 2;
-    const uint32_t cc = (uint32_t)__double2int_rn(p.p0 * 32768.0) | ((uint32_t)__double2int_rn(p.p1 * 32768.0) << 16);
+    // Q15 constants rounded UP: sums that are exact integers in real arithmetic (c1 = 0.3 with f = 10, 20, ...) stay at or above
+    // the integer, where the float64 expression of the exact mode puts them; the price is a one-sided error < 0.016 LSB
+    const uint32_t cc = (uint32_t)__double2int_ru(p.p0 * 32768.0 - 1e-9) | ((uint32_t)__double2int_ru(p.p1 * 32768.0 - 1e-9) << 16);
     if (p.tex_n == 0) {
       const uint32_t* fr = reinterpret_cast<const uint32_t*>(p.a) + (size_t)img * wpi;
       for (int i = lane; i < wpi; i += 32) om[i] = mix4(im[i], __ldg(fr + i), cc);

@@ -1,0 +1,250 @@
+// CIFAR-10-C-style stencil corruptions, throughput ("fast") forms on the team pipeline (team_pipeline.cuh).
+// Contract: see cifar_c_team.cuh (float32 evaluation of the exact mode's real-valued expression, <= 1 LSB per byte).
+#pragma once
+#include "team_pipeline.cuh"
+#include "rng.cuh"
+#include <cuda_fp16.h>
+
+namespace imgtx {
+
+// ---- u8 HWC image -> fp16 RGBx canvas (8 bytes per pixel; u8 is exact in fp16) ------------------------------------
+// half(1024 + b) has the bit pattern 0x6400 | b: plant two bytes, subtract 1024 (exact).
+__device__ __forceinline__ uint32_t bytes_to_half2(uint32_t a, uint32_t b, uint32_t sel) {
+  const uint32_t v = __byte_perm(__byte_perm(a, b, sel), 0x64646464u, 0x7160u);   // (b0, 0x64, b1, 0x64)
+  const __half2 r = __hsub2(*reinterpret_cast<const __half2*>(&v), __float2half2_rn(1024.0f));
+  return *reinterpret_cast<const uint32_t*>(&r);
+}
+// four pixels (three words) -> four uint2 {(r, g), (b, 0)}
+__device__ __forceinline__ void quad_to_half4(uint32_t w0, uint32_t w1, uint32_t w2, uint2* o) {
+  o[0] = make_uint2(bytes_to_half2(w0, w0, 0x0010u), bytes_to_half2(w0, w0, 0x0002u) & 0xFFFFu);
+  o[1] = make_uint2(bytes_to_half2(w0, w1, 0x0043u), bytes_to_half2(w1, w1, 0x0001u) & 0xFFFFu);
+  o[2] = make_uint2(bytes_to_half2(w1, w1, 0x0032u), bytes_to_half2(w2, w2, 0x0000u) & 0xFFFFu);
+  o[3] = make_uint2(bytes_to_half2(w2, w2, 0x0021u), bytes_to_half2(w2, w2, 0x0003u) & 0xFFFFu);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// motion_blur: out = floor(sum_i k_i * src[clamp(y + dy_i)][clamp(x + dx_i)] + 1/2), the line offsets (dx_i, dy_i) shared by
+// all pixels of an image.  32-pixel-wide images only (lane = column).  The image is expanded into an fp16 RGBx canvas with
+// `padv` replicated rows above and below, so the vertical clamp disappears and the address of (tap, row) is
+// base_tap[lane] + row*256: the inner loop is one 8-byte load, three conversions and three FFMA, no index arithmetic.
+// A team is four warps (8 rows each); 24 float accumulators per lane.
+struct MotionFastParams {
+  int width, n_eff, padv;
+  float k[32];
+  const int32_t* offsets;   // device (n, width, 2) (dx, dy) or nullptr: angle drawn on chip in [lo, hi] degrees
+  float lo, hi;
+  uint64_t seed;
+};
+
+struct OpTMotion : NoTeamPrepare {
+  using Params = MotionFastParams;
+  static constexpr int kTeamWarps = 4, kInBufs = 3, kOutBufs = 0, kMaxTeams = 4, kCtasPerSm = 2, kMinBlocks = 2;
+  static constexpr int kTT = kTeamWarps * 32, kRows = 32 / kTeamWarps;
+  static size_t team_scratch(const Shape&, const Params& p) { return 512 + (size_t)(32 + 2 * p.padv) * 256; }
+
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
+                             const uint8_t*, int tt, int team) {
+    int2* offs = reinterpret_cast<int2*>(scr);          // (dx, dy) per tap
+    uint8_t* cv = scr + 512;                             // [32 + 2 padv][32] x 8 B
+    const int lane = tt & 31, wq = tt >> 5;
+    if (tt < p.n_eff) {
+      if (p.offsets) {
+        const int32_t* o = p.offsets + ((size_t)img * p.width + tt) * 2;
+        offs[tt] = make_int2(o[0], o[1]);
+      } else {
+        const Philox rng(p.seed);
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x60u, 0u);
+        const float a = (p.lo + (p.hi - p.lo) * u01(r.x)) * 0.017453292519943295f;
+        float sn, cs;
+        sincosf(a, &sn, &cs);
+        offs[tt] = make_int2((int)ceilf((float)tt * cs - 0.5f), (int)ceilf((float)tt * sn - 0.5f));
+      }
+    }
+    {
+      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+      uint2* c2 = reinterpret_cast<uint2*>(cv + p.padv * 256);
+      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+    }
+    team_sync<kTeamWarps>(team);
+    {
+      uint4* c4 = reinterpret_cast<uint4*>(cv);
+      for (int i = tt; i < 2 * p.padv * 16; i += kTT) {
+        const int r = i >> 4, c = i & 15;
+        const int drow = r < p.padv ? r : r + 32, srow = r < p.padv ? p.padv : p.padv + 31;
+        c4[drow * 16 + c] = c4[srow * 16 + c];
+      }
+    }
+    team_sync<kTeamWarps>(team);
+    float acc[kRows][3];
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) acc[r][0] = acc[r][1] = acc[r][2] = 0.5f;
+    const uint8_t* base = cv + (p.padv + kRows * wq) * 256;
+    int2 o_next = offs[0];
+    float k_next = p.k[0];
+    for (int i = 0; i < p.n_eff; ++i) {
+      const int2 o = o_next;
+      const float k = k_next;
+      o_next = offs[min(i + 1, p.n_eff - 1)];   // the next tap's offsets are fetched while this one runs
+      k_next = p.k[min(i + 1, p.n_eff - 1)];
+      const uint8_t* a = base + min(max(o.y, -p.padv), p.padv) * 256 + min(max(lane + o.x, 0), 31) * 8;
+#pragma unroll
+      for (int r = 0; r < kRows; ++r) {
+        const uint2 v = *reinterpret_cast<const uint2*>(a + r * 256);
+        const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+        const float b = __low2float(*reinterpret_cast<const __half2*>(&v.y));
+        acc[r][0] = __fmaf_rn(rg.x, k, acc[r][0]);
+        acc[r][1] = __fmaf_rn(rg.y, k, acc[r][1]);
+        acc[r][2] = __fmaf_rn(b, k, acc[r][2]);
+      }
+    }
+    // floor(acc) (the 1/2 is already in): 0.5 <= acc < 256
+    uint8_t* o = dst + (kRows * wq) * 96 + lane * 3;
+#pragma unroll
+    for (int r = 0; r < kRows; ++r) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) o[r * 96 + c] = (uint8_t)floor_bits(acc[r][c]);
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// snow (32x32): noise layer -> centre zoom -> threshold -> 8 bits -> line blur -> blend.  A team is two warps, lane = column,
+// warp = 16 rows.  The layer up to its 8-bit quantisation follows the exact mode operation for operation (a threshold
+// decision that flipped would move a byte by far more than 1 LSB); the blur and the blend are float32 FFMA on the 0..255
+// scale.  The quantised layer lives in a float canvas with the rows the line can reach replicated above and below, so a
+// (tap, row) is one 4-byte load and one FFMA.
+struct SnowFastParams {
+  MotionFastParams m;        // layer blur: weights, offsets / angle range, seed
+  int pad_top, pad_bot;      // replicated canvas rows
+  float thresh, c6, one_minus_c6;
+  float loc, scale;          // on-chip layer draws: normal(loc, scale)
+  const double* layer;       // device (n, 32, 32) f64 or nullptr
+  int8_t y0[32], y1[32], x0[32], x1[32];
+  float ty[32], tx[32];
+};
+
+struct OpTSnow {
+  using Params = SnowFastParams;
+  static constexpr int kTeamWarps = 2, kInBufs = 3, kOutBufs = 0, kMaxTeams = 6, kCtasPerSm = 2, kMinBlocks = 2;
+  // CTA: ty[32] tx[32] f32 | y0 y1 x0 x1 [32] int
+  static size_t cta_scratch(const Shape&, const Params&) { return 256 + 512; }
+  // team: offsets (256 B) | L0 f32[1024] (later: blurred layer LB) | canvas f32 [32 + pads][32]
+  static size_t team_scratch(const Shape&, const Params& p) { return 256 + 4096 + (size_t)(32 + p.pad_top + p.pad_bot) * 128; }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    float* t = reinterpret_cast<float*>(cta);
+    int* idx = reinterpret_cast<int*>(cta + 256);
+    for (int i = threadIdx.x; i < 32; i += blockDim.x) {
+      t[i] = p.ty[i]; t[32 + i] = p.tx[i];
+      idx[i] = p.y0[i]; idx[32 + i] = p.y1[i]; idx[64 + i] = p.x0[i]; idx[96 + i] = p.x1[i];
+    }
+  }
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
+                             const uint8_t* cta, int tt, int team) {
+    const float* tyv = reinterpret_cast<const float*>(cta);
+    const float* txv = tyv + 32;
+    const int* idx = reinterpret_cast<const int*>(cta + 256);
+    int2* offs = reinterpret_cast<int2*>(scr);
+    float* L0 = reinterpret_cast<float*>(scr + 256);
+    float* cv = L0 + 1024;
+    const int lane = tt & 31, wq = tt >> 5;
+    const Philox rng(p.m.seed);
+    if (tt < p.m.n_eff) {
+      if (p.m.offsets) {
+        const int32_t* o = p.m.offsets + ((size_t)img * p.m.width + tt) * 2;
+        offs[tt] = make_int2(o[0], o[1]);
+      } else {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x62u, 0u);
+        const float a = (p.m.lo + (p.m.hi - p.m.lo) * u01(r.x)) * 0.017453292519943295f;
+        float sn, cs;
+        sincosf(a, &sn, &cs);
+        offs[tt] = make_int2((int)ceilf((float)tt * cs - 0.5f), (int)ceilf((float)tt * sn - 0.5f));
+      }
+    }
+    // A. noise layer (float64 draws cast to float32, like the exact mode)
+    if (p.layer) {
+      const double* l = p.layer + (size_t)img * 1024;
+      for (int i = tt; i < 1024; i += 64) L0[i] = (float)l[i];
+    } else {
+      for (int i = tt; i < 256; i += 64) {
+        const uint64_t e = (uint64_t)img * 256u + (uint64_t)i;
+        const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x61u, 1u);
+        float z0, z1, z2, z3;
+        box_muller_fast(r.x, r.y, z0, z1);
+        box_muller_fast(r.z, r.w, z2, z3);
+        *reinterpret_cast<float4*>(L0 + 4 * i) = make_float4(__fmaf_rn(p.scale, z0, p.loc), __fmaf_rn(p.scale, z1, p.loc),
+                                                             __fmaf_rn(p.scale, z2, p.loc), __fmaf_rn(p.scale, z3, p.loc));
+      }
+    }
+    team_sync<2>(team);
+    // B. centre zoom (order 1), threshold, 8 bits -> canvas rows pad_top .. pad_top + 31 (the exact mode's operation order)
+    {
+      const float tx = txv[lane], ux = __fsub_rn(1.0f, tx);
+      const int xa = idx[64 + lane], xb = idx[96 + lane];
+#pragma unroll 4
+      for (int r = 0; r < 16; ++r) {
+        const int y = 16 * wq + r;
+        const float ty = tyv[y], uy = __fsub_rn(1.0f, ty);
+        const int ya = idx[y] * 32, yb = idx[32 + y] * 32;
+        float acc = __fmul_rn(__fmul_rn(L0[ya + xa], uy), ux);
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[ya + xb], uy), tx));
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[yb + xa], ty), ux));
+        acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[yb + xb], ty), tx));
+        if (acc < p.thresh) acc = 0.0f;
+        acc = acc < 0.0f ? 0.0f : (acc > 1.0f ? 1.0f : acc);
+        cv[(p.pad_top + y) * 32 + lane] = (float)__float2int_rz(__fmul_rn(acc, 255.0f));
+      }
+    }
+    team_sync<2>(team);
+    // replicated rows above / below
+    for (int i = tt; i < (p.pad_top + p.pad_bot) * 32; i += 64) {
+      const int r = i >> 5, c = i & 31;
+      const int drow = r < p.pad_top ? r : r + 32, srow = r < p.pad_top ? p.pad_top : p.pad_top + 31;
+      cv[drow * 32 + c] = cv[srow * 32 + c];
+    }
+    team_sync<2>(team);
+    // C. line blur of the 8-bit layer, rounded back to 8 bits -> LB (aliases L0)
+    {
+      float acc[16];
+#pragma unroll
+      for (int r = 0; r < 16; ++r) acc[r] = 0.5f;
+      const float* base = cv + (p.pad_top + 16 * wq) * 32;
+      for (int i = 0; i < p.m.n_eff; ++i) {
+        const int2 o = offs[i];
+        const float k = p.m.k[i];
+        const float* a = base + min(max(o.y, -p.pad_top), p.pad_bot) * 32 + min(max(lane + o.x, 0), 31);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) acc[r] = __fmaf_rn(a[r * 32], k, acc[r]);
+      }
+#pragma unroll
+      for (int r = 0; r < 16; ++r) L0[(16 * wq + r) * 32 + lane] = __fsub_rn(__fadd_rd(acc[r], 8388608.0f), 8388608.0f);
+    }
+    team_sync<2>(team);
+    // D. blend: c6*x + (1 - c6)*max(x, 1.5*gray + 127.5) + layer + rotated layer, four pixels (three words) per step
+    {
+      const uint32_t* im = reinterpret_cast<const uint32_t*>(src);
+      uint32_t* om = reinterpret_cast<uint32_t*>(dst);
+      for (int q = tt; q < 256; q += 64) {
+        const uint32_t w0 = im[3 * q], w1 = im[3 * q + 1], w2 = im[3 * q + 2];
+        const float4 sl = *reinterpret_cast<const float4*>(L0 + 4 * q), sr = *reinterpret_cast<const float4*>(L0 + 1020 - 4 * q);
+        const float add[4] = {sl.x + sr.w, sl.y + sr.z, sl.z + sr.y, sl.w + sr.x};
+        const uint32_t px[4] = {w0, __funnelshift_r(w0, w1, 24), __funnelshift_r(w1, w2, 16), w2 >> 8};
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float r = byte_f(px[e], 0), g = byte_f(px[e], 1), b = byte_f(px[e], 2);
+          const float gray = __fmaf_rn(b, 0.114f, __fmaf_rn(g, 0.587f, r * 0.299f));
+          const float whit = __fmaf_rn(gray, 1.5f, 127.5f);
+          const float vr = fminf(__fmaf_rn(p.one_minus_c6, fmaxf(r, whit), __fmaf_rn(p.c6, r, add[e])), 255.0f);
+          const float vg = fminf(__fmaf_rn(p.one_minus_c6, fmaxf(g, whit), __fmaf_rn(p.c6, g, add[e])), 255.0f);
+          const float vb = fminf(__fmaf_rn(p.one_minus_c6, fmaxf(b, whit), __fmaf_rn(p.c6, b, add[e])), 255.0f);
+          o[e] = __byte_perm(__byte_perm(floor_bits(vr), floor_bits(vg), 0x0040u), floor_bits(vb), 0x7410u) & 0x00FFFFFFu;
+        }
+        uint32_t a, b, c;
+        pack_rgb4(o[0], o[1], o[2], o[3], a, b, c);
+        om[3 * q] = a; om[3 * q + 1] = b; om[3 * q + 2] = c;
+      }
+    }
+  }
+};
+
+}  // namespace imgtx

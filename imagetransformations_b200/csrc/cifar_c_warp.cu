@@ -12,6 +12,7 @@
 // Roofline: nominally HBM (2 B/element); both are integer/f64-ALU bound.
 #include "pipeline.cuh"
 #include "rng.cuh"
+#include "cifar_c_team2.cuh"
 #include <math.h>
 #include <string.h>
 #include <algorithm>
@@ -665,6 +666,282 @@ struct OpCcElasticFast : NoSpill, ElasticCommon {
 };
 
 // ------------------------------------------------------------------------------------------------
+// elastic_transform, throughput form (IMGTX_CC_FAST) on the team pipeline: a team of four warps owns one 32x32 image.
+//   fields     on-chip draws are uniform on the 1024-point grid (2m + 1 - 1024)/1024 of (-1, 1), built directly as fp16 from
+//              Philox bits (exactly representable, so the tensor-core products see the true draw); injected float64 fields
+//              are split into fp16 hi + lo
+//   smoothing  S = A F A^T with the folded 32x32 Gaussian operator: mma.sync.m16n8k16 (fp16 in, float32 accumulate), A and
+//              the intermediate G = A F carried as hi + lo halves (22 significant bits): |error| < 1e-6 of the field range.
+//              The accumulators of the first product are re-used in registers as the A operand of the second one.
+//   warp       cv2.warpAffine's integer coordinate arithmetic kept exactly (tables in float64 as OpenCV builds them); the
+//              bilinear weights are 10-bit products, so sum w*b is EXACT in float32 on the 0..255 scale; source pixels come
+//              from an fp16 RGBx canvas, REFLECT_101 through a shared index table
+//   remap      bilinear at (y + dy, x + dx) in float32 (floor by a round-down add), scipy 'reflect' through an index table
+// Everything stays on the 0..255 scale, so the output is floor(v) with no multiply.  Differences from the exact form:
+// float32 instead of float64 interpolation weights and the ~1e-6 smoothing error: <= 1 LSB after floor.
+struct ElasticFastParams {
+  ElasticParams e;
+  float alpha;
+};
+
+template <bool WARP_ONLY>
+struct OpTElastic : ElasticCommon {
+  using Params = ElasticFastParams;
+  static constexpr int kTeamWarps = 8, kInBufs = 3, kOutBufs = 0, kMaxTeams = 2, kCtasPerSm = 2, kMinBlocks = 2;
+  static constexpr int kTT = kTeamWarps * 32;
+  static constexpr int kPA = 40;            // pitch (halves) of the fp16 operator / field rows: conflict-free fragment loads
+  static constexpr int kLutLo = 64, kLut = 160;   // index tables cover [-64, 96)
+  // CTA: Ah, Al [32][40] half | refl101 row (x256) and col (x8) offsets for the canvas | reflect row (x512) / col (x16) for W
+  static size_t cta_scratch(const Shape&, const Params&) { return 2 * 32 * kPA * 2 + 4 * kLut * 4; }
+  // team: Mi (6 f64) + tables (128 int) | FT hi, lo [2][32][40] half (aliased by the canvas [1024] x 8 B) | DXY [2][32][32] f32 | W [1024] float4
+  static constexpr int kOffTab = 64, kOffFT = 64 + 512, kOffDXY = kOffFT + 10240, kOffW = kOffDXY + 8192;
+  static size_t team_scratch(const Shape&, const Params&) { return WARP_ONLY ? kOffFT + 8192 : kOffW + 16384; }
+
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    __half* Ah = reinterpret_cast<__half*>(cta);
+    __half* Al = Ah + 32 * kPA;
+    int* lut = reinterpret_cast<int*>(cta + 2 * 32 * kPA * 2);
+    if (!WARP_ONLY) {
+      for (int e = threadIdx.x; e < 32 * 32; e += blockDim.x) {
+        const int o = e >> 5, i = e & 31;
+        double a = 0.0;
+        for (int k = -p.e.lw; k <= p.e.lw; ++k)
+          if (refl_half(o + k, 32) == i) a += p.e.w[k < 0 ? -k : k];
+        const __half hi = __double2half(a);
+        Ah[o * kPA + i] = hi;
+        Al[o * kPA + i] = __double2half(a - (double)__half2float(hi));
+      }
+    }
+    for (int e = threadIdx.x; e < kLut; e += blockDim.x) {
+      const int i = e - kLutLo;
+      const int r101 = reflect101(i, 32), rh = reflect_half(i, 32);
+      lut[e] = r101 * 256; lut[kLut + e] = r101 * 8; lut[2 * kLut + e] = rh * 512; lut[3 * kLut + e] = rh * 16;
+    }
+  }
+
+  // 1 / x to ~1e-16 without the float64 division sequence (one thread does this per image: latency matters)
+  __device__ static __forceinline__ double rcp_fast(double x) {
+    double r = (double)__frcp_rn((float)x);
+    r = r * (2.0 - x * r);
+    r = r * (2.0 - x * r);
+    r = r * (2.0 - x * r);
+    return r;
+  }
+  // ElasticCommon::inverse_matrix with the divisions replaced by rcp_fast (on-chip jitter: two Philox calls)
+  __device__ static void inverse_matrix_fast(const ElasticParams& p, const Philox& rng, int64_t img, double* Mo) {
+    double M[6];
+    if (p.M) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) M[k] = p.M[img * 6 + k];
+    } else {
+      // on-chip jitter: the forward matrix through the three jittered corners in float32 (the draw itself is float32; no
+      // oracle sees this matrix), then the float64 inversion and tables below as cv2 does for any matrix
+      const float cs = 16.0f, q = 10.0f;
+      const float x0 = cs + q, y0 = cs + q, x1 = cs + q, y1 = cs - q, x2 = cs - q, y2 = cs - q;
+      const uint4 r0 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 0u);
+      const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x80u, 1u);
+      const float c2 = (float)p.c2, two = 2.0f * c2;
+      const float u[2][3] = {{x0 + (two * u01(r0.x) - c2), x1 + (two * u01(r0.z) - c2), x2 + (two * u01(r1.x) - c2)},
+                             {y0 + (two * u01(r0.y) - c2), y1 + (two * u01(r0.w) - c2), y2 + (two * u01(r1.y) - c2)}};
+      const float idet = 1.0f / (x0 * (y1 - y2) - y0 * (x1 - x2) + (x1 * y2 - x2 * y1));
+#pragma unroll
+      for (int rrow = 0; rrow < 2; ++rrow) {
+        const float u0 = u[rrow][0], u1 = u[rrow][1], u2 = u[rrow][2];
+        M[rrow * 3 + 0] = (double)((u0 * (y1 - y2) - y0 * (u1 - u2) + (u1 * y2 - u2 * y1)) * idet);
+        M[rrow * 3 + 1] = (double)((x0 * (u1 - u2) - u0 * (x1 - x2) + (x1 * u2 - x2 * u1)) * idet);
+        M[rrow * 3 + 2] = (double)((x0 * (y1 * u2 - y2 * u1) - y0 * (x1 * u2 - x2 * u1) + u0 * (x1 * y2 - x2 * y1)) * idet);
+      }
+    }
+    double D = M[0] * M[4] - M[1] * M[3];
+    D = D != 0.0 ? rcp_fast(D) : 0.0;
+    const double A11 = M[4] * D, A22 = M[0] * D;
+    M[0] = A11; M[1] *= -D; M[3] *= -D; M[4] = A22;
+    const double b1 = -M[0] * M[2] - M[1] * M[5];
+    const double b2 = -M[3] * M[2] - M[4] * M[5];
+    M[2] = b1; M[5] = b2;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) Mo[k] = M[k];
+  }
+
+  __device__ static __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+  // (x, y) -> fp16 pair hi and the residual pair lo
+  __device__ static __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(x, y);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(__fsub_rn(x, hf.x), __fsub_rn(y, hf.y));
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+  }
+
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
+                             const uint8_t* cta, int tt, int team) {
+    const __half* Ah = reinterpret_cast<const __half*>(cta);
+    const __half* Al = Ah + 32 * kPA;
+    const int* lut = reinterpret_cast<const int*>(cta + 2 * 32 * kPA * 2);
+    double* Mi = reinterpret_cast<double*>(scr);
+    int* tab = reinterpret_cast<int*>(scr + kOffTab);
+    __half* FT = reinterpret_cast<__half*>(scr + kOffFT);     // [hi/lo][f][x][kPA]  (element (y, x) of field f at x*kPA + y)
+    uint8_t* canvas = scr + kOffFT;                            // aliases FT (dead after the smoothing)
+    float* DXY = reinterpret_cast<float*>(scr + kOffDXY);      // [f][y][x]
+    uint8_t* Wb = scr + kOffW;                                 // [y][x] float4
+    const int lane = tt & 31, wq = tt >> 5;
+    const Philox rng(p.e.seed);
+    const bool has_lo = p.e.ux != nullptr;
+
+    if (tt == 0) inverse_matrix_fast(p.e, rng, img, Mi);
+    if (WARP_ONLY) {
+      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+      uint2* c2 = reinterpret_cast<uint2*>(canvas);
+      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+    }
+    if (!WARP_ONLY) {
+      // ---- fields -> FT (fp16, transposed) ----
+      if (p.e.ux) {
+        for (int i = tt; i < 2048; i += kTT) {
+          const int f = i >> 10, px = i & 1023, y = px >> 5, x = px & 31;
+          float v = (float)(f ? p.e.uy[img * 1024 + px] : p.e.ux[img * 1024 + px]);
+          v = fminf(fmaxf(v, -1.0f), 1.0f);
+          const __half hi = __float2half_rn(v);
+          FT[(f * 32 + x) * kPA + y] = hi;
+          FT[((2 + f) * 32 + x) * kPA + y] = __float2half_rn(__fsub_rn(v, __half2float(hi)));
+        }
+      } else {
+        const __half2 two = __float2half2_rn(2.0f), m3 = __float2half2_rn(-3.0f), ulp = __float2half2_rn(0.0009765625f);
+        for (int i = tt; i < 256; i += kTT) {   // (f, x, group of 8 rows)
+          const int f = i >> 7, x = (i >> 2) & 31, y0 = (i & 3) * 8;
+          const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x81u + f, (uint32_t)(i & 127));
+          uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const uint32_t hb = (rr[e] & 0x03FF03FFu) | 0x3C003C00u;    // two halves in [1, 2)
+            const __half2 u = __hadd2(__hfma2(*reinterpret_cast<const __half2*>(&hb), two, m3), ulp);
+            rr[e] = *reinterpret_cast<const uint32_t*>(&u);
+          }
+          *reinterpret_cast<uint4*>(FT + (f * 32 + x) * kPA + y0) = make_uint4(rr[0], rr[1], rr[2], rr[3]);
+        }
+      }
+    }
+    team_sync<8>(team);
+    if (tt < 64) affine_tables(Mi, 32, 32, tab, tt);
+    if (!WARP_ONLY && wq < 4) {
+      // ---- smoothing on the tensor cores: warp = (field, 16 output rows); warps 4-7 go straight to the barrier ----
+      const int f = wq >> 1, mt = wq & 1, g = lane >> 2, t = lane & 3;
+      const uint32_t* Ah32 = reinterpret_cast<const uint32_t*>(Ah);
+      const uint32_t* Al32 = reinterpret_cast<const uint32_t*>(Al);
+      const uint32_t* Fh32 = reinterpret_cast<const uint32_t*>(FT + f * 32 * kPA);
+      const uint32_t* Fl32 = reinterpret_cast<const uint32_t*>(FT + (2 + f) * 32 * kPA);
+      constexpr int PW = kPA / 2;   // pitch in 32-bit words
+      float c1[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) c1[nt][0] = c1[nt][1] = c1[nt][2] = c1[nt][3] = 0.0f;
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        uint32_t ah[4], al[4];
+        const int r0 = (16 * mt + g) * PW + 8 * kt + t, r1 = r0 + 8 * PW;
+        ah[0] = Ah32[r0]; ah[1] = Ah32[r1]; ah[2] = Ah32[r0 + 4]; ah[3] = Ah32[r1 + 4];
+        al[0] = Al32[r0]; al[1] = Al32[r1]; al[2] = Al32[r0 + 4]; al[3] = Al32[r1 + 4];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const int b = (8 * nt + g) * PW + 8 * kt + t;
+          const uint32_t b0 = Fh32[b], b1 = Fh32[b + 4];
+          mma16816(c1[nt], ah, b0, b1);
+          mma16816(c1[nt], al, b0, b1);
+          if (has_lo) mma16816(c1[nt], ah, Fl32[b], Fl32[b + 4]);
+        }
+      }
+      float c2[4][4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) c2[nt][0] = c2[nt][1] = c2[nt][2] = c2[nt][3] = 0.0f;
+#pragma unroll
+      for (int kt = 0; kt < 2; ++kt) {
+        uint32_t gh[4], gl[4];
+        split2(c1[2 * kt][0], c1[2 * kt][1], gh[0], gl[0]);
+        split2(c1[2 * kt][2], c1[2 * kt][3], gh[1], gl[1]);
+        split2(c1[2 * kt + 1][0], c1[2 * kt + 1][1], gh[2], gl[2]);
+        split2(c1[2 * kt + 1][2], c1[2 * kt + 1][3], gh[3], gl[3]);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+          const int b = (8 * nt + g) * PW + 8 * kt + t;
+          const uint32_t bh0 = Ah32[b], bh1 = Ah32[b + 4];
+          mma16816(c2[nt], gh, bh0, bh1);
+          mma16816(c2[nt], gl, bh0, bh1);
+          mma16816(c2[nt], gh, Al32[b], Al32[b + 4]);
+        }
+      }
+      float* D = DXY + f * 1024 + (16 * mt + g) * 32 + 2 * t;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        *reinterpret_cast<float2*>(D + 8 * nt) = make_float2(__fmul_rn(c2[nt][0], p.alpha), __fmul_rn(c2[nt][1], p.alpha));
+        *reinterpret_cast<float2*>(D + 8 * nt + 256) = make_float2(__fmul_rn(c2[nt][2], p.alpha), __fmul_rn(c2[nt][3], p.alpha));
+      }
+    }
+    team_sync<8>(team);   // FT is dead: the canvas may overwrite it; tables are ready
+    if (!WARP_ONLY) {
+      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+      uint2* c2 = reinterpret_cast<uint2*>(canvas);
+      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+      team_sync<8>(team);
+    }
+    // ---- affine warp (cv2.warpAffine coordinates), thread = column `lane`, rows wq, wq + 4, ... ----
+    const int* lrow = lut + kLutLo;
+    const int* lcol = lut + kLut + kLutLo;
+    const int adelta = tab[2 * lane], bdelta = tab[2 * lane + 1];
+#pragma unroll 2
+    for (int y = wq; y < 32; y += kTeamWarps) {
+      const int X = (tab[2 * (32 + y)] + adelta) >> 5, Y = (tab[2 * (32 + y) + 1] + bdelta) >> 5;
+      const int sx = min(max(X >> 5, -kLutLo), kLut - kLutLo - 2), sy = min(max(Y >> 5, -kLutLo), kLut - kLutLo - 2);
+      const float fx = __uint_as_float(0x4B000000u | (uint32_t)(X & 31)) - 8388608.0f,
+                  fy = __uint_as_float(0x4B000000u | (uint32_t)(Y & 31)) - 8388608.0f;
+      // weights in 1/1024 units as exact floats, scaled by 2^-10: w11 = fx fy, w10 = fy (32 - fx), ...
+      const float w11 = fx * fy * 0.0009765625f, w10 = fy * 0.03125f - w11, w01 = fx * 0.03125f - w11,
+                  w00 = 1.0f - fx * 0.03125f - w10;
+      const int ra = lrow[sy], rb = lrow[sy + 1], ca = lcol[sx], cb = lcol[sx + 1];
+      const uint2 p00 = *reinterpret_cast<const uint2*>(canvas + ra + ca), p01 = *reinterpret_cast<const uint2*>(canvas + ra + cb);
+      const uint2 p10 = *reinterpret_cast<const uint2*>(canvas + rb + ca), p11 = *reinterpret_cast<const uint2*>(canvas + rb + cb);
+      const float2 a00 = __half22float2(*reinterpret_cast<const __half2*>(&p00.x)), a01 = __half22float2(*reinterpret_cast<const __half2*>(&p01.x));
+      const float2 a10 = __half22float2(*reinterpret_cast<const __half2*>(&p10.x)), a11 = __half22float2(*reinterpret_cast<const __half2*>(&p11.x));
+      const float b00 = __low2float(*reinterpret_cast<const __half2*>(&p00.y)), b01 = __low2float(*reinterpret_cast<const __half2*>(&p01.y));
+      const float b10 = __low2float(*reinterpret_cast<const __half2*>(&p10.y)), b11 = __low2float(*reinterpret_cast<const __half2*>(&p11.y));
+      const float r = __fmaf_rn(a11.x, w11, __fmaf_rn(a10.x, w10, __fmaf_rn(a01.x, w01, a00.x * w00)));
+      const float gg = __fmaf_rn(a11.y, w11, __fmaf_rn(a10.y, w10, __fmaf_rn(a01.y, w01, a00.y * w00)));
+      const float b = __fmaf_rn(b11, w11, __fmaf_rn(b10, w10, __fmaf_rn(b01, w01, b00 * w00)));
+      if (WARP_ONLY) {
+        uint8_t* o = dst + (y * 32 + lane) * 3;
+        o[0] = (uint8_t)floor_bits(r); o[1] = (uint8_t)floor_bits(gg); o[2] = (uint8_t)floor_bits(b);
+      } else {
+        *reinterpret_cast<float4*>(Wb + (y * 32 + lane) * 16) = make_float4(r, gg, b, 0.0f);
+      }
+    }
+    if (WARP_ONLY) return;
+    team_sync<8>(team);
+    // ---- bilinear remap at (y + dy, x + dx), scipy 'reflect' ----
+    const int* hrow = lut + 2 * kLut;   // biased by kLutLo: index = floor(coordinate + 64)
+    const int* hcol = lut + 3 * kLut;
+    const float xb = (float)(lane + kLutLo);
+#pragma unroll 2
+    for (int y = wq; y < 32; y += kTeamWarps) {
+      const float yy = (float)(y + kLutLo) + DXY[1024 + y * 32 + lane], xx = xb + DXY[y * 32 + lane];
+      const float ry = __fadd_rd(yy, 8388608.0f), rx = __fadd_rd(xx, 8388608.0f);
+      const float ty = yy - (ry - 8388608.0f), tx = xx - (rx - 8388608.0f);
+      const int iy = min((int)(__float_as_uint(ry) & 255u), kLut - 2), ix = min((int)(__float_as_uint(rx) & 255u), kLut - 2);
+      const int ra = hrow[iy], rb = hrow[iy + 1], ca = hcol[ix], cb = hcol[ix + 1];
+      const float4 q00 = *reinterpret_cast<const float4*>(Wb + ra + ca), q01 = *reinterpret_cast<const float4*>(Wb + ra + cb);
+      const float4 q10 = *reinterpret_cast<const float4*>(Wb + rb + ca), q11 = *reinterpret_cast<const float4*>(Wb + rb + cb);
+      const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
+      const float r = __fmaf_rn(q11.x, w11, __fmaf_rn(q10.x, w10, __fmaf_rn(q01.x, w01, q00.x * w00)));
+      const float gg = __fmaf_rn(q11.y, w11, __fmaf_rn(q10.y, w10, __fmaf_rn(q01.y, w01, q00.y * w00)));
+      const float b = __fmaf_rn(q11.z, w11, __fmaf_rn(q10.z, w10, __fmaf_rn(q01.z, w01, q00.z * w00)));
+      uint8_t* o = dst + (y * 32 + lane) * 3;
+      o[0] = (uint8_t)floor_bits(fmaxf(r, 0.0f)); o[1] = (uint8_t)floor_bits(fmaxf(gg, 0.0f)); o[2] = (uint8_t)floor_bits(fmaxf(b, 0.0f));
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
 // jpeg_compression
 // ------------------------------------------------------------------------------------------------
 struct JpegParams {
@@ -880,6 +1157,14 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed; p.force_exact = (flags & IMGTX_CC_REPLAY_ALL) ? 1 : 0;
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
+  if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32 && (alpha == 0.0 || (lw >= 0 && fabs(alpha) <= 16.0))) {
+    ElasticFastParams f;
+    f.e = p;
+    f.alpha = (float)alpha;
+    const int rc = alpha == 0.0 ? launch_team_op<OpTElastic<true>>(in, out, n, shp, f, (cudaStream_t)stream)
+                                : launch_team_op<OpTElastic<false>>(in, out, n, shp, f, (cudaStream_t)stream);
+    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+  }
   if (alpha == 0.0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out))
     return launch_image_op<OpCcAffineWarp>(in, out, n, shp, p, (cudaStream_t)stream, 0, 96 * 1024);   // zero displacement: the warp alone (96 KB groups: 476 -> 438 us)
   if (lw <= std::min(h, w) && (h * w) % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out)) {

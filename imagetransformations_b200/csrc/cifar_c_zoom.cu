@@ -1,0 +1,191 @@
+// zoom_blur, throughput form (IMGTX_CC_FAST of imgtx_cc_csr_ell_u8).
+//
+// zoom_blur is ONE fixed sparse linear operator per severity (oracle/cifar_c.py:zoom_operator: 5.5-12.3 taps per output
+// pixel on average, 7-19 at most, inside an 8x8 window).  The exact form (cifar_c_stencil.cu:OpCcCsrEll) keeps the operator in
+// shared memory and is bound by shared-memory traffic: 18 bytes per tap and pixel (index + weight + three floats).  Here
+//   * a thread OWNS one output pixel for the whole launch and keeps its taps (byte offset, float weight) in REGISTERS: the
+//     operator is read from global memory once per CTA, never again;
+//   * a warp is one image row, so its lanes read neighbouring canvas pixels (conflict-free 8-byte loads) and run the
+//     longest tap count of that row, rounded up to a multiple of 4 (taps are issued four loads at a time);
+//   * the staged image is expanded once into an fp16 RGBx canvas (u8 is exact in fp16): a tap is ONE 8-byte shared-memory
+//     load, three conversions and three FFMA (float32 accumulation on the 0..255 scale);
+//   * persistent CTAs (one per SM, one thread per pixel), images arrive by 1-D bulk TMA into a 3-deep ring, results leave by bulk
+//     TMA stores; the canvas of image i+1 is built while image i is evaluated, so there is one CTA barrier per image.
+// Arithmetic: sum_k w_k * x_k in float32 FFMA order instead of the oracle's ordered float32 sum of rounded products on the
+// 0..1 scale: |difference| < 1e-4 LSB, i.e. <= 1 LSB after floor (tests/test_gpu_fast_mode.py).
+#include "team_pipeline.cuh"
+#include <cuda_fp16.h>
+#include <type_traits>
+
+namespace imgtx {
+
+constexpr int kZoomThreads = 1024;
+constexpr int kZoomRing = 6;
+constexpr int kZoomCanvas = 1024 * 8;   // bytes per canvas (fixed pitch: the second canvas is an immediate offset away)
+
+// 8-byte shared-memory load at a register address plus a compile-time offset
+template <int IMM>
+__device__ __forceinline__ uint2 lds64(uint32_t addr) {
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2+%3];" : "=r"(v.x), "=r"(v.y) : "r"(addr), "n"(IMM));
+  return v;
+}
+
+template <int T>
+__global__ void __launch_bounds__(kZoomThreads, 1)
+zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int P /* pixels, <= 1024, % 4 == 0 */,
+                 const int32_t* __restrict__ indptr, const int32_t* __restrict__ indices, const float* __restrict__ weights) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int img_bytes = P * 3, ib = (int)align_up((size_t)img_bytes, 128);
+  constexpr int cb = kZoomCanvas;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint8_t* in_buf = smem + 256;
+  uint8_t* canvas = in_buf + kZoomRing * ib;                   // 2 x P x half4
+  uint8_t* out_buf = canvas + 2 * cb;                          // 2 x ib
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    for (int i = 0; i < kZoomRing; ++i) mbar_init(&full[i], 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+
+  // my pixel and its taps (padding taps read canvas pixel 0 with weight 0)
+  const int pix = tid < P ? tid : -1;
+  int off[T];
+  float wt[T];
+  int cnt = 0;
+  {
+    const int k0 = pix >= 0 ? indptr[pix] : 0;
+    cnt = pix >= 0 ? min(indptr[pix + 1] - k0, T) : 0;
+#pragma unroll
+    for (int k = 0; k < T; ++k) {
+      const bool ok = k < cnt;
+      off[k] = (int)smem_u32(canvas) + (ok ? indices[k0 + k] * 8 : 0);   // absolute shared address in canvas 0
+      wt[k] = ok ? weights[k0 + k] : 0.0f;
+    }
+  }
+  int wmax = cnt;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+
+  const int64_t stride = gridDim.x, first = blockIdx.x;
+  if (tid == 0) {
+    for (int i = 0; i < kZoomRing; ++i) {
+      const int64_t img = first + (int64_t)i * stride;
+      if (img < n) {
+        mbar_expect_tx(&full[i], (uint32_t)img_bytes);
+        bulk_g2s(in_buf + i * ib, in + img * img_bytes, (uint32_t)img_bytes, &full[i]);
+      }
+    }
+  }
+  // u8 HWC -> half4 canvas, 4 pixels (3 words) per thread-step
+  auto build = [&](int it) {
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(in_buf + (it % kZoomRing) * ib);
+    uint2* cv = reinterpret_cast<uint2*>(canvas + (it & 1) * cb);
+    const __half2 k1024 = __float2half2_rn(1024.0f);
+    for (int q = tid; q < (P >> 2); q += kZoomThreads) {
+      const uint32_t w0 = s32[3 * q], w1 = s32[3 * q + 1], w2 = s32[3 * q + 2];
+      // half(1024 + b) has the bit pattern 0x6400 | b: plant two bytes, subtract 1024 (exact)
+      auto h2 = [&](uint32_t a, uint32_t b, uint32_t sel) {
+        const uint32_t v = __byte_perm(__byte_perm(a, b, sel), 0x64646464u, 0x7160u);   // (b0, 0x64, b1, 0x64)
+        const __half2 r = __hsub2(*reinterpret_cast<const __half2*>(&v), k1024);
+        return *reinterpret_cast<const uint32_t*>(&r);
+      };
+      // pixels: (w0.b0 b1 b2) (w0.b3 w1.b0 b1) (w1.b2 b3 w2.b0) (w2.b1 b2 b3); second half2 of a pixel = (blue, 0)
+      const uint32_t zero_hi = 0xFFFF0000u;
+      cv[4 * q + 0] = make_uint2(h2(w0, w0, 0x0010u), h2(w0, w0, 0x0002u) & ~zero_hi);
+      cv[4 * q + 1] = make_uint2(h2(w0, w1, 0x0043u), h2(w1, w1, 0x0001u) & ~zero_hi);
+      cv[4 * q + 2] = make_uint2(h2(w1, w1, 0x0032u), h2(w2, w2, 0x0000u) & ~zero_hi);
+      cv[4 * q + 3] = make_uint2(h2(w2, w2, 0x0021u), h2(w2, w2, 0x0003u) & ~zero_hi);
+    }
+  };
+
+  int64_t img = first;
+  if (img < n) {
+    mbar_wait(&full[0], 0u);
+    build(0);
+  }
+  __syncthreads();
+  // one image: build the next canvas, evaluate this one.  PAR (canvas / output buffer parity) is a compile-time constant so
+  // that `canvas + PAR * cb + off[k]` is one register plus an immediate: no address arithmetic per tap.
+  auto step = [&](auto par, int it, int64_t img) {
+    constexpr int PAR = decltype(par)::value;
+    if (img + stride < n) {
+      mbar_wait(&full[(it + 1) % kZoomRing], (uint32_t)((it + 1) / kZoomRing) & 1u);
+      build(it + 1);
+    }
+    uint8_t* ob = out_buf + PAR * ib;
+    float a0 = 0.0009765625f, a1 = a0, a2 = a0;   // 2^-10: an exactly integral sum floors to itself
+#pragma unroll
+    for (int k0 = 0; k0 < T; k0 += 4) {
+      if (k0 < wmax) {
+        uint2 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = lds64<PAR * cb>((uint32_t)off[k0 + u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const float2 rg = __half22float2(*reinterpret_cast<const __half2*>(&v[u].x));
+          const float b = __low2float(*reinterpret_cast<const __half2*>(&v[u].y));
+          a0 = __fmaf_rn(rg.x, wt[k0 + u], a0);
+          a1 = __fmaf_rn(rg.y, wt[k0 + u], a1);
+          a2 = __fmaf_rn(b, wt[k0 + u], a2);
+        }
+      }
+    }
+    if (pix >= 0) {
+      uint8_t* o = ob + pix * 3;
+      o[0] = (uint8_t)floor_bits(fminf(fmaxf(a0, 0.0f), 255.0f));
+      o[1] = (uint8_t)floor_bits(fminf(fmaxf(a1, 0.0f), 255.0f));
+      o[2] = (uint8_t)floor_bits(fminf(fmaxf(a2, 0.0f), 255.0f));
+    }
+    fence_async_smem();
+    if (tid == 0) bulk_wait_read<0>();   // the store of the previous image has finished reading the other output buffer
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(out + img * img_bytes, ob, (uint32_t)img_bytes);
+      bulk_commit();
+      const int64_t nxt = img + (int64_t)kZoomRing * stride;
+      if (nxt < n) {
+        const int st = it % kZoomRing;
+        mbar_expect_tx(&full[st], (uint32_t)img_bytes);
+        bulk_g2s(in_buf + st * ib, in + nxt * img_bytes, (uint32_t)img_bytes, &full[st]);
+      }
+    }
+  };
+  for (int it = 0; img < n; it += 2) {
+    step(std::integral_constant<int, 0>{}, it, img);
+    img += stride;
+    if (img < n) step(std::integral_constant<int, 1>{}, it + 1, img);
+    img += stride;
+  }
+  if (tid == 0) bulk_wait_all<0>();
+}
+
+template <int T>
+static int launch_zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int P, const int32_t* indptr, const int32_t* indices,
+                            const float* weights, cudaStream_t stream) {
+  const size_t ib = align_up((size_t)P * 3, 128);
+  const size_t smem = 256 + kZoomRing * ib + 2 * (size_t)kZoomCanvas + 2 * ib;
+  auto kern = zoom_fast_kernel<T>;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t grid = std::min<int64_t>(n, sm_count());
+  kern<<<(unsigned)grid, kZoomThreads, smem, stream>>>(in, out, n, P, indptr, indices, weights);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+// IMGTX_ERR_UNSUPPORTED when the shape is outside the fast form (the caller falls back to the exact ELL kernel)
+int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const int32_t* indptr, const int32_t* indices,
+              const float* weights, int max_row_taps, cudaStream_t stream) {
+  const int P = h * w;
+  if (P > 1024 || P % 4 != 0 || max_row_taps > 20 || (P * 3) % 16 != 0 || !aligned16(in) || !aligned16(out))
+    return IMGTX_ERR_UNSUPPORTED;
+  if (n <= 0) return IMGTX_OK;
+  if (max_row_taps <= 8) return launch_zoom_fast<8>(in, out, n, P, indptr, indices, weights, stream);
+  if (max_row_taps <= 12) return launch_zoom_fast<12>(in, out, n, P, indptr, indices, weights, stream);
+  if (max_row_taps <= 16) return launch_zoom_fast<16>(in, out, n, P, indptr, indices, weights, stream);
+  return launch_zoom_fast<20>(in, out, n, P, indptr, indices, weights, stream);
+}
+
+}  // namespace imgtx

@@ -48,9 +48,9 @@ def test_group_boundaries_and_batch_independence(cuda):
     xd = torch.from_numpy(x).cuda()
     for name, sev in (("defocus_blur", 5), ("zoom_blur", 2), ("jpeg_compression", 3), ("contrast", 1), ("pixelate", 4),
                       ("brightness", 4)):
-        full = C.corrupt(xd, name, sev).cpu().numpy()
+        full = C.corrupt(xd, name, sev, mode="exact").cpu().numpy()
         for i in (0, 1, 150, 299, 300):
-            one = C.corrupt(xd[i:i + 1], name, sev).cpu().numpy()
+            one = C.corrupt(xd[i:i + 1], name, sev, mode="exact").cpu().numpy()
             assert np.array_equal(full[i], one[0]), (name, i)
         assert np.array_equal(full[:9], CC.corrupt(name, sev, x[:9]))
 
@@ -103,18 +103,28 @@ def test_onchip_plasma_is_a_plasma(cuda):
 
 
 def test_full_suite_properties_at_scale(cuda):
-    """BASELINE config sizes (50000 x 32x32x3): deterministic passes are idempotent-stable / order-independent."""
+    """BASELINE config sizes (50000 x 32x32x3), every deterministic type: per-image independence at full size in both modes,
+    the exact mode bit-identical to the oracle on 1000 images, the fast (default, benchmarked) mode within 1 LSB of it."""
     C = _C()
     n = 50000
     x = torch.randint(0, 256, (n, 32, 32, 3), dtype=torch.uint8, device="cuda", generator=torch.Generator("cuda").manual_seed(3))
-    for name, sev in (("pixelate", 5), ("jpeg_compression", 5), ("contrast", 5), ("defocus_blur", 1), ("zoom_blur", 5)):
-        a = C.corrupt(x, name, sev)
-        perm = torch.randperm(n, device="cuda", generator=torch.Generator("cuda").manual_seed(4))
-        b = C.corrupt(x[perm].contiguous(), name, sev)
-        assert torch.equal(a[perm], b), name                     # per-image independence at full size
-        head = CC.corrupt(name, sev, x[:16].cpu().numpy())
-        assert np.array_equal(a[:16].cpu().numpy(), head), name  # and the first images match the oracle
-    # pixelate is idempotent only approximately; contrast c<1 shrinks the per-image range
+    perm = torch.randperm(n, device="cuda", generator=torch.Generator("cuda").manual_seed(4))
+    xp = x[perm].contiguous()
+    head_x = x[:1000].cpu().numpy()
+    for name, sev in (("pixelate", 5), ("jpeg_compression", 5), ("contrast", 5), ("defocus_blur", 1), ("zoom_blur", 5),
+                      ("brightness", 3), ("defocus_blur", 5), ("zoom_blur", 2)):
+        want = CC.corrupt(name, sev, head_x)
+        for mode in ("exact", "fast"):
+            a = C.corrupt(x, name, sev, mode=mode)
+            b = C.corrupt(xp, name, sev, mode=mode)
+            assert torch.equal(a[perm], b), (name, mode)               # per-image independence at full size
+            got = a[:1000].cpu().numpy()
+            if mode == "exact":
+                assert np.array_equal(got, want), name                 # 1000 images bit-identical to the oracle
+            else:
+                d = np.abs(got.astype(np.int32) - want.astype(np.int32))
+                assert d.max() <= 1 and (d > 0).mean() < 0.06, (name, int(d.max()), float((d > 0).mean()))
+    # contrast c<1 shrinks the per-image range
     a = C.corrupt(x[:1000], "contrast", 5).float()
     assert bool((a.amax((1, 2)) - a.amin((1, 2)) <= 0.15 * 255 + 1.01).all())   # per channel
 
@@ -126,7 +136,7 @@ def test_write_and_read_back_cifar_c_layout(cuda, tmp_path):
     # CIFARC_Dataset slices blocks of 10000: write a 10000-image set made of repeats
     xs = np.tile(x, (1000, 1, 1, 1))
     labels = np.arange(10000) % 10
-    C.write_cifar_c(str(tmp_path), xs, labels, corruptions=["contrast", "pixelate"])
+    C.write_cifar_c(str(tmp_path), xs, labels, corruptions=["contrast", "pixelate"], mode="exact")
     for sev in (1, 5):
         ds = CIFARC_Dataset(str(tmp_path), "contrast", sev)
         assert len(ds) == 10000
@@ -209,7 +219,7 @@ def test_brightness_all_colours(cuda, sev):
     C = _C()
     idx = np.arange(0, 1 << 24, 2, dtype=np.int64) + (np.arange(1 << 23) >> 11 & 1)   # alternate parity so both halves occur
     x = np.stack([idx & 255, (idx >> 8) & 255, (idx >> 16) & 255], -1).astype(np.uint8).reshape(-1, 32, 32, 3)
-    got = C.corrupt(torch.from_numpy(x).cuda(), "brightness", sev).cpu().numpy()
+    got = C.corrupt(torch.from_numpy(x).cuda(), "brightness", sev, mode="exact").cpu().numpy()
     want = np.concatenate([CC.brightness(x[i:i + 1024], CC.PARAMS["brightness"][sev - 1]) for i in range(0, len(x), 1024)])
     assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
 

@@ -14,9 +14,12 @@ from oracle import cifar_c as CC
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
-# (type, upper bound on the fraction of differing bytes).  The bounds are ~3x the fractions measured on B200.
+# (type, upper bound on the fraction of differing bytes).  The bounds are ~2-3x the fractions measured on B200.  brightness:
+# x*(M + 255c)/M is an exact integer for up to 6 % of the bytes (c = 0.2: 255c = 51 = 3*17), where the exact mode's float64
+# HSV round trip lands a few 1e-14 above or below the integer at random; the fast mode always takes the integer.
 FAST_TYPES = {
-    "contrast": 5e-3, "brightness": 1e-2, "frost": 2e-2, "fog": 5e-3,
+    "contrast": 5e-3, "brightness": 6e-2, "frost": 3e-2, "fog": 5e-3, "zoom_blur": 1e-2, "motion_blur": 1e-2,
+    "elastic_transform": 1e-2, "snow": 2e-2,
 }
 
 
