@@ -296,11 +296,15 @@ def resample(x: torch.Tensor, resized_wh, filt: int, crop_box=None, crop_xy=None
     bx, by, bw, bh = crop_box if crop_box is not None else (0, 0, w, h)
     rw, rh = resized_wh
     oh, ow = out_hw if out_hw is not None else (rh, rw)
-    out = torch.empty((n, oh, ow, c), dtype=torch.uint8, device=x.device) if out is None else out
+    out = _check_out(out, x, (n, oh, ow, c))
     ht = _resample_table(bw, rw, filt, x.device) if rw != bw else None
     vt = _resample_table(bh, rh, filt, x.device) if rh != bh else None
     cxy = None
     if crop_xy is not None:
+        if not isinstance(crop_xy, torch.Tensor):   # host origins can be validated for free (device ones are clamped in the kernel)
+            a = np.asarray(crop_xy, dtype=np.int64).reshape(n, 2)
+            if n and (a.min() < 0 or a[:, 0].max() > w - bw or a[:, 1].max() > h - bh):
+                raise ValueError("crop_xy places the crop box outside the image")
         cxy = crop_xy if isinstance(crop_xy, torch.Tensor) else torch.from_numpy(
             np.ascontiguousarray(np.asarray(crop_xy, dtype=np.int32).reshape(n, 2)))
         cxy = cxy.to(device=x.device, dtype=torch.int32).contiguous()

@@ -383,7 +383,8 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
                                         float(c2), seed, flags, st))
     elif name == "pixelate":
         sw, sh = int(w * p), int(h * p)
-        if sw == w or sh == h:     # Pillow skips a pass whose size does not change: use the general path
+        if sw == w or sh == h or h * w > 96 * 96:     # Pillow skips a pass whose size does not change; big images do not fit
+            # the fused chain's shared-memory planes: the general path (two resample launches, identical results)
             small = B.resample(x, (sw, sh), L.FILTER_BOX)
             B.resample(small, (w, h), L.FILTER_BOX, out=out)
         else:

@@ -1240,6 +1240,23 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
       K[p.dy[i] + 2][p.dx[i] + 2] += p.w[i];
       R = std::max(R, std::max(abs((int)p.dy[i]), abs((int)p.dx[i])));
     }
+    if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32) {
+      // throughput form: the kernel restricted to 3x3 when what lies outside carries < 2e-3 LSB of weight
+      bool ok = true;
+      double outside = 0.0;
+      for (int a = 0; a < 5; ++a)
+        for (int b = 0; b < 5; ++b) {
+          if (K[a][b] != K[4 - a][b] || K[a][b] != K[a][4 - b] || K[a][b] < 0.0) ok = false;
+          if (a == 0 || a == 4 || b == 0 || b == 4) outside += K[a][b];
+        }
+      if (ok && outside * 255.0 < 2e-3) {
+        Sym3x3 k3;
+        const double tot = K[2][2] + 2.0 * (K[2][3] + K[3][2]) + 4.0 * K[3][3];   // renormalised: flat regions keep their value
+        k3.k00 = (float)(K[2][2] / tot); k3.k01 = (float)(K[2][3] / tot); k3.k10 = (float)(K[3][2] / tot); k3.k11 = (float)(K[3][3] / tot);
+        const int rc = launch_team_op<OpTDefocus>(in, out, n, make_shape(h, w, c, h, w), k3, (cudaStream_t)stream);
+        if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+      }
+    }
     bool sym = (w % 4 == 0) && R >= 1 && !(flags & IMGTX_CC_REPLAY_ALL);   // test knob: the literal kernel instead of the fixed-point sweep
     for (int a = 0; a < 5 && sym; ++a)
       for (int b = 0; b < 5; ++b)
@@ -1314,6 +1331,18 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
   const Shape shp = make_shape(h, w, c, h, w);
+  if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32 && lw <= 2) {
+    GlassTeamParams f;
+    memset(&f, 0, sizeof(f));
+    f.lw = lw; f.iters = iters; f.deltas = deltas_dev; f.seed = seed; f.w0 = p.w[0]; f.n = n;
+    const double inside = (p.w[0] + 2.0 * p.w[1]) * (p.w[0] + 2.0 * p.w[1]);   // the 3x3 part, renormalised to sum to 1
+    f.k.k00 = (float)(p.w[0] * p.w[0] / inside); f.k.k01 = f.k.k10 = (float)(p.w[0] * p.w[1] / inside);
+    f.k.k11 = (float)(p.w[1] * p.w[1] / inside);
+    if (lw == 0 || (1.0 - inside) * 255.0 < 5e-3) {   // what the 3x3 form drops
+      const int rc = launch_team_op<OpTGlass>(in, out, n, shp, f, (cudaStream_t)stream);
+      if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+    }
+  }
   if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       !(flags & IMGTX_CC_REPLAY_ALL)) {   // test knob: the literal kernel instead of the fixed-point sweeps
     GlassFastParams f;

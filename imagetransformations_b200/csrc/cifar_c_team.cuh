@@ -174,13 +174,23 @@ struct OpTFrost : NoTeamPrepare {
     const size_t tex_pitch = (size_t)p.tex_w * 3;
     const int row_words = (s.w * 3) >> 2;
     const FastDiv rd(row_words);
-    for (int i = lane; i < wpi; i += 32) {
-      int y, xw;
-      rd.divmod(i, y, xw);
-      const uintptr_t a = reinterpret_cast<uintptr_t>(tex + (size_t)y * tex_pitch + (size_t)xw * 4);
-      const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-      const uint32_t f = __funnelshift_r(__ldg(wp), __ldg(wp + 1), (uint32_t)(a & 3) * 8);
-      om[i] = mix4(im[i], f, cc);
+    // the texture words come from L2: eight independent fetches are issued before the first one is consumed
+    for (int i0 = lane; i0 < wpi; i0 += 256) {
+      uint32_t f[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = min(i0 + 32 * u, wpi - 1);
+        int y, xw;
+        rd.divmod(i, y, xw);
+        const uintptr_t a = reinterpret_cast<uintptr_t>(tex + (size_t)y * tex_pitch + (size_t)xw * 4);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        f[u] = __funnelshift_r(__ldg(wp), __ldg(wp + 1), (uint32_t)(a & 3) * 8);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = i0 + 32 * u;
+        if (i < wpi) om[i] = mix4(im[i], f[u], cc);
+      }
     }
   }
 };
@@ -243,8 +253,92 @@ struct OpTNoiseAlias {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
-// fog: per-image byte maximum, plasma map (drawn on chip by OpCcFogFast::plasma_warp, or injected float64 maps read from
-// HBM), then q = x*S + plasma*C in float32 with S = m/(m + c0), C = 255*c0*S (m = max/255).  |error| < 2e-4 LSB.
+// fog: per-image byte maximum, plasma map (diamond-square drawn on chip, or injected float64 maps read from HBM), then
+// q = x*S + plasma*C in float32 with S = m/(m + c0), C = 255*c0*S (m = max/255).  |error| < 2e-4 LSB.
+//
+// On-chip plasma for 2^LG x 2^LG maps, one warp, every level constant compile-time: the points of a step are dealt flat to
+// the lanes (point -> (a, b) by shifts), both diamond families are the same "average of the four axis neighbours at distance
+// s/2" with wrap-around, and all 2^(2 LG) - 1 uniforms of a lane's points come from five Philox calls made up front (16 bits
+// per uniform, planted in a float mantissa and folded into the noise FFMA).  Leaves the UN-normalised map and returns its
+// minimum and 1 / (max - min).
+constexpr int plasma_iters(int LG, int ls_from) {   // lane-iterations of levels ls_from .. 1
+  int t = 0;
+  for (int ls = ls_from; ls >= 1; --ls) { const int mm = 1 << (2 * (LG - ls)); t += (mm + 31) / 32 + (2 * mm + 31) / 32; }
+  return t;
+}
+
+// one level (step 2^LS) of the diamond-square recursion; ITN0 = index of this level's first 16-bit uniform in the lane's pool
+template <int LG, int LS, int ITN0, int POOL>
+__device__ __forceinline__ void plasma_level(float* map, const uint32_t (&pool)[POOL], float wib2, int lane) {
+  constexpr int N = 1 << LG, MASK = N - 1, s = 1 << LS, half = s >> 1, lm = LG - LS, m = 1 << lm, mm = m * m;
+  constexpr int T1 = (mm + 31) / 32, T2 = (2 * mm + 31) / 32;
+  // uniform in (-1, 1) from 16 bits h: (h + 1/2)/32768 - 1; with hf = 2^23 + h:  noise = wib2*u = hf*k1 + k0
+  const float k1 = wib2 * (1.0f / 32768.0f), k0 = wib2 * (0.5f / 32768.0f - 1.0f) - 8388608.0f * k1;
+#pragma unroll
+  for (int t = 0; t < T1; ++t) {
+    constexpr int dummy = 0; (void)dummy;
+    const int itn = ITN0 + t, p = t * 32 + lane;
+    const float hf = __uint_as_float(__byte_perm(pool[itn >> 1], 0x4B000000u, (itn & 1) ? 0x7432u : 0x7410u));
+    if (p < mm) {
+      const int a = p >> lm, b = p & (m - 1);
+      const int y0 = a << LS, x0 = b << LS, y1 = (y0 + s) & MASK, x1 = (x0 + s) & MASK;
+      const float acc = (map[y0 * N + x0] + map[y1 * N + x0]) + (map[y0 * N + x1] + map[y1 * N + x1]);
+      map[(y0 + half) * N + x0 + half] = __fmaf_rn(acc, 0.25f, __fmaf_rn(hf, k1, k0));
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int t = 0; t < T2; ++t) {
+    const int itn = ITN0 + T1 + t, p = t * 32 + lane;
+    const float hf = __uint_as_float(__byte_perm(pool[itn >> 1], 0x4B000000u, (itn & 1) ? 0x7432u : 0x7410u));
+    if (p < 2 * mm) {
+      const int fam = p >> (2 * lm), k = p & (mm - 1), a = k >> lm, b = k & (m - 1);
+      const int y = (a << LS) + (fam ? half : 0), x = (b << LS) + (fam ? 0 : half);
+      const float acc = (map[((y - half) & MASK) * N + x] + map[((y + half) & MASK) * N + x]) +
+                        (map[y * N + ((x - half) & MASK)] + map[y * N + ((x + half) & MASK)]);
+      map[y * N + x] = __fmaf_rn(acc, 0.25f, __fmaf_rn(hf, k1, k0));
+    }
+  }
+  __syncwarp();
+}
+
+template <int LG, int LS, int POOL>
+__device__ __forceinline__ void plasma_levels(float* map, const uint32_t (&pool)[POOL], float wib2, float idec2, int lane) {
+  plasma_level<LG, LS, plasma_iters(LG, LG) - plasma_iters(LG, LS), POOL>(map, pool, wib2, lane);
+  if constexpr (LS > 1) plasma_levels<LG, LS - 1, POOL>(map, pool, wib2 * idec2, idec2, lane);
+}
+
+template <int LG>
+__device__ __forceinline__ void plasma_flat(float* map, float decay, const Philox& rng, uint32_t img_lo, uint32_t img_hi,
+                                            float& mn_out, float& inv_span_out) {
+  constexpr int N = 1 << LG;
+  const int lane = threadIdx.x & 31;
+  constexpr int kCalls = (plasma_iters(LG, LG) + 7) / 8;
+  uint32_t pool[kCalls * 4];
+#pragma unroll
+  for (int c = 0; c < kCalls; ++c) {
+    const uint4 r = rng(img_lo, img_hi, 0x78u, (uint32_t)(c * 32 + lane));
+    pool[4 * c] = r.x; pool[4 * c + 1] = r.y; pool[4 * c + 2] = r.z; pool[4 * c + 3] = r.w;
+  }
+  if (lane == 0) map[0] = 0.0f;
+  __syncwarp();
+  plasma_levels<LG, LG, kCalls * 4>(map, pool, 10000.0f, __fdiv_rn(1.0f, decay * decay), lane);
+  float mn = 3.0e38f, mx = -3.0e38f;
+#pragma unroll 4
+  for (int i = lane; i < N * N / 4; i += 32) {
+    const float4 v = *reinterpret_cast<const float4*>(map + 4 * i);
+    mn = fminf(fminf(mn, v.x), fminf(v.y, fminf(v.z, v.w)));
+    mx = fmaxf(fmaxf(mx, v.x), fmaxf(v.y, fmaxf(v.z, v.w)));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  mn_out = mn;
+  inv_span_out = __fdiv_rn(1.0f, mx - mn);
+}
+
 struct OpTFog : NoTeamPrepare {
   using Params = CcFastParams;
   static constexpr int kTeamWarps = 1, kInBufs = 3, kOutBufs = 0, kMaxTeams = 8, kCtasPerSm = 2, kMinBlocks = 2;
@@ -261,21 +355,31 @@ struct OpTFog : NoTeamPrepare {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mxb = max(mxb, __shfl_xor_sync(0xffffffffu, mxb, o));
     const float mval = __fdiv_rn((float)mxb, 255.0f), c0 = (float)p.p0;
-    const float S = __fdiv_rn(mval, mval + c0), C = 255.0f * c0 * S;
+    const float S = __fdiv_rn(mval, mval + c0);
+    float C = 255.0f * c0 * S, bias = 0.0f;
     if (p.a) {
       const double* pl = reinterpret_cast<const double*>(p.a) + (size_t)img * hw;
       for (int i = lane; i < hw; i += 32) map[i] = (float)pl[i];
       __syncwarp();
     } else {
       const Philox rng(p.seed);
-      OpCcFogFast::plasma_warp(map, 31 - __clz(s.h), (float)p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32));
+      float mn, inv;
+      if (s.h == 32) {
+        plasma_flat<5>(map, (float)p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32), mn, inv);
+      } else {
+        OpCcFogFast::plasma_warp(map, 31 - __clz(s.h), (float)p.p1, rng, (uint32_t)img, (uint32_t)(img >> 32));
+        mn = 0.0f; inv = 1.0f;
+      }
+      // (map - mn) * inv * C  ==  map * C' + bias
+      C *= inv;
+      bias = -mn * C;
     }
     for (int t = lane; t < triples; t += 32) {   // 4 pixels = 3 words
       const uint32_t w0 = im[3 * t], w1 = im[3 * t + 1], w2 = im[3 * t + 2];
       const float4 pl = *reinterpret_cast<const float4*>(map + 4 * t);
-      const float a = pl.x * C, b = pl.y * C, c = pl.z * C, d = pl.w * C;
-      // no clip: 0 <= q <= 255*m*(1 + 2^-22) (x <= 255 m, plasma <= 1), so floor(q) always fits the byte
-      auto q = [S](uint32_t w, int k, float add) { return floor_bits(__fmaf_rn(byte_f(w, k), S, add)); };
+      const float a = __fmaf_rn(pl.x, C, bias), b = __fmaf_rn(pl.y, C, bias), c = __fmaf_rn(pl.z, C, bias), d = __fmaf_rn(pl.w, C, bias);
+      // no clip: 0 <= q <= 255*m*(1 + 2^-20) (x <= 255 m, plasma <= 1), so floor(q) always fits the byte
+      auto q = [S](uint32_t w, int k, float add) { return floor_bits(fmaxf(__fmaf_rn(byte_f(w, k), S, add), 0.0f)); };
       om[3 * t] = pack4(q(w0, 0, a), q(w0, 1, a), q(w0, 2, a), q(w0, 3, b));
       om[3 * t + 1] = pack4(q(w1, 0, b), q(w1, 1, b), q(w1, 2, c), q(w1, 3, c));
       om[3 * t + 2] = pack4(q(w2, 0, c), q(w2, 1, d), q(w2, 2, d), q(w2, 3, d));

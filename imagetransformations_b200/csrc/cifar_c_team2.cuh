@@ -108,6 +108,182 @@ struct OpTMotion : NoTeamPrepare {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
+// Mirror-symmetric 3x3 stencil on a 32x32x3 image in float32: out = K00*c + K01*(l + r) + K10*(u + d) + K11*(four diagonals)
+// + 2^-12 (callers normalise the weights to sum to 1, so a flat region keeps its value instead of flooring one below it).
+// Serves defocus_blur (every CIFAR severity's disk kernel is 3x3 up to < 2e-3 LSB of weight) and glass_blur's Gaussians.
+// Work item = (word column c of 24, segment of 8 rows): the thread walks down its rows with a three-row register window;
+// per row it loads three words, forms the four left+right byte sums with packed 16-bit adds, and converts 4 centres +
+// 4 sums to float (byte / halfword planted in the mantissa of 2^23).  BORDER: 0 = REFLECT_101, 1 = replicate.
+struct Sym3x3 { float k00, k01, k10, k11; };
+
+template <int BORDER>
+__device__ __forceinline__ void sym3x3_load_row(const uint32_t* row, int c, float* C, float* H) {
+  const uint32_t wc = row[c], wl = row[max(c - 1, 0)], wr = row[min(c + 1, 23)];
+  uint32_t L = __funnelshift_r(wl, wc, 8), R = __funnelshift_r(wc, wr, 24);
+  if (c == 0) L = BORDER == 0 ? __byte_perm(wc, wr, 0x0543u) : __byte_perm(wc, wc, 0x0210u);      // bytes (3,4,5,0) / (0,1,2,0)
+  if (c == 23) R = BORDER == 0 ? __byte_perm(wl, wc, 0x4327u) : __byte_perm(wc, wc, 0x3213u);     // bytes (95,90,91,92) / (95,93,94,95)
+  const uint32_t he = (L & 0x00FF00FFu) + (R & 0x00FF00FFu), ho = ((L >> 8) & 0x00FF00FFu) + ((R >> 8) & 0x00FF00FFu);
+  H[0] = __uint_as_float(__byte_perm(he, 0x4B000000u, 0x7410u)) - 8388608.0f;
+  H[2] = __uint_as_float(__byte_perm(he, 0x4B000000u, 0x7432u)) - 8388608.0f;
+  H[1] = __uint_as_float(__byte_perm(ho, 0x4B000000u, 0x7410u)) - 8388608.0f;
+  H[3] = __uint_as_float(__byte_perm(ho, 0x4B000000u, 0x7432u)) - 8388608.0f;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) C[j] = byte_f(wc, j);
+}
+
+// rows [y0, y0 + 8) of word column c: src, dst = 32 x 24 words
+template <int BORDER>
+__device__ __forceinline__ void sym3x3_segment(const uint32_t* src, uint32_t* dst, int c, int y0, const Sym3x3& k) {
+  float C[3][4], H[3][4];
+  auto brow = [](int y) { return BORDER == 0 ? (y < 0 ? -y : (y > 31 ? 62 - y : y)) : min(max(y, 0), 31); };
+  sym3x3_load_row<BORDER>(src + brow(y0 - 1) * 24, c, C[0], H[0]);
+  sym3x3_load_row<BORDER>(src + brow(y0) * 24, c, C[1], H[1]);
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    // window slots rotate statically: row y0 + r - 1 in slot r % 3, y0 + r in (r + 1) % 3, y0 + r + 1 in (r + 2) % 3
+    const int a = r % 3, b = (r + 1) % 3, d = (r + 2) % 3;
+    sym3x3_load_row<BORDER>(src + brow(y0 + r + 1) * 24, c, C[d], H[d]);
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float v = __fmaf_rn(k.k11, H[a][j] + H[d][j], __fmaf_rn(k.k10, C[a][j] + C[d][j], __fmaf_rn(k.k01, H[b][j], __fmaf_rn(k.k00, C[b][j], 0.000244140625f))));
+      o[j] = floor_bits(v);
+    }
+    dst[(y0 + r) * 24 + c] = pack4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// defocus_blur (fast): K from the disk taps, REFLECT_101
+struct OpTDefocus : NoTeamPrepare {
+  using Params = Sym3x3;
+  static constexpr int kTeamWarps = 3, kInBufs = 3, kOutBufs = 2, kMaxTeams = 5, kCtasPerSm = 2, kMinBlocks = 2;
+  static size_t team_scratch(const Shape&, const Params&) { return 0; }
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t, const Shape&, const Params& p, uint8_t*, const uint8_t*,
+                             int tt, int) {
+    sym3x3_segment<0>(reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(dst), tt % 24, (tt / 24) * 8, p);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// glass_blur (32x32, fast): Gaussian -> 8 bits -> sequential local pixel swaps -> Gaussian.  A team is four warps: warps 0-2
+// (24 word columns x 4 row segments) run the two Gaussians as 3x3 float32 stencils (sigma <= 0.4: the taps at distance 2
+// carry < 4e-3 LSB and are dropped), warp 3 meanwhile runs the swap sweep of the same image on a u16 index map (the swaps
+// never look at pixel values: skew-2 wavefront, lane = row, 88 steps per iteration), then everybody applies the map as a
+// gather.  Every fourth image all four warps sweep (the maps of the team's next four images).  sigma < 0.125 (severity 1): both Gaussians are byte maps, composed into one 256-entry LUT with the float64 formula.
+struct GlassTeamParams {
+  Sym3x3 k;
+  int lw, iters;
+  double w0;                 // lw == 0: the single Gaussian weight (LUT build)
+  const int8_t* deltas;      // device (n, iters, 30, 30, 2) or nullptr (on-chip draws)
+  uint64_t seed;
+  int64_t n;                 // images in the batch (maps are made ahead: never past the end)
+};
+
+struct OpTGlass {
+  using Params = GlassTeamParams;
+  static constexpr int kTeamWarps = 4, kInBufs = 3, kOutBufs = 0, kMaxTeams = 4, kCtasPerSm = 2, kMinBlocks = 2;
+  static size_t cta_scratch(const Shape&, const Params&) { return 256; }
+  static size_t team_scratch(const Shape&, const Params&) { return 3072 + 3072 + 4 * 2048; }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    // lw == 0: x -> uint8(g*255) -> uint8(clip(g')*255) with g = (x/255*w0)*w0 evaluated as the exact mode does
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+      const double t = (double)i / 255.0;
+      const double a = (t * p.w0) * p.w0;
+      const int u = (int)(a * 255.0);
+      const double t2 = (double)u / 255.0;
+      double b = (t2 * p.w0) * p.w0;
+      b = b < 0.0 ? 0.0 : (b > 1.0 ? 1.0 : b);
+      cta[i] = (uint8_t)(int)(b * 255.0);
+    }
+  }
+  // the swap sweeps of image `img` on the index map m (one warp; skew-2 wavefront, lane = row, 88 steps per iteration)
+  __device__ static void sweep(uint16_t* m, int64_t img, const Params& p, int lane) {
+    for (int px = lane; px < 1024; px += 32) m[px] = (uint16_t)px;
+    __syncwarp();
+    const Philox rng(p.seed);
+    for (int it = 0; it < p.iters; ++it) {
+      const int h = 31 - lane;
+      if (p.deltas) {
+        for (int t = 0; t < 2 * 29 + 30; ++t) {
+          const int ci = t - 2 * lane;
+          if (lane < 30 && ci >= 0 && ci < 30) {
+            const int w = 31 - ci;
+            const int8_t* d = p.deltas + ((((img * p.iters + it) * 30 + lane) * 30 + ci) << 1);
+            const int a = h * 32 + w, b = (h + d[1]) * 32 + (w + d[0]);
+            const uint16_t ta = m[a], tb = m[b];
+            m[a] = tb; m[b] = ta;
+          }
+          __syncwarp();
+        }
+      } else {
+        // on-chip draws: one bit per swap and axis, consumed from two 64-bit shift registers (one Philox call per row)
+        uint64_t BX = 0, BY = 0;
+        if (lane < 30) {
+          const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)lane);
+          BX = (uint64_t)r.x | ((uint64_t)r.z << 32); BY = (uint64_t)r.y | ((uint64_t)r.w << 32);
+        }
+        uint16_t* ma = m + h * 32 + 31;
+        const uint32_t first = 2u * (uint32_t)lane, cnt = lane < 30 ? 30u : 0u;
+        for (int t = 0; t < 2 * 29 + 30; ++t) {
+          if ((uint32_t)t - first < cnt) {
+            uint16_t* mb = ma - ((int)((uint32_t)BY & 1u) * 32 + (int)((uint32_t)BX & 1u));
+            BX >>= 1; BY >>= 1;
+            const uint16_t ta = *ma, tb = *mb;
+            *ma = tb; *mb = ta;
+            --ma;
+          }
+          __syncwarp();
+        }
+      }
+    }
+  }
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
+                             const uint8_t* cta, int tt, int team) {
+    uint8_t* B1 = scr;
+    uint8_t* B2 = scr + 3072;
+    uint16_t* maps = reinterpret_cast<uint16_t*>(scr + 6144);    // four index maps: this image and the team's next three
+    const int lane = tt & 31, wq = tt >> 5;
+    // the sweep is a latency chain that keeps one warp busy, so every fourth image of the team all four warps sweep at once:
+    // warp q makes the map of the team's image it + q (the maps depend on the image index and the seed only)
+    const int64_t teams_per_cta = blockDim.x >> 7, stride = (int64_t)gridDim.x * teams_per_cta;
+    const int it = (int)((img - ((int64_t)blockIdx.x * teams_per_cta + team)) / stride);
+    if ((it & 3) == 0) {
+      if (img + wq * stride < p.n) sweep(maps + wq * 1024, img + wq * stride, p, lane);
+      team_sync<4>(team);
+    }
+    const uint16_t* m = maps + (it & 3) * 1024;
+    if (p.lw > 0) {
+      if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(B1), tt % 24, (tt / 24) * 8, p.k);
+      team_sync<4>(team);
+    }
+    // ---- apply the map: four pixels per thread ----
+    {
+      const uint8_t* from = p.lw > 0 ? B1 : src;
+      uint32_t* o = reinterpret_cast<uint32_t*>(B2);
+      for (int q = tt; q < 256; q += 128) {
+        uint32_t px[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t v = load_rgb(from, (int)m[4 * q + e] * 3);
+          px[e] = p.lw > 0 ? v : ((uint32_t)cta[v & 255u] | ((uint32_t)cta[(v >> 8) & 255u] << 8) | ((uint32_t)cta[v >> 16] << 16));
+        }
+        uint32_t a, b, c;
+        pack_rgb4(px[0], px[1], px[2], px[3], a, b, c);
+        o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
+      }
+    }
+    team_sync<4>(team);
+    if (p.lw > 0) {
+      if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(B2), reinterpret_cast<uint32_t*>(dst), tt % 24, (tt / 24) * 8, p.k);
+    } else {
+      const uint32_t* f = reinterpret_cast<const uint32_t*>(B2);
+      uint32_t* o = reinterpret_cast<uint32_t*>(dst);
+      for (int i = tt; i < 768; i += 128) o[i] = f[i];
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
 // snow (32x32): noise layer -> centre zoom -> threshold -> 8 bits -> line blur -> blend.  A team is two warps, lane = column,
 // warp = 16 rows.  The layer up to its 8-bit quantisation follows the exact mode operation for operation (a threshold
 // decision that flipped would move a byte by far more than 1 LSB); the blur and the blend are float32 FFMA on the 0..255

@@ -234,7 +234,13 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
   size_t gtmp_per_cta = 0;
   int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 8);
   if (scratch > (size_t)max_smem - 1024) {
-    // intermediate planes do not fit on chip: spill them to a stream-ordered global workspace
+    // intermediate planes do not fit on chip: spill them to a stream-ordered global workspace.  Operators without a spilled
+    // form (NoSpill) cannot run on images this large: refuse instead of launching with shared memory they would overrun.
+    if (Op::gtmp_bytes(s) == 0) {
+      set_error("image %dx%dx%d needs %zu bytes of shared memory per CTA (limit %d): this operator has no large-image form",
+                s.h, s.w, s.c, scratch, max_smem - 1024);
+      return IMGTX_ERR_INVALID_ARGUMENT;
+    }
     gtmp_per_cta = align_up(Op::gtmp_bytes(s), 256);
     scratch = Op::scratch_bytes_spilled(s) + extra_scratch;
     IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, gtmp_per_cta * grid, stream));
@@ -265,7 +271,9 @@ __device__ __forceinline__ uint32_t load_rgb(const uint8_t* base, int off) {
   // (LD.E + 64-bit address maths instead of LDS)
   const int mis = (int)(reinterpret_cast<uintptr_t>(base) & 3);
   const uint32_t* w = reinterpret_cast<const uint32_t*>(base - mis) + ((off + mis) >> 2);
-  return __funnelshift_r(w[0], w[1], (uint32_t)(off + mis) << 3) & 0x00FFFFFFu;
+  // the second word is read only when the three bytes straddle it (direct mode reads caller memory: never past its end)
+  const uint32_t hi = ((off + mis) & 3) > 1 ? w[1] : 0u;
+  return __funnelshift_r(w[0], hi, (uint32_t)(off + mis) << 3) & 0x00FFFFFFu;
 }
 // pack four 24-bit pixels into three words (little endian byte order r0 g0 b0 r1 ...)
 __device__ __forceinline__ void pack_rgb4(uint32_t p0, uint32_t p1, uint32_t p2, uint32_t p3, uint32_t& w0,

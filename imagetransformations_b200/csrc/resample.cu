@@ -73,7 +73,12 @@ struct OpResample {
       const uint8_t* im = src + (size_t)j * s.in_bytes;
       uint8_t* om = dst + (size_t)j * s.out_bytes;
       int ox = p.crop_x, oy = p.crop_y;
-      if (p.crop_xy) { ox = p.crop_xy[(img0 + j) * 2]; oy = p.crop_xy[(img0 + j) * 2 + 1]; }
+      if (p.crop_xy) {
+        // per-image origins live on the device and cannot be validated by the host without a sync: clamp the box into the
+        // image (Pillow would refuse such a box; here it can at least never read outside the image)
+        ox = min(max(p.crop_xy[(img0 + j) * 2], 0), s.w - p.crop_w);
+        oy = min(max(p.crop_xy[(img0 + j) * 2 + 1], 0), s.h - p.crop_h);
+      }
       // zero the canvas if the resized image does not cover it
       const bool covers = (p.place_x <= 0 && p.place_y <= 0 && p.place_x + p.rw >= s.ow && p.place_y + p.rh >= s.oh);
       if (!covers) {
@@ -441,6 +446,8 @@ extern "C" int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   IMGTX_CHECK_ARG((vtable_dev != nullptr) == (rh != crop_h), "vertical table must be given iff the height changes");
   if (n == 0) return IMGTX_OK;
   IMGTX_CHECK_ARG(in && out, "null image pointer");
+  IMGTX_CHECK_ARG(!htable_dev || htable_words >= 2, "horizontal table too short");
+  IMGTX_CHECK_ARG(!vtable_dev || vtable_words >= 2, "vertical table too short");
   ResampleParams p;
   memset(&p, 0, sizeof(p));
   p.htab = htable_dev; p.vtab = vtable_dev;

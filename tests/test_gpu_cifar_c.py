@@ -249,3 +249,24 @@ def test_fast_path_equals_literal_replay(cuda, name):
         fast = C.corrupt(x, name, sev, seed=11, mode="exact").cpu().numpy()
         lit = C.corrupt(x, name, sev, seed=11, mode="replay").cpu().numpy()
         assert np.array_equal(fast, lit), f"{name}/{sev}: {int((fast != lit).sum())} bytes differ"
+
+
+def test_pixelate_imagenette_shape_and_clean_error(cuda):
+    """224x224 pixelate goes through the general two-launch path (the fused chain's planes do not fit in shared memory);
+    calling the fused chain directly on such a shape must fail cleanly, not fault."""
+    from imagetransformations_b200 import _lib as L, batch as B
+    C = _C()
+    x = np.random.default_rng(3).integers(0, 256, (3, 224, 224, 3), dtype=np.uint8)
+    xd = torch.from_numpy(x).cuda()
+    got = C.corrupt(xd, "pixelate", 3, mode="exact").cpu().numpy()
+    assert np.array_equal(got, CC.pixelate(x, CC.PARAMS["pixelate"][2]))
+    sw = sh = int(224 * 0.85)
+    t = [B._resample_table(a, b, L.FILTER_BOX, xd.device) for a, b in ((224, sw), (224, sh), (sw, 224), (sh, 224))]
+    out = torch.empty_like(xd)
+    rc = L.load().imgtx_resize_chain_u8(xd.data_ptr(), out.data_ptr(), 3, 224, 224, 3, sw, sh, t[0].data_ptr(), t[0].numel(),
+                                        t[1].data_ptr(), t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(),
+                                        t[3].numel(), None)
+    torch.cuda.synchronize()
+    assert rc != 0 and b"large-image" in L.load().imgtx_last_error()
+    # the context is still healthy
+    assert torch.equal(C.corrupt(xd, "pixelate", 3, mode="exact").cpu(), torch.from_numpy(got))

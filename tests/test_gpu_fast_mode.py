@@ -16,10 +16,11 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 # (type, upper bound on the fraction of differing bytes).  The bounds are ~2-3x the fractions measured on B200.  brightness:
 # x*(M + 255c)/M is an exact integer for up to 6 % of the bytes (c = 0.2: 255c = 51 = 3*17), where the exact mode's float64
-# HSV round trip lands a few 1e-14 above or below the integer at random; the fast mode always takes the integer.
+# HSV round trip lands a few 1e-14 above or below the integer at random; the fast mode always takes the integer.  defocus
+# severity 4 (a 1/5 'plus' kernel) has the same ties on 20 % of the bytes.
 FAST_TYPES = {
     "contrast": 5e-3, "brightness": 6e-2, "frost": 3e-2, "fog": 5e-3, "zoom_blur": 1e-2, "motion_blur": 1e-2,
-    "elastic_transform": 1e-2, "snow": 2e-2,
+    "elastic_transform": 1e-2, "snow": 2e-2, "defocus_blur": 0.15, "glass_blur": 3e-2,
 }
 
 
