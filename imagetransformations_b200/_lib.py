@@ -51,6 +51,7 @@ _PROTOS = {
     "imgtx_version": [],
     "imgtx_last_error": [],
     "imgtx_device_info": [C.POINTER(C.c_int), C.POINTER(C.c_int)],
+    "imgtx_image_checksums_u8": [_vp, _i64, _i64, _vp, _vp],
     "imgtx_pointwise_u8": [_vp, _vp, _i64, _i64, _int, _f, _vp, _vp],
     "imgtx_geometry_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, C.POINTER(GeomRecord), _vp, _vp, _vp],
     "imgtx_enhance_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _f, _vp, _vp],
@@ -58,32 +59,33 @@ _PROTOS = {
     "imgtx_resample_table_host": [_int, _int, _int, _vp],
     "imgtx_resample_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _int, _int, _vp, _i64, _vp,
                           _i64, _int, _int, _int, _int, _vp],
-    "imgtx_box_pixelate_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _vp],
+    "imgtx_box_pixelate_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _vp, _vp],
     "imgtx_resize_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
     "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _int, _vp],
     "imgtx_pil_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_box_filter_h_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp],
     "imgtx_pil_transform_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _vp, _vp, _vp],
+    "imgtx_adaptive_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp],
     "imgtx_perspective_tensor_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _f, _vp],
     "imgtx_gaussian_blur_f32": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_noise_injected_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, C.c_double, _vp],
     "imgtx_noise_philox_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_uint64, _vp],
     "imgtx_cc_pointwise_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, C.c_double, _vp, _vp, C.c_uint64, _int,
-                              _int, _int, _int, _vp],
+                              _int, _int, _int, _vp, _vp],
     "imgtx_cc_noise_table_words": [_int, C.c_double],
     "imgtx_cc_noise_table_host": [_int, C.c_double, _vp, _i64],
-    "imgtx_cc_noise_onchip_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _i64, C.c_uint64, _vp],
-    "imgtx_cc_defocus_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _int, _vp],
+    "imgtx_cc_noise_onchip_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _i64, C.c_uint64, _int, _vp, _vp],
+    "imgtx_cc_defocus_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _int, _vp, _vp],
     "imgtx_cc_csr_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _vp],
-    "imgtx_cc_csr_ell_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _int, _int, _vp],
-    "imgtx_cc_glass_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _int, _vp, C.c_uint64, _int, _vp],
-    "imgtx_cc_motion_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, C.c_double, C.c_double, C.c_uint64, _int, _vp],
+    "imgtx_cc_csr_ell_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _int, _int, _int, _vp, _vp],
+    "imgtx_cc_glass_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _int, _vp, C.c_uint64, _int, _vp, _vp],
+    "imgtx_cc_motion_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, C.c_double, C.c_double, C.c_uint64, _int, _vp, _vp],
     "imgtx_cc_snow_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _f, _f, _vp, _vp, _int, _vp, _vp, _vp, C.c_double,
-                         C.c_double, C.c_double, C.c_double, C.c_uint64, _int, _vp],
+                         C.c_double, C.c_double, C.c_double, C.c_uint64, _int, _vp, _vp],
     "imgtx_cc_elastic_u8": [_vp, _vp, _i64, _int, _int, _int, C.c_double, _vp, _int, _vp, _vp, _vp, C.c_double,
-                            C.c_uint64, _int, _vp],
-    "imgtx_cc_jpeg_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _vp],
+                            C.c_uint64, _int, _vp, _vp],
+    "imgtx_cc_jpeg_u8": [_vp, _vp, _i64, _int, _int, _int, _vp, _int, _vp, _vp],
     "imgtx_to_tensor_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_to_uint8_f32": [_vp, _vp, _i64, _int, _int, _int, _vp, _vp, _int, _vp],
     "imgtx_augmix_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],

@@ -493,9 +493,10 @@ def shannon_entropy(x: torch.Tensor, mean=None, std=None, return_counts: bool = 
 
 
 def sign_step(x: torch.Tensor, g: torch.Tensor, eps, direction: float = 1.0, lo=None, hi=None,
-              return_pert: bool = False):
+              return_pert: bool = False, out: Optional[torch.Tensor] = None):
     """x + direction*eps*sign(g) (optionally clamped). eps scalar -> tensor like x; eps sequence of E
-    values -> (E, *x.shape) from ONE pass over x and g."""
+    values -> (E, *x.shape) from ONE pass over x and g.  `out` (scalar eps only) may be x itself: every element is read
+    before it is written, by the same thread."""
     x = _check_f32(x)
     g = _check_f32(g)
     if x.shape != g.shape:
@@ -510,7 +511,12 @@ def sign_step(x: torch.Tensor, g: torch.Tensor, eps, direction: float = 1.0, lo=
     many = not np.isscalar(eps)
     eps_l = [float(e) for e in (eps if many else [eps])]
     E = len(eps_l)
-    out = torch.empty((E,) + tuple(shp), dtype=torch.float32, device=x.device)
+    if out is not None:
+        if many or not (out.is_cuda and out.dtype == torch.float32 and out.shape == x.shape and out.is_contiguous()):
+            raise ValueError("out must be a contiguous float32 CUDA tensor shaped like x (scalar eps only)")
+        out = out.view((1,) + tuple(shp))
+    else:
+        out = torch.empty((E,) + tuple(shp), dtype=torch.float32, device=x.device)
     pert = torch.empty_like(out) if return_pert else None
     mode, lk, lp, hk, hp = _bounds(lo, hi, c)
     ek, ep = _fptr(eps_l)

@@ -281,19 +281,21 @@ def _ptr(t):
 
 def corrupt(x: torch.Tensor, name: str, severity: int, draws: Optional[dict] = None, seed: int = 0, table: str = "cifar",
             out: Optional[torch.Tensor] = None, frost_bank: Optional[torch.Tensor] = None,
-            mode: Optional[str] = None) -> torch.Tensor:
+            mode: Optional[str] = None, metrics: Optional[torch.Tensor] = None) -> torch.Tensor:
     """x: (n,h,w,3) uint8 CUDA -> same shape.  `draws` injects the random inputs (DRAW_KEYS[name]); None = on-chip RNG.
 
     mode: "exact"  the float64-specified arithmetic of oracle/cifar_c.py, bit for bit (default when draws are injected);
           "fast"   float32 / fixed-point throughput kernels, every byte within 1 LSB of "exact" on the same draws
                    (default when the draws are made on chip: no bit-wise oracle exists for those);
-          "replay" (tests) "exact" with every element forced through its literal replay."""
+          "replay" (tests) "exact" with every element forced through its literal replay.
+    metrics: optional (n, 2) int32/uint32 CUDA tensor receiving the pass's per-image metric (byte sum, position-weighted sum
+          mod 2^32) — written by the kernel's epilogue, ready to be all-gathered (shard.py)."""
     x = B._check_u8(x)
     with torch.cuda.device_of(x):
-        return _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode)
+        return _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metrics)
 
 
-def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
+def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metrics=None):
     n, h, w, c = x.shape
     if not 1 <= severity <= 5:
         raise ValueError("severity must be 1..5")
@@ -308,8 +310,17 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
     st = B._stream()
     seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     out = B._check_out(out, x)
+    mp = None
+    if metrics is not None:
+        if not (metrics.is_cuda and metrics.dtype in (torch.int32, torch.uint32) and tuple(metrics.shape) == (n, 2) and
+                metrics.is_contiguous()):
+            raise ValueError("metrics must be a contiguous (n, 2) int32 CUDA tensor")
+        mp = metrics.data_ptr()
     if table == "reference":
-        return _corrupt_reference(x, name, severity, d, seed, out)
+        res = _corrupt_reference(x, name, severity, d, seed, out)
+        if mp is not None:
+            L.check(lib.imgtx_image_checksums_u8(res.data_ptr(), n, h * w * c, mp, st))
+        return res
     if table != "cifar":
         raise ValueError("table must be 'cifar' or 'reference'")
     p = CIFAR_TABLE[name][severity - 1]
@@ -317,7 +328,7 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
 
     def point(kind, p0, p1=0.0, a=None, b=None, tex=(0, 0, 0)):
         L.check(lib.imgtx_cc_pointwise_u8(xp, op, n, h, w, c, kind, float(p0), float(p1), _ptr(a), _ptr(b), seed, tex[0],
-                                          tex[1], tex[2], flags, st))
+                                          tex[1], tex[2], flags, mp, st))
 
     # NB every device staging tensor is bound to a local name until the call returns: a temporary would hand its block
     # back to the caching allocator before the next one is staged
@@ -325,7 +336,7 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
         kind = L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SHOT
         tab = noise_alias_table(kind, float(p), dev)
         if tab is not None:
-            L.check(lib.imgtx_cc_noise_onchip_u8(xp, op, n, h, w, c, kind, tab.data_ptr(), tab.numel(), seed, st))
+            L.check(lib.imgtx_cc_noise_onchip_u8(xp, op, n, h, w, c, kind, tab.data_ptr(), tab.numel(), seed, flags, mp, st))
             return out
     if name in ("gaussian_noise", "speckle_noise"):
         point(L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SPECKLE, p, a=_dev(d.get("noise"), torch.float64, dev))
@@ -347,21 +358,21 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
             point(L.CC_FROST, p[0], p[1], a=bank, tex=(bank.shape[0], bank.shape[1], bank.shape[2]))
     elif name == "defocus_blur":
         dydx, wts = disk_taps(p[0], p[1])
-        L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, flags, st))
+        L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, flags, mp, st))
     elif name == "zoom_blur":
         ip, idx, wt, max_row = zoom_operator(h, w, severity, dev)
         L.check(lib.imgtx_cc_csr_ell_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(),
-                                        max_row, flags, st))
+                                        max_row, flags, mp, st))
     elif name == "glass_blur":
         wts = gaussian_taps(p[0], 4.0)
         deltas = _dev(d.get("deltas"), torch.int8, dev)
         if deltas is not None and deltas.numel() != n * p[2] * (h - 2) * (w - 2) * 2:
             raise ValueError("deltas must have shape (n, iters, h-2, w-2, 2)")
-        L.check(lib.imgtx_cc_glass_u8(xp, op, n, h, w, c, wts.ctypes.data, len(wts) - 1, p[2], _ptr(deltas), seed, flags, st))
+        L.check(lib.imgtx_cc_glass_u8(xp, op, n, h, w, c, wts.ctypes.data, len(wts) - 1, p[2], _ptr(deltas), seed, flags, mp, st))
     elif name == "motion_blur":
         k = motion_kernel(p[0], p[1])
         off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
-        L.check(lib.imgtx_cc_motion_u8(xp, op, n, h, w, c, len(k), k.ctypes.data, _ptr(off), -45.0, 45.0, seed, flags, st))
+        L.check(lib.imgtx_cc_motion_u8(xp, op, n, h, w, c, len(k), k.ctypes.data, _ptr(off), -45.0, 45.0, seed, flags, mp, st))
     elif name == "snow":
         k = motion_kernel(p[4], p[5])
         off = _dev(motion_offsets(len(k), d["angles"]), torch.int32, dev) if "angles" in d else None
@@ -369,7 +380,7 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
         layer = _dev(d.get("layer"), torch.float64, dev)
         L.check(lib.imgtx_cc_snow_u8(xp, op, n, h, w, c, float(np.float32(p[3])), float(np.float32(p[6])),
                                      float(np.float32(1 - p[6])), zi.ctypes.data, zt.ctypes.data, len(k), k.ctypes.data,
-                                     _ptr(off), _ptr(layer), float(p[0]), float(p[1]), -135.0, -45.0, seed, flags, st))
+                                     _ptr(off), _ptr(layer), float(p[0]), float(p[1]), -135.0, -45.0, seed, flags, mp, st))
     elif name == "elastic_transform":
         alpha, sigma, c2 = p[0] * h, p[1] * h, p[2] * h
         if sigma > 1e-15:
@@ -380,23 +391,27 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode):
         M = _dev(affine_from_jitter(d["jitter"], h), torch.float64, dev) if "jitter" in d else None
         ux, uy = _dev(d.get("ux"), torch.float64, dev), _dev(d.get("uy"), torch.float64, dev)
         L.check(lib.imgtx_cc_elastic_u8(xp, op, n, h, w, c, float(alpha), wts.ctypes.data, lw, _ptr(M), _ptr(ux), _ptr(uy),
-                                        float(c2), seed, flags, st))
+                                        float(c2), seed, flags, mp, st))
     elif name == "pixelate":
         sw, sh = int(w * p), int(h * p)
         if sw == w or sh == h or h * w > 96 * 96:     # Pillow skips a pass whose size does not change; big images do not fit
             # the fused chain's shared-memory planes: the general path (two resample launches, identical results)
             small = B.resample(x, (sw, sh), L.FILTER_BOX)
             B.resample(small, (w, h), L.FILTER_BOX, out=out)
+            if mp is not None:
+                L.check(lib.imgtx_image_checksums_u8(op, n, h * w * c, mp, st))
         else:
-            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, flags, st)   # small images: gather form; 1 = not applicable
+            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, flags, mp, st)   # small images: gather form; 1 = not applicable
             if rc == 1:
                 t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
                 rc = lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
                                                t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(), t[3].numel(), st)
+                if rc == 0 and mp is not None:
+                    rc = lib.imgtx_image_checksums_u8(op, n, h * w * c, mp, st)
             L.check(rc)
     elif name == "jpeg_compression":
         qt = jpeg_qtables(p)
-        L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, flags, st))
+        L.check(lib.imgtx_cc_jpeg_u8(xp, op, n, h, w, c, qt.ctypes.data, flags, mp, st))
     else:
         raise KeyError(name)
     return out

@@ -300,9 +300,9 @@ struct OpCcPoint : NoSpill {
 
 using namespace imgtx;
 
-extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0,
+static int impl_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0,
                                      double p1, const void* draws_a_dev, const void* draws_b_dev, uint64_t seed,
-                                     int tex_n, int tex_h, int tex_w, int flags, imgtx_stream_t stream) {
+                                     int tex_n, int tex_h, int tex_w, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(kind >= IMGTX_CC_GAUSSIAN && kind <= IMGTX_CC_FROST, "unknown corruption kind %d", kind);
   if (kind == IMGTX_CC_IMPULSE) IMGTX_CHECK_ARG((draws_a_dev == nullptr) == (draws_b_dev == nullptr), "impulse needs both draw arrays or none");
@@ -329,20 +329,20 @@ extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n,
       int rc = IMGTX_ERR_UNSUPPORTED;
       cudaStream_t st = (cudaStream_t)stream;
       if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && p0 >= 0.0 && p0 <= 1.0 && (int64_t)h * w * 255 < (1ll << 24))
-        rc = launch_team_op<OpTContrast>(in, out, n, shp, f, st);
+        rc = launch_team_op<OpTContrast>(in, out, n, shp, f, st, metrics_dev);
       else if (kind == IMGTX_CC_BRIGHTNESS && (h * w) % 4 == 0 && p0 > -10 && p0 < 10)
-        rc = launch_team_op<OpTBrightness>(in, out, n, shp, f, st);
+        rc = launch_team_op<OpTBrightness>(in, out, n, shp, f, st, metrics_dev);
       else if (kind == IMGTX_CC_IMPULSE && !draws_a_dev && p0 > 0.0 && p0 < 1.0) {
         f.p1 = 1.0 / log2(1.0 - p0);
-        rc = launch_team_op<OpTImpulse>(in, out, n, shp, f, st);
+        rc = launch_team_op<OpTImpulse>(in, out, n, shp, f, st, metrics_dev);
         f.p1 = p1;
       } else if (kind == IMGTX_CC_FROST && w % 4 == 0 && p0 >= 0 && p1 >= 0 && p0 < 1.99 && p1 < 1.99 &&
                  ((reinterpret_cast<uintptr_t>(draws_a_dev) & 3u) == 0))
-        rc = launch_team_op<OpTFrost>(in, out, n, shp, f, st);
+        rc = launch_team_op<OpTFrost>(in, out, n, shp, f, st, metrics_dev);
       else if (kind == IMGTX_CC_FOG && (h * w) % 4 == 0 && p0 > 0 && p0 < 100 &&
                (draws_a_dev || (h == w && (h & (h - 1)) == 0 && h >= 4 && h <= 64 && p1 > 0)))
-        rc = launch_team_op<OpTFog>(in, out, n, shp, f, st);
-      if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+        rc = launch_team_op<OpTFog>(in, out, n, shp, f, st, metrics_dev);
+      if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
     }
     if (kind == IMGTX_CC_IMPULSE && !draws_a_dev) return launch_image_op<OpCcImpulseFast>(in, out, n, shp, f, (cudaStream_t)stream);
     if (kind == IMGTX_CC_CONTRAST && (h * w) % 4 == 0 && (int64_t)h * w * 255 < (1ll << 31))
@@ -493,9 +493,9 @@ extern "C" int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_hos
   return IMGTX_OK;
 }
 
-extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
+static int impl_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
                                         const int32_t* table_dev, int64_t table_words, uint64_t seed,
-                                        imgtx_stream_t stream) {
+                                        uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   // (on-chip draws only: this entry point IS a throughput form; it runs on the team pipeline when the table fits beside it)
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(kind == IMGTX_CC_GAUSSIAN || kind == IMGTX_CC_SHOT, "alias-table noise is gaussian or shot");
@@ -509,13 +509,34 @@ extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t
   memset(&f, 0, sizeof(f));
   f.kind = kind; f.b = table_dev; f.seed = seed; f.table_words = (int)table_words;
   {
-    const int rc = tbytes > 48 * 1024 ? launch_team_op<OpTNoiseAlias<2>>(in, out, n, shp, f, (cudaStream_t)stream)
-                                      : launch_team_op<OpTNoiseAlias<1>>(in, out, n, shp, f, (cudaStream_t)stream);
-    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+    const int rc = tbytes > 48 * 1024 ? launch_team_op<OpTNoiseAlias<2>>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev)
+                                      : launch_team_op<OpTNoiseAlias<1>>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+    if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
   }
   // small table: default occupancy; large table (shot): one CTA per SM, the rest of shared memory stages images
   int target = 0;
   if (tbytes > 16 * 1024) target = max_smem_optin() - 1024;   // big table (shot noise): one CTA per SM anyway, give it every byte for images
   else target = 96 * 1024;   // small table (gaussian): larger groups measured 5 % faster than the default 56 KB target
   return launch_image_op<OpCcNoiseAlias>(in, out, n, shp, f, (cudaStream_t)stream, tbytes, target);
+}
+
+extern "C" int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0,
+                                     double p1, const void* draws_a_dev, const void* draws_b_dev, uint64_t seed,
+                                     int tex_n, int tex_h, int tex_w, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_pointwise_u8(in, out, n, h, w, c, kind, p0, p1, draws_a_dev, draws_b_dev, seed, tex_n, tex_h, tex_w, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
+                                        const int32_t* table_dev, int64_t table_words, uint64_t seed,
+                                        int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  (void)flags;
+  int rc = impl_cc_noise_onchip_u8(in, out, n, h, w, c, kind, table_dev, table_words, seed, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
 }

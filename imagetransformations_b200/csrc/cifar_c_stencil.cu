@@ -1218,8 +1218,8 @@ int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const in
               const float* weights, int max_row_taps, cudaStream_t stream);   // cifar_c_zoom.cu
 }
 
-extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
-                                   const int32_t* dydx_host, const double* weights_host, int flags, imgtx_stream_t stream) {
+static int impl_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
+                                   const int32_t* dydx_host, const double* weights_host, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 4 && w > 4 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(ntaps >= 1 && ntaps <= kMaxTaps && dydx_host && weights_host, "1..%d taps", kMaxTaps);
   DefocusParams p;
@@ -1253,8 +1253,8 @@ extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, i
         Sym3x3 k3;
         const double tot = K[2][2] + 2.0 * (K[2][3] + K[3][2]) + 4.0 * K[3][3];   // renormalised: flat regions keep their value
         k3.k00 = (float)(K[2][2] / tot); k3.k01 = (float)(K[2][3] / tot); k3.k10 = (float)(K[3][2] / tot); k3.k11 = (float)(K[3][3] / tot);
-        const int rc = launch_team_op<OpTDefocus>(in, out, n, make_shape(h, w, c, h, w), k3, (cudaStream_t)stream);
-        if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+        const int rc = launch_team_op<OpTDefocus>(in, out, n, make_shape(h, w, c, h, w), k3, (cudaStream_t)stream, metrics_dev);
+        if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
       }
     }
     bool sym = (w % 4 == 0) && R >= 1 && !(flags & IMGTX_CC_REPLAY_ALL);   // test knob: the literal kernel instead of the fixed-point sweep
@@ -1298,9 +1298,9 @@ extern "C" int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h
                                   (int)extra + 64 * 1024);
 }
 
-extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+static int impl_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                                    const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
-                                   int flags, imgtx_stream_t stream) {
+                                   int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0 && max_row_taps > 0, "missing operator");
   if (flags & IMGTX_CC_FAST) {
@@ -1322,8 +1322,8 @@ extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   return launch_image_op<OpCcCsrEll>(in, out, n, shp, p, (cudaStream_t)stream, 0, (int)need(G));
 }
 
-extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
-                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, imgtx_stream_t stream) {
+static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
+                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 2 && w > 2 && h <= 34 && c == 3 && n >= 0, "glass_blur takes (n,h<=34,w,3) images");
   IMGTX_CHECK_ARG(lw >= 0 && lw <= 3 && weights_host && iters >= 0, "bad Gaussian");
   GlassParams p;
@@ -1339,8 +1339,8 @@ extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int
     f.k.k00 = (float)(p.w[0] * p.w[0] / inside); f.k.k01 = f.k.k10 = (float)(p.w[0] * p.w[1] / inside);
     f.k.k11 = (float)(p.w[1] * p.w[1] / inside);
     if (lw == 0 || (1.0 - inside) * 255.0 < 5e-3) {   // what the 3x3 form drops
-      const int rc = launch_team_op<OpTGlass>(in, out, n, shp, f, (cudaStream_t)stream);
-      if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+      const int rc = launch_team_op<OpTGlass>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+      if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
     }
   }
   if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
@@ -1401,9 +1401,9 @@ static void fill_motion_fast(MotionFastParams& f, const MotionParams& m, double 
   f.offsets = m.offsets; f.lo = (float)lo; f.hi = (float)hi; f.seed = m.seed;
 }
 
-extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
+static int impl_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
                                   const float* k_host, const int32_t* offsets_dev, double angle_lo, double angle_hi,
-                                  uint64_t seed, int flags, imgtx_stream_t stream) {
+                                  uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   MotionParams p;
   int rc = fill_motion(p, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags);
@@ -1413,8 +1413,8 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
     MotionFastParams f;
     memset(&f, 0, sizeof(f));
     fill_motion_fast(f, p, angle_lo, angle_hi);
-    const int rc2 = launch_team_op<OpTMotion>(in, out, n, shp, f, (cudaStream_t)stream);
-    if (rc2 != IMGTX_ERR_UNSUPPORTED) return rc2;
+    const int rc2 = launch_team_op<OpTMotion>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+    if (rc2 != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc2; }
   }
   shp.aux = p.n_eff;
   if (w % 4 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
@@ -1425,11 +1425,11 @@ extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, in
   return launch_image_op<OpCcMotion>(in, out, n, shp, p, (cudaStream_t)stream);
 }
 
-extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
+static int impl_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
                                 float one_minus_c6, const int32_t* zoom_idx_host /* y0,y1 (h each), x0,x1 (w each) */,
                                 const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
                                 const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
-                                double angle_lo, double angle_hi, uint64_t seed, int flags, imgtx_stream_t stream) {
+                                double angle_lo, double angle_hi, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && h <= kSnowMax && w <= kSnowMax && c == 3 && n >= 0, "snow takes (n,h<=64,w<=64,3) images");
   IMGTX_CHECK_ARG(zoom_idx_host && zoom_t_host, "missing zoom tables");
   SnowParams p;
@@ -1455,8 +1455,8 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
     for (int i = 0; i < 32; ++i) {
       f.y0[i] = p.y0[i]; f.y1[i] = p.y1[i]; f.x0[i] = p.x0[i]; f.x1[i] = p.x1[i]; f.ty[i] = p.ty[i]; f.tx[i] = p.tx[i];
     }
-    const int rc2 = launch_team_op<OpTSnow>(in, out, n, shp, f, (cudaStream_t)stream);
-    if (rc2 != IMGTX_ERR_UNSUPPORTED) return rc2;
+    const int rc2 = launch_team_op<OpTSnow>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+    if (rc2 != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc2; }
   }
   shp.aux = p.m.n_eff;
   if (w % 8 == 0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
@@ -1465,4 +1465,54 @@ extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
     return launch_image_op<OpCcSnowFast>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
   }
   return launch_image_op<OpCcSnow>(in, out, n, shp, p, (cudaStream_t)stream);
+}
+
+extern "C" int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
+                                   const int32_t* dydx_host, const double* weights_host, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_defocus_u8(in, out, n, h, w, c, ntaps, dydx_host, weights_host, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
+                                   const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
+                                   int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_csr_ell_u8(in, out, n, h, w, c, indptr_dev, indices_dev, weights_dev, nnz, max_row_taps, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
+                                 int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_glass_u8(in, out, n, h, w, c, weights_host, lw, iters, deltas_dev, seed, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width,
+                                  const float* k_host, const int32_t* offsets_dev, double angle_lo, double angle_hi,
+                                  uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_motion_u8(in, out, n, h, w, c, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
+                                float one_minus_c6, const int32_t* zoom_idx_host /* y0,y1 (h each), x0,x1 (w each) */,
+                                const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
+                                const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
+                                double angle_lo, double angle_hi, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_snow_u8(in, out, n, h, w, c, thresh, c6, one_minus_c6, zoom_idx_host, zoom_t_host, width, k_host, offsets_dev, layer_dev, loc, scale, angle_lo, angle_hi, seed, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
 }

@@ -1146,9 +1146,9 @@ struct OpCcJpeg : NoSpill {
 
 using namespace imgtx;
 
-extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
+static int impl_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
                                    const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
-                                   const double* uy_dev, double c2, uint64_t seed, int flags, imgtx_stream_t stream) {
+                                   const double* uy_dev, double c2, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 1 && w > 1 && h <= 64 && w <= 64 && c == 3 && n >= 0, "elastic_transform takes (n,h<=64,w<=64,3) images");
   IMGTX_CHECK_ARG(lw >= -1 && lw <= kMaxLw && (lw < 0 || weights_host), "Gaussian radius must be <= %d", kMaxLw);
   IMGTX_CHECK_ARG((ux_dev == nullptr) == (uy_dev == nullptr), "give both displacement fields or none");
@@ -1161,9 +1161,9 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
     ElasticFastParams f;
     f.e = p;
     f.alpha = (float)alpha;
-    const int rc = alpha == 0.0 ? launch_team_op<OpTElastic<true>>(in, out, n, shp, f, (cudaStream_t)stream)
-                                : launch_team_op<OpTElastic<false>>(in, out, n, shp, f, (cudaStream_t)stream);
-    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+    const int rc = alpha == 0.0 ? launch_team_op<OpTElastic<true>>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev)
+                                : launch_team_op<OpTElastic<false>>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+    if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
   }
   if (alpha == 0.0 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out))
     return launch_image_op<OpCcAffineWarp>(in, out, n, shp, p, (cudaStream_t)stream, 0, 96 * 1024);   // zero displacement: the warp alone (96 KB groups: 476 -> 438 us)
@@ -1175,8 +1175,8 @@ extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, i
   return launch_image_op<OpCcElastic>(in, out, n, shp, p, (cudaStream_t)stream, 0, 72 * 1024);
 }
 
-extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
-                                const int32_t* qtables_host /* 2 x 64, natural order */, int flags, imgtx_stream_t stream) {
+static int impl_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                const int32_t* qtables_host /* 2 x 64, natural order */, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   (void)flags;   // integer arithmetic: one form
   IMGTX_CHECK_ARG(h > 0 && w > 0 && (h % 16) == 0 && (w % 16) == 0 && c == 3 && n >= 0,
                   "jpeg_compression takes (n,h,w,3) images with h, w multiples of 16");
@@ -1190,4 +1190,23 @@ extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
       p.rq[t][i] = (uint32_t)((1ull << 32) / (uint64_t)(8 * v)) + 1u;
     }
   return launch_image_op<OpCcJpeg>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 80 * 1024);
+}
+
+extern "C" int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
+                                   const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
+                                   const double* uy_dev, double c2, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_elastic_u8(in, out, n, h, w, c, alpha, weights_host, lw, M_dev, ux_dev, uy_dev, c2, seed, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}
+
+extern "C" int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                const int32_t* qtables_host /* 2 x 64, natural order */, int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_cc_jpeg_u8(in, out, n, h, w, c, qtables_host, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
 }

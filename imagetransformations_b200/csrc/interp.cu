@@ -14,6 +14,7 @@
 // B200; none of the three is on the C2 headline path.
 #include "common.cuh"
 #include <math.h>
+#include <algorithm>
 #include <string.h>
 
 namespace imgtx {
@@ -94,6 +95,66 @@ pil_transform_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, 
         const double v = bicubic_poly(rows[0], rows[1], rows[2], rows[3], dy);
         o[ch] = v <= 0.0 ? 0 : (v >= 255.0 ? 255 : (uint8_t)(int)v);
       }
+    }
+  }
+}
+
+// Entropy-gated adaptive chain of fall_2025/Initial_Experiments.py:88-92 on PIL images, one launch:
+//   RandomHorizontalFlip -> RandomAffine (Pillow AFFINE, NEAREST: libImaging affine_fixed, 16.16 fixed point, fill 0) ->
+//   RandomPerspective (Pillow PERSPECTIVE, BILINEAR: float64 bilinear_filter8, fill 0).
+// The intermediate images are never materialised: a tap of the bilinear stage at integer pixel (x, y) of the affine output is
+// fetched THROUGH the affine's fixed-point inverse map and the flip.  Per-image record: imgtx_adaptive_t (flags bit 0 = flip,
+// bit 1 = affine fired, bit 2 = perspective fired; a[6] = the FIX'ed coefficients; persp[8]).
+__device__ __forceinline__ uint32_t adaptive_fetch(const uint8_t* im, const imgtx_adaptive_t& r, int h, int w, int c, int x, int y,
+                                                   int ch) {
+  int xin = x, yin = y;
+  if (r.flags & 2) {
+    xin = (r.a[2] + y * r.a[1] + x * r.a[0]) >> 16;
+    yin = (r.a[5] + y * r.a[4] + x * r.a[3]) >> 16;
+    if (xin < 0 || xin >= w || yin < 0 || yin >= h) return 0u;
+  }
+  if (r.flags & 1) xin = w - 1 - xin;
+  return im[((int64_t)yin * w + xin) * c + ch];
+}
+
+__global__ void __launch_bounds__(256)
+adaptive_chain_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int h, int w, int c,
+                      const imgtx_adaptive_t* __restrict__ recs) {
+  const int64_t total = n * h * w;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t img = i / ((int64_t)h * w);
+    const int rem = (int)(i - img * h * w);
+    const int y = rem / w, x = rem - y * w;
+    const imgtx_adaptive_t r = recs[img];
+    const uint8_t* im = in + img * (int64_t)h * w * c;
+    uint8_t* o = out + i * c;
+    if (!(r.flags & 4)) {
+      for (int ch = 0; ch < c; ++ch) o[ch] = (uint8_t)adaptive_fetch(im, r, h, w, c, x, y, ch);
+      continue;
+    }
+    const double xin = x + 0.5, yin = y + 0.5;
+    const double den = r.persp[6] * xin + r.persp[7] * yin + 1;
+    double sx = (r.persp[0] * xin + r.persp[1] * yin + r.persp[2]) / den;
+    double sy = (r.persp[3] * xin + r.persp[4] * yin + r.persp[5]) / den;
+    if (sx < 0.0 || sx >= (double)w || sy < 0.0 || sy >= (double)h) {
+      for (int ch = 0; ch < c; ++ch) o[ch] = 0;
+      continue;
+    }
+    sx -= 0.5;
+    sy -= 0.5;
+    const int x0 = (int)floor(sx), y0 = (int)floor(sy);
+    const double dx = sx - x0, dy = sy - y0;
+    const int xl = clampi(x0, 0, w - 1), xr = clampi(x0 + 1, 0, w - 1), ya = clampi(y0, 0, h - 1);
+    const bool ok2 = (y0 + 1 >= 0) && (y0 + 1 < h);
+    for (int ch = 0; ch < c; ++ch) {
+      const double l1 = adaptive_fetch(im, r, h, w, c, xl, ya, ch), r1 = adaptive_fetch(im, r, h, w, c, xr, ya, ch);
+      const double v1 = l1 + (r1 - l1) * dx;
+      double v2 = v1;
+      if (ok2) {
+        const double l2 = adaptive_fetch(im, r, h, w, c, xl, y0 + 1, ch), r2 = adaptive_fetch(im, r, h, w, c, xr, y0 + 1, ch);
+        v2 = l2 + (r2 - l2) * dx;
+      }
+      o[ch] = (uint8_t)(int)(v1 + (v2 - v1) * dy);
     }
   }
 }
@@ -235,6 +296,19 @@ extern "C" int imgtx_gaussian_blur_f32(const float* in, float* out, int64_t plan
   for (int i = 0; i < kernel_size; ++i)
     for (int j = 0; j < kernel_size; ++j) K.k[i][j] = k1[i] * k1[j];
   gaussian_blur_f32_kernel<<<grid_for(planes * h * w), 256, 0, (cudaStream_t)stream>>>(in, out, planes, h, w, K);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_adaptive_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                       const imgtx_adaptive_t* records_dev, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4 && n >= 0, "bad image shape");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out && records_dev, "null pointer");
+  IMGTX_CHECK_ARG(in != out, "the chain gathers: it cannot run in place");
+  const int64_t total = n * h * w;
+  const int64_t grid = std::min<int64_t>((total + 255) / 256, (int64_t)imgtx::sm_count() * 16);
+  imgtx::adaptive_chain_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(in, out, n, h, w, c, records_dev);
   IMGTX_LAUNCH_OK();
   return IMGTX_OK;
 }

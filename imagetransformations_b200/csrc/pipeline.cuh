@@ -254,6 +254,9 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
 }
 
 // Default "no spill" hooks for operators without intermediate planes.
+// Per-image metric of an output batch (runtime.cu): metrics = device (n, 2) uint32 {byte sum, position-weighted sum}.
+int image_checksums(const uint8_t* x, int64_t n, int64_t image_bytes, uint32_t* metrics, cudaStream_t stream);
+
 struct NoSpill {
   static size_t gtmp_bytes(const Shape&) { return 0; }
   static size_t scratch_bytes_spilled(const Shape&) { return 0; }

@@ -483,8 +483,8 @@ extern "C" int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n,
 /* CIFAR-10-C pixelate, throughput form: Image.resize((sw, sh), BOX) then Image.resize((w, h), BOX) for images up to 64x64.
    Returns IMGTX_OK when launched, 1 when the BOX tables do not have the (<= 2 taps down, single unit tap up) structure or
    the shape is outside the fast path — the caller then uses imgtx_resize_chain_u8 (same results). */
-extern "C" int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
-                                     int flags, imgtx_stream_t stream) {
+static int impl_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                                     int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   (void)flags;   // integer arithmetic: one form
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "pixelate takes (n,h,w,3) images");
   IMGTX_CHECK_ARG(sw > 0 && sh > 0 && sw <= w && sh <= h, "the intermediate size must not exceed the image");
@@ -526,4 +526,13 @@ extern "C" int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n,
   Shape shp = make_shape(h, w, c, h, w);
   shp.aux = sw;
   return launch_image_op<OpBoxPixelate>(in, out, n, shp, p, (cudaStream_t)stream);
+}
+
+extern "C" int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
+                                     int flags, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  bool metrics_done = false;
+  int rc = impl_box_pixelate_u8(in, out, n, h, w, c, sw, sh, flags, metrics_dev, &metrics_done, stream);
+  // operators without a metric epilogue: one extra read of the output (imgtx_image_checksums_u8)
+  if (rc == IMGTX_OK && metrics_dev && !metrics_done) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
 }

@@ -1,6 +1,8 @@
 // Library runtime: error string, cached device attributes, staged-pipeline tuning.
 #include "common.cuh"
 #include "pipeline.cuh"
+#include "team_pipeline.cuh"
+#include <algorithm>
 #include <atomic>
 #include <mutex>
 #include <stdlib.h>
@@ -64,6 +66,46 @@ StagedTuning staged_tuning() {
 }
 
 }  // namespace imgtx
+
+namespace imgtx {
+// one warp per image; images of any size that is a multiple of 4 bytes (others: byte tail handled by lane 0)
+__global__ void __launch_bounds__(256) checksum_kernel(const uint8_t* __restrict__ x, int64_t n, int64_t image_bytes,
+                                                       uint2* __restrict__ metrics) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+  for (int64_t img = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); img < n; img += warps) {
+    const uint8_t* p = x + img * image_bytes;
+    uint32_t c0 = 0, c1 = 0;
+    if ((reinterpret_cast<uintptr_t>(p) & 3) == 0) {
+      const uint32_t* p32 = reinterpret_cast<const uint32_t*>(p);
+      for (int64_t i = lane; i < (image_bytes >> 2); i += 32) checksum_word(__ldg(p32 + i), (uint32_t)i, c0, c1);
+      if (lane == 0)
+        for (int64_t b = image_bytes & ~(int64_t)3; b < image_bytes; ++b) { c0 += p[b]; c1 += ((uint32_t)b + 1u) * p[b]; }
+    } else {
+      for (int64_t b = lane; b < image_bytes; b += 32) { c0 += p[b]; c1 += ((uint32_t)b + 1u) * p[b]; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+      c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+    }
+    if (lane == 0) metrics[img] = make_uint2(c0, c1);
+  }
+}
+
+int image_checksums(const uint8_t* x, int64_t n, int64_t image_bytes, uint32_t* metrics, cudaStream_t stream) {
+  if (n <= 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && metrics && image_bytes > 0, "null pointer");
+  const int64_t grid = std::min<int64_t>((n + 7) / 8, (int64_t)sm_count() * 8);
+  checksum_kernel<<<(unsigned)grid, 256, 0, stream>>>(x, n, image_bytes, reinterpret_cast<uint2*>(metrics));
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+}  // namespace imgtx
+
+extern "C" int imgtx_image_checksums_u8(const uint8_t* x, int64_t n, int64_t image_bytes, uint32_t* metrics_dev,
+                                        imgtx_stream_t stream) {
+  return imgtx::image_checksums(x, n, image_bytes, metrics_dev, (cudaStream_t)stream);
+}
 
 extern "C" int imgtx_version(void) { return IMGTX_VERSION; }
 extern "C" const char* imgtx_last_error(void) { return imgtx::g_err; }

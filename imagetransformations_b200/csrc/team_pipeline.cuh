@@ -41,12 +41,21 @@ struct TeamMinBlocks { static constexpr int value = 1; };
 template <class Op>
 struct TeamMinBlocks<Op, decltype((void)Op::kMinBlocks)> { static constexpr int value = Op::kMinBlocks; };
 
+// Per-image metric of a pass: {sum of the output bytes, sum of (index + 1) * byte mod 2^32} — order-sensitive inside an image,
+// so a sharded run and a single-GPU run can be compared without moving the images.  Partial sums of 4-byte
+// words: (4 i + 1) * (b0 + b1 + b2 + b3) + (b1 + 2 b2 + 3 b3), two IDP.4A per word.
+__device__ __forceinline__ void checksum_word(uint32_t w, uint32_t i, uint32_t& c0, uint32_t& c1) {
+  const uint32_t s = __dp4a(w, 0x01010101u, 0u);
+  c0 += s;
+  c1 += (4u * i + 1u) * s + __dp4a(w, 0x03020100u, 0u);
+}
+
 template <class Op>
 __global__ void __launch_bounds__(Op::kTeamWarps * 32 * Op::kMaxTeams, TeamMinBlocks<Op>::value)
 team_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, Shape s, typename Op::Params p,
-            int cta_scratch_bytes, int team_bytes) {
+            int cta_scratch_bytes, int team_bytes, uint2* __restrict__ metrics) {
   constexpr int TW = Op::kTeamWarps, TT = TW * 32, KI = Op::kInBufs, KO = Op::kOutBufs;
-  static_assert(KI >= 2 && KI <= 8 && KO != 1, "ring depths");
+  static_assert(KI >= 2 && KI <= 8 && KO != 1 && TW <= 8, "ring depths / header layout (8 mbarriers + 8 metric partials)");
   extern __shared__ __align__(128) uint8_t smem[];
   const int team = threadIdx.x / TT, tt = threadIdx.x - team * TT;
   const int teams_per_cta = blockDim.x / TT;
@@ -82,12 +91,36 @@ team_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n
     uint8_t* src = in_buf + st * ib;
     uint8_t* dst = KO == 0 ? src : out_buf + (it % (KO > 0 ? KO : 1)) * ob;
     Op::run(src, dst, img, s, p, scr, smem, tt, team);
+    if (metrics) {
+      // epilogue: the pass's per-image metric straight from the staged output (no second trip to HBM); each warp leaves its
+      // partial sums in the team header, the leader adds them after the barrier below
+      if (TW > 1) team_sync<TW>(team);   // every warp's part of dst is written
+      else __syncwarp();
+      const uint32_t* d32 = reinterpret_cast<const uint32_t*>(dst);
+      uint32_t c0 = 0, c1 = 0;
+      for (int i = tt; i < (s.out_bytes >> 2); i += TT) checksum_word(d32[i], (uint32_t)i, c0, c1);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+      }
+      if ((tt & 31) == 0) reinterpret_cast<uint2*>(base + 64)[tt >> 5] = make_uint2(c0, c1);
+    }
     fence_async_smem();
     // the output buffer of the NEXT iteration must be free before anybody passes the barrier below: the store issued
     // KO - 1 iterations ago has to have finished reading it
     if (KO >= 2 && tt == 0) bulk_wait_read<(KO >= 2 ? KO - 2 : 0)>();
     team_sync<TW>(team);
     if (tt == 0) {
+      if (metrics) {
+        uint2 m = make_uint2(0u, 0u);
+#pragma unroll
+        for (int w = 0; w < TW; ++w) {
+          const uint2 q = reinterpret_cast<const uint2*>(base + 64)[w];
+          m.x += q.x; m.y += q.y;
+        }
+        metrics[img] = m;
+      }
       bulk_s2g(out + img * s.out_bytes, dst, (uint32_t)s.out_bytes);
       bulk_commit();
       if (KO == 0) {
@@ -117,10 +150,10 @@ team_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n
 static inline int smem_per_sm() { return 228 * 1024; }
 
 // teams_override > 0 caps the teams per CTA (tuning).  Returns IMGTX_ERR_UNSUPPORTED (without an error string) when the
-// shape cannot be staged, so callers fall through to the general pipeline.
+// shape cannot be staged, so callers fall through to the general pipeline.  metrics: device (n, 2) uint32 or nullptr.
 template <class Op>
 int launch_team_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, const typename Op::Params& p,
-                   cudaStream_t stream) {
+                   cudaStream_t stream, uint32_t* metrics = nullptr) {
   if (n <= 0) return IMGTX_OK;
   IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
   if (s.in_bytes % 16 || s.out_bytes % 16 || !aligned16(in) || !aligned16(out)) return IMGTX_ERR_UNSUPPORTED;
@@ -145,7 +178,8 @@ int launch_team_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, c
   int64_t grid = (int64_t)sm_count() * ctas;
   const int64_t need = (n + teams - 1) / teams;
   if (grid > need) grid = need;
-  kern<<<(unsigned)grid, teams * TT, smem_bytes, stream>>>(in, out, n, s, p, (int)cta_scr, (int)team_bytes);
+  kern<<<(unsigned)grid, teams * TT, smem_bytes, stream>>>(in, out, n, s, p, (int)cta_scr, (int)team_bytes,
+                                                           reinterpret_cast<uint2*>(metrics));
   IMGTX_LAUNCH_OK();
   return IMGTX_OK;
 }

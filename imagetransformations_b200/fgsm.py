@@ -89,3 +89,17 @@ def pgd_attack(model, image, label, epsilon, alpha, num_iter, min_pixel_val, max
         data_grad = perturbed.grad.data
         perturbed = B.pgd_step(perturbed.detach(), original_image, data_grad, float(alpha), float(epsilon), lo, hi)
     return perturbed
+
+
+def patch_step_(patch: torch.Tensor, grad: torch.Tensor, epsilon: float) -> torch.Tensor:
+    """fall_2025/angellic_patches_fgsm.py:67-69, in place like the reference:  patch -= eps*grad.sign(); patch.clamp_(0, 1).
+    The same step without the in-place update is the entropy / margin descent of pipenline/cifar100_shannon.py:72-74."""
+    B.sign_step(patch, grad, float(epsilon), -1.0, 0.0, 1.0, out=patch)
+    return patch
+
+
+def odin_perturb(imgs: torch.Tensor, grads: torch.Tensor, epsilon: float) -> torch.Tensor:
+    """fall_2025/generalizedOdin2.py:47,76:  imgs - eps*torch.sign(-grads).  a - (-b) == a + b bit for bit in IEEE arithmetic
+    (sign(-g) == -sign(g) including zeros and NaN), so this is the un-clamped forward sign step."""
+    return B.sign_step(imgs, grads, float(epsilon), +1.0)
+

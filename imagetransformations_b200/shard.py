@@ -77,12 +77,25 @@ def all_gather_rows(local: torch.Tensor, n_total: int, group=None) -> torch.Tens
 
 
 def image_checksums(x: torch.Tensor) -> torch.Tensor:
-    """Per-image metric that is all-gathered after a pass: (n, 2) int64 = [sum of bytes, position-weighted sum mod 2^31-1].
-    Order-sensitive inside an image, so sharded and single-GPU runs can be compared without moving the images."""
+    """Per-image metric that is all-gathered after a pass: (n, 2) int32 holding the uint32 words
+    [sum of bytes, sum of (byte index + 1) * byte mod 2^32].  Order-sensitive inside an image, so sharded and single-GPU
+    runs can be compared without moving the images.  CUDA tensors: one libimgtx kernel (imgtx_image_checksums_u8; the suite's
+    throughput kernels produce the same words in their epilogue, see cifar_c.corrupt(metrics=...)).  CPU tensors (the gloo
+    tests of the host logic): the same formula in torch integer arithmetic."""
     n = x.shape[0]
-    flat = x.reshape(n, int(x[0].numel()) if n else max(1, x.numel())).to(torch.int64) if n else x.new_zeros((0, 1), dtype=torch.int64)
-    wts = (torch.arange(flat.shape[1], device=x.device, dtype=torch.int64) % 8191) + 1
-    return torch.stack([flat.sum(1), (flat * wts).sum(1) % 2147483647], dim=1)
+    nbytes = int(x[0].numel()) if n else 0
+    if x.is_cuda:
+        from . import _lib as L, batch as B
+        x = x.contiguous()
+        out = torch.empty((n, 2), dtype=torch.int32, device=x.device)
+        if n:
+            with torch.cuda.device_of(x):
+                L.check(L.load().imgtx_image_checksums_u8(x.data_ptr(), n, nbytes, out.data_ptr(), B._stream()))
+        return out
+    flat = x.reshape(n, max(nbytes, 1)).to(torch.int64) if n else x.new_zeros((0, 1), dtype=torch.int64)
+    wts = torch.arange(1, flat.shape[1] + 1, dtype=torch.int64)
+    both = torch.stack([flat.sum(1), (flat * wts).sum(1)], dim=1) & 0xFFFFFFFF
+    return torch.where(both >= 2 ** 31, both - 2 ** 32, both).to(torch.int32)   # the same 32 bits as the device words
 
 
 def corrupt_sharded(x_all, name: str, severity: int, draws: Optional[dict] = None, seed: int = 0,
@@ -102,8 +115,14 @@ def corrupt_sharded(x_all, name: str, severity: int, draws: Optional[dict] = Non
     if torch.cuda.is_available() and not xl.is_cuda:
         xl = xl.cuda(non_blocking=True)
     rank_seed = seed if draws else (seed * 0x9E3779B97F4A7C15 + lo) & 0xFFFFFFFFFFFFFFFF
-    out = corrupt_fn(xl, name, severity, draws=shard_draws(draws, n), seed=rank_seed)
-    sums = all_gather_rows(image_checksums(out), n)
+    if xl.is_cuda and corrupt_fn.__module__.endswith("cifar_c"):
+        # the pass kernel's epilogue writes the metric (no second read of the output)
+        local = torch.empty((xl.shape[0], 2), dtype=torch.int32, device=xl.device)
+        out = corrupt_fn(xl, name, severity, draws=shard_draws(draws, n), seed=rank_seed, metrics=local)
+    else:
+        out = corrupt_fn(xl, name, severity, draws=shard_draws(draws, n), seed=rank_seed)
+        local = image_checksums(out)
+    sums = all_gather_rows(local, n)
     gathered = all_gather_rows(out, n) if gather_outputs else None
     return out, sums, gathered
 

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define IMGTX_VERSION 100
+#define IMGTX_VERSION 200
 
 typedef enum {
   IMGTX_OK = 0,
@@ -55,6 +55,11 @@ int imgtx_device_info(int* sm_count, int* max_smem_per_block);
    specification's literal arithmetic only near a rounding boundary; with this flag EVERY element takes the literal replay,
    so tests can check that both routes give the same bytes (also on on-chip draws). */
 #define IMGTX_CC_REPLAY_ALL 2
+/* `metrics_dev` of the suite entry points (nullable): device (n, 2) uint32 receiving the per-image metric of the pass —
+   {sum of the output bytes, sum of (byte index + 1) * byte mod 2^32} — the small result the ranks all-gather after a pass
+   (north star: "NCCL ... only to all-gather per-image outputs and metrics").  The throughput kernels compute it
+   in their epilogue from the staged output; the others run imgtx_image_checksums_u8 on the output. */
+int imgtx_image_checksums_u8(const uint8_t* x, int64_t n, int64_t image_bytes, uint32_t* metrics_dev, imgtx_stream_t stream);
 
 /* ---- pointwise uint8 maps (256-entry LUT built with the library's exact f32 formula) -------- */
 typedef enum {
@@ -153,7 +158,7 @@ int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
    gather and BOX down-sampling has at most two taps, so only the small image is computed.  Returns IMGTX_OK when launched,
    1 when the shape or table structure is outside the fast path (use imgtx_resize_chain_u8: identical results). */
 int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
-                          int flags, imgtx_stream_t stream);
+                          int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 
 /* ---- stencils ------------------------------------------------------------------------------- */
 /* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
@@ -185,6 +190,20 @@ int imgtx_perspective_tensor_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
    fall_2025/angellic_with_corrupt.py:54-56 */
 int imgtx_gaussian_blur_f32(const float* in, float* out, int64_t planes, int h, int w, int kernel_size, float sigma,
                             imgtx_stream_t stream);
+
+/* Entropy-gated adaptive chain on PIL images — fall_2025/Initial_Experiments.py:88-92 (the Compose) and :161-167 (its call
+   site): RandomHorizontalFlip(0.5) -> RandomAffine(15, translate .1, scale .9-1.1) [Pillow AFFINE NEAREST, fill 0] ->
+   RandomPerspective(.2, p=.5) [Pillow PERSPECTIVE BILINEAR, fill 0], fused into one gather per output pixel.  One record per
+   image, built on the host from torchvision's own draws (imagetransformations_b200/Initial_Experiments.py). */
+typedef struct {
+  int32_t flags;   /* bit 0: flip fired; bit 1: affine present; bit 2: perspective fired */
+  int32_t a[6];    /* libImaging affine_fixed coefficients: FIX(m0), FIX(m1), FIX(m2 + m0/2 + m1/2), FIX(m3), FIX(m4),
+                      FIX(m5 + m3/2 + m4/2) with FIX(v) = floor(v*65536 + 0.5), m = the matrix torchvision hands to Pillow */
+  int32_t pad;
+  double persp[8]; /* _get_perspective_coeffs(startpoints, endpoints) */
+} imgtx_adaptive_t;
+int imgtx_adaptive_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                            const imgtx_adaptive_t* records_dev, imgtx_stream_t stream);
 
 /* ---- noise ---------------------------------------------------------------------------------- */
 typedef enum {
@@ -221,7 +240,7 @@ typedef enum {
 } imgtx_cc_kind;
 int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind, double p0, double p1,
                           const void* draws_a_dev, const void* draws_b_dev, uint64_t seed, int tex_n, int tex_h,
-                          int tex_w, int flags, imgtx_stream_t stream);
+                          int tex_w, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* On-chip gaussian_noise / shot_noise sampled in the OUTPUT domain.  Input and output are bytes, so gaussian_noise adds the
    integer floor(255*sigma*Z) (one discrete law) and shot_noise is a 256-row stochastic matrix (row x = law of
    uint8(clip(Poisson(x/255*c)/c)*255)); both are sampled with Walker alias tables: one 32-bit Philox word, one multiply and
@@ -232,11 +251,11 @@ int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
 int64_t imgtx_cc_noise_table_words(int kind, double p0);
 int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_host, int64_t capacity_words);
 int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,
-                             const int32_t* table_dev, int64_t table_words, uint64_t seed, imgtx_stream_t stream);
+                             const int32_t* table_dev, int64_t table_words, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* defocus_blur: correlation with the sparse taps (dy, dx, weight) of the anti-aliased disk kernel, REFLECT_101, f64.
    dydx_host: (ntaps, 2) int32; |offset| <= 2. */
 int imgtx_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
-                        const int32_t* dydx_host, const double* weights_host, int flags, imgtx_stream_t stream);
+                        const int32_t* dydx_host, const double* weights_host, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* zoom_blur (any fixed linear map on x/255 in CSR form, applied in f32 in stored order). */
 int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                     const int32_t* indices_dev, const float* weights_dev, int nnz, imgtx_stream_t stream);
@@ -245,30 +264,30 @@ int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, in
    to imgtx_cc_csr_u8 when the table does not fit. */
 int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                         const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
-                        int flags, imgtx_stream_t stream);
+                        int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* glass_blur: weights_host[0..lw] = scipy Gaussian taps (centre first); deltas_dev (n, iters, h-2, w-2, 2) int8 (dx, dy). */
 int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host, int lw,
-                      int iters, const int8_t* deltas_dev, uint64_t seed, int flags, imgtx_stream_t stream);
+                      int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* motion_blur: k_host[width] one-sided Gaussian line weights; offsets_dev (n, width, 2) int32 (dx, dy), or NULL with the
    angle drawn uniformly in [angle_lo, angle_hi] degrees. */
 int imgtx_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int width, const float* k_host,
                        const int32_t* offsets_dev, double angle_lo, double angle_hi, uint64_t seed,
-                       int flags, imgtx_stream_t stream);
+                       int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* snow: zoom_idx_host = [y0 (h), y1 (h), x0 (w), x1 (w)], zoom_t_host = [ty (h), tx (w)] (centre-zoom tables of the noise
    layer); layer_dev (n,h,w) f64 normal(loc, scale) draws or NULL. */
 int imgtx_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
                      float one_minus_c6, const int32_t* zoom_idx_host, const float* zoom_t_host, int width,
                      const float* k_host, const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
-                     double angle_lo, double angle_hi, uint64_t seed, int flags, imgtx_stream_t stream);
+                     double angle_lo, double angle_hi, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* elastic_transform: M_dev (n,6) f64 forward affine matrices (cv2.getAffineTransform) or NULL (corner jitter of amplitude
    c2 drawn on chip); ux_dev / uy_dev (n,h,w) f64 uniform(-1,1) fields or NULL; weights_host[0..lw] Gaussian taps (lw = -1:
    no smoothing). */
 int imgtx_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
                         const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
-                        const double* uy_dev, double c2, uint64_t seed, int flags, imgtx_stream_t stream);
+                        const double* uy_dev, double c2, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* jpeg_compression: baseline round trip (4:2:0, islow DCT) with the two quantisation tables (natural order). */
 int imgtx_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* qtables_host,
-                     int flags, imgtx_stream_t stream);
+                     int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 
 /* ---- tensors ------------------------------------------------------------------------------ */
 /* T.ToTensor() [+ T.Normalize(mean, std) when mean_host/std_host != NULL]: u8 NHWC -> f32 NCHW.

@@ -642,6 +642,88 @@ def gen_posthoc(X):
     b.save()
 
 
+def gen_adaptive(X):
+    """H26: adaptive_transforms of fall_2025/Initial_Experiments.py:88-92 (the live T.Compose) on PIL images under recorded
+    torch seeds, with the draws it consumed replayed through torchvision's own get_params (flip rand, RandomAffine.get_params:
+    angle, tx, ty, scale; perspective rand, then RandomPerspective.get_params), and the full call site :147-167 (normalised
+    tensor -> denormalise, clamp -> ToPILImage -> chain -> ToTensor + Normalize)."""
+    import torch
+    import torchvision.transforms as T
+    from PIL import Image
+    b = Book("adaptive")
+    A = R.adaptive()
+    b.put("x32", X["x32"])
+    b.put("xodd", X["xodd"])
+    for key in ("x32", "xodd"):
+        arr = X[key]
+        n, h, w, _ = arr.shape
+        outs, D = [], {k: [] for k in ("flip", "angle", "tx", "ty", "scale", "persp", "start", "end")}
+        reps = 6
+        for i in range(n):
+            for v in range(reps):
+                seed = 9000 + 100 * i + v
+                torch.manual_seed(seed)
+                outs.append(np.array(A.adaptive_transforms(Image.fromarray(arr[i]))))
+                torch.manual_seed(seed)
+                flip = bool(torch.rand(1) < 0.5)
+                angle, (tx, ty), scale, shear = T.RandomAffine.get_params([-15.0, 15.0], (0.1, 0.1), (0.9, 1.1), None, [w, h])
+                fired = bool(torch.rand(1) < 0.5)
+                sp, ep = T.RandomPerspective.get_params(w, h, 0.2) if fired else ([[0, 0]] * 4, [[0, 0]] * 4)
+                for k, val in zip(D, (flip, angle, tx, ty, scale, fired, sp, ep)):
+                    D[k].append(val)
+        b.case("Initial_Experiments.adaptive_transforms", key, np.stack(outs), args={"reps": reps, "seed0": 9000},
+               draws={"flip": np.array(D["flip"], np.int32), "angle": np.array(D["angle"], np.float64),
+                      "tx": np.array(D["tx"], np.int64), "ty": np.array(D["ty"], np.int64),
+                      "scale": np.array(D["scale"], np.float64), "persp": np.array(D["persp"], np.int32),
+                      "start": np.array(D["start"], np.int64), "end": np.array(D["end"], np.int64)})
+    # the call site: img (normalised) -> denorm, clamp -> ToPILImage -> adaptive_transforms -> transform
+    x = torch.from_numpy(X["x32"]).permute(0, 3, 1, 2).contiguous().float().div(255)
+    mean, std = torch.tensor(A.CIFAR_MEAN).view(1, 3, 1, 1), torch.tensor(A.CIFAR_STD).view(1, 3, 1, 1)
+    xn = (x - mean) / std
+    xn = xn + 0.3 * torch.randn(xn.shape, generator=torch.Generator().manual_seed(11))   # some values leave [0,1] after denorm
+    b.put("xn", xn.numpy())
+    outs = []
+    for i in range(len(xn)):
+        img = xn[i]
+        img_denorm = img.clone()
+        for c in range(3):
+            img_denorm[c] = img_denorm[c] * A.CIFAR_STD[c] + A.CIFAR_MEAN[c]
+        img_denorm = torch.clamp(img_denorm, 0, 1)
+        torch.manual_seed(9500 + i)
+        outs.append(A.transform(A.adaptive_transforms(T.ToPILImage()(img_denorm))).numpy())
+    b.case("Initial_Experiments.adapt_call_site", "xn", np.stack(outs), args={"seed0": 9500})
+    b.save()
+
+
+def gen_signsteps(X):
+    """H25: the in-place patch step of fall_2025/angellic_patches_fgsm.py:67-69 and the ODIN perturbation of
+    fall_2025/generalizedOdin2.py:47,76, evaluated with the literal torch expressions of those lines on tensors that carry
+    +-0, NaN, +-inf and denormals in the gradient."""
+    import torch
+    b = Book("signsteps")
+    gen = torch.Generator().manual_seed(25)
+    patch = torch.rand((3, 8, 8), generator=gen)
+    imgs = torch.randn((6, 3, 32, 32), generator=gen)
+    for t in (patch, imgs):
+        t.view(-1)[:3] = torch.tensor([0.0, -0.0, 1.0])
+    gp = torch.randn(patch.shape, generator=gen)
+    gi = torch.randn(imgs.shape, generator=gen)
+    for g in (gp, gi):
+        g[torch.rand(g.shape, generator=gen) < 0.02] = 0.0
+        g.view(-1)[:8] = torch.tensor([0.0, -0.0, float("nan"), float("inf"), -float("inf"), 1e-45, -1e-45, 3.0])
+    b.put("patch", patch.numpy()); b.put("imgs", imgs.numpy())
+    for eps in (0.05, 0.01, 0.0):
+        p = patch.clone()
+        with torch.no_grad():                      # angellic_patches_fgsm.py:67-69
+            p -= eps * gp.sign()
+            p.clamp_(0, 1)
+        b.case("angellic_patches_fgsm.patch_step", "patch", p.numpy(), args={"eps": eps}, draws={"g": gp.numpy()})
+    for eps in (0.0014, 0.01, 0.0):
+        perturbed = imgs - eps * torch.sign(-gi)   # generalizedOdin2.py:47 / :76
+        b.case("generalizedOdin2.perturb", "imgs", perturbed.numpy(), args={"eps": eps}, draws={"g": gi.numpy()})
+    b.save()
+
+
 def gen_fixtures(X):
     """The reference's own CIFAR-10-C samples (CIFAR-10-C/store/*.png, lossless, all severity 1 — SURVEY §2.1) as one
     array per corruption type, ordered by source index (0, 1001, 2002, 3003, 4004)."""
@@ -661,7 +743,8 @@ def main():
     if not R.available():
         raise SystemExit("the reference is not mounted at " + R.REF_ROOT)
     X = make_inputs()
-    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "entropy", "posthoc", "fixtures"]
+    which = sys.argv[1:] or ["transformation", "augmix", "tta", "pool", "fgsm", "entropy", "posthoc", "adaptive", "signsteps",
+                            "fixtures"]
     for w in which:
         globals()["gen_" + w](X)
 

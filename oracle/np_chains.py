@@ -302,3 +302,21 @@ def float_corrupt(x, mode: str, a=0.0, b=0.0, r=None):
     if mode == "add_noise":        # x + randn*std
         return (x + (r * f32(a)).astype(f32)).astype(f32)
     raise ValueError(mode)
+
+
+# =================================================================================================
+# H26  adaptive_transforms of fall_2025/Initial_Experiments.py:88-92 on PIL images
+# =================================================================================================
+def adaptive_chain(u: np.ndarray, flip: bool, affine_matrix, persp_coeffs=None) -> np.ndarray:
+    """RandomHorizontalFlip -> RandomAffine -> RandomPerspective on one (h,w,3) uint8 image: FLIP_LEFT_RIGHT, then
+    Image.transform(AFFINE, m, NEAREST, fillcolor 0) with m = torchvision's _get_inverse_affine_matrix about the centre, then
+    (if it fired) Image.transform(PERSPECTIVE, coeffs, BILINEAR, fillcolor 0)."""
+    x = u[None]
+    if flip:
+        x = O.hflip(x)
+    x = O.affine_nearest(x, np.asarray(affine_matrix, np.float64))
+    if persp_coeffs is not None:
+        x = O.pil_transform(x, np.asarray(persp_coeffs, np.float64), (u.shape[1], u.shape[0]), mode="perspective",
+                            resample="bilinear", fill=0)
+    return x[0]
+

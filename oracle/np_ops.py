@@ -407,6 +407,17 @@ def fgsm_step(x, g, eps, direction=+1.0, lo=None, hi=None):
     return out
 
 
+def patch_step(p, g, eps):
+    """fall_2025/angellic_patches_fgsm.py:67-69: p -= eps*sign(g); clamp_(0, 1) (f32)."""
+    return fgsm_step(p, g, eps, -1.0, 0.0, 1.0)
+
+
+def odin_perturb(x, g, eps):
+    """fall_2025/generalizedOdin2.py:47: x - eps*sign(-g) (f32, no clamp)."""
+    s = torch_sign(-np.asarray(g, np.float32))
+    return (np.asarray(x, np.float32) - (np.float32(eps) * s).astype(np.float32)).astype(np.float32)
+
+
 def pgd_step(x, x0, g, alpha, eps, lo, hi):
     """pgd_cifar10.py:37-45 / pgd_cifar10_corrupted.py:72-83: step, project to eps-ball, clamp."""
     xa = (x + (f32(alpha) * torch_sign(g)).astype(f32)).astype(f32)

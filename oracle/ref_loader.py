@@ -154,6 +154,15 @@ def entropy_gate():
     return _cache["entropy_gate"]
 
 
+def adaptive():
+    """adaptive_transforms (the T.Compose of fall_2025/Initial_Experiments.py:88-92) and `transform` (:81-84)."""
+    if "adaptive" not in _cache:
+        import torchvision.transforms as T
+        _cache["adaptive"] = slice_module("fall_2025/Initial_Experiments.py",
+                                          {"adaptive_transforms", "transform", "CIFAR_MEAN", "CIFAR_STD"}, extra_globals={"T": T})
+    return _cache["adaptive"]
+
+
 def post_hoc():
     """TestTimeAugmentation of fall_2025/post_hoc_aaryaa.py:22-51 (the class only; the file trains models at import)."""
     if "post_hoc" not in _cache:

@@ -233,7 +233,7 @@ def test_pixelate_gather_form_shapes(cuda, hw, c):
     xd = torch.from_numpy(x).cuda()
     out = torch.empty_like(xd)
     sw, sh = int(w * c), int(h * c)
-    rc = L.load().imgtx_box_pixelate_u8(xd.data_ptr(), out.data_ptr(), len(x), h, w, 3, sw, sh, 0, None)
+    rc = L.load().imgtx_box_pixelate_u8(xd.data_ptr(), out.data_ptr(), len(x), h, w, 3, sw, sh, 0, None, None)
     assert rc == 0
     torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), CC.pixelate(x, c))
