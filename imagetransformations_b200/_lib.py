@@ -91,6 +91,7 @@ _PROTOS = {
     "imgtx_augmix_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp],
     "imgtx_views_f32": [_vp, _int, _vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _int, _vp, _vp, _vp, _vp, _vp],
     "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
+    "imgtx_sign_step_post_f32": [_vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp, _vp, _vp, _vp],
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
     "imgtx_shannon_entropy_f32": [_vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _vp],

@@ -529,6 +529,25 @@ def sign_step(x: torch.Tensor, g: torch.Tensor, eps, direction: float = 1.0, lo=
     return (out, pert) if return_pert else out
 
 
+def sign_step_post(x: torch.Tensor, g: torch.Tensor, eps, lut, mean, std, direction: float = 1.0, lo=None, hi=None):
+    """BASELINE config 5 in one kernel: sign step (+clamp) -> tensor_to_pil(mean, std) -> 256-entry uint8 map `lut` ->
+    pil_to_tensor(mean, std), for every eps of the list: (E, n, c, h, w) f32 from ONE pass over x and g."""
+    x, g = _check_f32(x), _check_f32(g)
+    if x.shape != g.shape or x.dim() != 4:
+        raise ValueError("x and g must be (n, c, h, w) tensors of the same shape")
+    n, c, hw = x.shape[0], x.shape[1], x.shape[2] * x.shape[3]
+    eps_l = [float(e) for e in (eps if not np.isscalar(eps) else [eps])]
+    out = torch.empty((len(eps_l),) + tuple(x.shape), dtype=torch.float32, device=x.device)
+    mode, lk, lp, hk, hp = _bounds(lo, hi, c)
+    ek, ep = _fptr(eps_l)
+    mk, mp = _fptr(mean)
+    sk, sp = _fptr(std)
+    lut = np.ascontiguousarray(np.asarray(lut, np.uint8).reshape(256))
+    L.check(L.load().imgtx_sign_step_post_f32(x.data_ptr(), g.data_ptr(), out.data_ptr(), n, c, hw, ep, len(eps_l),
+                                              float(direction), mode, lp, hp, mp, sp, lut.ctypes.data, _stream()))
+    return out
+
+
 def pgd_step(x, x0, g, alpha: float, eps: float, lo=None, hi=None):
     x, x0, g = _check_f32(x), _check_f32(x0), _check_f32(g)
     shp = x.shape

@@ -445,18 +445,54 @@ def suite_passes(corruptions=None, severities=(1, 2, 3, 4, 5)):
 
 
 def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5), seed: int = 0, out=None, sink=None,
-                   mode: Optional[str] = None):
-    """Run every (corruption, severity) pass over the device-resident batch x.  Each pass is one kernel launch (two for
-    pixelate).  `out`: optional (len(passes), n, h, w, 3) uint8 CUDA tensor receiving every pass; otherwise `sink(name,
-    severity, tensor)` is called per pass with a reused buffer (e.g. to checksum or stage to the host)."""
+                   mode: Optional[str] = None, metrics: Optional[torch.Tensor] = None, graph: bool = False):
+    """Run every (corruption, severity) pass over the device-resident batch x.  Each pass is one kernel launch.  `out`:
+    optional (len(passes), n, h, w, 3) uint8 CUDA tensor receiving every pass; otherwise `sink(name, severity, tensor)` is
+    called per pass with a reused buffer (e.g. to checksum or stage to the host).  `metrics`: optional (len(passes), n, 2)
+    int32 tensor receiving the per-image metric of every pass.  graph=True returns a SuiteGraph: the whole step captured once
+    in a CUDA graph and replayed with one host call (the seeds are kernel arguments, so a replay re-draws the same noise;
+    capture again for new seeds)."""
+    if graph:
+        return SuiteGraph(x, corruptions, severities, seed, out, mode, metrics)
     passes = suite_passes(corruptions, severities)
     buf = None if out is not None else torch.empty_like(x)
     for k, (name, sev) in enumerate(passes):
         dst = out[k] if out is not None else buf
-        corrupt(x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode)
+        corrupt(x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode, metrics=None if metrics is None else metrics[k])
         if sink is not None:
             sink(name, sev, dst)
     return out if out is not None else buf
+
+
+class SuiteGraph:
+    """The 75-pass step as one CUDA graph.  The first (eager) run fills the host-side table caches and device-side constant
+    tables; the capture then records only kernel launches (the library allocates nothing and never synchronises)."""
+
+    def __init__(self, x, corruptions=None, severities=(1, 2, 3, 4, 5), seed=0, out=None, mode=None, metrics=None):
+        self.passes = suite_passes(corruptions, severities)
+        self.x = x
+        self.out = out if out is not None else [torch.empty_like(x) for _ in range(2)]
+        self.metrics = metrics
+        self._args = (seed, mode)
+        self._run()                       # warm: caches, cudaFuncSetAttribute
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._run()
+
+    def _run(self):
+        seed, mode = self._args
+        for k, (name, sev) in enumerate(self.passes):
+            dst = self.out[k] if isinstance(self.out, torch.Tensor) else self.out[k & 1]
+            corrupt(self.x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode,
+                    metrics=None if self.metrics is None else self.metrics[k])
+
+    def replay(self):
+        self.graph.replay()
+
+    @property
+    def launches(self):
+        return len(self.passes)
 
 
 def write_cifar_c(root: str, x_u8: np.ndarray, labels: np.ndarray, corruptions=None, seed: int = 0, batch: int = 10000,

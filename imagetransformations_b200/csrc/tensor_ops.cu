@@ -336,6 +336,79 @@ extern "C" int imgtx_sign_step_f32(const float* x, const float* g, float* out, f
   return IMGTX_OK;
 }
 
+// ---- C5: sign step fused with the post-attack leg ------------------------------------------------
+// BASELINE.json config 5: "fused sign-step + clamp + post-attack transformations".  The post-attack leg of the reference
+// (pipenline/cifar_image_transformations.py:141-152 applied to the stepped tensor) is tensor_to_pil (x*std + mean, clamp,
+// x255, truncate: :27-30) -> one pointwise TransformationPool op on the uint8 image (a 256-entry map, e.g.
+// ImageEnhance.Brightness :88-92) -> pil_to_tensor (/255, (t - mean)/std: :32-34).  Everything is elementwise, so the E
+// stepped tensors never exist in HBM: x and g are read once, E final tensors are written.
+struct PostParams {
+  ChanStats st;
+  uint8_t lut[256];
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(256)
+sign_step_post_kernel(const float* __restrict__ x, const float* __restrict__ g, float* __restrict__ out, int64_t count,
+                      int64_t hw, int c, StepParams p, PostParams q) {
+  __shared__ float tab[4][256];     // pil_to_tensor(lut[b]) per channel: (lut[b]/255 - mean)/std, the reference's op order
+  for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) {
+    const int ch = i >> 8;
+    tab[ch][i & 255] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)q.lut[i & 255], 255.0f), q.st.mean[ch < c ? ch : 0]), q.st.std[ch < c ? ch : 0]);
+  }
+  __syncthreads();
+  const int64_t n_items = count / VEC;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_items; i += (int64_t)gridDim.x * blockDim.x) {
+    float xv[4], gv[4];
+    if (VEC == 4) {
+      const float4 a = ldg_stream_f4(reinterpret_cast<const float4*>(x) + i), b = ldg_stream_f4(reinterpret_cast<const float4*>(g) + i);
+      xv[0] = a.x; xv[1] = a.y; xv[2] = a.z; xv[3] = a.w;
+      gv[0] = b.x; gv[1] = b.y; gv[2] = b.z; gv[3] = b.w;
+    } else {
+      xv[0] = x[i]; gv[0] = g[i];
+    }
+    const int ch = (int)(((i * VEC) / hw) % c);  // hw % VEC == 0
+    const int cl = p.clamp_mode == IMGTX_CLAMP_PER_CHANNEL ? ch : 0;
+    const float lo = p.lo[cl], hi = p.hi[cl];
+    for (int e = 0; e < p.n_eps; ++e) {
+      float o[4];
+#pragma unroll
+      for (int k = 0; k < VEC; ++k) {
+        const float pe = __fmul_rn(p.eps[e], tsign(gv[k]));
+        float v = p.dir > 0.0f ? __fadd_rn(xv[k], pe) : __fsub_rn(xv[k], pe);
+        if (p.clamp_mode != IMGTX_CLAMP_NONE) v = tclamp(v, lo, hi);
+        o[k] = tab[ch][quant8(v, ch, q.st, IMGTX_TOU8_DENORMALIZE | IMGTX_TOU8_CLAMP01)];
+      }
+      if (VEC == 4) stg_stream_f4(reinterpret_cast<float4*>(out + (int64_t)e * count) + i, make_float4(o[0], o[1], o[2], o[3]));
+      else out[(int64_t)e * count + i] = o[0];
+    }
+  }
+}
+
+extern "C" int imgtx_sign_step_post_f32(const float* x, const float* g, float* out, int64_t n, int c, int64_t hw,
+                                        const float* eps_host, int n_eps, float direction, int clamp_mode,
+                                        const float* lo_host, const float* hi_host, const float* mean_host,
+                                        const float* std_host, const uint8_t* lut_host, imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(n >= 0 && c >= 1 && c <= 4 && hw >= 1, "bad shape");
+  IMGTX_CHECK_ARG(mean_host && std_host && lut_host, "mean / std / map missing");
+  StepParams p;
+  int rc = fill_step(p, eps_host, n_eps, direction, clamp_mode, lo_host, hi_host, c);
+  if (rc) return rc;
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && g && out, "null pointer");
+  PostParams q;
+  memset(&q, 0, sizeof(q));
+  for (int i = 0; i < c; ++i) { q.st.mean[i] = mean_host[i]; q.st.std[i] = std_host[i]; }
+  memcpy(q.lut, lut_host, 256);
+  const int64_t count = n * c * hw;
+  const bool vec = (hw % 4 == 0) && aligned16(x) && aligned16(g) && aligned16(out);
+  if (vec) sign_step_post_kernel<4><<<grid_for(count / 4), 256, 0, stream>>>(x, g, out, count, hw, c, p, q);
+  else sign_step_post_kernel<1><<<grid_for(count), 256, 0, stream>>>(x, g, out, count, hw, c, p, q);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
 extern "C" int imgtx_pgd_step_f32(const float* x, const float* x0, const float* g, float* out, int64_t n,
                                   int c, int64_t hw, float alpha, float eps, int clamp_mode,
                                   const float* lo_host, const float* hi_host, imgtx_stream_t stream_) {

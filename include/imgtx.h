@@ -368,6 +368,15 @@ int imgtx_sign_step_f32(const float* x, const float* g, float* out, float* pert,
                         const float* eps_host, int n_eps, float direction, int clamp_mode,
                         const float* lo_host, const float* hi_host, imgtx_stream_t stream);
 
+/* BASELINE config 5: the sign step fused with the post-attack leg of pipenline/cifar_image_transformations.py:141-152 —
+   tensor_to_pil (x*std + mean, clamp [0,1], x255, truncate; :27-30) -> one pointwise uint8 op given as a 256-entry map
+   (lut_host; e.g. the ImageEnhance.Brightness map of :88-92) -> pil_to_tensor ((b/255 - mean)/std; :32-34).  x and g are
+   read once; out is (n_eps, n, c, hw) f32.  Same step / clamp arguments as imgtx_sign_step_f32. */
+int imgtx_sign_step_post_f32(const float* x, const float* g, float* out, int64_t n, int c, int64_t hw,
+                             const float* eps_host, int n_eps, float direction, int clamp_mode, const float* lo_host,
+                             const float* hi_host, const float* mean_host, const float* std_host,
+                             const uint8_t* lut_host, imgtx_stream_t stream);
+
 /* PGD iteration: xa = x + alpha*sign(g); eta = clamp(xa - x0, -eps, eps); out = clamp(x0 + eta, lo, hi)
    attacks/fgsm/cifar-10/pgd_cifar10.py:37-45, pgd_cifar10_corrupted.py:72-83 */
 int imgtx_pgd_step_f32(const float* x, const float* x0, const float* g, float* out, int64_t n, int c,

@@ -72,3 +72,27 @@ def test_sign_steps_golden(cuda):
             got = F.odin_perturb(xd, gd, c["args"]["eps"]).cpu().numpy()
         same = (got == want) | (np.isnan(got) & np.isnan(want))
         assert same.all(), (c["fn"], c["args"], int((~same).sum()))
+
+
+def test_sign_step_post_fused_equals_the_unfused_chain(cuda):
+    """BASELINE config 5: sign step + clamp, then tensor_to_pil -> ImageEnhance.Brightness -> pil_to_tensor
+    (pipenline/cifar_image_transformations.py:27-34,88-92,141-152), fused into one kernel: bit-identical to the oracle's chain
+    of the four golden-pinned stages."""
+    from imagetransformations_b200 import batch as B
+    from oracle import np_ops as O
+    mean, std = (0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010)
+    rng = np.random.default_rng(5)
+    x8 = rng.integers(0, 256, (40, 32, 32, 3), dtype=np.uint8)
+    x = O.to_tensor_normalize(x8, mean, std)
+    g = rng.standard_normal(x.shape).astype(np.float32)
+    g.reshape(-1)[:6] = [0.0, -0.0, np.nan, np.inf, -np.inf, 1e-45]
+    lo = [(0 - m) / s for m, s in zip(mean, std)]
+    hi = [(1 - m) / s for m, s in zip(mean, std)]
+    eps = [4 / 355, 8 / 255, 12 / 255]
+    lut = O.pil_blend_lut(0, 1.3)
+    got = B.sign_step_post(torch.from_numpy(x).cuda(), torch.from_numpy(g).cuda(), eps, lut, mean, std, -1.0, lo, hi).cpu().numpy()
+    for k, e in enumerate(eps):
+        step = O.fgsm_step(x, g, e, -1, lo, hi)
+        u = O.tensor_to_pil(step, mean, std)
+        want = O.to_tensor_normalize(lut[u], mean, std)
+        assert np.array_equal(got[k], want), (k, int((got[k] != want).sum()))
