@@ -1215,7 +1215,7 @@ using namespace imgtx;
 
 namespace imgtx {
 int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const int32_t* indptr, const int32_t* indices,
-              const float* weights, int max_row_taps, cudaStream_t stream);   // cifar_c_zoom.cu
+              const float* weights, int max_row_taps, uint32_t* metrics, cudaStream_t stream);   // cifar_c_zoom.cu
 }
 
 static int impl_cc_defocus_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ntaps,
@@ -1304,8 +1304,8 @@ static int impl_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h,
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
   IMGTX_CHECK_ARG(indptr_dev && indices_dev && weights_dev && nnz > 0 && max_row_taps > 0, "missing operator");
   if (flags & IMGTX_CC_FAST) {
-    const int rc = zoom_fast(in, out, n, h, w, indptr_dev, indices_dev, weights_dev, max_row_taps, (cudaStream_t)stream);
-    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+    const int rc = zoom_fast(in, out, n, h, w, indptr_dev, indices_dev, weights_dev, max_row_taps, metrics_dev, (cudaStream_t)stream);
+    if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
   }
   Shape shp = make_shape(h, w, c, h, w);
   const size_t tb = OpCcCsrEll::table_bytes(h * w, max_row_taps);

@@ -1177,7 +1177,6 @@ static int impl_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h,
 
 static int impl_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
                                 const int32_t* qtables_host /* 2 x 64, natural order */, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
-  (void)flags;   // integer arithmetic: one form
   IMGTX_CHECK_ARG(h > 0 && w > 0 && (h % 16) == 0 && (w % 16) == 0 && c == 3 && n >= 0,
                   "jpeg_compression takes (n,h,w,3) images with h, w multiples of 16");
   IMGTX_CHECK_ARG(qtables_host, "missing quantisation tables");
@@ -1189,6 +1188,7 @@ static int impl_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, in
       p.q[t][i] = (int16_t)v;
       p.rq[t][i] = (uint32_t)((1ull << 32) / (uint64_t)(8 * v)) + 1u;
     }
+  (void)flags;   // integer arithmetic: one form (a warp- or team-per-image port measured slower: 610-640 us vs 472 us per pass)
   return launch_image_op<OpCcJpeg>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 80 * 1024);
 }
 

@@ -34,12 +34,14 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
 template <int T>
 __global__ void __launch_bounds__(kZoomThreads, 1)
 zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int P /* pixels, <= 1024, % 4 == 0 */,
-                 const int32_t* __restrict__ indptr, const int32_t* __restrict__ indices, const float* __restrict__ weights) {
+                 const int32_t* __restrict__ indptr, const int32_t* __restrict__ indices, const float* __restrict__ weights,
+                 uint2* __restrict__ metrics) {
   extern __shared__ __align__(128) uint8_t smem[];
   const int img_bytes = P * 3, ib = (int)align_up((size_t)img_bytes, 128);
   constexpr int cb = kZoomCanvas;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint8_t* in_buf = smem + 256;
+  uint2* msum = reinterpret_cast<uint2*>(smem + 256);        // per-warp metric partials (32 x 8 B)
+  uint8_t* in_buf = smem + 512;
   uint8_t* canvas = in_buf + kZoomRing * ib;                   // 2 x P x half4
   uint8_t* out_buf = canvas + 2 * cb;                          // 2 x ib
   const int tid = threadIdx.x;
@@ -133,15 +135,35 @@ zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int6
         }
       }
     }
+    uint32_t b0 = 0, b1 = 0, b2 = 0;
     if (pix >= 0) {
       uint8_t* o = ob + pix * 3;
-      o[0] = (uint8_t)floor_bits(fminf(fmaxf(a0, 0.0f), 255.0f));
-      o[1] = (uint8_t)floor_bits(fminf(fmaxf(a1, 0.0f), 255.0f));
-      o[2] = (uint8_t)floor_bits(fminf(fmaxf(a2, 0.0f), 255.0f));
+      b0 = floor_bits(fminf(fmaxf(a0, 0.0f), 255.0f)) & 255u;
+      b1 = floor_bits(fminf(fmaxf(a1, 0.0f), 255.0f)) & 255u;
+      b2 = floor_bits(fminf(fmaxf(a2, 0.0f), 255.0f)) & 255u;
+      o[0] = (uint8_t)b0; o[1] = (uint8_t)b1; o[2] = (uint8_t)b2;
+    }
+    if (metrics) {   // per-image metric (see team_pipeline.cuh:checksum_word) from the bytes this thread just produced
+      uint32_t c0 = b0 + b1 + b2, c1 = (3u * (uint32_t)tid + 1u) * c0 + b1 + 2u * b2;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+      }
+      if ((tid & 31) == 0) msum[tid >> 5] = make_uint2(c0, c1);
     }
     fence_async_smem();
     if (tid == 0) bulk_wait_read<0>();   // the store of the previous image has finished reading the other output buffer
     __syncthreads();
+    if (metrics && tid < 32) {
+      uint2 m = msum[tid];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        m.x += __shfl_xor_sync(0xffffffffu, m.x, o);
+        m.y += __shfl_xor_sync(0xffffffffu, m.y, o);
+      }
+      if (tid == 0) metrics[img] = m;
+    }
     if (tid == 0) {
       bulk_s2g(out + img * img_bytes, ob, (uint32_t)img_bytes);
       bulk_commit();
@@ -164,28 +186,28 @@ zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int6
 
 template <int T>
 static int launch_zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int P, const int32_t* indptr, const int32_t* indices,
-                            const float* weights, cudaStream_t stream) {
+                            const float* weights, uint32_t* metrics, cudaStream_t stream) {
   const size_t ib = align_up((size_t)P * 3, 128);
-  const size_t smem = 256 + kZoomRing * ib + 2 * (size_t)kZoomCanvas + 2 * ib;
+  const size_t smem = 512 + kZoomRing * ib + 2 * (size_t)kZoomCanvas + 2 * ib;
   auto kern = zoom_fast_kernel<T>;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t grid = std::min<int64_t>(n, sm_count());
-  kern<<<(unsigned)grid, kZoomThreads, smem, stream>>>(in, out, n, P, indptr, indices, weights);
+  kern<<<(unsigned)grid, kZoomThreads, smem, stream>>>(in, out, n, P, indptr, indices, weights, reinterpret_cast<uint2*>(metrics));
   IMGTX_LAUNCH_OK();
   return IMGTX_OK;
 }
 
 // IMGTX_ERR_UNSUPPORTED when the shape is outside the fast form (the caller falls back to the exact ELL kernel)
 int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const int32_t* indptr, const int32_t* indices,
-              const float* weights, int max_row_taps, cudaStream_t stream) {
+              const float* weights, int max_row_taps, uint32_t* metrics, cudaStream_t stream) {
   const int P = h * w;
   if (P > 1024 || P % 4 != 0 || max_row_taps > 20 || (P * 3) % 16 != 0 || !aligned16(in) || !aligned16(out))
     return IMGTX_ERR_UNSUPPORTED;
   if (n <= 0) return IMGTX_OK;
-  if (max_row_taps <= 8) return launch_zoom_fast<8>(in, out, n, P, indptr, indices, weights, stream);
-  if (max_row_taps <= 12) return launch_zoom_fast<12>(in, out, n, P, indptr, indices, weights, stream);
-  if (max_row_taps <= 16) return launch_zoom_fast<16>(in, out, n, P, indptr, indices, weights, stream);
-  return launch_zoom_fast<20>(in, out, n, P, indptr, indices, weights, stream);
+  if (max_row_taps <= 8) return launch_zoom_fast<8>(in, out, n, P, indptr, indices, weights, metrics, stream);
+  if (max_row_taps <= 12) return launch_zoom_fast<12>(in, out, n, P, indptr, indices, weights, metrics, stream);
+  if (max_row_taps <= 16) return launch_zoom_fast<16>(in, out, n, P, indptr, indices, weights, metrics, stream);
+  return launch_zoom_fast<20>(in, out, n, P, indptr, indices, weights, metrics, stream);
 }
 
 }  // namespace imgtx
