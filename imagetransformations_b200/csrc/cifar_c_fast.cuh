@@ -39,6 +39,11 @@ __device__ __forceinline__ AliasView alias_view(const uint8_t* scratch) {
   v.out = reinterpret_cast<const uint8_t*>(v.entries + t[3]);
   return v;
 }
+// the same for a 512-slot table: slot = top 9 bits, fraction = the other 23
+__device__ __forceinline__ uint32_t alias_draw512(const uint32_t* entries, uint32_t base, uint32_t r) {
+  const uint32_t slot = r >> 23, e = entries[base + slot];
+  return ((r & 0x7FFFFFu) < (e >> 9)) ? slot : (e & 511u);
+}
 // one outcome index from one 32-bit random word
 __device__ __forceinline__ uint32_t alias_draw(const uint32_t* entries, uint2 row, uint32_t r) {
   const uint32_t W = row.y >> 16;

@@ -418,7 +418,10 @@ bool build_gaussian(double sigma, AliasTable& t) {
     pr[K + d] = pd;        // delta d
     pr[K - 1 - d] = pd;    // delta -d-1
   }
-  t.rows = {0u, ((uint32_t)(2 * K) << 16) | (uint32_t)(uint16_t)(int16_t)(-K)};
+  // padded with zero-probability outcomes to 512 slots: the device picks the slot with a shift instead of a 32 x 32 -> 64
+  // multiply (IMAD.WIDE is the scarcest pipe of the noise kernels)
+  pr.resize(512, 0.0);
+  t.rows = {0u, (512u << 16) | (uint32_t)(uint16_t)(int16_t)(-K)};
   vose(pr, t.entries);
   return true;
 }

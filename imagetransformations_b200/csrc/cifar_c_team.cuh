@@ -171,8 +171,29 @@ struct OpTFrost : NoTeamPrepare {
     const int ti = (int)(r.x % (uint32_t)p.tex_n);
     const int y0 = (int)(r.y % (uint32_t)(p.tex_h - s.h)), x0 = (int)(r.z % (uint32_t)(p.tex_w - s.w));
     const uint8_t* tex = reinterpret_cast<const uint8_t*>(p.a) + ((size_t)ti * p.tex_h + y0) * p.tex_w * 3 + (size_t)x0 * 3;
-    const size_t tex_pitch = (size_t)p.tex_w * 3;
-    const int row_words = (s.w * 3) >> 2;
+    const int tex_pitch = p.tex_w * 3, row_words = (s.w * 3) >> 2;
+    if (row_words == 24 && (tex_pitch & 3) == 0 && wpi == 768) {
+      // 32 x 32 images, texture rows a whole number of words: the crop's misalignment is the same on every row, so a lane
+      // owns three fixed word columns (j, j + 8, j + 16) of every fourth row and walks down with one pointer increment
+      const int rr = lane >> 3, jj = lane & 7;
+      const uintptr_t a0 = reinterpret_cast<uintptr_t>(tex + (size_t)rr * tex_pitch + (size_t)jj * 4);
+      const uint32_t sh = (uint32_t)(a0 & 3) * 8;
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(a0 & ~(uintptr_t)3);
+      const int step = tex_pitch;                 // four rows = 4 * pitch bytes = pitch words
+      const uint32_t* xi = im + rr * 24 + jj;
+      uint32_t* xo = om + rr * 24 + jj;
+#pragma unroll 4
+      for (int m = 0; m < 8; ++m) {
+        const uint32_t f0 = __funnelshift_r(__ldg(wp), __ldg(wp + 1), sh);
+        const uint32_t f1 = __funnelshift_r(__ldg(wp + 8), __ldg(wp + 9), sh);
+        const uint32_t f2 = __funnelshift_r(__ldg(wp + 16), __ldg(wp + 17), sh);
+        xo[0] = mix4(xi[0], f0, cc);
+        xo[8] = mix4(xi[8], f1, cc);
+        xo[16] = mix4(xi[16], f2, cc);
+        wp += step; xi += 96; xo += 96;
+      }
+      return;
+    }
     const FastDiv rd(row_words);
     // the texture words come from L2: eight independent fetches are issued before the first one is consumed
     for (int i0 = lane; i0 < wpi; i0 += 256) {
@@ -229,7 +250,7 @@ struct OpTNoiseAlias {
 #pragma unroll
         for (int b = 0; b < 4; ++b) {
           const int x = (int)((w >> (8 * b)) & 255u);
-          const int d = dlo + (int)alias_draw(av.entries, row, rr[b]);
+          const int d = dlo + (int)((row.y >> 16) == 512u ? alias_draw512(av.entries, row.x, rr[b]) : alias_draw(av.entries, row, rr[b]));
           o |= (uint32_t)min(max(x + d, 0), 255) << (8 * b);
         }
         d32[i] = o;
