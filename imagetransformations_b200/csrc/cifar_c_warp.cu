@@ -693,9 +693,12 @@ struct OpTElastic : ElasticCommon {
   static constexpr int kLutLo = 64, kLut = 160;   // index tables cover [-64, 96)
   // CTA: Ah, Al [32][40] half | refl101 row (x256) and col (x8) offsets for the canvas | reflect row (x512) / col (x16) for W
   static size_t cta_scratch(const Shape&, const Params&) { return 2 * 32 * kPA * 2 + 4 * kLut * 4; }
-  // team: Mi (6 f64) + tables (128 int) | FT hi, lo [2][32][40] half (aliased by the canvas [1024] x 8 B) | DXY [2][32][32] f32 | W [1024] float4
-  static constexpr int kOffTab = 64, kOffFT = 64 + 512, kOffDXY = kOffFT + 10240, kOffW = kOffDXY + 8192;
-  static size_t team_scratch(const Shape&, const Params&) { return WARP_ONLY ? kOffFT + 8192 : kOffW + 16384; }
+  // team: Mi (6 f64) + tables (128 int) | canvas [1024] x 8 B | DXY [2][32][32] f32 | W [1024] float4 | FT hi (, lo) [2][32][40] half
+  // (the canvas has its own region so that it is built WHILE the tensor-core warps smooth the fields)
+  static constexpr int kOffTab = 64, kOffCanvas = 64 + 512, kOffDXY = kOffCanvas + 8192, kOffW = kOffDXY + 8192, kOffFT = kOffW + 16384;
+  static size_t team_scratch(const Shape&, const Params& p) {
+    return WARP_ONLY ? kOffCanvas + 8192 : kOffFT + (p.e.ux ? 10240 : 5120);
+  }
 
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
     __half* Ah = reinterpret_cast<__half*>(cta);
@@ -785,18 +788,20 @@ struct OpTElastic : ElasticCommon {
     double* Mi = reinterpret_cast<double*>(scr);
     int* tab = reinterpret_cast<int*>(scr + kOffTab);
     __half* FT = reinterpret_cast<__half*>(scr + kOffFT);     // [hi/lo][f][x][kPA]  (element (y, x) of field f at x*kPA + y)
-    uint8_t* canvas = scr + kOffFT;                            // aliases FT (dead after the smoothing)
+    uint8_t* canvas = scr + kOffCanvas;
     float* DXY = reinterpret_cast<float*>(scr + kOffDXY);      // [f][y][x]
     uint8_t* Wb = scr + kOffW;                                 // [y][x] float4
     const int lane = tt & 31, wq = tt >> 5;
     const Philox rng(p.e.seed);
     const bool has_lo = p.e.ux != nullptr;
 
-    if (tt == 0) inverse_matrix_fast(p.e, rng, img, Mi);
     if (WARP_ONLY) {
+      if (tt == 0) inverse_matrix_fast(p.e, rng, img, Mi);
       const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
       uint2* c2 = reinterpret_cast<uint2*>(canvas);
       for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+      team_sync<8>(team);
+      if (tt < 64) affine_tables(Mi, 32, 32, tab, tt);
     }
     if (!WARP_ONLY) {
       // ---- fields -> FT (fp16, transposed) ----
@@ -825,8 +830,20 @@ struct OpTElastic : ElasticCommon {
         }
       }
     }
-    team_sync<8>(team);
-    if (tt < 64) affine_tables(Mi, 32, 32, tab, tt);
+    if (!WARP_ONLY) team_sync<8>(team);
+    // ---- three things at once: warps 0-3 smooth the fields on the tensor cores, warp 4 inverts the matrix and builds cv2's
+    // coordinate tables (float64, one lane then 64 entries), warps 5-7 expand the staged image into the fp16 canvas ----
+    if (!WARP_ONLY && wq == 4) {
+      if (lane == 0) inverse_matrix_fast(p.e, rng, img, Mi);
+      __syncwarp();
+      affine_tables(Mi, 32, 32, tab, lane);
+      affine_tables(Mi, 32, 32, tab, lane + 32);
+    }
+    if (!WARP_ONLY && wq >= 5) {
+      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+      uint2* c2 = reinterpret_cast<uint2*>(canvas);
+      for (int q = tt - 160; q < 256; q += 96) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+    }
     if (!WARP_ONLY && wq < 4) {
       // ---- smoothing on the tensor cores: warp = (field, 16 output rows); warps 4-7 go straight to the barrier ----
       const int f = wq >> 1, mt = wq & 1, g = lane >> 2, t = lane & 3;
@@ -879,13 +896,7 @@ struct OpTElastic : ElasticCommon {
         *reinterpret_cast<float2*>(D + 8 * nt + 256) = make_float2(__fmul_rn(c2[nt][2], p.alpha), __fmul_rn(c2[nt][3], p.alpha));
       }
     }
-    team_sync<8>(team);   // FT is dead: the canvas may overwrite it; tables are ready
-    if (!WARP_ONLY) {
-      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
-      uint2* c2 = reinterpret_cast<uint2*>(canvas);
-      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
-      team_sync<8>(team);
-    }
+    team_sync<8>(team);   // displacements, tables and canvas are ready
     // ---- affine warp (cv2.warpAffine coordinates), thread = column `lane`, rows wq, wq + 4, ... ----
     const int* lrow = lut + kLutLo;
     const int* lcol = lut + kLut + kLutLo;
