@@ -22,16 +22,16 @@ AUG_OP_DTYPE = np.dtype([("kind", "<i4"), ("a", "<i4", (6,)), ("param", "<i4")])
 assert AUG_OP_DTYPE.itemsize == 32
 
 
+def _cuda(t):
+    return t if t.is_cuda else t.cuda()
+
+
 def normalize_tensor(tensor):
-    mean = torch.tensor(CIFAR10_MEAN, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(CIFAR10_STD, device=tensor.device).view(3, 1, 1)
-    return (tensor - mean) / std
+    return B.channel_affine(_cuda(tensor), CIFAR10_MEAN, CIFAR10_STD, False)
 
 
 def denormalize_tensor(tensor):
-    mean = torch.tensor(CIFAR10_MEAN, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(CIFAR10_STD, device=tensor.device).view(3, 1, 1)
-    return tensor * std + mean
+    return B.channel_affine(_cuda(tensor), CIFAR10_MEAN, CIFAR10_STD, True)
 
 
 # ---- the eight PIL ops (single-image drop-ins) -----------------------------------------------------

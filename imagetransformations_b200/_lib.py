@@ -93,6 +93,7 @@ _PROTOS = {
     "imgtx_sign_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp],
     "imgtx_sign_step_post_f32": [_vp, _vp, _vp, _i64, _int, _i64, _vp, _int, _f, _int, _vp, _vp, _vp, _vp, _vp, _vp],
     "imgtx_pgd_step_f32": [_vp, _vp, _vp, _vp, _i64, _int, _i64, _f, _f, _int, _vp, _vp, _vp],
+    "imgtx_channel_affine_f32": [_vp, _vp, _i64, _int, _i64, _vp, _vp, _int, _vp],
     "imgtx_float_corrupt_f32": [_vp, _vp, _vp, _i64, _int, _f, _f, _int, _vp],
     "imgtx_shannon_entropy_f32": [_vp, _i64, _int, _int, _int, _vp, _vp, _vp, _vp, _vp],
     "imgtx_tensor_tta_f32": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp],

@@ -562,6 +562,25 @@ def pgd_step(x, x0, g, alpha: float, eps: float, lo=None, hi=None):
     return out
 
 
+def channel_affine(x: torch.Tensor, mean, std, denormalize: bool) -> torch.Tensor:
+    """normalize_tensor / denormalize_tensor of the reference on a (c,h,w) or (n,c,h,w) f32 CUDA tensor:
+    (x - mean) / std, or x * std + mean when denormalize (pipenline/cifar_image_transformations.py:19-25)."""
+    x = _check_f32(x)
+    if x.dim() not in (3, 4):
+        raise ValueError("expected a (c,h,w) or (n,c,h,w) tensor")
+    c, h, w = x.shape[-3:]
+    n = x.shape[0] if x.dim() == 4 else 1
+    if len(mean) != c or len(std) != c:
+        raise ValueError("one mean / std per channel")
+    out = torch.empty_like(x)
+    mk, mp = _fptr(list(mean))
+    sk, sp = _fptr(list(std))
+    with torch.cuda.device_of(x):
+        L.check(L.load().imgtx_channel_affine_f32(x.data_ptr(), out.data_ptr(), n, c, h * w, mp, sp, int(denormalize),
+                                                  _stream()))
+    return out
+
+
 def float_corrupt(x, mode: int, a: float = 0.0, b: float = 0.0, noise=None, clamp: bool = True):
     x = _check_f32(x)
     out = torch.empty_like(x)

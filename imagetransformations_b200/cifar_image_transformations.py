@@ -22,16 +22,16 @@ SHOT_LEVELS = [60, 25, 12, 5, 3]
 DEFOCUS_LEVELS = [3, 4, 6, 8, 10]
 
 
+def _cuda(t):
+    return t if t.is_cuda else t.cuda()
+
+
 def denormalize_tensor(tensor, mean=CIFAR10_MEAN, std=CIFAR10_STD):
-    mean = torch.tensor(mean, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(std, device=tensor.device).view(3, 1, 1)
-    return tensor * std + mean
+    return B.channel_affine(_cuda(tensor), mean, std, True)
 
 
 def normalize_tensor(tensor, mean=CIFAR10_MEAN, std=CIFAR10_STD):
-    mean = torch.tensor(mean, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(std, device=tensor.device).view(3, 1, 1)
-    return (tensor - mean) / std
+    return B.channel_affine(_cuda(tensor), mean, std, False)
 
 
 def tensor_to_pil(tensor):

@@ -9,7 +9,7 @@
 // exactly as Pillow does (imgtx_resample_table_host) and uploaded once by the caller.
 // Roofline: nominally HBM (in_bytes + out_bytes per image) but the 2x(up to 7-tap) integer stencil makes
 // this pass instruction-bound; see DESIGN.md.
-#include "team_pipeline.cuh"
+#include "sep_mma.cuh"
 #include <math.h>
 #include <string.h>
 #include <vector>
@@ -293,6 +293,87 @@ struct OpBoxPixelate : NoSpill {
   }
 };
 
+// ---- 32x32x3 images: the same passes as dense 32x32 operators on the tensor cores (sep_mma.cuh) ----------------------------
+// Operator of one Pillow pass along one axis in canvas coordinates: row o = output index on the 32-pixel canvas, column =
+// input index; rows outside the resized extent stay zero ((2^21 + 0) >> 22 = 0 is the zero canvas / the unused rows).
+__device__ inline void sep_fill_axis(int32_t* op, const int32_t* tab, int crop, int place, int rsize) {
+  for (int i = threadIdx.x; i < 1024; i += blockDim.x) op[i] = 0;
+  __syncthreads();
+  for (int o = threadIdx.x; o < 32; o += blockDim.x) {
+    const int r = o - place;
+    if (r < 0 || r >= rsize) continue;
+    if (tab) {
+      const int32_t* rec = tab + 2 + r * (2 + tab[1]);
+      for (int j = 0; j < rec[1]; ++j) op[o * 32 + crop + rec[0] + j] = rec[2 + j];
+    } else {
+      op[o * 32 + crop + r] = 1 << 22;
+    }
+  }
+  __syncthreads();
+}
+
+struct OpResampleMma {
+  using Params = ResampleParams;
+  static constexpr int kTeamWarps = 1, kInBufs = 3, kOutBufs = 0, kMaxTeams = 12, kCtasPerSm = 1;
+  static size_t team_scratch(const Shape&, const Params&) { return 0; }
+  static size_t cta_scratch(const Shape&, const Params&) { return kSepOpBytes + 6 * kSepFragBytes; }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    int32_t* op = reinterpret_cast<int32_t*>(cta);
+    uint4* frag = reinterpret_cast<uint4*>(cta + kSepOpBytes);
+    sep_fill_axis(op, p.htab, p.crop_x, p.place_x, p.rw);
+    sep_build_frags(op, frag, 0, 3, false);
+    __syncthreads();
+    sep_fill_axis(op, p.vtab, p.crop_y, p.place_y, p.rh);
+    sep_build_frags(op, frag + 3 * 64, 0, 3, true);
+  }
+  __device__ static void run(const uint8_t* in, uint8_t* out, int64_t, const Shape&, const Params&, uint8_t*,
+                             const uint8_t* cta, int tt, int) {
+    sep_q22_chain<3, 3, 0, 0>(in, out, reinterpret_cast<const uint4*>(cta + kSepOpBytes), tt);
+  }
+};
+
+// pixelate: BOX down (two taps at most) in both axes, then the two unit-tap BOX up passes
+struct OpBoxPixelateMma {
+  using Params = BoxPixParams;
+  static constexpr int kTeamWarps = 1, kInBufs = 3, kOutBufs = 0, kMaxTeams = 12, kCtasPerSm = 1;
+  static size_t team_scratch(const Shape&, const Params&) { return 0; }
+  static size_t cta_scratch(const Shape&, const Params&) { return kSepOpBytes + 8 * kSepFragBytes; }
+  __device__ static void fill_down(int32_t* op, const uint8_t* lo, const uint8_t* lo1, const int32_t* k0, const int32_t* k1, int size) {
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) op[i] = 0;
+    __syncthreads();
+    for (int o = threadIdx.x; o < size; o += blockDim.x) {
+      op[o * 32 + lo[o]] = k0[o];
+      if (lo1[o] != lo[o]) op[o * 32 + lo1[o]] = k1[o];
+    }
+    __syncthreads();
+  }
+  __device__ static void fill_up(int32_t* op, const uint8_t* map) {
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) op[i] = 0;
+    __syncthreads();
+    for (int o = threadIdx.x; o < 32; o += blockDim.x) op[o * 32 + map[o]] = 1 << 22;
+    __syncthreads();
+  }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    int32_t* op = reinterpret_cast<int32_t*>(cta);
+    uint4* frag = reinterpret_cast<uint4*>(cta + kSepOpBytes);
+    fill_down(op, p.hlo, p.hlo1, p.hk0, p.hk1, p.sw);
+    sep_build_frags(op, frag, 0, 3, false);
+    __syncthreads();
+    fill_down(op, p.vlo, p.vlo1, p.vk0, p.vk1, p.sh);
+    sep_build_frags(op, frag + 3 * 64, 0, 3, true);
+    __syncthreads();
+    fill_up(op, p.xmap);
+    sep_build_frags(op, frag + 6 * 64, 2, 1, true);
+    __syncthreads();
+    fill_up(op, p.ymap);
+    sep_build_frags(op, frag + 7 * 64, 2, 1, true);
+  }
+  __device__ static void run(const uint8_t* in, uint8_t* out, int64_t, const Shape&, const Params&, uint8_t*,
+                             const uint8_t* cta, int tt, int) {
+    sep_q22_chain<3, 3, 1, 1>(in, out, reinterpret_cast<const uint4*>(cta + kSepOpBytes), tt);
+  }
+};
+
 // Specialised launcher: scratch depends on the parameters (table sizes, needed window).
 static int launch_resample(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, const ResampleParams& p,
                            cudaStream_t stream) {
@@ -456,6 +537,10 @@ extern "C" int imgtx_resample_u8(const uint8_t* in, uint8_t* out, int64_t n, int
   p.crop_x = crop_x; p.crop_y = crop_y; p.crop_w = crop_w; p.crop_h = crop_h;
   p.crop_xy = crop_xy_per_image_dev;
   p.rw = rw; p.rh = rh; p.place_x = place_x; p.place_y = place_y;
+  if (h == 32 && w == 32 && c == 3 && oh == 32 && ow == 32 && !crop_xy_per_image_dev && (htable_dev || vtable_dev)) {
+    const int rc = launch_team_op<OpResampleMma>(in, out, n, make_shape(h, w, c, oh, ow), p, (cudaStream_t)stream);
+    if (rc != IMGTX_ERR_UNSUPPORTED) return rc;
+  }
   return launch_resample(in, out, n, make_shape(h, w, c, oh, ow), p, (cudaStream_t)stream);
 }
 
@@ -524,7 +609,15 @@ static int impl_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
     return 1;
   Shape shp = make_shape(h, w, c, h, w);
   shp.aux = sw;
-  (void)flags;   // integer arithmetic: one form (a warp- or team-per-image port measured slower: 360-545 us vs 295-348 us per pass)
+  // integer arithmetic: every form gives the same bytes.  32x32 images go through the tensor-core operator chain (sep_mma.cuh);
+  // IMGTX_CC_REPLAY_ALL keeps the scalar form (a scalar warp- or team-per-image port measured slower: 360-545 us vs 295-348 us).
+  if (h == 32 && w == 32 && !(flags & IMGTX_CC_REPLAY_ALL)) {
+    const int rc = launch_team_op<OpBoxPixelateMma>(in, out, n, shp, p, (cudaStream_t)stream, metrics_dev);
+    if (rc != IMGTX_ERR_UNSUPPORTED) {
+      *metrics_done = metrics_dev != nullptr;
+      return rc;
+    }
+  }
   return launch_image_op<OpBoxPixelate>(in, out, n, shp, p, (cudaStream_t)stream);
 }
 

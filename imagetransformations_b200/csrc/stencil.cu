@@ -10,7 +10,7 @@
 //                               horizontal box, REFLECT_101, f32 accumulate, round-half-even.
 //                               reference: pipenline/cifar_image_transformations.py:109-119 (motion_blur)
 // Roofline: nominally HBM (2 B/element); wide kernels (31 taps x 2 passes) are integer-ALU bound.
-#include "pipeline.cuh"
+#include "sep_mma.cuh"
 #include <math.h>
 #include <string.h>
 
@@ -367,6 +367,54 @@ extern "C" int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k
   return IMGTX_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// 32x32x3 images: with the REFLECT_101 border folded in, the Q8 kernel is a 32x32 byte operator per axis and both passes
+// run as integer MMAs in registers (sep_mma.cuh), whatever the tap count.  Valid when every folded weight is <= 255 and
+// the weights sum to 256 (checked on the host); same integers as the literal loop.
+struct OpCvGaussMma {
+  using Params = CvGaussParams;
+  static constexpr int kTeamWarps = 1, kInBufs = 3, kOutBufs = 0, kMaxTeams = 12, kCtasPerSm = 1;
+  static size_t team_scratch(const Shape&, const Params&) { return 0; }
+  static size_t cta_scratch(const Shape&, const Params&) { return kSepOpBytes + 2 * kSepFragBytes; }
+  __host__ __device__ static void fold_row(const Params& p, int o, int* row /* 32 */) {
+    const int r = p.ksize >> 1;
+    for (int i = 0; i < 32; ++i) row[i] = 0;
+    for (int j = 0; j < p.ksize; ++j) {
+      int i = o + j - r;
+      while (i < 0 || i >= 32) i = i < 0 ? -i : 62 - i;   // REFLECT_101
+      row[i] += p.k[j];
+    }
+  }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    int32_t* op = reinterpret_cast<int32_t*>(cta);
+    uint4* frag = reinterpret_cast<uint4*>(cta + kSepOpBytes);
+    for (int o = threadIdx.x; o < 32; o += blockDim.x) fold_row(p, o, op + o * 32);
+    __syncthreads();
+    sep_build_frags(op, frag, 0, 1, false);
+    sep_build_frags(op, frag + 64, 0, 1, true);
+  }
+  __device__ static void run(const uint8_t* in, uint8_t* out, int64_t, const Shape&, const Params&, uint8_t*,
+                             const uint8_t* cta, int tt, int) {
+    sep_cvq8_chain(in, out, reinterpret_cast<const uint4*>(cta + kSepOpBytes), tt);
+  }
+};
+
+static bool cv_mma_ok(const CvGaussParams& p) {
+  int sum = 0;
+  for (int j = 0; j < p.ksize; ++j) {
+    if (p.k[j] < 0) return false;
+    sum += p.k[j];
+  }
+  if (sum != 256 || (p.ksize >> 1) > 31) return false;
+  int row[32];
+  for (int o = 0; o < 32; ++o) {
+    OpCvGaussMma::fold_row(p, o, row);
+    for (int i = 0; i < 32; ++i)
+      if (row[i] > 255) return false;
+  }
+  return true;
+}
+
 extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
                                          double sigma, int flags, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4, "bad image shape");
@@ -380,6 +428,10 @@ extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_
   bool small_weights = true;
   for (int i = 0; i < ksize; ++i) small_weights = small_weights && p.k[i] >= 0 && p.k[i] <= 255;
   s.aux = r;
+  if (!(flags & IMGTX_CC_REPLAY_ALL) && h == 32 && w == 32 && c == 3 && r >= 1 && cv_mma_ok(p)) {
+    const int rc2 = launch_team_op<OpCvGaussMma>(in, out, n, s, p, (cudaStream_t)stream);
+    if (rc2 != IMGTX_ERR_UNSUPPORTED) return rc2;
+  }
   if (!(flags & IMGTX_CC_REPLAY_ALL) && small_weights && r >= 1 && r < std::min(h, w) && (w & 3) == 0 && (h & 3) == 0 &&
       OpCvGaussDp::per_image(s) <= 40 * 1024 && (OpCvGaussDp::row_bytes(h, r) & 3) == 0 && (OpCvGaussDp::row_bytes(w, r) & 3) == 0)
     return launch_image_op<OpCvGaussDp>(in, out, n, s, p, (cudaStream_t)stream);

@@ -429,6 +429,54 @@ extern "C" int imgtx_pgd_step_f32(const float* x, const float* x0, const float* 
   return IMGTX_OK;
 }
 
+// ---- normalize_tensor / denormalize_tensor helpers ----------------------------------------------------------------
+// (t - mean) / std and t * std + mean on (.., c, h, w) f32 tensors, torch's op order: two rounded f32 operations per
+// element (pipenline/cifar_image_transformations.py:19-25, fall_2025/AugMix.py:25-34,
+// fall_2025/tta_initial_claudeFixed.py:27-35).  8 B per element.
+template <int VEC>
+__global__ void __launch_bounds__(256)
+channel_affine_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t count, int64_t hw, int c,
+                      ChanStats st, int denorm) {
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * VEC; i < count;
+       i += (int64_t)gridDim.x * blockDim.x * VEC) {
+    const int ch = (int)((i / hw) % c);
+    const float m = st.mean[ch], s = st.std[ch];
+    if (VEC == 4) {
+      float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(x + i));
+      if (denorm) {
+        v.x = __fadd_rn(__fmul_rn(v.x, s), m); v.y = __fadd_rn(__fmul_rn(v.y, s), m);
+        v.z = __fadd_rn(__fmul_rn(v.z, s), m); v.w = __fadd_rn(__fmul_rn(v.w, s), m);
+      } else {
+        v.x = __fdiv_rn(__fsub_rn(v.x, m), s); v.y = __fdiv_rn(__fsub_rn(v.y, m), s);
+        v.z = __fdiv_rn(__fsub_rn(v.z, m), s); v.w = __fdiv_rn(__fsub_rn(v.w, m), s);
+      }
+      stg_stream_f4(reinterpret_cast<float4*>(out + i), v);
+    } else {
+      const float v = __ldg(x + i);
+      out[i] = denorm ? __fadd_rn(__fmul_rn(v, s), m) : __fdiv_rn(__fsub_rn(v, m), s);
+    }
+  }
+}
+
+extern "C" int imgtx_channel_affine_f32(const float* x, float* out, int64_t n, int c, int64_t hw,
+                                        const float* mean_host, const float* std_host, int denormalize,
+                                        imgtx_stream_t stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  IMGTX_CHECK_ARG(n >= 0 && c >= 1 && c <= 4 && hw >= 1, "bad shape (at most 4 channels)");
+  IMGTX_CHECK_ARG(mean_host && std_host, "mean / std missing");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && out, "null pointer");
+  ChanStats st;
+  for (int i = 0; i < 4; ++i) { st.mean[i] = mean_host[i < c ? i : 0]; st.std[i] = std_host[i < c ? i : 0]; }
+  const int64_t count = n * c * hw;
+  if ((hw % 4 == 0) && aligned16(x) && aligned16(out))
+    channel_affine_kernel<4><<<grid_for(count / 4), 256, 0, stream>>>(x, out, count, hw, c, st, denormalize);
+  else
+    channel_affine_kernel<1><<<grid_for(count), 256, 0, stream>>>(x, out, count, hw, c, st, denormalize);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
 extern "C" int imgtx_float_corrupt_f32(const float* x, const float* noise, float* out, int64_t count, int mode,
                                        float a, float b, int do_clamp, imgtx_stream_t stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

@@ -14,16 +14,16 @@ CIFAR100_MEAN = (0.5071, 0.4867, 0.4408)
 CIFAR100_STD = (0.2675, 0.2565, 0.2761)
 
 
+def _cuda(t):
+    return t if t.is_cuda else t.cuda()
+
+
 def denormalize_tensor(tensor, mean=CIFAR100_MEAN, std=CIFAR100_STD):
-    mean = torch.tensor(mean, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(std, device=tensor.device).view(3, 1, 1)
-    return tensor * std + mean
+    return B.channel_affine(_cuda(tensor), mean, std, True)
 
 
 def normalize_tensor(tensor, mean=CIFAR100_MEAN, std=CIFAR100_STD):
-    mean = torch.tensor(mean, device=tensor.device).view(3, 1, 1)
-    std = torch.tensor(std, device=tensor.device).view(3, 1, 1)
-    return (tensor - mean) / std
+    return B.channel_affine(_cuda(tensor), mean, std, False)
 
 
 def tensor_to_pil(tensor):

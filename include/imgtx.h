@@ -383,6 +383,13 @@ int imgtx_pgd_step_f32(const float* x, const float* x0, const float* g, float* o
                        int64_t hw, float alpha, float eps, int clamp_mode, const float* lo_host,
                        const float* hi_host, imgtx_stream_t stream);
 
+/* normalize_tensor / denormalize_tensor helpers on (n,c,hw) f32: denormalize == 0: (x - mean[ch]) / std[ch];
+   != 0: x * std[ch] + mean[ch]; two rounded f32 operations per element as torch evaluates them
+   (pipenline/cifar_image_transformations.py:19-25, fall_2025/AugMix.py:25-34,
+   fall_2025/tta_initial_claudeFixed.py:27-35). */
+int imgtx_channel_affine_f32(const float* x, float* out, int64_t n, int c, int64_t hw, const float* mean_host,
+                             const float* std_host, int denormalize, imgtx_stream_t stream);
+
 typedef enum {
   IMGTX_FC_GAUSSIAN_NOISE = 0, /* (x + (r*a + b)).clamp(0,1)        pipenline/angellic.py:34-38 */
   IMGTX_FC_BRIGHTNESS = 1,     /* (x + a).clamp(0,1)                pipenline/angellic.py:40-42 */

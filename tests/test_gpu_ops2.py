@@ -239,3 +239,27 @@ def test_cv_gaussian_blur_all_kernel_sizes(cuda, hw):
             assert np.array_equal(got, want), (ks, sigma, int((got != want).sum()))
             lit = B.cv_gaussian_blur(xd, ks, sigma, literal=True).cpu().numpy()
             assert np.array_equal(lit, want), (ks, sigma, "literal")
+
+
+@pytest.mark.parametrize("shape", [(3, 32, 32), (7, 3, 32, 32), (2, 3, 37, 53), (0, 3, 32, 32), (5, 1, 16, 16)])
+def test_normalize_denormalize_helpers(cuda, shape):
+    """normalize_tensor / denormalize_tensor (pipenline/cifar_image_transformations.py:19-25, fall_2025/AugMix.py:25-34,
+    fall_2025/tta_initial_claudeFixed.py:27-35): the kernel's two rounded f32 operations equal torch's CPU result bit for bit."""
+    B = _B()
+    from imagetransformations_b200 import AugMix, cifar_image_transformations as CT, tta_initial as TI
+    c = shape[-3]
+    mean, std = ((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010)) if c == 3 else ((0.1307,), (0.3081,))
+    x = torch.from_numpy(np.random.default_rng(3).standard_normal(shape).astype(np.float32) * 3)
+    m, s = torch.tensor(mean).view(c, 1, 1), torch.tensor(std).view(c, 1, 1)
+    for denorm, want in ((False, (x - m) / s), (True, x * s + m)):
+        got = B.channel_affine(x.cuda(), mean, std, denorm).cpu()
+        assert got.shape == x.shape and torch.equal(got, want)
+    if c == 3:
+        for mod in (AugMix, CT):
+            assert torch.equal(mod.normalize_tensor(x.cuda()).cpu(), (x - m) / s)
+            assert torch.equal(mod.denormalize_tensor(x.cuda()).cpu(), x * s + m)
+        m2, s2 = torch.tensor(TI.CIFAR100_MEAN).view(3, 1, 1), torch.tensor(TI.CIFAR100_STD).view(3, 1, 1)
+        assert torch.equal(TI.normalize_tensor(x.cuda()).cpu(), (x - m2) / s2)
+        assert torch.equal(TI.denormalize_tensor(x.cuda()).cpu(), x * s2 + m2)
+    with pytest.raises(ValueError):
+        B.channel_affine(x.cuda(), mean[:0], std, False)

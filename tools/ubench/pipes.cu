@@ -7,6 +7,7 @@ __global__ void k(double* out, int iters, double a, double b) {
   float f0 = threadIdx.x, f1 = f0 + 1, f2 = f0 + 2, f3 = f0 + 3, f4 = f0 + 4, f5 = f0 + 5, f6 = f0 + 6, f7 = f0 + 7;
   float fa = (float)a, fb = (float)b;
   unsigned u0 = threadIdx.x, u1 = u0 + 1, u2 = u0 + 2, u3 = u0 + 3, u4 = u0 + 4, u5 = u0 + 5, u6 = u0 + 6, u7 = u0 + 7, ua = (unsigned)a | 3u;
+  unsigned v0 = u0 * 3, v1 = u1 * 3, v2 = u2 * 3, v3 = u3 * 3, v4 = u4 * 3, v5 = u5 * 3, v6 = u6 * 3, v7 = u7 * 3;
   for (int i = 0; i < iters; ++i) {
     if (OP == 0) { x0 = __fma_rn(x0, a, b); x1 = __fma_rn(x1, a, b); x2 = __fma_rn(x2, a, b); x3 = __fma_rn(x3, a, b); x4 = __fma_rn(x4, a, b); x5 = __fma_rn(x5, a, b); x6 = __fma_rn(x6, a, b); x7 = __fma_rn(x7, a, b); }
     if (OP == 1) { x0 = __dadd_rn(x0, a); x1 = __dadd_rn(x1, a); x2 = __dadd_rn(x2, a); x3 = __dadd_rn(x3, a); x4 = __dadd_rn(x4, a); x5 = __dadd_rn(x5, a); x6 = __dadd_rn(x6, a); x7 = __dadd_rn(x7, a); }
@@ -27,9 +28,15 @@ __global__ void k(double* out, int iters, double a, double b) {
       asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+f"(g4), "+f"(g5), "+f"(g6), "+f"(g7) : "r"(u0), "r"(u1), "r"(u2), "r"(u3), "r"(u6), "r"(u7));
       x0 = g0; x1 = g1; x2 = g2; x3 = g3; x4 = g4; x5 = g5; x6 = g6; x7 = g7;
     }
+    if (OP == 13) {   // 4 independent IMMA m16n8k32 u8 x s8 -> s32 per iteration
+      asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+r"(u0), "+r"(u1), "+r"(u2), "+r"(u3) : "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua));
+      asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+r"(u4), "+r"(u5), "+r"(u6), "+r"(u7) : "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua));
+      asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+r"(v0), "+r"(v1), "+r"(v2), "+r"(v3) : "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua));
+      asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};" : "+r"(v4), "+r"(v5), "+r"(v6), "+r"(v7) : "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua), "r"(ua));
+    }
     if (OP == 7) { f0 = __log2f(f0) + fa; f1 = __log2f(f1) + fa; f2 = __log2f(f2) + fa; f3 = __log2f(f3) + fa; f4 = __log2f(f4) + fa; f5 = __log2f(f5) + fa; f6 = __log2f(f6) + fa; f7 = __log2f(f7) + fa; }  // MUFU + FADD
   }
-  out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + f0 + f1 + f2 + f3 + f4 + f5 + f6 + f7 + u0 + u1 + u2 + u3 + u4 + u5 + u6 + u7;
+  out[blockIdx.x * blockDim.x + threadIdx.x] = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7 + f0 + f1 + f2 + f3 + f4 + f5 + f6 + f7 + u0 + u1 + u2 + u3 + u4 + u5 + u6 + u7 + v0 + v1 + v2 + v3 + v4 + v5 + v6 + v7;
 }
 template <int OP>
 void run(const char* name, int ops_per_iter, double* out) {
@@ -50,6 +57,7 @@ int main() {
   run<0>("DFMA", 1, out); run<1>("DADD", 1, out); run<2>("FFMA", 1, out); run<3>("IMAD", 1, out); run<4>("IMAD.HI(+IADD)", 1, out);
   run<8>("IDP.2A/4A", 1, out); run<9>("IMAD.WIDE (x4 per 8)", 1, out); run<10>("FADD.RD", 1, out); run<11>("PRMT", 1, out);
   run<12>("HMMA.16816.F32 (4/iter: lane-ops = warp-MMAs*32/8*...)", 1, out);
+  run<13>("IMMA.16832.S32 u8xs8 (4/iter)", 1, out);
   run<5>("F2I+I2F+FADD (3 ops)", 3, out); run<6>("LOP3+SHF+IADD (3 ops)", 3, out); run<7>("MUFU.LG2+FADD (2 ops)", 2, out);
   printf("%s\n", cudaGetErrorString(cudaDeviceSynchronize()));
   return 0;
