@@ -691,13 +691,24 @@ struct OpTElastic : ElasticCommon {
   static constexpr int kTT = kTeamWarps * 32;
   static constexpr int kPA = 40;            // pitch (halves) of the fp16 operator / field rows: conflict-free fragment loads
   static constexpr int kLutLo = 64, kLut = 160;   // index tables cover [-64, 96)
-  // CTA: Ah, Al [32][40] half | refl101 row (x256) and col (x8) offsets for the canvas | reflect row (x512) / col (x16) for W
+  // Shared-memory traffic bounds this kernel (ncu: 125 M wavefronts per 50 000 images before the layouts below), so:
+  //   * index tables hold the byte offsets of i AND i + 1 in one word (one load per axis, not two);
+  //   * the fp16 canvas skips one 8-byte slot after every 16 pixels (row pitch 272 B): a lane expands four pixels (32 B), and
+  //     with the skew the 16 lanes of a store wavefront fall into 16 different bank pairs (was a 4-way conflict);
+  //   * the displacement rows have a pitch of 40 floats: the accumulator fragments store without bank conflicts;
+  //   * the warped image W is kept as three Q7 half-words per pixel (8 bytes, not a float4): 0x8000 | round(128 v) planted
+  //     under the exponent byte 0x43 IS the float 256 + v (one PRMT per tap and channel), and since the bilinear weights
+  //     sum to 1 the blend comes out as 256 + result, whose integer part has floor(result) in its low byte.  The Q7
+  //     rounding (<= 2^-8 of an LSB) is far inside the fast contract.
+  // CTA: Ah, Al [32][40] half | refl101 row / col offset pairs for the canvas | reflect row / col offset pairs for W
   static size_t cta_scratch(const Shape&, const Params&) { return 2 * 32 * kPA * 2 + 4 * kLut * 4; }
-  // team: Mi (6 f64) + tables (128 int) | canvas [1024] x 8 B | DXY [2][32][32] f32 | W [1024] float4 | FT hi (, lo) [2][32][40] half
+  // team: Mi (6 f64) + tables (128 int) | canvas [32][34] x 8 B | DXY [2][32][40] f32 | W [1024] x 8 B | FT hi (, lo) [2][32][40] half
   // (the canvas has its own region so that it is built WHILE the tensor-core warps smooth the fields)
-  static constexpr int kOffTab = 64, kOffCanvas = 64 + 512, kOffDXY = kOffCanvas + 8192, kOffW = kOffDXY + 8192, kOffFT = kOffW + 16384;
+  static constexpr int kPD = 40;
+  static constexpr int kOffTab = 64, kOffCanvas = 64 + 512, kOffDXY = kOffCanvas + 32 * 272, kOffW = kOffDXY + 2 * 32 * kPD * 4,
+                       kOffFT = kOffW + 8192;
   static size_t team_scratch(const Shape&, const Params& p) {
-    return WARP_ONLY ? kOffCanvas + 8192 : kOffFT + (p.e.ux ? 10240 : 5120);
+    return WARP_ONLY ? kOffCanvas + 32 * 272 : kOffFT + (p.e.ux ? 10240 : 5120);
   }
 
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
@@ -717,8 +728,12 @@ struct OpTElastic : ElasticCommon {
     }
     for (int e = threadIdx.x; e < kLut; e += blockDim.x) {
       const int i = e - kLutLo;
-      const int r101 = reflect101(i, 32), rh = reflect_half(i, 32);
-      lut[e] = r101 * 256; lut[kLut + e] = r101 * 8; lut[2 * kLut + e] = rh * 512; lut[3 * kLut + e] = rh * 16;
+      const int r0 = reflect101(i, 32), r1 = reflect101(i + 1, 32), h0 = reflect_half(i, 32), h1 = reflect_half(i + 1, 32);
+      auto ccol = [](int c) { return c * 8 + (c >> 4) * 8; };
+      lut[e] = (r0 * 272) | ((r1 * 272) << 16);
+      lut[kLut + e] = ccol(r0) | (ccol(r1) << 16);
+      lut[2 * kLut + e] = (h0 * 256) | ((h1 * 256) << 16);
+      lut[3 * kLut + e] = (h0 * 8) | ((h1 * 8) << 16);
     }
   }
 
@@ -799,7 +814,7 @@ struct OpTElastic : ElasticCommon {
       if (tt == 0) inverse_matrix_fast(p.e, rng, img, Mi);
       const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
       uint2* c2 = reinterpret_cast<uint2*>(canvas);
-      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+      for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q + (q >> 2));
       team_sync<8>(team);
       if (tt < 64) affine_tables(Mi, 32, 32, tab, tt);
     }
@@ -842,7 +857,7 @@ struct OpTElastic : ElasticCommon {
     if (!WARP_ONLY && wq >= 5) {
       const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
       uint2* c2 = reinterpret_cast<uint2*>(canvas);
-      for (int q = tt - 160; q < 256; q += 96) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q);
+      for (int q = tt - 160; q < 256; q += 96) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q + (q >> 2));
     }
     if (!WARP_ONLY && wq < 4) {
       // ---- smoothing on the tensor cores: warp = (field, 16 output rows); warps 4-7 go straight to the barrier ----
@@ -889,11 +904,11 @@ struct OpTElastic : ElasticCommon {
           mma16816(c2[nt], gh, Al32[b], Al32[b + 4]);
         }
       }
-      float* D = DXY + f * 1024 + (16 * mt + g) * 32 + 2 * t;
+      float* D = DXY + (f * 32 + 16 * mt + g) * kPD + 2 * t;
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
         *reinterpret_cast<float2*>(D + 8 * nt) = make_float2(__fmul_rn(c2[nt][0], p.alpha), __fmul_rn(c2[nt][1], p.alpha));
-        *reinterpret_cast<float2*>(D + 8 * nt + 256) = make_float2(__fmul_rn(c2[nt][2], p.alpha), __fmul_rn(c2[nt][3], p.alpha));
+        *reinterpret_cast<float2*>(D + 8 * nt + 8 * kPD) = make_float2(__fmul_rn(c2[nt][2], p.alpha), __fmul_rn(c2[nt][3], p.alpha));
       }
     }
     team_sync<8>(team);   // displacements, tables and canvas are ready
@@ -910,7 +925,8 @@ struct OpTElastic : ElasticCommon {
       // weights in 1/1024 units as exact floats, scaled by 2^-10: w11 = fx fy, w10 = fy (32 - fx), ...
       const float w11 = fx * fy * 0.0009765625f, w10 = fy * 0.03125f - w11, w01 = fx * 0.03125f - w11,
                   w00 = 1.0f - fx * 0.03125f - w10;
-      const int ra = lrow[sy], rb = lrow[sy + 1], ca = lcol[sx], cb = lcol[sx + 1];
+      const int rr2 = lrow[sy], cc2 = lcol[sx];
+      const int ra = rr2 & 0xFFFF, rb = rr2 >> 16, ca = cc2 & 0xFFFF, cb = cc2 >> 16;
       const uint2 p00 = *reinterpret_cast<const uint2*>(canvas + ra + ca), p01 = *reinterpret_cast<const uint2*>(canvas + ra + cb);
       const uint2 p10 = *reinterpret_cast<const uint2*>(canvas + rb + ca), p11 = *reinterpret_cast<const uint2*>(canvas + rb + cb);
       const float2 a00 = __half22float2(*reinterpret_cast<const __half2*>(&p00.x)), a01 = __half22float2(*reinterpret_cast<const __half2*>(&p01.x));
@@ -924,7 +940,10 @@ struct OpTElastic : ElasticCommon {
         uint8_t* o = dst + (y * 32 + lane) * 3;
         o[0] = (uint8_t)floor_bits(r); o[1] = (uint8_t)floor_bits(gg); o[2] = (uint8_t)floor_bits(b);
       } else {
-        *reinterpret_cast<float4*>(Wb + (y * 32 + lane) * 16) = make_float4(r, gg, b, 0.0f);
+        const float kq = 8388608.0f + 32768.0f;   // low half-word of the sum: 0x8000 | round(128 v)
+        const uint32_t qr = __float_as_uint(__fmaf_rn(r, 128.0f, kq)), qg = __float_as_uint(__fmaf_rn(gg, 128.0f, kq)),
+                       qb = __float_as_uint(__fmaf_rn(b, 128.0f, kq));
+        *reinterpret_cast<uint2*>(Wb + (y * 32 + lane) * 8) = make_uint2(__byte_perm(qr, qg, 0x5410u), qb);
       }
     }
     if (WARP_ONLY) return;
@@ -935,19 +954,24 @@ struct OpTElastic : ElasticCommon {
     const float xb = (float)(lane + kLutLo);
 #pragma unroll 2
     for (int y = wq; y < 32; y += kTeamWarps) {
-      const float yy = (float)(y + kLutLo) + DXY[1024 + y * 32 + lane], xx = xb + DXY[y * 32 + lane];
+      const float yy = (float)(y + kLutLo) + DXY[(32 + y) * kPD + lane], xx = xb + DXY[y * kPD + lane];
       const float ry = __fadd_rd(yy, 8388608.0f), rx = __fadd_rd(xx, 8388608.0f);
       const float ty = yy - (ry - 8388608.0f), tx = xx - (rx - 8388608.0f);
       const int iy = min((int)(__float_as_uint(ry) & 255u), kLut - 2), ix = min((int)(__float_as_uint(rx) & 255u), kLut - 2);
-      const int ra = hrow[iy], rb = hrow[iy + 1], ca = hcol[ix], cb = hcol[ix + 1];
-      const float4 q00 = *reinterpret_cast<const float4*>(Wb + ra + ca), q01 = *reinterpret_cast<const float4*>(Wb + ra + cb);
-      const float4 q10 = *reinterpret_cast<const float4*>(Wb + rb + ca), q11 = *reinterpret_cast<const float4*>(Wb + rb + cb);
+      const int rr2 = hrow[iy], cc2 = hcol[ix];
+      const int ra = rr2 & 0xFFFF, rb = rr2 >> 16, ca = cc2 & 0xFFFF, cb = cc2 >> 16;
+      const uint2 q00 = *reinterpret_cast<const uint2*>(Wb + ra + ca), q01 = *reinterpret_cast<const uint2*>(Wb + ra + cb);
+      const uint2 q10 = *reinterpret_cast<const uint2*>(Wb + rb + ca), q11 = *reinterpret_cast<const uint2*>(Wb + rb + cb);
       const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
-      const float r = __fmaf_rn(q11.x, w11, __fmaf_rn(q10.x, w10, __fmaf_rn(q01.x, w01, q00.x * w00)));
-      const float gg = __fmaf_rn(q11.y, w11, __fmaf_rn(q10.y, w10, __fmaf_rn(q01.y, w01, q00.y * w00)));
-      const float b = __fmaf_rn(q11.z, w11, __fmaf_rn(q10.z, w10, __fmaf_rn(q01.z, w01, q00.z * w00)));
+      // half-word h under the exponent byte 0x43: the float 256 + (h & 0x7FFF) / 128
+      auto lo = [](uint32_t w) { return __uint_as_float(__byte_perm(w, 0x43000000u, 0x7104u)); };
+      auto hi = [](uint32_t w) { return __uint_as_float(__byte_perm(w, 0x43000000u, 0x7324u)); };
+      const float r = __fmaf_rn(lo(q11.x), w11, __fmaf_rn(lo(q10.x), w10, __fmaf_rn(lo(q01.x), w01, lo(q00.x) * w00)));
+      const float gg = __fmaf_rn(hi(q11.x), w11, __fmaf_rn(hi(q10.x), w10, __fmaf_rn(hi(q01.x), w01, hi(q00.x) * w00)));
+      const float b = __fmaf_rn(lo(q11.y), w11, __fmaf_rn(lo(q10.y), w10, __fmaf_rn(lo(q01.y), w01, lo(q00.y) * w00)));
+      // the sums are 256 + value: the low byte of the integer part is floor(value)
       uint8_t* o = dst + (y * 32 + lane) * 3;
-      o[0] = (uint8_t)floor_bits(fmaxf(r, 0.0f)); o[1] = (uint8_t)floor_bits(fmaxf(gg, 0.0f)); o[2] = (uint8_t)floor_bits(fmaxf(b, 0.0f));
+      o[0] = (uint8_t)floor_bits(fmaxf(r, 256.0f)); o[1] = (uint8_t)floor_bits(fmaxf(gg, 256.0f)); o[2] = (uint8_t)floor_bits(fmaxf(b, 256.0f));
     }
   }
 };
