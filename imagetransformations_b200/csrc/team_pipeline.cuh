@@ -98,12 +98,31 @@ team_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n
       else __syncwarp();
       const uint32_t* d32 = reinterpret_cast<const uint32_t*>(dst);
       uint32_t c0 = 0, c1 = 0;
-      for (int i = tt; i < (s.out_bytes >> 2); i += TT) checksum_word(d32[i], (uint32_t)i, c0, c1);
+      if (768 % TT == 0 && s.out_bytes == 3072) {
+        // CIFAR images: thread tt owns words [tt WPL, (tt + 1) WPL), so the weight of a byte inside the thread's run is
+        // 4 k + t + 1 <= 96 and fits a dp4a weight: two IDP.4A per word, vector loads
+        constexpr int WPL = 768 % TT == 0 ? 768 / TT : 4;
+        constexpr int V = WPL % 4 == 0 ? 4 : (WPL % 2 == 0 ? 2 : 1);
+        const uint32_t* base = d32 + tt * WPL;
+        uint32_t Cw = 0;
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
-        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        for (int q = 0; q < WPL / V; ++q) {
+          uint32_t w[4];
+          if (V == 4) { const uint4 v = reinterpret_cast<const uint4*>(base)[q]; w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
+          else if (V == 2) { const uint2 v = reinterpret_cast<const uint2*>(base)[q]; w[0] = v.x; w[1] = v.y; }
+          else w[0] = base[q];
+#pragma unroll
+          for (int e = 0; e < V; ++e) {
+            c0 = __dp4a(w[e], 0x01010101u, c0);
+            Cw = __dp4a(w[e], 0x04030201u + (uint32_t)(q * V + e) * 0x04040404u, Cw);
+          }
+        }
+        c1 = Cw + 4u * (uint32_t)(tt * WPL) * c0;
+      } else {
+        for (int i = tt; i < (s.out_bytes >> 2); i += TT) checksum_word(d32[i], (uint32_t)i, c0, c1);
       }
+      c0 = __reduce_add_sync(0xffffffffu, c0);   // REDUX: one instruction per sum instead of a five-level shuffle tree
+      c1 = __reduce_add_sync(0xffffffffu, c1);
       if ((tt & 31) == 0) reinterpret_cast<uint2*>(base + 64)[tt >> 5] = make_uint2(c0, c1);
     }
     fence_async_smem();

@@ -17,17 +17,18 @@ def main():
     x = torch.from_numpy(np.random.default_rng(1001).integers(0, 256, (n, 32, 32, 3), dtype=np.uint8)).cuda()
     outs = [torch.empty_like(x) for _ in range(3)]
     peak = 6551.7
+    mt = torch.zeros((n, 2), dtype=torch.int32, device="cuda") if os.environ.get("METRICS") else None
     res = {}
     for name in names:
         for sev in range(1, 6):
             for r in range(3):
-                C.corrupt(x, name, sev, seed=r, out=outs[r % 3])
+                C.corrupt(x, name, sev, seed=r, out=outs[r % 3], metrics=mt)
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             reps = 10
             a.record()
             for r in range(reps):
-                C.corrupt(x, name, sev, seed=r, out=outs[r % 3])
+                C.corrupt(x, name, sev, seed=r, out=outs[r % 3], metrics=mt)
             b.record()
             torch.cuda.synchronize()
             us = a.elapsed_time(b) / reps * 1e3
