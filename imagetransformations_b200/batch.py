@@ -418,10 +418,21 @@ def noise_injected(x: torch.Tensor, kind: int, draws, param: float = 0.0, out=No
 
 
 def noise_philox(x: torch.Tensor, kind: int, param: float, seed: int, out=None) -> torch.Tensor:
-    """Throughput mode: draws generated on chip (Philox4x32-10)."""
+    """Throughput mode: draws generated on chip (Philox4x32-10).  Gaussian noise on bytes is "add floor(std Z), clip" — one
+    discrete law — so it is sampled in the output domain through a Walker alias table (one Philox word, one lookup per
+    element; transformation.py:272-281) whenever the table exists (std <= 39); Box-Muller otherwise."""
     x = _check_u8(x)
     n, h, w, c = x.shape
     out = torch.empty_like(x) if out is None else out
+    if kind in (L.NOISE_GAUSS_F32, L.NOISE_GAUSS_F64) and param > 0 and (n * h * w * c) % 4 == 0:
+        from .cifar_c import noise_alias_table
+        tab = noise_alias_table(L.CC_GAUSSIAN, float(param) / 255.0, x.device)
+        if tab is not None:
+            with torch.cuda.device_of(x):
+                L.check(L.load().imgtx_cc_noise_onchip_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, L.CC_GAUSSIAN,
+                                                          tab.data_ptr(), tab.numel(), int(seed) & 0xFFFFFFFFFFFFFFFF, 0, None,
+                                                          _stream()))
+            return out
     L.check(L.load().imgtx_noise_philox_u8(x.data_ptr(), out.data_ptr(), n, h, w, c, kind, float(param),
                                            int(seed) & 0xFFFFFFFFFFFFFFFF, _stream()))
     return out

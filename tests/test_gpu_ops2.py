@@ -263,3 +263,27 @@ def test_normalize_denormalize_helpers(cuda, shape):
         assert torch.equal(TI.denormalize_tensor(x.cuda()).cpu(), x * s2 + m2)
     with pytest.raises(ValueError):
         B.channel_affine(x.cuda(), mean[:0], std, False)
+
+
+def test_noise_philox_gaussian_law_matches_injected_draws(cuda):
+    """apply_gaussian_noise in throughput mode (alias-table sampling in the output domain) against the reference's own
+    arithmetic on numpy draws (transformation.py:272-281): per input value, the output histograms of two independent
+    ensembles agree (two-sample chi-square, z < 6), including the clipped ends."""
+    B = _B()
+    from imagetransformations_b200 import _lib as L
+    vals = np.array([0, 3, 17, 128, 200, 250, 255], np.uint8)
+    n = 1500
+    x = np.repeat(vals, n * 1024 * 3 // len(vals) + 1)[: n * 1024 * 3].reshape(n, 32, 32, 3)
+    for std in (0.02, 0.1):
+        got = B.noise_philox(_cu(x), L.NOISE_GAUSS_F32, std * 255.0, seed=11).cpu().numpy()
+        rs = np.random.RandomState(12)
+        want = O.gaussian_noise_f32(x, rs.normal(0, std * 255, x.shape).astype(np.float32))
+        for v in vals:
+            m = x == v
+            ha = np.bincount(got[m], minlength=256).astype(np.float64)
+            hb = np.bincount(want[m], minlength=256).astype(np.float64)
+            keep = (ha + hb) >= 20
+            chi = (((ha - hb) ** 2) / np.maximum(ha + hb, 1))[keep].sum()
+            dof = keep.sum() - 1
+            z = (chi - dof) / np.sqrt(2 * dof)
+            assert z < 6, (std, int(v), chi, dof)
