@@ -237,7 +237,7 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     passes = C.suite_passes()
-    no_epilogue = {"jpeg_compression"}      # the one kernel still on the group pipeline: its metric is one extra launch
+    no_epilogue = set()                     # every pass writes its per-image metric from its own epilogue
     launches_per_step = len(passes) + sum(1 for p in passes if p[0] in no_epilogue)
     peak, peak_src = peaks()
 

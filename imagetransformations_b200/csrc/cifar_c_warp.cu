@@ -982,6 +982,7 @@ struct OpTElastic : ElasticCommon {
 struct JpegParams {
   int16_t q[2][64];   // luma, chroma quantisation tables (natural order)
   uint32_t rq[2][64]; // floor(2^32 / (8 q)) + 1: (n * rq) >> 32 == n / (8 q) exactly for n < 2^17 (excess < n * 2^-32 < 1 / (8 q))
+  uint2* metrics;     // device (n) per-image {sum, weighted sum} of the output bytes, or nullptr
 };
 
 #define JFIX(x) ((int)((x) * 8192 + 0.5))
@@ -1056,7 +1057,7 @@ struct OpCcJpeg : NoSpill {
   }
 
   template <bool STAGED>
-  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t, const Shape& s, const Params& p,
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
                              uint8_t* scratch, uint8_t*) {
     const int tid = threadIdx.x;
     const int h = s.h, w = s.w, hw = h * w, ch = h >> 1, cw = w >> 1, pw = w + 1, pcw = cw + 1;
@@ -1176,6 +1177,19 @@ struct OpCcJpeg : NoSpill {
       o[1] = clip8(Y + ((-22554 * cbv - 46802 * crv + 32768) >> 16));
       o[2] = clip8(Y + ((116130 * cbv + 32768) >> 16));
     }
+    if (p.metrics) {
+      // per-image metric from the finished group (still in shared memory when staged): one warp per image
+      __syncthreads();
+      const int lane = tid & 31;
+      for (int j = tid >> 5; j < g; j += kThreads / 32) {
+        const uint32_t* d32 = reinterpret_cast<const uint32_t*>(dst + (size_t)j * s.out_bytes);
+        uint32_t c0 = 0, c1 = 0;
+        for (int i = lane; i < (s.out_bytes >> 2); i += 32) checksum_word(d32[i], (uint32_t)i, c0, c1);
+        c0 = __reduce_add_sync(0xffffffffu, c0);
+        c1 = __reduce_add_sync(0xffffffffu, c1);
+        if (lane == 0) p.metrics[img0 + j] = make_uint2(c0, c1);
+      }
+    }
   }
 };
 
@@ -1226,6 +1240,8 @@ static int impl_cc_jpeg_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, in
       p.rq[t][i] = (uint32_t)((1ull << 32) / (uint64_t)(8 * v)) + 1u;
     }
   (void)flags;   // integer arithmetic: one form (a warp- or team-per-image port measured slower: 610-640 us vs 472 us per pass)
+  p.metrics = reinterpret_cast<uint2*>(metrics_dev);
+  *metrics_done = true;
   return launch_image_op<OpCcJpeg>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, 0, 80 * 1024);
 }
 

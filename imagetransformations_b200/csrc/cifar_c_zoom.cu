@@ -40,8 +40,8 @@ zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int6
   const int img_bytes = P * 3, ib = (int)align_up((size_t)img_bytes, 128);
   constexpr int cb = kZoomCanvas;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem);
-  uint2* msum = reinterpret_cast<uint2*>(smem + 256);        // per-warp metric partials (32 x 8 B)
-  uint8_t* in_buf = smem + 512;
+  uint2* msum = reinterpret_cast<uint2*>(smem + 256);        // per-warp metric partials (2 parities x 32 x 8 B)
+  uint8_t* in_buf = smem + 768;
   uint8_t* canvas = in_buf + kZoomRing * ib;                   // 2 x P x half4
   uint8_t* out_buf = canvas + 2 * cb;                          // 2 x ib
   const int tid = threadIdx.x;
@@ -145,24 +145,17 @@ zoom_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int6
     }
     if (metrics) {   // per-image metric (see team_pipeline.cuh:checksum_word) from the bytes this thread just produced
       uint32_t c0 = b0 + b1 + b2, c1 = (3u * (uint32_t)tid + 1u) * c0 + b1 + 2u * b2;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
-        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
-      }
-      if ((tid & 31) == 0) msum[tid >> 5] = make_uint2(c0, c1);
+      c0 = __reduce_add_sync(0xffffffffu, c0);
+      c1 = __reduce_add_sync(0xffffffffu, c1);
+      if ((tid & 31) == 0) msum[PAR * 32 + (tid >> 5)] = make_uint2(c0, c1);
     }
     fence_async_smem();
     if (tid == 0) bulk_wait_read<0>();   // the store of the previous image has finished reading the other output buffer
     __syncthreads();
-    if (metrics && tid < 32) {
-      uint2 m = msum[tid];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        m.x += __shfl_xor_sync(0xffffffffu, m.x, o);
-        m.y += __shfl_xor_sync(0xffffffffu, m.y, o);
-      }
-      if (tid == 0) metrics[img] = m;
+    if (metrics && (tid >> 5) == 1) {   // warp 1: warp 0 has the copies to issue; the partials are double-buffered by parity
+      const uint2 m = msum[PAR * 32 + (tid & 31)];
+      const uint32_t mx = __reduce_add_sync(0xffffffffu, m.x), my = __reduce_add_sync(0xffffffffu, m.y);
+      if ((tid & 31) == 0) metrics[img] = make_uint2(mx, my);
     }
     if (tid == 0) {
       bulk_s2g(out + img * img_bytes, ob, (uint32_t)img_bytes);
@@ -188,7 +181,7 @@ template <int T>
 static int launch_zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int P, const int32_t* indptr, const int32_t* indices,
                             const float* weights, uint32_t* metrics, cudaStream_t stream) {
   const size_t ib = align_up((size_t)P * 3, 128);
-  const size_t smem = 512 + kZoomRing * ib + 2 * (size_t)kZoomCanvas + 2 * ib;
+  const size_t smem = 768 + kZoomRing * ib + 2 * (size_t)kZoomCanvas + 2 * ib;
   auto kern = zoom_fast_kernel<T>;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t grid = std::min<int64_t>(n, sm_count());
