@@ -63,6 +63,8 @@ _PROTOS = {
     "imgtx_resize_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
     "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _int, _vp],
+    "imgtx_noalloc_scratch_bytes": [],
+    "imgtx_cv_gaussian_blur_noalloc_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _vp],
     "imgtx_pil_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _f, _vp],
     "imgtx_box_filter_h_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp],
     "imgtx_pil_transform_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _int, _int, _vp, _vp, _vp, _vp],
@@ -100,7 +102,7 @@ _PROTOS = {
     "imgtx_mean_views_f32": [_vp, _vp, _i64, _int, _vp],
 }
 _RESTYPES = {"imgtx_last_error": C.c_char_p, "imgtx_resample_table_words": C.c_int64,
-             "imgtx_cc_noise_table_words": C.c_int64}
+             "imgtx_cc_noise_table_words": C.c_int64, "imgtx_noalloc_scratch_bytes": C.c_int64}
 
 
 def load():

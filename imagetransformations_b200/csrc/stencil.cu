@@ -467,3 +467,67 @@ extern "C" int imgtx_box_filter_h_u8(const uint8_t* in, uint8_t* out, int64_t n,
   p.kv = (float)(1.0 / size);
   return launch_image_op<OpBoxH>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------------
+// imgtx_cv_gaussian_blur_noalloc_u8: the literal cv2.GaussianBlur path (OpCvGauss through direct_kernel, u16 intermediate
+// in global memory) for callers that may not allocate: CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc.  No counterpart in the reference.  The u16 intermediate planes
+// (2*h*w*c bytes per resident CTA) live in the file-scope device array below instead of a cudaMallocAsync workspace.
+//   * The array is kNoAllocScratchBytes (32 MiB) on EVERY GPU that loads the library, until the process exits.
+//   * Nothing in it has to start at zero: the row pass writes every element of a CTA's slice before the column pass reads
+//     it, so the previous call's contents are never observed.
+//   * Every call on a device shares the array: calls that overlap on the GPU (different streams, or graph branches that
+//     run side by side) race.  Serialise them on one stream.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol; the device address comes from cudaGetSymbolAddress,
+// looked up once per device with that device current.
+constexpr size_t kNoAllocScratchBytes = 32u << 20;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) uint8_t g_noalloc_scratch[kNoAllocScratchBytes];
+
+#include <mutex>
+static int noalloc_scratch_ptr(uint8_t** ptr) {
+  static std::mutex mu;
+  static uint8_t* cache[kNoAllocMaxDevices] = {nullptr};
+  int dev = -1;
+  IMGTX_CUDA_OK(cudaGetDevice(&dev));
+  IMGTX_CHECK_ARG(dev >= 0 && dev < kNoAllocMaxDevices, "device ordinal %d outside the scratch table (%d)", dev, kNoAllocMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!cache[dev]) {
+    void* p = nullptr;
+    IMGTX_CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // the current device's instance of the array
+    IMGTX_CHECK_ARG(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    cache[dev] = static_cast<uint8_t*>(p);
+  }
+  *ptr = cache[dev];
+  return IMGTX_OK;
+}
+
+extern "C" int64_t imgtx_noalloc_scratch_bytes(void) { return (int64_t)kNoAllocScratchBytes; }
+
+extern "C" int imgtx_cv_gaussian_blur_noalloc_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
+                                                 double sigma, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4 && n >= 0, "bad image shape");
+  CvGaussParams p;
+  memset(&p, 0, sizeof(p));
+  p.ksize = ksize;
+  int rc = imgtx_cv_gaussian_kernel_host(ksize, sigma, p.k);
+  if (rc) return rc;
+  const Shape s = make_shape(h, w, c, h, w);
+  const size_t per_cta = align_up(OpCvGauss::gtmp_bytes(s), 256);
+  if (per_cta > kNoAllocScratchBytes) {
+    set_error("image %dx%dx%d needs %zu bytes of scratch for its 16-bit intermediate; the allocation-free entry point "
+              "holds %zu bytes (use imgtx_cv_gaussian_blur_u8 for larger images)", h, w, c, per_cta, kNoAllocScratchBytes);
+    return IMGTX_ERR_INVALID_ARGUMENT;
+  }
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in != nullptr && out != nullptr, "null image pointer");
+  uint8_t* scratch = nullptr;
+  rc = noalloc_scratch_ptr(&scratch);
+  if (rc) return rc;
+  int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 8);
+  grid = std::min<int64_t>(grid, (int64_t)(kNoAllocScratchBytes / per_cta));
+  const size_t smem = OpCvGauss::scratch_bytes_spilled(s);
+  direct_kernel<OpCvGauss><<<(unsigned)grid, OpCvGauss::kThreads, smem, (cudaStream_t)stream>>>(in, out, n, s, p, scratch, per_cta);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}

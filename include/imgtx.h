@@ -166,6 +166,16 @@ int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);
 /* cv2.GaussianBlur(img, (ksize, ksize), sigma) on uint8 — transformation.py:228-257 (apply_blur) */
 int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
                               double sigma, int flags, imgtx_stream_t stream);
+/* Allocation-free variant of imgtx_cv_gaussian_blur_u8 (same bytes out).  No counterpart in the reference: added
+   for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+   harnesses that forbid it).  The 16-bit intermediate planes live in a static device array of
+   imgtx_noalloc_scratch_bytes() = 32 MiB that every GPU loading the library holds until exit; the call performs no
+   cudaMalloc / cudaFree / allocating library call.  Limit: 2*h*w*c (rounded up to 256) must not exceed that size, else
+   IMGTX_ERR_INVALID_ARGUMENT.  All calls on a device share the array (nothing in it needs clearing between calls), so
+   calls that overlap on the GPU race: issue them on one stream. */
+int64_t imgtx_noalloc_scratch_bytes(void);
+int imgtx_cv_gaussian_blur_noalloc_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int ksize,
+                                      double sigma, imgtx_stream_t stream);
 /* img.filter(ImageFilter.GaussianBlur(radius)) — pipenline/cifar_image_transformations.py:72-77 */
 int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float radius,
                                imgtx_stream_t stream);
