@@ -337,40 +337,33 @@ struct OpBoxPixelateMma {
   using Params = BoxPixParams;
   static constexpr int kTeamWarps = 1, kInBufs = 3, kOutBufs = 0, kMaxTeams = 12, kCtasPerSm = 1;
   static size_t team_scratch(const Shape&, const Params&) { return 0; }
-  static size_t cta_scratch(const Shape&, const Params&) { return kSepOpBytes + 8 * kSepFragBytes; }
-  __device__ static void fill_down(int32_t* op, const uint8_t* lo, const uint8_t* lo1, const int32_t* k0, const int32_t* k1, int size) {
+  static size_t cta_scratch(const Shape&, const Params&) { return kSepOpBytes + 6 * kSepFragBytes; }
+  // The up-sampling passes are selections (unit taps), and a selection commutes with the rounding of the pass before it:
+  // out[yo][xo] = B[ymap[yo]][xmap[xo]] with B = round(Dv round(X Dh^T)).  So row o of the composed operator is row map[o]
+  // of the down-sampling operator, and the four Pillow passes are TWO 32x32 stages.
+  __device__ static void fill(int32_t* op, const uint8_t* map, const uint8_t* lo, const uint8_t* lo1, const int32_t* k0,
+                              const int32_t* k1) {
     for (int i = threadIdx.x; i < 1024; i += blockDim.x) op[i] = 0;
     __syncthreads();
-    for (int o = threadIdx.x; o < size; o += blockDim.x) {
-      op[o * 32 + lo[o]] = k0[o];
-      if (lo1[o] != lo[o]) op[o * 32 + lo1[o]] = k1[o];
+    for (int o = threadIdx.x; o < 32; o += blockDim.x) {
+      const int m = map[o];
+      op[o * 32 + lo[m]] = k0[m];
+      if (lo1[m] != lo[m]) op[o * 32 + lo1[m]] = k1[m];
     }
-    __syncthreads();
-  }
-  __device__ static void fill_up(int32_t* op, const uint8_t* map) {
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) op[i] = 0;
-    __syncthreads();
-    for (int o = threadIdx.x; o < 32; o += blockDim.x) op[o * 32 + map[o]] = 1 << 22;
     __syncthreads();
   }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
     int32_t* op = reinterpret_cast<int32_t*>(cta);
     uint4* frag = reinterpret_cast<uint4*>(cta + kSepOpBytes);
-    fill_down(op, p.hlo, p.hlo1, p.hk0, p.hk1, p.sw);
+    fill(op, p.xmap, p.hlo, p.hlo1, p.hk0, p.hk1);
     sep_build_frags(op, frag, 0, 3, false);
     __syncthreads();
-    fill_down(op, p.vlo, p.vlo1, p.vk0, p.vk1, p.sh);
+    fill(op, p.ymap, p.vlo, p.vlo1, p.vk0, p.vk1);
     sep_build_frags(op, frag + 3 * 64, 0, 3, true);
-    __syncthreads();
-    fill_up(op, p.xmap);
-    sep_build_frags(op, frag + 6 * 64, 2, 1, true);
-    __syncthreads();
-    fill_up(op, p.ymap);
-    sep_build_frags(op, frag + 7 * 64, 2, 1, true);
   }
   __device__ static void run(const uint8_t* in, uint8_t* out, int64_t, const Shape&, const Params&, uint8_t*,
                              const uint8_t* cta, int tt, int) {
-    sep_q22_chain<3, 3, 1, 1>(in, out, reinterpret_cast<const uint4*>(cta + kSepOpBytes), tt);
+    sep_q22_chain<3, 3, 0, 0>(in, out, reinterpret_cast<const uint4*>(cta + kSepOpBytes), tt);
   }
 };
 

@@ -11,7 +11,7 @@
 //   * the accumulator fragment of a stage IS the B fragment of the next stage up to a fixed permutation of the contraction
 //     index (a lane holds C[m][2t], C[m][2t+1] of every 8-column tile; packing two tiles gives it four k-slots of column
 //     n' = m), so the next operator is stored with its columns permuted the same way and the intermediate never goes to shared
-//     memory (the back-to-back GEMM trick).  Stages alternate horizontal / vertical, any number of them (pixelate: 4);
+//     memory (the back-to-back GEMM trick).  Stages alternate horizontal / vertical, any number of them;
 //   * Q22 coefficients (Pillow) are split into three byte limbs k = k2 2^16 + k1 2^8 + k0 (k2 signed): three IMMAs per tile
 //     chained through the accumulator, c = ((((2^21 + S0) >> 8) + S1) >> 8) + S2) >> 6 — nested floors of integers, i.e.
 //     exactly (2^21 + sum x k) >> 22 — then one saturating pack (I2IP) gives clip8 and the next stage's bytes;
