@@ -155,24 +155,42 @@ def zoom_operator(h: int, w: int, severity: int, device):
     lo, hi = CIFAR_TABLE["zoom_blur"][severity - 1]
     zs = np.arange(lo, hi, 0.01)
     P = h * w
-    W = np.zeros((P, P), np.float64)
-    rows = np.arange(P)
-    W[rows, rows] += 1.0
+    # entries (row, column, weight) in the order the canonical loop visits them: the identity, then per zoom factor the four
+    # bilinear taps; equal (row, column) pairs are then summed in float64 IN THAT ORDER (a stable sort keeps it), which is
+    # what a dense accumulation does, without the P x P matrix (20 GB at 224 x 224)
+    rows = np.arange(P, dtype=np.int64)
+    r_l, c_l, w_l = [rows], [rows], [np.ones(P, np.float64)]
     for z in zs:
         y0, y1, ty = zoom_axis_table(h, float(z))
         x0, x1, tx = zoom_axis_table(w, float(z))
         ty, tx = ty.astype(np.float64), tx.astype(np.float64)
         for ya, wy in ((y0, 1 - ty), (y1, ty)):
             for xa, wx in ((x0, 1 - tx), (x1, tx)):
-                q = (ya[:, None] * w + xa[None, :]).reshape(-1)
-                np.add.at(W, (rows, q), (wy[:, None] * wx[None, :]).reshape(-1))
-    W /= (len(zs) + 1)
-    nzr, nzc = np.nonzero(W)
-    indptr = np.zeros(P + 1, np.int32)
+                r_l.append(rows)
+                c_l.append((ya[:, None] * w + xa[None, :]).reshape(-1).astype(np.int64))
+                w_l.append((wy[:, None] * wx[None, :]).reshape(-1))
+    ekey = np.concatenate(r_l) * P + np.concatenate(c_l)
+    wts = np.concatenate(w_l)
+    order = np.argsort(ekey, kind="stable")
+    ekey, wts = ekey[order], wts[order]
+    first = np.concatenate([[True], ekey[1:] != ekey[:-1]])
+    group = np.cumsum(first) - 1
+    start = np.nonzero(first)[0]
+    rank = np.arange(len(ekey)) - start[group]
+    acc = np.zeros(len(start), np.float64)
+    for r in range(int(rank.max()) + 1):
+        sel = rank == r
+        acc[group[sel]] += wts[sel]
+    acc /= (len(zs) + 1)
+    keep = acc != 0.0
+    uekey, acc = ekey[start][keep], acc[keep]
+    nzr, nzc = uekey // P, uekey % P
+    indptr = np.zeros(P + 1, np.int64)
     np.add.at(indptr, nzr + 1, 1)
     indptr = np.cumsum(indptr).astype(np.int32)
+    wf32 = acc.astype(np.float32)
     op = (torch.from_numpy(indptr).to(device), torch.from_numpy(nzc.astype(np.int32)).to(device),
-          torch.from_numpy(W[nzr, nzc].astype(np.float32)).to(device), int(np.diff(indptr).max()))
+          torch.from_numpy(wf32).to(device), int(np.diff(indptr).max()))
     _zoom_cache[key] = op
     return op
 
@@ -354,7 +372,9 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metri
         if "frost" in d:
             point(L.CC_FROST, p[0], p[1], a=_dev(d["frost"], torch.uint8, dev))
         else:
-            bank = procedural_frost_bank(dev) if frost_bank is None else frost_bank
+            # the stand-in textures must be larger than the image: 96 x 96 for CIFAR, twice the image side above that
+            bank = (procedural_frost_bank(dev, size=96 if max(h, w) < 96 else 2 * max(h, w)) if frost_bank is None
+                    else frost_bank)
             point(L.CC_FROST, p[0], p[1], a=bank, tex=(bank.shape[0], bank.shape[1], bank.shape[2]))
     elif name == "defocus_blur":
         dydx, wts = disk_taps(p[0], p[1])

@@ -32,6 +32,7 @@ struct CcPointParams {
   const void* b;
   uint64_t seed;
   int tex_n, tex_h, tex_w;
+  int plasma_pitch;   // fog, maps generated on the device for large images: rows of `plasma_pitch` doubles, pitch^2 per image
 };
 
 __device__ __forceinline__ uint8_t q255(double v) {  // np.uint8(np.clip(v, 0, 1) * 255)
@@ -101,6 +102,17 @@ __device__ void plasma_device(double* map, int msz, double decay, const Philox& 
   const double lo = red[0], span = red[1] - red[0];
   for (int i = tid; i < msz * msz; i += nt) map[i] = (map[i] - lo) / span;
   __syncthreads();
+}
+
+// Plasma maps for images that are not a power-of-two square of at most 64 pixels: one CTA per image builds the msz x msz
+// map in global memory (msz = next power of two, as the canonical ImageNet-C generator draws 256 x 256 for 224 x 224); the
+// fog pass then reads its top-left h x w corner.  Same draw convention as the shared-memory form.
+__global__ void __launch_bounds__(256)
+plasma_map_kernel(double* maps, int msz, double decay, uint64_t seed, int64_t img0) {
+  __shared__ double red[2];
+  const Philox rng(seed);
+  const int64_t img = img0 + blockIdx.x;
+  plasma_device(maps + (size_t)blockIdx.x * msz * msz, msz, decay, rng, (uint32_t)img, (uint32_t)(img >> 32), red);
 }
 
 struct OpCcPoint : NoSpill {
@@ -252,6 +264,17 @@ struct OpCcPoint : NoSpill {
           __syncthreads();
           const double mval = T[(int)cells[4]];
           const double* pl = reinterpret_cast<const double*>(p.a);
+          if (pl && p.plasma_pitch) {
+            // maps made by plasma_map_kernel (power-of-two side, top-left h x w corner used): own loop, then next image
+            pl += img * (int64_t)p.plasma_pitch * p.plasma_pitch;
+            const double den2 = mval + p.p0;
+            for (int i = tid; i < ne; i += kThreads) {
+              const int px = i / 3, y = px / s.w, x = px - y * s.w;
+              const double v = T[im[i]] + p.p0 * pl[(size_t)y * p.plasma_pitch + x];
+              om[i] = q255(v * mval / den2);
+            }
+            break;
+          }
           if (pl) {
             pl += img * hw;
           } else {
@@ -309,7 +332,34 @@ static int impl_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
   if (kind == IMGTX_CC_SHOT || kind == IMGTX_CC_GAUSSIAN) IMGTX_CHECK_ARG(p0 > 0 || draws_a_dev, "scale must be positive");
   size_t extra = 0;
   if (kind == IMGTX_CC_FOG && !draws_a_dev) {
-    IMGTX_CHECK_ARG(h == w && (h & (h - 1)) == 0 && h <= 64, "on-chip plasma needs a square power-of-two image (<= 64)");
+    if (!(h == w && (h & (h - 1)) == 0 && h <= 64)) {
+      // other sizes: maps of the next power-of-two side made in global memory, in chunks of at most 256 MB, then the fog pass
+      // with those maps as its draws
+      IMGTX_CHECK_ARG(p1 > 0, "plasma decay must be positive");
+      int msz = 4;
+      while (msz < std::max(h, w)) msz <<= 1;
+      IMGTX_CHECK_ARG(msz <= 4096, "image too large for the on-chip plasma (side <= 4096)");
+      if (n == 0) return IMGTX_OK;
+      IMGTX_CHECK_ARG(in && out, "null image pointer");
+      cudaStream_t st = (cudaStream_t)stream;
+      const size_t per = (size_t)msz * msz * sizeof(double);
+      const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((256u << 20) / per)));
+      double* maps = nullptr;
+      IMGTX_CUDA_OK(cudaMallocAsync((void**)&maps, per * chunk, st));
+      CcPointParams q;
+      memset(&q, 0, sizeof(q));
+      q.kind = kind; q.p0 = p0; q.p1 = p1; q.a = maps; q.seed = seed; q.plasma_pitch = msz;
+      const Shape shl = make_shape(h, w, c, h, w);
+      int rc = IMGTX_OK;
+      for (int64_t c0 = 0; c0 < n && rc == IMGTX_OK; c0 += chunk) {
+        const int64_t cn = std::min<int64_t>(chunk, n - c0);
+        plasma_map_kernel<<<(unsigned)cn, 256, 0, st>>>(maps, msz, p1, seed, c0);
+        IMGTX_LAUNCH_OK();
+        rc = launch_image_op<OpCcPoint>(in + c0 * shl.in_bytes, out + c0 * shl.out_bytes, cn, shl, q, st);
+      }
+      IMGTX_CUDA_OK(cudaFreeAsync(maps, st));
+      return rc;
+    }
     extra = (size_t)h * w * sizeof(double);
   }
   if (kind == IMGTX_CC_FROST) {

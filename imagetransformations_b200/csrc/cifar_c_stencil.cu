@@ -192,6 +192,29 @@ struct OpCcCsr : NoSpill {
   }
 };
 
+// Operators too large for shared memory (224x224: 0.7-1.8 M taps): the same ordered float32 sums with the operator and the
+// image read through L2, one thread per output pixel.
+__global__ void __launch_bounds__(256)
+csr_global_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int P, CsrParams p) {
+  const int64_t total = n * P;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t j = i / P;
+    const int px = (int)(i - j * P);
+    const uint8_t* im = in + j * (int64_t)P * 3;
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+    const int k1 = __ldg(p.indptr + px + 1);
+    for (int k = __ldg(p.indptr + px); k < k1; ++k) {
+      const float wt = __ldg(p.weights + k);
+      const uint8_t* q = im + (int64_t)__ldg(p.indices + k) * 3;
+      a0 = __fadd_rn(a0, __fmul_rn(__fdiv_rn((float)q[0], 255.0f), wt));
+      a1 = __fadd_rn(a1, __fmul_rn(__fdiv_rn((float)q[1], 255.0f), wt));
+      a2 = __fadd_rn(a2, __fmul_rn(__fdiv_rn((float)q[2], 255.0f), wt));
+    }
+    uint8_t* o = out + i * 3;
+    o[0] = q255f(a0); o[1] = q255f(a1); o[2] = q255f(a2);
+  }
+}
+
 // Throughput form.  The gather is shared-memory-bandwidth bound, so everything is laid out for conflict-free access: the
 // operator is re-packed per CTA into ELL form [tap][pixel] (u16 source index, f32 weight; short rows padded with zero
 // weights, which leave the ordered float32 sum bit-identical), the group is converted once into PLANAR float images (one
@@ -282,12 +305,15 @@ struct GlassParams {
   uint64_t seed;
 };
 
-struct OpCcGlass : NoSpill {
+struct OpCcGlass {
   using Params = GlassParams;
   static constexpr int kThreads = 256;
   // T64 (2 KB) + one f64 plane (h*w*3*8)
   static size_t scratch_bytes(const Shape& s, int) { return 2048 + (size_t)s.in_bytes * 8 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  // large images (224x224: a 1.2 MB plane): the f64 plane of the CTA's image lives in a global workspace
+  static size_t gtmp_bytes(const Shape& s) { return (size_t)s.in_bytes * 8; }
+  static size_t scratch_bytes_spilled(const Shape&) { return 2048 + 16; }
   __device__ static void prepare(const Shape&, const Params&, uint8_t* scratch, bool) {
     double* T = reinterpret_cast<double*>(scratch);
     for (int i = threadIdx.x; i < 256; i += kThreads) T[i] = (double)i / 255.0;
@@ -321,16 +347,50 @@ struct OpCcGlass : NoSpill {
 
   template <bool STAGED>
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
-                             uint8_t* scratch, uint8_t*) {
+                             uint8_t* scratch, uint8_t* gtmp) {
     const double* T = reinterpret_cast<const double*>(scratch);
-    double* tmp = reinterpret_cast<double*>(scratch + 2048);
+    double* tmp = gtmp ? reinterpret_cast<double*>(gtmp) : reinterpret_cast<double*>(scratch + 2048);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int j = 0; j < g; ++j)
       gaussian<false>(src + (size_t)j * s.in_bytes, dst + (size_t)j * s.out_bytes, tmp, T, s, p);
-    // ---- swaps: one warp per image, rows on lanes, skew-2 wavefront (requires h - 2 <= 32) ----
     const int R = s.h - 2, Ccols = s.w - 2;
     const Philox rng(p.seed);
-    for (int j = warp; j < g; j += kThreads >> 5) {
+    if (R > 32) {
+      // ---- swaps, images taller than 34 rows (direct mode: g == 1, the image is the caller's output batch in global memory):
+      // the same skew-2 wavefront with the rows dealt to the threads of the CTA and a block barrier per step.  On-chip
+      // draws: one Philox call per (image, iteration, row, block of 64 columns); block 0 is the small-image convention ----
+      for (int j = 0; j < g; ++j) {
+        uint8_t* im = dst + (size_t)j * s.out_bytes;
+        const int64_t img = img0 + j;
+        for (int it = 0; it < p.iters; ++it) {
+          for (int t = 0; t < 2 * (R - 1) + Ccols; ++t) {
+            for (int r = tid; r < R; r += kThreads) {
+              const int ci = t - 2 * r;
+              if (ci < 0 || ci >= Ccols) continue;
+              const int h = s.h - 1 - r, w = s.w - 1 - ci;
+              int dx, dy;
+              if (p.deltas) {
+                const int8_t* d = p.deltas + ((((img * p.iters + it) * R + r) * Ccols + ci) << 1);
+                dx = d[0]; dy = d[1];
+              } else {
+                const uint4 rb = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)r + ((uint32_t)(ci >> 6) << 16));
+                const int cb = ci & 63;
+                dx = -(int)(((cb < 32 ? rb.x : rb.z) >> (cb & 31)) & 1u);
+                dy = -(int)(((cb < 32 ? rb.y : rb.w) >> (cb & 31)) & 1u);
+              }
+              uint8_t* a = im + (h * s.w + w) * 3;
+              uint8_t* b = im + ((h + dy) * s.w + (w + dx)) * 3;
+              const uint8_t t0 = a[0], t1 = a[1], t2 = a[2];
+              a[0] = b[0]; a[1] = b[1]; a[2] = b[2];
+              b[0] = t0; b[1] = t1; b[2] = t2;
+            }
+            __syncthreads();
+          }
+        }
+      }
+    }
+    // ---- swaps: one warp per image, rows on lanes, skew-2 wavefront (h - 2 <= 32) ----
+    for (int j = warp; j < g && R <= 32; j += kThreads >> 5) {
       uint8_t* im = dst + (size_t)j * s.out_bytes;
       const int64_t img = img0 + j;
       for (int it = 0; it < p.iters; ++it) {
@@ -689,9 +749,14 @@ struct SnowParams {
   float ty[kSnowMax], tx[kSnowMax];
   MotionParams m;          // layer blur
   const double* layer;     // device (n,h,w) f64 or nullptr
+  const int32_t* zidx;     // images larger than kSnowMax: the zoom tables in device memory (y0, y1 (h each), x0, x1 (w each))
+  const float* zt;         //                              ty (h), tx (w)
 };
 
-struct OpCcSnow : NoSpill {
+struct OpCcSnow {
+  // large images: the layers of the CTA's image live in a global workspace
+  static size_t gtmp_bytes(const Shape& s) { return per_image(s); }
+  static size_t scratch_bytes_spilled(const Shape&) { return 16; }
   using Params = SnowParams;
   static constexpr int kThreads = 256;
   // per image: L0 f32[hw] + L1 u8[hw] + L2 u8[hw] + offsets
@@ -701,10 +766,10 @@ struct OpCcSnow : NoSpill {
   __device__ static void prepare(const Shape&, const Params&, uint8_t*, bool) {}
   template <bool STAGED>
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
-                             uint8_t* scratch, uint8_t*) {
+                             uint8_t* scratch, uint8_t* gtmp) {
     const int tid = threadIdx.x, warp = tid >> 5;
     const int hw = s.h * s.w;
-    float* L0 = reinterpret_cast<float*>(scratch);                          // [g][hw]
+    float* L0 = reinterpret_cast<float*>(gtmp ? gtmp : scratch);            // [g][hw]
     int* off = reinterpret_cast<int*>(L0 + (size_t)g * hw);                  // [g][kMaxLine*2]
     uint8_t* L1 = reinterpret_cast<uint8_t*>(off + (size_t)g * kMaxLine * 2);  // [g][hw]
     uint8_t* L2 = L1 + (size_t)g * hw;
@@ -742,11 +807,14 @@ struct OpCcSnow : NoSpill {
       const int j = i / hw, px = i - j * hw;
       const int y = px / s.w, x = px - y * s.w;
       const float* L = L0 + (size_t)j * hw;
-      const float ty = p.ty[y], tx = p.tx[x], uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
-      float acc = __fmul_rn(__fmul_rn(L[p.y0[y] * s.w + p.x0[x]], uy), ux);
-      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y0[y] * s.w + p.x1[x]], uy), tx));
-      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y1[y] * s.w + p.x0[x]], ty), ux));
-      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[p.y1[y] * s.w + p.x1[x]], ty), tx));
+      const bool big = p.zidx != nullptr;
+      const int zy0 = big ? p.zidx[y] : p.y0[y], zy1 = big ? p.zidx[s.h + y] : p.y1[y];
+      const int zx0 = big ? p.zidx[2 * s.h + x] : p.x0[x], zx1 = big ? p.zidx[2 * s.h + s.w + x] : p.x1[x];
+      const float ty = big ? p.zt[y] : p.ty[y], tx = big ? p.zt[s.h + x] : p.tx[x], uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
+      float acc = __fmul_rn(__fmul_rn(L[zy0 * s.w + zx0], uy), ux);
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[zy0 * s.w + zx1], uy), tx));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[zy1 * s.w + zx0], ty), ux));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L[zy1 * s.w + zx1], ty), tx));
       if (acc < p.thresh) acc = 0.0f;
       L1[i] = q255f(acc);
     }
@@ -1293,7 +1361,15 @@ extern "C" int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h
   CsrParams p;
   p.indptr = indptr_dev; p.indices = indices_dev; p.weights = weights_dev; p.nnz = nnz;
   const size_t extra = OpCcCsr::table_bytes(h * w, nnz);
-  IMGTX_CHECK_ARG(extra + 64 * 1024 <= (size_t)max_smem_optin(), "operator too large for shared memory (%d taps)", nnz);
+  if (extra + 64 * 1024 > (size_t)max_smem_optin()) {
+    if (n == 0) return IMGTX_OK;
+    IMGTX_CHECK_ARG(in && out, "null image pointer");
+    const int64_t want = (n * h * w + 255) / 256;
+    const int64_t grid = std::min<int64_t>(want, (int64_t)sm_count() * 16);
+    csr_global_kernel<<<(unsigned)grid, 256, 0, (cudaStream_t)stream>>>(in, out, n, h * w, p);
+    IMGTX_LAUNCH_OK();
+    return IMGTX_OK;
+  }
   return launch_image_op<OpCcCsr>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream, extra,
                                   (int)extra + 64 * 1024);
 }
@@ -1324,7 +1400,7 @@ static int impl_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h,
 
 static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
                                  int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
-  IMGTX_CHECK_ARG(h > 2 && w > 2 && h <= 34 && c == 3 && n >= 0, "glass_blur takes (n,h<=34,w,3) images");
+  IMGTX_CHECK_ARG(h > 2 && w > 2 && c == 3 && n >= 0, "glass_blur takes (n,h>2,w>2,3) images");
   IMGTX_CHECK_ARG(lw >= 0 && lw <= 3 && weights_host && iters >= 0, "bad Gaussian");
   GlassParams p;
   memset(&p, 0, sizeof(p));
@@ -1343,7 +1419,7 @@ static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, i
       if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
     }
   }
-  if (lw <= 2 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
+  if (lw <= 2 && h <= 34 && w % 4 == 0 && w - 2 <= 64 && h * w <= 65536 && shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out) &&
       !(flags & IMGTX_CC_REPLAY_ALL)) {   // test knob: the literal kernel instead of the fixed-point sweeps
     GlassFastParams f;
     memset(&f, 0, sizeof(f));
@@ -1430,13 +1506,28 @@ static int impl_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, in
                                 const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
                                 const int32_t* offsets_dev, const double* layer_dev, double loc, double scale,
                                 double angle_lo, double angle_hi, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
-  IMGTX_CHECK_ARG(h > 0 && w > 0 && h <= kSnowMax && w <= kSnowMax && c == 3 && n >= 0, "snow takes (n,h<=64,w<=64,3) images");
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "snow takes (n,h,w,3) images");
   IMGTX_CHECK_ARG(zoom_idx_host && zoom_t_host, "missing zoom tables");
   SnowParams p;
   memset(&p, 0, sizeof(p));
   int rc = fill_motion(p.m, width, k_host, offsets_dev, angle_lo, angle_hi, seed, flags);
   if (rc) return rc;
   p.thresh = thresh; p.c6 = c6; p.one_minus_c6 = one_minus_c6; p.loc = loc; p.scale = scale; p.layer = layer_dev;
+  if (h > kSnowMax || w > kSnowMax) {
+    // large images: literal form, one CTA per image, layers in a global workspace, zoom tables in device memory
+    if (n == 0) return IMGTX_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    uint8_t* tab = nullptr;
+    const size_t ib = (size_t)(2 * h + 2 * w) * 4, tb = (size_t)(h + w) * 4;
+    IMGTX_CUDA_OK(cudaMallocAsync((void**)&tab, ib + tb, st));
+    IMGTX_CUDA_OK(cudaMemcpyAsync(tab, zoom_idx_host, ib, cudaMemcpyHostToDevice, st));
+    IMGTX_CUDA_OK(cudaMemcpyAsync(tab + ib, zoom_t_host, tb, cudaMemcpyHostToDevice, st));
+    p.zidx = reinterpret_cast<const int32_t*>(tab);
+    p.zt = reinterpret_cast<const float*>(tab + ib);
+    rc = launch_image_op<OpCcSnow>(in, out, n, make_shape(h, w, c, h, w), p, st);
+    IMGTX_CUDA_OK(cudaFreeAsync(tab, st));
+    return rc;
+  }
   for (int i = 0; i < h; ++i) { p.y0[i] = (int8_t)zoom_idx_host[i]; p.y1[i] = (int8_t)zoom_idx_host[h + i]; p.ty[i] = zoom_t_host[i]; }
   for (int i = 0; i < w; ++i) { p.x0[i] = (int8_t)zoom_idx_host[2 * h + i]; p.x1[i] = (int8_t)zoom_idx_host[2 * h + w + i]; p.tx[i] = zoom_t_host[h + i]; }
   Shape shp = make_shape(h, w, c, h, w);

@@ -32,7 +32,8 @@ struct ElasticParams {
   const double* uy;
   double c2;
   uint64_t seed;
-  int force_exact;        // test knob (imgtx_set_force_exact)
+  int force_exact;        // IMGTX_CC_REPLAY_ALL
+  const double* wdev;     // lw > kMaxLw (large images): the lw + 1 Gaussian weights in device memory instead of w[]
 };
 
 __device__ __forceinline__ int reflect_half(int i, int n) {  // scipy 'reflect': d c b a | a b c d | d c b a
@@ -42,9 +43,12 @@ __device__ __forceinline__ int reflect_half(int i, int n) {  // scipy 'reflect':
   return m >= n ? period - 1 - m : m;
 }
 
-struct OpCcElastic : NoSpill {
+struct OpCcElastic {
   using Params = ElasticParams;
   static constexpr int kThreads = 256;
+  // large images (224x224: 1.8 MB of planes): everything but the byte table lives in a global workspace
+  static size_t gtmp_bytes(const Shape& s) { return (size_t)s.h * s.w * (12 + 16 + 8) + 64; }
+  static size_t scratch_bytes_spilled(const Shape&) { return 1024 + 16; }
   // T32 (1 KB) + warped image f32 (hw*3*4) + two f64 field planes (hw*8 each) + dx, dy f32 (hw*4 each) + M (64 B)
   static size_t scratch_bytes(const Shape& s, int) { return 1024 + (size_t)s.h * s.w * (12 + 16 + 8) + 64 + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
@@ -62,19 +66,20 @@ struct OpCcElastic : NoSpill {
       __syncthreads();
       return;
     }
+    const double* wv = p.wdev ? p.wdev : p.w;
     for (int i = tid; i < hw; i += kThreads) {  // axis y
       const int y = i / s.w, x = i - y * s.w;
-      double acc = F0[i] * p.w[0];
+      double acc = F0[i] * wv[0];
       for (int k = p.lw; k >= 1; --k)
-        acc = acc + (F0[reflect_half(y - k, s.h) * s.w + x] + F0[reflect_half(y + k, s.h) * s.w + x]) * p.w[k];
+        acc = acc + (F0[reflect_half(y - k, s.h) * s.w + x] + F0[reflect_half(y + k, s.h) * s.w + x]) * wv[k];
       F1[i] = acc;
     }
     __syncthreads();
     for (int i = tid; i < hw; i += kThreads) {  // axis x
       const int y = i / s.w, x = i - y * s.w;
       const double* row = F1 + y * s.w;
-      double acc = row[x] * p.w[0];
-      for (int k = p.lw; k >= 1; --k) acc = acc + (row[reflect_half(x - k, s.w)] + row[reflect_half(x + k, s.w)]) * p.w[k];
+      double acc = row[x] * wv[0];
+      for (int k = p.lw; k >= 1; --k) acc = acc + (row[reflect_half(x - k, s.w)] + row[reflect_half(x + k, s.w)]) * wv[k];
       out[i] = (float)(acc * p.alpha);
     }
     __syncthreads();
@@ -82,11 +87,11 @@ struct OpCcElastic : NoSpill {
 
   template <bool STAGED>
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
-                             uint8_t* scratch, uint8_t*) {
+                             uint8_t* scratch, uint8_t* gtmp) {
     const int tid = threadIdx.x;
     const int hw = s.h * s.w;
     const float* T = reinterpret_cast<const float*>(scratch);
-    float* W = reinterpret_cast<float*>(scratch + 1024);        // warped image, HWC f32
+    float* W = reinterpret_cast<float*>(gtmp ? gtmp : scratch + 1024);        // warped image, HWC f32
     double* F0 = reinterpret_cast<double*>(W + hw * 3);
     double* F1 = F0 + hw;
     float* DX = reinterpret_cast<float*>(F1 + hw);
@@ -1039,7 +1044,7 @@ __device__ __forceinline__ void idct8(int* d) {
   d[3] = descale(tmp13 + t0, SH); d[4] = descale(tmp13 - t0, SH);
 }
 
-struct OpCcJpeg : NoSpill {
+struct OpCcJpeg {
   using Params = JpegParams;
   static constexpr bool kCifarCopy = true;
   static constexpr int kThreads = 256;
@@ -1050,6 +1055,9 @@ struct OpCcJpeg : NoSpill {
   static constexpr int kHeader = 2 * 64 * 8;   // quantiser and reciprocal per (table, coefficient), interleaved
   static size_t scratch_bytes(const Shape& s, int G) { return kHeader + (size_t)G * per_image(s) + 16; }
   static size_t scratch_bytes_direct(const Shape& s) { return scratch_bytes(s, 1); }
+  // large images (224x224: 303 KB of planes): the planes of the CTA's image live in a global workspace (L2 resident)
+  static size_t gtmp_bytes(const Shape& s) { return per_image(s); }
+  static size_t scratch_bytes_spilled(const Shape&) { return kHeader + 16; }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* scratch, bool) {
     uint2* qt = reinterpret_cast<uint2*>(scratch);
     for (int i = threadIdx.x; i < 128; i += kThreads) qt[i] = make_uint2((uint32_t)p.q[i >> 6][i & 63], p.rq[i >> 6][i & 63]);
@@ -1058,12 +1066,12 @@ struct OpCcJpeg : NoSpill {
 
   template <bool STAGED>
   __device__ static void run(const uint8_t* src, uint8_t* dst, int g, int64_t img0, const Shape& s, const Params& p,
-                             uint8_t* scratch, uint8_t*) {
+                             uint8_t* scratch, uint8_t* gtmp) {
     const int tid = threadIdx.x;
     const int h = s.h, w = s.w, hw = h * w, ch = h >> 1, cw = w >> 1, pw = w + 1, pcw = cw + 1;
     const int ysz = h * pw, csz = ch * pcw, plane_words = ysz + 2 * csz;
     const uint2* qtab = reinterpret_cast<const uint2*>(scratch);
-    int* planes = reinterpret_cast<int*>(scratch + kHeader);
+    int* planes = gtmp ? reinterpret_cast<int*>(gtmp) : reinterpret_cast<int*>(scratch + kHeader);
     __syncthreads();
     // ---- colour conversion + 4:2:0 downsample (one thread per 2x2 quad) ----
     for (int i = tid; i < g * ch * cw; i += kThreads) {
@@ -1200,14 +1208,30 @@ using namespace imgtx;
 static int impl_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, double alpha,
                                    const double* weights_host, int lw, const double* M_dev, const double* ux_dev,
                                    const double* uy_dev, double c2, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
-  IMGTX_CHECK_ARG(h > 1 && w > 1 && h <= 64 && w <= 64 && c == 3 && n >= 0, "elastic_transform takes (n,h<=64,w<=64,3) images");
-  IMGTX_CHECK_ARG(lw >= -1 && lw <= kMaxLw && (lw < 0 || weights_host), "Gaussian radius must be <= %d", kMaxLw);
+  IMGTX_CHECK_ARG(h > 1 && w > 1 && c == 3 && n >= 0, "elastic_transform takes (n,h,w,3) images");
+  IMGTX_CHECK_ARG(lw >= -1 && lw <= 4096 && (lw < 0 || weights_host), "Gaussian radius must be <= 4096");
+  const bool large = h > 64 || w > 64 || lw > kMaxLw;   // the literal form below: any size, any radius
   IMGTX_CHECK_ARG((ux_dev == nullptr) == (uy_dev == nullptr), "give both displacement fields or none");
   ElasticParams p;
   memset(&p, 0, sizeof(p));
   p.alpha = alpha; p.lw = lw; p.M = M_dev; p.ux = ux_dev; p.uy = uy_dev; p.c2 = c2; p.seed = seed; p.force_exact = (flags & IMGTX_CC_REPLAY_ALL) ? 1 : 0;
-  for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
+  for (int i = 0; i <= lw && i <= kMaxLw; ++i) p.w[i] = weights_host[i];
   const Shape shp = make_shape(h, w, c, h, w);
+  if (large) {
+    // large images or long Gaussians: literal form (planes in a global workspace when they do not fit on chip, weights beyond
+    // kMaxLw read from device memory)
+    if (n == 0) return IMGTX_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    double* wd = nullptr;
+    if (lw > kMaxLw) {
+      IMGTX_CUDA_OK(cudaMallocAsync((void**)&wd, (size_t)(lw + 1) * 8, st));
+      IMGTX_CUDA_OK(cudaMemcpyAsync(wd, weights_host, (size_t)(lw + 1) * 8, cudaMemcpyHostToDevice, st));
+      p.wdev = wd;
+    }
+    const int rc = launch_image_op<OpCcElastic>(in, out, n, shp, p, st);
+    if (wd) IMGTX_CUDA_OK(cudaFreeAsync(wd, st));
+    return rc;
+  }
   if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32 && (alpha == 0.0 || (lw >= 0 && fabs(alpha) <= 16.0))) {
     ElasticFastParams f;
     f.e = p;

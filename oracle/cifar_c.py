@@ -383,6 +383,44 @@ def zoom_operator(h, w, severity):
             np.concatenate(weights).astype(f32))
 
 
+def zoom_operator_sparse(h, w, severity):
+    """zoom_operator without the dense (h*w)^2 matrix (20 GB at 224x224): the same entries in the same visiting order,
+    equal (row, column) pairs summed in f64 in that order.  tests/test_oracle_cifar_c.py checks it against the dense
+    builder bit for bit at small sizes."""
+    zs = zoom_factors(severity)
+    P = h * w
+    rows = np.arange(P, dtype=np.int64)
+    ent = [(rows, rows, np.ones(P, f64))]
+    for z in zs:
+        y0, y1, ty = zoom_axis_table(h, float(z))
+        x0, x1, tx = zoom_axis_table(w, float(z))
+        ty, tx = ty.astype(f64), tx.astype(f64)
+        for ya, wy in ((y0, 1 - ty), (y1, ty)):
+            for xa, wx in ((x0, 1 - tx), (x1, tx)):
+                ent.append((rows, (ya[:, None] * w + xa[None, :]).reshape(-1).astype(np.int64),
+                            (wy[:, None] * wx[None, :]).reshape(-1)))
+    r = np.concatenate([e[0] for e in ent])
+    q = np.concatenate([e[1] for e in ent])
+    v = np.concatenate([e[2] for e in ent])
+    order = np.lexsort((np.arange(len(r)), q, r))        # by (row, column), ties in visiting order
+    r, q, v = r[order], q[order], v[order]
+    new = np.ones(len(r), bool)
+    new[1:] = (r[1:] != r[:-1]) | (q[1:] != q[:-1])
+    gid = np.cumsum(new) - 1
+    pos = np.arange(len(r)) - np.nonzero(new)[0][gid]
+    tot = np.zeros(int(gid[-1]) + 1, f64)
+    for k in range(int(pos.max()) + 1):
+        m = pos == k
+        tot[gid[m]] = tot[gid[m]] + v[m]
+    tot = tot / (len(zs) + 1)
+    ur, uq = r[new], q[new]
+    nzm = tot != 0
+    ur, uq, tot = ur[nzm], uq[nzm], tot[nzm]
+    indptr = np.zeros(P + 1, np.int64)
+    np.add.at(indptr, ur + 1, 1)
+    return np.cumsum(indptr).astype(np.int32), uq.astype(np.int32), tot.astype(f32)
+
+
 def apply_csr_f32(src, indptr, indices, weights):
     """out[:, p, :] = sum_k weights[k] * src[:, indices[k], :] for k in row p, f32, in stored order.
     src (n, h*w, c) f32."""
@@ -404,7 +442,7 @@ def zoom_blur(x, severity):
     n, h, w, c = x.shape
     key = (h, w, severity)
     if key not in _zoom_ops:
-        _zoom_ops[key] = zoom_operator(h, w, severity)
+        _zoom_ops[key] = zoom_operator(h, w, severity) if h * w <= 4096 else zoom_operator_sparse(h, w, severity)
     src = (x.astype(f32) / f32(255)).astype(f32).reshape(n, h * w, c)
     v = apply_csr_f32(src, *_zoom_ops[key]).reshape(n, h, w, c)
     return _u8((np.clip(v, 0, 1) * f32(255)).astype(f32))
@@ -828,7 +866,10 @@ def draw(name, severity, x, rng):
     if name == "frost":
         return {"frost": rng.randint(0, 256, size=x.shape).astype(np.uint8)}
     if name == "fog":
-        return {"plasma": np.stack([plasma_fractal(h, p[1], lambda lo, hi, s: rng.uniform(lo, hi, s))
+        # the diamond-square map needs a power-of-two side: sizes in between draw the next power of two and keep the top-left
+        # h x w corner, as the canonical ImageNet-C generator does (mapsize 256, [:224, :224]); 32 x 32 is unchanged
+        ms = 1 << int(np.ceil(np.log2(max(h, w))))
+        return {"plasma": np.stack([plasma_fractal(ms, p[1], lambda lo, hi, s: rng.uniform(lo, hi, s))[:h, :w]
                                     for _ in range(n)])}
     if name == "elastic_transform":
         c2 = p[2] * h

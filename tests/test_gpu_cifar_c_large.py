@@ -1,0 +1,93 @@
+"""The 15 x 5 suite on Imagenette-shaped (224 x 224) and in-between (96 x 96, 64 x 48) batches: every type with injected
+draws equals oracle/cifar_c.py byte for byte (same bar as the CIFAR-shaped tests), every type runs with on-chip draws
+(deterministic per seed, different across seeds for the random types, batch-independent), and the per-image metric
+is written for these shapes too."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cifar_c as CC
+
+pytestmark = pytest.mark.gpu
+
+RANDOM_TYPES = ["gaussian_noise", "shot_noise", "impulse_noise", "glass_blur", "motion_blur", "snow", "frost", "fog",
+                "elastic_transform"]
+
+
+def _C():
+    from imagetransformations_b200 import cifar_c
+    return cifar_c
+
+
+def _imgs(seed, n, h, w):
+    x = np.random.default_rng(seed).integers(0, 256, (n, h, w, 3), dtype=np.uint8)
+    x[0, : h // 2] = (x[0, : h // 2] // 4 + 100).astype(np.uint8)   # a smooth half: ties and flat regions
+    return x
+
+
+@pytest.mark.parametrize("sev", [1, 3, 5])
+@pytest.mark.parametrize("name", CC.CORRUPTIONS)
+def test_imagenette_shape_matches_oracle(cuda, name, sev):
+    C = _C()
+    x = _imgs(sev, 2, 224, 224)
+    d = CC.draw(name, sev, x, np.random.RandomState(2000 + sev))
+    want = CC.corrupt(name, sev, x, d)
+    got = C.corrupt(torch.from_numpy(x).cuda(), name, sev, draws=d).cpu().numpy()
+    diff = np.abs(got.astype(np.int32) - want.astype(np.int32))
+    assert diff.max() == 0, f"{name} s{sev} at 224x224: max diff {diff.max()}, {(diff > 0).mean():.4%} of bytes differ"
+
+
+@pytest.mark.parametrize("hw", [(96, 96), (64, 48)])
+@pytest.mark.parametrize("name", ["glass_blur", "snow", "elastic_transform", "zoom_blur", "fog", "frost", "motion_blur",
+                                  "defocus_blur"])
+def test_in_between_shapes_match_oracle(cuda, name, hw):
+    """Sizes between the shared-memory forms (<= 34 / 64 pixels) and 224: rectangular, rows that are no multiple of the
+    vector width, more rows than a warp has lanes."""
+    C = _C()
+    if name == "fog" and hw[0] != hw[1]:
+        pytest.skip("the oracle's plasma map is square")
+    x = _imgs(7, 3, *hw)
+    for sev in (2, 4):
+        d = CC.draw(name, sev, x, np.random.RandomState(sev))
+        want = CC.corrupt(name, sev, x, d)
+        got = C.corrupt(torch.from_numpy(x).cuda(), name, sev, draws=d).cpu().numpy()
+        assert np.array_equal(got, want), (name, sev, hw, int((got != want).sum()))
+
+
+@pytest.mark.parametrize("name", CC.CORRUPTIONS)
+def test_imagenette_shape_on_chip_draws(cuda, name):
+    C = _C()
+    x = _imgs(11, 5, 224, 224)
+    xd = torch.from_numpy(x).cuda()
+    m = torch.zeros((5, 2), dtype=torch.int32, device="cuda")
+    a = C.corrupt(xd, name, 3, seed=1, metrics=m).cpu().numpy()
+    b = C.corrupt(xd, name, 3, seed=1).cpu().numpy()
+    assert np.array_equal(a, b), "same seed, same bytes"
+    assert (a != x).mean() > 0.02, "the pass changed the images"
+    if name in RANDOM_TYPES:
+        c = C.corrupt(xd, name, 3, seed=2).cpu().numpy()
+        assert (c != a).mean() > 0.01, "another seed, other draws"
+    # an image's result depends on its index in the batch and the seed only, not on the batch around it
+    one = C.corrupt(xd[:2], name, 3, seed=1).cpu().numpy()
+    assert np.array_equal(one, a[:2])
+    y = a.reshape(5, -1).astype(np.int64)
+    want = np.stack([y.sum(1), (y * np.arange(1, y.shape[1] + 1)).sum(1)], 1) & 0xFFFFFFFF
+    assert np.array_equal(m.cpu().numpy().astype(np.int64) & 0xFFFFFFFF, want), "per-image metric"
+
+
+def test_imagenette_shape_fog_plasma_law(cuda):
+    """On-chip fog at 224 x 224 draws a 256 x 256 diamond-square map per image and uses its top-left corner, as the oracle's
+    draw() does: the per-byte mean and spread of the two ensembles agree (Welch z < 6 on the image means)."""
+    C = _C()
+    n = 48
+    x = np.full((n, 224, 224, 3), 96, np.uint8)
+    x[:, ::7] = 180
+    d = CC.draw("fog", 3, x, np.random.RandomState(5))
+    ref = CC.corrupt("fog", 3, x, d).astype(np.float64).reshape(n, -1)
+    got = C.corrupt(torch.from_numpy(x).cuda(), "fog", 3, seed=9).cpu().numpy().astype(np.float64).reshape(n, -1)
+    ma, mb = ref.mean(1), got.mean(1)
+    z = (ma.mean() - mb.mean()) / np.sqrt(ma.var(ddof=1) / n + mb.var(ddof=1) / n)
+    assert abs(z) < 6, z
+    sa, sb = ref.std(1), got.std(1)
+    z2 = (sa.mean() - sb.mean()) / np.sqrt(sa.var(ddof=1) / n + sb.var(ddof=1) / n)
+    assert abs(z2) < 6, z2

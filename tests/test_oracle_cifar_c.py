@@ -246,3 +246,20 @@ def test_severity1_spec_reproduces_reference_fixtures(name, limit):
     assert max(errs) < limit, (name, errs)
     if name not in ("contrast",):
         assert np.mean(errs) < np.mean(base), (name, errs, base)  # the spec explains the fixture better than "do nothing"
+
+
+def test_sparse_zoom_operator_equals_the_dense_builder():
+    """Large images build the zoom_blur operator without the (h*w)^2 matrix; at sizes where both exist they are identical
+    (indptr, indices and the float32 weights bit for bit), and so is the product's own builder."""
+    import torch
+    from imagetransformations_b200 import cifar_c as C
+    for h, w in ((32, 32), (16, 24), (24, 16)):
+        for sev in (1, 3, 5):
+            dense = CC.zoom_operator(h, w, sev)
+            sparse = CC.zoom_operator_sparse(h, w, sev)
+            prod = C.zoom_operator(h, w, sev, torch.device("cpu"))
+            for a, b, c in zip(dense, sparse, prod[:3]):
+                assert np.array_equal(a, b) and np.array_equal(a, c.numpy()), (h, w, sev)
+            assert prod[3] == int(np.diff(dense[0]).max())
+    ip, idx, wt = CC.zoom_operator_sparse(224, 224, 2)
+    assert ip[-1] == len(idx) == len(wt) and abs(float(wt.astype(np.float64).sum()) / (224 * 224) - 1.0) < 1e-6
