@@ -17,7 +17,8 @@ all-gathered over NCCL on a side stream, overlapped with the next pass — the o
 `roofline`     the corruption type with the largest share of the step, per-launch CUDA-event time: algorithmic bytes
                (6144 B/image: 3072 read + 3072 written) / duration vs the measured HBM copy peak (MEASURED_PEAKS.json).
 `configs`      the other BASELINE.json configs (C1 transformation.py grid, C3 16 TTA views, C4 AugMix 224x224, C5 FGSM
-               eps sweep fused with the post-attack leg), each with device time, fraction of the HBM peak, e2e with host
+               eps sweep fused with the post-attack leg; plus C2_224: the headline suite on Imagenette-shaped 224x224
+               images), each with device time, fraction of the HBM peak, e2e with host
                buffers and a CPU baseline (oracle/np_ops.py / np_chains.py: restatements pinned by goldens frozen from the
                live reference, tests/golden/).
 `cpu_baseline` / `--impl reference`: the CPU restatement of the suite (oracle/cifar_c.py — the reference has no code for 11
@@ -101,6 +102,21 @@ def _cpu_suite_worker(args):
     import numpy as np
     from oracle import cifar_c as CC
     x = np.random.default_rng(seed).integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    rng = np.random.RandomState(seed)
+    for s in range(1, 6):
+        CC.zoom_blur(x[:1], s)      # the merged zoom operator is a cached table on both arms
+    t0 = time.perf_counter()
+    for name in CC.CORRUPTIONS:
+        for sev in range(1, 6):
+            CC.corrupt(name, sev, x, CC.draw(name, sev, x, rng))
+    return time.perf_counter() - t0
+
+
+def _cpu_suite224_worker(args):
+    seed, n = args
+    import numpy as np
+    from oracle import cifar_c as CC
+    x = np.random.default_rng(seed).integers(0, 256, (n, 224, 224, 3), dtype=np.uint8)
     rng = np.random.RandomState(seed)
     for s in range(1, 6):
         CC.zoom_blur(x[:1], s)      # the merged zoom operator is a cached table on both arms
@@ -629,6 +645,37 @@ def bench_configs(dev, rank, world, peak, barrier, max_over_ranks, want_cpu):
                       "reverse-FGSM 3-eps sweep + per-channel clamp + tensor_to_pil -> Brightness(1.3) -> pil_to_tensor, ONE kernel, "
                       "10000 x 3x32x32 f32 image + gradient; 61440 B per input image (images_per_s counts output images)")
     res["C5"]["sign_step_only_ms"] = ms_step_only
+    del x8, xf, g, hx, hg, ho
+
+    # ---- C2 on Imagenette-shaped images (north star: "CIFAR- and Imagenette-shaped batches"): the same 75 passes over
+    #      1024 x 224x224x3 (154 MB per batch: the bytes of the 50000-image CIFAR batch), on-chip draws, two rotating outputs ----
+    from imagetransformations_b200 import cifar_c as Cc
+    n2 = 1024
+    hL = torch.from_numpy(rng.integers(0, 256, (n2, 224, 224, 3), dtype=np.uint8)).pin_memory()
+    xL = hL.to(dev)
+    oL = [torch.empty_like(xL) for _ in range(2)]
+    passes = Cc.suite_passes()
+
+    def suite224():
+        for j, (name, sev) in enumerate(passes):
+            Cc.corrupt(xL, name, sev, seed=3, out=oL[j & 1])
+    ms = timed(suite224, 2, warm=1)
+    per_type = {}
+    for name in Cc.CORRUPTIONS:
+        t = timed(lambda: [Cc.corrupt(xL, name, sev, seed=3, out=oL[sev & 1]) for sev in range(1, 6)], 2, warm=1)
+        per_type[name] = round(t, 3)
+    pinL = [torch.empty_like(hL).pin_memory() for _ in range(2)]
+
+    def suite224_e2e():
+        xin = hL.to(dev, non_blocking=True)
+        for j, (name, sev) in enumerate(passes):
+            pinL[j & 1].copy_(Cc.corrupt(xin, name, sev, seed=3, out=oL[j & 1]), non_blocking=True)
+    e2e = timed(suite224_e2e, 1, warm=1)
+    cpu = cpu_rate(_cpu_suite224_worker, 75, 2, cores, "75 passes at 224x224, random draws included, oracle/cifar_c.py")[0] if want_cpu else None
+    res["C2_224"] = entry(ms, n2 * 75, 2 * int(xL.numel()) * 75, e2e, int(xL.numel()), int(xL.numel()) * 75, cpu,
+                          "the 15 x 5 suite on 1024 x 224x224x3 uint8 (Imagenette-shaped), on-chip draws; general-size kernels "
+                          "(global workspaces), not the CIFAR throughput forms")
+    res["C2_224"]["per_corruption_ms"] = per_type
     return res
 
 

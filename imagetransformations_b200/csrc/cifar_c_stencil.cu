@@ -363,6 +363,8 @@ struct OpCcGlass {
         uint8_t* im = dst + (size_t)j * s.out_bytes;
         const int64_t img = img0 + j;
         for (int it = 0; it < p.iters; ++it) {
+          uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+          int rb_key = -1;   // (row, column block) the cached draw belongs to
           for (int t = 0; t < 2 * (R - 1) + Ccols; ++t) {
             for (int r = tid; r < R; r += kThreads) {
               const int ci = t - 2 * r;
@@ -373,7 +375,11 @@ struct OpCcGlass {
                 const int8_t* d = p.deltas + ((((img * p.iters + it) * R + r) * Ccols + ci) << 1);
                 dx = d[0]; dy = d[1];
               } else {
-                const uint4 rb = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)r + ((uint32_t)(ci >> 6) << 16));
+                const int key = r | ((ci >> 6) << 16);
+                if (key != rb_key) {
+                  rb = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)r + ((uint32_t)(ci >> 6) << 16));
+                  rb_key = key;
+                }
                 const int cb = ci & 63;
                 dx = -(int)(((cb < 32 ? rb.x : rb.z) >> (cb & 31)) & 1u);
                 dy = -(int)(((cb < 32 ? rb.y : rb.w) >> (cb & 31)) & 1u);

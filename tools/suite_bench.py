@@ -14,7 +14,8 @@ from imagetransformations_b200 import cifar_c as C
 def main():
     names = sys.argv[1:] or C.CORRUPTIONS
     n = int(os.environ.get("N", 50000))
-    x = torch.from_numpy(np.random.default_rng(1001).integers(0, 256, (n, 32, 32, 3), dtype=np.uint8)).cuda()
+    side = int(os.environ.get("SIDE", 32))
+    x = torch.from_numpy(np.random.default_rng(1001).integers(0, 256, (n, side, side, 3), dtype=np.uint8)).cuda()
     outs = [torch.empty_like(x) for _ in range(3)]
     peak = 6551.7
     mt = torch.zeros((n, 2), dtype=torch.int32, device="cuda") if os.environ.get("METRICS") else None
@@ -25,7 +26,7 @@ def main():
                 C.corrupt(x, name, sev, seed=r, out=outs[r % 3], metrics=mt)
             torch.cuda.synchronize()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            reps = 10
+            reps = int(os.environ.get("REPS", 10))
             a.record()
             for r in range(reps):
                 C.corrupt(x, name, sev, seed=r, out=outs[r % 3], metrics=mt)
