@@ -17,8 +17,8 @@ all-gathered over NCCL on a side stream, overlapped with the next pass — the o
 `roofline`     the corruption type with the largest share of the step, per-launch CUDA-event time: algorithmic bytes
                (6144 B/image: 3072 read + 3072 written) / duration vs the measured HBM copy peak (MEASURED_PEAKS.json).
 `configs`      the other BASELINE.json configs (C1 transformation.py grid, C3 16 TTA views, C4 AugMix 224x224, C5 FGSM
-               eps sweep fused with the post-attack leg; plus C2_224: the headline suite on Imagenette-shaped 224x224
-               images), each with device time, fraction of the HBM peak, e2e with host
+               eps sweep fused with the post-attack leg; plus H19: the TransformationPool population step as one fused
+               launch, and C2_224: the headline suite on Imagenette-shaped 224x224 images), each with device time, fraction of the HBM peak, e2e with host
                buffers and a CPU baseline (oracle/np_ops.py / np_chains.py: restatements pinned by goldens frozen from the
                live reference, tests/golden/).
 `cpu_baseline` / `--impl reference`: the CPU restatement of the suite (oracle/cifar_c.py — the reference has no code for 11
@@ -109,6 +109,30 @@ def _cpu_suite_worker(args):
     for name in CC.CORRUPTIONS:
         for sev in range(1, 6):
             CC.corrupt(name, sev, x, CC.draw(name, sev, x, rng))
+    return time.perf_counter() - t0
+
+
+def _cpu_h19_worker(args):
+    seed, n = args
+    import random
+    import numpy as np
+    from oracle import np_chains as CH, np_ops as O
+    rs = np.random.RandomState(seed)
+    random.seed(seed)
+    tn = O.to_tensor_normalize(rs.randint(0, 256, (n, H, W, 3)).astype(np.uint8), CH.CIFAR10_MEAN, CH.CIFAR10_STD)
+    enh = [("enhance_contrast", "factor"), ("enhance_brightness", "factor"), ("enhance_sharpness", "factor"),
+           ("enhance_color", "factor"), ("motion_blur", "size")]
+    t0 = time.perf_counter()
+    for i in range(n):
+        u = O.tensor_to_pil(tn[i:i + 1], CH.CIFAR10_MEAN, CH.CIFAR10_STD)
+        u = CH.pool_op(u, "gaussian_noise", {"severity": 3}, {"noise": rs.normal(0, CH.POOL_GAUSS[2] * 255, u.shape)})
+        u = CH.pool_op(u, "impulse_noise", {"severity": 3}, {"mask": rs.random_sample(u.shape[:3])})
+        u = CH.pool_op(u, "shot_noise", {"severity": 3}, {"counts": rs.poisson(O.shot_noise_scaled(u, CH.POOL_SHOT[2]))})
+        u = CH.pool_op(u, "defocus_blur", {"severity": 3})
+        for _ in range(random.randint(0, 3)):
+            name, key = random.choice(enh)
+            u = CH.pool_op(u, name, {key: random.choice([5, 7, 9, 11]) if key == "size" else random.uniform(0.5, 2.0)})
+        O.to_tensor_normalize(u, CH.CIFAR10_MEAN, CH.CIFAR10_STD)
     return time.perf_counter() - t0
 
 
@@ -646,6 +670,44 @@ def bench_configs(dev, rank, world, peak, barrier, max_over_ranks, want_cpu):
                       "10000 x 3x32x32 f32 image + gradient; 61440 B per input image (images_per_s counts output images)")
     res["C5"]["sign_step_only_ms"] = ms_step_only
     del x8, xf, g, hx, hg, ho
+
+    # ---- H19: the GA's population step (pipenline/cifar_image_transformations.py:141-152, 203-226): base chain + 0..3 enhancers,
+    #      10000 individuals (500 images x 20 individuals), ONE fused launch, noise drawn on chip ----
+    from imagetransformations_b200 import cifar_image_transformations as Mp
+    import random as _random
+    _random.seed(1234 + rank)
+    base = [("gaussian_noise", {"severity": 3}), ("impulse_noise", {"severity": 3}), ("shot_noise", {"severity": 3}),
+            ("defocus_blur", {"severity": 3})]
+    enh = ["enhance_contrast", "enhance_brightness", "enhance_sharpness", "enhance_color", "motion_blur"]
+    chains = [base + [(_random.choice(enh), {}) for _ in range(_random.randint(0, 3))] for _ in range(n1)]
+    recs = [Mp.encode_chain(c) for c in chains]
+    ops_np = np.zeros((n1, 7), Mp.POOL_OP_DTYPE)
+    ops_np["kind"] = -1
+    for i, r in enumerate(recs):
+        ops_np[i, :len(r)] = r
+    xg = B.to_tensor(torch.from_numpy(rng.integers(0, 256, (n1, H, W, 3), dtype=np.uint8)).to(dev), CIFAR10_MEAN, CIFAR10_STD)
+    ms = timed(lambda: Mp.pool_chain_batch(xg, ops_np, seed=3), 5)
+
+    def unfused():   # the same ops as separate launches over the whole batch (base chain only), on-chip noise
+        u = B.to_uint8(xg, CIFAR10_MEAN, CIFAR10_STD, clamp=True)
+        u = B.noise_philox(u, L.NOISE_GAUSS_F64, Mp.GAUSSIAN_LEVELS[2] * 255.0, 3)
+        u = B.noise_philox(u, L.NOISE_IMPULSE, Mp.IMPULSE_LEVELS[2], 4)
+        u = B.noise_philox(u, L.NOISE_SHOT, Mp.SHOT_LEVELS[2], 5)
+        u = B.pil_gaussian_blur(u, Mp.DEFOCUS_LEVELS[2])
+        return B.to_tensor(u, CIFAR10_MEAN, CIFAR10_STD)
+    ms_unfused = timed(unfused, 5)
+    hxg = xg.cpu().pin_memory()
+    hog = torch.empty_like(hxg).pin_memory()
+
+    def h19_e2e():
+        hog.copy_(Mp.pool_chain_batch(hxg.to(dev, non_blocking=True), ops_np, seed=3), non_blocking=True)
+    e2e = timed(h19_e2e, 1, warm=1)
+    cpu = cpu_rate(_cpu_h19_worker, 1, 256, cores, "base chain + 0..3 enhancers per individual, oracle/np_chains.py:individual_apply (golden-pinned)")[0] if want_cpu else None
+    res["H19"] = entry(ms, n1, n1 * 24576, e2e, n1 * 12288, n1 * 12288, cpu,
+                       "TransformationPool population step: tensor_to_pil -> gaussian/impulse/shot noise, defocus_blur (severity 3) "
+                       "-> 0..3 enhancers -> pil_to_tensor, 10000 individuals, ONE launch; 24576 B/individual")
+    res["H19"]["base_chain_as_separate_launches_ms"] = ms_unfused
+    del xg, hxg, hog
 
     # ---- C2 on Imagenette-shaped images (north star: "CIFAR- and Imagenette-shaped batches"): the same 75 passes over
     #      1024 x 224x224x3 (154 MB per batch: the bytes of the 50000-image CIFAR batch), on-chip draws, two rotating outputs ----

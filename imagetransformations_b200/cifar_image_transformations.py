@@ -144,3 +144,96 @@ class Individual:
         out = B.to_tensor(x, CIFAR10_MEAN, CIFAR10_STD)
         self.transformed_image = out[0] if single else out
         return self.transformed_image
+
+
+# ------------------------------------------------------------------------------------------------
+# The population in one launch (imgtx_pool_chain_f32)
+# ------------------------------------------------------------------------------------------------
+POOL_KINDS = {"gaussian_noise": 0, "impulse_noise": 1, "shot_noise": 2, "defocus_blur": 3, "enhance_contrast": 4,
+              "enhance_brightness": 5, "enhance_sharpness": 6, "enhance_color": 7, "motion_blur": 8,
+              "histogram_equalization": 9}
+POOL_OP_DTYPE = np.dtype([("kind", "<i4"), ("iparam", "<i4"), ("fparam", "<f4"), ("draw", "<i4")])
+assert POOL_OP_DTYPE.itemsize == 16
+
+
+def encode_chain(transformations) -> np.ndarray:
+    """[(name, params), ...] -> POOL_OP_DTYPE records.  Parameters left out are drawn from the global `random` module exactly
+    as the op itself would draw them (severity: random.choice([1..5]); factor: random.uniform(0.5, 2.0), sharpness
+    random.uniform(0.5, 3.0); size: random.choice([5, 7, 9, 11])), in chain order.  Noise ops get draw = -1 (on chip)."""
+    rec = np.zeros(len(transformations), POOL_OP_DTYPE)
+    for i, (name, params) in enumerate(transformations):
+        params = params or {}
+        k = POOL_KINDS[name]
+        rec[i]["kind"], rec[i]["draw"] = k, -1
+        if k <= 3:
+            sev = params.get("severity")
+            rec[i]["iparam"] = random.choice([1, 2, 3, 4, 5]) if sev is None else int(sev)
+        elif k <= 7:
+            f = params.get("factor")
+            rec[i]["fparam"] = (random.uniform(0.5, 3.0) if k == 6 else random.uniform(0.5, 2.0)) if f is None else float(f)
+        elif k == 8:
+            sz = params.get("size")
+            rec[i]["iparam"] = random.choice([5, 7, 9, 11]) if sz is None else int(sz)
+    return rec
+
+
+def pool_chain_batch(x: torch.Tensor, ops: np.ndarray, seed: int = 0, draws=None, shared_input: bool = False,
+                     mean=CIFAR10_MEAN, std=CIFAR10_STD) -> torch.Tensor:
+    """x: (n,3,h,w) normalised f32 CUDA batch, or one (3,h,w) image shared by all n individuals (shared_input);
+    ops: (n, max_ops) POOL_OP_DTYPE (kind -1 ends a list).  draws: {"gauss": (k,h,w,3) f64, "impulse": (k,h,w) f64,
+    "shot": (k,h,w,3) int64} blocks that ops[..]["draw"] index; without them the noise is drawn on chip from `seed`."""
+    x = B._check_f32(x)
+    ops = np.ascontiguousarray(ops)
+    if ops.dtype != POOL_OP_DTYPE or ops.ndim != 2:
+        raise ValueError("ops must be an (n, max_ops) array of POOL_OP_DTYPE records")
+    n, max_ops = ops.shape
+    if shared_input:
+        if x.dim() != 3:
+            raise ValueError("shared_input takes one (3,h,w) image")
+        stride = 0
+    else:
+        if x.dim() != 4 or x.shape[0] != n:
+            raise ValueError("one input image per individual")
+        stride = 3 * x.shape[-2] * x.shape[-1]
+    if x.shape[-3] != 3:
+        raise ValueError("RGB images only")
+    h, w = int(x.shape[-2]), int(x.shape[-1])
+    d = draws or {}
+    def f64(a):
+        return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(x.device)
+    g = f64(d["gauss"]) if "gauss" in d else None
+    m = f64(d["impulse"]) if "impulse" in d else None
+    s = torch.from_numpy(np.ascontiguousarray(d["shot"], dtype=np.int64)).to(x.device) if "shot" in d else None
+    for name, arr, per in (("gauss", g, h * w * 3), ("impulse", m, h * w), ("shot", s, h * w * 3)):
+        sel = ops["draw"][(ops["kind"] == POOL_KINDS[{"gauss": "gaussian_noise", "impulse": "impulse_noise", "shot": "shot_noise"}[name]])]
+        if len(sel) and sel.max() >= 0 and (arr is None or (int(sel.max()) + 1) * per > arr.numel()):
+            raise ValueError(f"ops refer to {name} draw blocks that were not given")
+    out = torch.empty((n, 3, h, w), dtype=torch.float32, device=x.device)
+    with torch.cuda.device_of(x):
+        od = torch.from_numpy(ops.view(np.uint8).reshape(n, -1)).to(x.device)
+        mk, mp = B._fptr(list(mean))
+        sk, sp = B._fptr(list(std))
+        L.check(L.load().imgtx_pool_chain_f32(x.data_ptr(), stride, out.data_ptr(), n, h, w, od.data_ptr(), max_ops, mp, sp,
+                                              g.data_ptr() if g is not None else None,
+                                              m.data_ptr() if m is not None else None,
+                                              s.data_ptr() if s is not None else None,
+                                              int(seed) & 0xFFFFFFFFFFFFFFFF, B._stream()))
+    return out
+
+
+def apply_population(individuals, original_image: torch.Tensor, seed: int = 0) -> torch.Tensor:
+    """Every Individual of a population applied to the same (3,h,w) normalised image in ONE launch (the loop of
+    evolutionary_search, pipenline/cifar_image_transformations.py:236-260, calls apply_transformations once per individual:
+    6+ launches, three numpy draws and one device->host round trip each).  Op parameters left open are drawn per
+    individual as the ops would draw them; the noise is drawn on chip (seed).  Sets transformed_image on each individual."""
+    t = _cuda(original_image)
+    chains = [encode_chain(ind.transformations) for ind in individuals]
+    max_ops = max(1, max(len(c) for c in chains))
+    ops = np.zeros((len(chains), max_ops), POOL_OP_DTYPE)
+    ops["kind"] = -1
+    for i, c in enumerate(chains):
+        ops[i, :len(c)] = c
+    out = pool_chain_batch(t, ops, seed=seed, shared_input=True)
+    for i, ind in enumerate(individuals):
+        ind.transformed_image = out[i]
+    return out

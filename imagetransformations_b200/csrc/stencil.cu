@@ -11,7 +11,11 @@
 //                               reference: pipenline/cifar_image_transformations.py:109-119 (motion_blur)
 // Roofline: nominally HBM (2 B/element); wide kernels (31 taps x 2 passes) are integer-ALU bound.
 #include "sep_mma.cuh"
+#include "enhance_op.cuh"
+#include "rng.cuh"
 #include <math.h>
+#include <mutex>
+#include <vector>
 #include <string.h>
 
 namespace imgtx {
@@ -339,6 +343,171 @@ struct OpBoxH : NoSpill {
   }
 };
 
+// ---------------------------------------------------------------------------------------------
+// TransformationPool chains (pipenline/cifar_image_transformations.py:141-152 applied to the population of
+// :203-226): tensor_to_pil -> up to max_ops TransformationPool ops -> pil_to_tensor as ONE launch.  One CTA owns one
+// individual: the uint8 image never leaves shared memory between the ops, every op is the operator the single-op entry
+// points run (OpPilGauss, OpEnhance, OpBoxH and the noise formulas of noise.cu), so the result is the composition of
+// those, byte for byte.  Random draws are injected per op (the reference's numpy draws: parity) or made on chip (Philox
+// keyed by image, op position and element; shot noise draws Poisson(rate) from the image it finds, which is what removes
+// the host round trip of the op-by-op path).
+struct PoolOp {  // == imgtx_pool_op_t
+  int32_t kind, iparam;
+  float fparam;
+  int32_t draw;   // index of this op's block in its draw array, < 0: on-chip draws
+};
+struct PoolChainParams {
+  float mean[3], std[3];
+  PilGaussParams blur[5];          // defocus_blur severities (:72-77: GaussianBlur radius 3, 4, 6, 8, 10)
+  const PoolOp* ops;               // device (n, max_ops)
+  int max_ops;
+  const double* gauss;             // device draw arrays (blocks of h*w*3, h*w, h*w*3 values)
+  const double* impulse;
+  const long long* shot;
+  uint64_t seed;
+  int64_t x_stride;                // floats between input images; 0: every individual starts from the same image
+};
+// the reference's severity tables (:43, :54, :65)
+__constant__ double kPoolGaussStd[5] = {0.08, 0.12, 0.18, 0.26, 0.38};
+__constant__ double kPoolImpulse[5] = {0.03, 0.06, 0.09, 0.17, 0.27};
+__constant__ int kPoolShot[5] = {60, 25, 12, 5, 3};
+// On-chip shot noise samples its Poisson count by inverting the CDF with one 32-bit uniform: per severity and input byte b,
+// cdf[k] = floor(P(K <= k) * 2^32) for k = 0 .. lam - 1 with K ~ Poisson(f32(b) / 255 * lam) (every k >= lam clips to 255),
+// built on the host in float64 and uploaded once per device (fill_pool_shot_cdf).  Offsets of the five tables below.
+constexpr int kPoolShotRows = 60 + 25 + 12 + 5 + 3;
+static __device__ uint32_t g_pool_shot_cdf[kPoolShotRows * 256];   // [severity offset + k][b]
+__constant__ int kPoolShotOff[5] = {0, 60, 85, 97, 102};
+
+__global__ void __launch_bounds__(256)
+pool_chain_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, Shape s, PoolChainParams p, int buf_bytes) {
+  extern __shared__ __align__(16) uint8_t psm[];
+  uint8_t* cur = psm;
+  uint8_t* oth = psm + buf_bytes;
+  uint8_t* scratch = psm + 2 * buf_bytes;                         // max(OpEnhance scratch, one image for OpPilGauss)
+  PoolOp* ops = reinterpret_cast<PoolOp*>(scratch + (buf_bytes > OpEnhance::kPerImage + 16 ? buf_bytes : OpEnhance::kPerImage + 16));
+  const int tid = threadIdx.x, hw = s.h * s.w, ne = hw * 3;
+  const Philox rng(p.seed);
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    __syncthreads();   // the previous image is out of the buffers
+    for (int i = tid; i < p.max_ops; i += 256) ops[i] = p.ops[img * p.max_ops + i];
+    // tensor_to_pil (:27-30): x * std + mean, clamp [0, 1], * 255, truncate
+    const float* xi = x + img * p.x_stride;
+    for (int i = tid; i < ne; i += 256) {
+      const int ch = i / hw, px = i - ch * hw;
+      float v = __fadd_rn(__fmul_rn(xi[i], p.std[ch]), p.mean[ch]);
+      v = fminf(fmaxf(v, 0.0f), 1.0f);
+      cur[px * 3 + ch] = (uint8_t)(__float2int_rz(__fmul_rn(v, 255.0f)) & 255);
+    }
+    __syncthreads();
+    for (int k = 0; k < p.max_ops; ++k) {
+      const PoolOp op = ops[k];
+      if (op.kind < 0) break;
+      const int sev = min(max(op.iparam, 1), 5) - 1;
+      bool swapped = true;
+      switch (op.kind) {
+        case IMGTX_POOL_GAUSSIAN_NOISE: {   // :39-48  clip(f32(p) + normal(0, std*255), 0, 255) in float64, truncate
+          if (op.draw >= 0) {
+            const double* d = p.gauss + (int64_t)op.draw * ne;
+            for (int i = tid; i < ne; i += 256) {
+              double v = __dadd_rn((double)(float)cur[i], d[i]);
+              v = v < 0.0 ? 0.0 : (v > 255.0 ? 255.0 : v);
+              cur[i] = (uint8_t)(int)v;
+            }
+          } else {
+            const float sd = (float)(kPoolGaussStd[sev] * 255.0);
+            for (int i = tid; 2 * i < ne; i += 256) {
+              const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x90u + k, (uint32_t)i);
+              float z[2];
+              box_muller_fast(r.x, r.y, z[0], z[1]);
+#pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                if (2 * i + e >= ne) break;
+                float v = (float)cur[2 * i + e] + z[e] * sd;
+                v = v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v);
+                cur[2 * i + e] = (uint8_t)__float2int_rz(v);
+              }
+            }
+          }
+          swapped = false;
+          break;
+        }
+        case IMGTX_POOL_IMPULSE_NOISE: {    // :50-59  one uniform per pixel: < p/2 -> 0, > 1 - p/2 -> 255
+          const double pr = kPoolImpulse[sev];
+          const double* d = op.draw >= 0 ? p.impulse + (int64_t)op.draw * hw : nullptr;
+          for (int px = tid; px < hw; px += 256) {
+            double m;
+            if (d) m = d[px];
+            else m = (double)u01(rng((uint32_t)img, (uint32_t)(img >> 32), 0x90u + k, (uint32_t)px).x);
+            if (m < pr / 2) { cur[px * 3] = 0; cur[px * 3 + 1] = 0; cur[px * 3 + 2] = 0; }
+            if (m > 1 - pr / 2) { cur[px * 3] = 255; cur[px * 3 + 1] = 255; cur[px * 3 + 2] = 255; }
+          }
+          swapped = false;
+          break;
+        }
+        case IMGTX_POOL_SHOT_NOISE: {       // :61-70  k ~ Poisson(f32(p) / 255 * lam);  clip(k / lam * 255, 0, 255)
+          const int lam = kPoolShot[sev];
+          const long long* d = op.draw >= 0 ? p.shot + (int64_t)op.draw * ne : nullptr;
+          // count -> byte once per op (the float64 division per element costs more than everything else here): counts of
+          // lam or more clip to 255
+          uint8_t* klut = scratch;
+          if (tid < lam) klut[tid] = (uint8_t)(int)__dmul_rn(__ddiv_rn((double)tid, (double)lam), 255.0);
+          __syncthreads();
+          for (int i = tid; i < ne; i += 256) {
+            long long cnt;
+            if (d) cnt = d[i];
+            else {
+              // one Philox call serves four elements; count = number of CDF entries the uniform has passed (binary search)
+              const uint4 r4 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x90u + k, (uint32_t)(i >> 2));
+              const uint32_t r = (i & 3) == 0 ? r4.x : ((i & 3) == 1 ? r4.y : ((i & 3) == 2 ? r4.z : r4.w));
+              const uint32_t* cdf = g_pool_shot_cdf + kPoolShotOff[sev] * 256 + cur[i];
+              int lo = 0, hi = lam;            // first k in [0, lam] with r < cdf[k]  (cdf[lam] = 2^32)
+              while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (r < cdf[mid * 256]) hi = mid; else lo = mid + 1;
+              }
+              cnt = lo;
+            }
+            cur[i] = cnt >= lam ? (uint8_t)255 : (cnt < 0 ? (uint8_t)0 : klut[cnt]);
+          }
+          swapped = false;
+          break;
+        }
+        case IMGTX_POOL_DEFOCUS_BLUR:       // :72-77
+          OpPilGauss::run<true>(cur, oth, 1, 0, s, p.blur[sev], scratch, nullptr);
+          break;
+        case IMGTX_POOL_MOTION_BLUR: {      // :109-119
+          BoxHParams b;
+          b.size = max(op.iparam, 1);
+          b.kv = (float)(1.0 / b.size);
+          OpBoxH::run<true>(cur, oth, 1, 0, s, b, scratch, nullptr);
+          break;
+        }
+        default: {                          // ImageEnhance ops :81-106, histogram_equalization :122-129
+          EnhanceParams e;
+          e.kind = op.kind == IMGTX_POOL_ENHANCE_CONTRAST ? IMGTX_ENH_CONTRAST
+                   : op.kind == IMGTX_POOL_ENHANCE_BRIGHTNESS ? IMGTX_ENH_BRIGHTNESS
+                   : op.kind == IMGTX_POOL_ENHANCE_SHARPNESS ? IMGTX_ENH_SHARPNESS
+                   : op.kind == IMGTX_POOL_ENHANCE_COLOR ? IMGTX_ENH_COLOR : IMGTX_ENH_HISTEQ_YUV;
+          e.factor = op.fparam;
+          e.factor_per_image = nullptr;
+          if ((ne & 3) == 0) OpEnhance::run<true>(cur, oth, 1, 0, s, e, scratch, nullptr);
+          else OpEnhance::run<false>(cur, oth, 1, 0, s, e, scratch, nullptr);
+          break;
+        }
+      }
+      __syncthreads();
+      if (swapped) { uint8_t* t = cur; cur = oth; oth = t; }
+    }
+    // pil_to_tensor (:32-34): ToTensor, Normalize
+    float* oi = out + img * (int64_t)ne;
+    for (int i = tid; i < ne; i += 256) {
+      const int ch = i / hw, px = i - ch * hw;
+      const float t = __fdiv_rn((float)cur[px * 3 + ch], 255.0f);
+      oi[i] = __fdiv_rn(__fsub_rn(t, p.mean[ch]), p.std[ch]);
+    }
+  }
+}
+
 }  // namespace imgtx
 
 using namespace imgtx;
@@ -439,11 +608,8 @@ extern "C" int imgtx_cv_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_
   return launch_image_op<OpCvGauss>(in, out, n, s, p, (cudaStream_t)stream);
 }
 
-extern "C" int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
-                                          float radius, imgtx_stream_t stream) {
-  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4, "bad image shape");
-  IMGTX_CHECK_ARG(radius > 0, "radius must be positive");
-  // libImaging/BoxBlur.c _gaussian_blur_radius (passes = 3), C float / double mix reproduced literally
+// libImaging/BoxBlur.c _gaussian_blur_radius (passes = 3), C float / double mix reproduced literally
+static PilGaussParams pil_gauss_params(float radius) {
   volatile float sigma2, L, l, a;
   sigma2 = radius * radius / 3;
   L = sqrt(12.0 * sigma2 + 1.0);
@@ -455,7 +621,87 @@ extern "C" int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64
   p.ri = (int)R;
   p.ww = (uint32_t)((uint32_t)(1 << 24) / (R * 2 + 1));
   p.fw = ((1u << 24) - (uint32_t)(p.ri * 2 + 1) * p.ww) / 2;
+  return p;
+}
+
+extern "C" int imgtx_pil_gaussian_blur_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c,
+                                          float radius, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c >= 1 && c <= 4, "bad image shape");
+  IMGTX_CHECK_ARG(radius > 0, "radius must be positive");
+  const PilGaussParams p = pil_gauss_params(radius);
   return launch_image_op<OpPilGauss>(in, out, n, make_shape(h, w, c, h, w), p, (cudaStream_t)stream);
+}
+
+// Poisson CDF tables of the on-chip shot noise, uploaded once per device (stream-ordered before the first launch using them).
+static int fill_pool_shot_cdf(cudaStream_t stream) {
+  static std::mutex mu;
+  constexpr int kPoolMaxDevices = 64;
+  static bool done[kPoolMaxDevices] = {false};
+  int dev = -1;
+  IMGTX_CUDA_OK(cudaGetDevice(&dev));
+  IMGTX_CHECK_ARG(dev >= 0 && dev < kPoolMaxDevices, "device ordinal %d outside the table cache", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (done[dev]) return IMGTX_OK;
+  static std::vector<uint32_t> host;
+  if (host.empty()) {
+    host.resize((size_t)kPoolShotRows * 256);
+    const int lams[5] = {60, 25, 12, 5, 3};
+    int off = 0;
+    for (int sv = 0; sv < 5; ++sv) {
+      for (int b = 0; b < 256; ++b) {
+        // the reference's rate: float32 array / 255.0 * lam stays float32 (pipenline/cifar_image_transformations.py:66)
+        volatile float t = (float)b / 255.0f;
+        volatile float rf = t * (float)lams[sv];
+        const double r = (double)rf;
+        double pk = exp(-r), cum = 0.0;
+        for (int k = 0; k < lams[sv]; ++k) {
+          cum += pk;
+          const double v = floor(std::min(cum, 1.0) * 4294967296.0);
+          host[(size_t)(off + k) * 256 + b] = v >= 4294967295.0 ? 0xFFFFFFFFu : (uint32_t)v;
+          pk = pk * r / (double)(k + 1);
+        }
+      }
+      off += lams[sv];
+    }
+  }
+  IMGTX_CUDA_OK(cudaMemcpyToSymbolAsync(g_pool_shot_cdf, host.data(), host.size() * 4, 0, cudaMemcpyHostToDevice, stream));
+  IMGTX_CUDA_OK(cudaStreamSynchronize(stream));   // once per device: later launches on any stream may use the table
+  done[dev] = true;
+  return IMGTX_OK;
+}
+
+extern "C" int imgtx_pool_chain_f32(const float* x, int64_t x_image_stride, float* out, int64_t n, int h, int w,
+                                    const imgtx_pool_op_t* ops_dev, int max_ops, const float* mean_host,
+                                    const float* std_host, const double* gauss_draws_dev, const double* impulse_draws_dev,
+                                    const int64_t* shot_draws_dev, uint64_t seed, imgtx_stream_t stream) {
+  static_assert(sizeof(imgtx_pool_op_t) == sizeof(PoolOp) && sizeof(PoolOp) == 16, "op record layout");
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && n >= 0, "bad image shape");
+  IMGTX_CHECK_ARG(max_ops >= 1 && max_ops <= 64, "max_ops must be in [1,64]");
+  IMGTX_CHECK_ARG(x_image_stride == 0 || x_image_stride >= (int64_t)3 * h * w, "input images overlap");
+  IMGTX_CHECK_ARG(mean_host && std_host, "mean / std missing");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(x && out && ops_dev, "null pointer");
+  const Shape s = make_shape(h, w, 3, h, w);
+  const int buf = (int)align_up((size_t)s.in_bytes + 4, 16);
+  const size_t smem = 2 * (size_t)buf + std::max<size_t>(buf, OpEnhance::kPerImage + 16) + (size_t)max_ops * sizeof(PoolOp) + 16;
+  IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image %dx%d does not fit in shared memory for the fused chain "
+                  "(three copies are kept on chip); apply the ops one by one", h, w);
+  PoolChainParams p;
+  memset(&p, 0, sizeof(p));
+  for (int i = 0; i < 3; ++i) { p.mean[i] = mean_host[i]; p.std[i] = std_host[i]; }
+  const float radii[5] = {3, 4, 6, 8, 10};
+  for (int i = 0; i < 5; ++i) p.blur[i] = pil_gauss_params(radii[i]);
+  p.ops = reinterpret_cast<const PoolOp*>(ops_dev); p.max_ops = max_ops;
+  p.gauss = gauss_draws_dev; p.impulse = impulse_draws_dev; p.shot = reinterpret_cast<const long long*>(shot_draws_dev);
+  p.seed = seed; p.x_stride = x_image_stride;
+  const int rc_tab = fill_pool_shot_cdf((cudaStream_t)stream);
+  if (rc_tab) return rc_tab;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(pool_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)smem_per_sm() / (smem + 1024)));
+  const int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * per_sm);
+  pool_chain_kernel<<<(unsigned)grid, 256, smem, (cudaStream_t)stream>>>(x, out, n, s, p, buf);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
 }
 
 extern "C" int imgtx_box_filter_h_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int size,

@@ -160,6 +160,38 @@ int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
 int imgtx_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
                           int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
 
+/* ---- TransformationPool chains ------------------------------------------------- */
+/* Individual(transformations).apply_transformations for a whole population in ONE launch
+   (pipenline/cifar_image_transformations.py:141-152 over the population of :203-226): tensor_to_pil -> the ops ->
+   pil_to_tensor; the uint8 image stays in shared memory between the ops. */
+typedef enum {
+  IMGTX_POOL_GAUSSIAN_NOISE = 0,         /* :39-48   iparam = severity 1..5 */
+  IMGTX_POOL_IMPULSE_NOISE = 1,          /* :50-59   iparam = severity */
+  IMGTX_POOL_SHOT_NOISE = 2,             /* :61-70   iparam = severity */
+  IMGTX_POOL_DEFOCUS_BLUR = 3,           /* :72-77   iparam = severity */
+  IMGTX_POOL_ENHANCE_CONTRAST = 4,       /* :81-85   fparam = factor */
+  IMGTX_POOL_ENHANCE_BRIGHTNESS = 5,     /* :88-92 */
+  IMGTX_POOL_ENHANCE_SHARPNESS = 6,      /* :95-99 */
+  IMGTX_POOL_ENHANCE_COLOR = 7,          /* :102-106 */
+  IMGTX_POOL_MOTION_BLUR = 8,            /* :109-119 iparam = size (odd) */
+  IMGTX_POOL_HISTOGRAM_EQUALIZATION = 9, /* :122-129 */
+  IMGTX_POOL_END = -1                    /* ends an individual's list before max_ops */
+} imgtx_pool_kind;
+typedef struct {
+  int32_t kind;    /* imgtx_pool_kind */
+  int32_t iparam;
+  float fparam;
+  int32_t draw;    /* noise ops: index of this op's block in its draw array; < 0 = draws made on chip from `seed` */
+} imgtx_pool_op_t;
+/* x: normalised f32, n images x_image_stride floats apart (0: every individual starts from the same (3,h,w) image);
+   out (n,3,h,w) f32; ops_dev (n, max_ops) records.  Draw arrays (device, nullable when no op refers to them): gaussian
+   blocks of h*w*3 f64 (np.random.normal(0, std*255, shape)), impulse blocks of h*w f64 (np.random.random), shot blocks of
+   h*w*3 int64 (np.random.poisson).  Three copies of the uint8 image are kept on chip: sizes up to about 150x150. */
+int imgtx_pool_chain_f32(const float* x, int64_t x_image_stride, float* out, int64_t n, int h, int w,
+                         const imgtx_pool_op_t* ops_dev, int max_ops, const float* mean_host, const float* std_host,
+                         const double* gauss_draws_dev, const double* impulse_draws_dev, const int64_t* shot_draws_dev,
+                         uint64_t seed, imgtx_stream_t stream);
+
 /* ---- stencils ------------------------------------------------------------------------------- */
 /* OpenCV's bit-exact Q8 Gaussian kernel for CV_8U (ksize odd <= 31): host helper. */
 int imgtx_cv_gaussian_kernel_host(int ksize, double sigma, int32_t* k_host);
