@@ -125,26 +125,3 @@ def corrupt_sharded(x_all, name: str, severity: int, draws: Optional[dict] = Non
     sums = all_gather_rows(local, n)
     gathered = all_gather_rows(out, n) if gather_outputs else None
     return out, sums, gathered
-
-
-def bind_to_gpu_cpus(device_index: int) -> int:
-    """Pin this process (one per GPU) to the CPU cores NVML reports as local to `device_index`, so that pinned host
-    buffers allocated afterwards land on the GPU's NUMA node and host<->device copies do not cross the socket link.
-    Returns the number of cores bound to (0 = left unchanged: NVML missing, or the mask does not intersect the cores
-    this process may use)."""
-    import os
-    try:
-        import pynvml
-        pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
-        ncpu = os.cpu_count() or 1
-        words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
-    except Exception:
-        return 0
-    local = {64 * wi + b for wi, wv in enumerate(words) for b in range(64) if (int(wv) >> b) & 1}
-    allowed = os.sched_getaffinity(0)
-    cores = local & allowed
-    if not cores or cores == allowed:
-        return 0
-    os.sched_setaffinity(0, cores)
-    return len(cores)
