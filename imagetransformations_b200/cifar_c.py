@@ -146,6 +146,25 @@ def zoom_axis_table(size: int, z: float):
 _zoom_cache = {}
 
 
+_zoom_level_cache = {}
+
+
+def zoom_level_tables(h: int, w: int, severity: int, device):
+    """Per-level, per-axis tables of zoom_blur on `device`: (yidx (nz,2,h) int32, yt (nz,h) f32, xidx (nz,2,w), xt (nz,w), nz)."""
+    key = (h, w, severity, str(device))
+    if key not in _zoom_level_cache:
+        lo, hi = CIFAR_TABLE["zoom_blur"][severity - 1]
+        zs = np.arange(lo, hi, 0.01)
+        ya = [zoom_axis_table(h, float(z)) for z in zs]
+        xa = [zoom_axis_table(w, float(z)) for z in zs]
+        yi = np.stack([np.stack([a[0], a[1]]) for a in ya]).astype(np.int32)
+        xi = np.stack([np.stack([a[0], a[1]]) for a in xa]).astype(np.int32)
+        yt = np.stack([a[2] for a in ya]).astype(np.float32)
+        xt = np.stack([a[2] for a in xa]).astype(np.float32)
+        _zoom_level_cache[key] = tuple(torch.from_numpy(np.ascontiguousarray(a)).to(device) for a in (yi, yt, xi, xt)) + (len(zs),)
+    return _zoom_level_cache[key]
+
+
 def zoom_operator(h: int, w: int, severity: int, device):
     """zoom_blur as one sparse linear operator W = (I + sum_z Zoom_z)/(n+1) in CSR form on `device` (taps of a row merged
     in f64, sorted by source index, weights f32)."""
@@ -379,6 +398,10 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metri
     elif name == "defocus_blur":
         dydx, wts = disk_taps(p[0], p[1])
         L.check(lib.imgtx_cc_defocus_u8(xp, op, n, h, w, c, len(wts), dydx.ctypes.data, wts.ctypes.data, flags, mp, st))
+    elif name == "zoom_blur" and (flags & L.CC_FAST) and h * w > 1024:
+        yi, yt, xi, xt, nz = zoom_level_tables(h, w, severity, dev)
+        L.check(lib.imgtx_cc_zoom_levels_u8(xp, op, n, h, w, c, nz, yi.data_ptr(), yt.data_ptr(), xi.data_ptr(), xt.data_ptr(),
+                                            mp, st))
     elif name == "zoom_blur":
         ip, idx, wt, max_row = zoom_operator(h, w, severity, dev)
         L.check(lib.imgtx_cc_csr_ell_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(),

@@ -203,4 +203,133 @@ int zoom_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const in
   return launch_zoom_fast<20>(in, out, n, P, indptr, indices, weights, metrics, stream);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// zoom_blur on images too large for the register-resident operator (224 x 224: 0.7-2.2 M merged taps), throughput form.
+// The merged operator is what the exact form streams through L2 (17 MB per image at severity 5); here the sum is evaluated
+// level by level instead, out = (x + sum_z bilinear_z(x)) / (nz + 1), from per-axis tables (i0, i1, t per zoom level and
+// output index: oracle/cifar_c.py:zoom_axis_table) that are tiny.  A CTA owns a 32 x 32 output tile: it copies the tables of
+// its rows and columns and the source window all levels touch (the tile shrunk towards the centre, at most ~80 x 80) into
+// shared memory, then every thread accumulates its four pixels in float32 on the 0..255 scale.
+// Same real-valued expression as the merged operator (whose weights are these products summed in float64): <= 1 LSB.
+struct ZoomLevelsParams {
+  const int32_t* yidx;   // device (nz, 2, h): i0, i1 per level
+  const float* yt;       // device (nz, h)
+  const int32_t* xidx;   // device (nz, 2, w)
+  const float* xt;       // device (nz, w)
+  int nz, h, w;
+  float inv;             // 1 / (nz + 1)
+};
+constexpr int kZoomTile = 32;
+constexpr int kZoomMaxLevels = 32;
+
+__global__ void __launch_bounds__(256)
+zoom_levels_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, ZoomLevelsParams p, int win_cap) {
+  extern __shared__ __align__(16) uint8_t zsm[];
+  // [nz][32] row tables (i0, i1, t) | [nz][32] column tables | source window (rows x cols x 3 bytes)
+  int* ry0 = reinterpret_cast<int*>(zsm);
+  int* ry1 = ry0 + p.nz * kZoomTile;
+  float* rty = reinterpret_cast<float*>(ry1 + p.nz * kZoomTile);
+  int* cx0 = reinterpret_cast<int*>(rty + p.nz * kZoomTile);
+  int* cx1 = cx0 + p.nz * kZoomTile;
+  float* ctx = reinterpret_cast<float*>(cx1 + p.nz * kZoomTile);
+  __shared__ int bbox[4];
+  uint8_t* win = reinterpret_cast<uint8_t*>(ctx + p.nz * kZoomTile);
+  const int tid = threadIdx.x, lane = tid & 31, wy = tid >> 5;
+  const int tiles_x = (p.w + kZoomTile - 1) / kZoomTile, tiles_y = (p.h + kZoomTile - 1) / kZoomTile;
+  const int64_t total = n * tiles_x * tiles_y;
+  for (int64_t job = blockIdx.x; job < total; job += gridDim.x) {
+    const int64_t img = job / (tiles_x * tiles_y);
+    const int tj = (int)(job - img * tiles_x * tiles_y), ty0 = (tj / tiles_x) * kZoomTile, tx0 = (tj % tiles_x) * kZoomTile;
+    __syncthreads();   // the previous tile is done with the tables and the window
+    if (tid < 4) bbox[tid] = tid < 2 ? 1 << 30 : -1;
+    __syncthreads();
+    int ymin = 1 << 30, ymax = -1, xmin = 1 << 30, xmax = -1;
+    for (int e = tid; e < p.nz * kZoomTile; e += 256) {
+      const int z = e >> 5, k = e & 31;
+      const int y = min(ty0 + k, p.h - 1), x = min(tx0 + k, p.w - 1);
+      const int a0 = p.yidx[(z * 2) * p.h + y], a1 = p.yidx[(z * 2 + 1) * p.h + y];
+      const int b0 = p.xidx[(z * 2) * p.w + x], b1 = p.xidx[(z * 2 + 1) * p.w + x];
+      ry0[e] = a0; ry1[e] = a1; rty[e] = p.yt[z * p.h + y];
+      cx0[e] = b0; cx1[e] = b1; ctx[e] = p.xt[z * p.w + x];
+      ymin = min(ymin, min(a0, a1)); ymax = max(ymax, max(a0, a1));
+      xmin = min(xmin, min(b0, b1)); xmax = max(xmax, max(b0, b1));
+    }
+    ymin = min(ymin, ty0); ymax = max(ymax, min(ty0 + kZoomTile, p.h) - 1);      // the identity term reads the tile itself
+    xmin = min(xmin, tx0); xmax = max(xmax, min(tx0 + kZoomTile, p.w) - 1);
+    atomicMin(&bbox[0], ymin); atomicMin(&bbox[1], xmin); atomicMax(&bbox[2], ymax); atomicMax(&bbox[3], xmax);
+    __syncthreads();
+    const int wy0 = bbox[0], wx0 = bbox[1], wh = bbox[2] - bbox[0] + 1, ww = bbox[3] - bbox[1] + 1;
+    const uint8_t* im = in + img * (int64_t)p.h * p.w * 3;
+    const bool in_smem = wh * ww * 3 <= win_cap;   // always, for the zoom ranges of the severity table; else read through L1
+    if (in_smem) {
+      const int rowb = ww * 3;
+      for (int e = tid; e < wh * rowb; e += 256) {
+        const int r = e / rowb, b = e - r * rowb;
+        win[e] = im[((int64_t)(wy0 + r) * p.w + wx0) * 3 + b];
+      }
+    }
+    __syncthreads();
+    const uint8_t* base = in_smem ? win : im;
+    const int pitch = in_smem ? ww * 3 : p.w * 3, oy = in_smem ? wy0 : 0, ox = in_smem ? wx0 : 0;
+    const int x = tx0 + lane;
+    if (x < p.w) {
+      for (int k = wy; k < kZoomTile; k += 8) {
+        const int y = ty0 + k;
+        if (y >= p.h) break;
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+        for (int z = 0; z < p.nz; ++z) {
+          const int e = z * kZoomTile;
+          const float ty = rty[e + k], tx = ctx[e + lane];
+          const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
+          const uint8_t* r0 = base + (ry0[e + k] - oy) * pitch;
+          const uint8_t* r1 = base + (ry1[e + k] - oy) * pitch;
+          const int c0 = (cx0[e + lane] - ox) * 3, c1 = (cx1[e + lane] - ox) * 3;
+          // byte -> float without the conversion pipe: the byte planted in the mantissa of 2^23 (exact)
+          auto bf = [](uint8_t b) { return __uint_as_float(0x4B000000u | (uint32_t)b) - 8388608.0f; };
+          a0 = __fmaf_rn(bf(r1[c1]), w11, __fmaf_rn(bf(r1[c0]), w10, __fmaf_rn(bf(r0[c1]), w01, __fmaf_rn(bf(r0[c0]), w00, a0))));
+          a1 = __fmaf_rn(bf(r1[c1 + 1]), w11, __fmaf_rn(bf(r1[c0 + 1]), w10, __fmaf_rn(bf(r0[c1 + 1]), w01, __fmaf_rn(bf(r0[c0 + 1]), w00, a1))));
+          a2 = __fmaf_rn(bf(r1[c1 + 2]), w11, __fmaf_rn(bf(r1[c0 + 2]), w10, __fmaf_rn(bf(r0[c1 + 2]), w01, __fmaf_rn(bf(r0[c0 + 2]), w00, a2))));
+        }
+        const uint8_t* self = base + (y - oy) * pitch + (x - ox) * 3;
+        uint8_t* o = out + (img * (int64_t)p.h * p.w + (int64_t)y * p.w + x) * 3;
+        // 2^-10: a sum that is an integer in real arithmetic floors to itself
+        o[0] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a0 + (float)self[0], p.inv, 0.0009765625f), 0.0f), 255.0f));
+        o[1] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a1 + (float)self[1], p.inv, 0.0009765625f), 0.0f), 255.0f));
+        o[2] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a2 + (float)self[2], p.inv, 0.0009765625f), 0.0f), 255.0f));
+      }
+    }
+  }
+}
+
+int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz, const int32_t* yidx, const float* yt,
+                const int32_t* xidx, const float* xt, cudaStream_t stream) {
+  IMGTX_CHECK_ARG(nz >= 1 && nz <= kZoomMaxLevels, "zoom levels must be in [1,%d]", kZoomMaxLevels);
+  IMGTX_CHECK_ARG(yidx && yt && xidx && xt, "missing zoom tables");
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null image pointer");
+  ZoomLevelsParams p;
+  p.yidx = yidx; p.yt = yt; p.xidx = xidx; p.xt = xt; p.nz = nz; p.h = h; p.w = w; p.inv = (float)(1.0 / (nz + 1));
+  const size_t tab = (size_t)nz * kZoomTile * 6 * 4;
+  const int win_cap = 96 * 96 * 3;
+  const size_t smem = tab + win_cap + 16;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(zoom_levels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t tiles = n * ((w + kZoomTile - 1) / kZoomTile) * ((h + kZoomTile - 1) / kZoomTile);
+  const int64_t grid = std::min<int64_t>(tiles, (int64_t)sm_count() * 4);
+  zoom_levels_kernel<<<(unsigned)grid, 256, smem, stream>>>(in, out, n, p, win_cap);
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
 }  // namespace imgtx
+
+using namespace imgtx;
+
+extern "C" int imgtx_cc_zoom_levels_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int n_levels,
+                                       const int32_t* yidx_dev, const float* yt_dev, const int32_t* xidx_dev,
+                                       const float* xt_dev, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
+  int rc = zoom_levels(in, out, n, h, w, n_levels, yidx_dev, yt_dev, xidx_dev, xt_dev, (cudaStream_t)stream);
+  if (rc == IMGTX_OK && metrics_dev) rc = imgtx::image_checksums(out, n, (int64_t)h * w * c, metrics_dev, (cudaStream_t)stream);
+  return rc;
+}

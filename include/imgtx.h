@@ -307,6 +307,13 @@ int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, in
 int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                         const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
                         int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
+/* zoom_blur, throughput form for images larger than 32x32 (<= 1 LSB from the operator form): the sum over the zoom levels
+   evaluated level by level from per-axis tables (device): yidx (n_levels, 2, h) = source rows i0, i1 of every output row,
+   yt (n_levels, h) = its interpolation weight, xidx / xt likewise for columns (the per-level tables the canonical
+   clipped_zoom defines; the merged operator of imgtx_cc_csr_u8 is their products summed over the levels).  n_levels <= 32. */
+int imgtx_cc_zoom_levels_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int n_levels,
+                            const int32_t* yidx_dev, const float* yt_dev, const int32_t* xidx_dev, const float* xt_dev,
+                            uint32_t* metrics_dev, imgtx_stream_t stream);
 /* glass_blur: weights_host[0..lw] = scipy Gaussian taps (centre first); deltas_dev (n, iters, h-2, w-2, 2) int8 (dx, dy). */
 int imgtx_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host, int lw,
                       int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
