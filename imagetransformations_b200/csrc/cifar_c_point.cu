@@ -345,7 +345,7 @@ static int impl_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
       const size_t per = (size_t)msz * msz * sizeof(double);
       const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((256u << 20) / per)));
       double* maps = nullptr;
-      IMGTX_CUDA_OK(cudaMallocAsync((void**)&maps, per * chunk, st));
+      IMGTX_CUDA_OK(workspace_alloc((void**)&maps, per * chunk, st));
       CcPointParams q;
       memset(&q, 0, sizeof(q));
       q.kind = kind; q.p0 = p0; q.p1 = p1; q.a = maps; q.seed = seed; q.plasma_pitch = msz;

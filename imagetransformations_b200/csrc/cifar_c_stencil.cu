@@ -1525,7 +1525,7 @@ static int impl_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, in
     cudaStream_t st = (cudaStream_t)stream;
     uint8_t* tab = nullptr;
     const size_t ib = (size_t)(2 * h + 2 * w) * 4, tb = (size_t)(h + w) * 4;
-    IMGTX_CUDA_OK(cudaMallocAsync((void**)&tab, ib + tb, st));
+    IMGTX_CUDA_OK(workspace_alloc((void**)&tab, ib + tb, st));
     IMGTX_CUDA_OK(cudaMemcpyAsync(tab, zoom_idx_host, ib, cudaMemcpyHostToDevice, st));
     IMGTX_CUDA_OK(cudaMemcpyAsync(tab + ib, zoom_t_host, tb, cudaMemcpyHostToDevice, st));
     p.zidx = reinterpret_cast<const int32_t*>(tab);

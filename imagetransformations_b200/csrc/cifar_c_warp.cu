@@ -16,6 +16,7 @@
 #include <math.h>
 #include <string.h>
 #include <algorithm>
+#include <vector>
 
 namespace imgtx {
 
@@ -982,6 +983,296 @@ struct OpTElastic : ElasticCommon {
 };
 
 // ------------------------------------------------------------------------------------------------
+// elastic_transform, throughput form for images that do not fit one team's shared memory (224 x 224).  Same stages as
+// OpTElastic, each as its own kernel over a chunk of the batch, intermediates (two float32 fields, the Q7 warped image:
+// 24 bytes per pixel) in a stream-ordered workspace that stays in L2:
+//   el_fields     U(-1, 1) fields (on-chip draws, or the injected float64 fields) and the inverse affine matrices
+//   el_smooth<A>  Gaussian along one axis, 'reflect' border, float32: a CTA owns a strip of 32 lines, holds it with its
+//                 reflected margins in shared memory ([sample][line], pitch 33) and every thread slides a window of eight
+//                 accumulators along its line: per new sample one load of the sample, one of a weight, eight FFMA
+//                 (269 taps at 224 x 224 severity 2: 54 M multiply-adds per image, ~1.3 instructions each)
+//   el_warp       cv2.warpAffine's fixed-point bilinear warp of the uint8 image -> Q7 RGB (exact integers / 1024)
+//   el_remap      bilinear resampling at (y + dy, x + dx), scipy 'reflect', float32 -> uint8
+// float32 instead of the exact form's float64 smoothing and interpolation: displacement error < 1e-4 pixel, <= 1 LSB.
+struct ElasticLargeParams {
+  ElasticParams e;
+  const float* wf;     // device, 2 * lw + 1 + 14 floats: the full symmetric kernel with 7 zeros on both sides
+  int h, w;
+};
+
+__global__ void __launch_bounds__(256)
+el_matrix_kernel(double* __restrict__ Minv, int64_t img0, int64_t cn, ElasticLargeParams p) {
+  const Philox rng(p.e.seed);
+  for (int64_t li = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; li < cn; li += (int64_t)gridDim.x * blockDim.x)
+    ElasticCommon::inverse_matrix(p.e, rng, img0 + li, p.h, Minv + li * 6);
+}
+
+// blockIdx.y walks (image, field) planes, blockIdx.x the plane in groups of four elements (one Philox call each)
+__global__ void __launch_bounds__(256)
+el_fields_kernel(float* __restrict__ F, int64_t img0, int64_t cn, ElasticLargeParams p) {
+  const int hw = p.h * p.w, nq = (hw + 3) / 4;
+  const Philox rng(p.e.seed);
+  for (int64_t plane = blockIdx.y; plane < cn * 2; plane += gridDim.y) {
+    const int64_t li = plane >> 1, img = img0 + li;
+    const int f = (int)(plane & 1);
+    float* dst = F + plane * (int64_t)hw;
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < nq; q += gridDim.x * blockDim.x) {
+      float v[4];
+      if (p.e.ux) {
+        const double* src = (f ? p.e.uy : p.e.ux) + img * hw;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = 4 * q + k < hw ? fminf(fmaxf((float)src[4 * q + k], -1.0f), 1.0f) : 0.0f;
+      } else {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x81u + f, (uint32_t)q);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = (float)(rr[k] >> 8) * (2.0f / 16777216.0f) - (1.0f - 1.0f / 16777216.0f);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (4 * q + k < hw) dst[4 * q + k] = v[k];
+    }
+  }
+}
+
+// AXIS 0: along y (strip = 32 columns), AXIS 1: along x (strip = 32 rows).  src, dst: (planes, h, w) float32.
+template <int AXIS>
+__global__ void __launch_bounds__(256)
+el_smooth_kernel(const float* __restrict__ src, float* __restrict__ dst, int64_t planes, ElasticLargeParams p, float scale) {
+  extern __shared__ __align__(16) float esm[];
+  const int L = AXIS == 0 ? p.h : p.w, other = AXIS == 0 ? p.w : p.h, lw = p.e.lw;
+  const int nk = 2 * lw + 1, E = L + 2 * lw;
+  float* wp = esm;                        // nk + 14 padded weights
+  float* ext = esm + ((nk + 14 + 3) & ~3);   // [E][33]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int strips = (other + 31) / 32;
+  for (int i = tid; i < nk + 14; i += 256) wp[i] = p.wf[i];
+  for (int64_t job = blockIdx.x; job < planes * strips; job += gridDim.x) {
+    const int64_t plane = job / strips;
+    const int s0 = (int)(job - plane * strips) * 32;
+    const float* sp = src + plane * (int64_t)p.h * p.w;
+    float* dp = dst + plane * (int64_t)p.h * p.w;
+    __syncthreads();
+    // interior samples [lw, lw + L)
+    if (AXIS == 0) {
+      for (int e = tid; e < L * 32; e += 256) {
+        const int j = e >> 5, c = e & 31;
+        ext[(lw + j) * 33 + c] = s0 + c < other ? sp[(int64_t)j * p.w + s0 + c] : 0.0f;
+      }
+    } else {
+      for (int r = warp; r < 32; r += 8) {
+        const bool ok = s0 + r < other;
+        for (int xx = lane; xx < L; xx += 32) ext[(lw + xx) * 33 + r] = ok ? sp[(int64_t)(s0 + r) * p.w + xx] : 0.0f;
+      }
+    }
+    __syncthreads();
+    // reflected margins ('reflect': d c b a | a b c d | d c b a), from the interior
+    for (int e = tid; e < 2 * lw * 32; e += 256) {
+      const int m = e >> 5, c = e & 31;
+      const int j = m < lw ? m : L + m;                       // ext index of the margin sample
+      const int period = 2 * L;
+      int q = (j - lw) % period;
+      if (q < 0) q += period;
+      q = q >= L ? period - 1 - q : q;
+      ext[j * 33 + c] = ext[(lw + q) * 33 + c];
+    }
+    __syncthreads();
+    // out[o + j] = sum_t ext[o + t] * wpad[t - j + 7], t = 0 .. nk + 6  (wpad: 7 zeros, the kernel, 7 zeros)
+    const int nblk = (L + 7) / 8;
+    for (int b = warp; b < nblk; b += 8) {
+      const int o = min(b * 8, L - 8 >= 0 ? L - 8 : 0);
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = 0.0f;
+      float wr[15];                                   // wp[8 tb + 0 .. 8 tb + 14]
+#pragma unroll
+      for (int u = 0; u < 7; ++u) wr[u] = wp[u];
+      const float* col = ext + o * 33 + lane;
+      const int nt = nk + 7;                          // samples that touch the eight outputs
+      for (int tb = 0; tb * 8 < nt; ++tb) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) wr[7 + u] = 8 * tb + 7 + u < nk + 14 ? wp[8 * tb + 7 + u] : 0.0f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int t = 8 * tb + u;
+          const float v = t < nt && o + t < E ? col[t * 33] : 0.0f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] = __fmaf_rn(v, wr[u + 7 - j], acc[j]);
+        }
+#pragma unroll
+        for (int u = 0; u < 7; ++u) wr[u] = wr[8 + u];
+      }
+      if (AXIS == 0) {
+        if (s0 + lane < other) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (o + j < L) dp[(int64_t)(o + j) * p.w + s0 + lane] = acc[j] * scale;
+        }
+      } else if (s0 + lane < other) {
+        float* row = dp + (int64_t)(s0 + lane) * p.w + o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (o + j < L) row[j] = acc[j] * scale;
+      }
+    }
+  }
+}
+
+// cv2.warpAffine's per-column / per-row fixed-point terms, tabulated once per image as OpenCV does:
+// tab[li] = adelta[w], bdelta[w], X0[h], Y0[h]
+__global__ void __launch_bounds__(256)
+el_tables_kernel(const double* __restrict__ Minv, int* __restrict__ tab, int64_t cn, int h, int w) {
+  const int per = 2 * w + 2 * h;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < cn * per; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t li = i / per;
+    const int k = (int)(i - li * per);
+    const double* Ms = Minv + li * 6;
+    int v;
+    if (k < w) v = (int)rint(Ms[0] * (double)k * 1024);
+    else if (k < 2 * w) v = (int)rint(Ms[3] * (double)(k - w) * 1024);
+    else if (k < 2 * w + h) v = (int)rint((Ms[1] * (double)(k - 2 * w) + Ms[2]) * 1024) + 16;
+    else v = (int)rint((Ms[4] * (double)(k - 2 * w - h) + Ms[5]) * 1024) + 16;
+    tab[i] = v;
+  }
+}
+
+// one reflection is enough while the coordinate is within one image size of the image; further out: the general routine
+__device__ __forceinline__ int el_refl101(int i, int n) {
+  if (i <= -n || i >= 2 * n - 1) return reflect101(i, n);
+  return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i);
+}
+__device__ __forceinline__ int el_refl_half(int i, int n) {
+  if (i < -n || i >= 2 * n) return reflect_half(i, n);
+  return i < 0 ? -1 - i : (i >= n ? 2 * n - 1 - i : i);
+}
+
+// cv2.warpAffine (fixed-point bilinear, REFLECT_101) -> Q7 RGB; alpha == 0: the finished uint8 image
+__global__ void __launch_bounds__(256)
+el_warp_kernel(const uint8_t* __restrict__ in, ushort4* __restrict__ Wq, uint8_t* __restrict__ out, const int* __restrict__ tab,
+               int64_t img0, int64_t cn, ElasticLargeParams p, int direct) {
+  const int hw = p.h * p.w;
+  for (int64_t li = blockIdx.y; li < cn; li += gridDim.y)
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < hw; px += gridDim.x * blockDim.x) {
+    const int64_t i = li * hw + px;
+    const int y = px / p.w, x = px - y * p.w;
+    const int* tb = tab + li * (2 * p.w + 2 * p.h);
+    const uint8_t* im = in + (img0 + li) * (int64_t)hw * 3;
+    const int X = (tb[2 * p.w + y] + tb[x]) >> 5, Y = (tb[2 * p.w + p.h + y] + tb[p.w + x]) >> 5;
+    const int sx = X >> 5, sy = Y >> 5, fx = X & 31, fy = Y & 31;
+    const int w11 = fx * fy, w10 = fy * 32 - w11, w01 = fx * 32 - w11, w00 = 1024 - fx * 32 - w10;   // sum 1024
+    const int ya = el_refl101(sy, p.h), yb = el_refl101(sy + 1, p.h), xa = el_refl101(sx, p.w), xb = el_refl101(sx + 1, p.w);
+    const uint8_t* q00 = im + ((int64_t)ya * p.w + xa) * 3;
+    const uint8_t* q01 = im + ((int64_t)ya * p.w + xb) * 3;
+    const uint8_t* q10 = im + ((int64_t)yb * p.w + xa) * 3;
+    const uint8_t* q11 = im + ((int64_t)yb * p.w + xb) * 3;
+    int v[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] = q00[c] * w00 + q01[c] * w01 + q10[c] * w10 + q11[c] * w11;   // value * 1024, exact
+    if (direct) {
+      uint8_t* o = out + ((img0 + li) * (int64_t)hw + px) * 3;
+      o[0] = (uint8_t)(v[0] >> 10); o[1] = (uint8_t)(v[1] >> 10); o[2] = (uint8_t)(v[2] >> 10);
+    } else {
+      Wq[i] = make_ushort4((unsigned short)((v[0] + 4) >> 3), (unsigned short)((v[1] + 4) >> 3), (unsigned short)((v[2] + 4) >> 3), 0);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+el_remap_kernel(const ushort4* __restrict__ Wq, const float* __restrict__ D, uint8_t* __restrict__ out, int64_t img0, int64_t cn,
+                ElasticLargeParams p) {
+  const int hw = p.h * p.w;
+  for (int64_t li = blockIdx.y; li < cn; li += gridDim.y)
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < hw; px += gridDim.x * blockDim.x) {
+    const int y = px / p.w, x = px - y * p.w;
+    const float yy = (float)y + D[(li * 2 + 1) * (int64_t)hw + px], xx = (float)x + D[(li * 2) * (int64_t)hw + px];
+    const float fy0 = floorf(yy), fx0 = floorf(xx);
+    const float ty = yy - fy0, tx = xx - fx0;
+    const int y0 = (int)fy0, x0 = (int)fx0;
+    const int ya = el_refl_half(y0, p.h), yb = el_refl_half(y0 + 1, p.h), xa = el_refl_half(x0, p.w), xb = el_refl_half(x0 + 1, p.w);
+    const ushort4* W = Wq + li * (int64_t)hw;
+    const ushort4 q00 = W[ya * p.w + xa], q01 = W[ya * p.w + xb], q10 = W[yb * p.w + xa], q11 = W[yb * p.w + xb];
+    const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
+    const float k = 0.0078125f;   // Q7
+    const float r = (__fmaf_rn((float)q11.x, w11, __fmaf_rn((float)q10.x, w10, __fmaf_rn((float)q01.x, w01, (float)q00.x * w00)))) * k;
+    const float g = (__fmaf_rn((float)q11.y, w11, __fmaf_rn((float)q10.y, w10, __fmaf_rn((float)q01.y, w01, (float)q00.y * w00)))) * k;
+    const float b = (__fmaf_rn((float)q11.z, w11, __fmaf_rn((float)q10.z, w10, __fmaf_rn((float)q01.z, w01, (float)q00.z * w00)))) * k;
+    uint8_t* o = out + ((img0 + li) * (int64_t)hw + px) * 3;
+    o[0] = (uint8_t)(int)fminf(fmaxf(r, 0.0f), 255.0f);
+    o[1] = (uint8_t)(int)fminf(fmaxf(g, 0.0f), 255.0f);
+    o[2] = (uint8_t)(int)fminf(fmaxf(b, 0.0f), 255.0f);
+  }
+}
+
+static bool elastic_large_fast_ok(int h, int w, int lw) {
+  const int L = std::max(h, w);
+  return lw <= 2048 && ((size_t)(2 * lw + 1 + 14 + 3) + (size_t)(L + 2 * std::max(lw, 0)) * 33) * 4 <= (size_t)max_smem_optin() - 1024;
+}
+
+static int elastic_large_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const ElasticParams& e,
+                              const double* weights_host, cudaStream_t st) {
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null image pointer");
+  const int hw = h * w, lw = e.lw;
+  ElasticLargeParams p;
+  memset(&p, 0, sizeof(p));
+  p.e = e; p.h = h; p.w = w;
+  const bool direct = e.alpha == 0.0;   // zero displacement: the warp alone
+  const size_t per = (size_t)hw * 24 + 64 + (size_t)(2 * w + 2 * h) * 4;
+  const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((768u << 20) / per)));   // workspace <= 768 MB
+  uint8_t* ws = nullptr;
+  const size_t wbytes = lw >= 0 ? (size_t)(2 * lw + 1 + 14) * 4 : 16;
+  IMGTX_CUDA_OK(workspace_alloc((void**)&ws, per * chunk + wbytes + 256, st));
+  float* F = reinterpret_cast<float*>(ws);                                   // [chunk][2][hw]
+  float* G = F + chunk * 2 * (size_t)hw;                                     // [chunk][2][hw]
+  ushort4* Wq = reinterpret_cast<ushort4*>(G + chunk * 2 * (size_t)hw);      // [chunk][hw]
+  double* Minv = reinterpret_cast<double*>(Wq + chunk * (size_t)hw);         // [chunk][8]
+  int* tab = reinterpret_cast<int*>(Minv + chunk * 8);                       // [chunk][2w + 2h]
+  float* wf = reinterpret_cast<float*>(ws + align_up(per * chunk, 256));
+  if (lw >= 0) {
+    std::vector<float> wh((size_t)2 * lw + 1 + 14, 0.0f);
+    for (int k = -lw; k <= lw; ++k) wh[7 + lw + k] = (float)weights_host[k < 0 ? -k : k];
+    // pageable source: the call returns once the buffer has been copied to the driver's staging memory
+    IMGTX_CUDA_OK(cudaMemcpyAsync(wf, wh.data(), wh.size() * 4, cudaMemcpyHostToDevice, st));
+  }
+  p.wf = wf;
+  const int grid = sm_count() * 8;
+  const size_t smem = lw >= 0 ? ((size_t)((2 * lw + 1 + 14 + 3) & ~3) + (size_t)(std::max(h, w) + 2 * lw) * 33) * 4 : 0;
+  if (lw >= 0) {
+    IMGTX_CUDA_OK(cudaFuncSetAttribute(el_smooth_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    IMGTX_CUDA_OK(cudaFuncSetAttribute(el_smooth_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  for (int64_t c0 = 0; c0 < n; c0 += chunk) {
+    const int64_t cn = std::min<int64_t>(chunk, n - c0);
+    el_matrix_kernel<<<(unsigned)((cn + 255) / 256), 256, 0, st>>>(Minv, c0, cn, p);
+    IMGTX_LAUNCH_OK();
+    const dim3 g2((unsigned)std::min(64, (hw + 255) / 256), (unsigned)std::min<int64_t>(cn, 4096));
+    if (!direct) {
+      el_fields_kernel<<<dim3(g2.x, (unsigned)std::min<int64_t>(2 * cn, 8192)), 256, 0, st>>>(F, c0, cn, p);
+      IMGTX_LAUNCH_OK();
+    }
+    const float* D = F;
+    if (!direct && lw >= 0) {
+      const int64_t planes = cn * 2;
+      const int sg = (int)std::min<int64_t>(planes * ((std::max(h, w) + 31) / 32), (int64_t)sm_count() * 3);
+      el_smooth_kernel<0><<<sg, 256, smem, st>>>(F, G, planes, p, 1.0f);
+      IMGTX_LAUNCH_OK();
+      el_smooth_kernel<1><<<sg, 256, smem, st>>>(G, F, planes, p, (float)e.alpha);
+      IMGTX_LAUNCH_OK();
+    }
+    el_tables_kernel<<<(unsigned)std::min<int64_t>(grid, (cn * (2 * w + 2 * h) + 255) / 256), 256, 0, st>>>(Minv, tab, cn, h, w);
+    IMGTX_LAUNCH_OK();
+    el_warp_kernel<<<g2, 256, 0, st>>>(in, Wq, out, tab, c0, cn, p, direct ? 1 : 0);
+    IMGTX_LAUNCH_OK();
+    if (!direct) {
+      el_remap_kernel<<<g2, 256, 0, st>>>(Wq, D, out, c0, cn, p);
+      IMGTX_LAUNCH_OK();
+    }
+  }
+  IMGTX_CUDA_OK(cudaFreeAsync(ws, st));
+  return IMGTX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // jpeg_compression
 // ------------------------------------------------------------------------------------------------
 struct JpegParams {
@@ -1222,9 +1513,11 @@ static int impl_cc_elastic_u8(const uint8_t* in, uint8_t* out, int64_t n, int h,
     // kMaxLw read from device memory)
     if (n == 0) return IMGTX_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    if ((flags & IMGTX_CC_FAST) && (alpha == 0.0 || lw >= 0) && fabs(alpha) <= 4096.0 && elastic_large_fast_ok(h, w, lw))
+      return elastic_large_fast(in, out, n, h, w, p, weights_host, st);
     double* wd = nullptr;
     if (lw > kMaxLw) {
-      IMGTX_CUDA_OK(cudaMallocAsync((void**)&wd, (size_t)(lw + 1) * 8, st));
+      IMGTX_CUDA_OK(workspace_alloc((void**)&wd, (size_t)(lw + 1) * 8, st));
       IMGTX_CUDA_OK(cudaMemcpyAsync(wd, weights_host, (size_t)(lw + 1) * 8, cudaMemcpyHostToDevice, st));
       p.wdev = wd;
     }

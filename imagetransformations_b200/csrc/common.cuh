@@ -18,6 +18,7 @@ namespace imgtx {
 // ---------------------------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
 int sm_count();
+cudaError_t workspace_alloc(void** ptr, size_t bytes, cudaStream_t stream);   // cudaMallocAsync from a pool that keeps its memory
 int max_smem_optin();
 
 #define IMGTX_CHECK_ARG(cond, ...)                 \

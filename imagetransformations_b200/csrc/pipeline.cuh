@@ -243,7 +243,7 @@ int launch_image_op(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s,
     }
     gtmp_per_cta = align_up(Op::gtmp_bytes(s), 256);
     scratch = Op::scratch_bytes_spilled(s) + extra_scratch;
-    IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, gtmp_per_cta * grid, stream));
+    IMGTX_CUDA_OK(workspace_alloc((void**)&gtmp, gtmp_per_cta * grid, stream));
   }
   auto kern = direct_kernel<Op>;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch));

@@ -121,7 +121,7 @@ extern "C" int imgtx_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, in
     // per-image kernel with a broadcast parameter
     if (!vec) {
       float* tmp = nullptr;
-      IMGTX_CUDA_OK(cudaMallocAsync((void**)&tmp, sizeof(float), stream));
+      IMGTX_CUDA_OK(workspace_alloc((void**)&tmp, sizeof(float), stream));
       IMGTX_CUDA_OK(cudaMemcpyAsync(tmp, &param, sizeof(float), cudaMemcpyHostToDevice, stream));
       pointwise_per_image_kernel<<<1, kPwThreads, 0, stream>>>(in, out, 1, total, op, tmp, 0);
       IMGTX_LAUNCH_OK();

@@ -408,7 +408,7 @@ static int launch_resample(const uint8_t* in, uint8_t* out, int64_t n, const Sha
     per_cta = align_up(OpResample::tmp_bytes(s, p), 256);
     scratch = OpResample::table_bytes(p) + 16;
     IMGTX_CHECK_ARG(scratch <= (size_t)max_smem - 1024, "resample tables do not fit in shared memory");
-    IMGTX_CUDA_OK(cudaMallocAsync((void**)&gtmp, per_cta * grid, stream));
+    IMGTX_CUDA_OK(workspace_alloc((void**)&gtmp, per_cta * grid, stream));
   }
   auto kern = direct_kernel<OpResample>;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scratch));
