@@ -1404,6 +1404,122 @@ static int impl_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h,
   return launch_image_op<OpCcCsrEll>(in, out, n, shp, p, (cudaStream_t)stream, 0, (int)need(G));
 }
 
+// glass_blur, throughput form for images larger than 32 x 32 (up to 65536 pixels; 224 x 224): one CTA per image.
+//   1. Gaussian (3x3 float32, 'nearest' border; sigma <= 0.4: what lies outside carries < 5e-3 LSB) src -> B1 (workspace)
+//   2. the swap sweeps on a u16 index map in SHARED memory (100 KB at 224 x 224): rows dealt to the threads, skew-2 wavefront,
+//      one block barrier per step — the exact form does the same swaps on the pixels in global memory (~20x the latency)
+//   3. gather B2[p] = B1[map[p]]      4. Gaussian B2 -> out.      sigma < 0.125: both Gaussians are one composed byte LUT.
+// Same draw convention as OpCcGlass; <= 1 LSB from it (tests/test_gpu_cifar_c_large.py).
+namespace imgtx {
+__device__ __forceinline__ void glass_blur3_large(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int h, int w,
+                                                  const Sym3x3& k) {
+  // byte -> float without the conversion pipe: the byte planted in the mantissa of 2^23
+  auto bf = [](uint8_t b) { return __uint_as_float(0x4B000000u | (uint32_t)b) - 8388608.0f; };
+  for (int px = threadIdx.x; px < h * w; px += blockDim.x) {
+    const int y = px / w, x = px - y * w;
+    const int yu = max(y - 1, 0), yd = min(y + 1, h - 1), xl = max(x - 1, 0), xr = min(x + 1, w - 1);
+    const uint8_t *ru = src + (size_t)yu * w * 3, *rc = src + (size_t)y * w * 3, *rd = src + (size_t)yd * w * 3;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const float ctr = bf(rc[x * 3 + c]);
+      const float edge_h = bf(rc[xl * 3 + c]) + bf(rc[xr * 3 + c]);
+      const float edge_v = bf(ru[x * 3 + c]) + bf(rd[x * 3 + c]);
+      const float diag = (bf(ru[xl * 3 + c]) + bf(ru[xr * 3 + c])) + (bf(rd[xl * 3 + c]) + bf(rd[xr * 3 + c]));
+      const float v = __fmaf_rn(k.k11, diag, __fmaf_rn(k.k10, edge_v, __fmaf_rn(k.k01, edge_h, __fmaf_rn(k.k00, ctr, 0.000244140625f))));
+      dst[(size_t)px * 3 + c] = (uint8_t)(int)fminf(v, 255.0f);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+glass_large_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int h, int w, GlassTeamParams p,
+                   uint8_t* __restrict__ work) {
+  extern __shared__ __align__(16) uint8_t gsm[];
+  uint8_t* lut = gsm;                                        // 256: composed byte map (lw == 0)
+  uint16_t* map = reinterpret_cast<uint16_t*>(gsm + 256);   // h * w
+  const int tid = threadIdx.x, hw = h * w, R = h - 2, Ccols = w - 2;
+  uint8_t* B1 = work + (size_t)blockIdx.x * 2 * hw * 3;
+  uint8_t* B2 = B1 + (size_t)hw * 3;
+  if (p.lw == 0) {
+    for (int i = tid; i < 256; i += 256) {
+      const double t = (double)i / 255.0;
+      const double a = (t * p.w0) * p.w0;
+      const int u = (int)(a * 255.0);
+      const double t2 = (double)u / 255.0;
+      double b = (t2 * p.w0) * p.w0;
+      b = b < 0.0 ? 0.0 : (b > 1.0 ? 1.0 : b);
+      lut[i] = (uint8_t)(int)(b * 255.0);
+    }
+  }
+  const Philox rng(p.seed);
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    const uint8_t* src = in + img * (int64_t)hw * 3;
+    uint8_t* dst = out + img * (int64_t)hw * 3;
+    __syncthreads();
+    if (p.lw > 0) glass_blur3_large(src, B1, h, w, p.k);
+    for (int i = tid; i < hw; i += 256) map[i] = (uint16_t)i;
+    __syncthreads();
+    for (int it = 0; it < p.iters; ++it) {
+      uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+      int rb_key = -1;
+      for (int t = 0; t < 2 * (R - 1) + Ccols; ++t) {
+        for (int r = tid; r < R; r += 256) {
+          const int ci = t - 2 * r;
+          if (ci < 0 || ci >= Ccols) continue;
+          int dx, dy;
+          if (p.deltas) {
+            const int8_t* d = p.deltas + ((((img * p.iters + it) * R + r) * Ccols + ci) << 1);
+            dx = d[0]; dy = d[1];
+          } else {
+            const int key = r | ((ci >> 6) << 16);
+            if (key != rb_key) {
+              rb = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)r + ((uint32_t)(ci >> 6) << 16));
+              rb_key = key;
+            }
+            const int cb = ci & 63;
+            dx = -(int)(((cb < 32 ? rb.x : rb.z) >> (cb & 31)) & 1u);
+            dy = -(int)(((cb < 32 ? rb.y : rb.w) >> (cb & 31)) & 1u);
+          }
+          const int a = (h - 1 - r) * w + (w - 1 - ci), b = a + dy * w + dx;
+          const uint16_t ta = map[a], tb = map[b];
+          map[a] = tb; map[b] = ta;
+        }
+        __syncthreads();
+      }
+    }
+    if (p.lw > 0) {
+      for (int i = tid; i < hw; i += 256) {
+        const uint8_t* q = B1 + (size_t)map[i] * 3;
+        B2[(size_t)i * 3] = q[0]; B2[(size_t)i * 3 + 1] = q[1]; B2[(size_t)i * 3 + 2] = q[2];
+      }
+      __syncthreads();
+      glass_blur3_large(B2, dst, h, w, p.k);
+    } else {
+      for (int i = tid; i < hw; i += 256) {
+        const uint8_t* q = src + (size_t)map[i] * 3;
+        dst[(size_t)i * 3] = lut[q[0]]; dst[(size_t)i * 3 + 1] = lut[q[1]]; dst[(size_t)i * 3 + 2] = lut[q[2]];
+      }
+    }
+  }
+}
+}  // namespace imgtx
+
+static int glass_large_fast(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, const imgtx::GlassTeamParams& f,
+                            cudaStream_t st) {
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out, "null image pointer");
+  const size_t smem = 256 + (size_t)h * w * 2 + 16;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(imgtx::glass_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, (size_t)imgtx::smem_per_sm() / (smem + 1024)));
+  const int64_t grid = std::min<int64_t>(n, (int64_t)imgtx::sm_count() * per_sm);
+  uint8_t* work = nullptr;
+  IMGTX_CUDA_OK(imgtx::workspace_alloc((void**)&work, (size_t)grid * 2 * h * w * 3, st));
+  imgtx::glass_large_kernel<<<(unsigned)grid, 256, smem, st>>>(in, out, n, h, w, f, work);
+  IMGTX_LAUNCH_OK();
+  IMGTX_CUDA_OK(cudaFreeAsync(work, st));
+  return IMGTX_OK;
+}
+
 static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const double* weights_host,
                                  int lw, int iters, const int8_t* deltas_dev, uint64_t seed, int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 2 && w > 2 && c == 3 && n >= 0, "glass_blur takes (n,h>2,w>2,3) images");
@@ -1413,7 +1529,8 @@ static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, i
   for (int i = 0; i <= lw; ++i) p.w[i] = weights_host[i];
   p.lw = lw; p.iters = iters; p.deltas = deltas_dev; p.seed = seed;
   const Shape shp = make_shape(h, w, c, h, w);
-  if ((flags & IMGTX_CC_FAST) && h == 32 && w == 32 && lw <= 2) {
+  const bool cifar = h == 32 && w == 32;
+  if ((flags & IMGTX_CC_FAST) && lw <= 2 && (cifar || (h * w <= 65536 && (size_t)h * w * 2 + 2048 <= (size_t)max_smem_optin()))) {
     GlassTeamParams f;
     memset(&f, 0, sizeof(f));
     f.lw = lw; f.iters = iters; f.deltas = deltas_dev; f.seed = seed; f.w0 = p.w[0]; f.n = n;
@@ -1421,6 +1538,7 @@ static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, i
     f.k.k00 = (float)(p.w[0] * p.w[0] / inside); f.k.k01 = f.k.k10 = (float)(p.w[0] * p.w[1] / inside);
     f.k.k11 = (float)(p.w[1] * p.w[1] / inside);
     if (lw == 0 || (1.0 - inside) * 255.0 < 5e-3) {   // what the 3x3 form drops
+      if (!cifar) return glass_large_fast(in, out, n, h, w, f, (cudaStream_t)stream);
       const int rc = launch_team_op<OpTGlass>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
       if (rc != IMGTX_ERR_UNSUPPORTED) { *metrics_done = true; return rc; }
     }
