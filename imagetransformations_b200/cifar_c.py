@@ -437,15 +437,18 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metri
                                         float(c2), seed, flags, mp, st))
     elif name == "pixelate":
         sw, sh = int(w * p), int(h * p)
-        if sw == w or sh == h or h * w > 96 * 96:     # Pillow skips a pass whose size does not change; big images do not fit
-            # the fused chain's shared-memory planes: the general path (two resample launches, identical results)
+        if sw == w or sh == h:     # Pillow skips a pass whose size does not change: the general path (two resample launches)
             small = B.resample(x, (sw, sh), L.FILTER_BOX)
             B.resample(small, (w, h), L.FILTER_BOX, out=out)
             if mp is not None:
                 L.check(lib.imgtx_image_checksums_u8(op, n, h * w * c, mp, st))
         else:
-            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, flags, mp, st)   # small images: gather form; 1 = not applicable
-            if rc == 1:
+            rc = lib.imgtx_box_pixelate_u8(xp, op, n, h, w, c, sw, sh, flags, mp, st)   # gather forms; 1 = not applicable
+            if rc == 1 and h * w > 96 * 96:     # the fused chain's shared-memory planes do not fit: two resample launches
+                small = B.resample(x, (sw, sh), L.FILTER_BOX)
+                B.resample(small, (w, h), L.FILTER_BOX, out=out)
+                rc = lib.imgtx_image_checksums_u8(op, n, h * w * c, mp, st) if mp is not None else 0
+            elif rc == 1:
                 t = [B._resample_table(a, b, L.FILTER_BOX, dev) for a, b in ((w, sw), (h, sh), (sw, w), (sh, h))]
                 rc = lib.imgtx_resize_chain_u8(xp, op, n, h, w, c, sw, sh, t[0].data_ptr(), t[0].numel(), t[1].data_ptr(),
                                                t[1].numel(), t[2].data_ptr(), t[2].numel(), t[3].data_ptr(), t[3].numel(), st)

@@ -367,6 +367,32 @@ struct OpBoxPixelateMma {
   }
 };
 
+// pixelate on images larger than the table block of BoxPixParams (224 x 224): one thread per output pixel evaluates its two
+// BOX passes from the four source pixels they touch (the up-sampling passes are selections); tables in device memory:
+// xt[x] = {3 * c0, 3 * c1, kh0, kh1} and yt[y] = {r0, r1, kv0, kv1} of the output pixel's column / row.  Integer arithmetic:
+// the same bytes as the chained passes.
+__global__ void __launch_bounds__(256)
+box_pixelate_large_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int h, int w,
+                          const int4* __restrict__ xt, const int4* __restrict__ yt) {
+  const int hw = h * w;
+  for (int64_t img = blockIdx.y; img < n; img += gridDim.y) {
+    const uint8_t* im = in + img * (int64_t)hw * 3;
+    uint8_t* om = out + img * (int64_t)hw * 3;
+    for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < hw; px += gridDim.x * blockDim.x) {
+      const int y = px / w, x = px - y * w;
+      const int4 cx = __ldg(xt + x), ry = __ldg(yt + y);
+      const uint8_t* r0 = im + (int64_t)ry.x * w * 3;
+      const uint8_t* r1 = im + (int64_t)ry.y * w * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const int a0 = min(((1 << 21) + r0[cx.x + c] * cx.z + r0[cx.y + c] * cx.w) >> 22, 255);
+        const int a1 = min(((1 << 21) + r1[cx.x + c] * cx.z + r1[cx.y + c] * cx.w) >> 22, 255);
+        om[(int64_t)px * 3 + c] = (uint8_t)min(((1 << 21) + a0 * ry.z + a1 * ry.w) >> 22, 255);
+      }
+    }
+  }
+}
+
 // Specialised launcher: scratch depends on the parameters (table sizes, needed window).
 static int launch_resample(const uint8_t* in, uint8_t* out, int64_t n, const Shape& s, const ResampleParams& p,
                            cudaStream_t stream) {
@@ -558,14 +584,53 @@ extern "C" int imgtx_resize_chain_u8(const uint8_t* in, uint8_t* out, int64_t n,
   return launch_image_op<OpResizeChain>(in, out, n, shp, p, (cudaStream_t)stream, 0, std::min(target, max_smem_optin() - 2048));
 }
 
-/* CIFAR-10-C pixelate, throughput form: Image.resize((sw, sh), BOX) then Image.resize((w, h), BOX) for images up to 64x64.
+/* CIFAR-10-C pixelate: Image.resize((sw, sh), BOX) then Image.resize((w, h), BOX); gather forms (shared-memory tables up to
+   64x64, device tables above).
    Returns IMGTX_OK when launched, 1 when the BOX tables do not have the (<= 2 taps down, single unit tap up) structure or
    the shape is outside the fast path — the caller then uses imgtx_resize_chain_u8 (same results). */
 static int impl_box_pixelate_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int sw, int sh,
                                      int flags, uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "pixelate takes (n,h,w,3) images");
   IMGTX_CHECK_ARG(sw > 0 && sh > 0 && sw <= w && sh <= h, "the intermediate size must not exceed the image");
-  if (h > kPixMax || w > kPixMax || (w & 3) || sw == w || sh == h) return 1;
+  if (sw == w || sh == h) return 1;
+  if (h > kPixMax || w > kPixMax || (w & 3)) {
+    // large images: per-pixel form with the tables in device memory (same structure test as below)
+    const int kBoxL = IMGTX_FILTER_BOX;
+    std::vector<int32_t> th((size_t)imgtx_resample_table_words(w, sw, kBoxL)), tv((size_t)imgtx_resample_table_words(h, sh, kBoxL)),
+        uh((size_t)imgtx_resample_table_words(sw, w, kBoxL)), uv((size_t)imgtx_resample_table_words(sh, h, kBoxL));
+    if (imgtx_resample_table_host(w, sw, kBoxL, th.data()) || imgtx_resample_table_host(h, sh, kBoxL, tv.data()) ||
+        imgtx_resample_table_host(sw, w, kBoxL, uh.data()) || imgtx_resample_table_host(sh, h, kBoxL, uv.data()))
+      return 1;
+    std::vector<int32_t> host((size_t)(w + h) * 4);
+    auto fill = [&](const std::vector<int32_t>& up, const std::vector<int32_t>& down, int out_size, int mul, int32_t* dst) -> bool {
+      const int ku = up[1], kd = down[1];
+      for (int i = 0; i < out_size; ++i) {
+        const int32_t* ru = up.data() + 2 + (size_t)i * (2 + ku);
+        if (ru[1] != 1 || ru[2] != (1 << 22)) return false;          // up-sampling: one unit tap
+        const int32_t* rd = down.data() + 2 + (size_t)ru[0] * (2 + kd);
+        if (rd[1] < 1 || rd[1] > 2 || rd[2] < 0 || (rd[1] == 2 && rd[3] < 0)) return false;   // down-sampling: <= 2 taps
+        dst[4 * i] = rd[0] * mul;
+        dst[4 * i + 1] = (rd[1] == 2 ? rd[0] + 1 : rd[0]) * mul;
+        dst[4 * i + 2] = rd[2];
+        dst[4 * i + 3] = rd[1] == 2 ? rd[3] : 0;
+      }
+      return true;
+    };
+    if (!fill(uh, th, w, 3, host.data()) || !fill(uv, tv, h, 1, host.data() + (size_t)w * 4)) return 1;
+    if (n == 0) return IMGTX_OK;
+    IMGTX_CHECK_ARG(in && out, "null image pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    int32_t* tab = nullptr;
+    IMGTX_CUDA_OK(workspace_alloc((void**)&tab, host.size() * 4, st));
+    // pageable source: the call returns once the buffer has been copied to the driver's staging memory
+    IMGTX_CUDA_OK(cudaMemcpyAsync(tab, host.data(), host.size() * 4, cudaMemcpyHostToDevice, st));
+    const dim3 grid((unsigned)std::min(64, (h * w + 255) / 256), (unsigned)std::min<int64_t>(n, 4096));
+    box_pixelate_large_kernel<<<grid, 256, 0, st>>>(in, out, n, h, w, reinterpret_cast<const int4*>(tab),
+                                                    reinterpret_cast<const int4*>(tab) + w);
+    IMGTX_LAUNCH_OK();
+    IMGTX_CUDA_OK(cudaFreeAsync(tab, st));
+    return IMGTX_OK;
+  }
   if (n == 0) return IMGTX_OK;
   BoxPixParams p;
   memset(&p, 0, sizeof(p));

@@ -224,9 +224,11 @@ def test_brightness_all_colours(cuda, sev):
     assert np.array_equal(got, want), f"{int((got != want).sum())} bytes differ"
 
 
-@pytest.mark.parametrize("hw,c", [((32, 32), 0.95), ((32, 32), 0.65), ((64, 48), 0.75), ((16, 40), 0.5), ((48, 64), 0.9)])
+@pytest.mark.parametrize("hw,c", [((32, 32), 0.95), ((32, 32), 0.65), ((64, 48), 0.75), ((16, 40), 0.5), ((48, 64), 0.9),
+                                  ((224, 224), 0.65), ((224, 224), 0.95), ((96, 80), 0.75), ((37, 53), 0.85), ((130, 66), 0.6)])
 def test_pixelate_gather_form_shapes(cuda, hw, c):
-    """BOX pixelate fast path (<= 64x64) on non-CIFAR shapes against the Pillow-exact oracle."""
+    """BOX pixelate gather forms (tables in shared memory up to 64x64, in device memory above; odd widths too) on non-CIFAR
+    shapes against the Pillow-exact oracle."""
     from imagetransformations_b200 import _lib as L
     h, w = hw
     x = np.random.default_rng(h * w).integers(0, 256, (37, h, w, 3), dtype=np.uint8)
@@ -252,8 +254,8 @@ def test_fast_path_equals_literal_replay(cuda, name):
 
 
 def test_pixelate_imagenette_shape_and_clean_error(cuda):
-    """224x224 pixelate goes through the general two-launch path (the fused chain's planes do not fit in shared memory);
-    calling the fused chain directly on such a shape must fail cleanly, not fault."""
+    """224x224 pixelate has its own gather form; calling the fused shared-memory chain directly on such a shape must fail
+    cleanly, not fault."""
     from imagetransformations_b200 import _lib as L, batch as B
     C = _C()
     x = np.random.default_rng(3).integers(0, 256, (3, 224, 224, 3), dtype=np.uint8)
