@@ -109,3 +109,36 @@ def test_fast_mode_within_one_lsb_at_large_sizes(cuda, name, hw):
         diff = np.abs(got - want)
         assert diff.max() <= 1, (name, sev, hw, int(diff.max()))
         assert (diff > 0).mean() < 0.02, (name, sev, hw, float((diff > 0).mean()))
+
+
+@pytest.mark.parametrize("name,sev", [("elastic_transform", 2), ("elastic_transform", 4), ("glass_blur", 4), ("snow", 3),
+                                      ("motion_blur", 3), ("frost", 3)])
+def test_imagenette_shape_on_chip_law(cuda, name, sev):
+    """On-chip draws at 224 x 224 against the oracle fed numpy draws, same input image repeated: the per-pixel means of the two
+    ensembles agree (Welch z < 6 on every 8 x 8 block mean) and so do the per-image mean and spread."""
+    C = _C()
+    if name == "frost":
+        pytest.skip("the oracle draws uniform crops; the on-chip mode crops a stand-in texture bank (documented)")
+    n = 40
+    base = _imgs(31, 1, 224, 224)[0]
+    base[100:180, 40:200] = (np.add.outer(np.arange(80), np.arange(160)) % 256)[:, :, None].astype(np.uint8)
+    x = np.repeat(base[None], n, 0)
+    d = CC.draw(name, sev, x, np.random.RandomState(77))
+    ref = CC.corrupt(name, sev, x, d).astype(np.float64)
+    got = C.corrupt(torch.from_numpy(x).cuda(), name, sev, seed=5).cpu().numpy().astype(np.float64)
+
+    def blocks(a):   # 8 x 8 x 3 block means: near-Gaussian even where a single byte takes two or three values
+        return a.reshape(n, 28, 8, 28, 8, 3).mean(axis=(2, 4, 5)).reshape(n, -1)
+    rb, gb = blocks(ref), blocks(got)
+    se = np.sqrt(rb.var(0, ddof=1) / n + gb.var(0, ddof=1) / n)
+    ok = se > 1e-3
+    # the throughput forms may differ from the exact ones by 1 LSB on a few per cent of the bytes: 0.05 LSB of slack on a mean
+    slack = lambda dlt: np.sign(dlt) * np.maximum(np.abs(dlt) - 0.05, 0.0)   # noqa: E731
+    z = slack(rb.mean(0) - gb.mean(0))[ok] / se[ok]
+    # one draw (angle, jitter) moves a whole image, so the z of different blocks are correlated: bound the extremes only
+    assert np.abs(z).max() < 6 and abs(z.mean()) < 2.0, (name, sev, float(np.abs(z).max()), float(z.mean()))
+    ref, got = ref.reshape(n, -1), got.reshape(n, -1)
+    for stat in (lambda a: a.mean(1), lambda a: a.std(1)):
+        a, b = stat(ref), stat(got)
+        zz = slack(a.mean() - b.mean()) / np.sqrt(a.var(ddof=1) / n + b.var(ddof=1) / n + 1e-12)
+        assert abs(zz) < 6, (name, sev, float(zz))
