@@ -115,6 +115,93 @@ plasma_map_kernel(double* maps, int msz, double decay, uint64_t seed, int64_t im
   plasma_device(maps + (size_t)blockIdx.x * msz * msz, msz, decay, rng, (uint32_t)img, (uint32_t)(img >> 32), red);
 }
 
+// fog with on-chip draws on large images, throughput form: one CTA of 1024 threads per image draws the msz x msz
+// diamond-square map in float32 in a global workspace (power-of-two index arithmetic, four uniforms per Philox call),
+// reduces its range and the image's maximum, and writes q = x * S + plasma * C with S = m / (m + c0), C = 255 * c0 * S
+// (m = max / 255) — the float32 evaluation of the exact form's expression, as OpTFog does for 32 x 32.
+__global__ void __launch_bounds__(1024)
+fog_large_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int h, int w, int lg, float c0,
+                      float decay, uint64_t seed, float* __restrict__ work) {
+  __shared__ float red[3][32];
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
+  const int msz = 1 << lg, MASK = msz - 1;
+  float* map = work + (size_t)blockIdx.x * msz * msz;
+  const Philox rng(seed);
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    __syncthreads();
+    if (tid == 0) map[0] = 0.0f;
+    __syncthreads();
+    float wib = 100.0f;
+    uint32_t draw = 0;
+    for (int ls = lg; ls >= 1; --ls) {
+      const int s = 1 << ls, half = s >> 1, lm = lg - ls, m = 1 << lm, mm = m * m;
+      const float w2 = wib * wib;   // wibble * uniform(-wibble, wibble)
+      // square centres, four per thread and Philox call
+      for (int g4 = tid; 4 * g4 < mm; g4 += nt) {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x70u + draw, (uint32_t)g4);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = 4 * g4 + e;
+          if (i >= mm) break;
+          const int a = i >> lm, b = i & (m - 1);
+          const int y0 = a << ls, x0 = b << ls, y1 = (y0 + s) & MASK, x1 = (x0 + s) & MASK;
+          const float acc = map[y0 * msz + x0] + map[y1 * msz + x0] + map[y0 * msz + x1] + map[y1 * msz + x1];
+          const float u = (float)(rr[e] >> 8) * (2.0f / 16777216.0f) - 1.0f + (1.0f / 16777216.0f);
+          map[(y0 + half) * msz + x0 + half] = acc * 0.25f + w2 * u;
+        }
+      }
+      __syncthreads();
+      // edge midpoints: family 0 at (a s, b s + half), family 1 at (a s + half, b s); both read corners and centres only
+      for (int g4 = tid; 4 * g4 < 2 * mm; g4 += nt) {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x71u + draw, (uint32_t)g4);
+        const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = 4 * g4 + e;
+          if (i >= 2 * mm) break;
+          const int fam = i >= mm, k = i - fam * mm, a = k >> lm, b = k & (m - 1);
+          const int y = (a << ls) + (fam ? half : 0), x = (b << ls) + (fam ? 0 : half);
+          const float acc = map[((y - half) & MASK) * msz + x] + map[((y + half) & MASK) * msz + x] +
+                            map[y * msz + ((x - half) & MASK)] + map[y * msz + ((x + half) & MASK)];
+          const float u = (float)(rr[e] >> 8) * (2.0f / 16777216.0f) - 1.0f + (1.0f / 16777216.0f);
+          map[y * msz + x] = acc * 0.25f + w2 * u;
+        }
+      }
+      __syncthreads();
+      draw += 2;
+      wib /= decay;
+    }
+    // range of the whole map (the canonical generator normalises before cropping) and the image's maximum
+    float mn = 3.4e38f, mx = -3.4e38f;
+    for (int i = tid; i < msz * msz; i += nt) { const float v = map[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
+    const uint8_t* im = in + img * (int64_t)h * w * 3;
+    unsigned bm = 0;
+    for (int i = tid; i < h * w * 3; i += nt) bm = max(bm, (unsigned)im[i]);
+    for (int o = 16; o > 0; o >>= 1) {
+      mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      bm = max(bm, __shfl_xor_sync(0xffffffffu, bm, o));
+    }
+    if (lane == 0) { red[0][warp] = mn; red[1][warp] = mx; red[2][warp] = (float)bm; }
+    __syncthreads();
+    mn = red[0][0]; mx = red[1][0];
+    float bmf = red[2][0];
+    for (int k = 1; k < (nt >> 5); ++k) { mn = fminf(mn, red[0][k]); mx = fmaxf(mx, red[1][k]); bmf = fmaxf(bmf, red[2][k]); }
+    const float mval = bmf / 255.0f, S = mval / (mval + c0), C = 255.0f * c0 * S / (mx - mn);
+    uint8_t* om = out + img * (int64_t)h * w * 3;
+    for (int px = tid; px < h * w; px += nt) {
+      const int y = px / w, x = px - y * w;
+      const float pl = (map[y * msz + x] - mn) * C;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float q = __fmaf_rn((float)im[px * 3 + c], S, pl);
+        om[px * 3 + c] = (uint8_t)(int)fminf(fmaxf(q, 0.0f), 255.0f);
+      }
+    }
+  }
+}
+
 struct OpCcPoint : NoSpill {
   using Params = CcPointParams;
   static constexpr int kThreads = 256;
@@ -342,6 +429,17 @@ static int impl_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int 
       if (n == 0) return IMGTX_OK;
       IMGTX_CHECK_ARG(in && out, "null image pointer");
       cudaStream_t st = (cudaStream_t)stream;
+      if ((flags & IMGTX_CC_FAST) && p0 > 0 && p0 < 100) {
+        int lg = 2;
+        while ((1 << lg) < msz) ++lg;
+        const int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 2);
+        float* work = nullptr;
+        IMGTX_CUDA_OK(workspace_alloc((void**)&work, (size_t)grid * msz * msz * sizeof(float), st));
+        fog_large_fast_kernel<<<(unsigned)grid, 1024, 0, st>>>(in, out, n, h, w, lg, (float)p0, (float)p1, seed, work);
+        IMGTX_LAUNCH_OK();
+        IMGTX_CUDA_OK(cudaFreeAsync(work, st));
+        return IMGTX_OK;
+      }
       const size_t per = (size_t)msz * msz * sizeof(double);
       const int64_t chunk = std::max<int64_t>(1, std::min<int64_t>(n, (int64_t)((256u << 20) / per)));
       double* maps = nullptr;
