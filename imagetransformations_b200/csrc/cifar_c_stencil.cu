@@ -1625,6 +1625,86 @@ static int impl_cc_motion_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, 
   return launch_image_op<OpCcMotion>(in, out, n, shp, p, (cudaStream_t)stream);
 }
 
+// snow, throughput form for large images: one CTA of 1024 threads per image, the three layers (float32 noise, its zoomed and
+// thresholded 8-bit form, the blurred 8-bit form: 6 bytes per pixel) in a workspace.  Up to the 8-bit layer the arithmetic is
+// the exact form's, operation for operation (a threshold decision that flipped would move a byte by far more than 1 LSB);
+// the line blur and the blend are float32 FFMA on the 0..255 scale.
+namespace imgtx {
+__global__ void __launch_bounds__(1024)
+snow_large_fast_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int h, int w, SnowParams p,
+                       uint8_t* __restrict__ work) {
+  __shared__ int off[kMaxLine * 2];
+  const int tid = threadIdx.x, nt = blockDim.x, hw = h * w;
+  uint8_t* base = work + (size_t)blockIdx.x * align_up((size_t)hw * 6, 256);
+  float* L0 = reinterpret_cast<float*>(base);
+  uint8_t* L1 = base + (size_t)hw * 4;
+  uint8_t* L2 = L1 + hw;
+  const Philox rng(p.m.seed);
+  const int width = p.m.n_eff;
+  for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
+    __syncthreads();
+    if (p.layer) {
+      for (int i = tid; i < hw; i += nt) L0[i] = (float)p.layer[img * hw + i];
+    } else {
+      const float loc = (float)p.loc, sc = (float)p.scale;
+      for (int i = tid; 2 * i < hw; i += nt) {
+        const uint64_t e = (uint64_t)img * (uint64_t)((hw + 1) / 2) + (uint64_t)i;
+        const uint4 r = rng((uint32_t)e, (uint32_t)(e >> 32), 0x61u, 0u);
+        float z0, z1;
+        box_muller_fast(r.x, r.y, z0, z1);
+        L0[2 * i] = __fmaf_rn(sc, z0, loc);
+        if (2 * i + 1 < hw) L0[2 * i + 1] = __fmaf_rn(sc, z1, loc);
+      }
+    }
+    if (tid < 32) {
+      if (p.m.offsets) {
+        for (int k = tid; k < p.m.width * 2; k += 32) off[k] = p.m.offsets[img * p.m.width * 2 + k];
+      } else {
+        const uint4 r = rng((uint32_t)img, (uint32_t)(img >> 32), 0x62u, 0u);
+        motion_offsets(p.m.lo + (p.m.hi - p.m.lo) * (double)u01(r.x), p.m.width, off);
+      }
+    }
+    __syncthreads();
+    for (int i = tid; i < hw; i += nt) {   // centre zoom (order 1), threshold, 8 bits: the exact form's float32 operations
+      const int y = i / w, x = i - y * w;
+      const int zy0 = p.zidx[y], zy1 = p.zidx[h + y], zx0 = p.zidx[2 * h + x], zx1 = p.zidx[2 * h + w + x];
+      const float ty = p.zt[y], tx = p.zt[h + x], uy = __fsub_rn(1.0f, ty), ux = __fsub_rn(1.0f, tx);
+      float acc = __fmul_rn(__fmul_rn(L0[zy0 * w + zx0], uy), ux);
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[zy0 * w + zx1], uy), tx));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[zy1 * w + zx0], ty), ux));
+      acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[zy1 * w + zx1], ty), tx));
+      if (acc < p.thresh) acc = 0.0f;
+      L1[i] = q255f(acc);
+    }
+    __syncthreads();
+    for (int i = tid; i < hw; i += nt) {   // line blur of the 8-bit layer
+      const int y = i / w, x = i - y * w;
+      float acc = 0.5f;
+      for (int k = 0; k < width; ++k) {
+        const int xx = min(max(x + off[2 * k], 0), w - 1), yy = min(max(y + off[2 * k + 1], 0), h - 1);
+        acc = __fmaf_rn(__uint_as_float(0x4B000000u | (uint32_t)L1[yy * w + xx]) - 8388608.0f, p.m.k[k], acc);
+      }
+      L2[i] = (uint8_t)(int)fminf(acc, 255.0f);
+    }
+    __syncthreads();
+    const uint8_t* im = in + img * (int64_t)hw * 3;
+    uint8_t* om = out + img * (int64_t)hw * 3;
+    const float c6 = p.c6, d6 = p.one_minus_c6;
+    for (int i = tid; i < hw; i += nt) {   // blend on the 0..255 scale
+      const float r = (float)im[i * 3], g = (float)im[i * 3 + 1], b = (float)im[i * 3 + 2];
+      const float whit = __fmaf_rn(__fmaf_rn(b, 0.114f, __fmaf_rn(g, 0.587f, r * 0.299f)), 1.5f, 127.5f);
+      const float sn = (float)L2[i] + (float)L2[hw - 1 - i] + 0.0009765625f;
+      const float v0 = __fmaf_rn(d6, fmaxf(r, whit), __fmaf_rn(c6, r, sn));
+      const float v1 = __fmaf_rn(d6, fmaxf(g, whit), __fmaf_rn(c6, g, sn));
+      const float v2 = __fmaf_rn(d6, fmaxf(b, whit), __fmaf_rn(c6, b, sn));
+      om[i * 3] = (uint8_t)(int)fminf(fmaxf(v0, 0.0f), 255.0f);
+      om[i * 3 + 1] = (uint8_t)(int)fminf(fmaxf(v1, 0.0f), 255.0f);
+      om[i * 3 + 2] = (uint8_t)(int)fminf(fmaxf(v2, 0.0f), 255.0f);
+    }
+  }
+}
+}  // namespace imgtx
+
 static int impl_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, float thresh, float c6,
                                 float one_minus_c6, const int32_t* zoom_idx_host /* y0,y1 (h each), x0,x1 (w each) */,
                                 const float* zoom_t_host /* ty (h), tx (w) */, int width, const float* k_host,
@@ -1648,7 +1728,17 @@ static int impl_cc_snow_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, in
     IMGTX_CUDA_OK(cudaMemcpyAsync(tab + ib, zoom_t_host, tb, cudaMemcpyHostToDevice, st));
     p.zidx = reinterpret_cast<const int32_t*>(tab);
     p.zt = reinterpret_cast<const float*>(tab + ib);
-    rc = launch_image_op<OpCcSnow>(in, out, n, make_shape(h, w, c, h, w), p, st);
+    if (flags & IMGTX_CC_FAST) {
+      const int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * 2);
+      uint8_t* work = nullptr;
+      IMGTX_CUDA_OK(workspace_alloc((void**)&work, (size_t)grid * align_up((size_t)h * w * 6, 256), st));
+      snow_large_fast_kernel<<<(unsigned)grid, 1024, 0, st>>>(in, out, n, h, w, p, work);
+      IMGTX_LAUNCH_OK();
+      IMGTX_CUDA_OK(cudaFreeAsync(work, st));
+      rc = IMGTX_OK;
+    } else {
+      rc = launch_image_op<OpCcSnow>(in, out, n, make_shape(h, w, c, h, w), p, st);
+    }
     IMGTX_CUDA_OK(cudaFreeAsync(tab, st));
     return rc;
   }
