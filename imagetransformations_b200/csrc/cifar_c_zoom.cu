@@ -219,22 +219,27 @@ struct ZoomLevelsParams {
   const float* xt;       // device (nz, w)
   int nz, h, w;
   float inv;             // 1 / (nz + 1)
+  uint32_t magic;        // 0x4b000000 (2^23 as float bits)
 };
 constexpr int kZoomTile = 32;
+
+// byte K of w as a float: PRMT it into the mantissa of 2^23 (selector immediate, 2^23 in a register), subtract 2^23
+template <int K>
+__device__ __forceinline__ float zbyte(uint32_t w, uint32_t magic) {
+  uint32_t r;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(w), "r"(magic), "n"(0x7440 + K));
+  return __uint_as_float(r) - 8388608.0f;
+}
 constexpr int kZoomMaxLevels = 32;
 
 __global__ void __launch_bounds__(256)
 zoom_levels_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, ZoomLevelsParams p, int win_cap) {
   extern __shared__ __align__(16) uint8_t zsm[];
   // [nz][32] row tables (i0, i1, t) | [nz][32] column tables | source window (rows x cols x 3 bytes)
-  int* ry0 = reinterpret_cast<int*>(zsm);
-  int* ry1 = ry0 + p.nz * kZoomTile;
-  float* rty = reinterpret_cast<float*>(ry1 + p.nz * kZoomTile);
-  int* cx0 = reinterpret_cast<int*>(rty + p.nz * kZoomTile);
-  int* cx1 = cx0 + p.nz * kZoomTile;
-  float* ctx = reinterpret_cast<float*>(cx1 + p.nz * kZoomTile);
+  int4* rowt = reinterpret_cast<int4*>(zsm);          // per (level, row): i0, i1, t -> then window byte offsets of the two rows, t
+  int4* colt = rowt + p.nz * kZoomTile;               // per (level, column): the same for columns
   __shared__ int bbox[4];
-  uint8_t* win = reinterpret_cast<uint8_t*>(ctx + p.nz * kZoomTile);
+  uint8_t* win = reinterpret_cast<uint8_t*>(colt + p.nz * kZoomTile);
   const int tid = threadIdx.x, lane = tid & 31, wy = tid >> 5;
   const int tiles_x = (p.w + kZoomTile - 1) / kZoomTile, tiles_y = (p.h + kZoomTile - 1) / kZoomTile;
   const int64_t total = n * tiles_x * tiles_y;
@@ -250,8 +255,8 @@ zoom_levels_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, in
       const int y = min(ty0 + k, p.h - 1), x = min(tx0 + k, p.w - 1);
       const int a0 = p.yidx[(z * 2) * p.h + y], a1 = p.yidx[(z * 2 + 1) * p.h + y];
       const int b0 = p.xidx[(z * 2) * p.w + x], b1 = p.xidx[(z * 2 + 1) * p.w + x];
-      ry0[e] = a0; ry1[e] = a1; rty[e] = p.yt[z * p.h + y];
-      cx0[e] = b0; cx1[e] = b1; ctx[e] = p.xt[z * p.w + x];
+      rowt[e] = make_int4(a0, a1, __float_as_int(p.yt[z * p.h + y]), 0);
+      colt[e] = make_int4(b0, b1, __float_as_int(p.xt[z * p.w + x]), 0);
       ymin = min(ymin, min(a0, a1)); ymax = max(ymax, max(a0, a1));
       xmin = min(xmin, min(b0, b1)); xmax = max(xmax, max(b0, b1));
     }
@@ -261,30 +266,73 @@ zoom_levels_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, in
     __syncthreads();
     const int wy0 = bbox[0], wx0 = bbox[1], wh = bbox[2] - bbox[0] + 1, ww = bbox[3] - bbox[1] + 1;
     const uint8_t* im = in + img * (int64_t)p.h * p.w * 3;
-    const bool in_smem = wh * ww * 3 <= win_cap;   // always, for the zoom ranges of the severity table; else read through L1
+    const bool in_smem = wh * ww * 4 <= win_cap;   // always, for the zoom ranges of the severity table; else read through L1
+    uint32_t* win32 = reinterpret_cast<uint32_t*>(win);
     if (in_smem) {
-      const int rowb = ww * 3;
-      for (int e = tid; e < wh * rowb; e += 256) {
-        const int r = e / rowb, b = e - r * rowb;
-        win[e] = im[((int64_t)(wy0 + r) * p.w + wx0) * 3 + b];
+      // the window as one RGBx word per pixel: a tap is ONE shared-memory load
+      // a warp per window row, lanes along it: 96 contiguous bytes per load instruction, several rows in flight
+#pragma unroll 4
+      for (int r = wy; r < wh; r += 8) {
+        const uint8_t* q = im + ((int64_t)(wy0 + r) * p.w + wx0) * 3;
+        for (int cc = lane; cc < ww; cc += 32)
+          win32[r * ww + cc] = (uint32_t)q[cc * 3] | ((uint32_t)q[cc * 3 + 1] << 8) | ((uint32_t)q[cc * 3 + 2] << 16);
       }
     }
     __syncthreads();
-    const uint8_t* base = in_smem ? win : im;
-    const int pitch = in_smem ? ww * 3 : p.w * 3, oy = in_smem ? wy0 : 0, ox = in_smem ? wx0 : 0;
     const int x = tx0 + lane;
-    if (x < p.w) {
+    if (in_smem) {
+      // tables of the inner loop, one 16-byte record per (level, row) and per (level, column): byte offsets into the window
+      // (row records carry the window origin, so a tap's address is one add) and the interpolation weight
+      for (int e = tid; e < p.nz * kZoomTile; e += 256) {
+        const int4 r = rowt[e], c = colt[e];
+        rowt[e] = make_int4(((r.x - wy0) * ww - wx0) * 4, ((r.y - wy0) * ww - wx0) * 4, r.z, 0);
+        colt[e] = make_int4(c.x * 4, c.y * 4, c.z, 0);
+      }
+      __syncthreads();
+      const uint32_t magic = p.magic;   // 0x4b000000 from the parameters: kept in a register, the selectors stay immediates
+      const char* wb = reinterpret_cast<const char*>(win32);
+      if (x < p.w) {
+        for (int k = wy; k < kZoomTile; k += 8) {
+          const int y = ty0 + k;
+          if (y >= p.h) break;
+          float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+#pragma unroll 2
+          for (int z = 0; z < p.nz; ++z) {
+            const int4 rr = rowt[z * kZoomTile + k], cc = colt[z * kZoomTile + lane];
+            const float ty = __int_as_float(rr.z), tx = __int_as_float(cc.z);
+            const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
+            const uint32_t p00 = *reinterpret_cast<const uint32_t*>(wb + (rr.x + cc.x));
+            const uint32_t p01 = *reinterpret_cast<const uint32_t*>(wb + (rr.x + cc.y));
+            const uint32_t p10 = *reinterpret_cast<const uint32_t*>(wb + (rr.y + cc.x));
+            const uint32_t p11 = *reinterpret_cast<const uint32_t*>(wb + (rr.y + cc.y));
+            a0 = __fmaf_rn(zbyte<0>(p11, magic), w11, __fmaf_rn(zbyte<0>(p10, magic), w10, __fmaf_rn(zbyte<0>(p01, magic), w01, __fmaf_rn(zbyte<0>(p00, magic), w00, a0))));
+            a1 = __fmaf_rn(zbyte<1>(p11, magic), w11, __fmaf_rn(zbyte<1>(p10, magic), w10, __fmaf_rn(zbyte<1>(p01, magic), w01, __fmaf_rn(zbyte<1>(p00, magic), w00, a1))));
+            a2 = __fmaf_rn(zbyte<2>(p11, magic), w11, __fmaf_rn(zbyte<2>(p10, magic), w10, __fmaf_rn(zbyte<2>(p01, magic), w01, __fmaf_rn(zbyte<2>(p00, magic), w00, a2))));
+          }
+          const uint32_t self = win32[(y - wy0) * ww + (x - wx0)];
+          uint8_t* o = out + (img * (int64_t)p.h * p.w + (int64_t)y * p.w + x) * 3;
+          // 2^-10: a sum that is an integer in real arithmetic floors to itself
+          o[0] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a0 + zbyte<0>(self, magic), p.inv, 0.0009765625f), 0.0f), 255.0f));
+          o[1] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a1 + zbyte<1>(self, magic), p.inv, 0.0009765625f), 0.0f), 255.0f));
+          o[2] = (uint8_t)floor_bits(fminf(fmaxf(__fmaf_rn(a2 + zbyte<2>(self, magic), p.inv, 0.0009765625f), 0.0f), 255.0f));
+        }
+      }
+    }
+    const uint8_t* base = im;
+    const int pitch = p.w * 3, oy = 0, ox = 0;
+    if (x < p.w && !in_smem) {
       for (int k = wy; k < kZoomTile; k += 8) {
         const int y = ty0 + k;
         if (y >= p.h) break;
         float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
         for (int z = 0; z < p.nz; ++z) {
           const int e = z * kZoomTile;
-          const float ty = rty[e + k], tx = ctx[e + lane];
+          const int4 rr = rowt[e + k], cr = colt[e + lane];
+          const float ty = __int_as_float(rr.z), tx = __int_as_float(cr.z);
           const float w11 = ty * tx, w10 = ty - w11, w01 = tx - w11, w00 = 1.0f - ty - w01;
-          const uint8_t* r0 = base + (ry0[e + k] - oy) * pitch;
-          const uint8_t* r1 = base + (ry1[e + k] - oy) * pitch;
-          const int c0 = (cx0[e + lane] - ox) * 3, c1 = (cx1[e + lane] - ox) * 3;
+          const uint8_t* r0 = base + (rr.x - oy) * pitch;
+          const uint8_t* r1 = base + (rr.y - oy) * pitch;
+          const int c0 = (cr.x - ox) * 3, c1 = (cr.y - ox) * 3;
           // byte -> float without the conversion pipe: the byte planted in the mantissa of 2^23 (exact)
           auto bf = [](uint8_t b) { return __uint_as_float(0x4B000000u | (uint32_t)b) - 8388608.0f; };
           a0 = __fmaf_rn(bf(r1[c1]), w11, __fmaf_rn(bf(r1[c0]), w10, __fmaf_rn(bf(r0[c1]), w01, __fmaf_rn(bf(r0[c0]), w00, a0))));
@@ -310,8 +358,12 @@ int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz
   IMGTX_CHECK_ARG(in && out, "null image pointer");
   ZoomLevelsParams p;
   p.yidx = yidx; p.yt = yt; p.xidx = xidx; p.xt = xt; p.nz = nz; p.h = h; p.w = w; p.inv = (float)(1.0 / (nz + 1));
-  const size_t tab = (size_t)nz * kZoomTile * 6 * 4;
-  const int win_cap = 96 * 96 * 3;
+  p.magic = 0x4b000000u;
+  const size_t tab = (size_t)nz * kZoomTile * 32;
+  // window side: the tile plus the drift of its source towards the centre over the levels (zoom <= 1.34 in the severity
+  // table); a table with larger factors falls back to reading the source through L1
+  const int side = std::min(96, kZoomTile + (int)(std::max(h, w) * 0.13f) + 6);
+  const int win_cap = side * side * 4;
   const size_t smem = tab + win_cap + 16;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(zoom_levels_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t tiles = n * ((w + kZoomTile - 1) / kZoomTile) * ((h + kZoomTile - 1) / kZoomTile);
