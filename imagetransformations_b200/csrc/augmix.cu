@@ -92,6 +92,7 @@ __device__ void build_composed(const AugOp* ops, const uint8_t* stage_lut, int u
 
 // Trace four horizontally adjacent output pixels back through the chain's geometric records [s0, ng) (stored in trace-back
 // order).  A pixel whose source leaves the image at some stage stops there: ok = false, fk = that stage's index.
+template <bool kNeedFk>
 __device__ __forceinline__ void trace4(const int32_t* g, int s0, int ng, int w, int h, int (&xs)[4], int (&ys)[4],
                                        int (&fk)[4], bool (&ok)[4]) {
   for (int s2 = s0; s2 < ng; ++s2) {
@@ -102,7 +103,7 @@ __device__ __forceinline__ void trace4(const int32_t* g, int s0, int ng, int w, 
       const int nx = (A.z + ys[k] * A.y + xs[k] * A.x) >> 16;
       const int ny = (Bv.y + ys[k] * Bv.x + xs[k] * A.w) >> 16;
       const bool in = ok[k] && (unsigned)nx < (unsigned)w && (unsigned)ny < (unsigned)h;
-      if (ok[k] && !in) fk[k] = Bv.z;
+      if (kNeedFk && ok[k] && !in) fk[k] = Bv.z;
       ok[k] = in;
       xs[k] = in ? nx : xs[k];
       ys[k] = in ? ny : ys[k];
@@ -123,7 +124,7 @@ __device__ __forceinline__ bool zero_is_fixed(const AugOp* ops, const uint8_t* s
 
 __global__ void __launch_bounds__(1024)
 augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, int h, int w, int width,
-              int depth, const AugOp* __restrict__ ops_g, const float* __restrict__ wts_g) {
+              int depth, const AugOp* __restrict__ ops_g, const float* __restrict__ wts_g, int use_stash) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int hw = h * w;
   const int nstage = width * depth;
@@ -140,7 +141,8 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
   int32_t* G = reinterpret_cast<int32_t*>(FF + (size_t)nstage * 4);    // per chain: [ng,-,-,-] + depth * [a0..a5,k,-]
   const int gstride = 4 + depth * 8;
   AugOp* ops = reinterpret_cast<AugOp*>(G + (size_t)width * gstride);  // nstage
-  float* wts = reinterpret_cast<float*>(ops + nstage);                 // width + 2
+  float* wts = reinterpret_cast<float*>(ops + nstage);                 // width + 2 (+pad)
+  float* stash = use_stash ? wts + ((width + 2 + 3) & ~3) : nullptr;   // blockDim * 12 floats (when they fit)
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, warp = tid >> 5;
   const bool vec = (hw & 3) == 0 && (w & 3) == 0;
   const int zoff = hw * 3;                                             // a pixel of zero bytes behind the image
@@ -149,17 +151,31 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
   for (int i = tid; i < 256; i += nt) T[i] = __fdiv_rn((float)i, 255.0f);
   const uint64_t keep = l2_policy_keep(), drop = l2_policy_drop();
 
+  // the records and weights of the NEXT image ride in one register per thread (fetched while this image is gathered), so
+  // an image does not start with a dependent global load that stalls the whole CTA
+  const int nrec = nstage * 8, nhead = nrec + width + 2;
+  const bool pre = nhead <= nt;
+  auto fetch_head = [&](int64_t im) -> int32_t {
+    if (im >= n || tid >= nhead) return 0;
+    return tid < nrec ? reinterpret_cast<const int32_t*>(ops_g + im * nstage)[tid]
+                      : __float_as_int(wts_g[im * (width + 2) + (tid - nrec)]);
+  };
+  int32_t head = pre ? fetch_head(blockIdx.x) : 0;
+
   for (int64_t img = blockIdx.x; img < n; img += gridDim.x) {
     const float* xi = x + img * 3 * (int64_t)hw;
     float* oi = out + img * 3 * (int64_t)hw;
     __syncthreads();  // previous image fully written before its tables are overwritten
-    {
+    if (pre) {
+      if (tid < nrec) reinterpret_cast<int32_t*>(ops)[tid] = head;
+      else if (tid < nhead) wts[tid - nrec] = __int_as_float(head);
+    } else {
       const int32_t* src = reinterpret_cast<const int32_t*>(ops_g + img * nstage);
       int32_t* dst = reinterpret_cast<int32_t*>(ops);
-      for (int i = tid; i < nstage * 8; i += nt) dst[i] = src[i];
+      for (int i = tid; i < nrec; i += nt) dst[i] = src[i];
       for (int i = tid; i < width + 2; i += nt) wts[i] = wts_g[img * (width + 2) + i];
-      for (int i = tid; i < 768; i += nt) base[i] = 0u;
     }
+    for (int i = tid; i < 768; i += nt) base[i] = 0u;
     __syncthreads();
     // the chain's geometric stages compacted in trace-back order; does any equalize see the quantised image itself?
     if (tid < width) {
@@ -253,7 +269,7 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
               bool ok[4];
 #pragma unroll
               for (int k = 0; k < 4; ++k) { xs[k] = x0 + k; ys[k] = y; fk[k] = 0; ok[k] = true; }
-              trace4(g, s0, ng, w, h, xs, ys, fk, ok);
+              trace4<false>(g, s0, ng, w, h, xs, ys, fk, ok);
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint8_t* sp = q + (ok[k] ? (ys[k] * w + xs[k]) * 3 : zoff);
@@ -293,6 +309,7 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
 
     // ---- phase C: mix and write ----
     const float m = wts[width], one_m = wts[width + 1];
+    if (pre) head = fetch_head(img + gridDim.x);
     uint32_t zfix = 0;   // chains whose fill is the zero pixel
     for (int ci = 0; ci < width && ci < 32; ++ci)
       if (zero_is_fixed(ops + ci * depth, stage_lut + (size_t)ci * depth * 768, depth)) zfix |= 1u << ci;
@@ -302,11 +319,13 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
       for (int p4 = tid; p4 < (hw >> 2); p4 += nt, y += dy, xq += dx) {
         if (xq >= wq) { xq -= wq; ++y; }
         const int p0 = p4 * 4, x0 = xq * 4;
-        if (p4 + nt < (hw >> 2)) {
-          // the blend's second read of x, one iteration ahead, pulled towards L2 while the chains are traced
+        if (stash) {
+          // the blend's second read of x starts now and lands in this thread's 48-byte slot while the chains are traced
 #pragma unroll
           for (int c = 0; c < 3; ++c)
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(xi + (int64_t)c * hw + p0 + nt * 4));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stash + (tid * 3 + c) * 4)),
+                         "l"(xi + (int64_t)c * hw + p0) : "memory");
+          asm volatile("cp.async.commit_group;" ::: "memory");
         }
         float mix[3][4];
 #pragma unroll
@@ -321,8 +340,8 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
           bool ok[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) { xs[k] = x0 + k; ys[k] = y; fk[k] = 0; ok[k] = true; }
-          trace4(g, 0, g[0], w, h, xs, ys, fk, ok);
           if (zfix & (1u << ci)) {
+            trace4<false>(g, 0, g[0], w, h, xs, ys, fk, ok);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               const uint8_t* sp = q + (ok[k] ? (ys[k] * w + xs[k]) * 3 : zoff);
@@ -330,6 +349,7 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
               for (int c = 0; c < 3; ++c) mix[c][k] = __fadd_rn(mix[c][k], ft[c * 256 + sp[c]]);
             }
           } else {
+            trace4<true>(g, 0, g[0], w, h, xs, ys, fk, ok);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               if (ok[k]) {
@@ -344,9 +364,11 @@ augmix_kernel(const float* __restrict__ x, float* __restrict__ out, int64_t n, i
             }
           }
         }
+        if (stash) asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
-          const float4 f = ldg_hint_f4(xi + (int64_t)c * hw + p0, drop);
+          const float4 f = stash ? *reinterpret_cast<const float4*>(stash + (tid * 3 + c) * 4)
+                                 : ldg_hint_f4(xi + (int64_t)c * hw + p0, drop);
           float4 r;
           r.x = __fadd_rn(__fmul_rn(one_m, f.x), __fmul_rn(m, mix[c][0]));
           r.y = __fadd_rn(__fmul_rn(one_m, f.y), __fmul_rn(m, mix[c][1]));
@@ -393,11 +415,15 @@ extern "C" int imgtx_augmix_f32(const float* x, float* out, int64_t n, int h, in
                 ((size_t)nstage * 4 + 15) / 16 * 16 + 3 * 768 * 4 + 256 * 4 + (size_t)width * 768 * 4 + (size_t)nstage * 16 +
                 (size_t)width * (4 + depth * 8) * 4 + (size_t)nstage * 32 + (size_t)(width + 2) * 4 + 16;
   IMGTX_CHECK_ARG(smem <= (size_t)max_smem_optin(), "image (%dx%d) does not fit in shared memory for fused AugMix", h, w);
+  // 48 bytes per thread for the blend's second read of x (cp.async issued before the chains are traced) when they fit
+  const size_t stash_bytes = (size_t)threads * 48 + 16;
+  const int use_stash = (hw % 4 == 0 && w % 4 == 0 && smem + stash_bytes <= (size_t)max_smem_optin()) ? 1 : 0;
+  if (use_stash) smem += stash_bytes;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(augmix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int per_sm = (int)std::max<size_t>(1, std::min<size_t>(2048 / threads, (size_t)max_smem_optin() / (smem + 1024)));
   int64_t grid = std::min<int64_t>(n, (int64_t)sm_count() * per_sm);
   augmix_kernel<<<(unsigned)grid, threads, smem, (cudaStream_t)stream>>>(x, out, n, h, w, width, depth,
-                                                                        reinterpret_cast<const AugOp*>(ops_dev), weights_dev);
+                                                                        reinterpret_cast<const AugOp*>(ops_dev), weights_dev, use_stash);
   IMGTX_LAUNCH_OK();
   return IMGTX_OK;
 }
