@@ -63,6 +63,7 @@ _PROTOS = {
     "imgtx_resize_chain_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _int, _vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _vp],
     "imgtx_cv_gaussian_kernel_host": [_int, C.c_double, _vp],
     "imgtx_cv_gaussian_blur_u8": [_vp, _vp, _i64, _int, _int, _int, _int, C.c_double, _int, _vp],
+    "imgtx_cc_op32_mma_u8": [_vp, _vp, _i64, _vp, _i64, _int, _vp, _vp],
     "imgtx_cc_zoom_levels_u8": [_vp, _vp, _i64, _int, _int, _int, _int, _vp, _vp, _vp, _vp, _vp, _vp],
     "imgtx_pool_chain_f32": [_vp, _i64, _vp, _i64, _int, _int, _vp, _int, _vp, _vp, _vp, _vp, _vp, C.c_uint64, _vp],
     "imgtx_noalloc_scratch_bytes": [],

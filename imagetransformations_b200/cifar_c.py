@@ -211,7 +211,87 @@ def zoom_operator(h: int, w: int, severity: int, device):
     op = (torch.from_numpy(indptr).to(device), torch.from_numpy(nzc.astype(np.int32)).to(device),
           torch.from_numpy(wf32).to(device), int(np.diff(indptr).max()))
     _zoom_cache[key] = op
+    _zoom_host_csr[key] = (indptr, nzc.astype(np.int64), acc)
     return op
+
+
+_zoom_host_csr = {}
+_zoom_mma_cache = {}
+OP32_MAGIC = 0x4F503332   # 'OP32'
+
+
+def op32_mma_tables(indptr, cols, weights):
+    """A sparse row-stochastic operator with non-negative weights on 32x32 images (zoom_blur's merged operator) compiled for
+    imgtx_cc_op32_mma_u8 (csrc/cifar_c_zoom.cu): 64 tiles of 4x4 output pixels, each contracting over the aligned 4-pixel
+    groups ("quads") of the source rows its taps touch, 8 quads = one m16n8k32 integer-MMA step, at most 3 steps per tile.
+    Weights are Q16 (rounded to nearest, the largest of a row absorbs the rounding so a row sums to 2^16 and flat regions
+    stay exact), split into a low and a high byte limb.  Returns (int32 table words, total steps) or None when a tile needs
+    more than 3 steps."""
+    indptr, cols, weights = np.asarray(indptr, np.int64), np.asarray(cols, np.int64), np.asarray(weights, np.float64)
+    if len(indptr) != 1025 or (weights < 0).any():
+        return None
+    meta = np.zeros((64, 4), np.int32)
+    bias = np.zeros((64, 8), np.uint32)
+    qtab = np.zeros((64, 3, 4, 2), np.int32)
+    hi = np.zeros((64, 3, 32, 4), np.uint32)
+    lo_steps = []
+    lane = np.arange(32)
+    gid, tig = lane >> 2, lane & 3
+    for t in range(64):
+        ty, tx = divmod(t, 8)
+        m = np.arange(16)
+        pix = (ty * 4 + ((m % 8) >> 1)) * 32 + tx * 4 + ((m % 8) & 1) * 2 + (m >> 3)   # rows m and m + 8 are neighbours
+        quads = np.unique(np.concatenate([cols[indptr[q]:indptr[q + 1]] for q in pix]) // 4)
+        ns = (len(quads) + 7) // 8
+        if ns > 3 or ns < 1:
+            return None
+        qpos = np.full(256, -1, np.int64)
+        qpos[quads] = np.arange(len(quads))
+        qpad = np.concatenate([quads, np.zeros(ns * 8 - len(quads), np.int64)])
+        W = np.zeros((16, 96), np.int64)
+        rb = np.full(16, 32, np.int64)       # rounding bias per row: 2^-11 LSB, so an exactly integral sum floors to itself
+        for r, q in enumerate(pix):
+            cs, ws = cols[indptr[q]:indptr[q + 1]], weights[indptr[q]:indptr[q + 1]]
+            if len(cs) == 0:
+                continue
+            wq = np.rint(ws * 65536.0).astype(np.int64)
+            wq[np.argmax(wq)] += int(round(ws.sum() * 65536.0)) - wq.sum()
+            if wq.max() > 65535:              # a weight of 1.0: 65535 x + 256 still floors to x for every byte x
+                wq = np.minimum(wq, 65535)
+                rb[r] = 256
+            W[r, qpos[cs // 4] * 4 + cs % 4] = wq
+        meta[t, 0], meta[t, 1] = ns, len(lo_steps)
+        bias[t] = (rb[:8] | (rb[8:] << 16)).astype(np.uint32)
+        for sidx in range(ns):
+            qtab[t, sidx, :, 0] = qpad[sidx * 8 + np.arange(4)] * 4
+            qtab[t, sidx, :, 1] = qpad[sidx * 8 + 4 + np.arange(4)] * 4
+            fr = np.zeros((2, 32, 4), np.uint32)
+            for reg in range(4):
+                row = gid + (reg & 1) * 8
+                kb = sidx * 32 + (reg >> 1) * 16 + tig * 4
+                for i in range(4):
+                    w_ = W[row, kb + i]
+                    fr[0, :, reg] |= ((w_ & 255) << (8 * i)).astype(np.uint32)
+                    fr[1, :, reg] |= ((w_ >> 8) << (8 * i)).astype(np.uint32)
+            lo_steps.append(fr[0])
+            hi[t, sidx] = fr[1]
+    lo = np.stack(lo_steps)
+    head = np.zeros(16, np.int32)
+    parts = [head, meta.reshape(-1), bias.view(np.int32).reshape(-1), qtab.reshape(-1), lo.view(np.int32).reshape(-1),
+             hi.view(np.int32).reshape(-1)]
+    offs = np.cumsum([0] + [len(a) for a in parts])
+    head[:8] = [OP32_MAGIC, len(lo_steps), offs[1], offs[2], offs[3], offs[4], offs[5], offs[6]]
+    return np.concatenate(parts).astype(np.int32), len(lo_steps)
+
+
+def zoom_mma_tables(severity: int, device):
+    """zoom_blur's merged operator at 32x32 compiled for the integer tensor cores, on `device` (None if it does not fit)."""
+    key = (32, 32, severity, str(device))
+    if key not in _zoom_mma_cache:
+        zoom_operator(32, 32, severity, device)
+        r = op32_mma_tables(*_zoom_host_csr[key])
+        _zoom_mma_cache[key] = None if r is None else (torch.from_numpy(r[0]).to(device), r[1])
+    return _zoom_mma_cache[key]
 
 
 _JPEG_LUMA = np.array([16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55, 14, 13, 16, 24, 40, 57, 69, 56,
@@ -402,6 +482,9 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metri
         yi, yt, xi, xt, nz = zoom_level_tables(h, w, severity, dev)
         L.check(lib.imgtx_cc_zoom_levels_u8(xp, op, n, h, w, c, nz, yi.data_ptr(), yt.data_ptr(), xi.data_ptr(), xt.data_ptr(),
                                             mp, st))
+    elif name == "zoom_blur" and (flags & L.CC_FAST) and h == 32 and w == 32 and zoom_mma_tables(severity, dev) is not None:
+        tab, steps = zoom_mma_tables(severity, dev)
+        L.check(lib.imgtx_cc_op32_mma_u8(xp, op, n, tab.data_ptr(), tab.numel(), steps, mp, st))
     elif name == "zoom_blur":
         ip, idx, wt, max_row = zoom_operator(h, w, severity, dev)
         L.check(lib.imgtx_cc_csr_ell_u8(xp, op, n, h, w, c, ip.data_ptr(), idx.data_ptr(), wt.data_ptr(), idx.numel(),

@@ -13,7 +13,7 @@
 //     TMA stores; the canvas of image i+1 is built while image i is evaluated, so there is one CTA barrier per image.
 // Arithmetic: sum_k w_k * x_k in float32 FFMA order instead of the oracle's ordered float32 sum of rounded products on the
 // 0..1 scale: |difference| < 1e-4 LSB, i.e. <= 1 LSB after floor (tests/test_gpu_fast_mode.py).
-#include "team_pipeline.cuh"
+#include "sep_mma.cuh"
 #include <cuda_fp16.h>
 #include <type_traits>
 
@@ -373,9 +373,234 @@ int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz
   return IMGTX_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The merged zoom_blur operator of 32 x 32 images on the integer tensor cores (imgtx_cc_op32_mma_u8).
+//
+// zoom_blur is ONE linear operator per severity with non-negative weights that sum to 1 per output pixel, the same for every
+// image: out[p][c] = floor(sum_k W[p][k] x[k][c]).  zoom_fast_kernel above spends 7 issue slots per tap and pixel on it.
+// As a matrix product the images are the columns: C[16 output pixels][8 images] += A[16][32 source pixels] B[32][8 images]
+// is one `mma.sync.m16n8k32.u8.u8.s32` (IMMA.16832, 2.1 clk per SM), and W is sparse but local: the taps of a 4 x 4 tile of
+// output pixels touch 14-24 aligned 4-pixel groups ("quads") of the source rows, i.e. 2-3 MMA steps of 8 quads each
+// (113-144 steps per image for the five severities instead of 1024 x 5.5-12.3 taps).
+//   * The host compiles W (imagetransformations_b200/cifar_c.py:op32_mma_tables): per tile its quad list and the A fragments
+//     of the Q16 weights, low and high byte limb; per row a rounding bias.  Q16 rounded to nearest with the row sum kept at
+//     2^16: flat regions are exact, the result differs from the real-valued sum by < 0.01 LSB before the floor.
+//   * A CTA (16 warps) works on a GROUP of 8 consecutive images (24 576 contiguous bytes: one bulk TMA load into a ring slot,
+//     one bulk store from the same slot).  The group is de-interleaved once into byte planes (8 images x 3 channels, image
+//     pitch 3088 B so the eight images of a B-fragment load fall into different banks); a B fragment is then two 32-bit
+//     shared-memory loads at (image = lane / 4, quad = table[lane % 4]).
+//   * Warp w owns tiles 4w .. 4w+3 for the whole launch: the high-limb A fragments stay in 48 REGISTERS, the low-limb ones in
+//     shared memory (56-72 KB).  out = (((bias + sum lo x) >> 8) + sum hi x) >> 8 is exactly (bias + sum w x) >> 16.
+//   * Accumulator rows m and m + 8 are horizontal neighbours, so a lane packs 6 contiguous output bytes per image.
+constexpr int kOpGroup = 8;
+constexpr int kOpImg = 3072;
+constexpr int kOpGroupBytes = kOpGroup * kOpImg;
+constexpr int kOpPlanePitch = kOpImg + 16;
+constexpr int kOpThreads = 512;
+constexpr int kOpFixed = 384 + 6144 + 2048 + 1024;   // barriers + metric partials | quad table | row biases | tile meta
+
+struct Op32Tables {
+  const int32_t* meta;    // [64][4]: steps, first low-limb fragment
+  const uint32_t* bias;   // [64][8]: bias of row gid | bias of row gid + 8 << 16
+  const int2* qtab;       // [64][3][4]: plane byte offsets of quad slots tig and tig + 4
+  const uint4* lo;        // [total_steps][32]
+  const uint4* hi;        // [64][3][32]
+  int total_steps;
+};
+
+__global__ void __launch_bounds__(kOpThreads, 1)
+op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, Op32Tables tb, int ring,
+                uint2* __restrict__ metrics) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint2* msum = reinterpret_cast<uint2*>(smem + 128);
+  int2* qt = reinterpret_cast<int2*>(smem + 384);
+  uint32_t* biasw = reinterpret_cast<uint32_t*>(smem + 384 + 6144);
+  int32_t* meta = reinterpret_cast<int32_t*>(smem + 384 + 6144 + 2048);
+  uint4* alo = reinterpret_cast<uint4*>(smem + kOpFixed);
+  uint8_t* planar = smem + kOpFixed + (size_t)tb.total_steps * 512;
+  uint8_t* slots = planar + align_up((size_t)kOpGroup * kOpPlanePitch, 128);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+
+  if (tid == 0) {
+    for (int i = 0; i < ring; ++i) mbar_init(&full[i], 1);
+    fence_mbar_init();
+  }
+  for (int i = tid; i < 64 * 3 * 4; i += kOpThreads) qt[i] = tb.qtab[i];
+  for (int i = tid; i < 64 * 8; i += kOpThreads) biasw[i] = tb.bias[i];
+  for (int i = tid; i < 64 * 4; i += kOpThreads) meta[i] = tb.meta[i];
+  for (int i = tid; i < tb.total_steps * 32; i += kOpThreads) alo[i] = tb.lo[i];
+  uint4 ahi[4][3];
+#pragma unroll
+  for (int tl = 0; tl < 4; ++tl)
+#pragma unroll
+    for (int s2 = 0; s2 < 3; ++s2) ahi[tl][s2] = tb.hi[((warp * 4 + tl) * 3 + s2) * 32 + lane];
+  __syncthreads();
+
+  const int64_t ngroups = (n + kOpGroup - 1) / kOpGroup, stride = gridDim.x, first = blockIdx.x;
+  auto group_bytes = [&](int64_t g) { return (uint32_t)min((int64_t)kOpGroup, n - g * kOpGroup) * (uint32_t)kOpImg; };
+  if (tid == 0) {
+    for (int i = 0; i < ring; ++i) {
+      const int64_t g = first + (int64_t)i * stride;
+      if (g < ngroups) {
+        mbar_expect_tx(&full[i], group_bytes(g));
+        bulk_g2s(slots + (size_t)i * kOpGroupBytes, in + g * kOpGroupBytes, group_bytes(g), &full[i]);
+      }
+    }
+  }
+  // metric of the group of iteration `it` from the per-warp partials (8 lanes of warp 0, one image each)
+  auto flush_metrics = [&](int it, int64_t g) {
+    if (warp == 0 && lane < kOpGroup && g * kOpGroup + lane < n) {
+      const uint2 a = msum[(it & 1) * 16 + 2 * lane], b = msum[(it & 1) * 16 + 2 * lane + 1];
+      metrics[g * kOpGroup + lane] = make_uint2(a.x + b.x, a.y + b.y);
+    }
+  };
+
+  int it = 0;
+  int64_t g = first;
+  for (; g < ngroups; ++it, g += stride) {
+    const int slot = it % ring;
+    uint8_t* sb = slots + (size_t)slot * kOpGroupBytes;
+    mbar_wait(&full[slot], (uint32_t)(it / ring) & 1u);
+    // RGB bytes -> byte planes, one quad (4 pixels, 3 words) per thread-step
+    {
+      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(sb);
+      uint32_t* p32 = reinterpret_cast<uint32_t*>(planar);
+#pragma unroll
+      for (int task = tid; task < kOpGroup * 256; task += kOpThreads) {
+        const int img = task >> 8, q = task & 255;
+        const uint32_t* w = s32 + img * 768 + q * 3;
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+        uint32_t* d = p32 + img * (kOpPlanePitch / 4) + q;
+        d[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);     // bytes 0, 3, 6, 9
+        d[256] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);   // bytes 1, 4, 7, 10
+        d[512] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);   // bytes 2, 5, 8, 11
+      }
+    }
+    __syncthreads();   // planes complete; everybody is done with the previous group's slot and partials
+    if (metrics && it > 0) flush_metrics(it - 1, g - stride);
+
+    const uint8_t* pl = planar + gid * kOpPlanePitch;
+#pragma unroll
+    for (int tl = 0; tl < 4; ++tl) {
+      const int tile = warp * 4 + tl;
+      const int ns = meta[tile * 4], ab = meta[tile * 4 + 1];
+      const uint32_t bw = biasw[tile * 8 + gid];
+      int acc[3][4];
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) {
+        acc[ch][0] = acc[ch][1] = (int)(bw & 0xffffu);
+        acc[ch][2] = acc[ch][3] = (int)(bw >> 16);
+      }
+      uint32_t b[3][3][2];
+#pragma unroll
+      for (int s2 = 0; s2 < 3; ++s2) {
+        if (s2 < ns) {
+          const int2 qo = qt[(tile * 3 + s2) * 4 + tig];
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) {
+            b[s2][ch][0] = *reinterpret_cast<const uint32_t*>(pl + ch * 1024 + qo.x);
+            b[s2][ch][1] = *reinterpret_cast<const uint32_t*>(pl + ch * 1024 + qo.y);
+          }
+          const uint4 a = alo[(ab + s2) * 32 + lane];
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) imma_uu(acc[ch], a, b[s2][ch][0], b[s2][ch][1]);
+        }
+      }
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[ch][i] >>= 8;
+#pragma unroll
+      for (int s2 = 0; s2 < 3; ++s2) {
+        if (s2 < ns) {
+#pragma unroll
+          for (int ch = 0; ch < 3; ++ch) imma_uu(acc[ch], ahi[tl][s2], b[s2][ch][0], b[s2][ch][1]);
+        }
+      }
+      // rows gid and gid + 8 are the pixel pair (x, x + 1): six contiguous bytes per image, images 2 tig and 2 tig + 1
+      const int p = ((tile >> 3) * 4 + (gid >> 1)) * 32 + (tile & 7) * 4 + (gid & 1) * 2;
+      uint8_t* o = sb + (2 * tig) * kOpImg + p * 3;
+#pragma unroll
+      for (int im = 0; im < 2; ++im) {
+        const uint32_t wa = sat_pack4(acc[0][im] >> 8, acc[1][im] >> 8, acc[2][im] >> 8, acc[0][2 + im] >> 8);
+        const uint32_t wb = sat_pack4(acc[1][2 + im] >> 8, acc[2][2 + im] >> 8, 0, 0);
+        uint16_t* o16 = reinterpret_cast<uint16_t*>(o + im * kOpImg);
+        o16[0] = (uint16_t)wa;
+        o16[1] = (uint16_t)(wa >> 16);
+        o16[2] = (uint16_t)wb;
+      }
+    }
+    fence_async_smem();
+    __syncthreads();   // the slot holds the group's output
+    if (metrics) {     // two warps per image
+      const uint32_t* o32 = reinterpret_cast<const uint32_t*>(sb) + (warp >> 1) * 768;
+      uint32_t c0 = 0, c1 = 0;
+#pragma unroll
+      for (int j = 0; j < 12; ++j) {
+        const uint32_t i = (uint32_t)((warp & 1) * 384 + j * 32 + lane);
+        checksum_word(o32[i], i, c0, c1);
+      }
+      c0 = __reduce_add_sync(0xffffffffu, c0);
+      c1 = __reduce_add_sync(0xffffffffu, c1);
+      if (lane == 0) msum[(it & 1) * 16 + warp] = make_uint2(c0, c1);
+    }
+    if (tid == 0) {
+      bulk_s2g(out + g * kOpGroupBytes, sb, group_bytes(g));
+      bulk_commit();
+      if (it >= 1) {
+        bulk_wait_read<1>();   // the store of the previous iteration has finished reading its slot: refill it
+        const int64_t gn = g + (int64_t)(ring - 1) * stride;
+        if (gn < ngroups) {
+          const int ps = (it - 1) % ring;
+          mbar_expect_tx(&full[ps], group_bytes(gn));
+          bulk_g2s(slots + (size_t)ps * kOpGroupBytes, in + gn * kOpGroupBytes, group_bytes(gn), &full[ps]);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (metrics && it > 0) flush_metrics(it - 1, g - stride);
+  if (tid == 0) bulk_wait_all<0>();
+}
+
+int op32_mma(const uint8_t* in, uint8_t* out, int64_t n, const int32_t* tables, int64_t table_words, int total_steps,
+             uint32_t* metrics, cudaStream_t stream) {
+  IMGTX_CHECK_ARG(total_steps >= 64 && total_steps <= 192, "operator tables: %d steps (64..192)", total_steps);
+  const int64_t off_meta = 16, off_bias = off_meta + 256, off_qtab = off_bias + 512, off_lo = off_qtab + 1536,
+                off_hi = off_lo + (int64_t)total_steps * 128, words = off_hi + 64 * 3 * 128;
+  IMGTX_CHECK_ARG(tables != nullptr && table_words == words && aligned16(tables),
+                  "operator tables: %lld words, %lld expected for %d steps", (long long)table_words, (long long)words, total_steps);
+  if (n == 0) return IMGTX_OK;
+  IMGTX_CHECK_ARG(in && out && aligned16(in) && aligned16(out), "image buffers must be 16-byte aligned");
+  Op32Tables tb;
+  tb.meta = tables + off_meta;
+  tb.bias = reinterpret_cast<const uint32_t*>(tables + off_bias);
+  tb.qtab = reinterpret_cast<const int2*>(tables + off_qtab);
+  tb.lo = reinterpret_cast<const uint4*>(tables + off_lo);
+  tb.hi = reinterpret_cast<const uint4*>(tables + off_hi);
+  tb.total_steps = total_steps;
+  const size_t base = kOpFixed + (size_t)total_steps * 512 + align_up((size_t)kOpGroup * kOpPlanePitch, 128);
+  const int ring = (int)std::min<size_t>(6, ((size_t)max_smem_optin() - base) / kOpGroupBytes);
+  IMGTX_CHECK_ARG(ring >= 2, "operator tables too large for shared memory");
+  const size_t smem = base + (size_t)ring * kOpGroupBytes;
+  IMGTX_CUDA_OK(cudaFuncSetAttribute(op32_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t ngroups = (n + kOpGroup - 1) / kOpGroup;
+  const int64_t grid = std::min<int64_t>(ngroups, sm_count());
+  op32_mma_kernel<<<(unsigned)grid, kOpThreads, smem, stream>>>(in, out, n, tb, ring, reinterpret_cast<uint2*>(metrics));
+  IMGTX_LAUNCH_OK();
+  return IMGTX_OK;
+}
+
 }  // namespace imgtx
 
 using namespace imgtx;
+
+extern "C" int imgtx_cc_op32_mma_u8(const uint8_t* in, uint8_t* out, int64_t n, const int32_t* tables_dev, int64_t table_words,
+                                    int total_steps, uint32_t* metrics_dev, imgtx_stream_t stream) {
+  IMGTX_CHECK_ARG(n >= 0, "negative batch size");
+  return op32_mma(in, out, n, tables_dev, table_words, total_steps, metrics_dev, (cudaStream_t)stream);
+}
 
 extern "C" int imgtx_cc_zoom_levels_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int n_levels,
                                        const int32_t* yidx_dev, const float* yt_dev, const int32_t* xidx_dev,

@@ -307,6 +307,14 @@ int imgtx_cc_csr_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, in
 int imgtx_cc_csr_ell_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, const int32_t* indptr_dev,
                         const int32_t* indices_dev, const float* weights_dev, int nnz, int max_row_taps,
                         int flags, uint32_t* metrics_dev, imgtx_stream_t stream);
+/* A sparse linear operator with non-negative weights summing to 1 per output pixel on (n,32,32,3) images — zoom_blur's merged
+   operator (the one imgtx_cc_csr_u8 takes) — evaluated on the integer tensor cores, <= 1 LSB from imgtx_cc_csr_u8.
+   tables_dev: the operator compiled by imagetransformations_b200/cifar_c.py:op32_mma_tables (Q16 weights as byte limbs in
+   mma fragment order, per 4x4 output tile the aligned 4-pixel source groups it contracts over; layout in
+   csrc/cifar_c_zoom.cu), table_words its length in int32, total_steps its number of MMA steps (64..192).  Replaces the
+   per-image scipy zoom + mean of the canonical zoom_blur (the reference loads its output: SURVEY H27). */
+int imgtx_cc_op32_mma_u8(const uint8_t* in, uint8_t* out, int64_t n, const int32_t* tables_dev, int64_t table_words,
+                         int total_steps, uint32_t* metrics_dev, imgtx_stream_t stream);
 /* zoom_blur, throughput form for images larger than 32x32 (<= 1 LSB from the operator form): the sum over the zoom levels
    evaluated level by level from per-axis tables (device): yidx (n_levels, 2, h) = source rows i0, i1 of every output row,
    yt (n_levels, h) = its interpolation weight, xidx / xt likewise for columns (the per-level tables the canonical
