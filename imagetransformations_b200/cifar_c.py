@@ -237,11 +237,26 @@ def op32_mma_tables(indptr, cols, weights):
     lo_steps = []
     lane = np.arange(32)
     gid, tig = lane >> 2, lane & 3
+    m = np.arange(16)
+
+    def tile_pixels(blk):
+        ty, tx = divmod(blk, 8)
+        return (ty * 4 + ((m % 8) >> 1)) * 32 + tx * 4 + ((m % 8) & 1) * 2 + (m >> 3)   # rows m and m + 8 are neighbours
+
+    def tile_quads(blk):
+        return np.unique(np.concatenate([cols[indptr[q]:indptr[q + 1]] for q in tile_pixels(blk)]) // 4)
+    # warp w of the kernel owns table slots 4w .. 4w+3: deal the pixel blocks out by step count so the warps carry equal work
+    need = [(len(tile_quads(blk)) + 7) // 8 for blk in range(64)]
+    order = sorted(range(64), key=lambda blk: -need[blk])
+    slot_of = {}
+    for i, blk in enumerate(order):
+        rnd, k = divmod(i, 16)
+        wv = k if rnd % 2 == 0 else 15 - k
+        slot_of[wv * 4 + rnd] = blk
     for t in range(64):
-        ty, tx = divmod(t, 8)
-        m = np.arange(16)
-        pix = (ty * 4 + ((m % 8) >> 1)) * 32 + tx * 4 + ((m % 8) & 1) * 2 + (m >> 3)   # rows m and m + 8 are neighbours
-        quads = np.unique(np.concatenate([cols[indptr[q]:indptr[q + 1]] for q in pix]) // 4)
+        blk = slot_of[t]
+        pix = tile_pixels(blk)
+        quads = tile_quads(blk)
         ns = (len(quads) + 7) // 8
         if ns > 3 or ns < 1:
             return None
@@ -260,7 +275,7 @@ def op32_mma_tables(indptr, cols, weights):
                 wq = np.minimum(wq, 65535)
                 rb[r] = 256
             W[r, qpos[cs // 4] * 4 + cs % 4] = wq
-        meta[t, 0], meta[t, 1] = ns, len(lo_steps)
+        meta[t, 0], meta[t, 1], meta[t, 2] = ns, len(lo_steps), (blk // 8) * 128 + (blk % 8) * 4
         bias[t] = (rb[:8] | (rb[8:] << 16)).astype(np.uint32)
         for sidx in range(ns):
             qtab[t, sidx, :, 0] = qpad[sidx * 8 + np.arange(4)] * 4

@@ -388,14 +388,15 @@ int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz
 //   * A CTA (16 warps) works on a GROUP of 8 consecutive images (24 576 contiguous bytes: one bulk TMA load into a ring slot,
 //     one bulk store from the same slot).  The group is de-interleaved once into byte planes (8 images x 3 channels, image
 //     pitch 3088 B so the eight images of a B-fragment load fall into different banks); a B fragment is then two 32-bit
-//     shared-memory loads at (image = lane / 4, quad = table[lane % 4]).
+//     shared-memory loads at (image = lane / 4, quad = table[lane % 4]).  The planes are double-buffered: group i+1 is
+//     de-interleaved by the warps as they finish group i, so there is ONE CTA barrier per group.
 //   * Warp w owns tiles 4w .. 4w+3 for the whole launch: the high-limb A fragments stay in 48 REGISTERS, the low-limb ones in
 //     shared memory (56-72 KB).  out = (((bias + sum lo x) >> 8) + sum hi x) >> 8 is exactly (bias + sum w x) >> 16.
 //   * Accumulator rows m and m + 8 are horizontal neighbours, so a lane packs 6 contiguous output bytes per image.
 constexpr int kOpGroup = 8;
 constexpr int kOpImg = 3072;
 constexpr int kOpGroupBytes = kOpGroup * kOpImg;
-constexpr int kOpPlanePitch = kOpImg + 16;
+constexpr int kOpPlanePitch = kOpImg + 16;   // three byte planes per image
 constexpr int kOpThreads = 512;
 constexpr int kOpFixed = 384 + 6144 + 2048 + 1024;   // barriers + metric partials | quad table | row biases | tile meta
 
@@ -419,7 +420,7 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
   int32_t* meta = reinterpret_cast<int32_t*>(smem + 384 + 6144 + 2048);
   uint4* alo = reinterpret_cast<uint4*>(smem + kOpFixed);
   uint8_t* planar = smem + kOpFixed + (size_t)tb.total_steps * 512;
-  uint8_t* slots = planar + align_up((size_t)kOpGroup * kOpPlanePitch, 128);
+  uint8_t* slots = planar + 2 * align_up((size_t)kOpGroup * kOpPlanePitch, 128);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
 
   if (tid == 0) {
@@ -456,31 +457,37 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
     }
   };
 
-  int it = 0;
-  int64_t g = first;
-  for (; g < ngroups; ++it, g += stride) {
-    const int slot = it % ring;
-    uint8_t* sb = slots + (size_t)slot * kOpGroupBytes;
-    mbar_wait(&full[slot], (uint32_t)(it / ring) & 1u);
-    // RGB bytes -> byte planes, one quad (4 pixels, 3 words) per thread-step
-    {
-      const uint32_t* s32 = reinterpret_cast<const uint32_t*>(sb);
-      uint32_t* p32 = reinterpret_cast<uint32_t*>(planar);
+  constexpr int kPlanes = (kOpGroup * kOpPlanePitch + 127) / 128 * 128;
+  // RGB bytes of a ring slot -> byte planes, one quad (4 pixels, 3 words) per thread-step
+  auto convert = [&](const uint8_t* sb, uint8_t* dst) {
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(sb);
+    uint32_t* p32 = reinterpret_cast<uint32_t*>(dst);
 #pragma unroll
-      for (int task = tid; task < kOpGroup * 256; task += kOpThreads) {
-        const int img = task >> 8, q = task & 255;
-        const uint32_t* w = s32 + img * 768 + q * 3;
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-        uint32_t* d = p32 + img * (kOpPlanePitch / 4) + q;
-        d[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);     // bytes 0, 3, 6, 9
-        d[256] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);   // bytes 1, 4, 7, 10
-        d[512] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);   // bytes 2, 5, 8, 11
-      }
+    for (int task = tid; task < kOpGroup * 256; task += kOpThreads) {
+      const int img = task >> 8, q = task & 255;
+      const uint32_t* w = s32 + img * 768 + q * 3;
+      const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+      uint32_t* d = p32 + img * (kOpPlanePitch / 4) + q;
+      d[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);     // bytes 0, 3, 6, 9
+      d[256] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);   // bytes 1, 4, 7, 10
+      d[512] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);   // bytes 2, 5, 8, 11
     }
-    __syncthreads();   // planes complete; everybody is done with the previous group's slot and partials
-    if (metrics && it > 0) flush_metrics(it - 1, g - stride);
+  };
+  int it = 0, slot = 0, prev_slot = 0;
+  uint32_t phase = 0;
+  int64_t g = first;
+  if (g < ngroups) {
+    mbar_wait(&full[0], 0u);
+    convert(slots, planar);
+  }
+  __syncthreads();
+  for (; g < ngroups; ++it, g += stride) {
+    uint8_t* sb = slots + (size_t)slot * kOpGroupBytes;
+    int nslot = slot + 1;
+    uint32_t nphase = phase;
+    if (nslot == ring) { nslot = 0; nphase ^= 1u; }
 
-    const uint8_t* pl = planar + gid * kOpPlanePitch;
+    const uint8_t* pl = planar + (it & 1) * kPlanes + gid * kOpPlanePitch;
 #pragma unroll
     for (int tl = 0; tl < 4; ++tl) {
       const int tile = warp * 4 + tl;
@@ -496,7 +503,7 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
 #pragma unroll
       for (int s2 = 0; s2 < 3; ++s2) {
         if (s2 < ns) {
-          const int2 qo = qt[(tile * 3 + s2) * 4 + tig];
+          const int2 qo = qt[(tile * 3 + s2) * 4 + tig];   // quad index * 4
 #pragma unroll
           for (int ch = 0; ch < 3; ++ch) {
             b[s2][ch][0] = *reinterpret_cast<const uint32_t*>(pl + ch * 1024 + qo.x);
@@ -519,28 +526,40 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
         }
       }
       // rows gid and gid + 8 are the pixel pair (x, x + 1): six contiguous bytes per image, images 2 tig and 2 tig + 1
-      const int p = ((tile >> 3) * 4 + (gid >> 1)) * 32 + (tile & 7) * 4 + (gid & 1) * 2;
+      // the weights of a row sum to 2^16 at most: the result is byte 1 of the accumulator, no saturation needed
+      const int p = meta[tile * 4 + 2] + (gid >> 1) * 32 + (gid & 1) * 2;
       uint8_t* o = sb + (2 * tig) * kOpImg + p * 3;
 #pragma unroll
       for (int im = 0; im < 2; ++im) {
-        const uint32_t wa = sat_pack4(acc[0][im] >> 8, acc[1][im] >> 8, acc[2][im] >> 8, acc[0][2 + im] >> 8);
-        const uint32_t wb = sat_pack4(acc[1][2 + im] >> 8, acc[2][2 + im] >> 8, 0, 0);
         uint16_t* o16 = reinterpret_cast<uint16_t*>(o + im * kOpImg);
-        o16[0] = (uint16_t)wa;
-        o16[1] = (uint16_t)(wa >> 16);
-        o16[2] = (uint16_t)wb;
+        o16[0] = (uint16_t)__byte_perm(acc[0][im], acc[1][im], 0x0051);
+        o16[1] = (uint16_t)__byte_perm(acc[2][im], acc[0][2 + im], 0x0051);
+        o16[2] = (uint16_t)__byte_perm(acc[1][2 + im], acc[2][2 + im], 0x0051);
       }
     }
+    if (g + stride < ngroups) {   // the next group's planes, while slower warps are still on this group's tiles
+      mbar_wait(&full[nslot], nphase);
+      convert(slots + (size_t)nslot * kOpGroupBytes, planar + ((it + 1) & 1) * kPlanes);
+    }
     fence_async_smem();
-    __syncthreads();   // the slot holds the group's output
+    __syncthreads();   // the slot holds the group's output, the other plane buffer the next group's input
+    if (metrics && it > 0) flush_metrics(it - 1, g - stride);
     if (metrics) {     // two warps per image
-      const uint32_t* o32 = reinterpret_cast<const uint32_t*>(sb) + (warp >> 1) * 768;
-      uint32_t c0 = 0, c1 = 0;
+      // lane owns words [12 l, 12 l + 12) of its half image: byte weights 1..48 fit a dp4a operand (team_pipeline.cuh)
+      const int w0i = (warp & 1) * 384 + lane * 12;
+      const uint4* o128 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(sb) + (warp >> 1) * 768 + w0i);
+      uint32_t c0 = 0, c1 = 0, cw = 0;
 #pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        const uint32_t i = (uint32_t)((warp & 1) * 384 + j * 32 + lane);
-        checksum_word(o32[i], i, c0, c1);
+      for (int q = 0; q < 3; ++q) {
+        const uint4 v = o128[q];
+        const uint32_t wv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          c0 = __dp4a(wv[e], 0x01010101u, c0);
+          cw = __dp4a(wv[e], 0x04030201u + (uint32_t)(q * 4 + e) * 0x04040404u, cw);
+        }
       }
+      c1 = cw + 4u * (uint32_t)w0i * c0;
       c0 = __reduce_add_sync(0xffffffffu, c0);
       c1 = __reduce_add_sync(0xffffffffu, c1);
       if (lane == 0) msum[(it & 1) * 16 + warp] = make_uint2(c0, c1);
@@ -552,12 +571,14 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
         bulk_wait_read<1>();   // the store of the previous iteration has finished reading its slot: refill it
         const int64_t gn = g + (int64_t)(ring - 1) * stride;
         if (gn < ngroups) {
-          const int ps = (it - 1) % ring;
-          mbar_expect_tx(&full[ps], group_bytes(gn));
-          bulk_g2s(slots + (size_t)ps * kOpGroupBytes, in + gn * kOpGroupBytes, group_bytes(gn), &full[ps]);
+          mbar_expect_tx(&full[prev_slot], group_bytes(gn));
+          bulk_g2s(slots + (size_t)prev_slot * kOpGroupBytes, in + gn * kOpGroupBytes, group_bytes(gn), &full[prev_slot]);
         }
       }
     }
+    prev_slot = slot;
+    slot = nslot;
+    phase = nphase;
   }
   __syncthreads();
   if (metrics && it > 0) flush_metrics(it - 1, g - stride);
@@ -580,9 +601,9 @@ int op32_mma(const uint8_t* in, uint8_t* out, int64_t n, const int32_t* tables, 
   tb.lo = reinterpret_cast<const uint4*>(tables + off_lo);
   tb.hi = reinterpret_cast<const uint4*>(tables + off_hi);
   tb.total_steps = total_steps;
-  const size_t base = kOpFixed + (size_t)total_steps * 512 + align_up((size_t)kOpGroup * kOpPlanePitch, 128);
+  const size_t base = kOpFixed + (size_t)total_steps * 512 + 2 * align_up((size_t)kOpGroup * kOpPlanePitch, 128);
   const int ring = (int)std::min<size_t>(6, ((size_t)max_smem_optin() - base) / kOpGroupBytes);
-  IMGTX_CHECK_ARG(ring >= 2, "operator tables too large for shared memory");
+  IMGTX_CHECK_ARG(ring >= 3, "operator tables too large for shared memory");
   const size_t smem = base + (size_t)ring * kOpGroupBytes;
   IMGTX_CUDA_OK(cudaFuncSetAttribute(op32_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t ngroups = (n + kOpGroup - 1) / kOpGroup;
