@@ -260,9 +260,31 @@ def op32_mma_tables(indptr, cols, weights):
         ns = (len(quads) + 7) // 8
         if ns > 3 or ns < 1:
             return None
+        # Slot order.  The kernel's byte planes have a row pitch of 10 words and an image pitch = 4 (mod 32) words, so the bank
+        # of a B-fragment load is 4 * image + 2 * row + column (mod 32): a half-step (the 4 quads the lanes tig = 0..3 load
+        # together, for 8 images) is conflict-free iff its quads differ in (2 * row + column) mod 4.  Deal the quads to the
+        # half-steps accordingly; padding slots take one of the quads 0..3 (row 0) with a residue the half-step lacks.
+        G = 2 * ns
+        members, used = [[] for _ in range(G)], [set() for _ in range(G)]
+        res = ((quads >> 3) * 2 + (quads & 7)) % 4
+        for r in sorted(range(4), key=lambda r: -int((res == r).sum())):
+            for qd in quads[res == r]:
+                free = [g_ for g_ in range(G) if len(members[g_]) < 4]
+                good = [g_ for g_ in free if r not in used[g_]]
+                g_ = min(good or free, key=lambda g_: len(members[g_]))
+                members[g_].append(int(qd))
+                used[g_].add(r)
         qpos = np.full(256, -1, np.int64)
-        qpos[quads] = np.arange(len(quads))
-        qpad = np.concatenate([quads, np.zeros(ns * 8 - len(quads), np.int64)])
+        qpad = np.zeros(ns * 8, np.int64)
+        for g_ in range(G):
+            for j, qd in enumerate(members[g_]):
+                qpos[qd] = g_ * 4 + j
+                qpad[g_ * 4 + j] = qd
+            for j in range(len(members[g_]), 4):
+                lack = [r for r in range(4) if r not in used[g_]]
+                r = lack[0] if lack else 0
+                used[g_].add(r)
+                qpad[g_ * 4 + j] = r          # a zero-weight column: any readable quad does
         W = np.zeros((16, 96), np.int64)
         rb = np.full(16, 32, np.int64)       # rounding bias per row: 2^-11 LSB, so an exactly integral sum floors to itself
         for r, q in enumerate(pix):
@@ -278,8 +300,9 @@ def op32_mma_tables(indptr, cols, weights):
         meta[t, 0], meta[t, 1], meta[t, 2] = ns, len(lo_steps), (blk // 8) * 128 + (blk % 8) * 4
         bias[t] = (rb[:8] | (rb[8:] << 16)).astype(np.uint32)
         for sidx in range(ns):
-            qtab[t, sidx, :, 0] = qpad[sidx * 8 + np.arange(4)] * 4
-            qtab[t, sidx, :, 1] = qpad[sidx * 8 + 4 + np.arange(4)] * 4
+            qa, qb = qpad[sidx * 8 + np.arange(4)], qpad[sidx * 8 + 4 + np.arange(4)]
+            qtab[t, sidx, :, 0] = ((qa >> 3) * 10 + (qa & 7)) * 4      # byte offset in a plane of row pitch 10 words
+            qtab[t, sidx, :, 1] = ((qb >> 3) * 10 + (qb & 7)) * 4
             fr = np.zeros((2, 32, 4), np.uint32)
             for reg in range(4):
                 row = gid + (reg & 1) * 8

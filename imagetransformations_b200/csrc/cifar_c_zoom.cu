@@ -386,8 +386,9 @@ int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz
 //     of the Q16 weights, low and high byte limb; per row a rounding bias.  Q16 rounded to nearest with the row sum kept at
 //     2^16: flat regions are exact, the result differs from the real-valued sum by < 0.01 LSB before the floor.
 //   * A CTA (16 warps) works on a GROUP of 8 consecutive images (24 576 contiguous bytes: one bulk TMA load into a ring slot,
-//     one bulk store from the same slot).  The group is de-interleaved once into byte planes (8 images x 3 channels, image
-//     pitch 3088 B so the eight images of a B-fragment load fall into different banks); a B fragment is then two 32-bit
+//     one bulk store from the same slot).  The group is de-interleaved once into byte planes (8 images x 3 channels, row
+//     pitch 10 words, image pitch = 4 mod 32 words: bank = 4 image + 2 row + column, and the host orders the quads of a step
+//     so that the four a load touches differ in 2 row + column mod 4 -> conflict-free); a B fragment is then two 32-bit
 //     shared-memory loads at (image = lane / 4, quad = table[lane % 4]).  The planes are double-buffered: group i+1 is
 //     de-interleaved by the warps as they finish group i, so there is ONE CTA barrier per group.
 //   * Warp w owns tiles 4w .. 4w+3 for the whole launch: the high-limb A fragments stay in 48 REGISTERS, the low-limb ones in
@@ -396,7 +397,9 @@ int zoom_levels(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int nz
 constexpr int kOpGroup = 8;
 constexpr int kOpImg = 3072;
 constexpr int kOpGroupBytes = kOpGroup * kOpImg;
-constexpr int kOpPlanePitch = kOpImg + 16;   // three byte planes per image
+constexpr int kOpRowWords = 10;                               // plane row pitch: 8 quads + 2 (bank spread, see op32_mma_tables)
+constexpr int kOpPlane = 32 * kOpRowWords * 4;                 // one channel plane
+constexpr int kOpPlanePitch = 3 * kOpPlane + 16;               // image pitch = 4 (mod 32) words
 constexpr int kOpThreads = 512;
 constexpr int kOpFixed = 384 + 6144 + 2048 + 1024;   // barriers + metric partials | quad table | row biases | tile meta
 
@@ -467,10 +470,10 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
       const int img = task >> 8, q = task & 255;
       const uint32_t* w = s32 + img * 768 + q * 3;
       const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
-      uint32_t* d = p32 + img * (kOpPlanePitch / 4) + q;
-      d[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);     // bytes 0, 3, 6, 9
-      d[256] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);   // bytes 1, 4, 7, 10
-      d[512] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);   // bytes 2, 5, 8, 11
+      uint32_t* d = p32 + img * (kOpPlanePitch / 4) + (q >> 3) * kOpRowWords + (q & 7);
+      d[0] = __byte_perm(__byte_perm(w0, w1, 0x6630), w2, 0x5210);                  // bytes 0, 3, 6, 9
+      d[kOpPlane / 4] = __byte_perm(__byte_perm(w0, w1, 0x7741), w2, 0x6210);       // bytes 1, 4, 7, 10
+      d[2 * kOpPlane / 4] = __byte_perm(__byte_perm(w0, w1, 0x5552), w2, 0x7410);   // bytes 2, 5, 8, 11
     }
   };
   int it = 0, slot = 0, prev_slot = 0;
@@ -506,8 +509,8 @@ op32_mma_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64
           const int2 qo = qt[(tile * 3 + s2) * 4 + tig];   // quad index * 4
 #pragma unroll
           for (int ch = 0; ch < 3; ++ch) {
-            b[s2][ch][0] = *reinterpret_cast<const uint32_t*>(pl + ch * 1024 + qo.x);
-            b[s2][ch][1] = *reinterpret_cast<const uint32_t*>(pl + ch * 1024 + qo.y);
+            b[s2][ch][0] = *reinterpret_cast<const uint32_t*>(pl + ch * kOpPlane + qo.x);
+            b[s2][ch][1] = *reinterpret_cast<const uint32_t*>(pl + ch * kOpPlane + qo.y);
           }
           const uint4 a = alo[(ab + s2) * 32 + lane];
 #pragma unroll
