@@ -306,8 +306,15 @@ def run_ours(args, rank, world, local_rank):
     n_groups = len(passes) // n_sev
     gbuf = torch.zeros((n_groups, world, n_sev, N_IMAGES, 2), dtype=torch.int32, device=dev)
     mviews = [gbuf[k // n_sev, rank, k % n_sev] for k in range(len(passes))]
+    pbuf = None
+    if os.environ.get("IMGTX_BENCH_GATHER", "group") == "pass":   # (pass, rank, image, 2): one gather per pass
+        pbuf = torch.zeros((len(passes), world, N_IMAGES, 2), dtype=torch.int32, device=dev)
+        mviews = [pbuf[k, rank] for k in range(len(passes))]
     side = torch.cuda.Stream()
     group_graphs = None
+
+    gdone = [None] * n_groups   # the all-gather of a type's metrics, issued by the previous step, has finished
+    per_pass_gather = os.environ.get("IMGTX_BENCH_GATHER", "group") == "pass"   # development knob: 75 small gathers per step
 
     def gather_group(g):
         done = torch.cuda.Event()
@@ -315,15 +322,32 @@ def run_ours(args, rank, world, local_rank):
         with torch.cuda.stream(side):
             side.wait_event(done)
             dist.all_gather_into_tensor(gbuf[g].view(-1), gbuf[g, rank].view(-1))
+            gdone[g] = torch.cuda.Event()
+            gdone[g].record()
 
     def step(seed):
+        # the gathers run on the side stream behind the passes; a type's kernels only wait for the gather that read their
+        # metric slice in the PREVIOUS step, so the last gather of a step overlaps the first passes of the next one
         for k, (name, sev) in enumerate(passes):
+            if world > 1 and k % n_sev == 0 and gdone[k // n_sev] is not None:
+                torch.cuda.current_stream().wait_event(gdone[k // n_sev])
             if group_graphs is None:
                 C.corrupt(x, name, sev, seed=seed * 1000 + k, out=outs[k & 1], metrics=mviews[k])
             elif k % n_sev == 0:
                 group_graphs[k // n_sev].replay()
-            if world > 1 and k % n_sev == n_sev - 1:
+            if world > 1 and per_pass_gather and group_graphs is None:
+                done = torch.cuda.Event()
+                done.record()
+                with torch.cuda.stream(side):
+                    side.wait_event(done)
+                    dist.all_gather_into_tensor(pbuf[k].view(-1), pbuf[k, rank].view(-1))
+                    if k % n_sev == n_sev - 1:
+                        gdone[k // n_sev] = torch.cuda.Event()
+                        gdone[k // n_sev].record()
+            elif world > 1 and k % n_sev == n_sev - 1:
                 gather_group(k // n_sev)
+
+    def drain():
         if world > 1:
             torch.cuda.current_stream().wait_stream(side)
 
@@ -376,6 +400,7 @@ def run_ours(args, rank, world, local_rank):
             graph.replay()
         else:
             step(100 + i)
+    drain()            # every gather of the K steps is inside the timed region
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
