@@ -612,15 +612,15 @@ def suite_passes(corruptions=None, severities=(1, 2, 3, 4, 5)):
 
 
 def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5), seed: int = 0, out=None, sink=None,
-                   mode: Optional[str] = None, metrics: Optional[torch.Tensor] = None, graph: bool = False):
+                   mode: Optional[str] = None, metrics: Optional[torch.Tensor] = None, graph: bool = False, lanes: int = 1):
     """Run every (corruption, severity) pass over the device-resident batch x.  Each pass is one kernel launch.  `out`:
     optional (len(passes), n, h, w, 3) uint8 CUDA tensor receiving every pass; otherwise `sink(name, severity, tensor)` is
     called per pass with a reused buffer (e.g. to checksum or stage to the host).  `metrics`: optional (len(passes), n, 2)
     int32 tensor receiving the per-image metric of every pass.  graph=True returns a SuiteGraph: the whole step captured once
     in a CUDA graph and replayed with one host call (the seeds are kernel arguments, so a replay re-draws the same noise;
-    capture again for new seeds)."""
+    capture again for new seeds); lanes: see SuiteGraph."""
     if graph:
-        return SuiteGraph(x, corruptions, severities, seed, out, mode, metrics)
+        return SuiteGraph(x, corruptions, severities, seed, out, mode, metrics, lanes)
     passes = suite_passes(corruptions, severities)
     buf = None if out is not None else torch.empty_like(x)
     for k, (name, sev) in enumerate(passes):
@@ -633,26 +633,47 @@ def generate_suite(x: torch.Tensor, corruptions=None, severities=(1, 2, 3, 4, 5)
 
 class SuiteGraph:
     """The 75-pass step as one CUDA graph.  The first (eager) run fills the host-side table caches and device-side constant
-    tables; the capture then records only kernel launches (the library allocates nothing and never synchronises)."""
+    tables; the capture then records only kernel launches (the library allocates nothing and never synchronises).
 
-    def __init__(self, x, corruptions=None, severities=(1, 2, 3, 4, 5), seed=0, out=None, mode=None, metrics=None):
+    lanes > 1: the passes read the same batch and write their own outputs, so nothing orders them but the output buffers.
+    Pass k is captured on stream k % lanes (and writes out[k % len(out)], len(out) a multiple of lanes, so two lanes never
+    share a buffer): the graph becomes `lanes` independent chains and a kernel's tail — its last, partly idle wave of CTAs
+    and the launch gap behind it — is filled by the other chain's next kernel."""
+
+    def __init__(self, x, corruptions=None, severities=(1, 2, 3, 4, 5), seed=0, out=None, mode=None, metrics=None, lanes=1):
         self.passes = suite_passes(corruptions, severities)
         self.x = x
-        self.out = out if out is not None else [torch.empty_like(x) for _ in range(2)]
+        self.lanes = max(1, int(lanes))
+        self.out = out if out is not None else [torch.empty_like(x) for _ in range(2 * ((self.lanes + 1) // 2))]
+        if self.lanes > 1 and not isinstance(self.out, torch.Tensor) and len(self.out) % self.lanes:
+            raise ValueError("SuiteGraph: the number of rotating output buffers must be a multiple of lanes")
         self.metrics = metrics
         self._args = (seed, mode)
         self._run()                       # warm: caches, cudaFuncSetAttribute
         torch.cuda.synchronize()
+        self._side = [torch.cuda.Stream() for _ in range(self.lanes - 1)]
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self._run()
+            self._run(self._side)
 
-    def _run(self):
+    def _run(self, side=()):
         seed, mode = self._args
+        main = torch.cuda.current_stream()
+        streams = [main] + list(side)
+        if side:
+            fork = torch.cuda.Event()
+            fork.record(main)
+            for st in side:
+                st.wait_event(fork)
         for k, (name, sev) in enumerate(self.passes):
-            dst = self.out[k] if isinstance(self.out, torch.Tensor) else self.out[k & 1]
-            corrupt(self.x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode,
-                    metrics=None if self.metrics is None else self.metrics[k])
+            dst = self.out[k] if isinstance(self.out, torch.Tensor) else self.out[k % len(self.out)]
+            with torch.cuda.stream(streams[k % len(streams)]):
+                corrupt(self.x, name, sev, seed=seed * 1000 + k, out=dst, mode=mode,
+                        metrics=None if self.metrics is None else self.metrics[k])
+        for st in side:
+            join = torch.cuda.Event()
+            join.record(st)
+            main.wait_event(join)
 
     def replay(self):
         self.graph.replay()

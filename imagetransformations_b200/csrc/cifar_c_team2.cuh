@@ -183,7 +183,7 @@ struct OpTGlass {
   using Params = GlassTeamParams;
   static constexpr int kTeamWarps = 4, kInBufs = 3, kOutBufs = 0, kMaxTeams = 4, kCtasPerSm = 2, kMinBlocks = 2;
   static size_t cta_scratch(const Shape&, const Params&) { return 256; }
-  static size_t team_scratch(const Shape&, const Params&) { return 3072 + 3072 + 4 * 2048; }
+  static size_t team_scratch(const Shape&, const Params&) { return 3072 + 3072 + 4 * 2048 + 256; }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
     // lw == 0: x -> uint8(g*255) -> uint8(clip(g')*255) with g = (x/255*w0)*w0 evaluated as the exact mode does
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -237,18 +237,89 @@ struct OpTGlass {
       }
     }
   }
+  // On-chip draws, TWO images per warp.  In the skew-2 wavefront row r is busy during steps [2r, 2r + 30), so at most 15 rows
+  // of an image are in flight at any step: 15 lanes per image are all the parallelism there is.  Lanes 0-14 sweep image `img0`
+  // and lanes 16-30 image `img0 + stride`; lane l takes row l during steps [2l, 2l + 30) and row l + 15 during
+  // [2l + 30, 2l + 60) (row 15 starts two steps after row 14, as the skew wants), 88 steps in all as before.  The loop body
+  // is branch-free: a lane that has not started or has finished swaps inside a small dummy region.  Three phases of the
+  // step counter have one kind of event each (start / switch to the second row / finish), so a step costs one compare and
+  // three selects on top of the swap.  Same draws as `sweep` (one Philox call per image, iteration and row; column ci uses
+  // bit ci of words x and y), hence the same maps.  About 17 instructions per step for two images instead of 25 for one.
+  __device__ static __forceinline__ void swap_step(uint32_t& a, uint32_t& X, uint32_t& Y) {
+    const uint32_t b = a - (X & 2u) - (Y & 64u);
+    uint16_t ta, tb;
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(ta) : "r"(a) : "memory");
+    asm volatile("ld.shared.u16 %0, [%1];" : "=h"(tb) : "r"(b) : "memory");
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(a), "h"(tb) : "memory");
+    asm volatile("st.shared.u16 [%0], %1;" ::"r"(b), "h"(ta) : "memory");
+    a -= 2u;
+    X >>= 1;
+    Y = __funnelshift_r(Y, Y, 1);
+    __syncwarp();
+  }
+  __device__ static void sweep_pair(uint16_t* maps, uint16_t* dummy, int64_t img0, int64_t stride, const Params& p, int lane) {
+    const int half = lane >> 4, l = lane & 15;
+    const int64_t img = img0 + half * stride;
+    uint16_t* m = maps + half * 1024;
+    for (int i = l; i < 128; i += 16) {   // identity map, eight entries per store
+      const uint32_t w0 = (uint32_t)(8 * i) * 0x00010001u + 0x00010000u;
+      reinterpret_cast<uint4*>(m)[i] = make_uint4(w0, w0 + 0x00020002u, w0 + 0x00040004u, w0 + 0x00060006u);
+    }
+    __syncwarp();
+    const bool valid = img < p.n && l < 15;
+    const uint32_t dm = (uint32_t)__cvta_generic_to_shared(dummy + 100);
+    const uint32_t row1 = (uint32_t)__cvta_generic_to_shared(m + (31 - l) * 32 + 31), row2 = row1 - 15u * 64u;
+    const int first = valid ? 2 * l : 1000;
+    const Philox rng(p.seed);
+    for (int it = 0; it < p.iters; ++it) {
+      uint32_t X1 = 0, Y1 = 0, X2 = 0, Y2 = 0;
+      if (valid) {
+        const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)l);
+        const uint4 r2 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)(l + 15));
+        // X: bit ci at position 1 after ci shifts (byte offset 2 = one entry); Y: bit ci at position 6 after ci rotations
+        // (byte offset 64 = one map row)
+        X1 = (r1.x & 0x3FFFFFFFu) << 1; Y1 = __funnelshift_l(r1.y & 0x3FFFFFFFu, r1.y & 0x3FFFFFFFu, 6);
+        X2 = (r2.x & 0x3FFFFFFFu) << 1; Y2 = __funnelshift_l(r2.y & 0x3FFFFFFFu, r2.y & 0x3FFFFFFFu, 6);
+      }
+      uint32_t a = dm, X = 0, Y = 0;
+#pragma unroll 6
+      for (int t = 0; t < 30; ++t) {
+        const bool ev = t == first;
+        a = ev ? row1 : a; X = ev ? X1 : X; Y = ev ? Y1 : Y;
+        swap_step(a, X, Y);
+      }
+#pragma unroll 6
+      for (int t = 30; t < 60; ++t) {
+        const bool ev = t == first + 30;
+        a = ev ? row2 : a; X = ev ? X2 : X; Y = ev ? Y2 : Y;
+        swap_step(a, X, Y);
+      }
+#pragma unroll 7
+      for (int t = 60; t < 88; ++t) {
+        const bool ev = t == first + 60;
+        a = ev ? dm : a;   // X has run out; whatever Y holds keeps the partner inside the dummy region
+        swap_step(a, X, Y);
+      }
+    }
+  }
   __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
                              const uint8_t* cta, int tt, int team) {
     uint8_t* B1 = scr;
     uint8_t* B2 = scr + 3072;
     uint16_t* maps = reinterpret_cast<uint16_t*>(scr + 6144);    // four index maps: this image and the team's next three
+    uint16_t* dummy = maps + 4 * 1024;                           // 128 entries where idle lanes of sweep_pair swap
     const int lane = tt & 31, wq = tt >> 5;
-    // the sweep is a latency chain that keeps one warp busy, so every fourth image of the team all four warps sweep at once:
-    // warp q makes the map of the team's image it + q (the maps depend on the image index and the seed only)
+    // the sweep is a latency chain, so the maps of the team's next four images are made together every fourth image (they
+    // depend on the image index and the seed only): on-chip draws, warps 0 and 1 sweep two images each; injected deltas,
+    // warp q makes the map of the team's image it + q
     const int64_t teams_per_cta = blockDim.x >> 7, stride = (int64_t)gridDim.x * teams_per_cta;
     const int it = (int)((img - ((int64_t)blockIdx.x * teams_per_cta + team)) / stride);
     if ((it & 3) == 0) {
-      if (img + wq * stride < p.n) sweep(maps + wq * 1024, img + wq * stride, p, lane);
+      if (p.deltas) {
+        if (img + wq * stride < p.n) sweep(maps + wq * 1024, img + wq * stride, p, lane);
+      } else if (wq < 2) {
+        sweep_pair(maps + 2 * wq * 1024, dummy, img + 2 * wq * stride, stride, p, lane);
+      }
       team_sync<4>(team);
     }
     const uint16_t* m = maps + (it & 3) * 1024;

@@ -693,7 +693,9 @@ struct ElasticFastParams {
 template <bool WARP_ONLY>
 struct OpTElastic : ElasticCommon {
   using Params = ElasticFastParams;
-  static constexpr int kTeamWarps = 8, kInBufs = 3, kOutBufs = 0, kMaxTeams = 2, kCtasPerSm = 2, kMinBlocks = 2;
+  // the affine-only form (alpha = 0, CIFAR severity 1) is a latency chain per image (one thread inverts the matrix, 64 build
+  // cv2's tables, then four rows per lane): four-warp teams, twice as many of them, hide it twice as well
+  static constexpr int kTeamWarps = WARP_ONLY ? 4 : 8, kInBufs = 3, kOutBufs = 0, kMaxTeams = WARP_ONLY ? 4 : 2, kCtasPerSm = 2, kMinBlocks = 2;
   static constexpr int kTT = kTeamWarps * 32;
   static constexpr int kPA = 40;            // pitch (halves) of the fp16 operator / field rows: conflict-free fragment loads
   static constexpr int kLutLo = 64, kLut = 160;   // index tables cover [-64, 96)
@@ -821,7 +823,7 @@ struct OpTElastic : ElasticCommon {
       const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
       uint2* c2 = reinterpret_cast<uint2*>(canvas);
       for (int q = tt; q < 256; q += kTT) quad_to_half4(s32[3 * q], s32[3 * q + 1], s32[3 * q + 2], c2 + 4 * q + (q >> 2));
-      team_sync<8>(team);
+      team_sync<kTeamWarps>(team);
       if (tt < 64) affine_tables(Mi, 32, 32, tab, tt);
     }
     if (!WARP_ONLY) {
@@ -851,7 +853,7 @@ struct OpTElastic : ElasticCommon {
         }
       }
     }
-    if (!WARP_ONLY) team_sync<8>(team);
+    if (!WARP_ONLY) team_sync<kTeamWarps>(team);
     // ---- three things at once: warps 0-3 smooth the fields on the tensor cores, warp 4 inverts the matrix and builds cv2's
     // coordinate tables (float64, one lane then 64 entries), warps 5-7 expand the staged image into the fp16 canvas ----
     if (!WARP_ONLY && wq == 4) {
@@ -917,7 +919,7 @@ struct OpTElastic : ElasticCommon {
         *reinterpret_cast<float2*>(D + 8 * nt + 8 * kPD) = make_float2(__fmul_rn(c2[nt][2], p.alpha), __fmul_rn(c2[nt][3], p.alpha));
       }
     }
-    team_sync<8>(team);   // displacements, tables and canvas are ready
+    team_sync<kTeamWarps>(team);   // displacements, tables and canvas are ready
     // ---- affine warp (cv2.warpAffine coordinates), thread = column `lane`, rows wq, wq + 4, ... ----
     const int* lrow = lut + kLutLo;
     const int* lcol = lut + kLut + kLutLo;
@@ -953,7 +955,7 @@ struct OpTElastic : ElasticCommon {
       }
     }
     if (WARP_ONLY) return;
-    team_sync<8>(team);
+    team_sync<kTeamWarps>(team);
     // ---- bilinear remap at (y + dy, x + dx), scipy 'reflect' ----
     const int* hrow = lut + 2 * kLut;   // biased by kLutLo: index = floor(coordinate + 64)
     const int* hcol = lut + 3 * kLut;

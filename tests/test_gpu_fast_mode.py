@@ -114,3 +114,37 @@ def test_fast_impulse_law(cuda):
     b = C.corrupt(xd[:64], "impulse_noise", 3, seed=1, mode="fast")
     c = C.corrupt(xd[:64], "impulse_noise", 3, seed=2, mode="fast")
     assert torch.equal(a, b) and not torch.equal(a, c)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 1237, 4096 + 5])
+def test_glass_paired_sweep_makes_the_maps_of_the_exact_mode(cuda, n):
+    """The throughput form sweeps two images per warp (lanes 0-14 / 16-30, two rows per lane); the exact mode sweeps the pixels
+    themselves, one image per warp.  Same seed => same swaps, so every byte must be within 1 LSB (a wrong map moves bytes by
+    tens of levels), for batch sizes that leave half-filled pairs and idle sweep warps at the end of the batch."""
+    C = _C()
+    x = np.random.default_rng(n).integers(0, 256, (n, 32, 32, 3), dtype=np.uint8)
+    x[:, ::2] //= 3                      # rows of different brightness: a misplaced pixel is visible after the blur
+    xd = torch.from_numpy(x).cuda()
+    for sev in (1, 2, 4, 5):
+        fast = C.corrupt(xd, "glass_blur", sev, seed=77, mode="fast").cpu().numpy().astype(np.int16)
+        exact = C.corrupt(xd, "glass_blur", sev, seed=77, mode="exact").cpu().numpy().astype(np.int16)
+        assert np.abs(fast - exact).max() <= 1, (n, sev, int(np.abs(fast - exact).max()))
+
+
+def test_suite_graph_lanes_equal_eager_passes(cuda):
+    """SuiteGraph with one or two independent chains of passes writes the same bytes and metrics as the eager passes."""
+    C = _C()
+    x = torch.from_numpy(np.random.default_rng(8).integers(0, 256, (600, 32, 32, 3), dtype=np.uint8)).cuda()
+    names = ["contrast", "glass_blur", "zoom_blur", "elastic_transform", "shot_noise"]
+    passes = C.suite_passes(names, (1, 3, 5))
+    want = torch.empty((len(passes),) + tuple(x.shape), dtype=torch.uint8, device="cuda")
+    wm = torch.zeros((len(passes), len(x), 2), dtype=torch.int32, device="cuda")
+    C.generate_suite(x, names, (1, 3, 5), seed=4, out=want, metrics=wm)
+    for lanes in (1, 2):
+        got = torch.zeros_like(want)
+        gm = torch.zeros_like(wm)
+        g = C.generate_suite(x, names, (1, 3, 5), seed=4, out=got, metrics=gm, graph=True, lanes=lanes)
+        got.zero_(); gm.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(got, want) and torch.equal(gm, wm), lanes
