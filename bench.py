@@ -299,60 +299,48 @@ def run_ours(args, rank, world, local_rank):
 
     host = torch.from_numpy(np.random.default_rng(1001 + rank).integers(0, 256, (N_IMAGES, H, W, 3), dtype=np.uint8)).pin_memory()
     x = host.to(dev)
-    outs = [torch.empty_like(x) for _ in range(2)]  # alternate: 2 x 153.6 MB, with x 460 MB > 126 MB of L2
-    # per-pass metric buffers: this rank's kernels write their slice, NCCL all-gathers in place.  Layout
-    # (type, rank, severity, image, 2): the five severities of a type are one contiguous slice per rank = one all-gather
-    n_sev = 5
-    n_groups = len(passes) // n_sev
-    gbuf = torch.zeros((n_groups, world, n_sev, N_IMAGES, 2), dtype=torch.int32, device=dev)
-    mviews = [gbuf[k // n_sev, rank, k % n_sev] for k in range(len(passes))]
-    pbuf = None
-    if os.environ.get("IMGTX_BENCH_GATHER", "group") == "pass":   # (pass, rank, image, 2): one gather per pass
-        pbuf = torch.zeros((len(passes), world, N_IMAGES, 2), dtype=torch.int32, device=dev)
-        mviews = [pbuf[k, rank] for k in range(len(passes))]
+    # The 75 passes read the same batch and write their own outputs and metric slices, so nothing orders them: the step is
+    # captured as ONE CUDA graph of `lanes` independent chains of passes (pass k on chain k % lanes, writing out[k % 2]), and
+    # a kernel's tail -- its last, partly idle wave of CTAs and the launch gap behind it -- is filled by the other chain.
+    lanes = max(1, int(os.environ.get("IMGTX_BENCH_LANES", "2")))
+    outs = [torch.empty_like(x) for _ in range(2 if lanes <= 2 else lanes)]  # rotate: 2 x 153.6 MB, with x 460 MB > 126 MB of L2
+    # Per-pass metrics: this rank's kernels write their slice of a (rank, pass, image, 2) buffer from their epilogue, and ONE
+    # NCCL all-gather per step fills in every other rank's slices in place.  Two buffers at N > 1: the gather of
+    # step i runs on a side stream under the passes of step i + 1, which write the other buffer.
+    n_buf = 2 if world > 1 else 1
+    gbufs = [torch.zeros((world, len(passes), N_IMAGES, 2), dtype=torch.int32, device=dev) for _ in range(n_buf)]
+    mviews_b = [[gb[rank, k] for k in range(len(passes))] for gb in gbufs]
+    mviews = mviews_b[0]
     side = torch.cuda.Stream()
-    group_graphs = None
+    graphs = None
+    gdone = [None] * n_buf     # the gather that read buffer b has finished
 
-    gdone = [None] * n_groups   # the all-gather of a type's metrics, issued by the previous step, has finished
-    per_pass_gather = os.environ.get("IMGTX_BENCH_GATHER", "group") == "pass"   # development knob: 75 small gathers per step
-
-    def gather_group(g):
+    def gather(b):
         done = torch.cuda.Event()
         done.record()
         with torch.cuda.stream(side):
             side.wait_event(done)
-            dist.all_gather_into_tensor(gbuf[g].view(-1), gbuf[g, rank].view(-1))
-            gdone[g] = torch.cuda.Event()
-            gdone[g].record()
+            dist.all_gather_into_tensor(gbufs[b].view(-1), gbufs[b][rank].view(-1))
+            gdone[b] = torch.cuda.Event()
+            gdone[b].record()
 
-    def step(seed):
-        # the gathers run on the side stream behind the passes; a type's kernels only wait for the gather that read their
-        # metric slice in the PREVIOUS step, so the last gather of a step overlaps the first passes of the next one
-        for k, (name, sev) in enumerate(passes):
-            if world > 1 and k % n_sev == 0 and gdone[k // n_sev] is not None:
-                torch.cuda.current_stream().wait_event(gdone[k // n_sev])
-            if group_graphs is None:
-                C.corrupt(x, name, sev, seed=seed * 1000 + k, out=outs[k & 1], metrics=mviews[k])
-            elif k % n_sev == 0:
-                group_graphs[k // n_sev].replay()
-            if world > 1 and per_pass_gather and group_graphs is None:
-                done = torch.cuda.Event()
-                done.record()
-                with torch.cuda.stream(side):
-                    side.wait_event(done)
-                    dist.all_gather_into_tensor(pbuf[k].view(-1), pbuf[k, rank].view(-1))
-                    if k % n_sev == n_sev - 1:
-                        gdone[k // n_sev] = torch.cuda.Event()
-                        gdone[k // n_sev].record()
-            elif world > 1 and k % n_sev == n_sev - 1:
-                gather_group(k // n_sev)
+    def step(i):
+        b = i % n_buf
+        if world > 1 and gdone[b] is not None:
+            torch.cuda.current_stream().wait_event(gdone[b])   # the passes overwrite the slices that gather was reading
+        if graphs is not None:
+            graphs[b].replay()
+        else:
+            for k, (name, sev) in enumerate(passes):
+                C.corrupt(x, name, sev, seed=i * 1000 + k, out=outs[k % len(outs)], metrics=mviews_b[b][k])
+        if world > 1:
+            gather(b)
 
     def drain():
         if world > 1:
             torch.cuda.current_stream().wait_stream(side)
 
     warm = max(args.warmup, 3)
-    t_host0 = time.perf_counter()
     for i in range(warm):
         step(i)
     host_us_per_launch = None
@@ -363,31 +351,16 @@ def run_ours(args, rank, world, local_rank):
     host_us_per_launch = (time.perf_counter() - t0) * 1e6 / launches_per_step
     barrier()
 
-    graph = None
-    if world == 1 and not args.no_graph:
+    if not args.no_graph:
         try:
-            graph = C.generate_suite(x, seed=100, out=outs, metrics=mviews, graph=True)
-            graph.replay()
+            gg = [C.generate_suite(x, seed=100 + b, out=outs, metrics=mviews_b[b], graph=True, lanes=lanes) for b in range(n_buf)]
             torch.cuda.synchronize()
-        except Exception as e:   # capture is an optimisation of the launch path, never a requirement
-            graph = None
-            sys.stderr.write(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches\n")
-    elif world > 1 and not args.no_graph:
-        # N > 1: the five passes of a type are one graph (compute only), the NCCL all-gather of their metrics follows eagerly
-        # on the side stream: 15 graph launches + 15 collectives per step instead of 75 + 75 host calls
-        try:
-            names = []
-            for name, _ in passes:
-                if name not in names:
-                    names.append(name)
-            gg = [C.generate_suite(x, corruptions=[nm], seed=100 + gi, out=outs, metrics=mviews[gi * n_sev:(gi + 1) * n_sev],
-                                   graph=True) for gi, nm in enumerate(names)]
-            torch.cuda.synchronize()
-            group_graphs = gg
-            step(0)
+            graphs = gg
+            for i in range(n_buf):
+                step(i)
             barrier()
-        except Exception as e:
-            group_graphs = None
+        except Exception as e:   # capture is an optimisation of the launch path, never a requirement
+            graphs = None
             sys.stderr.write(f"[bench] CUDA graph capture unavailable ({type(e).__name__}: {e}); timing eager launches\n")
 
     sampler = ClockSampler(local_rank)
@@ -396,24 +369,23 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     e0.record()
     for i in range(args.steps):
-        if graph is not None:
-            graph.replay()
-        else:
-            step(100 + i)
+        step(100 + i)
     drain()            # every gather of the K steps is inside the timed region
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
+    timed_graph = graphs is not None
     clocks = sampler.stop()
     ms_per_step = ms / args.steps
     value = world * len(passes) * N_IMAGES / (ms_per_step * 1e-3)
 
     # the gathered metrics are real: every rank now holds every rank's words for every pass
-    metrics_ok = bool((gbuf[:, rank].abs().sum() > 0).item()) and all(bool((gbuf[:, r].abs().sum() > 0).item()) for r in range(world))
+    metrics_ok = all(bool((gb[r].abs().sum() > 0).item()) for gb in gbufs for r in range(world))
     if world > 1:
-        ref = gbuf[3].clone()
-        dist.broadcast(ref, 0)
-        metrics_ok = metrics_ok and bool(torch.equal(ref, gbuf[3]))
+        for gb in gbufs:
+            ref = gb[:, 15:20].clone()
+            dist.broadcast(ref, 0)
+            metrics_ok = metrics_ok and bool(torch.equal(ref, gb[:, 15:20]))
 
     # ---- per-pass timing (CUDA events on the launching stream) -> dominant kernel + roofline ----
     per_pass = {}
@@ -505,7 +477,7 @@ def run_ours(args, rank, world, local_rank):
 
     configs = None
     if not args.no_configs:
-        del outs, gbuf
+        del outs, gbufs, mviews_b, mviews, graphs
         torch.cuda.empty_cache()
         configs = bench_configs(dev, rank, world, peak, barrier, max_over_ranks, want_cpu=(rank == 0 and world == 1 and not args.no_cpu))
 
@@ -521,11 +493,10 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": CONFIG,
             "details": {"severity_table": "cifar", "rng": "on-chip Philox4x32-10", "mode": "fast (<= 1 LSB from the exact mode)",
                         "l2": "working set 461 MB (input + 2 rotating outputs) > 126 MB L2",
-                        "timed_with": ("CUDA graph replay" if graph is not None else
-                                       "one CUDA graph per corruption type (5 passes) + eager NCCL" if group_graphs is not None
+                        "timed_with": (f"CUDA graph replay, {lanes} independent chain(s) of passes per graph" if timed_graph
                                        else "eager launches"),
-                        "collective": ("NCCL all_gather_into_tensor of the per-image metrics of the 5 severities of a type "
-                                       "(4 MB per rank), 15 per step, side stream"
+                        "collective": ("one NCCL all_gather_into_tensor per step of the per-image metrics of its 75 passes "
+                                       "(30 MB per rank), on a side stream under the next step's passes (two metric buffers)"
                                        if world > 1 else "none at N=1 (metrics still written by every pass)"),
                         "metrics_gathered_ok": metrics_ok},
             "suite_algorithmic_gbs": suite_gbs, "suite_frac_of_hbm_peak": suite_gbs / peak,

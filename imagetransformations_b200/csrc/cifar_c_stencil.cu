@@ -1534,6 +1534,8 @@ static int impl_cc_glass_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, i
     GlassTeamParams f;
     memset(&f, 0, sizeof(f));
     f.lw = lw; f.iters = iters; f.deltas = deltas_dev; f.seed = seed; f.w0 = p.w[0]; f.n = n;
+    static const int kSweeper = getenv("IMGTX_GLASS_SWEEPER") ? atoi(getenv("IMGTX_GLASS_SWEEPER")) : 1;   // tuning, read once
+    f.sweeper = kSweeper;
     const double inside = (p.w[0] + 2.0 * p.w[1]) * (p.w[0] + 2.0 * p.w[1]);   // the 3x3 part, renormalised to sum to 1
     f.k.k00 = (float)(p.w[0] * p.w[0] / inside); f.k.k01 = f.k.k10 = (float)(p.w[0] * p.w[1] / inside);
     f.k.k11 = (float)(p.w[1] * p.w[1] / inside);

@@ -177,6 +177,7 @@ struct GlassTeamParams {
   const int8_t* deltas;      // device (n, iters, 30, 30, 2) or nullptr (on-chip draws)
   uint64_t seed;
   int64_t n;                 // images in the batch (maps are made ahead: never past the end)
+  int sweeper;               // on-chip draws: 1 = warp 3 of a team only sweeps (see OpTGlass::run), 0 = grouped sweeps
 };
 
 struct OpTGlass {
@@ -257,13 +258,17 @@ struct OpTGlass {
     Y = __funnelshift_r(Y, Y, 1);
     __syncwarp();
   }
-  __device__ static void sweep_pair(uint16_t* maps, uint16_t* dummy, int64_t img0, int64_t stride, const Params& p, int lane) {
+  __device__ static void sweep_pair(uint16_t* maps, uint16_t* dummy, int64_t img0, int64_t stride, const Params& p, int lane,
+                                    int it_lo, int it_hi, bool init) {
+    if (img0 >= p.n) return;
     const int half = lane >> 4, l = lane & 15;
     const int64_t img = img0 + half * stride;
     uint16_t* m = maps + half * 1024;
-    for (int i = l; i < 128; i += 16) {   // identity map, eight entries per store
-      const uint32_t w0 = (uint32_t)(8 * i) * 0x00010001u + 0x00010000u;
-      reinterpret_cast<uint4*>(m)[i] = make_uint4(w0, w0 + 0x00020002u, w0 + 0x00040004u, w0 + 0x00060006u);
+    if (init) {
+      for (int i = l; i < 128; i += 16) {   // identity map, eight entries per store
+        const uint32_t w0 = (uint32_t)(8 * i) * 0x00010001u + 0x00010000u;
+        reinterpret_cast<uint4*>(m)[i] = make_uint4(w0, w0 + 0x00020002u, w0 + 0x00040004u, w0 + 0x00060006u);
+      }
     }
     __syncwarp();
     const bool valid = img < p.n && l < 15;
@@ -271,7 +276,7 @@ struct OpTGlass {
     const uint32_t row1 = (uint32_t)__cvta_generic_to_shared(m + (31 - l) * 32 + 31), row2 = row1 - 15u * 64u;
     const int first = valid ? 2 * l : 1000;
     const Philox rng(p.seed);
-    for (int it = 0; it < p.iters; ++it) {
+    for (int it = it_lo; it < it_hi; ++it) {
       uint32_t X1 = 0, Y1 = 0, X2 = 0, Y2 = 0;
       if (valid) {
         const uint4 r1 = rng((uint32_t)img, (uint32_t)(img >> 32), 0x40u + it, (uint32_t)l);
@@ -309,29 +314,54 @@ struct OpTGlass {
     uint16_t* maps = reinterpret_cast<uint16_t*>(scr + 6144);    // four index maps: this image and the team's next three
     uint16_t* dummy = maps + 4 * 1024;                           // 128 entries where idle lanes of sweep_pair swap
     const int lane = tt & 31, wq = tt >> 5;
-    // the sweep is a latency chain, so the maps of the team's next four images are made together every fourth image (they
-    // depend on the image index and the seed only): on-chip draws, warps 0 and 1 sweep two images each; injected deltas,
-    // warp q makes the map of the team's image it + q
+    // The sweep is a latency chain (88 dependent steps per iteration) that does not look at the pixels: the map of an image
+    // depends on its index and the seed only, so maps are made ahead of the images in a ring of four.
+    //   injected deltas      every fourth image warp q makes the map of the team's image it + q
+    //   on-chip, grouped     every fourth image warps 0 and 1 sweep two images each (sweep_pair), warps 2 and 3 wait
+    //   on-chip, sweeper     warp 3 only sweeps: while warps 0-2 run the two Gaussians and the gather of images it, it + 1 (their
+    //                        own 96-thread barrier), it makes the maps of images it + 2, it + 3 — half of the iterations during
+    //                        each of the two images — and meets the others at the end-of-image barrier of the pipeline
     const int64_t teams_per_cta = blockDim.x >> 7, stride = (int64_t)gridDim.x * teams_per_cta;
-    const int it = (int)((img - ((int64_t)blockIdx.x * teams_per_cta + team)) / stride);
-    if ((it & 3) == 0) {
-      if (p.deltas) {
+    const int64_t done = img - ((int64_t)blockIdx.x * teams_per_cta + team);
+    const int it = (uint64_t)p.n >> 31 ? (int)(done / stride) : (int)((uint32_t)done / (uint32_t)stride);
+    int nt = 128;
+    if (p.deltas) {
+      if ((it & 3) == 0) {
         if (img + wq * stride < p.n) sweep(maps + wq * 1024, img + wq * stride, p, lane);
-      } else if (wq < 2) {
-        sweep_pair(maps + 2 * wq * 1024, dummy, img + 2 * wq * stride, stride, p, lane);
+        team_sync<4>(team);
       }
-      team_sync<4>(team);
+    } else if (!p.sweeper) {
+      if ((it & 3) == 0) {
+        if (wq < 2) sweep_pair(maps + 2 * wq * 1024, dummy, img + 2 * wq * stride, stride, p, lane, 0, p.iters, true);
+        team_sync<4>(team);
+      }
+    } else {
+      const int h = (p.iters + 1) >> 1;
+      if (it == 0) {
+        if (wq == 3) sweep_pair(maps, dummy, img, stride, p, lane, 0, p.iters, true);
+        team_sync<4>(team);
+      }
+      if (wq == 3) {
+        if ((it & 1) == 0) sweep_pair(maps + ((it + 2) & 3) * 1024, dummy, img + 2 * stride, stride, p, lane, 0, h, true);
+        else sweep_pair(maps + ((it + 1) & 3) * 1024, dummy, img + stride, stride, p, lane, h, p.iters, false);
+        return;
+      }
+      nt = 96;
     }
+    auto csync = [&]() {   // the threads that compute this image
+      if (nt == 128) team_sync<4>(team);
+      else asm volatile("bar.sync %0, 96;" ::"r"(team + 9) : "memory");
+    };
     const uint16_t* m = maps + (it & 3) * 1024;
     if (p.lw > 0) {
       if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(B1), tt % 24, (tt / 24) * 8, p.k);
-      team_sync<4>(team);
+      csync();
     }
     // ---- apply the map: four pixels per thread ----
     {
       const uint8_t* from = p.lw > 0 ? B1 : src;
       uint32_t* o = reinterpret_cast<uint32_t*>(B2);
-      for (int q = tt; q < 256; q += 128) {
+      for (int q = tt; q < 256; q += nt) {
         uint32_t px[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -343,13 +373,13 @@ struct OpTGlass {
         o[3 * q] = a; o[3 * q + 1] = b; o[3 * q + 2] = c;
       }
     }
-    team_sync<4>(team);
+    csync();
     if (p.lw > 0) {
       if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(B2), reinterpret_cast<uint32_t*>(dst), tt % 24, (tt / 24) * 8, p.k);
     } else {
       const uint32_t* f = reinterpret_cast<const uint32_t*>(B2);
       uint32_t* o = reinterpret_cast<uint32_t*>(dst);
-      for (int i = tt; i < 768; i += 128) o[i] = f[i];
+      for (int i = tt; i < 768; i += nt) o[i] = f[i];
     }
   }
 };
