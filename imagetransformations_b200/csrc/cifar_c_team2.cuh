@@ -184,7 +184,7 @@ struct OpTGlass {
   using Params = GlassTeamParams;
   static constexpr int kTeamWarps = 4, kInBufs = 3, kOutBufs = 0, kMaxTeams = 4, kCtasPerSm = 2, kMinBlocks = 2;
   static size_t cta_scratch(const Shape&, const Params&) { return 256; }
-  static size_t team_scratch(const Shape&, const Params&) { return 3072 + 3072 + 4 * 2048 + 256; }
+  static size_t team_scratch(const Shape&, const Params&) { return 3072 + 3072 + 4 * 2052 + 256 + 16; }
   __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
     // lw == 0: x -> uint8(g*255) -> uint8(clip(g')*255) with g = (x/255*w0)*w0 evaluated as the exact mode does
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -263,12 +263,9 @@ struct OpTGlass {
     if (img0 >= p.n) return;
     const int half = lane >> 4, l = lane & 15;
     const int64_t img = img0 + half * stride;
-    uint16_t* m = maps + half * 1024;
+    uint16_t* m = maps + half * 1026;   // the next ring slot (map_slot): one word past 2 KB, so the two halves use disjoint banks
     if (init) {
-      for (int i = l; i < 128; i += 16) {   // identity map, eight entries per store
-        const uint32_t w0 = (uint32_t)(8 * i) * 0x00010001u + 0x00010000u;
-        reinterpret_cast<uint4*>(m)[i] = make_uint4(w0, w0 + 0x00020002u, w0 + 0x00040004u, w0 + 0x00060006u);
-      }
+      for (int i = l; i < 512; i += 16) reinterpret_cast<uint32_t*>(m)[i] = (uint32_t)(2 * i) * 0x00010001u + 0x00010000u;   // identity
     }
     __syncwarp();
     const bool valid = img < p.n && l < 15;
@@ -307,12 +304,15 @@ struct OpTGlass {
       }
     }
   }
+  // ring slot s of the index maps; the slot pitch is 1024 entries + one 4-byte word, so that the lanes of the two images of a
+  // sweep_pair (slots 2k, 2k + 1) fall into disjoint shared-memory banks (lane l: bank 15 l + const, resp. + 1)
+  __device__ static __forceinline__ uint16_t* map_slot(uint16_t* maps, int s) { return maps + s * 1026; }
   __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape&, const Params& p, uint8_t* scr,
                              const uint8_t* cta, int tt, int team) {
     uint8_t* B1 = scr;
     uint8_t* B2 = scr + 3072;
     uint16_t* maps = reinterpret_cast<uint16_t*>(scr + 6144);    // four index maps: this image and the team's next three
-    uint16_t* dummy = maps + 4 * 1024;                           // 128 entries where idle lanes of sweep_pair swap
+    uint16_t* dummy = maps + 4 * 1026 + 8;                       // 128 entries where idle lanes of sweep_pair swap
     const int lane = tt & 31, wq = tt >> 5;
     // The sweep is a latency chain (88 dependent steps per iteration) that does not look at the pixels: the map of an image
     // depends on its index and the seed only, so maps are made ahead of the images in a ring of four.
@@ -327,34 +327,37 @@ struct OpTGlass {
     int nt = 128;
     if (p.deltas) {
       if ((it & 3) == 0) {
-        if (img + wq * stride < p.n) sweep(maps + wq * 1024, img + wq * stride, p, lane);
+        if (img + wq * stride < p.n) sweep(map_slot(maps, wq), img + wq * stride, p, lane);
         team_sync<4>(team);
       }
     } else if (!p.sweeper) {
       if ((it & 3) == 0) {
-        if (wq < 2) sweep_pair(maps + 2 * wq * 1024, dummy, img + 2 * wq * stride, stride, p, lane, 0, p.iters, true);
+        if (wq < 2) sweep_pair(map_slot(maps, 2 * wq), dummy, img + 2 * wq * stride, stride, p, lane, 0, p.iters, true);
         team_sync<4>(team);
       }
     } else {
-      const int h = (p.iters + 1) >> 1;
+      // the warps of a team sit on the four schedulers of the SM in order, so the sweeper is warp (team mod 4): every
+      // scheduler gets one latency-bound sweeper per four teams instead of one scheduler getting all of them
+      const int h = (p.iters + 1) >> 1, sw = team & 3;
       if (it == 0) {
-        if (wq == 3) sweep_pair(maps, dummy, img, stride, p, lane, 0, p.iters, true);
+        if (wq == sw) sweep_pair(maps, dummy, img, stride, p, lane, 0, p.iters, true);
         team_sync<4>(team);
       }
-      if (wq == 3) {
-        if ((it & 1) == 0) sweep_pair(maps + ((it + 2) & 3) * 1024, dummy, img + 2 * stride, stride, p, lane, 0, h, true);
-        else sweep_pair(maps + ((it + 1) & 3) * 1024, dummy, img + stride, stride, p, lane, h, p.iters, false);
+      if (wq == sw) {
+        if ((it & 1) == 0) sweep_pair(map_slot(maps, (it + 2) & 3), dummy, img + 2 * stride, stride, p, lane, 0, h, true);
+        else sweep_pair(map_slot(maps, (it + 1) & 3), dummy, img + stride, stride, p, lane, h, p.iters, false);
         return;
       }
       nt = 96;
+      if (wq > sw) tt -= 32;   // the 96 computing threads, numbered 0..95
     }
     auto csync = [&]() {   // the threads that compute this image
       if (nt == 128) team_sync<4>(team);
       else asm volatile("bar.sync %0, 96;" ::"r"(team + 9) : "memory");
     };
-    const uint16_t* m = maps + (it & 3) * 1024;
+    const uint16_t* m = map_slot(maps, it & 3);
     if (p.lw > 0) {
-      if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(B1), tt % 24, (tt / 24) * 8, p.k);
+      if (tt < 96) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(src), reinterpret_cast<uint32_t*>(B1), tt % 24, (tt / 24) * 8, p.k);
       csync();
     }
     // ---- apply the map: four pixels per thread ----
@@ -375,7 +378,7 @@ struct OpTGlass {
     }
     csync();
     if (p.lw > 0) {
-      if (wq < 3) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(B2), reinterpret_cast<uint32_t*>(dst), tt % 24, (tt / 24) * 8, p.k);
+      if (tt < 96) sym3x3_segment<1>(reinterpret_cast<const uint32_t*>(B2), reinterpret_cast<uint32_t*>(dst), tt % 24, (tt / 24) * 8, p.k);
     } else {
       const uint32_t* f = reinterpret_cast<const uint32_t*>(B2);
       uint32_t* o = reinterpret_cast<uint32_t*>(dst);
