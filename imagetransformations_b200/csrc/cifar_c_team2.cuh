@@ -470,8 +470,9 @@ struct OpTSnow {
         acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[yb + xa], ty), ux));
         acc = __fadd_rn(acc, __fmul_rn(__fmul_rn(L0[yb + xb], ty), tx));
         if (acc < p.thresh) acc = 0.0f;
-        acc = acc < 0.0f ? 0.0f : (acc > 1.0f ? 1.0f : acc);
-        cv[(p.pad_top + y) * 32 + lane] = (float)__float2int_rz(__fmul_rn(acc, 255.0f));
+        acc = fminf(fmaxf(acc, 0.0f), 1.0f);   // (a NaN draw becomes 0, as the float -> int conversion made it)
+        // trunc(255 acc) as a float, 0 <= 255 acc <= 255: floor by a round-down add of 2^23 (no F2I / I2F: 16 lanes/clk)
+        cv[(p.pad_top + y) * 32 + lane] = __fsub_rn(__fadd_rd(__fmul_rn(acc, 255.0f), 8388608.0f), 8388608.0f);
       }
     }
     team_sync<2>(team);
