@@ -40,6 +40,8 @@ CC_GAUSSIAN, CC_SHOT, CC_IMPULSE, CC_SPECKLE, CC_BRIGHTNESS, CC_CONTRAST, CC_FOG
  VIEW_FLIP_CROP_REFLECT, VIEW_RESIZE_CENTER_CROP) = range(8)
 AUG_NONE, AUG_GEOM, AUG_POSTERIZE, AUG_SOLARIZE, AUG_EQUALIZE = range(5)
 CC_FAST, CC_REPLAY_ALL = 1, 2   # `flags` of the imgtx_cc_* entry points
+CC_SHOT_FLAT = 0x101             # table layout selector of the on-chip shot_noise (include/imgtx.h)
+ERR_UNSUPPORTED = -3
 
 _vp = C.c_void_p
 _i64 = C.c_int64

@@ -489,6 +489,15 @@ def _corrupt(x, name, severity, draws, seed, table, out, frost_bank, mode, metri
     # back to the caching allocator before the next one is staged
     if name in ("gaussian_noise", "shot_noise") and not d and (h * w * c) % 16 == 0:
         kind = L.CC_GAUSSIAN if name == "gaussian_noise" else L.CC_SHOT
+        if kind == L.CC_SHOT and h * w * c <= 16384:
+            # small images: the flat table (one shared-memory lookup per element); the library answers "unsupported" when
+            # the batch cannot be staged beside it (unaligned views) and the row-record table below takes over
+            flat = noise_alias_table(L.CC_SHOT_FLAT, float(p), dev)
+            if flat is not None:
+                rc = lib.imgtx_cc_noise_onchip_u8(xp, op, n, h, w, c, L.CC_SHOT_FLAT, flat.data_ptr(), flat.numel(), seed, flags, mp, st)
+                if rc != L.ERR_UNSUPPORTED:
+                    L.check(rc)
+                    return out
         tab = noise_alias_table(kind, float(p), dev)
         if tab is not None:
             L.check(lib.imgtx_cc_noise_onchip_u8(xp, op, n, h, w, c, kind, tab.data_ptr(), tab.numel(), seed, flags, mp, st))

@@ -25,6 +25,9 @@ namespace imgtx {
 //   out:     n_out bytes (padded to a word): shot only, outcome index -> output byte
 constexpr int kAliasHeaderWords = 8;
 constexpr uint32_t kAliasMagic = 0x31544C41u;
+// flat shot_noise table (IMGTX_CC_SHOT_FLAT): [0] magic 'ALT2'  [1] kind  [2] 256  [3] 256 K  [5] log2 K, then 256 rows of K
+// entries (threshold16 << 16) | (alias output byte << 8) | own output byte: slot kept iff (16 random bits) < threshold
+constexpr uint32_t kAliasMagicFlat = 0x32544C41u;
 
 struct AliasView {
   const uint2* rows;

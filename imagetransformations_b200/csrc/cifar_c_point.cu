@@ -609,7 +609,66 @@ bool build_shot(double c, AliasTable& t) {
   return true;
 }
 
+// shot_noise, flat layout (IMGTX_CC_SHOT_FLAT): the same rows, each padded with zero-probability outcomes to K slots
+bool build_shot_flat(double c, std::vector<uint32_t>& words) {
+  if (!(c > 0)) return false;
+  std::vector<std::vector<double>> prs(256);
+  std::vector<std::vector<uint8_t>> ovs(256);
+  size_t widest = 1;
+  for (int x = 0; x < 256; ++x) {
+    const double lam = (double)x / 255.0 * c;
+    std::vector<double>& pr = prs[x];
+    std::vector<uint8_t>& ov = ovs[x];
+    auto outv = [&](long long k) {
+      double v = (double)k / c;
+      v = v < 0.0 ? 0.0 : (v > 1.0 ? 1.0 : v);
+      return (uint8_t)(int)(v * 255.0);
+    };
+    if (lam <= 0) {
+      pr.push_back(1.0); ov.push_back(outv(0));
+    } else {
+      const double ll = log(lam);
+      auto pmf = [&](long long k) { return exp((double)k * ll - lam - lgamma((double)k + 1.0)); };
+      long long mode = (long long)floor(lam), klo = mode, khi = mode;
+      while (klo > 0 && pmf(klo - 1) > 1e-10) --klo;
+      while (pmf(khi + 1) > 1e-10) ++khi;
+      for (long long k = klo; k <= khi; ++k) {
+        const uint8_t o = outv(k);
+        if (!ov.empty() && ov.back() == o) pr.back() += pmf(k);
+        else { ov.push_back(o); pr.push_back(pmf(k)); }
+      }
+    }
+    widest = std::max(widest, pr.size());
+  }
+  int lg = 1;
+  while ((size_t)1 << lg < widest) ++lg;
+  if (lg > 7) return false;   // 256 x 128 words = 128 KB is the most that leaves room for the images
+  const int K = 1 << lg;
+  words.assign(kAliasHeaderWords, 0u);
+  words[0] = kAliasMagicFlat; words[1] = (uint32_t)IMGTX_CC_SHOT; words[2] = 256u; words[3] = 256u * (uint32_t)K; words[5] = (uint32_t)lg;
+  for (int x = 0; x < 256; ++x) {
+    std::vector<double> pr = prs[x];
+    pr.resize(K, 0.0);
+    std::vector<uint32_t> e;
+    vose(pr, e);   // (threshold23 << 9) | alias9
+    for (int i = 0; i < K; ++i) {
+      const uint32_t a = e[i] & 511u, t23 = e[i] >> 9;
+      uint32_t t16 = t23 >= 8388607u ? 65535u : (t23 + 64u) >> 7;     // own outcome iff (16 random bits) < t16
+      if (t16 > 65535u) t16 = 65535u;
+      const bool real = (size_t)i < ovs[x].size(), areal = (size_t)a < ovs[x].size();
+      // a padded slot has probability 0: its alias is a real outcome (vose pairs it with a large one) and t16 = 0
+      uint32_t own = real ? ovs[x][i] : (areal ? ovs[x][a] : ovs[x][0]);
+      uint32_t ali = areal ? ovs[x][a] : own;
+      if (a == (uint32_t)i) ali = own;                                  // "always keep"
+      if (!real) t16 = 0;
+      words.push_back((t16 << 16) | (ali << 8) | own);
+    }
+  }
+  return true;
+}
+
 bool build_table(int kind, double p0, std::vector<uint32_t>& words) {
+  if (kind == IMGTX_CC_SHOT_FLAT) return build_shot_flat(p0, words);
   AliasTable t;
   const bool ok = kind == IMGTX_CC_GAUSSIAN ? build_gaussian(p0, t) : (kind == IMGTX_CC_SHOT ? build_shot(p0, t) : false);
   if (!ok) return false;
@@ -649,9 +708,19 @@ static int impl_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, i
                                         uint32_t* metrics_dev, bool* metrics_done, imgtx_stream_t stream) {
   // (on-chip draws only: this entry point IS a throughput form; it runs on the team pipeline when the table fits beside it)
   IMGTX_CHECK_ARG(h > 0 && w > 0 && c == 3 && n >= 0, "CIFAR-C corruptions take (n,h,w,3) images");
-  IMGTX_CHECK_ARG(kind == IMGTX_CC_GAUSSIAN || kind == IMGTX_CC_SHOT, "alias-table noise is gaussian or shot");
+  IMGTX_CHECK_ARG(kind == IMGTX_CC_GAUSSIAN || kind == IMGTX_CC_SHOT || kind == IMGTX_CC_SHOT_FLAT, "alias-table noise is gaussian or shot");
   IMGTX_CHECK_ARG(table_dev != nullptr && table_words > kAliasHeaderWords && aligned16(table_dev), "bad alias table");
   const Shape shp = make_shape(h, w, c, h, w);
+  if (kind == IMGTX_CC_SHOT_FLAT) {
+    IMGTX_CHECK_ARG(table_words >= kAliasHeaderWords + 512 && ((table_words - kAliasHeaderWords) & (table_words - kAliasHeaderWords - 1)) == 0,
+                    "a flat shot table is 8 + 256 K words, K a power of two");
+    CcFastParams f;
+    memset(&f, 0, sizeof(f));
+    f.kind = IMGTX_CC_SHOT; f.b = table_dev; f.seed = seed; f.table_words = (int)table_words;
+    const int rc = launch_team_op<OpTShotFlat>(in, out, n, shp, f, (cudaStream_t)stream, metrics_dev);
+    if (rc == IMGTX_OK) *metrics_done = true;
+    return rc;   // IMGTX_ERR_UNSUPPORTED (no error string): the caller falls back to the IMGTX_CC_SHOT table
+  }
   IMGTX_CHECK_ARG(shp.in_bytes % 16 == 0 && aligned16(in) && aligned16(out),
                   "image bytes must be a multiple of 16 and the buffers 16-byte aligned");
   const size_t tbytes = (size_t)table_words * 4;

@@ -273,6 +273,52 @@ struct OpTNoiseAlias {
   }
 };
 
+// shot_noise with on-chip draws from the FLAT table (cifar_c_fast.cuh): one lookup per element.  The slot is the top log2 K
+// bits of the element's Philox word, the keep / alias decision its low 16 bits; the entry carries both output bytes.
+// Table in shared memory once per CTA (one CTA per SM: 64 KB at c = 60), two-warp teams beside it.
+struct OpTShotFlat {
+  using Params = CcFastParams;
+  static constexpr int kTeamWarps = 2, kInBufs = 3, kOutBufs = 0, kMaxTeams = 15, kCtasPerSm = 1, kMinBlocks = 1;
+  static size_t team_scratch(const Shape&, const Params&) { return 0; }
+  static size_t cta_scratch(const Shape&, const Params& p) { return (size_t)(p.table_words - kAliasHeaderWords) * 4 + 16; }
+  __device__ static void prepare(const Shape&, const Params& p, uint8_t* cta) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(p.b);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(cta);
+    const int ne = p.table_words - kAliasHeaderWords;
+    for (int i = threadIdx.x; i < ne; i += blockDim.x) dst[i] = __ldg(src + kAliasHeaderWords + i);
+    if (threadIdx.x == 0) dst[ne] = __ldg(src + 5);   // log2 K
+  }
+  __device__ static void run(const uint8_t* src, uint8_t* dst, int64_t img, const Shape& s, const Params& p, uint8_t*,
+                             const uint8_t* cta, int tt, int) {
+    const int ne = p.table_words - kAliasHeaderWords;
+    const uint32_t lg = reinterpret_cast<const uint32_t*>(cta)[ne];
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(cta);
+    const Philox rng(p.seed);
+    const int wpi = s.in_bytes >> 2;
+    const uint32_t* s32 = reinterpret_cast<const uint32_t*>(src);
+    uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
+    const uint64_t word0 = (uint64_t)img * (uint64_t)wpi;
+    const uint32_t rsh = 30u - lg, smask = ((1u << lg) - 1u) << 2, xsh = lg + 2u;   // byte offsets: (x << lg | slot) * 4
+    for (int i = tt; i < wpi; i += kTeamWarps * 32) {
+      const uint32_t w = s32[i];
+      const uint64_t gw = word0 + (uint64_t)i;
+      const uint4 r = rng((uint32_t)gw, (uint32_t)(gw >> 32), 0x21u, 0u);
+      const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+      uint32_t e[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t x = (w >> (8 * b)) & 255u;
+        const uint32_t a = tab + ((x << xsh) | ((rr[b] >> rsh) & smask));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(e[b]) : "r"(a));
+      }
+      uint32_t o[4];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) o[b] = (rr[b] & 0xFFFFu) < (e[b] >> 16) ? e[b] : (e[b] >> 8);
+      d32[i] = pack4(o[0], o[1], o[2], o[3]);
+    }
+  }
+};
+
 // ---------------------------------------------------------------------------------------------------------------
 // fog: per-image byte maximum, plasma map (diamond-square drawn on chip, or injected float64 maps read from HBM), then
 // q = x*S + plasma*C in float32 with S = m/(m + c0), C = 255*c0*S (m = max/255).  |error| < 2e-4 LSB.

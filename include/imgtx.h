@@ -290,6 +290,13 @@ int imgtx_cc_pointwise_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int
    rounded to 2^-23) by imgtx_cc_noise_table_host, uploaded by the caller and passed as table_dev (16-byte aligned).
    imgtx_cc_noise_table_words returns 0 when no table exists for the parameter (gaussian: 255*sigma > 39; shot: more than
    512 outcomes per input value); imgtx_cc_pointwise_u8 with NULL draws is the general (slower) on-chip path. */
+/* kind IMGTX_CC_SHOT_FLAT (both for the table calls and for imgtx_cc_noise_onchip_u8) selects the FLAT shot_noise table:
+   every row padded to the same power-of-two number K of slots, entry = threshold16 << 16 | alias output byte << 8 | own
+   output byte, so an element costs ONE shared-memory lookup at word (x << log2 K) + top bits of the Philox word (no row
+   record, no multiply, no output table) and the table is 256 K words (64 KB at c = 60).  Thresholds carry 16 bits: every
+   outcome probability is within 2^-17 of the exact law.  Small images only (they are staged per team beside the table):
+   IMGTX_ERR_UNSUPPORTED otherwise, and the caller uses the IMGTX_CC_SHOT table. */
+#define IMGTX_CC_SHOT_FLAT 0x101
 int64_t imgtx_cc_noise_table_words(int kind, double p0);
 int imgtx_cc_noise_table_host(int kind, double p0, int32_t* table_host, int64_t capacity_words);
 int imgtx_cc_noise_onchip_u8(const uint8_t* in, uint8_t* out, int64_t n, int h, int w, int c, int kind,

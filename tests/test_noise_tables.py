@@ -76,3 +76,34 @@ def test_shot_table_is_quantised_poisson(c):
 def test_no_table_outside_range():
     assert C.noise_alias_table_host(L.CC_GAUSSIAN, 0.38) is None     # 255*sigma = 97 > 39: general path
     assert C.noise_alias_table_host(L.CC_CONTRAST, 0.5) is None
+
+
+@pytest.mark.parametrize("c", list(CC.PARAMS["shot_noise"]) + [60, 12, 3])
+def test_flat_shot_table_is_the_same_law_to_16_bit_thresholds(c):
+    """IMGTX_CC_SHOT_FLAT: 256 rows of K = 2^lg slots, entry = threshold16 << 16 | alias byte << 8 | own byte.  Decoded, every
+    row must be the quantised Poisson law of the oracle formula to 2^-17 per outcome (the thresholds carry 16 bits), padded
+    slots must never be kept, and the table must be refused when a row needs more than 128 slots (c = 250)."""
+    tab = C.noise_alias_table_host(L.CC_SHOT_FLAT, c)
+    if c == 250:
+        assert tab is None
+        return
+    t = tab.view(np.uint32)
+    lg = int(t[5])
+    K = 1 << lg
+    assert t[0] == 0x32544C41 and t[2] == 256 and len(t) == 8 + 256 * K and 1 <= lg <= 7
+    e = t[8:].reshape(256, K)
+    for x in range(256):
+        thr = (e[x] >> 16).astype(np.float64) / 65536
+        ali, own = (e[x] >> 8) & 255, e[x] & 255
+        got = np.zeros(256)
+        np.add.at(got, own, thr / K)
+        np.add.at(got, ali, (1 - thr) / K)
+        lam = x / 255.0 * c
+        k = np.arange(0, int(lam + 12 * np.sqrt(lam + 1) + 30))
+        pk = stats.poisson.pmf(k, lam) if lam > 0 else (k == 0).astype(float)
+        o = CC.shot_noise(np.zeros((1, 1, 1, len(k)), np.uint8), k.reshape(1, 1, 1, -1), c).ravel().astype(int)
+        want = np.zeros(256)
+        np.add.at(want, o, pk)
+        assert abs(got.sum() - 1) < 1e-9
+        assert np.abs(got - want).max() < 2.0 ** -17, (c, x)
+        assert (got[want == 0] == 0).all(), (c, x)          # nothing outside the support (1e-10 tail cut aside)
