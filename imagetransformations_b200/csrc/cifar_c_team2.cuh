@@ -67,6 +67,7 @@ struct OpTMotion : NoTeamPrepare {
     }
     team_sync<kTeamWarps>(team);
     {
+      // (expanding the replicated rows straight from the source instead, to save this barrier, measured 7 % slower)
       uint4* c4 = reinterpret_cast<uint4*>(cv);
       for (int i = tt; i < 2 * p.padv * 16; i += kTT) {
         const int r = i >> 4, c = i & 15;
@@ -472,15 +473,12 @@ struct OpTSnow {
         if (acc < p.thresh) acc = 0.0f;
         acc = fminf(fmaxf(acc, 0.0f), 1.0f);   // (a NaN draw becomes 0, as the float -> int conversion made it)
         // trunc(255 acc) as a float, 0 <= 255 acc <= 255: floor by a round-down add of 2^23 (no F2I / I2F: 16 lanes/clk)
-        cv[(p.pad_top + y) * 32 + lane] = __fsub_rn(__fadd_rd(__fmul_rn(acc, 255.0f), 8388608.0f), 8388608.0f);
+        const float q8 = __fsub_rn(__fadd_rd(__fmul_rn(acc, 255.0f), 8388608.0f), 8388608.0f);
+        cv[(p.pad_top + y) * 32 + lane] = q8;
+        // the first and the last row are replicated above / below by the lanes that hold them (no extra pass, no barrier)
+        if (y == 0) for (int k = 0; k < p.pad_top; ++k) cv[k * 32 + lane] = q8;
+        if (y == 31) for (int k = 0; k < p.pad_bot; ++k) cv[(p.pad_top + 32 + k) * 32 + lane] = q8;
       }
-    }
-    team_sync<2>(team);
-    // replicated rows above / below
-    for (int i = tt; i < (p.pad_top + p.pad_bot) * 32; i += 64) {
-      const int r = i >> 5, c = i & 31;
-      const int drow = r < p.pad_top ? r : r + 32, srow = r < p.pad_top ? p.pad_top : p.pad_top + 31;
-      cv[drow * 32 + c] = cv[srow * 32 + c];
     }
     team_sync<2>(team);
     // C. line blur of the 8-bit layer, rounded back to 8 bits -> LB (aliases L0)
